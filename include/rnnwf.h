@@ -1,0 +1,142 @@
+/*
+ * rnnwf.h -- C-ABI of the B200-native RNN-wavefunction VMC hot path (librnnwf.so).
+ *
+ * The reference (mhibatallah/RNNWavefunctions) is pure Python on TensorFlow 1.13 graph mode and has no
+ * FFI/plugin layer of its own: its boundary for this path is the Python class / function API
+ *     RNNwavefunction(...).sample / .log_probability / .log_amplitude      (L1)
+ *     Ising_local_energies / J1J2Slices / Get_Elocs / Rydberg_local_energies   (L2)
+ *     optimizer.compute_gradients(cost)                                     (backward, via TF autodiff)
+ * Each entry point below names the reference interface it replaces (file:line under the reference root).
+ * The Python package `rnnwavefunctions_b200` mirrors those reference names one-to-one and calls these
+ * symbols through ctypes; INTEGRATION.md shows the stub a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - every pointer marked `dev` is a device pointer on the CUDA device current at the call; the caller
+ *     (PyTorch in our package) owns every buffer; the library owns only the opaque handle (step tables,
+ *     packed weights);
+ *   - all entry points are asynchronous on `stream` (a cudaStream_t passed as void*), allocate nothing
+ *     (create/destroy excepted) and return 0 on success or a negative RNNWF_E* code; the message of the
+ *     last error on the calling thread is returned by rnnwf_last_error();
+ *   - configurations are int8 occupation numbers in the reference's array layout:
+ *       1D [B, N];  2D [B, Nx, Ny];  Rydberg [B, Lx, Ly, 3];
+ *   - log-probabilities / phases are float64 (the reference returns float64 / complex128);
+ *     log psi = 0.5*logp + i*phase for the complex models.
+ *   - there is no CPU fallback: without a CUDA device every compute entry point fails with RNNWF_ECUDA.
+ */
+#ifndef RNNWF_H_
+#define RNNWF_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rnnwf_model* rnnwf_handle;
+
+/* cell families */
+enum {
+  RNNWF_CELL_GRU1D     = 0, /* stacked CudnnCompatibleGRUCell: 1DTFIM/RNNwavefunction.py:32, J1J2/ComplexRNNwavefunction.py:40 */
+  RNNWF_CELL_VANILLA2D = 1, /* 2DTFIM_2DRNN/MDRNNcell.py:51-66 */
+  RNNWF_CELL_TENS2D    = 2, /* 2DHeisenberg/MDTensorizedcell.py:40-49 */
+  RNNWF_CELL_TENSGRU2D = 3, /* 2DHeisenberg/MDTensorizedGRUcell.py:49-61 */
+  RNNWF_CELL_GRU4      = 4  /* RydbergKagome_2DGRU/MDGRUcell.py:48-59 (periodic, 4 neighbours, 8-way softmax) */
+};
+
+/* error codes */
+enum { RNNWF_OK = 0, RNNWF_EINVAL = -1, RNNWF_ECUDA = -2, RNNWF_ENOMEM = -3, RNNWF_ESTATE = -4 };
+
+typedef struct {
+  int32_t cell;          /* RNNWF_CELL_* */
+  int32_t complex_head;  /* 0: softmax head only (positive wavefunction); 1: + pi*softsign phase head */
+  int32_t nx, ny;        /* lattice; 1D chains: nx = N, ny = 1; Rydberg: unit cells Lx, Ly */
+  int32_t num_units;     /* hidden units per layer */
+  int32_t num_layers;    /* GRU1D only (MultiRNNCell depth); 1 otherwise */
+  int32_t u1;            /* 1: U(1) projection (J1J2/ComplexRNNwavefunction.py:85-93; 2DHeisenberg/MDComplexRNN.py:69-76) */
+  int32_t magnetization; /* 2*Sz target of the projection */
+  int32_t reserved[8];
+} rnnwf_config;
+
+const char* rnnwf_last_error(void);
+int rnnwf_version(void);
+
+/* Replaces the graph construction of RNNwavefunction.__init__ (1DTFIM/RNNwavefunction.py:8-33,
+ * J1J2/ComplexRNNwavefunction.py:16-43, 2DTFIM_2DRNN/RNNwavefunction.py, 2DHeisenberg/MDComplexRNN.py:28-65,
+ * RydbergKagome_2DGRU/MDRNNWavefunction.py:38-68): builds the lattice sweep tables on the current device. */
+int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out);
+int rnnwf_destroy(rnnwf_handle h);
+
+/* Parameter vector: one flat float32 array holding the TF variables in creation order and TF layout
+ * (SURVEY App. B).  rnnwf_param_info enumerates them (name without scope prefix, offset, shape). */
+int64_t rnnwf_count_params(const rnnwf_config* cfg); /* host-only: no device needed (notebook checks: 422 / 444 parameters) */
+int64_t rnnwf_num_params(rnnwf_handle h);
+int rnnwf_num_tensors(rnnwf_handle h);
+int rnnwf_param_info(rnnwf_handle h, int index, char* name, int name_cap, int64_t* offset, int32_t* ndim, int64_t shape[4]);
+
+/* Replaces sess.run(init) / saver.restore: (re)packs `params` (dev, float32[num_params]) into the
+ * kernels' weight layout.  Must be called after every parameter update. */
+int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream);
+
+/* Size of the scratch workspace (bytes) the sweep kernels need for batches of any size. */
+int64_t rnnwf_workspace_bytes(rnnwf_handle h);
+/* Size of the per-sample "saved state" (hidden-state history + gate activations + running sums)
+ * that sample()/logpsi() can record for `rows` configurations and backward()/eloc() consume. */
+int64_t rnnwf_saved_bytes(rnnwf_handle h, int64_t rows);
+
+/* wf.sample(numsamples, inputdim)  -- 1DTFIM/RNNwavefunction.py:35-74, J1J2/ComplexRNNwavefunction.py:45-103,
+ * 2DTFIM_2DRNN/RNNwavefunction.py:35-118, 2DHeisenberg/MDComplexRNN.py:80-173,
+ * RydbergKagome_2DGRU/MDRNNWavefunction.py:73-153.
+ * Inverse-CDF draws (TF CPU multinomial semantics) from `uniforms` (dev float32 [rows, nsteps], u[b,t] with
+ * t the generation-order step) or, when uniforms == NULL, from Philox4x32-10 keyed by `seed` with counter
+ * (row_offset + b, t).  Also returns log P and the phase of every sample (the forward pass the reference
+ * repeats in log_probability).  `saved` may be NULL. */
+int rnnwf_sample(rnnwf_handle h, int64_t rows, const float* uniforms_dev, uint64_t seed, uint64_t row_offset,
+                 int8_t* samples_dev, double* logp_dev, double* phase_dev, void* saved_dev,
+                 void* workspace_dev, int64_t workspace_bytes, void* stream);
+
+/* wf.log_probability / wf.log_amplitude(samples, inputdim) -- 1DTFIM/RNNwavefunction.py:76-118,
+ * J1J2/ComplexRNNwavefunction.py:105-169, 2DTFIM_2DRNN/RNNwavefunction.py:120-200,
+ * 2DHeisenberg/MDComplexRNN.py:177-286, RydbergKagome_2DGRU/MDRNNWavefunction.py:157-238. */
+int rnnwf_logpsi(rnnwf_handle h, int64_t rows, const int8_t* samples_dev, double* logp_dev, double* phase_dev,
+                 void* saved_dev, void* workspace_dev, int64_t workspace_bytes, void* stream);
+
+/* Local energies.  All of them: enumerate the connected configurations of every sample on the device,
+ * evaluate their log-amplitudes in one batched sweep and reduce E_loc in-kernel.
+ *   eloc_dev   : float64 [rows, 2] (re, im)  -- im == 0 for the positive wavefunctions
+ *   logp/phase : log psi of the samples themselves (from rnnwf_sample / rnnwf_logpsi)
+ *   nconn_dev  : optional int64 [1], number of configurations with non-zero matrix element evaluated
+ *   `saved`    : optional saved state of the samples -> connected configurations restart from the first
+ *                changed site (prefix reuse); NULL -> full sweeps.
+ * Hamiltonian parameter block `ham` (host pointer, float64):
+ *   RNNWF_HAM_TFIM1D  {Bx, Jz[0..N-2]}                 Ising_local_energies   1DTFIM/TrainingRNN_1DTFIM.py:13-75
+ *   RNNWF_HAM_TFIM2D  {Bx, Jz[nx*Ny+ny] ...}           Ising2D_local_energies 2DTFIM_2DRNN/Training2DRNN_2DTFIM.py:13-83
+ *   RNNWF_HAM_J1J2    {periodic, marshall, J1[N], J2[N], Bz[N]}  J1J2MatrixElements/J1J2Slices J1J2/TrainingRNN_J1J2.py:12-127,277-279
+ *   RNNWF_HAM_HEIS2D  {J2}                             Triangular2DHeis_* / Get_Elocs 2DHeisenberg/Helper_Functions.py:19-177
+ *   RNNWF_HAM_RYDBERG {V, delta, Omega, Rcutoff}       generate_kagome / neighbouring_atoms / Rydberg_local_energies
+ *                                                      RydbergKagome_2DGRU/Helping_Functions.py:33-153 */
+enum { RNNWF_HAM_TFIM1D = 0, RNNWF_HAM_TFIM2D = 1, RNNWF_HAM_J1J2 = 2, RNNWF_HAM_HEIS2D = 3, RNNWF_HAM_RYDBERG = 4 };
+int64_t rnnwf_eloc_workspace_bytes(rnnwf_handle h, int hamiltonian, int64_t rows);
+int rnnwf_local_energies(rnnwf_handle h, int hamiltonian, const double* ham, int ham_len,
+                         int64_t rows, const int8_t* samples_dev, const double* logp_dev, const double* phase_dev,
+                         const void* saved_dev, double* eloc_dev, int64_t* nconn_dev,
+                         void* workspace_dev, int64_t workspace_bytes, void* stream);
+
+/* Backward of log psi: grad[k] = sum_b seed_logp[b] * dlogP_b/dtheta_k + seed_phase[b] * dphase_b/dtheta_k,
+ * i.e. exactly what TF autodiff of the surrogate costs produces (1DTFIM/TrainingRNN_1DTFIM.py:157-161,
+ * J1J2/TrainingRNN_J1J2.py:197-200, 2DHeisenberg/Run_RNNWF_2DHeis.py:199-217,
+ * RydbergKagome_2DGRU/Run_RNNWF_Rydberg.py:158-176) once the caller has formed the seeds from E_loc
+ * (SURVEY 3.4).  `saved` must come from rnnwf_sample / rnnwf_logpsi on the same `samples` and weights.
+ * grad_dev: float32 [num_params] in the parameter layout (overwritten).  seed_phase may be NULL. */
+int64_t rnnwf_backward_workspace_bytes(rnnwf_handle h, int64_t rows);
+int rnnwf_backward(rnnwf_handle h, int64_t rows, const int8_t* samples_dev, const void* saved_dev,
+                   const double* seed_logp_dev, const double* seed_phase_dev, float* grad_dev,
+                   void* workspace_dev, int64_t workspace_bytes, void* stream);
+
+/* Kernel-regime report for the profiler notes: fills `buf` with a one-line description of the tile
+ * shape / pipe (FFMA or tcgen05) the handle's sweeps run in. */
+int rnnwf_describe(rnnwf_handle h, char* buf, int cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RNNWF_H_ */

@@ -1,0 +1,15 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU float64 restatement of mhibatallah/RNNWavefunctions' VMC hot path.
+
+Nothing under ``oracle/`` is part of the product: only ``tests/``, ``__graft_entry__.smoke()``
+and ``bench.py``'s ``cpu_baseline`` / ``--impl reference`` leg may import it, and only as the
+checker (or as the timed CPU baseline), never as the thing shipped.
+
+Parity status: the *network* part of the reference lives in TensorFlow 1.13.1 (not vendored, not
+installable here), and the reference ships no tests / golden vectors / weights, so network-level
+parity is **"parity unpinned"** by the reference itself.  What *is* pinned:
+  * the host-side NumPy local-energy code of the reference runs here unmodified; its outputs on
+    seeded inputs are committed under ``tests/golden/`` (``tests/golden/make_golden.py``) and the
+    restatements in ``oracle/local_energies.py`` are checked against them;
+  * parameter counts 422 / 444 (Tutorial notebooks) pin the GRU / Dense parameterisation;
+  * exact-diagonalisation energies pin the Hamiltonians end to end (brute-force <psi|H|psi>).
+"""

@@ -1,0 +1,73 @@
+// Host-side model description: lattice sweep tables, tile shape, parameter layout.
+#pragma once
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "../../include/rnnwf.h"
+
+namespace rnnwf {
+
+struct TensorInfo {
+  std::string name;
+  long long offset;
+  int ndim;
+  long long shape[4];
+  long long numel() const { long long n = 1; for (int i = 0; i < ndim; ++i) n *= shape[i]; return n; }
+};
+
+struct HostVariant {
+  VariantMeta meta;
+  int vkind;       // tensorized: 0 both, 1 horizontal only, 2 vertical only, 3 none; GRU1D: layer
+  int nsl;         // packed slots
+  int slot_of_rank[MAX_SLOTS];
+  long long w_float4;  // packed size of this variant (all column blocks)
+};
+
+struct Saved {   // byte offsets inside a caller-provided saved-state buffer for `rows` rows
+  long long off_hist, off_gates, off_cum, total;
+};
+
+struct rnnwf_model_impl {
+  rnnwf_config cfg;
+  int device;
+  int num_sms;
+  // derived
+  int cell, nh, nhp, ldH, nslots, D, ND, complex_head, u1, cap_up, cap_dn;
+  int Q, Tsym, symL, nsites, bits, cps;
+  int TJ, NTU, WC, Gblk, ncb, Gp, Greal, ncls_max, ring_len;
+  bool gru_type;   // cells whose backward needs saved gate activations
+  std::vector<StepMeta> steps;
+  std::vector<HostVariant> variants;
+  std::vector<int16_t> site_of_t, t_of_site;
+  std::vector<TensorInfo> tensors;
+  long long num_params;
+  long long wpack_float4, xtab_float4, bias_float4;
+  // device buffers owned by the handle
+  StepMeta* d_steps = nullptr;
+  VariantMeta* d_variants = nullptr;
+  int16_t* d_site_of_t = nullptr;
+  float4* d_wpack = nullptr;
+  float4* d_xtab = nullptr;
+  float4* d_bias = nullptr;
+  float* d_head_w = nullptr;
+  float* d_head_b = nullptr;
+  const float* d_params = nullptr;  // last parameter vector handed to set_weights (caller-owned)
+  bool weights_set = false;
+
+  const TensorInfo* tensor(const std::string& n) const {
+    for (auto& t : tensors) if (t.name == n) return &t;
+    return nullptr;
+  }
+  Saved saved_layout(long long rows) const {
+    auto al = [](long long x) { return (x + 255) & ~255LL; };
+    Saved s;
+    s.off_hist = 0;
+    s.off_gates = al((long long)Q * rows * nhp * 4);
+    s.off_cum = s.off_gates + al(gru_type ? (long long)Q * rows * Gp * 16 : 0);
+    s.total = s.off_cum + al((long long)Tsym * rows * 16);
+    return s;
+  }
+};
+
+}  // namespace rnnwf

@@ -1,0 +1,795 @@
+// librnnwf.so -- C-ABI entry points (see include/rnnwf.h) and host-side orchestration.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "model.h"
+#include "sweep.cuh"
+#include "pack.cuh"
+#include "eloc.cuh"
+#include "backward.cuh"
+
+using namespace rnnwf;
+
+struct rnnwf_model : rnnwf::rnnwf_model_impl {};
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) { g_err = msg; return code; }
+
+#define CUDA_TRY(expr)                                                                             \
+  do {                                                                                             \
+    cudaError_t e__ = (expr);                                                                      \
+    if (e__ != cudaSuccess)                                                                        \
+      return fail(RNNWF_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(e__));               \
+  } while (0)
+
+inline long long align256(long long x) { return (x + 255) & ~255LL; }
+inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+// ------------------------------------------------------------------------------------------------
+// model construction
+// ------------------------------------------------------------------------------------------------
+void add_tensor(rnnwf_model& m, const std::string& name, std::initializer_list<long long> shape) {
+  TensorInfo t;
+  t.name = name;
+  t.offset = m.num_params;
+  t.ndim = (int)shape.size();
+  int i = 0;
+  for (auto s : shape) t.shape[i++] = s;
+  for (; i < 4; ++i) t.shape[i] = 1;
+  m.num_params += t.numel();
+  m.tensors.push_back(t);
+}
+
+int step_of_2d(int nx, int ny, int Nx) { return ny * Nx + ((ny % 2 == 0) ? nx : Nx - 1 - nx); }
+
+int build_model(rnnwf_model& m) {
+  const rnnwf_config& c = m.cfg;
+  m.cell = c.cell;
+  m.nh = c.num_units;
+  m.nhp = (m.nh + 7) & ~7;
+  m.ldH = (m.nhp % 16 == 0) ? m.nhp + 8 : m.nhp;
+  m.complex_head = c.complex_head ? 1 : 0;
+  m.u1 = c.u1 ? 1 : 0;
+  m.cps = m.nhp / KC;
+  m.num_params = 0;
+  const int nh = m.nh, Nx = c.nx, Ny = c.ny;
+  if (nh < 1 || nh > 1024 || Nx < 1 || Ny < 1) return fail(RNNWF_EINVAL, "bad lattice / num_units");
+  if ((long long)Nx * Ny * std::max(1, c.num_layers) > 30000) return fail(RNNWF_EINVAL, "lattice too large for int16 step tables");
+
+  auto blank_step = [] {
+    StepMeta s;
+    std::memset(&s, 0, sizeof(s));
+    for (int k = 0; k < MAX_SLOTS; ++k) { s.nbr[k] = -1; s.nsym[k] = -1; }
+    s.sym = -1; s.own = 0xff;
+    return s;
+  };
+  auto blank_variant = [] {
+    HostVariant v;
+    std::memset(&v, 0, sizeof(v));
+    v.meta.ncls = 1;
+    return v;
+  };
+
+  switch (c.cell) {
+    case RNNWF_CELL_GRU1D: {
+      const int L = std::max(1, c.num_layers), N = Nx;
+      if (Ny != 1) return fail(RNNWF_EINVAL, "GRU1D needs ny == 1");
+      m.nslots = 2; m.D = 2; m.bits = 1; m.Tsym = N; m.symL = L; m.Q = N * L; m.nsites = N;
+      m.NTU = 4; m.Greal = nh; m.gru_type = true;
+      for (int l = 0; l < L; ++l) {
+        const long long din = (l == 0) ? 2 : nh;
+        const std::string p = "gru" + std::to_string(l) + ".";
+        add_tensor(m, p + "Wg", {din + nh, 2LL * nh});
+        add_tensor(m, p + "bg", {2LL * nh});
+        add_tensor(m, p + "Wci", {din, (long long)nh});
+        add_tensor(m, p + "Wch", {(long long)nh, (long long)nh});
+        add_tensor(m, p + "bci", {(long long)nh});
+        add_tensor(m, p + "bch", {(long long)nh});
+        HostVariant v = blank_variant();
+        v.vkind = l;
+        v.meta.slot_mask = (l == 0) ? 1 : 3;
+        v.meta.x_mask = (l == 0) ? 1 : 0;
+        v.nsl = (l == 0) ? 1 : 2;
+        v.slot_of_rank[0] = 0; v.slot_of_rank[1] = 1;
+        v.meta.slot_rank[0] = 0; v.meta.slot_rank[1] = 1;
+        m.variants.push_back(v);
+      }
+      for (int t = 0; t < N; ++t)
+        for (int l = 0; l < L; ++l) {
+          StepMeta s = blank_step();
+          const int q = t * L + l;
+          if (t > 0) s.nbr[0] = (int16_t)(q - L);
+          if (l > 0) s.nbr[1] = (int16_t)(q - 1);
+          if (l == 0 && t > 0) s.nsym[0] = (int16_t)(t - 1);
+          s.sym = (l == L - 1) ? (int16_t)t : (int16_t)-1;
+          s.site = (int16_t)t;
+          s.head = (l == L - 1);
+          s.own = 0;
+          s.variant = (uint8_t)l;
+          m.steps.push_back(s);
+        }
+      m.site_of_t.resize(N);
+      for (int t = 0; t < N; ++t) m.site_of_t[t] = (int16_t)t;
+      break;
+    }
+    case RNNWF_CELL_VANILLA2D:
+    case RNNWF_CELL_TENS2D:
+    case RNNWF_CELL_TENSGRU2D: {
+      m.nslots = 2; m.D = 2; m.bits = 1; m.Tsym = Nx * Ny; m.symL = 1; m.Q = Nx * Ny; m.nsites = Nx * Ny;
+      const bool tens = c.cell != RNNWF_CELL_VANILLA2D;
+      m.gru_type = (c.cell == RNNWF_CELL_TENSGRU2D);
+      m.NTU = m.gru_type ? 3 : 4;
+      m.Greal = m.gru_type ? nh : (nh + 3) / 4;
+      if (!tens) {
+        add_tensor(m, "Wh", {(long long)nh, (long long)nh});
+        add_tensor(m, "Uh", {2, (long long)nh});
+        add_tensor(m, "Wv", {(long long)nh, (long long)nh});
+        add_tensor(m, "Uv", {2, (long long)nh});
+        add_tensor(m, "b", {(long long)nh});
+        HostVariant v = blank_variant();
+        v.meta.slot_mask = 3; v.meta.x_mask = 3; v.nsl = 2;
+        v.slot_of_rank[0] = 0; v.slot_of_rank[1] = 1; v.meta.slot_rank[0] = 0; v.meta.slot_rank[1] = 1;
+        m.variants.push_back(v);
+      } else {
+        add_tensor(m, "W", {(long long)nh, 2LL * nh, 4});
+        add_tensor(m, "b", {(long long)nh});
+        if (m.gru_type) {
+          add_tensor(m, "Wg", {(long long)nh, 2LL * nh, 4});
+          add_tensor(m, "bg", {(long long)nh});
+          add_tensor(m, "Wmerge", {2LL * nh, (long long)nh});
+        }
+        for (int k = 0; k < 4; ++k) {
+          HostVariant v = blank_variant();
+          v.vkind = k;
+          if (k == 0) { v.meta.ncls = 4; v.meta.slot_mask = 3; v.nsl = 2; v.meta.cls_mult[0] = 1; v.meta.cls_mult[1] = 2;
+                        v.slot_of_rank[0] = 0; v.slot_of_rank[1] = 1; v.meta.slot_rank[0] = 0; v.meta.slot_rank[1] = 1; }
+          if (k == 1) { v.meta.ncls = 2; v.meta.slot_mask = 1; v.nsl = 1; v.meta.cls_mult[0] = 1; v.slot_of_rank[0] = 0; v.meta.slot_rank[0] = 0; }
+          if (k == 2) { v.meta.ncls = 2; v.meta.slot_mask = 2; v.nsl = 1; v.meta.cls_mult[1] = 1; v.slot_of_rank[0] = 1; v.meta.slot_rank[1] = 0; }
+          if (k == 3) { v.meta.ncls = 1; v.meta.slot_mask = 0; v.nsl = 0; }
+          m.variants.push_back(v);
+        }
+      }
+      m.site_of_t.resize(Nx * Ny);
+      for (int ny = 0; ny < Ny; ++ny)
+        for (int ix = 0; ix < Nx; ++ix) {
+          const int nx = (ny % 2 == 0) ? ix : Nx - 1 - ix;
+          StepMeta s = blank_step();
+          const int t = ny * Nx + ix;
+          const int px = (ny % 2 == 0) ? nx - 1 : nx + 1;
+          const bool has_h = px >= 0 && px < Nx, has_v = ny > 0;
+          if (has_h) s.nbr[0] = s.nsym[0] = (int16_t)step_of_2d(px, ny, Nx);
+          if (has_v) s.nbr[1] = s.nsym[1] = (int16_t)step_of_2d(nx, ny - 1, Nx);
+          s.sym = (int16_t)t;
+          s.site = (int16_t)(nx * Ny + ny);
+          s.head = 1;
+          s.variant = tens ? (uint8_t)(has_h && has_v ? 0 : (has_h ? 1 : (has_v ? 2 : 3))) : 0;
+          m.steps.push_back(s);
+          m.site_of_t[t] = s.site;
+        }
+      break;
+    }
+    case RNNWF_CELL_GRU4: {
+      m.nslots = 4; m.D = 8; m.bits = 3; m.Tsym = Nx * Ny; m.symL = 1; m.Q = Nx * Ny; m.nsites = Nx * Ny * 3;
+      m.NTU = 3; m.Greal = nh; m.gru_type = true;
+      add_tensor(m, "W", {4LL * (nh + 6), (long long)nh});
+      add_tensor(m, "b", {(long long)nh});
+      add_tensor(m, "Wg", {4LL * (nh + 6), (long long)nh});
+      add_tensor(m, "bg", {(long long)nh});
+      add_tensor(m, "Wmerge", {4LL * nh, (long long)nh});
+      HostVariant v = blank_variant();
+      v.meta.slot_mask = 15; v.meta.x_mask = 15; v.nsl = 4;
+      for (int k = 0; k < 4; ++k) { v.slot_of_rank[k] = k; v.meta.slot_rank[k] = (uint8_t)k; }
+      m.variants.push_back(v);
+      m.site_of_t.resize(Nx * Ny);
+      for (int ny = 0; ny < Ny; ++ny)
+        for (int ix = 0; ix < Nx; ++ix) {
+          const int nx = (ny % 2 == 0) ? ix : Nx - 1 - ix;
+          const int t = ny * Nx + ix;
+          const int dir = (ny % 2 == 0) ? 1 : -1;
+          int keys[4][2] = {{nx - dir, ny}, {nx, ny - 1}, {((nx + dir) % Nx + Nx) % Nx, ny}, {nx, (ny + 1) % Ny}};
+          StepMeta s = blank_step();
+          for (int k = 0; k < 4; ++k) {
+            const int kx = keys[k][0], ky = keys[k][1];
+            if (kx < 0 || kx >= Nx || ky < 0 || ky >= Ny) continue;
+            const int st = step_of_2d(kx, ky, Nx);
+            if (st < t) s.nbr[k] = s.nsym[k] = (int16_t)st;
+          }
+          s.sym = (int16_t)t;
+          s.site = (int16_t)(nx * Ny + ny);
+          s.head = 1;
+          s.variant = 0;
+          m.steps.push_back(s);
+          m.site_of_t[t] = s.site;
+        }
+      break;
+    }
+    default:
+      return fail(RNNWF_EINVAL, "unknown cell type");
+  }
+  // heads
+  add_tensor(m, "dense.W", {(long long)nh, (long long)m.D});
+  add_tensor(m, "dense.b", {(long long)m.D});
+  if (m.complex_head) {
+    if (m.D != 2) return fail(RNNWF_EINVAL, "complex head needs a two-state model");
+    add_tensor(m, "dense_phase.W", {(long long)nh, 2});
+    add_tensor(m, "dense_phase.b", {2});
+  }
+  m.ND = m.complex_head ? 4 : m.D;
+  // U(1) caps (2DHeisenberg/MDComplexRNN.py:71-72): H((N +- m)//2 - 1 - n)
+  const int N = m.Tsym;
+  auto floordiv2 = [](int a) { return (a >= 0) ? a / 2 : -((-a + 1) / 2); };
+  m.cap_up = floordiv2(N + c.magnetization) - 1;
+  m.cap_dn = floordiv2(N - c.magnetization) - 1;
+  if (m.u1 && m.bits != 1) return fail(RNNWF_EINVAL, "U(1) projection needs a spin-1/2 model");
+
+  m.t_of_site.assign(m.Tsym, 0);
+  for (int t = 0; t < m.Tsym; ++t) m.t_of_site[m.site_of_t[t]] = (int16_t)t;
+
+  // ring length = 1 + largest look-back
+  int look = 1;
+  for (int q = 0; q < m.Q; ++q)
+    for (int k = 0; k < MAX_SLOTS; ++k)
+      if (m.steps[q].nbr[k] >= 0) look = std::max(look, q - m.steps[q].nbr[k]);
+  m.ring_len = std::min(m.Q, look + 1);
+
+  // tile shape: TJ in {4,5} for the three-gate cells, 4 otherwise; WC <= 5 warp columns
+  int best_tj = 4, best_wc = 1;
+  long long best_cost = -1;
+  for (int tj = 4; tj <= ((m.NTU == 3) ? 5 : 4); ++tj)
+    for (int wc = 1; wc <= 5; ++wc) {
+      const int gblk = tj * CL * wc;
+      const int ncb = cdiv(m.Greal, gblk);
+      const long long cost = (long long)ncb * gblk * 100 + ncb;  // padded columns first, then fewer passes
+      const long long cost2 = cost + (wc < 2 ? 1 : 0);
+      if (best_cost < 0 || cost2 < best_cost) { best_cost = cost2; best_tj = tj; best_wc = wc; }
+    }
+  m.TJ = best_tj; m.WC = best_wc;
+  m.Gblk = m.TJ * CL * m.WC;
+  m.ncb = cdiv(m.Greal, m.Gblk);
+  m.Gp = m.ncb * m.Gblk;
+  m.ncls_max = 1;
+  for (auto& v : m.variants) m.ncls_max = std::max<int>(m.ncls_max, v.meta.ncls);
+
+  // packed-buffer offsets
+  long long woff = 0, xoff = 0, boff = 0;
+  for (auto& v : m.variants) {
+    const long long per_cb = (long long)v.nsl * m.cps * v.meta.ncls * KC * m.Gblk;
+    v.meta.w_off = (uint32_t)woff;
+    v.meta.w_cb_stride = (uint32_t)per_cb;
+    v.w_float4 = per_cb * m.ncb;
+    woff += v.w_float4;
+    v.meta.x_off = (uint32_t)xoff;
+    if (v.meta.x_mask) xoff += (long long)m.nslots * m.D * m.Gp;
+    v.meta.b_off = (uint32_t)boff;
+    boff += m.Gp;
+  }
+  m.wpack_float4 = std::max(1LL, woff);
+  m.xtab_float4 = std::max(1LL, xoff);
+  m.bias_float4 = std::max(1LL, boff);
+  return RNNWF_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// sweep launch
+// ------------------------------------------------------------------------------------------------
+struct LaunchShape { int WR, Mp, Mr, threads, smem, grid; };
+
+int pick_shape(const rnnwf_model& m, long long rows, LaunchShape& s) {
+  const int pad = (m.ncls_max > 1) ? 3 * m.ncls_max : 0;
+  for (int wr = 4; wr >= 1; wr >>= 1) {
+    const int Mp = 32 * wr, Mr = Mp - pad;
+    if (Mr <= 0) continue;
+    SmemLayout L(m.ncls_max, m.Gblk, Mp, m.ldH, m.nhp, m.ND, m.Tsym);
+    const long long tiles = (rows + Mr - 1) / Mr;
+    const bool fits = L.total <= 227 * 1024;
+    if (!fits) continue;
+    // prefer the tallest tile that still gives every SM a tile
+    if (wr == 1 || tiles >= m.num_sms) {
+      s.WR = wr; s.Mp = Mp; s.Mr = Mr; s.threads = 32 * wr * m.WC; s.smem = L.total;
+      s.grid = (int)std::max(1LL, std::min<long long>(tiles, m.num_sms));
+      return RNNWF_OK;
+    }
+  }
+  return fail(RNNWF_ENOMEM, "model does not fit in shared memory (lattice too long / too many units)");
+}
+
+void fill_model_params(const rnnwf_model& m, const LaunchShape& s, SweepParams& P) {
+  std::memset(&P, 0, sizeof(P));
+  P.cell = m.cell; P.nh = m.nh; P.nhp = m.nhp; P.ldH = m.ldH; P.nslots = m.nslots; P.D = m.D; P.ND = m.ND;
+  P.complex_head = m.complex_head; P.u1 = m.u1; P.cap_up = m.cap_up; P.cap_dn = m.cap_dn;
+  P.Q = m.Q; P.Tsym = m.Tsym; P.symL = m.symL; P.nsites = m.nsites; P.bits = m.bits; P.cps = m.cps;
+  P.Gblk = m.Gblk; P.ncb = m.ncb; P.Gp = m.Gp; P.Greal = m.Greal; P.ntu = m.NTU;
+  P.ring_len = m.ring_len; P.WR = s.WR; P.WC = m.WC; P.Mp = s.Mp; P.Mr = s.Mr; P.ncls_max = m.ncls_max;
+  P.steps = m.d_steps; P.variants = m.d_variants; P.Wpack = m.d_wpack; P.Xtab = m.d_xtab; P.bias = m.d_bias;
+  P.head_w = m.d_head_w; P.head_b = m.d_head_b;
+}
+
+template <int TJ, int NTU>
+cudaError_t launch_inst(const SweepParams& P, const LaunchShape& s, cudaStream_t st) {
+  sweep_kernel<TJ, NTU><<<s.grid, s.threads, s.smem, st>>>(P);
+  return cudaGetLastError();
+}
+
+int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& s, cudaStream_t st) {
+  cudaError_t e;
+  if (m.NTU == 3 && m.TJ == 5) e = launch_inst<5, 3>(P, s, st);
+  else if (m.NTU == 3 && m.TJ == 4) e = launch_inst<4, 3>(P, s, st);
+  else e = launch_inst<4, 4>(P, s, st);
+  if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("sweep kernel launch: ") + cudaGetErrorString(e));
+  return RNNWF_OK;
+}
+
+long long ring_bytes(const rnnwf_model& m, int grid, int Mp) { return (long long)grid * m.ring_len * Mp * m.nhp * 4; }
+
+int set_saved(const rnnwf_model& m, SweepParams& P, void* saved, long long rows) {
+  if (saved == nullptr) return RNNWF_OK;
+  const Saved sv = m.saved_layout(rows);
+  char* b = static_cast<char*>(saved);
+  P.sv_hist = reinterpret_cast<float*>(b + sv.off_hist);
+  P.sv_gates = m.gru_type ? reinterpret_cast<float4*>(b + sv.off_gates) : nullptr;
+  P.sv_cum = reinterpret_cast<double2*>(b + sv.off_cum);
+  P.sv_rows = rows;
+  return RNNWF_OK;
+}
+
+// single-block exclusive scan of int32 (n <= ~1e8); out[n-1] + in[n-1] is not needed: callers append a 0.
+__global__ void scan_kernel(const int* __restrict__ in, int* __restrict__ out, long long n) {
+  __shared__ int tot[1024];
+  const int tid = threadIdx.x;
+  const long long chunk = (n + 1023) / 1024;
+  long long lo = tid * chunk; if (lo > n) lo = n;
+  long long hi = lo + chunk; if (hi > n) hi = n;
+  int s = 0;
+  for (long long i = lo; i < hi; ++i) s += in[i];
+  tot[tid] = s;
+  __syncthreads();
+  for (int off = 1; off < 1024; off <<= 1) {
+    const int v = (tid >= off) ? tot[tid - off] : 0;
+    __syncthreads();
+    tot[tid] += v;
+    __syncthreads();
+  }
+  int run = tot[tid] - s;
+  for (long long i = lo; i < hi; ++i) { const int v = in[i]; out[i] = run; run += v; }
+}
+
+__global__ void count_children_kernel(const int* rows_dev, long long fixed, long long* out) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) *out = (rows_dev != nullptr) ? (long long)(*rows_dev) : fixed;
+}
+
+int check_ready(rnnwf_handle h) {
+  if (h == nullptr) return fail(RNNWF_EINVAL, "null handle");
+  if (!h->weights_set) return fail(RNNWF_ESTATE, "rnnwf_set_weights has not been called");
+  return RNNWF_OK;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// C-ABI
+// ------------------------------------------------------------------------------------------------
+extern "C" {
+
+const char* rnnwf_last_error(void) { return g_err.c_str(); }
+int rnnwf_version(void) { return 1; }
+
+int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
+  if (cfg == nullptr || out == nullptr) return fail(RNNWF_EINVAL, "null argument");
+  *out = nullptr;
+  int dev = 0;
+  CUDA_TRY(cudaGetDevice(&dev));
+  rnnwf_model* m = new rnnwf_model();
+  m->cfg = *cfg;
+  m->device = dev;
+  int sms = 0;
+  cudaError_t e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (e != cudaSuccess) { delete m; return fail(RNNWF_ECUDA, std::string("no CUDA device: ") + cudaGetErrorString(e)); }
+  m->num_sms = sms;
+  int rc = build_model(*m);
+  if (rc != RNNWF_OK) { delete m; return rc; }
+  std::vector<VariantMeta> vmeta;
+  for (auto& v : m->variants) vmeta.push_back(v.meta);
+#define CREATE_TRY(expr)                                                                        \
+  do {                                                                                          \
+    cudaError_t e__ = (expr);                                                                   \
+    if (e__ != cudaSuccess) {                                                                   \
+      std::string msg = std::string(#expr) + ": " + cudaGetErrorString(e__);                    \
+      rnnwf_destroy(m);                                                                         \
+      return fail(RNNWF_ECUDA, msg);                                                            \
+    }                                                                                           \
+  } while (0)
+  CREATE_TRY(cudaMalloc(&m->d_steps, m->steps.size() * sizeof(StepMeta)));
+  CREATE_TRY(cudaMalloc(&m->d_variants, vmeta.size() * sizeof(VariantMeta)));
+  CREATE_TRY(cudaMalloc(&m->d_site_of_t, m->site_of_t.size() * sizeof(int16_t)));
+  CREATE_TRY(cudaMalloc(&m->d_wpack, m->wpack_float4 * 16));
+  CREATE_TRY(cudaMalloc(&m->d_xtab, m->xtab_float4 * 16));
+  CREATE_TRY(cudaMalloc(&m->d_bias, m->bias_float4 * 16));
+  CREATE_TRY(cudaMalloc(&m->d_head_w, (size_t)m->nhp * m->ND * 4));
+  CREATE_TRY(cudaMalloc(&m->d_head_b, 64));
+  CREATE_TRY(cudaMemcpy(m->d_steps, m->steps.data(), m->steps.size() * sizeof(StepMeta), cudaMemcpyHostToDevice));
+  CREATE_TRY(cudaMemcpy(m->d_variants, vmeta.data(), vmeta.size() * sizeof(VariantMeta), cudaMemcpyHostToDevice));
+  CREATE_TRY(cudaMemcpy(m->d_site_of_t, m->site_of_t.data(), m->site_of_t.size() * sizeof(int16_t), cudaMemcpyHostToDevice));
+  CREATE_TRY(cudaMemset(m->d_wpack, 0, m->wpack_float4 * 16));
+  CREATE_TRY(cudaMemset(m->d_xtab, 0, m->xtab_float4 * 16));
+  CREATE_TRY(cudaMemset(m->d_bias, 0, m->bias_float4 * 16));
+  const int max_smem = 227 * 1024;
+  CREATE_TRY(cudaFuncSetAttribute(sweep_kernel<5, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+  CREATE_TRY(cudaFuncSetAttribute(sweep_kernel<4, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+  CREATE_TRY(cudaFuncSetAttribute(sweep_kernel<4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+  CREATE_TRY(backward_init());
+#undef CREATE_TRY
+  *out = m;
+  return RNNWF_OK;
+}
+
+int rnnwf_destroy(rnnwf_handle h) {
+  if (h == nullptr) return RNNWF_OK;
+  cudaFree(h->d_steps); cudaFree(h->d_variants); cudaFree(h->d_site_of_t); cudaFree(h->d_wpack);
+  cudaFree(h->d_xtab); cudaFree(h->d_bias); cudaFree(h->d_head_w); cudaFree(h->d_head_b);
+  delete h;
+  return RNNWF_OK;
+}
+
+int64_t rnnwf_count_params(const rnnwf_config* cfg) {
+  // host-only: parameter count of a configuration (no device needed)
+  if (cfg == nullptr) return fail(RNNWF_EINVAL, "null argument");
+  rnnwf_model m;
+  m.cfg = *cfg;
+  m.num_sms = 1;
+  int rc = build_model(m);
+  return rc == RNNWF_OK ? m.num_params : (int64_t)rc;
+}
+
+int64_t rnnwf_num_params(rnnwf_handle h) { return h ? h->num_params : 0; }
+int rnnwf_num_tensors(rnnwf_handle h) { return h ? (int)h->tensors.size() : 0; }
+
+int rnnwf_param_info(rnnwf_handle h, int index, char* name, int name_cap, int64_t* offset, int32_t* ndim, int64_t shape[4]) {
+  if (h == nullptr || index < 0 || index >= (int)h->tensors.size()) return fail(RNNWF_EINVAL, "bad tensor index");
+  const TensorInfo& t = h->tensors[index];
+  if (name != nullptr && name_cap > 0) { std::strncpy(name, t.name.c_str(), name_cap - 1); name[name_cap - 1] = 0; }
+  if (offset) *offset = t.offset;
+  if (ndim) *ndim = t.ndim;
+  if (shape) for (int i = 0; i < 4; ++i) shape[i] = t.shape[i];
+  return RNNWF_OK;
+}
+
+static void make_pack_ctx(const rnnwf_model& m, const HostVariant& v, const float* params, float* grads, PackCtx& c) {
+  std::memset(&c, 0, sizeof(c));
+  c.cell = m.cell; c.nh = m.nh; c.nhp = m.nhp; c.Gblk = m.Gblk; c.ncb = m.ncb; c.Gp = m.Gp; c.Greal = m.Greal;
+  c.cps = m.cps; c.D = m.D; c.ncls = v.meta.ncls; c.nsl = v.nsl; c.vkind = v.vkind;
+  for (int k = 0; k < MAX_SLOTS; ++k) c.slot_of_rank[k] = v.slot_of_rank[k];
+  auto bind = [&](int slot, const std::string& name) {
+    const TensorInfo* t = m.tensor(name);
+    c.t[slot] = (t && params) ? params + t->offset : nullptr;
+    c.gt[slot] = (t && grads) ? grads + t->offset : nullptr;
+  };
+  switch (m.cell) {
+    case CELL_GRU1D: {
+      const std::string p = "gru" + std::to_string(v.vkind) + ".";
+      c.din = (v.vkind == 0) ? 2 : m.nh;
+      bind(0, p + "Wg"); bind(1, p + "bg"); bind(2, p + "Wci"); bind(3, p + "Wch"); bind(4, p + "bci"); bind(5, p + "bch");
+      break;
+    }
+    case CELL_VANILLA2D: bind(0, "Wh"); bind(1, "Uh"); bind(2, "Wv"); bind(3, "Uv"); bind(4, "b"); break;
+    case CELL_TENS2D: bind(0, "W"); bind(1, "b"); break;
+    case CELL_TENSGRU2D:
+    case CELL_GRU4: bind(0, "W"); bind(1, "b"); bind(2, "Wg"); bind(3, "bg"); bind(4, "Wmerge"); break;
+  }
+}
+
+int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
+  if (h == nullptr || params_dev == nullptr) return fail(RNNWF_EINVAL, "null argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  for (auto& v : h->variants) {
+    PackCtx c;
+    make_pack_ctx(*h, v, params_dev, nullptr, c);
+    if (v.w_float4 > 0) pack_w_kernel<<<std::min(1024, cdiv(v.w_float4, 256)), 256, 0, st>>>(c, h->d_wpack + v.meta.w_off);
+    if (v.meta.x_mask) pack_x_kernel<<<std::min(256, cdiv((long long)h->nslots * h->D * h->Gp, 256)), 256, 0, st>>>(c, h->nslots, h->d_xtab + v.meta.x_off);
+    pack_b_kernel<<<cdiv(h->Gp, 256), 256, 0, st>>>(c, h->d_bias + v.meta.b_off);
+  }
+  const TensorInfo* wd = h->tensor("dense.W");
+  const TensorInfo* bd = h->tensor("dense.b");
+  const TensorInfo* wp = h->tensor("dense_phase.W");
+  const TensorInfo* bp = h->tensor("dense_phase.b");
+  pack_head_kernel<<<cdiv((long long)h->nhp * h->ND, 256), 256, 0, st>>>(
+      params_dev + wd->offset, params_dev + bd->offset, wp ? params_dev + wp->offset : nullptr,
+      bp ? params_dev + bp->offset : nullptr, h->nh, h->nhp, h->D, h->ND, h->d_head_w, h->d_head_b);
+  CUDA_TRY(cudaGetLastError());
+  h->d_params = params_dev;
+  h->weights_set = true;
+  return RNNWF_OK;
+}
+
+int64_t rnnwf_workspace_bytes(rnnwf_handle h) {
+  if (h == nullptr) return 0;
+  return align256(ring_bytes(*h, h->num_sms, 128));
+}
+
+int64_t rnnwf_saved_bytes(rnnwf_handle h, int64_t rows) { return h ? h->saved_layout(rows).total : 0; }
+
+int rnnwf_sample(rnnwf_handle h, int64_t rows, const float* uniforms_dev, uint64_t seed, uint64_t row_offset,
+                 int8_t* samples_dev, double* logp_dev, double* phase_dev, void* saved_dev, void* workspace_dev,
+                 int64_t workspace_bytes, void* stream) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (rows <= 0 || samples_dev == nullptr) return fail(RNNWF_EINVAL, "rnnwf_sample: rows must be positive and samples non-null");
+  LaunchShape s;
+  if ((rc = pick_shape(*h, rows, s))) return rc;
+  if (workspace_dev == nullptr || workspace_bytes < ring_bytes(*h, s.grid, s.Mp)) return fail(RNNWF_ENOMEM, "rnnwf_sample: workspace too small");
+  SweepParams P;
+  fill_model_params(*h, s, P);
+  P.mode = MODE_SAMPLE; P.rows = rows; P.cfg_out = samples_dev; P.uniforms = uniforms_dev; P.seed = seed; P.row_offset = row_offset;
+  P.out_logp = logp_dev; P.out_phase = phase_dev; P.ring = static_cast<float*>(workspace_dev);
+  set_saved(*h, P, saved_dev, rows);
+  return launch_sweep(*h, P, s, static_cast<cudaStream_t>(stream));
+}
+
+int rnnwf_logpsi(rnnwf_handle h, int64_t rows, const int8_t* samples_dev, double* logp_dev, double* phase_dev,
+                 void* saved_dev, void* workspace_dev, int64_t workspace_bytes, void* stream) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (rows <= 0 || samples_dev == nullptr) return fail(RNNWF_EINVAL, "rnnwf_logpsi: rows must be positive and samples non-null");
+  LaunchShape s;
+  if ((rc = pick_shape(*h, rows, s))) return rc;
+  if (workspace_dev == nullptr || workspace_bytes < ring_bytes(*h, s.grid, s.Mp)) return fail(RNNWF_ENOMEM, "rnnwf_logpsi: workspace too small");
+  SweepParams P;
+  fill_model_params(*h, s, P);
+  P.mode = MODE_EVAL; P.rows = rows; P.cfg_in = samples_dev; P.out_logp = logp_dev; P.out_phase = phase_dev;
+  P.ring = static_cast<float*>(workspace_dev);
+  set_saved(*h, P, saved_dev, rows);
+  return launch_sweep(*h, P, s, static_cast<cudaStream_t>(stream));
+}
+
+// ---- local energies --------------------------------------------------------------------------------
+namespace {
+struct ElocLayout {
+  long long off_ham, off_bonds, off_bstart, off_nb, off_counts, off_offsets, off_nchild, off_children, off_ring, total;
+  long long max_children;
+};
+
+long long max_children_per_sample(const rnnwf_model& m, int ham) {
+  switch (ham) {
+    case RNNWF_HAM_TFIM1D:
+    case RNNWF_HAM_TFIM2D: return m.Tsym;
+    case RNNWF_HAM_RYDBERG: return 3LL * m.Tsym;
+    case RNNWF_HAM_J1J2: return 2LL * m.Tsym;
+    case RNNWF_HAM_HEIS2D: return 3LL * m.Tsym;
+  }
+  return 0;
+}
+
+ElocLayout eloc_layout(const rnnwf_model& m, int ham, long long rows) {
+  ElocLayout L;
+  long long o = 0;
+  L.off_ham = o;      o += align256((3LL * m.Tsym + 16) * 8);
+  L.off_bonds = o;    o += align256(3LL * m.Tsym * sizeof(Bond) + 64);
+  L.off_bstart = o;   o += align256((m.Tsym + 2) * 4LL);
+  L.off_nb = o;       o += align256(256 * sizeof(RydNb));
+  const bool variable = (ham == RNNWF_HAM_J1J2 || ham == RNNWF_HAM_HEIS2D);
+  const long long ncnt = variable ? (long long)m.Tsym * rows + 1 : 0;
+  L.off_counts = o;   o += align256(ncnt * 4);
+  L.off_offsets = o;  o += align256(ncnt * 4);
+  L.off_nchild = o;   o += 256;
+  L.max_children = max_children_per_sample(m, ham) * rows;
+  L.off_children = o; o += align256(L.max_children * (long long)sizeof(Child));
+  L.off_ring = o;     o += align256(ring_bytes(m, m.num_sms, 128));
+  L.total = o;
+  return L;
+}
+}  // namespace
+
+int64_t rnnwf_eloc_workspace_bytes(rnnwf_handle h, int hamiltonian, int64_t rows) {
+  if (h == nullptr || rows <= 0) return 0;
+  return eloc_layout(*h, hamiltonian, rows).total;
+}
+
+int rnnwf_local_energies(rnnwf_handle h, int hamiltonian, const double* ham, int ham_len, int64_t rows,
+                         const int8_t* samples_dev, const double* logp_dev, const double* phase_dev,
+                         const void* saved_dev, double* eloc_dev, int64_t* nconn_dev, void* workspace_dev,
+                         int64_t workspace_bytes, void* stream) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (rows <= 0 || samples_dev == nullptr || logp_dev == nullptr || eloc_dev == nullptr || ham == nullptr)
+    return fail(RNNWF_EINVAL, "rnnwf_local_energies: null argument or rows <= 0");
+  if (rows > 0x7fffffffLL) return fail(RNNWF_EINVAL, "rnnwf_local_energies: too many rows");
+  const rnnwf_model& m = *h;
+  const ElocLayout L = eloc_layout(m, hamiltonian, rows);
+  if (workspace_dev == nullptr || workspace_bytes < L.total) return fail(RNNWF_ENOMEM, "rnnwf_local_energies: workspace too small");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  char* ws = static_cast<char*>(workspace_dev);
+  double* d_ham = reinterpret_cast<double*>(ws + L.off_ham);
+  Bond* d_bonds = reinterpret_cast<Bond*>(ws + L.off_bonds);
+  int* d_bstart = reinterpret_cast<int*>(ws + L.off_bstart);
+  RydNb* d_nb = reinterpret_cast<RydNb*>(ws + L.off_nb);
+  int* d_counts = reinterpret_cast<int*>(ws + L.off_counts);
+  int* d_offsets = reinterpret_cast<int*>(ws + L.off_offsets);
+  Child* d_children = reinterpret_cast<Child*>(ws + L.off_children);
+  const int Nx = m.cfg.nx, Ny = m.cfg.ny, T = m.Tsym;
+  const int tpb = 256;
+  const int gsamp = std::min(4096, cdiv(rows, tpb));
+  long long nchild_fixed = 0;
+  const int* rows_dev = nullptr;
+  bool have_children = true;
+
+  auto need_cell = [&](bool ok, const char* what) { return ok ? RNNWF_OK : fail(RNNWF_EINVAL, std::string("rnnwf_local_energies: ") + what); };
+
+  switch (hamiltonian) {
+    case RNNWF_HAM_TFIM1D:
+    case RNNWF_HAM_TFIM2D: {
+      if ((rc = need_cell(m.bits == 1, "TFIM needs a spin-1/2 wavefunction"))) return rc;
+      const int nJ = (hamiltonian == RNNWF_HAM_TFIM1D) ? std::max(1, Nx - 1) : Nx * Ny;
+      if (hamiltonian == RNNWF_HAM_TFIM1D && Ny != 1) return fail(RNNWF_EINVAL, "TFIM1D needs a chain");
+      if (ham_len < 1 + nJ) return fail(RNNWF_EINVAL, "TFIM: ham = {Bx, Jz...} too short");
+      // 1D: Jz[i] couples (i,i+1) == 2D kernel with Ny = 1 and Jz[i*1+0]
+      std::vector<double> J(Nx * Ny, 0.0);
+      for (int i = 0; i < nJ && i < Nx * Ny; ++i) J[i] = ham[1 + i];
+      CUDA_TRY(cudaMemcpyAsync(d_ham, J.data(), J.size() * 8, cudaMemcpyHostToDevice, st));
+      tfim_diag_kernel<<<gsamp, tpb, 0, st>>>(samples_dev, rows, Nx, Ny, d_ham, eloc_dev);
+      const double Bx = ham[0];
+      if (Bx == 0.0) have_children = false;
+      else {
+        nchild_fixed = (long long)T * rows;
+        all_flips_kernel<<<std::min(8192, cdiv(nchild_fixed, tpb)), tpb, 0, st>>>(rows, T, 1, (float)(-Bx), d_children);
+      }
+      break;
+    }
+    case RNNWF_HAM_RYDBERG: {
+      if ((rc = need_cell(m.cell == CELL_GRU4, "Rydberg needs the Kagome unit-cell wavefunction"))) return rc;
+      if (ham_len < 4) return fail(RNNWF_EINVAL, "Rydberg: ham = {V, delta, Omega, Rcutoff}");
+      const double V = ham[0], delta = ham[1], Omega = ham[2], Rc = ham[3];
+      // generate_kagome + neighbouring_atoms (RydbergKagome_2DGRU/Helping_Functions.py:33-96)
+      auto pos = [&](int i, int j, int k, double& x, double& y) {
+        const double lx = 2.0 * (i + j / 2.0), ly = 2.0 * (std::sqrt(3.0) / 2.0 * j);
+        if (k == 1) { x = lx; y = ly; } else if (k == 2) { x = lx + 1.0; y = ly; } else { x = lx + 0.5; y = ly + std::sqrt(3.0) / 2.0; }
+      };
+      std::vector<RydNb> nb;
+      const double a1x = 2.0, a1y = 0.0, a2x = 1.0, a2y = std::sqrt(3.0);
+      for (int i = 0; i < Nx; ++i)
+        for (int j = 0; j < Ny; ++j)
+          for (int k = 0; k < 3; ++k)
+            for (int kc = 0; kc < 3; ++kc) {
+              double x, y, x0, y0;
+              pos(i, j, k, x, y);
+              pos(0, 0, kc, x0, y0);
+              const double sx[4] = {0.0, Nx * a1x, Ny * a2x, Nx * a1x + Ny * a2x};
+              const double sy[4] = {0.0, Nx * a1y, Ny * a2y, Nx * a1y + Ny * a2y};
+              for (int im = 0; im < 4; ++im) {
+                const double dx = x - sx[im] - x0, dy = y - sy[im] - y0;
+                const double d = std::sqrt(dx * dx + dy * dy);
+                if (d > 0 && d <= Rc) {
+                  RydNb e; e.kc = (int16_t)kc; e.di = (int16_t)i; e.dj = (int16_t)j; e.k = (int16_t)k;
+                  e.w = (V / 2.0) / std::pow(d, 6.0);
+                  nb.push_back(e);
+                }
+              }
+            }
+      if (nb.size() > 256) return fail(RNNWF_EINVAL, "Rydberg: too many neighbours within Rcutoff (max 256)");
+      if (!nb.empty()) CUDA_TRY(cudaMemcpyAsync(d_nb, nb.data(), nb.size() * sizeof(RydNb), cudaMemcpyHostToDevice, st));
+      rydberg_diag_kernel<<<gsamp, tpb, 0, st>>>(samples_dev, rows, Nx, Ny, d_nb, (int)nb.size(), delta, eloc_dev);
+      if (Omega == 0.0) have_children = false;
+      else {
+        nchild_fixed = 3LL * T * rows;
+        all_flips_kernel<<<std::min(8192, cdiv(nchild_fixed, tpb)), tpb, 0, st>>>(rows, T, 3, (float)(-Omega / 2.0), d_children);
+      }
+      break;
+    }
+    case RNNWF_HAM_J1J2:
+    case RNNWF_HAM_HEIS2D: {
+      if ((rc = need_cell(m.bits == 1, "exchange Hamiltonians need a spin-1/2 wavefunction"))) return rc;
+      struct HB { int ta, tb; float off, diag; };
+      std::vector<HB> hb;
+      std::vector<double> Bz;
+      auto add_bond = [&](int sa, int sb, double off, double diag) {
+        int ta = m.t_of_site[sa], tb = m.t_of_site[sb];
+        if (ta > tb) std::swap(ta, tb);
+        hb.push_back({ta, tb, (float)off, (float)diag});
+      };
+      if (hamiltonian == RNNWF_HAM_J1J2) {
+        const int N = Nx;
+        if (Ny != 1) return fail(RNNWF_EINVAL, "J1J2 needs a chain");
+        if (ham_len < 2 + 3 * N) return fail(RNNWF_EINVAL, "J1J2: ham = {periodic, marshall, J1[N], J2[N], Bz[N]}");
+        const bool periodic = ham[0] != 0.0, marshall = ham[1] != 0.0;
+        const double* J1 = ham + 2; const double* J2 = ham + 2 + N; const double* B = ham + 2 + 2 * N;
+        const int lim1 = periodic ? N : N - 1, lim2 = periodic ? N : N - 2;
+        for (int i = 0; i < lim1; ++i) add_bond(i, (i + 1) % N, J1[i] != 0.0 ? (marshall ? -J1[i] / 2 : J1[i] / 2) : 0.0, 0.25 * J1[i]);
+        for (int i = 0; i < lim2; ++i) if (J2[i] != 0.0) add_bond(i, (i + 2) % N, J2[i] / 2, 0.25 * J2[i]);
+        Bz.assign(B, B + N);
+      } else {
+        if (ham_len < 1) return fail(RNNWF_EINVAL, "HEIS2D: ham = {J2}");
+        if ((rc = need_cell(Ny >= 1 && m.cell != CELL_GRU1D, "HEIS2D needs a 2D wavefunction"))) return rc;
+        const double J2 = ham[0];
+        for (int nx = 0; nx < Nx; ++nx)
+          for (int ny = 0; ny < Ny; ++ny) {
+            if (nx + 1 < Nx) add_bond(nx * Ny + ny, (nx + 1) * Ny + ny, -0.5, 0.25);
+            if (ny + 1 < Ny) add_bond(nx * Ny + ny, nx * Ny + ny + 1, -0.5, 0.25);
+            if (nx + 1 < Nx && ny + 1 < Ny) add_bond(nx * Ny + ny, (nx + 1) * Ny + ny + 1, J2 / 2, 0.25 * J2);
+          }
+      }
+      if ((long long)hb.size() > 3LL * T) return fail(RNNWF_EINVAL, "too many bonds");
+      std::stable_sort(hb.begin(), hb.end(), [](const HB& a, const HB& b) { return a.ta < b.ta; });
+      std::vector<Bond> bonds(hb.size());
+      std::vector<int> bstart(T + 1, 0);
+      for (size_t i = 0; i < hb.size(); ++i) {
+        bonds[i].ta = (int16_t)hb[i].ta; bonds[i].tb = (int16_t)hb[i].tb; bonds[i].offdiag = hb[i].off; bonds[i].diag = hb[i].diag; bonds[i].pad = 0;
+        bstart[hb[i].ta + 1]++;
+      }
+      for (int t = 0; t < T; ++t) bstart[t + 1] += bstart[t];
+      if (!bonds.empty()) CUDA_TRY(cudaMemcpyAsync(d_bonds, bonds.data(), bonds.size() * sizeof(Bond), cudaMemcpyHostToDevice, st));
+      CUDA_TRY(cudaMemcpyAsync(d_bstart, bstart.data(), bstart.size() * 4, cudaMemcpyHostToDevice, st));
+      if (!Bz.empty()) CUDA_TRY(cudaMemcpyAsync(d_ham, Bz.data(), Bz.size() * 8, cudaMemcpyHostToDevice, st));
+      bond_diag_kernel<<<gsamp, tpb, 0, st>>>(samples_dev, rows, m.nsites, m.d_site_of_t, d_bonds, (int)bonds.size(), d_ham, (int)Bz.size(), eloc_dev);
+      const long long ncnt = (long long)T * rows;
+      bond_count_kernel<<<std::min(8192, cdiv(ncnt + 1, tpb)), tpb, 0, st>>>(samples_dev, rows, m.nsites, T, m.d_site_of_t, d_bonds, d_bstart, d_counts);
+      scan_kernel<<<1, 1024, 0, st>>>(d_counts, d_offsets, ncnt + 1);
+      bond_fill_kernel<<<std::min(8192, cdiv(ncnt, tpb)), tpb, 0, st>>>(samples_dev, rows, m.nsites, T, m.d_site_of_t, d_bonds, d_bstart, d_offsets, d_children);
+      rows_dev = d_offsets + ncnt;
+      nchild_fixed = L.max_children;
+      break;
+    }
+    default:
+      return fail(RNNWF_EINVAL, "unknown hamiltonian");
+  }
+  CUDA_TRY(cudaGetLastError());
+  if (nconn_dev != nullptr) {
+    // connected configurations evaluated (+ the diagonal one per sample, already known from `logp`)
+    count_children_kernel<<<1, 32, 0, st>>>(have_children ? rows_dev : nullptr, have_children ? (rows_dev ? 0 : nchild_fixed) : 0, (long long*)nconn_dev);
+  }
+  if (!have_children) return RNNWF_OK;
+
+  LaunchShape s;
+  if ((rc = pick_shape(m, nchild_fixed, s))) return rc;
+  SweepParams P;
+  fill_model_params(m, s, P);
+  P.mode = MODE_CHILD; P.rows = nchild_fixed; P.rows_dev = rows_dev; P.cfg_in = samples_dev; P.children = d_children;
+  P.par_logp = logp_dev; P.par_phase = phase_dev; P.eloc = eloc_dev;
+  P.ring = reinterpret_cast<float*>(ws + L.off_ring);
+  if (saved_dev != nullptr) {
+    const Saved sv = m.saved_layout(rows);
+    const char* b = static_cast<const char*>(saved_dev);
+    P.par_hist = reinterpret_cast<const float*>(b + sv.off_hist);
+    P.par_cum = reinterpret_cast<const double2*>(b + sv.off_cum);
+    P.par_rows = rows;
+  }
+  return launch_sweep(m, P, s, st);
+}
+
+// ---- backward ------------------------------------------------------------------------------------
+int64_t rnnwf_backward_workspace_bytes(rnnwf_handle h, int64_t rows) {
+  if (h == nullptr || rows <= 0) return 0;
+  return backward_workspace_bytes(*h, rows);
+}
+
+int rnnwf_backward(rnnwf_handle h, int64_t rows, const int8_t* samples_dev, const void* saved_dev,
+                   const double* seed_logp_dev, const double* seed_phase_dev, float* grad_dev, void* workspace_dev,
+                   int64_t workspace_bytes, void* stream) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (rows <= 0 || samples_dev == nullptr || saved_dev == nullptr || seed_logp_dev == nullptr || grad_dev == nullptr)
+    return fail(RNNWF_EINVAL, "rnnwf_backward: null argument or rows <= 0");
+  if (workspace_dev == nullptr || workspace_bytes < backward_workspace_bytes(*h, rows))
+    return fail(RNNWF_ENOMEM, "rnnwf_backward: workspace too small");
+  std::string err;
+  rc = backward_run(*h, rows, samples_dev, saved_dev, seed_logp_dev, seed_phase_dev, grad_dev, workspace_dev,
+                    static_cast<cudaStream_t>(stream), err);
+  if (rc) return fail(rc, err);
+  return RNNWF_OK;
+}
+
+int rnnwf_describe(rnnwf_handle h, char* buf, int cap) {
+  if (h == nullptr || buf == nullptr || cap <= 0) return fail(RNNWF_EINVAL, "null argument");
+  std::snprintf(buf, cap,
+                "cell=%d nh=%d (padded %d) steps=%d symbols=%d slots=%d classes=%d | pipe=FFMA fp32, tile=128 rows x %d col-groups "
+                "(TJ=%d NTU=%d WC=%d passes=%d), k-chunk=%d, ring=%d steps, params=%lld",
+                h->cell, h->nh, h->nhp, h->Q, h->Tsym, h->nslots, h->ncls_max, h->Gblk, h->TJ, h->NTU, h->WC, h->ncb, KC,
+                h->ring_len, (long long)h->num_params);
+  return RNNWF_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,193 @@
+"""Host-side engine: owns the C-ABI handle, the flat parameter vector and the device workspaces.
+
+PyTorch is used for device memory, streams and (in ``vmc.py``) ``torch.distributed`` only; every
+number on the hot path is produced by ``librnnwf.so``.
+"""
+import ctypes as C
+import math
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import lib, check, Config
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class Engine:
+    """One wavefunction on the current CUDA device.
+
+    cell: _lib.CELL_*;  nx, ny: lattice (chains: ny = 1; Rydberg: unit cells).
+    """
+
+    def __init__(self, cell, nx, ny=1, num_units=10, num_layers=1, complex_head=False, u1=False,
+                 magnetization=0, seed=111, device=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("rnnwavefunctions_b200 needs a CUDA device (there is no CPU fallback)")
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        torch.cuda.set_device(self.device)
+        self.cfg = Config(cell=cell, complex_head=int(bool(complex_head)), nx=nx, ny=ny, num_units=num_units,
+                          num_layers=num_layers, u1=int(bool(u1)), magnetization=magnetization)
+        self.cell, self.nx, self.ny, self.nh, self.num_layers = cell, nx, ny, num_units, num_layers
+        self.complex_head, self.u1 = bool(complex_head), bool(u1)
+        h = C.c_void_p()
+        check(lib.rnnwf_create(C.byref(self.cfg), C.byref(h)), "rnnwf_create")
+        self._h = h
+        self.num_params = int(lib.rnnwf_num_params(h))
+        self.tensors = []  # (name, offset, shape)
+        name = C.create_string_buffer(64)
+        for i in range(lib.rnnwf_num_tensors(h)):
+            off, nd, shp = C.c_int64(), C.c_int32(), (C.c_int64 * 4)()
+            check(lib.rnnwf_param_info(h, i, name, 64, C.byref(off), C.byref(nd), shp), "rnnwf_param_info")
+            self.tensors.append((name.value.decode(), int(off.value), tuple(int(shp[k]) for k in range(nd.value))))
+        if cell == _lib.CELL_GRU4:
+            self.cfg_shape = (nx, ny, 3)
+        elif ny == 1 and cell == _lib.CELL_GRU1D:
+            self.cfg_shape = (nx,)
+        else:
+            self.cfg_shape = (nx, ny)
+        self.nsteps = nx * ny  # symbols (= uniforms) per configuration
+        self.params = torch.zeros(self.num_params, dtype=torch.float32, device=self.device)
+        self._ws = None
+        self._eloc_ws = None
+        self._bwd_ws = None
+        self.init_params(seed)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                lib.rnnwf_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    # ---------------------------------------------------------------- parameters
+    def views(self, flat=None):
+        """dict name -> view of the flat parameter (or gradient) vector in TF layout."""
+        flat = self.params if flat is None else flat
+        return {n: flat[o:o + int(np.prod(s))].view(*s) for n, o, s in self.tensors}
+
+    def init_params(self, seed=111):
+        """Reference initialisers: glorot-uniform kernels (VarianceScaling(1, fan_avg, uniform)
+        for the MD cells, biases included), GRU gate bias 1, other GRU / dense biases 0."""
+        g = torch.Generator().manual_seed(int(seed))
+        flat = torch.zeros(self.num_params, dtype=torch.float32)
+        for n, o, s in self.tensors:
+            numel = int(np.prod(s))
+            base = n.split(".")[-1]
+            md_cell = self.cell != _lib.CELL_GRU1D and not n.startswith("dense")
+            if base in ("bg",) and not md_cell:
+                v = torch.ones(numel)
+            elif (base.startswith("b") and not md_cell) or n in ("dense.b", "dense_phase.b"):
+                v = torch.zeros(numel)
+            else:
+                if len(s) == 1:
+                    fan_in = fan_out = s[0]
+                elif len(s) == 2:
+                    fan_in, fan_out = s
+                else:
+                    rec = int(np.prod(s[:-2]))
+                    fan_in, fan_out = s[-2] * rec, s[-1] * rec
+                lim = math.sqrt(6.0 / (fan_in + fan_out))
+                v = (torch.rand(numel, generator=g, dtype=torch.float64) * 2 - 1) * lim
+            flat[o:o + numel] = v.to(torch.float32)
+        self.params.copy_(flat)
+        self.set_weights()
+
+    def set_weights(self, params=None):
+        if params is not None:
+            self.params.copy_(params.reshape(-1).to(self.params))
+        check(lib.rnnwf_set_weights(self._h, _ptr(self.params), _stream()), "rnnwf_set_weights")
+
+    # ---------------------------------------------------------------- workspaces
+    def _workspace(self):
+        if self._ws is None:
+            self._ws = torch.empty(int(lib.rnnwf_workspace_bytes(self._h)), dtype=torch.uint8, device=self.device)
+        return self._ws
+
+    def new_saved(self, rows):
+        return torch.empty(int(lib.rnnwf_saved_bytes(self._h, rows)), dtype=torch.uint8, device=self.device)
+
+    def _as_cfg(self, samples):
+        s = samples.to(device=self.device)
+        if s.dtype != torch.int8:
+            s = s.to(torch.int8)
+        s = s.contiguous()
+        if tuple(s.shape[1:]) != self.cfg_shape:
+            raise ValueError(f"configurations must have shape [B, {self.cfg_shape}], got {tuple(s.shape)}")
+        return s
+
+    # ---------------------------------------------------------------- hot path
+    def sample(self, numsamples, uniforms=None, seed=0, row_offset=0, saved=None):
+        """-> (samples int8 [B, *cfg_shape], logp float64 [B], phase float64 [B])."""
+        B = int(numsamples)
+        out = torch.empty((B,) + self.cfg_shape, dtype=torch.int8, device=self.device)
+        logp = torch.empty(B, dtype=torch.float64, device=self.device)
+        phase = torch.zeros(B, dtype=torch.float64, device=self.device)
+        u = None
+        if uniforms is not None:
+            u = uniforms.to(device=self.device, dtype=torch.float32).contiguous()
+            if tuple(u.shape) != (B, self.nsteps):
+                raise ValueError(f"uniforms must have shape [{B}, {self.nsteps}]")
+        ws = self._workspace()
+        check(lib.rnnwf_sample(self._h, B, _ptr(u), int(seed), int(row_offset), _ptr(out), _ptr(logp), _ptr(phase),
+                               _ptr(saved), _ptr(ws), ws.numel(), _stream()), "rnnwf_sample")
+        return out, logp, phase
+
+    def logpsi(self, samples, saved=None):
+        """-> (logp float64 [B], phase float64 [B]);  log psi = 0.5*logp + i*phase."""
+        s = self._as_cfg(samples)
+        B = s.shape[0]
+        logp = torch.empty(B, dtype=torch.float64, device=self.device)
+        phase = torch.zeros(B, dtype=torch.float64, device=self.device)
+        if B == 0:
+            return logp, phase
+        ws = self._workspace()
+        check(lib.rnnwf_logpsi(self._h, B, _ptr(s), _ptr(logp), _ptr(phase), _ptr(saved), _ptr(ws), ws.numel(), _stream()),
+              "rnnwf_logpsi")
+        return logp, phase
+
+    def local_energies(self, ham, ham_params, samples, logp=None, phase=None, saved=None, return_count=False):
+        """-> complex128 [B] (imaginary part 0 for the positive wavefunctions)."""
+        s = self._as_cfg(samples)
+        B = s.shape[0]
+        if logp is None:
+            logp, phase = self.logpsi(s)
+        hp = np.ascontiguousarray(np.asarray(ham_params, dtype=np.float64).reshape(-1))
+        need = int(lib.rnnwf_eloc_workspace_bytes(self._h, ham, B))
+        if self._eloc_ws is None or self._eloc_ws.numel() < need:
+            self._eloc_ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        eloc = torch.empty(B, 2, dtype=torch.float64, device=self.device)
+        ncount = torch.zeros(1, dtype=torch.int64, device=self.device)
+        check(lib.rnnwf_local_energies(self._h, ham, hp.ctypes.data_as(C.POINTER(C.c_double)), hp.size, B, _ptr(s),
+                                       _ptr(logp), _ptr(phase if self.complex_head else None), _ptr(saved), _ptr(eloc),
+                                       _ptr(ncount), _ptr(self._eloc_ws), self._eloc_ws.numel(), _stream()),
+              "rnnwf_local_energies")
+        e = torch.view_as_complex(eloc)
+        return (e, ncount) if return_count else e
+
+    def backward(self, samples, saved, seed_logp, seed_phase=None):
+        """-> float32 [num_params]: sum_b seed_logp[b] dlogP_b/dtheta + seed_phase[b] dphase_b/dtheta."""
+        s = self._as_cfg(samples)
+        B = s.shape[0]
+        need = int(lib.rnnwf_backward_workspace_bytes(self._h, B))
+        if self._bwd_ws is None or self._bwd_ws.numel() < need:
+            self._bwd_ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        grad = torch.empty(self.num_params, dtype=torch.float32, device=self.device)
+        sl = seed_logp.to(device=self.device, dtype=torch.float64).contiguous()
+        sp = None if seed_phase is None else seed_phase.to(device=self.device, dtype=torch.float64).contiguous()
+        check(lib.rnnwf_backward(self._h, B, _ptr(s), _ptr(saved), _ptr(sl), _ptr(sp), _ptr(grad), _ptr(self._bwd_ws),
+                                 self._bwd_ws.numel(), _stream()), "rnnwf_backward")
+        return grad
+
+    def describe(self):
+        buf = C.create_string_buffer(512)
+        check(lib.rnnwf_describe(self._h, buf, 512), "rnnwf_describe")
+        return buf.value.decode()
