@@ -1,14 +1,545 @@
-// Backward of log psi (BPTT over the lattice sweep) -- placeholder until the kernels land.
+// Backward of log psi: hand-written back-propagation through the lattice sweep.
+//
+// grad[k] = sum_b seed_logp[b] dlogP_b/dtheta_k + seed_phase[b] dphase_b/dtheta_k  -- what TF autodiff of
+// the reference's surrogate costs yields (1DTFIM/TrainingRNN_1DTFIM.py:157-161, J1J2/TrainingRNN_J1J2.py:197-200,
+// 2DHeisenberg/Run_RNNWF_2DHeis.py:199-217, RydbergKagome_2DGRU/Run_RNNWF_Rydberg.py:158-176).
+//
+// The sweep is walked in reverse generation order over the saved hidden-state history and gate
+// activations of the samples (written by the forward sweep).  Per step: head backward (softmax / U(1)
+// mask / phase), cell non-linearity backward (element-wise), then the three GEMM shapes of a dense layer
+// backward, written here as plain FP32 FFMA tiles: dX = dY W^T (gemm_nt), dX = dY W (gemm_nn) and
+// dW += X^T dY (gemm_tn_atomic, split over the batch).  The operands are the reference-form ones (the
+// expanded outer product h (x) x of the tensorized cells, the concatenated [x, h] of the GRUs), so the
+// weight gradients land directly in the TF parameter layout.  Backward runs on `numsamples` rows only,
+// i.e. ~1-3% of the rows a VMC step pushes through the forward sweep for its local energies.
 #pragma once
 #include <string>
+
 #include "model.h"
 
 namespace rnnwf {
-inline cudaError_t backward_init() { return cudaSuccess; }
-inline long long backward_workspace_bytes(const rnnwf_model_impl&, long long) { return 256; }
-inline int backward_run(const rnnwf_model_impl&, long long, const int8_t*, const void*, const double*, const double*,
-                        float*, void*, cudaStream_t, std::string& err) {
-  err = "rnnwf_backward: not implemented yet";
-  return RNNWF_ESTATE;
+
+// ------------------------------------------------------------------------------------------------
+// generic FP32 GEMM tiles (64x64x16, 256 threads, 4x4 per thread)
+// ------------------------------------------------------------------------------------------------
+constexpr int GB = 64, GK = 16;
+
+// C[M,N] (+)= A[M,K] * B[N,K]^T
+__global__ void __launch_bounds__(256) gemm_nt_kernel(const float* __restrict__ A, int lda, const float* __restrict__ B,
+                                                      int ldb, float* __restrict__ C, int ldc, int M, int N, int K, int beta) {
+  __shared__ float As[GK][GB + 4], Bs[GK][GB + 4];
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  const long long m0 = (long long)blockIdx.y * GB;
+  const int n0 = blockIdx.x * GB;
+  float acc[4][4] = {};
+  for (int k0 = 0; k0 < K; k0 += GK) {
+    for (int i = threadIdx.x; i < GB * GK; i += 256) {
+      const int r = i / GK, k = i % GK;
+      As[k][r] = (m0 + r < M && k0 + k < K) ? A[(m0 + r) * lda + k0 + k] : 0.f;
+      Bs[k][r] = (n0 + r < N && k0 + k < K) ? B[(long long)(n0 + r) * ldb + k0 + k] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < GK; ++k) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { a[i] = As[k][ty * 4 + i]; b[i] = Bs[k][tx * 4 + i]; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j) {
+      const long long m = m0 + ty * 4 + i;
+      const int n = n0 + tx * 4 + j;
+      if (m < M && n < N) { float* c = C + m * ldc + n; *c = beta ? (*c + acc[i][j]) : acc[i][j]; }
+    }
 }
+
+// C[M,N] (+)= A[M,K] * B[K,N]
+__global__ void __launch_bounds__(256) gemm_nn_kernel(const float* __restrict__ A, int lda, const float* __restrict__ B,
+                                                      int ldb, float* __restrict__ C, int ldc, int M, int N, int K, int beta) {
+  __shared__ float As[GK][GB + 4], Bs[GK][GB + 4];
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  const long long m0 = (long long)blockIdx.y * GB;
+  const int n0 = blockIdx.x * GB;
+  float acc[4][4] = {};
+  for (int k0 = 0; k0 < K; k0 += GK) {
+    for (int i = threadIdx.x; i < GB * GK; i += 256) {
+      const int r = i / GK, k = i % GK;
+      As[k][r] = (m0 + r < M && k0 + k < K) ? A[(m0 + r) * lda + k0 + k] : 0.f;
+      const int kk = i / GB, c = i % GB;
+      Bs[kk][c] = (k0 + kk < K && n0 + c < N) ? B[(long long)(k0 + kk) * ldb + n0 + c] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < GK; ++k) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { a[i] = As[k][ty * 4 + i]; b[i] = Bs[k][tx * 4 + i]; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j) {
+      const long long m = m0 + ty * 4 + i;
+      const int n = n0 + tx * 4 + j;
+      if (m < M && n < N) { float* c = C + m * ldc + n; *c = beta ? (*c + acc[i][j]) : acc[i][j]; }
+    }
+}
+
+// C[K1,N] += A[M,K1]^T * B[M,N]; blockIdx.z splits the batch dimension M, partial tiles are added atomically
+__global__ void __launch_bounds__(256) gemm_tn_atomic_kernel(const float* __restrict__ A, int lda, const float* __restrict__ B,
+                                                             int ldb, float* __restrict__ C, int ldc, long long M, int K1, int N,
+                                                             long long mchunk) {
+  __shared__ float As[GK][GB + 4], Bs[GK][GB + 4];
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  const int k0 = blockIdx.y * GB, n0 = blockIdx.x * GB;
+  const long long mlo = (long long)blockIdx.z * mchunk;
+  const long long mhi = (mlo + mchunk < M) ? mlo + mchunk : M;
+  float acc[4][4] = {};
+  for (long long m0 = mlo; m0 < mhi; m0 += GK) {
+    for (int i = threadIdx.x; i < GB * GK; i += 256) {
+      const int mm = i / GB, c = i % GB;
+      const bool mok = m0 + mm < mhi;
+      As[mm][c] = (mok && k0 + c < K1) ? A[(m0 + mm) * lda + k0 + c] : 0.f;
+      Bs[mm][c] = (mok && n0 + c < N) ? B[(m0 + mm) * ldb + n0 + c] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < GK; ++k) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { a[i] = As[k][ty * 4 + i]; b[i] = Bs[k][tx * 4 + i]; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j) {
+      const int kk = k0 + ty * 4 + i, n = n0 + tx * 4 + j;
+      if (kk < K1 && n < N && acc[i][j] != 0.f) atomicAdd(C + (long long)kk * ldc + n, acc[i][j]);
+    }
+}
+
+// out[n] += sum_m X[m, n]
+__global__ void colsum_atomic_kernel(const float* __restrict__ X, int ldx, long long M, int N, float* __restrict__ out) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  const long long chunk = (M + gridDim.y - 1) / gridDim.y;
+  const long long lo = blockIdx.y * chunk, hi = (lo + chunk < M) ? lo + chunk : M;
+  float s = 0.f;
+  for (long long m = lo; m < hi; ++m) s += X[m * ldx + n];
+  if (s != 0.f) atomicAdd(out + n, s);
+}
+
+// ------------------------------------------------------------------------------------------------
+// per-step element-wise kernels
+// ------------------------------------------------------------------------------------------------
+struct BwdStep {
+  int q, t, cell, nh, nhp, Gp, D, ND, complex_head, u1, cap_up, cap_dn, bits, nsites, Tsym, L;
+  int nbr[MAX_SLOTS], nsym_site[MAX_SLOTS];  // history index / configuration offset of each slot (-1 = none)
+  int sym_site;                              // configuration offset of this step's own symbol
+  long long R;
+  const int8_t* cfg;
+  const float* hist;      // [Q][R][nhp]
+  const float4* gates;    // [Q][R][Gp]
+  float* dh;              // [Q][R][nhp]
+};
+
+__device__ __forceinline__ int cfg_symbol(const int8_t* row, int site, int bits) {
+  if (bits == 1) return row[site] & 1;
+  return (row[site * 3] & 1) | ((row[site * 3 + 1] & 1) << 1) | ((row[site * 3 + 2] & 1) << 2);
+}
+
+// One warp per row: recompute the heads from the saved hidden state, form d(logits), push it into dh.
+__global__ void head_bwd_kernel(const BwdStep S, const int16_t* __restrict__ site_of_t, const float* __restrict__ head_w,
+                                const float* __restrict__ head_b, const double* __restrict__ seed_logp,
+                                const double* __restrict__ seed_phase, float* __restrict__ dlog) {
+  const int lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= S.R) return;
+  const float* h = S.hist + ((long long)S.q * S.R + row) * S.nhp;
+  float part[8];
+#pragma unroll
+  for (int d = 0; d < 8; ++d) part[d] = 0.f;
+  for (int j = lane; j < S.nh; j += 32) {
+    const float hv = h[j];
+#pragma unroll
+    for (int d = 0; d < 8; ++d) if (d < S.ND) part[d] = fmaf(hv, head_w[j * S.ND + d], part[d]);
+  }
+#pragma unroll
+  for (int d = 0; d < 8; ++d)
+    if (d < S.ND)
+      for (int o = 16; o > 0; o >>= 1) part[d] += __shfl_xor_sync(0xffffffffu, part[d], o);
+  const int8_t* crow = S.cfg + row * S.nsites;
+  const int s = cfg_symbol(crow, S.sym_site, S.bits);
+  float p[8];
+  float mx = -INFINITY;
+#pragma unroll
+  for (int d = 0; d < 8; ++d) if (d < S.D) { p[d] = part[d] + head_b[d]; mx = fmaxf(mx, p[d]); } else p[d] = 0.f;
+  float ssum = 0.f;
+#pragma unroll
+  for (int d = 0; d < 8; ++d) if (d < S.D) { p[d] = expf(p[d] - mx); ssum += p[d]; }
+#pragma unroll
+  for (int d = 0; d < 8; ++d) p[d] /= ssum;
+  if (S.u1) {
+    int nup = 0;
+    for (int tt = lane; tt < S.t; tt += 32) nup += crow[site_of_t[tt]] & 1;
+    for (int o = 16; o > 0; o >>= 1) nup += __shfl_xor_sync(0xffffffffu, nup, o);
+    const int ndn = S.t - nup;
+    p[0] *= (S.cap_dn - ndn >= 0) ? 1.f : 0.f;
+    p[1] *= (S.cap_up - nup >= 0) ? 1.f : 0.f;
+    const float nrm = p[0] + p[1];
+    p[0] /= nrm;
+    p[1] /= nrm;
+  }
+  const float sl = (float)seed_logp[row];
+  float dl[8];
+#pragma unroll
+  for (int d = 0; d < 8; ++d) dl[d] = (d < S.D) ? sl * (((d == s) ? 1.f : 0.f) - p[d]) : 0.f;
+  if (S.complex_head) {
+    const float sp = (seed_phase != nullptr) ? (float)seed_phase[row] : 0.f;
+    const float x = ((s == 0) ? part[2] : part[3]) + ((s == 0) ? head_b[2] : head_b[3]);
+    const float den = 1.f + fabsf(x);
+    const float g = sp * 3.14159265358979f / (den * den);
+    dl[2] = (s == 0) ? g : 0.f;
+    dl[3] = (s == 1) ? g : 0.f;
+  }
+  if (lane == 0)
+    for (int d = 0; d < S.ND; ++d) dlog[row * S.ND + d] = dl[d];
+  float* dh = S.dh + ((long long)S.q * S.R + row) * S.nhp;
+  for (int j = lane; j < S.nh; j += 32) {
+    float a = 0.f;
+#pragma unroll
+    for (int d = 0; d < 8; ++d) if (d < S.ND) a = fmaf(head_w[j * S.ND + d], dl[d], a);
+    dh[j] += a;
+  }
+}
+
+// d(pre-activations) of the cell from d(new state); blocks of `dpre`: each [R][nh] (GRU1D block 0 is [R][2nh])
+__global__ void cell_bwd_kernel(const BwdStep S, float* __restrict__ dp0, float* __restrict__ dp1, float* __restrict__ dp2) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= S.R * S.nh) return;
+  const long long row = idx / S.nh;
+  const int j = (int)(idx - row * S.nh);
+  const float dhp = S.dh[((long long)S.q * S.R + row) * S.nhp + j];
+  if (S.cell == CELL_TENSGRU2D || S.cell == CELL_GRU4) {
+    const float4 g = S.gates[((long long)S.q * S.R + row) * S.Gp + j];  // (u, ht, m, -)
+    dp0[idx] = dhp * g.x * (1.f - g.y * g.y);
+    dp1[idx] = dhp * (g.y - g.z) * g.x * (1.f - g.x);
+    dp2[idx] = dhp * (1.f - g.x);
+  } else if (S.cell == CELL_GRU1D) {
+    const float4 g = S.gates[((long long)S.q * S.R + row) * S.Gp + j];  // (r, u, c, hh)
+    float hown = 0.f;
+    if (S.nbr[0] >= 0) {
+      hown = S.hist[((long long)S.nbr[0] * S.R + row) * S.nhp + j];
+      S.dh[((long long)S.nbr[0] * S.R + row) * S.nhp + j] += dhp * g.y;
+    }
+    const float du = dhp * (hown - g.z), dc = dhp * (1.f - g.y);
+    const float dcp = dc * (1.f - g.z * g.z);
+    dp0[row * 2 * S.nh + j] = dcp * g.w * g.x * (1.f - g.x);   // d r_pre
+    dp0[row * 2 * S.nh + S.nh + j] = du * g.y * (1.f - g.y);   // d u_pre
+    dp1[idx] = dcp;                                            // d (x Wci + bci)
+    dp2[idx] = dcp * g.x;                                      // d (h Wch + bch)
+  } else {
+    const float hv = S.hist[((long long)S.q * S.R + row) * S.nhp + j];
+    dp0[idx] = (S.cell == CELL_VANILLA2D) ? dhp * (hv > 0.f ? 1.f : hv + 1.f) : dhp * (1.f - hv * hv);
+  }
+}
+
+// tensorized cells: T[row][i*4+k] = hc_i * xc_k and hc[row][i]
+__global__ void build_tens_kernel(const BwdStep S, float* __restrict__ T, float* __restrict__ hc) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int nh2 = 2 * S.nh;
+  if (idx >= S.R * nh2) return;
+  const long long row = idx / nh2;
+  const int i = (int)(idx - row * nh2);
+  const int slot = i / S.nh, k = i - slot * S.nh;
+  const float hv = (S.nbr[slot] >= 0) ? S.hist[((long long)S.nbr[slot] * S.R + row) * S.nhp + k] : 0.f;
+  const int8_t* crow = S.cfg + row * S.nsites;
+  float xc[4] = {0.f, 0.f, 0.f, 0.f};
+  if (S.nsym_site[0] >= 0) xc[crow[S.nsym_site[0]] & 1] = 1.f;
+  if (S.nsym_site[1] >= 0) xc[2 + (crow[S.nsym_site[1]] & 1)] = 1.f;
+  hc[idx] = hv;
+  *reinterpret_cast<float4*>(T + idx * 4) = make_float4(hv * xc[0], hv * xc[1], hv * xc[2], hv * xc[3]);
+}
+
+__global__ void scatter_tens_kernel(const BwdStep S, const float* __restrict__ dT, const float* __restrict__ dhc) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int nh2 = 2 * S.nh;
+  if (idx >= S.R * nh2) return;
+  const long long row = idx / nh2;
+  const int i = (int)(idx - row * nh2);
+  const int slot = i / S.nh, k = i - slot * S.nh;
+  if (S.nbr[slot] < 0) return;
+  const int8_t* crow = S.cfg + row * S.nsites;
+  const float4 d = *reinterpret_cast<const float4*>(dT + idx * 4);
+  float v = (dhc != nullptr) ? dhc[idx] : 0.f;
+  if (S.nsym_site[0] >= 0) v += (crow[S.nsym_site[0]] & 1) ? d.y : d.x;
+  if (S.nsym_site[1] >= 0) v += (crow[S.nsym_site[1]] & 1) ? d.w : d.z;
+  S.dh[((long long)S.nbr[slot] * S.R + row) * S.nhp + k] += v;
+}
+
+// Rydberg cell: z[row] = [x0..x3 (one-hots of 3 bits, 6 wide each), h0..h3]
+__global__ void build_gru4_kernel(const BwdStep S, float* __restrict__ z) {
+  const int Kz = 24 + 4 * S.nh;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= S.R * Kz) return;
+  const long long row = idx / Kz;
+  const int c = (int)(idx - row * Kz);
+  float v = 0.f;
+  if (c < 24) {
+    const int slot = c / 6, b = (c % 6) >> 1, bit = c & 1;
+    if (S.nsym_site[slot] >= 0) v = ((S.cfg[row * S.nsites + S.nsym_site[slot] * 3 + b] & 1) == bit) ? 1.f : 0.f;
+  } else {
+    const int slot = (c - 24) / S.nh, k = (c - 24) - slot * S.nh;
+    if (S.nbr[slot] >= 0) v = S.hist[((long long)S.nbr[slot] * S.R + row) * S.nhp + k];
+  }
+  z[idx] = v;
+}
+
+__global__ void scatter_gru4_kernel(const BwdStep S, const float* __restrict__ dz) {
+  const int Kz = 24 + 4 * S.nh, nh4 = 4 * S.nh;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= S.R * nh4) return;
+  const long long row = idx / nh4;
+  const int i = (int)(idx - row * nh4);
+  const int slot = i / S.nh, k = i - slot * S.nh;
+  if (S.nbr[slot] < 0) return;
+  S.dh[((long long)S.nbr[slot] * S.R + row) * S.nhp + k] += dz[row * Kz + 24 + i];
+}
+
+// one-hot inputs of the two-neighbour / chain models: X[row][2*slot + v]
+__global__ void build_onehot_kernel(const BwdStep S, int nslots, float* __restrict__ X) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= S.R * nslots) return;
+  const long long row = idx / nslots;
+  const int slot = (int)(idx - row * nslots);
+  float a = 0.f, b = 0.f;
+  if (S.nsym_site[slot] >= 0) { if (S.cfg[row * S.nsites + S.nsym_site[slot]] & 1) b = 1.f; else a = 1.f; }
+  X[idx * 2] = a;
+  X[idx * 2 + 1] = b;
+}
+
+// ------------------------------------------------------------------------------------------------
+// orchestration
+// ------------------------------------------------------------------------------------------------
+inline cudaError_t backward_init() { return cudaSuccess; }
+
+struct BwdLayout { long long off_dh, off_dp, off_Z, off_dZ, off_hc, off_dhc, off_dlog, off_X, total; long long dpw; int Kz; };
+
+inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
+  auto al = [](long long x) { return (x + 255) & ~255LL; };
+  BwdLayout L;
+  const long long nh = m.nh;
+  L.Kz = (m.cell == CELL_TENS2D || m.cell == CELL_TENSGRU2D) ? 8 * m.nh : (m.cell == CELL_GRU4 ? 24 + 4 * m.nh : 0);
+  L.dpw = (m.cell == CELL_GRU1D) ? 4 * nh : 3 * nh;
+  long long o = 0;
+  L.off_dh = o;   o += al((long long)m.Q * R * m.nhp * 4);
+  L.off_dp = o;   o += al(R * L.dpw * 4);
+  L.off_Z = o;    o += al(R * (long long)L.Kz * 4);
+  L.off_dZ = o;   o += al(R * (long long)L.Kz * 4);
+  L.off_hc = o;   o += al(R * 2 * nh * 4);
+  L.off_dhc = o;  o += al(R * 2 * nh * 4);
+  L.off_dlog = o; o += al(R * 8 * 4);
+  L.off_X = o;    o += al(R * 8 * 4);
+  L.total = o;
+  return L;
+}
+
+inline long long backward_workspace_bytes(const rnnwf_model_impl& m, long long R) { return backward_layout(m, R).total; }
+
+struct Gemm {
+  cudaStream_t st;
+  void nt(const float* A, int lda, const float* B, int ldb, float* C, int ldc, long long M, int N, int K, int beta) const {
+    if (M <= 0 || N <= 0 || K <= 0) return;
+    dim3 g((N + GB - 1) / GB, (unsigned)((M + GB - 1) / GB));
+    gemm_nt_kernel<<<g, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, N, K, beta);
+  }
+  void nn(const float* A, int lda, const float* B, int ldb, float* C, int ldc, long long M, int N, int K, int beta) const {
+    if (M <= 0 || N <= 0 || K <= 0) return;
+    dim3 g((N + GB - 1) / GB, (unsigned)((M + GB - 1) / GB));
+    gemm_nn_kernel<<<g, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, N, K, beta);
+  }
+  void tn(const float* A, int lda, const float* B, int ldb, float* C, int ldc, long long M, int K1, int N) const {
+    if (M <= 0 || N <= 0 || K1 <= 0) return;
+    const int tiles = ((N + GB - 1) / GB) * ((K1 + GB - 1) / GB);
+    long long split = (592 + tiles - 1) / tiles;                 // ~4 CTAs per SM in flight
+    const long long maxsplit = (M + 255) / 256;
+    if (split > maxsplit) split = maxsplit;
+    if (split < 1) split = 1;
+    long long mchunk = ((M + split - 1) / split + GK - 1) / GK * GK;
+    split = (M + mchunk - 1) / mchunk;
+    dim3 g((N + GB - 1) / GB, (K1 + GB - 1) / GB, (unsigned)split);
+    gemm_tn_atomic_kernel<<<g, 256, 0, st>>>(A, lda, B, ldb, C, ldc, M, K1, N, mchunk);
+  }
+  void colsum(const float* X, int ldx, long long M, int N, float* out) const {
+    if (M <= 0 || N <= 0) return;
+    dim3 g((N + 127) / 128, (unsigned)std::max<long long>(1, std::min<long long>(64, M / 256)));
+    colsum_atomic_kernel<<<g, 128, 0, st>>>(X, ldx, M, N, out);
+  }
+};
+
+inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cfg, const void* saved,
+                        const double* seed_logp, const double* seed_phase, float* grad, void* workspace,
+                        cudaStream_t st, std::string& err) {
+  if (R > 0x7fffffffLL / std::max(1, m.nhp)) { err = "rnnwf_backward: too many rows"; return RNNWF_EINVAL; }
+  const Saved sv = m.saved_layout(R);
+  const char* sb = static_cast<const char*>(saved);
+  const float* hist = reinterpret_cast<const float*>(sb + sv.off_hist);
+  const float4* gates = reinterpret_cast<const float4*>(sb + sv.off_gates);
+  const BwdLayout L = backward_layout(m, R);
+  char* ws = static_cast<char*>(workspace);
+  float* dh = reinterpret_cast<float*>(ws + L.off_dh);
+  float* dp = reinterpret_cast<float*>(ws + L.off_dp);
+  float* Z = reinterpret_cast<float*>(ws + L.off_Z);
+  float* dZ = reinterpret_cast<float*>(ws + L.off_dZ);
+  float* hc = reinterpret_cast<float*>(ws + L.off_hc);
+  float* dhc = reinterpret_cast<float*>(ws + L.off_dhc);
+  float* dlog = reinterpret_cast<float*>(ws + L.off_dlog);
+  float* X = reinterpret_cast<float*>(ws + L.off_X);
+  const float* params = m.d_params;
+  const int nh = m.nh, nhp = m.nhp;
+  Gemm G{st};
+
+  cudaError_t e = cudaMemsetAsync(dh, 0, (size_t)m.Q * R * nhp * 4, st);
+  if (e == cudaSuccess) e = cudaMemsetAsync(grad, 0, (size_t)m.num_params * 4, st);
+  if (e != cudaSuccess) { err = std::string("rnnwf_backward memset: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
+
+  auto P = [&](const std::string& n) { return params + m.tensor(n)->offset; };
+  auto Gd = [&](const std::string& n) { return grad + m.tensor(n)->offset; };
+  const int tpb = 256;
+  auto nblk = [&](long long n) { return (unsigned)((n + tpb - 1) / tpb); };
+  auto hrow = [&](int q) { return hist + (long long)q * R * nhp; };
+  auto dhrow = [&](int q) { return dh + (long long)q * R * nhp; };
+
+  for (int q = m.Q - 1; q >= 0; --q) {
+    const StepMeta& sm = m.steps[q];
+    BwdStep S;
+    std::memset(&S, 0, sizeof(S));
+    S.q = q; S.t = sm.sym; S.cell = m.cell; S.nh = nh; S.nhp = nhp; S.Gp = m.Gp; S.D = m.D; S.ND = m.ND;
+    S.complex_head = m.complex_head; S.u1 = m.u1; S.cap_up = m.cap_up; S.cap_dn = m.cap_dn; S.bits = m.bits;
+    S.nsites = m.nsites; S.Tsym = m.Tsym; S.L = m.symL; S.R = R; S.cfg = cfg; S.hist = hist; S.gates = gates; S.dh = dh;
+    for (int k = 0; k < MAX_SLOTS; ++k) {
+      S.nbr[k] = sm.nbr[k];
+      S.nsym_site[k] = (sm.nsym[k] >= 0) ? m.site_of_t[sm.nsym[k]] : -1;
+    }
+    S.sym_site = sm.site;
+
+    if (sm.head) {
+      const int wpb = 8;
+      head_bwd_kernel<<<(unsigned)((R + wpb - 1) / wpb), wpb * 32, 0, st>>>(S, m.d_site_of_t, m.d_head_w, m.d_head_b, seed_logp, seed_phase, dlog);
+      G.tn(hrow(q), nhp, dlog, m.ND, Gd("dense.W"), m.D, R, nh, m.D);
+      G.colsum(dlog, m.ND, R, m.D, Gd("dense.b"));
+      if (m.complex_head) {
+        G.tn(hrow(q), nhp, dlog + m.D, m.ND, Gd("dense_phase.W"), 2, R, nh, 2);
+        G.colsum(dlog + m.D, m.ND, R, 2, Gd("dense_phase.b"));
+      }
+    }
+    float* dp0 = dp;
+    float* dp1 = dp + ((m.cell == CELL_GRU1D) ? 2 * R * nh : R * nh);
+    float* dp2 = dp1 + R * nh;
+    cell_bwd_kernel<<<nblk(R * nh), tpb, 0, st>>>(S, dp0, dp1, dp2);
+
+    switch (m.cell) {
+      case CELL_TENS2D:
+      case CELL_TENSGRU2D: {
+        const bool gru = m.cell == CELL_TENSGRU2D;
+        const int K8 = 8 * nh;
+        if (sm.nbr[0] < 0 && sm.nbr[1] < 0) {  // first site: no inputs, only the biases receive gradient
+          G.colsum(dp0, nh, R, nh, Gd("b"));
+          if (gru) G.colsum(dp1, nh, R, nh, Gd("bg"));
+          break;
+        }
+        build_tens_kernel<<<nblk(R * 2 * nh), tpb, 0, st>>>(S, Z, hc);
+        G.nn(dp0, nh, P("W"), K8, dZ, K8, R, K8, nh, 0);                 // dT  = ds W2
+        G.tn(dp0, nh, Z, K8, Gd("W"), K8, R, nh, K8);                     // dW2 += ds^T T
+        G.colsum(dp0, nh, R, nh, Gd("b"));
+        if (gru) {
+          G.nn(dp1, nh, P("Wg"), K8, dZ, K8, R, K8, nh, 1);              // dT += dg Wg2
+          G.tn(dp1, nh, Z, K8, Gd("Wg"), K8, R, nh, K8);
+          G.colsum(dp1, nh, R, nh, Gd("bg"));
+          G.nt(dp2, nh, P("Wmerge"), nh, dhc, 2 * nh, R, 2 * nh, nh, 0);  // dhc = dm Wmerge^T
+          G.tn(hc, 2 * nh, dp2, nh, Gd("Wmerge"), nh, R, 2 * nh, nh);     // dWmerge += hc^T dm
+        }
+        scatter_tens_kernel<<<nblk(R * 2 * nh), tpb, 0, st>>>(S, dZ, gru ? dhc : nullptr);
+        break;
+      }
+      case CELL_GRU4: {
+        const int Kz = 24 + 4 * nh;
+        build_gru4_kernel<<<nblk(R * Kz), tpb, 0, st>>>(S, Z);
+        G.nt(dp0, nh, P("W"), nh, dZ, Kz, R, Kz, nh, 0);                  // dz  = ds W^T
+        G.nt(dp1, nh, P("Wg"), nh, dZ, Kz, R, Kz, nh, 1);                 // dz += dg Wg^T
+        G.nt(dp2, nh, P("Wmerge"), nh, dZ + 24, Kz, R, 4 * nh, nh, 1);    // dz[:,24:] += dm Wmerge^T
+        G.tn(Z, Kz, dp0, nh, Gd("W"), nh, R, Kz, nh);
+        G.tn(Z, Kz, dp1, nh, Gd("Wg"), nh, R, Kz, nh);
+        G.tn(Z + 24, Kz, dp2, nh, Gd("Wmerge"), nh, R, 4 * nh, nh);
+        G.colsum(dp0, nh, R, nh, Gd("b"));
+        G.colsum(dp1, nh, R, nh, Gd("bg"));
+        scatter_gru4_kernel<<<nblk(R * 4 * nh), tpb, 0, st>>>(S, dZ);
+        break;
+      }
+      case CELL_VANILLA2D: {
+        build_onehot_kernel<<<nblk(R * 2), tpb, 0, st>>>(S, 2, X);       // X[row] = [x_h (2), x_v (2)]
+        G.tn(X, 4, dp0, nh, Gd("Uh"), nh, R, 2, nh);
+        G.tn(X + 2, 4, dp0, nh, Gd("Uv"), nh, R, 2, nh);
+        G.colsum(dp0, nh, R, nh, Gd("b"));
+        if (sm.nbr[0] >= 0) {
+          G.tn(hrow(sm.nbr[0]), nhp, dp0, nh, Gd("Wh"), nh, R, nh, nh);
+          G.nt(dp0, nh, P("Wh"), nh, dhrow(sm.nbr[0]), nhp, R, nh, nh, 1);
+        }
+        if (sm.nbr[1] >= 0) {
+          G.tn(hrow(sm.nbr[1]), nhp, dp0, nh, Gd("Wv"), nh, R, nh, nh);
+          G.nt(dp0, nh, P("Wv"), nh, dhrow(sm.nbr[1]), nhp, R, nh, nh, 1);
+        }
+        break;
+      }
+      case CELL_GRU1D: {
+        const int l = sm.variant;
+        const int din = (l == 0) ? 2 : nh;
+        const std::string p = "gru" + std::to_string(l) + ".";
+        const float* Wg = P(p + "Wg");
+        float* dWg = Gd(p + "Wg");
+        G.colsum(dp0, 2 * nh, R, 2 * nh, Gd(p + "bg"));
+        G.colsum(dp1, nh, R, nh, Gd(p + "bci"));
+        G.colsum(dp2, nh, R, nh, Gd(p + "bch"));
+        if (sm.nbr[0] >= 0) {  // own previous state h
+          G.tn(hrow(sm.nbr[0]), nhp, dp0, 2 * nh, dWg + (long long)din * 2 * nh, 2 * nh, R, nh, 2 * nh);
+          G.tn(hrow(sm.nbr[0]), nhp, dp2, nh, Gd(p + "Wch"), nh, R, nh, nh);
+          G.nt(dp0, 2 * nh, Wg + (long long)din * 2 * nh, 2 * nh, dhrow(sm.nbr[0]), nhp, R, nh, 2 * nh, 1);
+          G.nt(dp2, nh, P(p + "Wch"), nh, dhrow(sm.nbr[0]), nhp, R, nh, nh, 1);
+        }
+        if (l == 0) {          // one-hot input of the previous spin
+          if (sm.nsym[0] >= 0) {
+            build_onehot_kernel<<<nblk(R), tpb, 0, st>>>(S, 1, X);
+            G.tn(X, 2, dp0, 2 * nh, dWg, 2 * nh, R, 2, 2 * nh);
+            G.tn(X, 2, dp1, nh, Gd(p + "Wci"), nh, R, 2, nh);
+          }
+        } else {               // dense input from the layer below (same lattice site)
+          const int qb = sm.nbr[1];
+          G.tn(hrow(qb), nhp, dp0, 2 * nh, dWg, 2 * nh, R, nh, 2 * nh);
+          G.tn(hrow(qb), nhp, dp1, nh, Gd(p + "Wci"), nh, R, nh, nh);
+          G.nt(dp0, 2 * nh, Wg, 2 * nh, dhrow(qb), nhp, R, nh, 2 * nh, 1);
+          G.nt(dp1, nh, P(p + "Wci"), nh, dhrow(qb), nhp, R, nh, nh, 1);
+        }
+        break;
+      }
+    }
+  }
+  e = cudaGetLastError();
+  if (e != cudaSuccess) { err = std::string("rnnwf_backward kernels: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
+  return RNNWF_OK;
+}
+
 }  // namespace rnnwf

@@ -1,0 +1,67 @@
+"""GPU parity of the hand-written backward against the oracle's autograd (torch float64 on the CPU) of the
+reference's surrogate costs, through the C-ABI.  Tolerance: 1e-4 of the largest gradient entry of each
+tensor (FP32 kernels with atomically accumulated weight gradients vs a float64 reference)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import costs
+from rnnwavefunctions_b200 import _lib
+from rnnwavefunctions_b200.engine import Engine
+from helpers import oracle_params, oracle_run
+
+MODELS = {
+    "gru1d": dict(cell=_lib.CELL_GRU1D, nx=12, ny=1, num_units=20, num_layers=1),
+    "gru1d_3layer": dict(cell=_lib.CELL_GRU1D, nx=8, ny=1, num_units=14, num_layers=3),
+    "cgru1d_u1": dict(cell=_lib.CELL_GRU1D, nx=10, ny=1, num_units=17, complex_head=True, u1=True),
+    "vanilla2d": dict(cell=_lib.CELL_VANILLA2D, nx=4, ny=4, num_units=18),
+    "tens2d_u1": dict(cell=_lib.CELL_TENS2D, nx=4, ny=4, num_units=11, complex_head=True, u1=True),
+    "tensgru2d_u1": dict(cell=_lib.CELL_TENSGRU2D, nx=4, ny=4, num_units=20, complex_head=True, u1=True),
+    "tensgru2d_free": dict(cell=_lib.CELL_TENSGRU2D, nx=3, ny=4, num_units=9, complex_head=True),
+    "rydberg": dict(cell=_lib.CELL_GRU4, nx=3, ny=3, num_units=24),
+}
+
+
+def _randomize(eng, seed):
+    g = torch.Generator().manual_seed(seed)
+    p = eng.params.cpu()
+    eng.set_weights(p + 0.15 * (torch.rand(p.shape, generator=g) - 0.5))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", list(MODELS))
+@pytest.mark.parametrize("from_sampling", [True, False])
+def test_gradient_matches_oracle_autograd(cuda, name, from_sampling):
+    ns = 257
+    eng = Engine(seed=31, **MODELS[name])
+    _randomize(eng, 32)
+    g = torch.Generator().manual_seed(33)
+    saved = eng.new_saved(ns)
+    u = torch.rand(ns, eng.nsteps, generator=g, dtype=torch.float32)
+    if from_sampling:
+        s, lp, ph = eng.sample(ns, uniforms=u, saved=saved)
+    else:
+        s, _, _ = eng.sample(ns, uniforms=u)
+        lp, ph = eng.logpsi(s, saved=saved)
+    # arbitrary (complex) "local energies": the seeds of the reference's surrogate costs
+    Er = torch.randn(ns, generator=g, dtype=torch.float64)
+    Ei = torch.randn(ns, generator=g, dtype=torch.float64)
+    P = oracle_params(eng, requires_grad=True)
+    ref = oracle_run(eng, P, samples=s.cpu().numpy())
+    if eng.complex_head:
+        T = 0.3
+        cost = costs.cost_complex(ref["logp"], ref["phase"], torch.complex(Er, Ei), T=T)
+        sl, sp = costs.seeds_complex(lp.cpu(), torch.complex(Er, Ei), T=T)
+    else:
+        cost = costs.cost_real(ref["logp"], Er)
+        sl, sp = costs.seeds_real(Er), None
+    cost.backward()
+    grad = eng.backward(s, saved, sl, sp).cpu()
+    bad = []
+    for n, v in eng.views(grad).items():
+        gr = P[n].grad
+        scale = float(gr.abs().max()) + 1e-30
+        err = float((v.double() - gr).abs().max()) / scale
+        if not err < 1e-4:
+            bad.append((n, err, scale))
+    assert not bad, f"gradient mismatch (tensor, rel err, scale): {bad}"
