@@ -1,0 +1,518 @@
+#!/usr/bin/env python
+"""bench.py -- the VMC hot path of the 2D Heisenberg 10x10 tensorized-GRU wavefunction (BASELINE.json
+config 4, the configuration the north-star target is quoted on), one process per GPU.
+
+A "step" is one full VMC step over one batch of synthetic input (random-init weights):
+    sample 10^4 configurations  ->  enumerate + evaluate the ~1.3*10^6 connected configurations and reduce
+    E_loc  ->  energy moments (all-reduce)  ->  backward of log psi seeded with (E_loc - <E>)
+    ->  gradient all-reduce  ->  TF-Adam update  ->  weight repack.
+metric  = E_loc configurations per second (1 diagonal + every connected configuration with non-zero matrix
+          element, summed over samples) through that whole step, whole job.   samples/s is reported beside it.
+value   : inputs resident in HBM (Philox uniforms generated in-kernel).
+e2e     : same step through the reference-facing API with HOST buffers: pinned uniforms H2D, samples and
+          local energies D2H (as the reference's sess.run fetches), Eloc fed back H2D for the backward.
+roofline: the dominant kernel (connected-configuration sweep).  It runs FP32 FFMA in this round, so the bound
+          is the FP32-FFMA peak measured live by a probe kernel; the fraction of the measured bf16
+          tensor peak is given beside it for context.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload NAME]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+WORKLOADS = {
+    # name: (engine kwargs, hamiltonian name, ham params builder, numsamples, description)
+    "heis10x10_tri_tgru100": dict(eng=dict(cell="TENSGRU2D", nx=10, ny=10, num_units=100, complex_head=True, u1=True),
+                                  ham="HEIS2D", hp=[1.0], ns=10000,
+                                  desc="2DHeisenberg 10x10 triangular (J2=1) tensorized complex GRU, 100 units, U(1) Sz=0, 1e4 samples/step/GPU"),
+    "heis10x10_sq_tgru100": dict(eng=dict(cell="TENSGRU2D", nx=10, ny=10, num_units=100, complex_head=True, u1=True),
+                                 ham="HEIS2D", hp=[0.0], ns=10000,
+                                 desc="2DHeisenberg 10x10 square (J2=0) tensorized complex GRU, 100 units, U(1) Sz=0, 1e4 samples/step/GPU"),
+    "tfim1d_n20_gru50": dict(eng=dict(cell="GRU1D", nx=20, ny=1, num_units=50, num_layers=1), ham="TFIM1D",
+                             hp=[1.0] + [1.0] * 19, ns=500, desc="1DTFIM N=20 pRNN GRU 1x50, 500 samples/step/GPU"),
+    "j1j2_n20_cgru50": dict(eng=dict(cell="GRU1D", nx=20, ny=1, num_units=50, complex_head=True, u1=True), ham="J1J2",
+                            hp=[0.0, 0.0] + [1.0] * 20 + [0.2] * 20 + [0.0] * 20, ns=500,
+                            desc="J1J2 N=20 cRNN GRU 50, J2=0.2, U(1), 500 samples/step/GPU"),
+    "tfim2d_12x12_rnn50": dict(eng=dict(cell="VANILLA2D", nx=12, ny=12, num_units=50), ham="TFIM2D",
+                               hp=[3.0] + [1.0] * 144, ns=10000, desc="2DTFIM 12x12 2D RNN 50 units, h=3, 1e4 samples/step/GPU"),
+    "rydberg_4x4_gru256": dict(eng=dict(cell="GRU4", nx=4, ny=4, num_units=256), ham="RYDBERG",
+                               hp=[1.7 ** 6, 3.3, 1.0, 2.001], ns=12500,
+                               desc="Rydberg Kagome 4x4 cells (48 atoms) 2D GRU 256 units, 12500 samples/step/GPU"),
+}
+DEFAULT_WORKLOAD = "heis10x10_tri_tgru100"
+
+
+# ------------------------------------------------------------------------------------------------------
+# algorithmic / executed work
+# ------------------------------------------------------------------------------------------------------
+def flops_per_site(w):
+    """Algorithmic flops per configuration per site (2 flop per multiply-add, activations excluded)."""
+    e = w["eng"]
+    nh = e["num_units"]
+    cell = e["cell"]
+    if cell == "TENSGRU2D":
+        return 2 * (2 * nh * 4) + 2 * 2 * (8 * nh * nh) + 2 * (2 * nh * nh) + 2 * (2 * nh * 2)   # 362 400 at nh=100
+    if cell == "GRU1D":
+        heads = 2 if e.get("complex_head") else 1
+        L = e.get("num_layers", 1)
+        return 6 * nh * (2 + nh) + (L - 1) * 6 * nh * (nh + nh) + heads * 2 * nh * 2
+    if cell == "VANILLA2D":
+        return 2 * (2 * nh * nh + 4 * nh) + 4 * nh
+    if cell == "GRU4":
+        K = 4 * (nh + 6)
+        return 2 * 2 * K * nh + 2 * 4 * nh * nh + 2 * nh * 8
+    raise ValueError(cell)
+
+
+def executed_flops_per_step_site(w):
+    """Flops the sweep kernel actually executes per row per interior site (one-hot inputs are row selects,
+    tensorized weight slices are pre-summed per class): 2*K*N_out + heads."""
+    e = w["eng"]
+    nh = e["num_units"]
+    cell = e["cell"]
+    if cell == "TENSGRU2D":
+        return 2 * (2 * nh) * (3 * nh) + 2 * nh * 4
+    if cell == "GRU1D":
+        heads = 2 if e.get("complex_head") else 1
+        L = e.get("num_layers", 1)
+        return 2 * nh * 3 * nh + (L - 1) * 2 * (2 * nh) * 3 * nh + heads * 2 * nh * 2
+    if cell == "VANILLA2D":
+        return 2 * (2 * nh) * nh + 2 * nh * 2
+    if cell == "GRU4":
+        return 2 * (2 * nh) * (3 * nh) + 2 * nh * 8     # two of the four neighbour slots are live on interior sites
+    raise ValueError(cell)
+
+
+# ------------------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.FIELDS}",
+                                       "--format=csv,noheader,nounits", "-lms", "200"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        for line in self.f.read().splitlines():
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 9:
+                continue
+            try:
+                sm.append(float(parts[1]))
+                mx.append(float(parts[2]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), parts[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        try:
+            os.unlink(self.f.name)
+        except OSError:
+            pass
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# ------------------------------------------------------------------------------------------------------
+# CPU baseline: the float64 oracle (kind "port"; TensorFlow 1.13 is unavailable on this box)
+# ------------------------------------------------------------------------------------------------------
+def oracle_step(w, ns, seed=0):
+    """One VMC step of the workload on the host cores with the oracle: sample + E_loc + gradient.
+    Returns (configs evaluated, seconds, breakdown)."""
+    from oracle import wavefunctions as owf, local_energies as ole, costs
+    e = w["eng"]
+    cell = e["cell"]
+    nh, nx, ny = e["num_units"], e["nx"], e["ny"]
+    g = torch.Generator().manual_seed(seed)
+    P = make_oracle_params(w, g)
+    nsteps = nx * ny
+    u = torch.rand(ns, nsteps, generator=g, dtype=torch.float32)
+    cname = {"VANILLA2D": "vanilla", "TENS2D": "tens", "TENSGRU2D": "tensgru"}
+
+    def run(samples=None, grad=False):
+        ctx = torch.enable_grad() if grad else torch.no_grad()
+        with ctx:
+            if cell == "GRU1D":
+                return owf.rnn1d(P, nx, [nh] * e.get("num_layers", 1), samples=samples, uniforms=u, numsamples=ns,
+                                 complex_=bool(e.get("complex_head")), u1=bool(e.get("u1")))
+            if cell == "GRU4":
+                return owf.rydberg2d(P, nx, ny, nh, samples=samples, uniforms=u, numsamples=ns)
+            return owf.rnn2d(P, nx, ny, nh, cname[cell], samples=samples, uniforms=u, numsamples=ns,
+                             complex_=bool(e.get("complex_head")), mag_fixed=bool(e.get("u1")))
+
+    t0 = time.perf_counter()
+    s = run()["samples"]
+    t1 = time.perf_counter()
+
+    def logpsi(cfg):
+        r = run(samples=torch.as_tensor(cfg))
+        return r["logp"].numpy(), r["phase"].numpy()
+
+    sn = s.numpy()
+    hp = w["hp"]
+    ham = w["ham"]
+    if ham == "HEIS2D":
+        E, counts = ole.heis2d_local_energies(hp[0], sn, logpsi)
+        nconf = int(counts.sum())
+        if hp[0] == 0.0:   # count only the non-zero matrix elements, like the GPU metric
+            nconf = ns + sum(int((ole.heis2d_connected(0.0, x)[1][1:] != 0).sum()) for x in sn)
+    elif ham == "J1J2":
+        N = nx
+        E, counts = ole.j1j2_local_energies(np.asarray(hp[2:2 + N]), np.asarray(hp[2 + N:2 + 2 * N]), np.asarray(hp[2 + 2 * N:2 + 3 * N]),
+                                            sn, logpsi, periodic=bool(hp[0]), Marshall_sign=bool(hp[1]))
+        nconf = int(counts.sum())
+    elif ham == "TFIM1D":
+        E = ole.ising1d_local_energies(np.asarray(hp[1:] + [0.0]), hp[0], sn, logpsi)
+        nconf = ns * (nx + 1)
+    elif ham == "TFIM2D":
+        E = ole.ising2d_local_energies(np.asarray(hp[1:]).reshape(nx, ny), hp[0], sn, logpsi)
+        nconf = ns * (nx * ny + 1)
+    else:
+        pos = ole.generate_kagome(nx, ny)
+        nb, dist = ole.neighbouring_atoms(pos, hp[3], nx, ny)
+        E = ole.rydberg_local_energies(hp[0], hp[1], hp[2], nb, dist, sn, logpsi)
+        nconf = ns * (3 * nx * ny + 1)
+    t2 = time.perf_counter()
+    for v in P.values():
+        v.requires_grad_(True)
+    r = run(samples=s, grad=True)
+    Et = torch.as_tensor(E)
+    if e.get("complex_head"):
+        cost = costs.cost_complex(r["logp"], r["phase"], Et.to(torch.complex128))
+    else:
+        cost = costs.cost_real(r["logp"], Et.real if Et.is_complex() else Et)
+    cost.backward()
+    t3 = time.perf_counter()
+    return nconf, t3 - t0, dict(sample_s=t1 - t0, eloc_s=t2 - t1, grad_s=t3 - t2)
+
+
+def make_oracle_params(w, g):
+    """Random-init parameters with the shapes of the TF variables (values do not matter for timing)."""
+    e = w["eng"]
+    nh, cell = e["num_units"], e["cell"]
+    D = 8 if cell == "GRU4" else 2
+    r = lambda *s: (torch.rand(*s, generator=g, dtype=torch.float64) - 0.5) * 0.4
+    P = {"dense.W": r(nh, D), "dense.b": r(D)}
+    if e.get("complex_head"):
+        P["dense_phase.W"], P["dense_phase.b"] = r(nh, 2), r(2)
+    if cell == "GRU1D":
+        for l in range(e.get("num_layers", 1)):
+            din = 2 if l == 0 else nh
+            P.update({f"gru{l}.Wg": r(din + nh, 2 * nh), f"gru{l}.bg": r(2 * nh), f"gru{l}.Wci": r(din, nh),
+                      f"gru{l}.Wch": r(nh, nh), f"gru{l}.bci": r(nh), f"gru{l}.bch": r(nh)})
+    elif cell == "VANILLA2D":
+        P.update(Wh=r(nh, nh), Uh=r(2, nh), Wv=r(nh, nh), Uv=r(2, nh), b=r(nh))
+    elif cell in ("TENS2D", "TENSGRU2D"):
+        P.update(W=r(nh, 2 * nh, 4), b=r(nh), Wg=r(nh, 2 * nh, 4), bg=r(nh), Wmerge=r(2 * nh, nh))
+    else:
+        P.update(W=r(4 * (nh + 6), nh), b=r(nh), Wg=r(4 * (nh + 6), nh), bg=r(nh), Wmerge=r(4 * nh, nh))
+    return P
+
+
+def cpu_baseline(w, target_s=15.0):
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    n0 = 2
+    nconf, dt, _ = oracle_step(w, n0)
+    ns = int(max(n0, min(4096, n0 * target_s / max(dt, 1e-3))))
+    nconf, dt, br = oracle_step(w, ns)
+    return dict(value=nconf / dt, unit="eloc_configs/s", cores=cores, kind="port",
+                sample=f"oracle (torch float64, {cores} threads) on {ns} samples = {nconf} configurations of the same workload: "
+                       f"sample {br['sample_s']:.2f}s + E_loc (host enumeration + chunked forwards) {br['eloc_s']:.2f}s + autograd {br['grad_s']:.2f}s",
+                seconds=dt)
+
+
+# ------------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
+    ap.add_argument("--numsamples", type=int, default=None)
+    ap.add_argument("--no-prefix-reuse", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    w = dict(WORKLOADS[args.workload])
+    if args.numsamples:
+        w["ns"] = args.numsamples
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    metric, unit = "vmc_eloc_configs_per_s", "eloc_configs/s"
+    config = {"workload": f"{args.workload}: {w['desc']}", "numsamples_per_gpu": w["ns"],
+              "parallelism": f"dp{world} (samples sharded, weights replicated)",
+              "l2": "per-step working set (saved hidden states + gates of the samples, ~2 GB) exceeds the 126 MB L2; no explicit flush"}
+
+    if args.impl == "reference":
+        # The reference's own implementation needs TensorFlow 1.13.1 (unavailable on this box): the timed arm is
+        # the oracle port of its algorithm on the host cores, on a bounded sample of the same workload.
+        if rank != 0:
+            return
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        ns_ref = 48 if "heis" in args.workload else min(w["ns"], 64)
+        for _ in range(max(0, min(args.warmup, 1))):
+            oracle_step(w, 2)
+        tot_c, tot_t = 0, 0.0
+        for k in range(args.steps):
+            c, dt, br = oracle_step(w, ns_ref, seed=k)
+            tot_c += c
+            tot_t += dt
+        val = tot_c / tot_t
+        line = {"impl": "reference", "metric": metric, "value": val, "unit": unit, "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+                "cpu_baseline": {"value": val, "unit": unit, "cores": cores, "kind": "port",
+                                 "sample": f"{ns_ref} samples/step of the same workload ({tot_c // args.steps} configurations/step), oracle port, torch float64, {cores} threads"},
+                "e2e": {"value": val, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line), flush=True)
+        return
+
+    import torch.distributed as dist
+    from rnnwavefunctions_b200 import _lib
+    from rnnwavefunctions_b200.engine import Engine
+    from rnnwavefunctions_b200 import vmc
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    ek = dict(w["eng"])
+    ek["cell"] = getattr(_lib, "CELL_" + ek["cell"])
+    eng = Engine(seed=111, **ek)
+    ham = getattr(_lib, "HAM_" + w["ham"])
+    ns = w["ns"]
+    V = vmc.VMC(eng, ham, w["hp"], ns, lr=5e-4, seed=111, prefix_reuse=not args.no_prefix_reuse)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    phase_ms = {"sample": 0.0, "eloc": 0.0, "backward": 0.0}
+    nconn_total = [0]
+
+    def step_resident(timed):
+        e0, e1, e2, e3 = ev(), ev(), ev(), ev()
+        offset = (V.it * V.world + V.rank) * ns
+        e0.record()
+        s, lp, ph = eng.sample(ns, seed=111, row_offset=offset, saved=V.saved)
+        e1.record()
+        e, cnt = eng.local_energies(ham, w["hp"], s, lp, ph, saved=V.saved if V.prefix_reuse else None, return_count=True)
+        e2.record()
+        grad, mean_e, var = V.gradient(s, lp, ph, e)
+        V.opt.step(eng.params, grad, V.lr)
+        eng.set_weights()
+        e3.record()
+        V.it += 1
+        return (e0, e1, e2, e3), cnt, s
+
+    for _ in range(args.warmup):
+        step_resident(False)
+    barrier()
+    launches0 = _lib.lib.rnnwf_launch_count()
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    t_start, t_end = ev(), ev()
+    recs = []
+    barrier()
+    t_start.record()
+    for _ in range(args.steps):
+        recs.append(step_resident(True))
+    t_end.record()
+    barrier()
+    clk = clocks.stop()
+    launches = _lib.lib.rnnwf_launch_count() - launches0
+    elapsed_ms = t_start.elapsed_time(t_end)
+    nconf_local = 0
+    for (e0, e1, e2, e3), cnt, s in recs:
+        phase_ms["sample"] += e0.elapsed_time(e1)
+        phase_ms["eloc"] += e1.elapsed_time(e2)
+        phase_ms["backward"] += e2.elapsed_time(e3)
+        nconf_local += int(cnt) + ns
+    tmax = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
+    tot = torch.tensor([float(nconf_local), float(ns * args.steps)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    elapsed_ms = float(tmax)
+    value = float(tot[0]) / (elapsed_ms * 1e-3)
+    samples_per_s = float(tot[1]) / (elapsed_ms * 1e-3)
+
+    # ---- roofline of the dominant kernel (the connected-configuration sweep inside local_energies)
+    s_last = recs[-1][2]
+    nchild = int(recs[-1][1])
+    eloc_ms = phase_ms["eloc"] / args.steps
+    fl_site = executed_flops_per_step_site(w)
+    T = eng.nsteps
+    if V.prefix_reuse:
+        # executed sites per child = T - (generation step of its first changed symbol); recomputed here from
+        # the samples exactly as the device enumeration orders them (measurement only, outside the timed region)
+        exec_sites = executed_sites(w, s_last.cpu().numpy(), eng)
+    else:
+        exec_sites = nchild * T
+    exec_flops = exec_sites * fl_site
+    alg_flops = (nchild) * T * flops_per_site(w)
+    probe_out = torch.zeros(4, dtype=torch.float32, device=dev)
+    import ctypes as C
+    best = 0.0
+    blocks, iters = 148 * 4, 20000
+    for _ in range(5):
+        a, b = ev(), ev()
+        a.record()
+        _lib.lib.rnnwf_ffma_probe(C.c_void_p(probe_out.data_ptr()), blocks, iters, C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        b.record()
+        torch.cuda.synchronize()
+        best = max(best, blocks * 512 * iters * 16 * 2 / (a.elapsed_time(b) * 1e-3) / 1e12)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    bf16_peak = peaks.get("bf16_tflops_sustained", 1400.0)
+    achieved = exec_flops / (eloc_ms * 1e-3) / 1e12
+    roofline = {"bound": "fp32-ffma", "kernel": "sweep_kernel (MODE_CHILD)", "achieved": achieved, "peak": best, "unit": "TFLOP/s",
+                "frac": achieved / best if best > 0 else None, "traffic": None,
+                "peak_source": "measured live: rnnwf_ffma_probe (16 FMA chains/thread, 592x512 threads), best of 5",
+                "executed_flops_per_launch": exec_flops, "algorithmic_flops_per_launch": alg_flops,
+                "algorithmic_tflops": alg_flops / (eloc_ms * 1e-3) / 1e12,
+                "frac_of_bf16_tensor_peak": achieved / bf16_peak,
+                "bf16_peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1400",
+                "launch_ms": eloc_ms, "note": "launch_ms brackets rnnwf_local_energies (enumeration kernels + sweep; the sweep is >99% of it)"}
+
+    # ---- end to end through the reference-facing API with host buffers
+    e2e = None
+    if not args.no_e2e:
+        K = max(1, min(args.steps, 3))
+        pinned_u = torch.rand(ns, eng.nsteps, dtype=torch.float32).pin_memory()
+        host_s = torch.empty((ns,) + eng.cfg_shape, dtype=torch.int8).pin_memory()
+        host_e = torch.empty(ns, dtype=torch.complex128).pin_memory()
+        host_eloc_in = torch.empty(ns, dtype=torch.complex128).pin_memory()
+        h2d = pinned_u.numel() * 4 + host_eloc_in.numel() * 16 + host_s.numel()
+        d2h = host_s.numel() + host_e.numel() * 16 + 16
+        nconf_e2e = 0
+        barrier()
+        a, b = ev(), ev()
+        a.record()
+        for _ in range(K):
+            u = pinned_u.to(dev, non_blocking=True)
+            s, lp, ph = eng.sample(ns, uniforms=u, saved=V.saved)
+            e, cnt = eng.local_energies(ham, w["hp"], s, lp, ph, saved=V.saved if V.prefix_reuse else None, return_count=True)
+            host_s.copy_(s, non_blocking=True)
+            host_e.copy_(e, non_blocking=True)
+            torch.cuda.synchronize()                       # the reference's sess.run returns numpy arrays here
+            host_eloc_in.copy_(host_e)                     # meanE / varE on the host, Eloc fed back (optstep feed_dict)
+            mean_host = complex(host_e.mean())
+            s_dev = host_s.to(dev, non_blocking=True)
+            e_dev = host_eloc_in.to(dev, non_blocking=True)
+            grad, mean_e, var = V.gradient(s_dev, lp, ph, e_dev)
+            V.opt.step(eng.params, grad, V.lr)
+            eng.set_weights()
+            _ = complex(mean_e)                            # D2H of the step's result
+            nconf_e2e += int(cnt) + ns
+        b.record()
+        barrier()
+        t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
+        c = torch.tensor([float(nconf_e2e)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(c, op=dist.ReduceOp.SUM)
+        e2e = {"value": float(c) / (float(t) * 1e-3), "unit": unit, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+               "steps": K, "ms_per_step": float(t) / K}
+
+    if rank == 0:
+        line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic", "config": config, "samples_per_s": samples_per_s,
+                "phase_ms_per_step": {k: v / args.steps for k, v in phase_ms.items()},
+                "eloc_configs_per_step_per_gpu": nconf_local / args.steps, "gpu_launches": int(launches),
+                "clocks": clk, "roofline": roofline, "e2e": e2e, "engine": eng.describe(),
+                "prefix_reuse": V.prefix_reuse}
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(w)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def executed_sites(w, samples, eng):
+    """Sum over connected configurations of (sites - first changed generation step)."""
+    e = w["eng"]
+    nx, ny = e["nx"], e["ny"]
+    T = nx * ny
+    ham = w["ham"]
+    ns = samples.shape[0]
+    if ham in ("TFIM1D", "TFIM2D"):
+        return ns * sum(T - t for t in range(T))
+    if ham == "RYDBERG":
+        return 3 * ns * sum(T - t for t in range(T))
+
+    def step_of(ix, iy):
+        return iy * nx + (ix if iy % 2 == 0 else nx - 1 - ix)
+
+    total = 0
+    if ham == "HEIS2D":
+        J2 = w["hp"][0]
+        s = samples.reshape(ns, nx, ny)
+        for dx, dy, wgt in ((1, 0, 1.0), (0, 1, 1.0), (1, 1, J2)):
+            if wgt == 0.0:
+                continue
+            for ix in range(nx - dx):
+                for iy in range(ny - dy):
+                    ts = min(step_of(ix, iy), step_of(ix + dx, iy + dy))
+                    total += int((s[:, ix, iy] != s[:, ix + dx, iy + dy]).sum()) * (T - ts)
+        return total
+    if ham == "J1J2":
+        N = nx
+        hp = w["hp"]
+        periodic = bool(hp[0])
+        J1, J2 = hp[2:2 + N], hp[2 + N:2 + 2 * N]
+        s = samples.reshape(ns, N)
+        for d, J, lim in ((1, J1, N if periodic else N - 1), (2, J2, N if periodic else N - 2)):
+            for i in range(lim):
+                if J[i] != 0.0:
+                    j = (i + d) % N
+                    total += int((s[:, i] != s[:, j]).sum()) * (T - min(i, j))
+        return total
+    raise ValueError(ham)
+
+
+if __name__ == "__main__":
+    main()

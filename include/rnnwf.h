@@ -136,6 +136,12 @@ int rnnwf_backward(rnnwf_handle h, int64_t rows, const int8_t* samples_dev, cons
  * shape / pipe (FFMA or tcgen05) the handle's sweeps run in. */
 int rnnwf_describe(rnnwf_handle h, char* buf, int cap);
 
+/* Measurement helpers (no reference counterpart): number of kernels launched by this library so far in
+ * this process, and an FP32-FFMA throughput probe (blocks x 512 threads x iters x 16 FMA chains) used by
+ * bench.py as the roofline denominator of the FFMA regime. */
+long long rnnwf_launch_count(void);
+int rnnwf_ffma_probe(float* out_dev, int blocks, int iters, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -365,12 +365,12 @@ struct Gemm {
   void nt(const float* A, int lda, const float* B, int ldb, float* C, int ldc, long long M, int N, int K, int beta) const {
     if (M <= 0 || N <= 0 || K <= 0) return;
     dim3 g((N + GB - 1) / GB, (unsigned)((M + GB - 1) / GB));
-    gemm_nt_kernel<<<g, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, N, K, beta);
+    RNNWF_COUNT_LAUNCH(); gemm_nt_kernel<<<g, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, N, K, beta);
   }
   void nn(const float* A, int lda, const float* B, int ldb, float* C, int ldc, long long M, int N, int K, int beta) const {
     if (M <= 0 || N <= 0 || K <= 0) return;
     dim3 g((N + GB - 1) / GB, (unsigned)((M + GB - 1) / GB));
-    gemm_nn_kernel<<<g, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, N, K, beta);
+    RNNWF_COUNT_LAUNCH(); gemm_nn_kernel<<<g, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, N, K, beta);
   }
   void tn(const float* A, int lda, const float* B, int ldb, float* C, int ldc, long long M, int K1, int N) const {
     if (M <= 0 || N <= 0 || K1 <= 0) return;
@@ -382,12 +382,12 @@ struct Gemm {
     long long mchunk = ((M + split - 1) / split + GK - 1) / GK * GK;
     split = (M + mchunk - 1) / mchunk;
     dim3 g((N + GB - 1) / GB, (K1 + GB - 1) / GB, (unsigned)split);
-    gemm_tn_atomic_kernel<<<g, 256, 0, st>>>(A, lda, B, ldb, C, ldc, M, K1, N, mchunk);
+    RNNWF_COUNT_LAUNCH(); gemm_tn_atomic_kernel<<<g, 256, 0, st>>>(A, lda, B, ldb, C, ldc, M, K1, N, mchunk);
   }
   void colsum(const float* X, int ldx, long long M, int N, float* out) const {
     if (M <= 0 || N <= 0) return;
     dim3 g((N + 127) / 128, (unsigned)std::max<long long>(1, std::min<long long>(64, M / 256)));
-    colsum_atomic_kernel<<<g, 128, 0, st>>>(X, ldx, M, N, out);
+    RNNWF_COUNT_LAUNCH(); colsum_atomic_kernel<<<g, 128, 0, st>>>(X, ldx, M, N, out);
   }
 };
 
@@ -439,7 +439,7 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
 
     if (sm.head) {
       const int wpb = 8;
-      head_bwd_kernel<<<(unsigned)((R + wpb - 1) / wpb), wpb * 32, 0, st>>>(S, m.d_site_of_t, m.d_head_w, m.d_head_b, seed_logp, seed_phase, dlog);
+      RNNWF_COUNT_LAUNCH(); head_bwd_kernel<<<(unsigned)((R + wpb - 1) / wpb), wpb * 32, 0, st>>>(S, m.d_site_of_t, m.d_head_w, m.d_head_b, seed_logp, seed_phase, dlog);
       G.tn(hrow(q), nhp, dlog, m.ND, Gd("dense.W"), m.D, R, nh, m.D);
       G.colsum(dlog, m.ND, R, m.D, Gd("dense.b"));
       if (m.complex_head) {
@@ -450,7 +450,7 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
     float* dp0 = dp;
     float* dp1 = dp + ((m.cell == CELL_GRU1D) ? 2 * R * nh : R * nh);
     float* dp2 = dp1 + R * nh;
-    cell_bwd_kernel<<<nblk(R * nh), tpb, 0, st>>>(S, dp0, dp1, dp2);
+    RNNWF_COUNT_LAUNCH(); cell_bwd_kernel<<<nblk(R * nh), tpb, 0, st>>>(S, dp0, dp1, dp2);
 
     switch (m.cell) {
       case CELL_TENS2D:
@@ -462,7 +462,7 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
           if (gru) G.colsum(dp1, nh, R, nh, Gd("bg"));
           break;
         }
-        build_tens_kernel<<<nblk(R * 2 * nh), tpb, 0, st>>>(S, Z, hc);
+        RNNWF_COUNT_LAUNCH(); build_tens_kernel<<<nblk(R * 2 * nh), tpb, 0, st>>>(S, Z, hc);
         G.nn(dp0, nh, P("W"), K8, dZ, K8, R, K8, nh, 0);                 // dT  = ds W2
         G.tn(dp0, nh, Z, K8, Gd("W"), K8, R, nh, K8);                     // dW2 += ds^T T
         G.colsum(dp0, nh, R, nh, Gd("b"));
@@ -473,12 +473,12 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
           G.nt(dp2, nh, P("Wmerge"), nh, dhc, 2 * nh, R, 2 * nh, nh, 0);  // dhc = dm Wmerge^T
           G.tn(hc, 2 * nh, dp2, nh, Gd("Wmerge"), nh, R, 2 * nh, nh);     // dWmerge += hc^T dm
         }
-        scatter_tens_kernel<<<nblk(R * 2 * nh), tpb, 0, st>>>(S, dZ, gru ? dhc : nullptr);
+        RNNWF_COUNT_LAUNCH(); scatter_tens_kernel<<<nblk(R * 2 * nh), tpb, 0, st>>>(S, dZ, gru ? dhc : nullptr);
         break;
       }
       case CELL_GRU4: {
         const int Kz = 24 + 4 * nh;
-        build_gru4_kernel<<<nblk(R * Kz), tpb, 0, st>>>(S, Z);
+        RNNWF_COUNT_LAUNCH(); build_gru4_kernel<<<nblk(R * Kz), tpb, 0, st>>>(S, Z);
         G.nt(dp0, nh, P("W"), nh, dZ, Kz, R, Kz, nh, 0);                  // dz  = ds W^T
         G.nt(dp1, nh, P("Wg"), nh, dZ, Kz, R, Kz, nh, 1);                 // dz += dg Wg^T
         G.nt(dp2, nh, P("Wmerge"), nh, dZ + 24, Kz, R, 4 * nh, nh, 1);    // dz[:,24:] += dm Wmerge^T
@@ -487,11 +487,11 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
         G.tn(Z + 24, Kz, dp2, nh, Gd("Wmerge"), nh, R, 4 * nh, nh);
         G.colsum(dp0, nh, R, nh, Gd("b"));
         G.colsum(dp1, nh, R, nh, Gd("bg"));
-        scatter_gru4_kernel<<<nblk(R * 4 * nh), tpb, 0, st>>>(S, dZ);
+        RNNWF_COUNT_LAUNCH(); scatter_gru4_kernel<<<nblk(R * 4 * nh), tpb, 0, st>>>(S, dZ);
         break;
       }
       case CELL_VANILLA2D: {
-        build_onehot_kernel<<<nblk(R * 2), tpb, 0, st>>>(S, 2, X);       // X[row] = [x_h (2), x_v (2)]
+        RNNWF_COUNT_LAUNCH(); build_onehot_kernel<<<nblk(R * 2), tpb, 0, st>>>(S, 2, X);       // X[row] = [x_h (2), x_v (2)]
         G.tn(X, 4, dp0, nh, Gd("Uh"), nh, R, 2, nh);
         G.tn(X + 2, 4, dp0, nh, Gd("Uv"), nh, R, 2, nh);
         G.colsum(dp0, nh, R, nh, Gd("b"));
@@ -522,7 +522,7 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
         }
         if (l == 0) {          // one-hot input of the previous spin
           if (sm.nsym[0] >= 0) {
-            build_onehot_kernel<<<nblk(R), tpb, 0, st>>>(S, 1, X);
+            RNNWF_COUNT_LAUNCH(); build_onehot_kernel<<<nblk(R), tpb, 0, st>>>(S, 1, X);
             G.tn(X, 2, dp0, 2 * nh, dWg, 2 * nh, R, 2, 2 * nh);
             G.tn(X, 2, dp1, nh, Gd(p + "Wci"), nh, R, 2, nh);
           }

@@ -5,6 +5,10 @@
 
 namespace rnnwf {
 
+// number of kernels this library has launched (bench.py reports it as gpu_launches)
+inline long long& launch_counter() { static long long c = 0; return c; }
+#define RNNWF_COUNT_LAUNCH() (++::rnnwf::launch_counter())
+
 constexpr int KC = 8;          // k-chunk depth of one pipeline stage
 constexpr int TM = 4;          // rows per thread (one LDS.128 of the A operand)
 constexpr int RL = 8;          // row lanes per warp

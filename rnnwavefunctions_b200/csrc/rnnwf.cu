@@ -313,7 +313,7 @@ void fill_model_params(const rnnwf_model& m, const LaunchShape& s, SweepParams& 
 
 template <int TJ, int NTU>
 cudaError_t launch_inst(const SweepParams& P, const LaunchShape& s, cudaStream_t st) {
-  sweep_kernel<TJ, NTU><<<s.grid, s.threads, s.smem, st>>>(P);
+  RNNWF_COUNT_LAUNCH(); sweep_kernel<TJ, NTU><<<s.grid, s.threads, s.smem, st>>>(P);
   return cudaGetLastError();
 }
 
@@ -490,15 +490,15 @@ int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
   for (auto& v : h->variants) {
     PackCtx c;
     make_pack_ctx(*h, v, params_dev, nullptr, c);
-    if (v.w_float4 > 0) pack_w_kernel<<<std::min(1024, cdiv(v.w_float4, 256)), 256, 0, st>>>(c, h->d_wpack + v.meta.w_off);
-    if (v.meta.x_mask) pack_x_kernel<<<std::min(256, cdiv((long long)h->nslots * h->D * h->Gp, 256)), 256, 0, st>>>(c, h->nslots, h->d_xtab + v.meta.x_off);
-    pack_b_kernel<<<cdiv(h->Gp, 256), 256, 0, st>>>(c, h->d_bias + v.meta.b_off);
+    if (v.w_float4 > 0) { RNNWF_COUNT_LAUNCH(); pack_w_kernel<<<std::min(1024, cdiv(v.w_float4, 256)), 256, 0, st>>>(c, h->d_wpack + v.meta.w_off); }
+    if (v.meta.x_mask) { RNNWF_COUNT_LAUNCH(); pack_x_kernel<<<std::min(256, cdiv((long long)h->nslots * h->D * h->Gp, 256)), 256, 0, st>>>(c, h->nslots, h->d_xtab + v.meta.x_off); }
+    RNNWF_COUNT_LAUNCH(); pack_b_kernel<<<cdiv(h->Gp, 256), 256, 0, st>>>(c, h->d_bias + v.meta.b_off);
   }
   const TensorInfo* wd = h->tensor("dense.W");
   const TensorInfo* bd = h->tensor("dense.b");
   const TensorInfo* wp = h->tensor("dense_phase.W");
   const TensorInfo* bp = h->tensor("dense_phase.b");
-  pack_head_kernel<<<cdiv((long long)h->nhp * h->ND, 256), 256, 0, st>>>(
+  RNNWF_COUNT_LAUNCH(); pack_head_kernel<<<cdiv((long long)h->nhp * h->ND, 256), 256, 0, st>>>(
       params_dev + wd->offset, params_dev + bd->offset, wp ? params_dev + wp->offset : nullptr,
       bp ? params_dev + bp->offset : nullptr, h->nh, h->nhp, h->D, h->ND, h->d_head_w, h->d_head_b);
   CUDA_TRY(cudaGetLastError());
@@ -631,12 +631,12 @@ int rnnwf_local_energies(rnnwf_handle h, int hamiltonian, const double* ham, int
       std::vector<double> J(Nx * Ny, 0.0);
       for (int i = 0; i < nJ && i < Nx * Ny; ++i) J[i] = ham[1 + i];
       CUDA_TRY(cudaMemcpyAsync(d_ham, J.data(), J.size() * 8, cudaMemcpyHostToDevice, st));
-      tfim_diag_kernel<<<gsamp, tpb, 0, st>>>(samples_dev, rows, Nx, Ny, d_ham, eloc_dev);
+      RNNWF_COUNT_LAUNCH(); tfim_diag_kernel<<<gsamp, tpb, 0, st>>>(samples_dev, rows, Nx, Ny, d_ham, eloc_dev);
       const double Bx = ham[0];
       if (Bx == 0.0) have_children = false;
       else {
         nchild_fixed = (long long)T * rows;
-        all_flips_kernel<<<std::min(8192, cdiv(nchild_fixed, tpb)), tpb, 0, st>>>(rows, T, 1, (float)(-Bx), d_children);
+        RNNWF_COUNT_LAUNCH(); all_flips_kernel<<<std::min(8192, cdiv(nchild_fixed, tpb)), tpb, 0, st>>>(rows, T, 1, (float)(-Bx), d_children);
       }
       break;
     }
@@ -672,11 +672,11 @@ int rnnwf_local_energies(rnnwf_handle h, int hamiltonian, const double* ham, int
             }
       if (nb.size() > 256) return fail(RNNWF_EINVAL, "Rydberg: too many neighbours within Rcutoff (max 256)");
       if (!nb.empty()) CUDA_TRY(cudaMemcpyAsync(d_nb, nb.data(), nb.size() * sizeof(RydNb), cudaMemcpyHostToDevice, st));
-      rydberg_diag_kernel<<<gsamp, tpb, 0, st>>>(samples_dev, rows, Nx, Ny, d_nb, (int)nb.size(), delta, eloc_dev);
+      RNNWF_COUNT_LAUNCH(); rydberg_diag_kernel<<<gsamp, tpb, 0, st>>>(samples_dev, rows, Nx, Ny, d_nb, (int)nb.size(), delta, eloc_dev);
       if (Omega == 0.0) have_children = false;
       else {
         nchild_fixed = 3LL * T * rows;
-        all_flips_kernel<<<std::min(8192, cdiv(nchild_fixed, tpb)), tpb, 0, st>>>(rows, T, 3, (float)(-Omega / 2.0), d_children);
+        RNNWF_COUNT_LAUNCH(); all_flips_kernel<<<std::min(8192, cdiv(nchild_fixed, tpb)), tpb, 0, st>>>(rows, T, 3, (float)(-Omega / 2.0), d_children);
       }
       break;
     }
@@ -724,11 +724,11 @@ int rnnwf_local_energies(rnnwf_handle h, int hamiltonian, const double* ham, int
       if (!bonds.empty()) CUDA_TRY(cudaMemcpyAsync(d_bonds, bonds.data(), bonds.size() * sizeof(Bond), cudaMemcpyHostToDevice, st));
       CUDA_TRY(cudaMemcpyAsync(d_bstart, bstart.data(), bstart.size() * 4, cudaMemcpyHostToDevice, st));
       if (!Bz.empty()) CUDA_TRY(cudaMemcpyAsync(d_ham, Bz.data(), Bz.size() * 8, cudaMemcpyHostToDevice, st));
-      bond_diag_kernel<<<gsamp, tpb, 0, st>>>(samples_dev, rows, m.nsites, m.d_site_of_t, d_bonds, (int)bonds.size(), d_ham, (int)Bz.size(), eloc_dev);
+      RNNWF_COUNT_LAUNCH(); bond_diag_kernel<<<gsamp, tpb, 0, st>>>(samples_dev, rows, m.nsites, m.d_site_of_t, d_bonds, (int)bonds.size(), d_ham, (int)Bz.size(), eloc_dev);
       const long long ncnt = (long long)T * rows;
-      bond_count_kernel<<<std::min(8192, cdiv(ncnt + 1, tpb)), tpb, 0, st>>>(samples_dev, rows, m.nsites, T, m.d_site_of_t, d_bonds, d_bstart, d_counts);
-      scan_kernel<<<1, 1024, 0, st>>>(d_counts, d_offsets, ncnt + 1);
-      bond_fill_kernel<<<std::min(8192, cdiv(ncnt, tpb)), tpb, 0, st>>>(samples_dev, rows, m.nsites, T, m.d_site_of_t, d_bonds, d_bstart, d_offsets, d_children);
+      RNNWF_COUNT_LAUNCH(); bond_count_kernel<<<std::min(8192, cdiv(ncnt + 1, tpb)), tpb, 0, st>>>(samples_dev, rows, m.nsites, T, m.d_site_of_t, d_bonds, d_bstart, d_counts);
+      RNNWF_COUNT_LAUNCH(); scan_kernel<<<1, 1024, 0, st>>>(d_counts, d_offsets, ncnt + 1);
+      RNNWF_COUNT_LAUNCH(); bond_fill_kernel<<<std::min(8192, cdiv(ncnt, tpb)), tpb, 0, st>>>(samples_dev, rows, m.nsites, T, m.d_site_of_t, d_bonds, d_bstart, d_offsets, d_children);
       rows_dev = d_offsets + ncnt;
       nchild_fixed = L.max_children;
       break;
@@ -739,7 +739,7 @@ int rnnwf_local_energies(rnnwf_handle h, int hamiltonian, const double* ham, int
   CUDA_TRY(cudaGetLastError());
   if (nconn_dev != nullptr) {
     // connected configurations evaluated (+ the diagonal one per sample, already known from `logp`)
-    count_children_kernel<<<1, 32, 0, st>>>(have_children ? rows_dev : nullptr, have_children ? (rows_dev ? 0 : nchild_fixed) : 0, (long long*)nconn_dev);
+    RNNWF_COUNT_LAUNCH(); count_children_kernel<<<1, 32, 0, st>>>(have_children ? rows_dev : nullptr, have_children ? (rows_dev ? 0 : nchild_fixed) : 0, (long long*)nconn_dev);
   }
   if (!have_children) return RNNWF_OK;
 
@@ -779,6 +779,31 @@ int rnnwf_backward(rnnwf_handle h, int64_t rows, const int8_t* samples_dev, cons
   rc = backward_run(*h, rows, samples_dev, saved_dev, seed_logp_dev, seed_phase_dev, grad_dev, workspace_dev,
                     static_cast<cudaStream_t>(stream), err);
   if (rc) return fail(rc, err);
+  return RNNWF_OK;
+}
+
+long long rnnwf_launch_count(void) { return rnnwf::launch_counter(); }
+
+// FP32 FFMA peak probe (roofline denominator of the FFMA regime): every thread runs 16 independent
+// FMA chains; flops = blocks * threads * iters * 16 * 2.
+__global__ void __launch_bounds__(512) ffma_probe_kernel(float* out, int iters, float seedv) {
+  float a[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) a[i] = seedv + (float)(threadIdx.x + i);
+  const float m = 0.999f + seedv * 1e-9f, c = 1e-3f;
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) a[i] = fmaf(a[i], m, c);
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) s += a[i];
+  if (s == 123.456f) out[0] = s;
+}
+
+int rnnwf_ffma_probe(float* out_dev, int blocks, int iters, void* stream) {
+  RNNWF_COUNT_LAUNCH(); ffma_probe_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(out_dev, iters, 1.0f);
+  CUDA_TRY(cudaGetLastError());
   return RNNWF_OK;
 }
 

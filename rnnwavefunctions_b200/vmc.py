@@ -1,0 +1,130 @@
+"""One VMC step of the reference's training loops, on the device:
+
+    sample -> local energies (connected configurations, one batched sweep) -> energy moments
+           -> backward of log psi seeded with (E_loc - <E>) -> optimiser update -> repack weights
+
+mirroring 1DTFIM/TrainingRNN_1DTFIM.py:200-222, J1J2/TrainingRNN_J1J2.py:240-305,
+2DTFIM_2DRNN/Training2DRNN_2DTFIM.py:200-231, 2DHeisenberg/Run_RNNWF_2DHeis.py:288-349 and
+RydbergKagome_2DGRU/Run_RNNWF_Rydberg.py:243-293.
+
+Data parallelism (new; the reference is single-replica): every rank draws its own shard of the samples
+(Philox counters offset by rank * numsamples_per_rank, so the union over ranks is the single-rank stream),
+and the only collectives are an all-reduce of the float64 energy moments (needed before the backward
+because the seed is (E_b - <E>_global)/ns_global) and an all-reduce of the float32 gradient.
+"""
+import math
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+
+
+def _dist_on():
+    return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+
+
+def allreduce_(t):
+    if _dist_on():
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return t
+
+
+def energy_moments(eloc, extra=None):
+    """Global moments from the local shard: returns (ns_global, mean E (complex), var, mean(extra))."""
+    e = torch.view_as_real(eloc) if eloc.is_complex() else torch.stack([eloc, torch.zeros_like(eloc)], dim=-1)
+    m = torch.zeros(6, dtype=torch.float64, device=e.device)
+    m[0] = e.shape[0]
+    m[1] = e[:, 0].sum()
+    m[2] = e[:, 1].sum()
+    m[3] = (e[:, 0] ** 2).sum()
+    m[4] = (e[:, 1] ** 2).sum()
+    if extra is not None:
+        m[5] = extra.sum()
+    allreduce_(m)
+    n = m[0]
+    mean_re, mean_im = m[1] / n, m[2] / n
+    var = m[3] / n - mean_re ** 2 + m[4] / n - mean_im ** 2   # np.var of a complex array = var(re) + var(im)
+    return n, torch.complex(mean_re, mean_im), var, m[5] / n
+
+
+def seeds(eloc, mean_e, n_global, complex_head, logp=None, mean_logp=None, T=0.0, free_energy=False):
+    """Per-sample backward seeds of the reference's surrogate costs.
+
+    real:     d cost/d logP_b = (E_b - <E>)/ns                       (1DTFIM/TrainingRNN_1DTFIM.py:157)
+    free en.: E -> E + T*logP                                        (RydbergKagome_2DGRU/Run_RNNWF_Rydberg.py:158-159)
+    complex:  d/d logP_b = Re(E_b - <E>)/ns + T (logP_b - <logP>)/ns,  d/d phase_b = 2 Im(E_b - <E>)/ns
+                                                                     (J1J2/TrainingRNN_J1J2.py:197, 2DHeisenberg/Run_RNNWF_2DHeis.py:199)
+    """
+    d = eloc - mean_e
+    if complex_head:
+        s_logp = d.real / n_global
+        if T != 0.0:
+            s_logp = s_logp + T * (logp - mean_logp) / n_global
+        return s_logp.contiguous(), (2.0 * d.imag / n_global).contiguous()
+    s = d.real if d.is_complex() else d
+    if free_energy and T != 0.0:
+        s = s + T * (logp - mean_logp)
+    return (s / n_global).contiguous(), None
+
+
+class TFAdam:
+    """tf.train.AdamOptimizer semantics: lr_t = lr*sqrt(1-b2^t)/(1-b1^t); theta -= lr_t*m/(sqrt(v)+eps)."""
+
+    def __init__(self, numel, device, beta1=0.9, beta2=0.999, eps=1e-8):
+        self.m = torch.zeros(numel, dtype=torch.float32, device=device)
+        self.v = torch.zeros(numel, dtype=torch.float32, device=device)
+        self.b1, self.b2, self.eps, self.t = beta1, beta2, eps, 0
+
+    def step(self, params, grad, lr):
+        self.t += 1
+        self.m.mul_(self.b1).add_(grad, alpha=1 - self.b1)
+        self.v.mul_(self.b2).addcmul_(grad, grad, value=1 - self.b2)
+        lr_t = lr * math.sqrt(1 - self.b2 ** self.t) / (1 - self.b1 ** self.t)
+        params.addcdiv_(self.m, self.v.sqrt().add_(self.eps), value=-lr_t)
+
+
+class VMC:
+    """Sample -> E_loc -> gradient -> update for one engine and one Hamiltonian."""
+
+    def __init__(self, engine, ham, ham_params, numsamples, lr=1e-3, seed=111, T=0.0, free_energy=False,
+                 prefix_reuse=True, clip=None):
+        self.eng, self.ham, self.ham_params = engine, ham, ham_params
+        self.ns = int(numsamples)
+        self.rank = dist.get_rank() if _dist_on() else 0
+        self.world = dist.get_world_size() if _dist_on() else 1
+        self.seed, self.T, self.free_energy, self.lr, self.clip = seed, T, free_energy, lr, clip
+        self.saved = engine.new_saved(self.ns)
+        self.prefix_reuse = prefix_reuse
+        self.opt = TFAdam(engine.num_params, engine.device)
+        self.it = 0
+        self.last = {}
+
+    def sample_and_energies(self, uniforms=None):
+        eng = self.eng
+        offset = (self.it * self.world + self.rank) * self.ns   # disjoint Philox rows per step and rank
+        s, lp, ph = eng.sample(self.ns, uniforms=uniforms, seed=self.seed, row_offset=offset, saved=self.saved)
+        e, cnt = eng.local_energies(self.ham, self.ham_params, s, lp, ph,
+                                    saved=self.saved if self.prefix_reuse else None, return_count=True)
+        return s, lp, ph, e, cnt
+
+    def gradient(self, s, lp, ph, e):
+        eng = self.eng
+        extra = lp if (self.T != 0.0) else None
+        n, mean_e, var, mean_lp = energy_moments(e, extra)
+        sl, sp = seeds(e, mean_e, n, eng.complex_head, logp=lp, mean_logp=mean_lp, T=self.T, free_energy=self.free_energy)
+        grad = eng.backward(s, self.saved, sl, sp)
+        allreduce_(grad)
+        return grad, mean_e, var
+
+    def step(self, uniforms=None, lr=None, update=True):
+        s, lp, ph, e, cnt = self.sample_and_energies(uniforms)
+        grad, mean_e, var = self.gradient(s, lp, ph, e)
+        if update:
+            if self.clip is not None:
+                grad.clamp_(-self.clip, self.clip)
+            self.opt.step(self.eng.params, grad, self.lr if lr is None else lr)
+            self.eng.set_weights()
+        self.it += 1
+        self.last = dict(samples=s, logp=lp, phase=ph, eloc=e, nconn=cnt, grad=grad)
+        return mean_e, var
