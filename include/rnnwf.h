@@ -132,6 +132,20 @@ int rnnwf_backward(rnnwf_handle h, int64_t rows, const int8_t* samples_dev, cons
                    const double* seed_logp_dev, const double* seed_phase_dev, float* grad_dev,
                    void* workspace_dev, int64_t workspace_bytes, void* stream);
 
+/* No counterpart in the reference.  rnnwf_logpsi for hosts that cannot give the library any device
+ * scratch: a process whose runtime has already claimed the whole GPU (TensorFlow 1.x does by default), or a
+ * bare ctypes script that holds nothing but its input and output arrays.  The sweep's history ring then lives
+ * in a fixed RNNWF_STATIC_SCRATCH_BYTES array inside the library image (each GPU that loads the library keeps
+ * it until exit).  Same inputs, outputs and results as rnnwf_logpsi without `saved`; no workspace argument;
+ * the call allocates nothing.  Limit: one thread block's ring (ring_len x 32 rows x padded units x 4 bytes)
+ * must fit in the array, otherwise the call fails with RNNWF_ENOMEM and says so; fewer thread blocks run
+ * concurrently than with a caller workspace, so it is slower on large batches.  The first call on a device
+ * resolves the array's device address (cudaGetSymbolAddress) -- make it outside any stream capture.  All
+ * calls on a device share the array: calls that overlap on the GPU (different streams) race. */
+#define RNNWF_STATIC_SCRATCH_BYTES (16u << 20)
+int rnnwf_logpsi_static(rnnwf_handle h, int64_t rows, const int8_t* samples_dev, double* logp_dev, double* phase_dev,
+                        void* stream);
+
 /* Kernel-regime report for the profiler notes: fills `buf` with a one-line description of the tile
  * shape / pipe (FFMA or tcgen05) the handle's sweeps run in. */
 int rnnwf_describe(rnnwf_handle h, char* buf, int cap);

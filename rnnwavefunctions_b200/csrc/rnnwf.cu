@@ -3,6 +3,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -818,3 +819,90 @@ int rnnwf_describe(rnnwf_handle h, char* buf, int cap) {
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// rnnwf_logpsi_static -- log-amplitudes for callers that cannot obtain device scratch memory.
+//
+// Some hosts of this library have no way to hand us a workspace: the process's deep-learning runtime
+// has reserved the whole GPU up front (TensorFlow 1.x, the reference's own runtime, does so by default),
+// or the binding is a bare ctypes/NumPy script with no device allocator of its own beyond the tensors
+// it was given.  For them the history ring of the sweep lives in the fixed array below, which is part
+// of the library image: every GPU that loads librnnwf.so carries these RNNWF_STATIC_SCRATCH_BYTES until
+// the process exits, whether or not this entry point is ever called.
+//
+// The array's name is only meaningful in device code; on the host it is a handle for the symbol.  The
+// device address is looked up once per device with cudaGetSymbolAddress (first call on that device,
+// with that device current) and remembered.  Make that first call outside any stream capture.
+// Nothing in the ring has to start at zero (every history slot is written before it is read), so it
+// is never cleared; it simply keeps whatever the previous call left.  All calls on a device share the
+// one array: two calls whose kernels overlap on the GPU (different streams) corrupt each other.
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_scratch[RNNWF_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float* g_static_scratch_addr[kMaxDevices] = {nullptr};
+std::mutex g_static_scratch_mu;
+
+int static_scratch_address(int device, float** out) {
+  if (device < 0 || device >= kMaxDevices) return fail(RNNWF_EINVAL, "rnnwf_logpsi_static: device index out of range");
+  std::lock_guard<std::mutex> lock(g_static_scratch_mu);
+  if (g_static_scratch_addr[device] == nullptr) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess || p == nullptr)
+      return fail(RNNWF_ECUDA, std::string("rnnwf_logpsi_static: cudaGetSymbolAddress(g_static_scratch): ") + cudaGetErrorString(e));
+    g_static_scratch_addr[device] = static_cast<float*>(p);
+  }
+  *out = g_static_scratch_addr[device];
+  return RNNWF_OK;
+}
+}  // namespace
+
+extern "C" int rnnwf_logpsi_static(rnnwf_handle h, int64_t rows, const int8_t* samples_dev, double* logp_dev,
+                                   double* phase_dev, void* stream) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (rows <= 0 || samples_dev == nullptr || logp_dev == nullptr)
+    return fail(RNNWF_EINVAL, "rnnwf_logpsi_static: rows must be positive, samples and logp non-null");
+  int dev = -1;
+  CUDA_TRY(cudaGetDevice(&dev));
+  if (dev != h->device) return fail(RNNWF_EINVAL, "rnnwf_logpsi_static: the handle's device is not the current device");
+  const rnnwf_model& m = *h;
+  // tallest tile whose per-CTA ring fits; as many CTAs as the fixed array can serve
+  const int pad = (m.ncls_max > 1) ? 3 * m.ncls_max : 0;
+  LaunchShape s;
+  bool found = false;
+  long long smallest = 0;
+  for (int wr = 4; wr >= 1 && !found; wr >>= 1) {
+    const int Mp = 32 * wr, Mr = Mp - pad;
+    if (Mr <= 0) continue;
+    SmemLayout L(m.ncls_max, m.Gblk, Mp, m.ldH, m.nhp, m.ND, m.Tsym);
+    if (L.total > 227 * 1024) continue;
+    const long long per_cta = ring_bytes(m, 1, Mp);
+    smallest = per_cta;
+    const long long tiles = (rows + Mr - 1) / Mr;
+    if (per_cta > (long long)RNNWF_STATIC_SCRATCH_BYTES) continue;
+    if (wr == 1 || tiles >= m.num_sms) {
+      s.WR = wr; s.Mp = Mp; s.Mr = Mr; s.threads = 32 * wr * m.WC; s.smem = L.total;
+      const long long cap = (long long)RNNWF_STATIC_SCRATCH_BYTES / per_cta;
+      s.grid = (int)std::max(1LL, std::min<long long>(std::min<long long>(tiles, m.num_sms), cap));
+      found = true;
+    }
+  }
+  if (!found) {
+    char msg[256];
+    std::snprintf(msg, sizeof(msg),
+                  "rnnwf_logpsi_static: this model needs %lld bytes of history ring per thread block, the built-in scratch "
+                  "holds %u (RNNWF_STATIC_SCRATCH_BYTES); use rnnwf_logpsi with a caller workspace",
+                  smallest, (unsigned)RNNWF_STATIC_SCRATCH_BYTES);
+    return fail(RNNWF_ENOMEM, msg);
+  }
+  float* ring = nullptr;
+  if ((rc = static_scratch_address(dev, &ring))) return rc;
+  SweepParams P;
+  fill_model_params(m, s, P);
+  P.mode = MODE_EVAL; P.rows = rows; P.cfg_in = samples_dev; P.out_logp = logp_dev; P.out_phase = phase_dev;
+  P.ring = ring;
+  return launch_sweep(m, P, s, static_cast<cudaStream_t>(stream));
+}
