@@ -1,0 +1,184 @@
+"""Drop-in for the reference package ``2DHeisenberg/``.
+Reference: 2DHeisenberg/MDTensorizedcell.py, MDTensorizedGRUcell.py, MDComplexRNN.py, Helper_Functions.py,
+Run_RNNWF_2DHeis.py."""
+import numpy as np
+import torch
+
+from . import _lib
+from .compat import Handle, Placeholder, Session, find_wf, to_numpy
+from .engine import Engine
+
+
+class MDTensorizedcell:
+    """tanh(sum_ik [h_h;h_v]_i [x_h;x_v]_k W_jik + b)  (2DHeisenberg/MDTensorizedcell.py:7-49)."""
+    cell_id = _lib.CELL_TENS2D
+
+
+class MDTensorizedGRUcell:
+    """Tensorized 2D GRU cell (2DHeisenberg/MDTensorizedGRUcell.py:7-61) -- the reference's ``MDRNNcell`` when
+    imported from MDTensorizedGRUcell, as Run_RNNWF_2DHeis.py does."""
+    cell_id = _lib.CELL_TENSGRU2D
+
+
+MDRNNcell = MDTensorizedGRUcell
+
+# group elements in the order the reference builds its sample lists (MDComplexRNN.py:320-577)
+_ROT = lambda k: (lambda s: torch.rot90(s, k, dims=(1, 2)))          # tf.image.rot90(k) == np.rot90(axes=(1,2))
+_OPS = {
+    "id": lambda s: s, "r1": _ROT(-1), "r2": _ROT(-2), "r3": _ROT(-3),
+    "fx": lambda s: torch.flip(s, dims=[1]), "fy": lambda s: torch.flip(s, dims=[2]),
+    "t": lambda s: s.transpose(1, 2), "tr2": lambda s: torch.rot90(s, -2, dims=(1, 2)).transpose(1, 2),
+}
+_GROUPS = {
+    "rotsym": (["id", "r1", "r2", "r3"], {"A": [1, 1, 1, 1], "B": [1, -1, 1, -1]}),
+    "rotreducedsym": (["id", "r1"], {"A": [1, 1], "B": [1, -1]}),
+    "c2sym": (["id", "r2"], {"A": [1, 1], "B": [1, -1]}),
+    "c2vsym": (["id", "r2", "fx", "fy"], {"A1": [1, 1, 1, 1], "A2": [1, 1, -1, -1], "B1": [1, -1, 1, -1], "B2": [1, -1, -1, 1]}),
+    "c2dsym": (["id", "r2", "t", "tr2"], {"A1": [1, 1, 1, 1], "A2": [1, 1, -1, -1], "B1": [1, -1, 1, -1], "B2": [1, -1, -1, 1]}),
+    "c4vsym": (["id", "r1", "r2", "r3", "fx", "fy", "t", "tr2"],
+               {"A1": [1] * 8, "A2": [1, 1, 1, 1, -1, -1, -1, -1], "B1": [1, -1, 1, -1, 1, 1, -1, -1], "B2": [1, -1, 1, -1, -1, -1, 1, 1]}),
+}
+
+
+def regularized_identity(x, epsilon=1e-4):
+    """2DHeisenberg/MDComplexRNN.py:23-25."""
+    sign = torch.where(x >= 0, torch.ones_like(x), -torch.ones_like(x))
+    return sign * torch.sqrt(x * x + epsilon * epsilon)
+
+
+class RNNwavefunction:
+    """2DHeisenberg/MDComplexRNN.py:27-65."""
+
+    def __init__(self, systemsize_x, systemsize_y, cell=None, activation=None, units=[10], scope='RNNwavefunction', seed=111,
+                 mag_fixed=True, magnetization=0):
+        self.Nx, self.Ny, self.N = systemsize_x, systemsize_y, systemsize_x * systemsize_y
+        self.scope, self.seed, self.mag_fixed, self.magnetization = scope, seed, mag_fixed, magnetization
+        cid = getattr(cell, "cell_id", _lib.CELL_TENSGRU2D)
+        self.engine = Engine(cid, systemsize_x, systemsize_y, num_units=units[0], complex_head=True, u1=bool(mag_fixed),
+                             magnetization=int(magnetization), seed=seed)
+        self._step = 0
+
+    def sample(self, numsamples, inputdim, uniforms=None, philox=None):
+        """MDComplexRNN.py:80-173 -> int64 [numsamples, Nx, Ny]."""
+        if isinstance(numsamples, Placeholder):
+            raise TypeError("numsamples must be an int")
+        if uniforms is None and philox is None:
+            philox = (self.seed, self._step * numsamples)
+            self._step += 1
+        sd, off = philox if philox is not None else (0, 0)
+        s, lp, ph = self.engine.sample(numsamples, uniforms=uniforms, seed=sd, row_offset=off)
+        self.samples = s.long()
+        return self.samples
+
+    def log_amplitude_nosymmetry(self, samples, inputdim):
+        """MDComplexRNN.py:177-281 -> (log_probs, log_phases), float64 [B] each."""
+        self.log_probs, self.log_phases = self.engine.logpsi(torch.as_tensor(samples))
+        return self.log_probs, self.log_phases
+
+    def log_amplitude_nosym(self, samples, inputdim):
+        """MDComplexRNN.py:284-286 -> complex128 [B]."""
+        if isinstance(samples, Placeholder):
+            return Handle(self, lambda s: self.log_amplitude_nosym(s, inputdim), samples)
+        lp, ph = self.log_amplitude_nosymmetry(samples, inputdim)
+        return torch.complex(0.5 * lp, ph)
+
+    def log_amplitudes_fromsymmetrygroup(self, list_samples, inputdim, group_character_signs):
+        """MDComplexRNN.py:290-316: amplitude sqrt(mean_g P_g), phase arg(sum_g e^{i phi_g}/chi_g) with the real part
+        regularised.  All G copies go through the device sweep in one batch."""
+        G = len(list_samples)
+        allc = torch.cat([torch.as_tensor(s).reshape(-1, self.Nx, self.Ny) for s in list_samples], dim=0)
+        lp, ph = self.engine.logpsi(allc)
+        lp, ph = lp.view(G, -1), ph.view(G, -1)
+        ch = torch.as_tensor(np.asarray(group_character_signs, dtype=np.float64), device=lp.device).view(G, 1)
+        re = (torch.cos(ph) / ch).sum(0)
+        im = (torch.sin(ph) / ch).sum(0)
+        logp = torch.log(torch.exp(lp).sum(0) / G)
+        return torch.complex(0.5 * logp, torch.atan2(im, regularized_identity(re)))
+
+    def _sym(self, name, samples, inputdim, group_character, spinparity_value=None):
+        if isinstance(samples, Placeholder):
+            return Handle(self, lambda s: self._sym(name, s, inputdim, group_character, spinparity_value), samples)
+        ops, table = _GROUPS[name]
+        s = torch.as_tensor(samples).to(self.engine.device)
+        lst = [_OPS[o](s) for o in ops]
+        signs = list(table[group_character])
+        if spinparity_value is not None:
+            lst = lst + [_OPS[o](1 - s) for o in ops]
+            signs = signs + [spinparity_value * c for c in signs]
+        return self.log_amplitudes_fromsymmetrygroup(lst, inputdim, signs)
+
+
+def _add_symmetry_methods():
+    def plain(name):
+        return lambda self, samples, inputdim, group_character: self._sym(name, samples, inputdim, group_character)
+
+    def parity(name):
+        return lambda self, samples, inputdim, group_character, spinparity_value: self._sym(name, samples, inputdim, group_character, spinparity_value)
+    for name in _GROUPS:
+        setattr(RNNwavefunction, f"log_amplitude_{name}", plain(name))
+        pname = "log_amplitude_c2v_spinparity" if name == "c2vsym" else f"log_amplitude_{name}_spinparity"
+        setattr(RNNwavefunction, pname, parity(name))
+    RNNwavefunction.log_amplitude_c2vsym_spinparity = RNNwavefunction.log_amplitude_c2v_spinparity
+
+
+_add_symmetry_methods()
+
+
+def Triangular2DHeis_MatrixElements(J2, Nx, Ny, sigmap, sigmas, matrixelements):
+    """2DHeisenberg/Helper_Functions.py:19-93 for ONE configuration (compatibility helper, host arrays);
+    returns the number of entries.  The training path enumerates on the device (Get_Elocs below)."""
+    s = to_numpy(sigmap).astype(np.int64)
+    z = 2.0 * s - 1
+    matrixelements[0] = 0.25 * (z[:-1] * z[1:]).sum() + 0.25 * (z[:, :-1] * z[:, 1:]).sum() + 0.25 * J2 * (z[:-1, :-1] * z[1:, 1:]).sum()
+    sigmas[0] = s
+    num = 1
+    for ny in range(Ny):
+        for nx in range(Nx):
+            for dx, dy, w in ((1, 0, -0.5), (0, 1, -0.5), (1, 1, J2 / 2)):
+                mx, my = nx + dx, ny + dy
+                if mx < Nx and my < Ny and s[nx, ny] != s[mx, my]:
+                    c = s.copy()
+                    c[nx, ny], c[mx, my] = s[mx, my], s[nx, ny]
+                    sigmas[num] = c
+                    matrixelements[num] = w
+                    num += 1
+    return num
+
+
+def Triangular2DHeis_LocalEnergies(J2, Nx, Ny, sigmasp, sigmas, H, sigmaH, matrixelements):
+    """2DHeisenberg/Helper_Functions.py:95-119 -> (slices, total)."""
+    slices, length = [], 0
+    for n in range(sigmasp.shape[0]):
+        num = Triangular2DHeis_MatrixElements(J2, Nx, Ny, sigmasp[n], sigmaH, matrixelements)
+        slices.append(slice(length, length + num))
+        H[slices[n]] = matrixelements[:num]
+        sigmas[slices[n]] = sigmaH[:num]
+        length += num
+    return slices, length
+
+
+def Get_Elocs(J2, Nx, Ny, samples, sigmas=None, H=None, log_amplitudes=None, sigmaH=None, matrixelements=None, inputs=None,
+              log_amps=None, sess=None, RNN_symmetry="nosym"):
+    """2DHeisenberg/Helper_Functions.py:152-177 -> complex128 ndarray [numsamples].  ``log_amps`` is the wavefunction
+    or a handle from ``wf.log_amplitude_nosym(placeholder, 2)``; the scratch arrays are not needed."""
+    wf = find_wf(log_amps, sess, inputs)
+    if RNN_symmetry != "nosym":
+        raise NotImplementedError("fused E_loc with symmetry-projected amplitudes: P2 row, not built yet")
+    e = wf.engine.local_energies(_lib.HAM_HEIS2D, [float(J2)], torch.as_tensor(to_numpy(samples)))
+    return e.cpu().numpy()
+
+
+def Get_Samples_and_Elocs(J2, Nx, Ny, samples=None, sigmas=None, H=None, log_amplitudes=None, sigmaH=None, matrixelements=None,
+                          samples_tensor=None, inputs=None, log_amps=None, sess=None, RNN_symmetry="nosym"):
+    """2DHeisenberg/Helper_Functions.py:123-150 -> (samples int64 ndarray, local_energies complex128 ndarray).
+    Sampling, the saved hidden states and the connected-configuration sweep stay on the device in between."""
+    wf = find_wf(log_amps, samples_tensor, sess)
+    if RNN_symmetry != "nosym":
+        raise NotImplementedError("fused E_loc with symmetry-projected amplitudes: P2 row, not built yet")
+    ns = samples.shape[0] if samples is not None else samples_tensor.numsamples
+    eng = wf.engine
+    saved = eng.new_saved(ns)
+    s, lp, ph = eng.sample(ns, seed=wf.seed, row_offset=wf._step * ns, saved=saved)
+    wf._step += 1
+    e = eng.local_energies(_lib.HAM_HEIS2D, [float(J2)], s, lp, ph, saved=saved)
+    return s.long().cpu().numpy(), e.cpu().numpy()
