@@ -20,6 +20,11 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src)
   unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem_src));
 }
+// 4-byte variant with zero-fill: src_bytes == 0 writes zeros without touching global memory
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gmem_src, int src_bytes) {
+  unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(s), "l"(gmem_src), "r"(src_bytes));
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
 
@@ -173,7 +178,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) sweep_kernel(const SweepParams
             for (int c = 0; c < NTU; ++c) acc[a][b][c] = 0.f;
 
         if (nchunks > 0) {
-          float4 areg[2];
+          // One pipeline stage = the class-sliced weights of one k-chunk (bulk 16 B cp.async) plus the matching
+          // 8 columns of the neighbours' hidden states, transposed on the fly into As[kk][position] by 4 B cp.async
+          // (zero-filled for padding positions) -- nothing is staged through registers.
           auto issue = [&](int ci, int buf) {
             const int sidx = ci / P.cps, c = ci - sidx * P.cps;
             const int s = (apack >> (4 * sidx)) & 15;
@@ -182,33 +189,19 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) sweep_kernel(const SweepParams
                                 (size_t)(vm->slot_rank[s] * P.cps + c) * n4;
             float4* dst = Ws + buf * wstage;
             for (int i = tid; i < n4; i += nthreads) cp_async16(dst + i, src + i);
-            cp_async_commit();
             const int qn = sm->nbr[s];
-#pragma unroll
-            for (int u = 0; u < 2; ++u) {
-              const int idx = tid + u * nthreads;
-              areg[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (idx < 2 * Mp) {
-                const int r = perm[idx >> 1];
-                if (r >= 0) areg[u] = __ldcg(reinterpret_cast<const float4*>(hist_ptr(qn, r) + c * KC + (idx & 1) * 4));
-              }
+            float* abase = As + buf * KC * ldA;
+            for (int idx = tid; idx < Mp * KC; idx += nthreads) {
+              const int pos = idx >> 3, kk = idx & 7;
+              const int r = perm[pos];
+              const float* g = (r >= 0) ? hist_ptr(qn, r) + c * KC + kk : P.head_b;
+              cp_async4(abase + kk * ldA + pos, g, r >= 0 ? 4 : 0);
             }
+            cp_async_commit();
           };
-          auto storeA = [&](int buf) {
-#pragma unroll
-            for (int u = 0; u < 2; ++u) {
-              const int idx = tid + u * nthreads;
-              if (idx < 2 * Mp) {
-                float* a = As + buf * KC * ldA + (idx & 1) * 4 * ldA + (idx >> 1);
-                a[0] = areg[u].x; a[ldA] = areg[u].y; a[2 * ldA] = areg[u].z; a[3 * ldA] = areg[u].w;
-              }
-            }
-          };
-
           issue(0, 0);
           for (int ci = 0; ci < nchunks; ++ci) {
             const int buf = ci & 1;
-            storeA(buf);
             cp_async_wait_all();
             __syncthreads();
             if (ci + 1 < nchunks) issue(ci + 1, buf ^ 1);
