@@ -96,6 +96,10 @@ struct SweepParams {
   float4* sv_gates;         // [Q][sv_rows][Gp]
   double2* sv_cum;          // [Tsym][sv_rows]
   long long sv_rows;
+  // ---- tensor-core regime (sweep_tc.cuh)
+  const unsigned char* tc_B;   // [3 variants][tc_np passes][weight image]
+  const float* tc_bias;        // [2][nhp]: b, bg
+  int tc_np;
   // ---- scratch
   float* ring;              // [gridDim.x][ring_len][Mp][nhp]
 };

@@ -52,6 +52,12 @@ struct rnnwf_model_impl {
   float4* d_bias = nullptr;
   float* d_head_w = nullptr;
   float* d_head_b = nullptr;
+  // tensor-core regime
+  int precision = 0;            // 0: FP32 FFMA, 1: BF16 tensor cores (tcgen05), hi+lo split activations
+  bool tc_enabled = false;
+  int tc_np = 0;
+  unsigned char* d_tcB = nullptr;
+  float* d_tcbias = nullptr;
   const float* d_params = nullptr;  // last parameter vector handed to set_weights (caller-owned)
   bool weights_set = false;
 

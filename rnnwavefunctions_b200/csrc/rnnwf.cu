@@ -9,6 +9,7 @@
 
 #include "model.h"
 #include "sweep.cuh"
+#include "sweep_tc.cuh"
 #include "pack.cuh"
 #include "eloc.cuh"
 #include "backward.cuh"
@@ -60,6 +61,8 @@ int build_model(rnnwf_model& m) {
   m.u1 = c.u1 ? 1 : 0;
   m.cps = m.nhp / KC;
   m.num_params = 0;
+  m.precision = c.reserved[0];
+  if (m.precision != 0 && m.precision != 1) return fail(RNNWF_EINVAL, "precision must be 0 (fp32) or 1 (bf16 tensor cores)");
   const int nh = m.nh, Nx = c.nx, Ny = c.ny;
   if (nh < 1 || nh > 1024 || Nx < 1 || Ny < 1) return fail(RNNWF_EINVAL, "bad lattice / num_units");
   if ((long long)Nx * Ny * std::max(1, c.num_layers) > 30000) return fail(RNNWF_EINVAL, "lattice too large for int16 step tables");
@@ -271,6 +274,9 @@ int build_model(rnnwf_model& m) {
     v.meta.b_off = (uint32_t)boff;
     boff += m.Gp;
   }
+  m.tc_enabled = (m.precision == 1 && m.cell == CELL_TENSGRU2D);
+  if (m.precision == 1 && !m.tc_enabled) return fail(RNNWF_EINVAL, "the tensor-core regime is implemented for the tensorized 2D GRU cell");
+  m.tc_np = (m.nh + TC_JP - 1) / TC_JP;
   m.wpack_float4 = std::max(1LL, woff);
   m.xtab_float4 = std::max(1LL, xoff);
   m.bias_float4 = std::max(1LL, boff);
@@ -283,6 +289,13 @@ int build_model(rnnwf_model& m) {
 struct LaunchShape { int WR, Mp, Mr, threads, smem, grid; };
 
 int pick_shape(const rnnwf_model& m, long long rows, LaunchShape& s) {
+  if (m.tc_enabled) {
+    const TcSmem ts(m.nhp, m.Tsym);
+    const long long tiles = (rows + TC_ROWS - 1) / TC_ROWS;
+    s.WR = 4; s.Mp = TC_ROWS; s.Mr = TC_ROWS; s.threads = TC_THREADS; s.smem = ts.total;
+    s.grid = (int)std::max(1LL, std::min<long long>(tiles, m.num_sms));
+    return RNNWF_OK;
+  }
   const int pad = (m.ncls_max > 1) ? 3 * m.ncls_max : 0;
   for (int wr = 4; wr >= 1; wr >>= 1) {
     const int Mp = 32 * wr, Mr = Mp - pad;
@@ -310,6 +323,7 @@ void fill_model_params(const rnnwf_model& m, const LaunchShape& s, SweepParams& 
   P.ring_len = m.ring_len; P.WR = s.WR; P.WC = m.WC; P.Mp = s.Mp; P.Mr = s.Mr; P.ncls_max = m.ncls_max;
   P.steps = m.d_steps; P.variants = m.d_variants; P.Wpack = m.d_wpack; P.Xtab = m.d_xtab; P.bias = m.d_bias;
   P.head_w = m.d_head_w; P.head_b = m.d_head_b;
+  P.tc_B = m.d_tcB; P.tc_bias = m.d_tcbias; P.tc_np = m.tc_np;
 }
 
 template <int TJ, int NTU>
@@ -320,6 +334,12 @@ cudaError_t launch_inst(const SweepParams& P, const LaunchShape& s, cudaStream_t
 
 int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& s, cudaStream_t st) {
   cudaError_t e;
+  if (m.tc_enabled) {
+    RNNWF_COUNT_LAUNCH(); sweep_tc_kernel<<<s.grid, s.threads, s.smem, st>>>(P);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("tensor-core sweep launch: ") + cudaGetErrorString(e));
+    return RNNWF_OK;
+  }
   if (m.NTU == 3 && m.TJ == 5) e = launch_inst<5, 3>(P, s, st);
   else if (m.NTU == 3 && m.TJ == 4) e = launch_inst<4, 3>(P, s, st);
   else e = launch_inst<4, 4>(P, s, st);
@@ -424,6 +444,13 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
   CREATE_TRY(cudaFuncSetAttribute(sweep_kernel<5, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
   CREATE_TRY(cudaFuncSetAttribute(sweep_kernel<4, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
   CREATE_TRY(cudaFuncSetAttribute(sweep_kernel<4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+  if (m->tc_enabled) {
+    const TcSmem ts(m->nhp, m->Tsym);
+    if (ts.total > 227 * 1024) { rnnwf_destroy(m); return fail(RNNWF_ENOMEM, "tensor-core sweep does not fit in shared memory for this lattice / width"); }
+    CREATE_TRY(cudaMalloc(&m->d_tcB, (size_t)3 * m->tc_np * ts.b_bytes));
+    CREATE_TRY(cudaMalloc(&m->d_tcbias, (size_t)2 * m->nhp * 4));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+  }
   CREATE_TRY(backward_init());
 #undef CREATE_TRY
   *out = m;
@@ -434,6 +461,7 @@ int rnnwf_destroy(rnnwf_handle h) {
   if (h == nullptr) return RNNWF_OK;
   cudaFree(h->d_steps); cudaFree(h->d_variants); cudaFree(h->d_site_of_t); cudaFree(h->d_wpack);
   cudaFree(h->d_xtab); cudaFree(h->d_bias); cudaFree(h->d_head_w); cudaFree(h->d_head_b);
+  cudaFree(h->d_tcB); cudaFree(h->d_tcbias);
   delete h;
   return RNNWF_OK;
 }
@@ -502,6 +530,14 @@ int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
   RNNWF_COUNT_LAUNCH(); pack_head_kernel<<<cdiv((long long)h->nhp * h->ND, 256), 256, 0, st>>>(
       params_dev + wd->offset, params_dev + bd->offset, wp ? params_dev + wp->offset : nullptr,
       bp ? params_dev + bp->offset : nullptr, h->nh, h->nhp, h->D, h->ND, h->d_head_w, h->d_head_b);
+  if (h->tc_enabled) {
+    const TcSmem ts(h->nhp, h->Tsym);
+    const long long n = 3LL * h->tc_np * (ts.b_bytes / 2);
+    RNNWF_COUNT_LAUNCH(); pack_tc_kernel<<<std::min(2048, cdiv(n, 256)), 256, 0, st>>>(
+        params_dev + h->tensor("W")->offset, params_dev + h->tensor("Wg")->offset, params_dev + h->tensor("Wmerge")->offset,
+        h->nh, h->nhp, h->tc_np, reinterpret_cast<__nv_bfloat16*>(h->d_tcB));
+    RNNWF_COUNT_LAUNCH(); pack_tc_bias_kernel<<<1, 256, 0, st>>>(params_dev + h->tensor("b")->offset, params_dev + h->tensor("bg")->offset, h->nh, h->nhp, h->d_tcbias);
+  }
   CUDA_TRY(cudaGetLastError());
   h->d_params = params_dev;
   h->weights_set = true;
@@ -811,9 +847,10 @@ int rnnwf_ffma_probe(float* out_dev, int blocks, int iters, void* stream) {
 int rnnwf_describe(rnnwf_handle h, char* buf, int cap) {
   if (h == nullptr || buf == nullptr || cap <= 0) return fail(RNNWF_EINVAL, "null argument");
   std::snprintf(buf, cap,
-                "cell=%d nh=%d (padded %d) steps=%d symbols=%d slots=%d classes=%d | pipe=FFMA fp32, tile=128 rows x %d col-groups "
+                "cell=%d nh=%d (padded %d) steps=%d symbols=%d slots=%d classes=%d | pipe=%s, tile=128 rows x %d col-groups "
                 "(TJ=%d NTU=%d WC=%d passes=%d), k-chunk=%d, ring=%d steps, params=%lld",
-                h->cell, h->nh, h->nhp, h->Q, h->Tsym, h->nslots, h->ncls_max, h->Gblk, h->TJ, h->NTU, h->WC, h->ncb, KC,
+                h->cell, h->nh, h->nhp, h->Q, h->Tsym, h->nslots, h->ncls_max,
+                h->tc_enabled ? "tcgen05 BF16 (hi+lo activations, FP32 accumulate in TMEM; 7 column passes of 112)" : "FFMA fp32", h->Gblk, h->TJ, h->NTU, h->WC, h->ncb, KC,
                 h->ring_len, (long long)h->num_params);
   return RNNWF_OK;
 }

@@ -1,0 +1,468 @@
+// Tensor-core regime of the lattice sweep (tcgen05 / TMEM), for the tensorized 2D GRU cell.
+//
+// Per lattice site and 128-row tile the cell needs  s, g = hc (W[:,:,sl] + W[:,:,2+su]) , m = hc Wmerge  with a weight
+// slice that depends on the row's neighbouring spins (sl, su).  On the tensor cores the dependence is moved to
+// the epilogue by linearity:
+//        s = hc Wa + sl * (hc Wb) + su * (hc Wc),   Wa = W0 + W2,  Wb = W1 - W0,  Wc = W3 - W2   (same for g)
+// so every row multiplies the SAME operand: one dense [128 x 208] x [208 x 700] contraction per site, issued as
+// tcgen05.mma (kind::f16, BF16 in, FP32 accumulate in TMEM) in 7 column passes of 112 (16 hidden units x 7 blocks),
+// double-buffered in TMEM against the epilogue.  Weights are BF16; the hidden state is split hi + lo (two BF16
+// operands, two MMAs per k-step), which keeps E_loc within 1e-4 of the FP32 path (plain BF16 activations: 2.4e-3).
+//
+//   warp 0, lane 0 : control -- cp.async.bulk of the pre-packed weight images (UMMA K-major core-matrix layout,
+//                    mbarrier complete_tx), tcgen05.mma issue, tcgen05.commit
+//   warps 1..4     : one thread per row == TMEM lane.  Builds its row of the A operand (hi/lo) in shared memory from
+//                    the FP32 history ring, reads the accumulators with tcgen05.ld, applies the gates, evaluates the
+//                    heads / U(1) mask / draw / log-probability for its row without any cross-thread reduction.
+// Everything is synchronised by mbarriers; every wait is bounded and traps instead of hanging.
+//
+// Same reference behaviour as sweep.cuh for 2DHeisenberg/MDTensorizedGRUcell.py:49-61 and MDComplexRNN.py:69-286.
+#pragma once
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace rnnwf {
+
+constexpr int TC_ROWS = 128;
+constexpr int TC_JP = 16;               // hidden units per column pass
+constexpr int TC_NB = 7;                // column blocks per unit: Wa_s Wb_s Wc_s Wa_g Wb_g Wc_g Wmerge
+constexpr int TC_N = TC_JP * TC_NB;     // 112 MMA columns per pass
+constexpr int TC_THREADS = 160;
+constexpr int TC_TMEM_COLS = 256;
+constexpr uint32_t TC_SPIN_LIMIT = 1u << 26;
+
+struct TcSmem {
+  int off_Ahi, off_Alo, off_B, off_headw, off_headb, off_bias, off_sym, off_bar, off_tmem, total;
+  int a_bytes, b_bytes, kc;
+  __host__ __device__ TcSmem(int nhp, int Tsym) {
+    kc = 2 * (nhp / 8);                       // 16-byte k-cores of the concatenated [h_h ; h_v] operand
+    a_bytes = kc * (TC_ROWS / 8) * 128;
+    b_bytes = kc * (TC_N / 8) * 128;
+    int o = 0;
+    off_Ahi = o; o += a_bytes;
+    off_Alo = o; o += a_bytes;
+    off_B = o;   o += 2 * b_bytes;
+    off_headw = o; o += ((nhp * 4 * 4) + 15) & ~15;
+    off_headb = o; o += 16;
+    off_bias = o;  o += ((2 * (nhp + TC_JP) * 4) + 15) & ~15;
+    off_bar = o;   o += 128;
+    off_tmem = o;  o += 16;
+    off_sym = o;   o += ((Tsym * TC_ROWS) + 15) & ~15;
+    total = o + 1024;                          // slack for the 1024-byte alignment of the base
+  }
+};
+
+// ---- PTX wrappers ------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ uint32_t mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  return ok;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  for (uint32_t spin = 0; !mbar_try_wait(bar, parity); ++spin)
+    if (spin > TC_SPIN_LIMIT) { asm volatile("trap;"); }
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_alloc(uint32_t* smem_result, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_result)), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tc_dealloc(uint32_t taddr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T ; both operands K-major, no swizzle
+__device__ __forceinline__ void tc_mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&d)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]), "=r"(d[7]), "=r"(d[8]),
+        "=r"(d[9]), "=r"(d[10]), "=r"(d[11]), "=r"(d[12]), "=r"(d[13]), "=r"(d[14]), "=r"(d[15])
+      : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// shared-memory matrix descriptor: K-major, SWIZZLE_NONE, core matrix = 8 rows x 16 bytes (128 contiguous bytes);
+// LBO = byte distance between the two k-cores of one K=16 slice, SBO = byte distance between 8-row groups.
+__device__ __forceinline__ uint64_t tc_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+  return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) | ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) |
+         (1ull << 46);
+}
+// instruction descriptor: D=F32, A=B=BF16, both K-major, N, M
+__host__ __device__ constexpr uint32_t tc_idesc(int M, int N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// ------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepParams P) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const TcSmem L(P.nhp, P.Tsym);
+  unsigned char* const Ahi = smem + L.off_Ahi;
+  unsigned char* const Alo = smem + L.off_Alo;
+  unsigned char* const Bst = smem + L.off_B;
+  float* const headW = reinterpret_cast<float*>(smem + L.off_headw);
+  float* const headB = reinterpret_cast<float*>(smem + L.off_headb);
+  float* const biasS = reinterpret_cast<float*>(smem + L.off_bias);       // [2][nhp + 16]: b, bg
+  uint8_t* const symS = smem + L.off_sym;                                 // [Tsym][128]
+  uint64_t* const bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
+  uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(smem + L.off_tmem);
+  uint64_t* const bar_A = bars + 0;
+  uint64_t* const bar_B = bars + 1;      // [2]
+  uint64_t* const bar_mma = bars + 3;    // [2]
+  uint64_t* const bar_free = bars + 5;   // [2]
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const bool is_ctrl = (tid == 0);
+  const bool is_epi = (warp >= 1);
+  const int row = ((warp & 3) << 5) + lane;           // TMEM lane quarter of this warp -> tile row
+  const int nhp = P.nhp, nh = P.nh, ldb = nhp + TC_JP;
+  const int NP = P.tc_np, kc = L.kc;
+  const uint32_t A_LBO = (TC_ROWS / 8) * 128, B_LBO = (TC_N / 8) * 128, SBO = 128;
+  const uint32_t idesc = tc_idesc(TC_ROWS, TC_N);
+  float* const ring = P.ring + (size_t)blockIdx.x * P.ring_len * TC_ROWS * nhp;
+
+  if (tid == 0) {
+    mbar_init(bar_A, TC_ROWS);
+    mbar_init(bar_B + 0, 1); mbar_init(bar_B + 1, 1);
+    mbar_init(bar_mma + 0, 1); mbar_init(bar_mma + 1, 1);
+    mbar_init(bar_free + 0, TC_ROWS); mbar_init(bar_free + 1, TC_ROWS);
+    fence_mbar_init();
+  }
+  if (warp == 0) tc_alloc(tmem_slot, TC_TMEM_COLS);
+  for (int i = tid; i < nhp * 4; i += TC_THREADS) headW[i] = P.head_w[i];
+  if (tid < 4) headB[tid] = P.head_b[tid];
+  for (int i = tid; i < 2 * ldb; i += TC_THREADS) {
+    const int which = i / ldb, j = i - which * ldb;
+    biasS[i] = (j < nh) ? P.tc_bias[which * nhp + j] : 0.f;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // consumed-completion counters (parity = count & 1)
+  uint32_t nA = 0, nB[2] = {0, 0}, nMc[2] = {0, 0}, nF[2] = {0, 0};   // control thread
+  uint32_t nMe[2] = {0, 0};                                             // epilogue threads
+
+  const long long total_rows = (P.rows_dev != nullptr) ? (long long)(*P.rows_dev) : P.rows;
+  const long long ntiles = (total_rows + TC_ROWS - 1) / TC_ROWS;
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const long long row0 = tile * TC_ROWS;
+    const int nrows = (int)((total_rows - row0 < (long long)TC_ROWS) ? (total_rows - row0) : (long long)TC_ROWS);
+    int ts0 = 0;
+    if (P.mode == MODE_CHILD && P.par_hist != nullptr) {
+      const Child c0 = P.children[row0];
+      ts0 = (c0.tb >= 0 && c0.tb < c0.ta) ? c0.tb : c0.ta;
+    }
+    const int q0 = ts0 * P.symL;
+    const bool live = is_epi && row < nrows;
+
+    // ---- per-row state (registers of the row's thread)
+    double rlogp = 0.0, rphase = 0.0;
+    int rnup = 0, rparent = 0;
+    float rcoef = 0.f;
+    if (is_epi) {
+      if (live && P.mode != MODE_SAMPLE) {
+        const long long src = (P.mode == MODE_CHILD) ? (long long)P.children[row0 + row].parent : row0 + row;
+        const int8_t* c = P.cfg_in + src * P.nsites;
+        for (int t = 0; t < P.Tsym; ++t) symS[t * TC_ROWS + row] = (uint8_t)(c[P.steps[t].site] & 1);
+        if (P.mode == MODE_CHILD) {
+          const Child ch = P.children[row0 + row];
+          symS[ch.ta * TC_ROWS + row] ^= 1;
+          if (ch.tb >= 0) symS[ch.tb * TC_ROWS + row] ^= 1;
+          rparent = ch.parent;
+          rcoef = ch.coef;
+          for (int t = 0; t < ts0; ++t) rnup += symS[t * TC_ROWS + row];
+        }
+      } else {
+        for (int t = 0; t < P.Tsym; ++t) symS[t * TC_ROWS + row] = 0;
+      }
+    }
+    auto hist_ptr = [&](int qn) -> const float* {
+      if (P.par_hist != nullptr && qn < q0) return P.par_hist + ((size_t)qn * (size_t)P.par_rows + (size_t)rparent) * nhp;
+      return ring + ((size_t)(qn % P.ring_len) * TC_ROWS + row) * nhp;
+    };
+
+    for (int q = q0; q < P.Q; ++q) {
+      const StepMeta* sm = P.steps + q;
+      const int nb0 = sm->nbr[0], nb1 = sm->nbr[1];
+      const int variant = (nb0 >= 0 && nb1 >= 0) ? 0 : (nb0 >= 0 ? 1 : (nb1 >= 0 ? 2 : 3));
+      const int t = sm->sym;
+
+      if (is_ctrl && variant != 3) {
+        // ================= control thread: weight stream + MMA issue =================
+        const unsigned char* Bsrc = P.tc_B + (size_t)variant * NP * L.b_bytes;
+        for (int p = 0; p < 2 && p < NP; ++p) {
+          mbar_expect_tx(bar_B + p, L.b_bytes);
+          bulk_g2s(Bst + p * L.b_bytes, Bsrc + (size_t)p * L.b_bytes, L.b_bytes, bar_B + p);
+        }
+        mbar_wait(bar_A, nA & 1); ++nA;
+        for (int p = 0; p < NP; ++p) {
+          const int s = p & 1;
+          mbar_wait(bar_B + s, nB[s] & 1); ++nB[s];
+          mbar_wait(bar_free + s, (nF[s] & 1) ^ 1); ++nF[s];
+          tc_fence_after();
+          const uint32_t tmem_d = tmem_base + (uint32_t)(s * TC_N);
+          const uint32_t a_hi = smem_u32(Ahi), a_lo = smem_u32(Alo), b_s = smem_u32(Bst + s * L.b_bytes);
+          for (int ks = 0; ks < kc / 2; ++ks) {
+            const uint64_t bd = tc_desc(b_s + ks * 2 * B_LBO, B_LBO, SBO);
+            tc_mma_bf16(tmem_d, tc_desc(a_hi + ks * 2 * A_LBO, A_LBO, SBO), bd, idesc, ks > 0 ? 1u : 0u);
+            tc_mma_bf16(tmem_d, tc_desc(a_lo + ks * 2 * A_LBO, A_LBO, SBO), bd, idesc, 1u);
+          }
+          tc_commit(bar_mma + s);
+          if (p >= 1) {   // pass p-1 has finished reading its weight stage -> refill it with pass p+1
+            const int s1 = (p - 1) & 1;
+            mbar_wait(bar_mma + s1, nMc[s1] & 1); ++nMc[s1];
+            if (p + 1 < NP) {
+              mbar_expect_tx(bar_B + s1, L.b_bytes);
+              bulk_g2s(Bst + s1 * L.b_bytes, Bsrc + (size_t)(p + 1) * L.b_bytes, L.b_bytes, bar_B + s1);
+            }
+          }
+        }
+        { const int s1 = (NP - 1) & 1; mbar_wait(bar_mma + s1, nMc[s1] & 1); ++nMc[s1]; }
+      }
+
+      if (is_epi) {
+        // ================= one thread per row =================
+        if (variant != 3) {
+          // A operand rows: [h_h ; h_v] of this row, split hi + lo, core-matrix layout [k-core][row/8][row%8][8 bf16]
+          const uint32_t roff = (uint32_t)(row >> 3) * 128 + (uint32_t)(row & 7) * 16;
+#pragma unroll
+          for (int s = 0; s < 2; ++s) {
+            const int qn = (s == 0) ? nb0 : nb1;
+            const float* src = (qn >= 0 && live) ? hist_ptr(qn) : nullptr;
+            for (int c = 0; c < kc / 2; ++c) {
+              float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+              if (src != nullptr) {
+                v0 = *reinterpret_cast<const float4*>(src + c * 8);
+                v1 = *reinterpret_cast<const float4*>(src + c * 8 + 4);
+              }
+              const float f[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+              float lo[8];
+              uint4 hi4, lo4;
+              uint32_t* hp = reinterpret_cast<uint32_t*>(&hi4);
+              uint32_t* lp = reinterpret_cast<uint32_t*>(&lo4);
+#pragma unroll
+              for (int e = 0; e < 8; e += 2) {
+                const __nv_bfloat16 h0 = __float2bfloat16_rn(f[e]), h1 = __float2bfloat16_rn(f[e + 1]);
+                lo[e] = f[e] - __bfloat162float(h0);
+                lo[e + 1] = f[e + 1] - __bfloat162float(h1);
+                hp[e >> 1] = pack_bf16x2(__bfloat162float(h0), __bfloat162float(h1));
+                lp[e >> 1] = pack_bf16x2(lo[e], lo[e + 1]);
+              }
+              const uint32_t off = (uint32_t)(s * (kc / 2) + c) * A_LBO + roff;
+              *reinterpret_cast<uint4*>(Ahi + off) = hi4;
+              *reinterpret_cast<uint4*>(Alo + off) = lo4;
+            }
+          }
+          fence_proxy_async_smem();
+          mbar_arrive(bar_A);
+        }
+        const float cl = (nb0 >= 0) ? (float)symS[sm->nsym[0] * TC_ROWS + row] : 0.f;
+        const float cu = (nb1 >= 0) ? (float)symS[sm->nsym[1] * TC_ROWS + row] : 0.f;
+        float lg[4] = {0.f, 0.f, 0.f, 0.f};
+        float* ring_row = ring + ((size_t)(q % P.ring_len) * TC_ROWS + row) * nhp;
+        for (int p = 0; p < NP; ++p) {
+          const int s = p & 1;
+          uint32_t d[TC_NB][16];
+          if (variant != 3) {
+            mbar_wait(bar_mma + s, nMe[s] & 1); ++nMe[s];
+            __syncwarp();
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(s * TC_N);
+#pragma unroll
+            for (int b = 0; b < TC_NB; ++b) tc_ld16(taddr + b * 16, d[b]);
+            tc_wait_ld();
+            tc_fence_before();
+            mbar_arrive(bar_free + s);
+          } else {
+#pragma unroll
+            for (int b = 0; b < TC_NB; ++b)
+#pragma unroll
+              for (int e = 0; e < 16; ++e) d[b][e] = 0u;
+          }
+          float hnew[16];
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {
+            const int j = p * TC_JP + e;
+            const float sv = __uint_as_float(d[0][e]) + cl * __uint_as_float(d[1][e]) + cu * __uint_as_float(d[2][e]) + biasS[j];
+            const float gv = __uint_as_float(d[3][e]) + cl * __uint_as_float(d[4][e]) + cu * __uint_as_float(d[5][e]) + biasS[ldb + j];
+            const float mv = __uint_as_float(d[6][e]);
+            const float u = 1.0f / (1.0f + expf(-gv));
+            const float ht = tanhf(sv);
+            const float hv = (j < nh) ? (u * ht + (1.f - u) * mv) : 0.f;
+            hnew[e] = hv;
+            if (j < nh) {
+              const float4 w = *reinterpret_cast<const float4*>(headW + j * 4);
+              lg[0] = fmaf(hv, w.x, lg[0]); lg[1] = fmaf(hv, w.y, lg[1]); lg[2] = fmaf(hv, w.z, lg[2]); lg[3] = fmaf(hv, w.w, lg[3]);
+              if (live && P.sv_gates != nullptr && P.mode != MODE_CHILD)
+                P.sv_gates[((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * P.Gp + j] = make_float4(u, ht, mv, 0.f);
+            }
+          }
+          if (live) {
+#pragma unroll
+            for (int e4 = 0; e4 < 4; ++e4) {
+              const int j = p * TC_JP + e4 * 4;
+              if (j < nhp) {
+                const float4 v = make_float4(hnew[e4 * 4], hnew[e4 * 4 + 1], hnew[e4 * 4 + 2], hnew[e4 * 4 + 3]);
+                *reinterpret_cast<float4*>(ring_row + j) = v;
+                if (P.sv_hist != nullptr && P.mode != MODE_CHILD)
+                  *reinterpret_cast<float4*>(P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + j) = v;
+              }
+            }
+          }
+        }
+
+        // ---- heads for this row (softmax, U(1) mask, draw / teacher forcing, log psi)
+        if (live) {
+          float p0 = lg[0] + headB[0], p1 = lg[1] + headB[1];
+          const float mx = fmaxf(p0, p1);
+          p0 = expf(p0 - mx); p1 = expf(p1 - mx);
+          const float ssum = p0 + p1;
+          p0 /= ssum; p1 /= ssum;
+          if (P.u1) {
+            const int ndn = t - rnup;
+            p0 *= (P.cap_dn - ndn >= 0) ? 1.f : 0.f;
+            p1 *= (P.cap_up - rnup >= 0) ? 1.f : 0.f;
+            const float nrm = p0 + p1;
+            p0 /= nrm; p1 /= nrm;
+          }
+          int sy;
+          if (P.mode == MODE_SAMPLE) {
+            const float u = (P.uniforms != nullptr)
+                                ? P.uniforms[(size_t)(row0 + row) * P.Tsym + t]
+                                : philox_uniform(P.seed, P.row_offset + (unsigned long long)(row0 + row), (uint32_t)t);
+            const double tot = (double)p0 + (double)p1;
+            const double target = (double)u * tot;
+            sy = ((double)p0 <= target) ? 1 : 0;   // # of CDF entries <= target, clamped to the last class
+            symS[t * TC_ROWS + row] = (uint8_t)sy;
+          } else {
+            sy = symS[t * TC_ROWS + row];
+          }
+          rlogp += log((double)(sy ? p1 : p0));
+          if (P.complex_head) {
+            const double xs = (double)((sy ? lg[3] : lg[2]) + (sy ? headB[3] : headB[2]));
+            rphase += 3.14159265358979323846 * (xs / (1.0 + fabs(xs)));
+          }
+          rnup += sy;
+          if (P.sv_cum != nullptr && P.mode != MODE_CHILD)
+            P.sv_cum[(size_t)t * (size_t)P.sv_rows + (size_t)(row0 + row)] = make_double2(rlogp, rphase);
+        }
+      }
+    }  // steps
+
+    // ---- tile results
+    if (live) {
+      if (P.mode == MODE_CHILD) {
+        double base_lp = P.par_logp[rparent], base_ph = (P.par_phase != nullptr) ? P.par_phase[rparent] : 0.0;
+        if (ts0 > 0 && P.par_cum != nullptr) {
+          const double2 c = P.par_cum[(size_t)(ts0 - 1) * (size_t)P.par_rows + rparent];
+          base_lp -= c.x;
+          base_ph -= c.y;
+        }
+        const double amp = exp(0.5 * (rlogp - base_lp)) * (double)rcoef;
+        if (P.complex_head) {
+          double sn, cs;
+          sincos(rphase - base_ph, &sn, &cs);
+          atomicAdd(P.eloc + 2 * (size_t)rparent, amp * cs);
+          atomicAdd(P.eloc + 2 * (size_t)rparent + 1, amp * sn);
+        } else {
+          atomicAdd(P.eloc + 2 * (size_t)rparent, amp);
+        }
+      } else {
+        if (P.out_logp != nullptr) P.out_logp[row0 + row] = rlogp;
+        if (P.out_phase != nullptr) P.out_phase[row0 + row] = rphase;
+        if (P.mode == MODE_SAMPLE && P.cfg_out != nullptr) {
+          int8_t* c = P.cfg_out + (size_t)(row0 + row) * P.nsites;
+          for (int t = 0; t < P.Tsym; ++t) c[P.steps[t].site] = (int8_t)symS[t * TC_ROWS + row];
+        }
+      }
+    }
+  }  // tiles
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) { __syncwarp(); tc_dealloc(tmem_base, TC_TMEM_COLS); }
+}
+
+// ---- weight image for the tensor-core sweep --------------------------------------------------------------
+// [variant 3][pass NP][k-core kc][n-core 14][8 rows][8 bf16]:  B[n][k] of the pass, K-major core matrices.
+// variants: 0 both neighbours, 1 horizontal only, 2 vertical only.
+__global__ void pack_tc_kernel(const float* __restrict__ W, const float* __restrict__ Wg, const float* __restrict__ Wmerge,
+                               int nh, int nhp, int NP, __nv_bfloat16* __restrict__ out) {
+  const int kc = 2 * (nhp / 8);
+  const long long per_pass = (long long)kc * (TC_N / 8) * 64;
+  const long long total = 3LL * NP * per_pass;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    long long r = idx;
+    const int e = (int)(r % 8); r /= 8;
+    const int r8 = (int)(r % 8); r /= 8;
+    const int ni = (int)(r % (TC_N / 8)); r /= (TC_N / 8);
+    const int ki = (int)(r % kc); r /= kc;
+    const int p = (int)(r % NP); r /= NP;
+    const int variant = (int)r;
+    const int n = ni * 8 + r8, k = ki * 8 + e;
+    const int blk = n / TC_JP, j = p * TC_JP + (n % TC_JP);
+    const int slot = k / nhp, unit = k - slot * nhp;
+    float v = 0.f;
+    if (unit < nh && j < nh) {
+      const int i = slot * nh + unit;
+      if (blk == 6) {
+        v = Wmerge[(long long)i * nh + j];
+      } else {
+        const float* T = (blk < 3) ? W : Wg;
+        const float* w = T + ((long long)j * 2 * nh + i) * 4;
+        const int kind = blk % 3;
+        if (variant == 0) v = (kind == 0) ? (w[0] + w[2]) : (kind == 1 ? (w[1] - w[0]) : (w[3] - w[2]));
+        else if (variant == 1) v = (kind == 0) ? w[0] : (kind == 1 ? (w[1] - w[0]) : 0.f);
+        else v = (kind == 0) ? w[2] : (kind == 1 ? 0.f : (w[3] - w[2]));
+      }
+    }
+    out[idx] = __float2bfloat16_rn(v);
+  }
+}
+
+__global__ void pack_tc_bias_kernel(const float* __restrict__ b, const float* __restrict__ bg, int nh, int nhp, float* __restrict__ out) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * nhp; i += gridDim.x * blockDim.x) {
+    const int which = i / nhp, j = i - which * nhp;
+    out[i] = (j < nh) ? (which == 0 ? b[j] : bg[j]) : 0.f;
+  }
+}
+
+}  // namespace rnnwf

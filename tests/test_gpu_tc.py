@@ -1,0 +1,95 @@
+"""GPU parity of the tensor-core (tcgen05, BF16) regime of the tensorized 2D GRU sweep against the float64
+oracle.  Tolerance: 1e-3 relative on log-amplitudes and E_loc (the "BF16 mode" bound of BASELINE.json's north_star);
+samples must agree with the oracle wherever no draw falls within 1e-3 of a CDF threshold."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import local_energies as ole
+from oracle import costs
+from rnnwavefunctions_b200 import _lib
+from rnnwavefunctions_b200.engine import Engine
+from helpers import oracle_params, oracle_run, oracle_logpsi_fn
+
+RTOL = 1e-3
+
+
+def _mk(nx, ny, nh, seed=51, u1=True):
+    eng = Engine(_lib.CELL_TENSGRU2D, nx, ny, num_units=nh, complex_head=True, u1=u1, seed=seed, precision="bf16")
+    g = torch.Generator().manual_seed(seed + 1)
+    p = eng.params.cpu()
+    eng.set_weights(p + 0.15 * (torch.rand(p.shape, generator=g) - 0.5))
+    return eng
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nx,ny,nh,ns", [(4, 4, 24, 100), (6, 6, 100, 700), (3, 5, 13, 37), (10, 10, 100, 300)])
+def test_tc_sample_and_logpsi(cuda, nx, ny, nh, ns):
+    u1 = (nx * ny) % 2 == 0     # zero magnetisation needs an even number of sites
+    eng = _mk(nx, ny, nh, u1=u1)
+    assert "tcgen05" in eng.describe()
+    g = torch.Generator().manual_seed(ns)
+    u = torch.rand(ns, eng.nsteps, generator=g, dtype=torch.float32)
+    s, lp, ph = eng.sample(ns, uniforms=u)
+    P = oracle_params(eng)
+    with torch.no_grad():
+        ref = oracle_run(eng, P, uniforms=u, numsamples=ns)
+    ok = (ref["margin"].min(dim=1).values > 1e-3).numpy()
+    assert ok.mean() > 0.7
+    s_cpu = s.cpu().long().numpy()
+    assert (s_cpu[ok] == ref["samples"].numpy()[ok]).all()
+    if u1:
+        assert (s_cpu.reshape(ns, -1).sum(1) == eng.nsteps // 2).all()
+    scale = np.abs(ref["logp"].numpy()).max()
+    np.testing.assert_allclose(lp.cpu().numpy()[ok], ref["logp"].numpy()[ok], rtol=RTOL, atol=RTOL * scale * 0.1)
+    np.testing.assert_allclose(ph.cpu().numpy()[ok], ref["phase"].numpy()[ok], rtol=RTOL, atol=RTOL * 0.5 * scale)
+    lp2, ph2 = eng.logpsi(s)
+    np.testing.assert_allclose(lp2.cpu().numpy(), lp.cpu().numpy(), rtol=1e-12, atol=1e-12)
+    with torch.no_grad():
+        ref2 = oracle_run(eng, P, samples=s_cpu)
+    np.testing.assert_allclose(lp2.cpu().numpy(), ref2["logp"].numpy(), rtol=RTOL, atol=RTOL * scale * 0.1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("reuse", [False, True])
+@pytest.mark.parametrize("J2", [0.0, 1.0])
+def test_tc_local_energies(cuda, reuse, J2):
+    eng = _mk(6, 6, 48, seed=61)
+    ns = 200
+    saved = eng.new_saved(ns) if reuse else None
+    u = torch.rand(ns, eng.nsteps, generator=torch.Generator().manual_seed(3), dtype=torch.float32)
+    s, lp, ph = eng.sample(ns, uniforms=u, saved=saved)
+    e = eng.local_energies(_lib.HAM_HEIS2D, [J2], s, lp, ph, saved=saved).cpu().numpy()
+    ref, _ = ole.heis2d_local_energies(J2, s.cpu().numpy().astype(np.int64), oracle_logpsi_fn(eng, oracle_params(eng)))
+    np.testing.assert_allclose(e, ref, rtol=RTOL, atol=RTOL * np.abs(ref).max())
+
+
+@pytest.mark.gpu
+def test_tc_matches_fp32_regime_and_feeds_backward(cuda):
+    """Same weights in both regimes: log psi within 1e-3, and the backward (which consumes the saved states the
+    tensor-core sweep wrote) within 1e-2 of the oracle's autograd per tensor (the saved hidden states carry the
+    BF16 regime's ~1e-3 perturbation)."""
+    kw = dict(cell=_lib.CELL_TENSGRU2D, nx=4, ny=4, num_units=20, complex_head=True, u1=True, seed=71)
+    e32, e16 = Engine(precision="fp32", **kw), Engine(precision="bf16", **kw)
+    g = torch.Generator().manual_seed(72)
+    p = e32.params.cpu() + 0.15 * (torch.rand(e32.params.shape, generator=g) - 0.5)
+    e32.set_weights(p)
+    e16.set_weights(p)
+    ns = 257
+    u = torch.rand(ns, 16, generator=g, dtype=torch.float32)
+    s, lp32, ph32 = e32.sample(ns, uniforms=u)
+    saved = e16.new_saved(ns)
+    lp16, ph16 = e16.logpsi(s, saved=saved)
+    np.testing.assert_allclose(lp16.cpu().numpy(), lp32.cpu().numpy(), rtol=RTOL, atol=1e-3)
+    np.testing.assert_allclose(ph16.cpu().numpy(), ph32.cpu().numpy(), rtol=RTOL, atol=1e-2)
+    Er = torch.randn(ns, generator=g, dtype=torch.float64)
+    Ei = torch.randn(ns, generator=g, dtype=torch.float64)
+    P = oracle_params(e16, requires_grad=True)
+    ref = oracle_run(e16, P, samples=s.cpu().numpy())
+    costs.cost_complex(ref["logp"], ref["phase"], torch.complex(Er, Ei)).backward()
+    sl, sp = costs.seeds_complex(lp16.cpu(), torch.complex(Er, Ei))
+    grad = e16.backward(s, saved, sl, sp).cpu()
+    for n, v in e16.views(grad).items():
+        gr = P[n].grad
+        scale = float(gr.abs().max()) + 1e-30
+        assert float((v.double() - gr).abs().max()) / scale < 1e-2, n
