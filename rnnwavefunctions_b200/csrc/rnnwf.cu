@@ -535,7 +535,7 @@ int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
     const long long n = 3LL * h->tc_np * (ts.b_bytes / 2);
     RNNWF_COUNT_LAUNCH(); pack_tc_kernel<<<std::min(2048, cdiv(n, 256)), 256, 0, st>>>(
         params_dev + h->tensor("W")->offset, params_dev + h->tensor("Wg")->offset, params_dev + h->tensor("Wmerge")->offset,
-        h->nh, h->nhp, h->tc_np, reinterpret_cast<__nv_bfloat16*>(h->d_tcB));
+        h->nh, h->nhp, h->tc_np, reinterpret_cast<__half*>(h->d_tcB));
     RNNWF_COUNT_LAUNCH(); pack_tc_bias_kernel<<<1, 256, 0, st>>>(params_dev + h->tensor("b")->offset, params_dev + h->tensor("bg")->offset, h->nh, h->nhp, h->d_tcbias);
   }
   CUDA_TRY(cudaGetLastError());
@@ -850,7 +850,7 @@ int rnnwf_describe(rnnwf_handle h, char* buf, int cap) {
                 "cell=%d nh=%d (padded %d) steps=%d symbols=%d slots=%d classes=%d | pipe=%s, tile=128 rows x %d col-groups "
                 "(TJ=%d NTU=%d WC=%d passes=%d), k-chunk=%d, ring=%d steps, params=%lld",
                 h->cell, h->nh, h->nhp, h->Q, h->Tsym, h->nslots, h->ncls_max,
-                h->tc_enabled ? "tcgen05 BF16 (hi+lo activations, FP32 accumulate in TMEM; 7 column passes of 112)" : "FFMA fp32", h->Gblk, h->TJ, h->NTU, h->WC, h->ncb, KC,
+                h->tc_enabled ? "tcgen05 FP16 operands, FP32 accumulate in TMEM (column passes of 112, double-buffered)" : "FFMA fp32", h->Gblk, h->TJ, h->NTU, h->WC, h->ncb, KC,
                 h->ring_len, (long long)h->num_params);
   return RNNWF_OK;
 }
