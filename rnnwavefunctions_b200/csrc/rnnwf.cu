@@ -290,7 +290,7 @@ struct LaunchShape { int WR, Mp, Mr, threads, smem, grid; };
 
 int pick_shape(const rnnwf_model& m, long long rows, LaunchShape& s) {
   if (m.tc_enabled) {
-    const TcSmem ts(m.nhp, m.Tsym);
+    const TcSmem ts(m.nhp, m.Tsym, m.Q);
     const long long tiles = (rows + TC_ROWS - 1) / TC_ROWS;
     s.WR = 4; s.Mp = TC_ROWS; s.Mr = TC_ROWS; s.threads = TC_THREADS; s.smem = ts.total;
     s.grid = (int)std::max(1LL, std::min<long long>(tiles, m.num_sms));
@@ -445,7 +445,7 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
   CREATE_TRY(cudaFuncSetAttribute(sweep_kernel<4, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
   CREATE_TRY(cudaFuncSetAttribute(sweep_kernel<4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
   if (m->tc_enabled) {
-    const TcSmem ts(m->nhp, m->Tsym);
+    const TcSmem ts(m->nhp, m->Tsym, m->Q);
     if (ts.total > 227 * 1024) { rnnwf_destroy(m); return fail(RNNWF_ENOMEM, "tensor-core sweep does not fit in shared memory for this lattice / width"); }
     CREATE_TRY(cudaMalloc(&m->d_tcB, (size_t)3 * m->tc_np * ts.b_bytes));
     CREATE_TRY(cudaMalloc(&m->d_tcbias, (size_t)2 * m->nhp * 4));
@@ -531,7 +531,7 @@ int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
       params_dev + wd->offset, params_dev + bd->offset, wp ? params_dev + wp->offset : nullptr,
       bp ? params_dev + bp->offset : nullptr, h->nh, h->nhp, h->D, h->ND, h->d_head_w, h->d_head_b);
   if (h->tc_enabled) {
-    const TcSmem ts(h->nhp, h->Tsym);
+    const TcSmem ts(h->nhp, h->Tsym, h->Q);
     const long long n = 3LL * h->tc_np * (ts.b_bytes / 2);
     RNNWF_COUNT_LAUNCH(); pack_tc_kernel<<<std::min(2048, cdiv(n, 256)), 256, 0, st>>>(
         params_dev + h->tensor("W")->offset, params_dev + h->tensor("Wg")->offset, params_dev + h->tensor("Wmerge")->offset,

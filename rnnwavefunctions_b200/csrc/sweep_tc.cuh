@@ -37,9 +37,9 @@ constexpr int TC_TMEM_COLS = 256;
 constexpr uint32_t TC_SPIN_LIMIT = 1u << 26;
 
 struct TcSmem {
-  int off_A, off_B, off_headw, off_headb, off_bias, off_part, off_sym, off_bar, off_tmem, total;
+  int off_A, off_B, off_headw, off_headb, off_bias, off_part, off_meta, off_sym, off_bar, off_tmem, total;
   int a_bytes, b_bytes, kc;
-  __host__ __device__ TcSmem(int nhp, int Tsym) {
+  __host__ __device__ TcSmem(int nhp, int Tsym, int Q = 0) {
     kc = 2 * (nhp / 8);                       // 16-byte k-cores of the concatenated [h_h ; h_v] operand
     a_bytes = kc * (TC_ROWS / 8) * 128;
     b_bytes = kc * (TC_N / 8) * 128;
@@ -50,6 +50,7 @@ struct TcSmem {
     off_headb = o; o += 16;
     off_bias = o;  o += ((2 * (nhp + TC_JP) * 4) + 15) & ~15;
     off_part = o;  o += TC_ROWS * 4 * 16;      // partial head sums [128][TC_SUB] float4
+    off_meta = o;  o += ((Q > 0 ? Q : Tsym) * 8 + 15) & ~15;   // per step: nbr0, nbr1, site, pad (int16 x 4)
     off_bar = o;   o += 128;
     off_tmem = o;  o += 16;
     off_sym = o;   o += ((Tsym * TC_ROWS) + 15) & ~15;
@@ -137,7 +138,8 @@ __device__ __forceinline__ void tc_ld4(uint32_t taddr, uint32_t (&d)[4]) {
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
                : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]) : "r"(taddr) : "memory");
 }
-__device__ __forceinline__ void epi_barrier() { asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI_THREADS) : "memory"); }
+// the four warps that share a TMEM lane quarter (= the four threads of each of its 32 rows)
+__device__ __forceinline__ void quarter_barrier(int quarter) { asm volatile("bar.sync %0, 128;" ::"r"(1 + quarter) : "memory"); }
 // 1e-3 regime: exp2-based sigmoid / tanh (abs. error ~1e-6, far below the BF16 operand rounding)
 __device__ __forceinline__ float fast_sigmoid(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
 __device__ __forceinline__ float fast_tanh(float x) { return 2.0f * fast_sigmoid(2.0f * x) - 1.0f; }
@@ -145,13 +147,14 @@ __device__ __forceinline__ float fast_tanh(float x) { return 2.0f * fast_sigmoid
 __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepParams P) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  const TcSmem L(P.nhp, P.Tsym);
+  const TcSmem L(P.nhp, P.Tsym, P.Q);
   unsigned char* const Abuf = smem + L.off_A;          // [2][a_bytes]: operand of step q lives in buffer q & 1
   unsigned char* const Bst = smem + L.off_B;
   float* const headW = reinterpret_cast<float*>(smem + L.off_headw);
   float* const headB = reinterpret_cast<float*>(smem + L.off_headb);
   float* const biasS = reinterpret_cast<float*>(smem + L.off_bias);       // [2][nhp + 16]: b, bg
-  float4* const partS = reinterpret_cast<float4*>(smem + L.off_part);     // [128][TC_SUB] partial head sums
+  float4* const partS = reinterpret_cast<float4*>(smem + L.off_part);     // [2][128][TC_SUB] partial head sums
+  short4* const metaS = reinterpret_cast<short4*>(smem + L.off_meta);     // per step: (nbr0, nbr1, site, -)
   uint8_t* const symS = smem + L.off_sym;                                 // [Tsym][128]
   uint64_t* const bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
   uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(smem + L.off_tmem);
@@ -167,11 +170,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
   const int sub = (warp - 1) >> 2;                    // which 4 of the 16 units of a pass this thread handles
   const int row = (quarter << 5) + lane;              // tile row == TMEM lane
   const int nhp = P.nhp, nh = P.nh, ldb = nhp + TC_JP;
-  const int NP = P.tc_np, kc = L.kc, hc = L.kc / 2;   // k-cores of the whole operand / of one neighbour half
+  const int NP = P.tc_np, hc = L.kc / 2;   // k-cores of the whole operand / of one neighbour half
   const uint32_t A_LBO = (TC_ROWS / 8) * 128, B_LBO = (TC_N / 8) * 128, SBO = 128;
   const uint32_t idesc = tc_idesc(TC_ROWS, TC_N);
   const uint32_t roff = (uint32_t)(row >> 3) * 128 + (uint32_t)(row & 7) * 16;   // this row inside a k-core
-  float* const ring = P.ring + (size_t)blockIdx.x * P.ring_len * TC_ROWS * nhp;
+  // history ring of this CTA, stored as FP16 operand images [slot][k-core][row/8][row%8][8 halves] (L2-resident)
+  const uint32_t img_bytes = (uint32_t)hc * A_LBO;
+  unsigned char* const ring = reinterpret_cast<unsigned char*>(P.ring) + (size_t)blockIdx.x * P.ring_len * img_bytes;
 
   if (tid == 0) {
     mbar_init(bar_A, TC_EPI_THREADS);
@@ -187,6 +192,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
     const int which = i / ldb, j = i - which * ldb;
     biasS[i] = (j < nh) ? P.tc_bias[which * nhp + j] : 0.f;
   }
+  for (int i = tid; i < P.Q; i += TC_THREADS) {
+    const StepMeta* m = P.steps + i;
+    metaS[i] = make_short4(m->nbr[0], m->nbr[1], m->site, 0);
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -199,6 +208,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
   // consumed-completion counters (parity = count & 1)
   uint32_t nA = 0, nB[2] = {0, 0}, nMc[2] = {0, 0}, nF[2] = {0, 0};   // control thread
   uint32_t nMe[2] = {0, 0};                                             // epilogue threads
+  bool b_prefetched = false;
 
   const long long total_rows = (P.rows_dev != nullptr) ? (long long)(*P.rows_dev) : P.rows;
   const long long ntiles = (total_rows + TC_ROWS - 1) / TC_ROWS;
@@ -226,72 +236,75 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         const long long src = (P.mode == MODE_CHILD) ? (long long)ch.parent : row0 + row;
         const int8_t* c = P.cfg_in + src * P.nsites;
         for (int t = sub; t < P.Tsym; t += TC_SUB) {
-          int sy = c[P.steps[t].site] & 1;
+          int sy = c[metaS[t].z] & 1;
           if (P.mode == MODE_CHILD && (t == ch.ta || t == ch.tb)) sy ^= 1;
           symS[t * TC_ROWS + row] = (uint8_t)sy;
         }
       } else {
         for (int t = sub; t < P.Tsym; t += TC_SUB) symS[t * TC_ROWS + row] = 0;
       }
-      epi_barrier();
+      quarter_barrier(quarter);
       if (fin && P.mode == MODE_CHILD)
         for (int t = 0; t < ts0; ++t) rnup += symS[t * TC_ROWS + row];
     }
-    auto hist_ptr = [&](int qn) -> const float* {
-      if (P.par_hist != nullptr && qn < q0) return P.par_hist + ((size_t)qn * (size_t)P.par_rows + (size_t)rparent) * nhp;
-      return ring + ((size_t)(qn % P.ring_len) * TC_ROWS + row) * nhp;
-    };
-    // One neighbour half of an A operand: this row's hidden state of step qn (zeros if absent), FP16, core-matrix
-    // layout [k-core][row/8][row%8][8 halves]; the row's four threads take every 4th k-core.  Loads first, then convert.
+    // One neighbour half of an A operand: this row's hidden state of step qn (zeros if absent) in the core-matrix
+    // layout [k-core][row/8][row%8][8 halves]; the row's four threads take every 4th k-core.  Source: the FP16 ring
+    // image (straight 16-byte copies) or, before the tile's first step under prefix reuse, the parent's FP32 history.
     auto build_half = [&](unsigned char* A, int half, int qn) {
-      const float* src = (qn >= 0 && live) ? hist_ptr(qn) : nullptr;
+      const bool have = (qn >= 0) && live;
+      const bool from_parent = have && (P.par_hist != nullptr) && (qn < q0);
+      const float* psrc = from_parent ? P.par_hist + ((size_t)qn * (size_t)P.par_rows + (size_t)rparent) * nhp : nullptr;
+      const unsigned char* isrc = (have && !from_parent) ? ring + (size_t)(qn % P.ring_len) * img_bytes + roff : nullptr;
       for (int cbase = 0; cbase < hc; cbase += 4 * TC_SUB) {
-        float4 v[4][2];
+        uint4 o[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const int c = cbase + sub + i * TC_SUB;
-          v[i][0] = v[i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (src != nullptr && c < hc) {
-            v[i][0] = __ldcg(reinterpret_cast<const float4*>(src + c * 8));
-            v[i][1] = __ldcg(reinterpret_cast<const float4*>(src + c * 8 + 4));
+          o[i] = make_uint4(0u, 0u, 0u, 0u);
+          if (c < hc) {
+            if (isrc != nullptr) {
+              o[i] = __ldcg(reinterpret_cast<const uint4*>(isrc + (uint32_t)c * A_LBO));
+            } else if (psrc != nullptr) {
+              const float4 v0 = __ldg(reinterpret_cast<const float4*>(psrc + c * 8));
+              const float4 v1 = __ldg(reinterpret_cast<const float4*>(psrc + c * 8 + 4));
+              o[i].x = pack_f16x2(v0.x, v0.y); o[i].y = pack_f16x2(v0.z, v0.w);
+              o[i].z = pack_f16x2(v1.x, v1.y); o[i].w = pack_f16x2(v1.z, v1.w);
+            }
           }
         }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const int c = cbase + sub + i * TC_SUB;
-          if (c < hc) {
-            uint4 o;
-            o.x = pack_f16x2(v[i][0].x, v[i][0].y); o.y = pack_f16x2(v[i][0].z, v[i][0].w);
-            o.z = pack_f16x2(v[i][1].x, v[i][1].y); o.w = pack_f16x2(v[i][1].z, v[i][1].w);
-            *reinterpret_cast<uint4*>(A + (uint32_t)(half * hc + c) * A_LBO + roff) = o;
-          }
+          if (c < hc) *reinterpret_cast<uint4*>(A + (uint32_t)(half * hc + c) * A_LBO + roff) = o[i];
         }
       }
     };
 
     // operand of the tile's first step: both halves from the history (parent's saved history under prefix reuse)
     if (is_epi) {
-      const StepMeta* s0 = P.steps + q0;
-      if (s0->nbr[0] >= 0 || s0->nbr[1] >= 0) {
-        build_half(Abuf + (q0 & 1) * L.a_bytes, 0, s0->nbr[0]);
-        build_half(Abuf + (q0 & 1) * L.a_bytes, 1, s0->nbr[1]);
+      const short4 s0 = metaS[q0];
+      if (s0.x >= 0 || s0.y >= 0) {
+        build_half(Abuf + (q0 & 1) * L.a_bytes, 0, s0.x);
+        build_half(Abuf + (q0 & 1) * L.a_bytes, 1, s0.y);
         fence_proxy_async_smem();
         mbar_arrive(bar_A);
       }
     }
 
     for (int q = q0; q < P.Q; ++q) {
-      const StepMeta* sm = P.steps + q;
-      const int nb0 = sm->nbr[0], nb1 = sm->nbr[1];
+      const short4 sm = metaS[q];
+      const int nb0 = sm.x, nb1 = sm.y;      // history index == symbol index of the two neighbours (2D cells)
       const int variant = (nb0 >= 0 && nb1 >= 0) ? 0 : (nb0 >= 0 ? 1 : (nb1 >= 0 ? 2 : 3));
-      const int t = sm->sym;
+      const int t = q;
 
       if (is_ctrl && variant != 3) {
         // ================= control thread: weight stream + MMA issue =================
         const unsigned char* Bsrc = P.tc_B + (size_t)variant * NP * L.b_bytes;
-        for (int p = 0; p < 2 && p < NP; ++p) {
-          mbar_expect_tx(bar_B + p, L.b_bytes);
-          bulk_g2s(Bst + p * L.b_bytes, Bsrc + (size_t)p * L.b_bytes, L.b_bytes, bar_B + p);
+        if (!b_prefetched) {
+          for (int p = 0; p < 2 && p < NP; ++p) {
+            mbar_expect_tx(bar_B + p, L.b_bytes);
+            bulk_g2s(Bst + p * L.b_bytes, Bsrc + (size_t)p * L.b_bytes, L.b_bytes, bar_B + p);
+          }
         }
         mbar_wait(bar_A, nA & 1); ++nA;
         const uint64_t ad0 = adesc0 + (uint64_t)(((q & 1) * L.a_bytes) >> 4);
@@ -317,6 +330,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           }
         }
         { const int s1 = (NP - 1) & 1; mbar_wait(bar_mma + s1, nMc[s1] & 1); ++nMc[s1]; }
+        // both weight stages are free again: start streaming the first two passes of the next step
+        b_prefetched = false;
+        if (q + 1 < P.Q) {
+          const short4 sn = metaS[q + 1];
+          const int vn = (sn.x >= 0 && sn.y >= 0) ? 0 : (sn.x >= 0 ? 1 : 2);
+          const unsigned char* Bn = P.tc_B + (size_t)vn * NP * L.b_bytes;
+          for (int p = 0; p < 2 && p < NP; ++p) {
+            mbar_expect_tx(bar_B + p, L.b_bytes);
+            bulk_g2s(Bst + p * L.b_bytes, Bn + (size_t)p * L.b_bytes, L.b_bytes, bar_B + p);
+          }
+          b_prefetched = true;
+        }
       }
 
       if (is_epi) {
@@ -327,17 +352,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         unsigned char* Anext = nullptr;
         int carry_half = 0;
         if (q + 1 < P.Q) {
-          const StepMeta* sn = P.steps + q + 1;
-          if (sn->nbr[0] >= 0 || sn->nbr[1] >= 0) {
+          const short4 sn = metaS[q + 1];
+          if (sn.x >= 0 || sn.y >= 0) {
             Anext = Abuf + ((q + 1) & 1) * L.a_bytes;
-            carry_half = (sn->nbr[0] == q) ? 0 : 1;
-            build_half(Anext, 1 - carry_half, (carry_half == 0) ? sn->nbr[1] : sn->nbr[0]);
+            carry_half = (sn.x == q) ? 0 : 1;
+            build_half(Anext, 1 - carry_half, (carry_half == 0) ? sn.y : sn.x);
           }
         }
-        const float cl = (nb0 >= 0) ? (float)symS[sm->nsym[0] * TC_ROWS + row] : 0.f;
-        const float cu = (nb1 >= 0) ? (float)symS[sm->nsym[1] * TC_ROWS + row] : 0.f;
+        const float cl = (nb0 >= 0) ? (float)symS[nb0 * TC_ROWS + row] : 0.f;
+        const float cu = (nb1 >= 0) ? (float)symS[nb1 * TC_ROWS + row] : 0.f;
         float lg[4] = {0.f, 0.f, 0.f, 0.f};
-        float* ring_row = ring + ((size_t)(q % P.ring_len) * TC_ROWS + row) * nhp;
+        unsigned char* ring_img = ring + (size_t)(q % P.ring_len) * img_bytes + roff;
+        float4* const part = partS;
         for (int p = 0; p < NP; ++p) {
           const int s = p & 1;
           uint32_t d[TC_NB][4];
@@ -377,16 +403,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
             }
           }
           if (j0 < nhp) {
-            if (Anext != nullptr) {   // 4 halves = half a k-core row of the next operand's carry half
-              uint2 o;
-              o.x = pack_f16x2(hnew[0], hnew[1]); o.y = pack_f16x2(hnew[2], hnew[3]);
-              *reinterpret_cast<uint2*>(Anext + (uint32_t)(carry_half * hc + (j0 >> 3)) * A_LBO + roff + (uint32_t)(j0 & 7) * 2) = o;
-            }
+            // 4 halves = half a k-core row: into the next operand's carry half and into the ring image
+            uint2 o;
+            o.x = pack_f16x2(hnew[0], hnew[1]); o.y = pack_f16x2(hnew[2], hnew[3]);
+            const uint32_t coff = (uint32_t)(j0 >> 3) * A_LBO + (uint32_t)(j0 & 7) * 2;
+            if (Anext != nullptr) *reinterpret_cast<uint2*>(Anext + (uint32_t)(carry_half * hc) * A_LBO + coff + roff) = o;
             if (live) {
-              const float4 v = make_float4(hnew[0], hnew[1], hnew[2], hnew[3]);
-              *reinterpret_cast<float4*>(ring_row + j0) = v;
+              *reinterpret_cast<uint2*>(ring_img + coff) = o;
               if (P.sv_hist != nullptr && P.mode != MODE_CHILD)
-                *reinterpret_cast<float4*>(P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + j0) = v;
+                *reinterpret_cast<float4*>(P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + j0) =
+                    make_float4(hnew[0], hnew[1], hnew[2], hnew[3]);
             }
           }
         }
@@ -394,15 +420,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           fence_proxy_async_smem();
           mbar_arrive(bar_A);
         }
-        partS[row * TC_SUB + sub] = make_float4(lg[0], lg[1], lg[2], lg[3]);
-        epi_barrier();   // partial head sums and this step's ring rows are visible to the row's other threads
+        part[row * TC_SUB + sub] = make_float4(lg[0], lg[1], lg[2], lg[3]);
+        quarter_barrier(quarter);   // partial head sums and this step's ring rows are visible to the row's other threads
 
         // ---- heads for this row (softmax, U(1) mask, draw / teacher forcing, log psi)
         if (fin) {
           float l4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
           for (int k = 0; k < TC_SUB; ++k) {
-            const float4 v = partS[row * TC_SUB + k];
+            const float4 v = part[row * TC_SUB + k];
             l4[0] += v.x; l4[1] += v.y; l4[2] += v.z; l4[3] += v.w;
           }
           float p0 = l4[0] + headB[0], p1 = l4[1] + headB[1];
@@ -438,7 +464,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           if (P.sv_cum != nullptr && P.mode != MODE_CHILD)
             P.sv_cum[(size_t)t * (size_t)P.sv_rows + (size_t)(row0 + row)] = make_double2(rlogp, rphase);
         }
-        epi_barrier();   // the drawn symbol (sampling) is visible; partS may be reused
+        quarter_barrier(quarter);   // the drawn symbol (sampling) is visible to the row's other threads; partS reusable
       }
     }  // steps
 
@@ -465,11 +491,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         if (P.out_phase != nullptr) P.out_phase[row0 + row] = rphase;
         if (P.mode == MODE_SAMPLE && P.cfg_out != nullptr) {
           int8_t* c = P.cfg_out + (size_t)(row0 + row) * P.nsites;
-          for (int t = 0; t < P.Tsym; ++t) c[P.steps[t].site] = (int8_t)symS[t * TC_ROWS + row];
+          for (int t = 0; t < P.Tsym; ++t) c[metaS[t].z] = (int8_t)symS[t * TC_ROWS + row];
         }
       }
     }
-    if (is_epi) epi_barrier();   // symS is rewritten by the next tile's set-up
+    if (is_epi) quarter_barrier(quarter);   // symS is rewritten by the next tile's set-up
   }  // tiles
 
   tc_fence_before();
