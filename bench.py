@@ -245,9 +245,10 @@ def make_oracle_params(w, g):
 def cpu_baseline(w, target_s=15.0):
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    n0 = 2
+    n0 = 8
+    nconf, dt, _ = oracle_step(w, n0)          # also warms the BLAS threads up
     nconf, dt, _ = oracle_step(w, n0)
-    ns = int(max(n0, min(4096, n0 * target_s / max(dt, 1e-3))))
+    ns = int(max(n0, min(8192, n0 * target_s / max(dt, 1e-3))))
     nconf, dt, br = oracle_step(w, ns)
     return dict(value=nconf / dt, unit="eloc_configs/s", cores=cores, kind="port",
                 sample=f"oracle (torch float64, {cores} threads) on {ns} samples = {nconf} configurations of the same workload: "
@@ -264,6 +265,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
     ap.add_argument("--numsamples", type=int, default=None)
+    ap.add_argument("--precision", default="auto", choices=["auto", "fp32", "tc"],
+                    help="sweep regime: fp32 = FFMA (1e-5 parity), tc = tcgen05 FP16-operand tensor-core sweep (1e-3 bound); "
+                         "auto = tc where it exists (tensorized 2D GRU), fp32 otherwise")
     ap.add_argument("--no-prefix-reuse", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -315,7 +319,10 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     ek = dict(w["eng"])
     ek["cell"] = getattr(_lib, "CELL_" + ek["cell"])
-    eng = Engine(seed=111, **ek)
+    precision = args.precision
+    if precision == "auto":
+        precision = "tc" if w["eng"]["cell"] == "TENSGRU2D" else "fp32"
+    eng = Engine(seed=111, precision=precision, **ek)
     ham = getattr(_lib, "HAM_" + w["ham"])
     ns = w["ns"]
     V = vmc.VMC(eng, ham, w["hp"], ns, lr=5e-4, seed=111, prefix_reuse=not args.no_prefix_reuse)
@@ -407,15 +414,31 @@ def main():
     except Exception:
         pass
     bf16_peak = peaks.get("bf16_tflops_sustained", 1400.0)
-    achieved = exec_flops / (eloc_ms * 1e-3) / 1e12
-    roofline = {"bound": "fp32-ffma", "kernel": "sweep_kernel (MODE_CHILD)", "achieved": achieved, "peak": best, "unit": "TFLOP/s",
-                "frac": achieved / best if best > 0 else None, "traffic": None,
-                "peak_source": "measured live: rnnwf_ffma_probe (16 FMA chains/thread, 592x512 threads), best of 5",
-                "executed_flops_per_launch": exec_flops, "algorithmic_flops_per_launch": alg_flops,
-                "algorithmic_tflops": alg_flops / (eloc_ms * 1e-3) / 1e12,
-                "frac_of_bf16_tensor_peak": achieved / bf16_peak,
-                "bf16_peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1400",
-                "launch_ms": eloc_ms, "note": "launch_ms brackets rnnwf_local_energies (enumeration kernels + sweep; the sweep is >99% of it)"}
+    if precision == "tc":
+        # the tensor-core sweep executes, per row and site, the dense [2*nhp] x [7*16*passes] contraction
+        nhp = (w["eng"]["num_units"] + 7) // 8 * 8
+        npass = (w["eng"]["num_units"] + 15) // 16
+        exec_flops = exec_sites * (2 * (2 * nhp) * (112 * npass) + 2 * w["eng"]["num_units"] * 4)
+        achieved = exec_flops / (eloc_ms * 1e-3) / 1e12
+        roofline = {"bound": "tensor", "kernel": "sweep_tc_kernel (MODE_CHILD)", "achieved": achieved, "peak": bf16_peak, "unit": "TFLOP/s",
+                    "frac": achieved / bf16_peak, "traffic": None,
+                    "peak_source": ("MEASURED_PEAKS.json bf16_tflops_sustained (16-bit tensor peak, kernel timed inside a long step)"
+                                    if peaks else "fallback 1400 (B200_PROFILING.md)"),
+                    "executed_flops_per_launch": exec_flops, "algorithmic_flops_per_launch": alg_flops,
+                    "algorithmic_tflops": alg_flops / (eloc_ms * 1e-3) / 1e12, "ffma_peak_tflops_measured": best,
+                    "launch_ms": eloc_ms,
+                    "note": "executed = MMA flops actually issued (linearised class trick: 784 accumulator columns per row-site, "
+                            "prefix reuse counted); launch_ms brackets rnnwf_local_energies (enumeration kernels + sweep; the sweep is >99%)"}
+    else:
+        achieved = exec_flops / (eloc_ms * 1e-3) / 1e12
+        roofline = {"bound": "fp32-ffma", "kernel": "sweep_kernel (MODE_CHILD)", "achieved": achieved, "peak": best, "unit": "TFLOP/s",
+                    "frac": achieved / best if best > 0 else None, "traffic": None,
+                    "peak_source": "measured live: rnnwf_ffma_probe (16 FMA chains/thread, 592x512 threads), best of 5",
+                    "executed_flops_per_launch": exec_flops, "algorithmic_flops_per_launch": alg_flops,
+                    "algorithmic_tflops": alg_flops / (eloc_ms * 1e-3) / 1e12,
+                    "frac_of_bf16_tensor_peak": achieved / bf16_peak,
+                    "bf16_peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1400",
+                    "launch_ms": eloc_ms, "note": "launch_ms brackets rnnwf_local_energies (enumeration kernels + sweep; the sweep is >99% of it)"}
 
     # ---- end to end through the reference-facing API with host buffers
     e2e = None
@@ -460,7 +483,8 @@ def main():
     if rank == 0:
         line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "f32", "data": "synthetic", "config": config, "samples_per_s": samples_per_s,
+                "dtype": ("f16 operands / f32 accumulate (tcgen05); heads, log psi, E_loc in f32/f64" if precision == "tc" else "f32"),
+                "precision_mode": precision, "data": "synthetic", "config": config, "samples_per_s": samples_per_s,
                 "phase_ms_per_step": {k: v / args.steps for k, v in phase_ms.items()},
                 "eloc_configs_per_step_per_gpu": nconf_local / args.steps, "gpu_launches": int(launches),
                 "clocks": clk, "roofline": roofline, "e2e": e2e, "engine": eng.describe(),

@@ -54,8 +54,8 @@ typedef struct {
   int32_t num_layers;    /* GRU1D only (MultiRNNCell depth); 1 otherwise */
   int32_t u1;            /* 1: U(1) projection (J1J2/ComplexRNNwavefunction.py:85-93; 2DHeisenberg/MDComplexRNN.py:69-76) */
   int32_t magnetization; /* 2*Sz target of the projection */
-  int32_t reserved[8];   /* reserved[0] = precision: 0 FP32 FFMA sweep (1e-5 parity), 1 BF16 tcgen05 tensor-core sweep
-                          * (BF16 weights, hi+lo split activations, FP32 accumulate; 1e-3 parity; tensorized 2D GRU) */
+  int32_t reserved[8];   /* reserved[0] = precision: 0 FP32 FFMA sweep (1e-5 parity), 1 tcgen05 tensor-core sweep
+                          * (FP16 operands, FP32 accumulate in TMEM; 1e-3 parity bound; tensorized 2D GRU cell) */
 } rnnwf_config;
 
 const char* rnnwf_last_error(void);

@@ -15,7 +15,7 @@ RTOL = 1e-3
 
 
 def _mk(nx, ny, nh, seed=51, u1=True):
-    eng = Engine(_lib.CELL_TENSGRU2D, nx, ny, num_units=nh, complex_head=True, u1=u1, seed=seed, precision="bf16")
+    eng = Engine(_lib.CELL_TENSGRU2D, nx, ny, num_units=nh, complex_head=True, u1=u1, seed=seed, precision="tc")
     g = torch.Generator().manual_seed(seed + 1)
     p = eng.params.cpu()
     eng.set_weights(p + 0.15 * (torch.rand(p.shape, generator=g) - 0.5))
@@ -70,7 +70,7 @@ def test_tc_matches_fp32_regime_and_feeds_backward(cuda):
     tensor-core sweep wrote) within 1e-2 of the oracle's autograd per tensor (the saved hidden states carry the
     BF16 regime's ~1e-3 perturbation)."""
     kw = dict(cell=_lib.CELL_TENSGRU2D, nx=4, ny=4, num_units=20, complex_head=True, u1=True, seed=71)
-    e32, e16 = Engine(precision="fp32", **kw), Engine(precision="bf16", **kw)
+    e32, e16 = Engine(precision="fp32", **kw), Engine(precision="tc", **kw)
     g = torch.Generator().manual_seed(72)
     p = e32.params.cpu() + 0.15 * (torch.rand(e32.params.shape, generator=g) - 0.5)
     e32.set_weights(p)
