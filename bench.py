@@ -309,6 +309,9 @@ def main():
         return
 
     import torch.distributed as dist
+    if local_rank == 0:
+        import __graft_entry__ as _g
+        _g.build()                      # no-op when librnnwf.so is newer than its sources
     from rnnwavefunctions_b200 import _lib
     from rnnwavefunctions_b200.engine import Engine
     from rnnwavefunctions_b200 import vmc

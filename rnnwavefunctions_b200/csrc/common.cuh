@@ -100,6 +100,7 @@ struct SweepParams {
   const unsigned char* tc_B;   // [3 variants][tc_np passes][weight image]
   const float* tc_bias;        // [2][nhp]: b, bg
   int tc_np;
+  unsigned long long* tc_prof;  // optional per-CTA cycle counters (debug)
   // ---- scratch
   float* ring;              // [gridDim.x][ring_len][Mp][nhp]
 };

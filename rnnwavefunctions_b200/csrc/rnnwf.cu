@@ -21,6 +21,7 @@ struct rnnwf_model : rnnwf::rnnwf_model_impl {};
 namespace {
 
 thread_local std::string g_err;
+unsigned long long* g_tc_prof = nullptr;   // debug: per-CTA cycle counters of the tensor-core sweep
 
 int fail(int code, const std::string& msg) { g_err = msg; return code; }
 
@@ -323,7 +324,7 @@ void fill_model_params(const rnnwf_model& m, const LaunchShape& s, SweepParams& 
   P.ring_len = m.ring_len; P.WR = s.WR; P.WC = m.WC; P.Mp = s.Mp; P.Mr = s.Mr; P.ncls_max = m.ncls_max;
   P.steps = m.d_steps; P.variants = m.d_variants; P.Wpack = m.d_wpack; P.Xtab = m.d_xtab; P.bias = m.d_bias;
   P.head_w = m.d_head_w; P.head_b = m.d_head_b;
-  P.tc_B = m.d_tcB; P.tc_bias = m.d_tcbias; P.tc_np = m.tc_np;
+  P.tc_B = m.d_tcB; P.tc_bias = m.d_tcbias; P.tc_np = m.tc_np; P.tc_prof = g_tc_prof;
 }
 
 template <int TJ, int NTU>
@@ -820,6 +821,9 @@ int rnnwf_backward(rnnwf_handle h, int64_t rows, const int8_t* samples_dev, cons
 }
 
 long long rnnwf_launch_count(void) { return rnnwf::launch_counter(); }
+
+// debug hook (not declared in the public header): device buffer of gridDim.x * 16 uint64 cycle counters
+void rnnwf_debug_set_tc_prof(unsigned long long* dev) { g_tc_prof = dev; }
 
 // FP32 FFMA peak probe (roofline denominator of the FFMA regime): every thread runs 16 independent
 // FMA chains; flops = blocks * threads * iters * 16 * 2.

@@ -78,6 +78,7 @@ __device__ __forceinline__ uint32_t mbar_try_wait(uint64_t* bar, uint32_t parity
       : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
   return ok;
 }
+__device__ __forceinline__ long long tc_clock() { long long c; asm volatile("mov.u64 %0, %%clock64;" : "=l"(c)); return c; }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   for (uint32_t spin = 0; !mbar_try_wait(bar, parity); ++spin)
     if (spin > TC_SPIN_LIMIT) { asm volatile("trap;"); }
@@ -85,6 +86,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+// one lane of a converged warp
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
 }
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
@@ -209,6 +216,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
   uint32_t nA = 0, nB[2] = {0, 0}, nMc[2] = {0, 0}, nF[2] = {0, 0};   // control thread
   uint32_t nMe[2] = {0, 0};                                             // epilogue threads
   bool b_prefetched = false;
+  // optional cycle accounting (debug builds of the bench only): [0] bar_A [1] bar_B [2] bar_free [3] mma issue [4] bar_mma(ctrl)
+  // [5] total ctrl; [8] epi bar_mma wait [9] epi pass compute [10] epi build_half [11] epi finalize+barriers [12] epi total
+  long long prof[16];
+  for (int i = 0; i < 16; ++i) prof[i] = 0;
+  const bool do_prof = (P.tc_prof != nullptr) && (tid == 0 || tid == 32);
+#define TC_T0() long long t0__ = do_prof ? tc_clock() : 0
+#define TC_ACC(k) do { if (do_prof) { const long long t1__ = tc_clock(); prof[k] += t1__ - t0__; t0__ = t1__; } } while (0)
+  const long long kstart = do_prof ? tc_clock() : 0;
 
   const long long total_rows = (P.rows_dev != nullptr) ? (long long)(*P.rows_dev) : P.rows;
   const long long ntiles = (total_rows + TC_ROWS - 1) / TC_ROWS;
@@ -297,51 +312,67 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
       const int variant = (nb0 >= 0 && nb1 >= 0) ? 0 : (nb0 >= 0 ? 1 : (nb1 >= 0 ? 2 : 3));
       const int t = q;
 
-      if (is_ctrl && variant != 3) {
-        // ================= control thread: weight stream + MMA issue =================
+      if (warp == 0 && variant != 3) {
+        // ================= control warp: weight stream + MMA issue =================
+        // The whole warp walks this path convergently (so descriptors and addresses stay in uniform registers);
+        // only the instructions that must be issued once are predicated on one elected lane.
         const unsigned char* Bsrc = P.tc_B + (size_t)variant * NP * L.b_bytes;
-        if (!b_prefetched) {
+        const bool leader = elect_one();
+        if (!b_prefetched && leader) {
           for (int p = 0; p < 2 && p < NP; ++p) {
             mbar_expect_tx(bar_B + p, L.b_bytes);
             bulk_g2s(Bst + p * L.b_bytes, Bsrc + (size_t)p * L.b_bytes, L.b_bytes, bar_B + p);
           }
         }
+        TC_T0();
         mbar_wait(bar_A, nA & 1); ++nA;
+        TC_ACC(0);
         const uint64_t ad0 = adesc0 + (uint64_t)(((q & 1) * L.a_bytes) >> 4);
         for (int p = 0; p < NP; ++p) {
           const int s = p & 1;
           mbar_wait(bar_B + s, nB[s] & 1); ++nB[s];
+          TC_ACC(1);
           mbar_wait(bar_free + s, (nF[s] & 1) ^ 1); ++nF[s];
+          TC_ACC(2);
           tc_fence_after();
           const uint32_t tmem_d = tmem_base + (uint32_t)(s * TC_N);
           // descriptors differ between k-steps only in the 14-bit start-address field: one add per MMA
           const uint64_t bd0 = bdesc0 + (uint64_t)((s * L.b_bytes) >> 4);
+          if (leader) {
 #pragma unroll 1
-          for (int ks = 0; ks < hc; ++ks)
-            tc_mma_f16(tmem_d, ad0 + (uint64_t)ks * a_kstep, bd0 + (uint64_t)ks * b_kstep, idesc, ks > 0 ? 1u : 0u);
-          tc_commit(bar_mma + s);
+            for (int ks = 0; ks < hc; ++ks)
+              tc_mma_f16(tmem_d, ad0 + (uint64_t)ks * a_kstep, bd0 + (uint64_t)ks * b_kstep, idesc, ks > 0 ? 1u : 0u);
+            tc_commit(bar_mma + s);
+          }
+          __syncwarp();
+          TC_ACC(3);
           if (p >= 1) {   // pass p-1 has finished reading its weight stage -> refill it with pass p+1
             const int s1 = (p - 1) & 1;
             mbar_wait(bar_mma + s1, nMc[s1] & 1); ++nMc[s1];
-            if (p + 1 < NP) {
+            if (p + 1 < NP && leader) {
               mbar_expect_tx(bar_B + s1, L.b_bytes);
               bulk_g2s(Bst + s1 * L.b_bytes, Bsrc + (size_t)(p + 1) * L.b_bytes, L.b_bytes, bar_B + s1);
             }
+            TC_ACC(4);
           }
         }
         { const int s1 = (NP - 1) & 1; mbar_wait(bar_mma + s1, nMc[s1] & 1); ++nMc[s1]; }
+        TC_ACC(4);
         // both weight stages are free again: start streaming the first two passes of the next step
         b_prefetched = false;
         if (q + 1 < P.Q) {
           const short4 sn = metaS[q + 1];
           const int vn = (sn.x >= 0 && sn.y >= 0) ? 0 : (sn.x >= 0 ? 1 : 2);
           const unsigned char* Bn = P.tc_B + (size_t)vn * NP * L.b_bytes;
-          for (int p = 0; p < 2 && p < NP; ++p) {
-            mbar_expect_tx(bar_B + p, L.b_bytes);
-            bulk_g2s(Bst + p * L.b_bytes, Bn + (size_t)p * L.b_bytes, L.b_bytes, bar_B + p);
+          if (leader) {
+            for (int p = 0; p < 2 && p < NP; ++p) {
+              mbar_expect_tx(bar_B + p, L.b_bytes);
+              bulk_g2s(Bst + p * L.b_bytes, Bn + (size_t)p * L.b_bytes, L.b_bytes, bar_B + p);
+            }
           }
           b_prefetched = true;
         }
+        __syncwarp();
       }
 
       if (is_epi) {
@@ -349,6 +380,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         // The operand of step q+1 is produced here: the half that is this step's own output is written slice by
         // slice as the gates are evaluated; the other half (an older neighbour, or nothing) is fetched first, while
         // the tensor core is still busy with this step.
+        TC_T0();
         unsigned char* Anext = nullptr;
         int carry_half = 0;
         if (q + 1 < P.Q) {
@@ -359,6 +391,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
             build_half(Anext, 1 - carry_half, (carry_half == 0) ? sn.y : sn.x);
           }
         }
+        TC_ACC(10);
         const float cl = (nb0 >= 0) ? (float)symS[nb0 * TC_ROWS + row] : 0.f;
         const float cu = (nb1 >= 0) ? (float)symS[nb1 * TC_ROWS + row] : 0.f;
         float lg[4] = {0.f, 0.f, 0.f, 0.f};
@@ -369,6 +402,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           uint32_t d[TC_NB][4];
           if (variant != 3) {
             mbar_wait(bar_mma + s, nMe[s] & 1); ++nMe[s];
+            TC_ACC(8);
             __syncwarp();
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(s * TC_N + sub * 4);
@@ -416,6 +450,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
             }
           }
         }
+        TC_ACC(9);
         if (Anext != nullptr) {       // next step's operand complete: release the tensor core before the heads
           fence_proxy_async_smem();
           mbar_arrive(bar_A);
@@ -465,6 +500,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
             P.sv_cum[(size_t)t * (size_t)P.sv_rows + (size_t)(row0 + row)] = make_double2(rlogp, rphase);
         }
         quarter_barrier(quarter);   // the drawn symbol (sampling) is visible to the row's other threads; partS reusable
+        TC_ACC(11);
       }
     }  // steps
 
@@ -498,6 +534,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
     if (is_epi) quarter_barrier(quarter);   // symS is rewritten by the next tile's set-up
   }  // tiles
 
+  if (do_prof) {
+    prof[tid == 0 ? 5 : 12] = tc_clock() - kstart;
+    for (int i = (tid == 0 ? 0 : 8); i < (tid == 0 ? 8 : 16); ++i) P.tc_prof[(size_t)blockIdx.x * 16 + i] = (unsigned long long)prof[i];
+  }
   tc_fence_before();
   __syncthreads();
   if (warp == 0) { __syncwarp(); tc_dealloc(tmem_base, TC_TMEM_COLS); }
