@@ -12,6 +12,7 @@
 #include "sweep_tc.cuh"
 #include "pack.cuh"
 #include "eloc.cuh"
+#include "gemm_tc.cuh"
 #include "backward.cuh"
 
 using namespace rnnwf;
@@ -821,6 +822,15 @@ int rnnwf_backward(rnnwf_handle h, int64_t rows, const int8_t* samples_dev, cons
 }
 
 long long rnnwf_launch_count(void) { return rnnwf::launch_counter(); }
+
+// debug hook (not declared in the public header): run the tcgen05 TF32 GEMM on raw FP32 device matrices
+int rnnwf_debug_gemm_tc(const float* A, long long lda, int a_kc, const float* B, long long ldb, int b_kc, float* C, long long ldc,
+                        long long M, int N, long long K, int mode, void* stream) {
+  cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * GT_TILE_BYTES);
+  if (!gemm_tc_launch(static_cast<cudaStream_t>(stream), A, lda, a_kc, B, ldb, b_kc, C, ldc, M, N, K, mode)) return fail(RNNWF_EINVAL, "gemm_tc: unaligned operands");
+  CUDA_TRY(cudaGetLastError());
+  return RNNWF_OK;
+}
 
 // debug hook (not declared in the public header): device buffer of gridDim.x * 16 uint64 cycle counters
 void rnnwf_debug_set_tc_prof(unsigned long long* dev) { g_tc_prof = dev; }
