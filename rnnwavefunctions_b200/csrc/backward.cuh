@@ -132,15 +132,28 @@ __global__ void __launch_bounds__(256) gemm_tn_atomic_kernel(const float* __rest
     }
 }
 
-// out[n] += sum_m X[m, n]
-__global__ void colsum_atomic_kernel(const float* __restrict__ X, int ldx, long long M, int N, float* __restrict__ out) {
-  const int n = blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= N) return;
-  const long long chunk = (M + gridDim.y - 1) / gridDim.y;
-  const long long lo = blockIdx.y * chunk, hi = (lo + chunk < M) ? lo + chunk : M;
-  float s = 0.f;
-  for (long long m = lo; m < hi; ++m) s += X[m * ldx + n];
-  if (s != 0.f) atomicAdd(out + n, s);
+// out[n] += sum_m X[m, n]   (block = 32 columns x 8 row lanes, 4 loads in flight per thread)
+__global__ void __launch_bounds__(256) colsum_atomic_kernel(const float* __restrict__ X, int ldx, long long M, int N, float* __restrict__ out) {
+  __shared__ float red[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int n = blockIdx.x * 32 + tx;
+  const long long stride = 8LL * gridDim.y;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  if (n < N) {
+    long long m = (long long)blockIdx.y * 8 + ty;
+    for (; m + 3 * stride < M; m += 4 * stride) {
+      s0 += X[m * ldx + n]; s1 += X[(m + stride) * ldx + n]; s2 += X[(m + 2 * stride) * ldx + n]; s3 += X[(m + 3 * stride) * ldx + n];
+    }
+    for (; m < M; m += stride) s0 += X[m * ldx + n];
+  }
+  red[ty][tx] = (s0 + s1) + (s2 + s3);
+  __syncthreads();
+  if (ty == 0 && n < N) {
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += red[k][tx];
+    if (s != 0.f) atomicAdd(out + n, s);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -335,9 +348,11 @@ __global__ void build_onehot_kernel(const BwdStep S, int nslots, float* __restri
 // ------------------------------------------------------------------------------------------------
 // orchestration
 // ------------------------------------------------------------------------------------------------
-inline cudaError_t backward_init() { return cudaSuccess; }
+inline cudaError_t backward_init() {
+  return cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * GT_TILE_BYTES);
+}
 
-struct BwdLayout { long long off_dh, off_dp, off_Z, off_dZ, off_hc, off_dhc, off_dlog, off_X, total; long long dpw; int Kz; };
+struct BwdLayout { long long off_dh, off_dp, off_Z, off_dZ, off_hc, off_dhc, off_dlog, off_X, total; long long dpw; int Kz; bool batched; };
 
 inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   auto al = [](long long x) { return (x + 255) & ~255LL; };
@@ -345,14 +360,19 @@ inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   const long long nh = m.nh;
   L.Kz = (m.cell == CELL_TENS2D || m.cell == CELL_TENSGRU2D) ? 8 * m.nh : (m.cell == CELL_GRU4 ? 24 + 4 * m.nh : 0);
   L.dpw = (m.cell == CELL_GRU1D) ? 4 * nh : 3 * nh;
+  // Tensorized cells: the operands of the weight-gradient GEMMs (d pre-activations, h (x) x, hc, d logits) are kept for
+  // ALL steps, so that dW, dWg, dWmerge, the head kernels and every bias come out of one long-K GEMM / reduction each
+  // after the reverse sweep instead of ~10 small launches per lattice site.
+  L.batched = (m.cell == CELL_TENS2D || m.cell == CELL_TENSGRU2D);
+  const long long nb = L.batched ? m.Q : 1;
   long long o = 0;
   L.off_dh = o;   o += al((long long)m.Q * R * m.nhp * 4);
-  L.off_dp = o;   o += al(R * L.dpw * 4);
-  L.off_Z = o;    o += al(R * (long long)L.Kz * 4);
+  L.off_dp = o;   o += al(nb * R * L.dpw * 4);
+  L.off_Z = o;    o += al(nb * R * (long long)L.Kz * 4);
   L.off_dZ = o;   o += al(R * (long long)L.Kz * 4);
-  L.off_hc = o;   o += al(R * 2 * nh * 4);
+  L.off_hc = o;   o += al(nb * R * 2 * nh * 4);
   L.off_dhc = o;  o += al(R * 2 * nh * 4);
-  L.off_dlog = o; o += al(R * 8 * 4);
+  L.off_dlog = o; o += al(nb * R * 8 * 4);
   L.off_X = o;    o += al(R * 8 * 4);
   L.total = o;
   return L;
@@ -362,6 +382,12 @@ inline long long backward_workspace_bytes(const rnnwf_model_impl& m, long long R
 
 struct Gemm {
   cudaStream_t st;
+  bool tc = false;   // reduced-precision regime: long-K weight-gradient GEMMs on the tensor cores (TF32, gemm_tc.cuh)
+  // C[K1,N] += A[M,K1]^T B[M,N] with a long reduction M
+  void tn_long(const float* A, int lda, const float* B, int ldb, float* C, int ldc, long long M, int K1, int N) const {
+    if (tc && N >= 16 && K1 >= 16 && gemm_tc_launch(st, A, lda, 0, B, ldb, 0, C, ldc, K1, N, M, 2)) return;
+    tn(A, lda, B, ldb, C, ldc, M, K1, N);
+  }
   void nt(const float* A, int lda, const float* B, int ldb, float* C, int ldc, long long M, int N, int K, int beta) const {
     if (M <= 0 || N <= 0 || K <= 0) return;
     dim3 g((N + GB - 1) / GB, (unsigned)((M + GB - 1) / GB));
@@ -386,8 +412,8 @@ struct Gemm {
   }
   void colsum(const float* X, int ldx, long long M, int N, float* out) const {
     if (M <= 0 || N <= 0) return;
-    dim3 g((N + 127) / 128, (unsigned)std::max<long long>(1, std::min<long long>(64, M / 256)));
-    RNNWF_COUNT_LAUNCH(); colsum_atomic_kernel<<<g, 128, 0, st>>>(X, ldx, M, N, out);
+    dim3 g((N + 31) / 32, (unsigned)std::max<long long>(1, std::min<long long>(1024, M / 64)));
+    RNNWF_COUNT_LAUNCH(); colsum_atomic_kernel<<<g, 256, 0, st>>>(X, ldx, M, N, out);
   }
 };
 
@@ -403,15 +429,16 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
   char* ws = static_cast<char*>(workspace);
   float* dh = reinterpret_cast<float*>(ws + L.off_dh);
   float* dp = reinterpret_cast<float*>(ws + L.off_dp);
-  float* Z = reinterpret_cast<float*>(ws + L.off_Z);
+  float* Z_base = reinterpret_cast<float*>(ws + L.off_Z);
   float* dZ = reinterpret_cast<float*>(ws + L.off_dZ);
-  float* hc = reinterpret_cast<float*>(ws + L.off_hc);
+  float* hc_base = reinterpret_cast<float*>(ws + L.off_hc);
   float* dhc = reinterpret_cast<float*>(ws + L.off_dhc);
-  float* dlog = reinterpret_cast<float*>(ws + L.off_dlog);
+  float* dlog_base = reinterpret_cast<float*>(ws + L.off_dlog);
   float* X = reinterpret_cast<float*>(ws + L.off_X);
   const float* params = m.d_params;
   const int nh = m.nh, nhp = m.nhp;
   Gemm G{st};
+  G.tc = (m.precision == 1);
 
   cudaError_t e = cudaMemsetAsync(dh, 0, (size_t)m.Q * R * nhp * 4, st);
   if (e == cudaSuccess) e = cudaMemsetAsync(grad, 0, (size_t)m.num_params * 4, st);
@@ -437,19 +464,26 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
     }
     S.sym_site = sm.site;
 
+    const bool batched = L.batched;
+    float* dlog = batched ? dlog_base + (long long)q * R * m.ND : dlog_base;
     if (sm.head) {
       const int wpb = 8;
       RNNWF_COUNT_LAUNCH(); head_bwd_kernel<<<(unsigned)((R + wpb - 1) / wpb), wpb * 32, 0, st>>>(S, m.d_site_of_t, m.d_head_w, m.d_head_b, seed_logp, seed_phase, dlog);
-      G.tn(hrow(q), nhp, dlog, m.ND, Gd("dense.W"), m.D, R, nh, m.D);
-      G.colsum(dlog, m.ND, R, m.D, Gd("dense.b"));
-      if (m.complex_head) {
-        G.tn(hrow(q), nhp, dlog + m.D, m.ND, Gd("dense_phase.W"), 2, R, nh, 2);
-        G.colsum(dlog + m.D, m.ND, R, 2, Gd("dense_phase.b"));
+      if (!batched) {
+        G.tn(hrow(q), nhp, dlog, m.ND, Gd("dense.W"), m.D, R, nh, m.D);
+        G.colsum(dlog, m.ND, R, m.D, Gd("dense.b"));
+        if (m.complex_head) {
+          G.tn(hrow(q), nhp, dlog + m.D, m.ND, Gd("dense_phase.W"), 2, R, nh, 2);
+          G.colsum(dlog + m.D, m.ND, R, 2, Gd("dense_phase.b"));
+        }
       }
     }
-    float* dp0 = dp;
-    float* dp1 = dp + ((m.cell == CELL_GRU1D) ? 2 * R * nh : R * nh);
-    float* dp2 = dp1 + R * nh;
+    // batched layout: three arrays [Q][R*nh] (ds, dg, dm); otherwise one per-step block
+    float* dp0 = batched ? dp + (long long)q * R * nh : dp;
+    float* dp1 = batched ? dp + ((long long)m.Q + q) * R * nh : dp + ((m.cell == CELL_GRU1D) ? 2 * R * nh : R * nh);
+    float* dp2 = batched ? dp + (2LL * m.Q + q) * R * nh : dp1 + R * nh;
+    float* Z = batched ? Z_base + (long long)q * R * L.Kz : Z_base;
+    float* hc = batched ? hc_base + (long long)q * R * 2 * nh : hc_base;
     RNNWF_COUNT_LAUNCH(); cell_bwd_kernel<<<nblk(R * nh), tpb, 0, st>>>(S, dp0, dp1, dp2);
 
     switch (m.cell) {
@@ -457,21 +491,12 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
       case CELL_TENSGRU2D: {
         const bool gru = m.cell == CELL_TENSGRU2D;
         const int K8 = 8 * nh;
-        if (sm.nbr[0] < 0 && sm.nbr[1] < 0) {  // first site: no inputs, only the biases receive gradient
-          G.colsum(dp0, nh, R, nh, Gd("b"));
-          if (gru) G.colsum(dp1, nh, R, nh, Gd("bg"));
-          break;
-        }
+        if (sm.nbr[0] < 0 && sm.nbr[1] < 0) break;  // first site: no inputs (its bias gradient is in the batched sums)
         RNNWF_COUNT_LAUNCH(); build_tens_kernel<<<nblk(R * 2 * nh), tpb, 0, st>>>(S, Z, hc);
         G.nn(dp0, nh, P("W"), K8, dZ, K8, R, K8, nh, 0);                 // dT  = ds W2
-        G.tn(dp0, nh, Z, K8, Gd("W"), K8, R, nh, K8);                     // dW2 += ds^T T
-        G.colsum(dp0, nh, R, nh, Gd("b"));
         if (gru) {
           G.nn(dp1, nh, P("Wg"), K8, dZ, K8, R, K8, nh, 1);              // dT += dg Wg2
-          G.tn(dp1, nh, Z, K8, Gd("Wg"), K8, R, nh, K8);
-          G.colsum(dp1, nh, R, nh, Gd("bg"));
           G.nt(dp2, nh, P("Wmerge"), nh, dhc, 2 * nh, R, 2 * nh, nh, 0);  // dhc = dm Wmerge^T
-          G.tn(hc, 2 * nh, dp2, nh, Gd("Wmerge"), nh, R, 2 * nh, nh);     // dWmerge += hc^T dm
         }
         RNNWF_COUNT_LAUNCH(); scatter_tens_kernel<<<nblk(R * 2 * nh), tpb, 0, st>>>(S, dZ, gru ? dhc : nullptr);
         break;
@@ -535,6 +560,30 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
         }
         break;
       }
+    }
+  }
+  if (L.batched) {
+    // The step-0 site has no inputs; steps 1..Q-1 are contiguous in the batched operand arrays.
+    const bool gru = m.cell == CELL_TENSGRU2D;
+    const int K8 = 8 * nh;
+    const long long RQ = (long long)m.Q * R, R1 = (long long)(m.Q - 1) * R;
+    float* dsA = dp;
+    float* dgA = dp + (long long)m.Q * R * nh;
+    float* dmA = dp + 2LL * m.Q * R * nh;
+    if (m.Q > 1) {
+      G.tn_long(dsA + R * nh, nh, Z_base + R * (long long)K8, K8, Gd("W"), K8, R1, nh, K8);          // dW2 += ds^T T
+      if (gru) {
+        G.tn_long(dgA + R * nh, nh, Z_base + R * (long long)K8, K8, Gd("Wg"), K8, R1, nh, K8);
+        G.tn_long(hc_base + R * 2LL * nh, 2 * nh, dmA + R * nh, nh, Gd("Wmerge"), nh, R1, 2 * nh, nh);  // dWmerge += hc^T dm
+      }
+    }
+    G.colsum(dsA, nh, RQ, nh, Gd("b"));
+    if (gru) G.colsum(dgA, nh, RQ, nh, Gd("bg"));
+    G.tn(hist, nhp, dlog_base, m.ND, Gd("dense.W"), m.D, RQ, nh, m.D);
+    G.colsum(dlog_base, m.ND, RQ, m.D, Gd("dense.b"));
+    if (m.complex_head) {
+      G.tn(hist, nhp, dlog_base + m.D, m.ND, Gd("dense_phase.W"), 2, RQ, nh, 2);
+      G.colsum(dlog_base + m.D, m.ND, RQ, 2, Gd("dense_phase.b"));
     }
   }
   e = cudaGetLastError();
