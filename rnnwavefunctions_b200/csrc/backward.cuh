@@ -271,6 +271,75 @@ __global__ void cell_bwd_kernel(const BwdStep S, float* __restrict__ dp0, float*
   }
 }
 
+// Tensorized cells, d(pre-activations) + the operand of the linearised input-gradient GEMM:
+//   P[row] = [ds, cl*ds, cu*ds, dg, cl*dg, cu*dg, dm]   (cl, cu = left / up neighbour spin, 0 if absent)
+// so that  d[h_h ; h_v] = P * Wstack  with  Wstack = [Wa; Wb; Wc; Wga; Wgb; Wgc; Wmerge^T]  (see sweep_tc.cuh).
+__global__ void cell_bwd_tens_kernel(const BwdStep S, int gru, float* __restrict__ dp0, float* __restrict__ dp1,
+                                     float* __restrict__ dp2, float* __restrict__ Pm) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= S.R * S.nh) return;
+  const long long row = idx / S.nh;
+  const int j = (int)(idx - row * S.nh);
+  const int pw = (gru ? 7 : 3) * S.nh;
+  const float dhp = S.dh[((long long)S.q * S.R + row) * S.nhp + j];
+  const int8_t* crow = S.cfg + row * S.nsites;
+  const float cl = (S.nsym_site[0] >= 0) ? (float)(crow[S.nsym_site[0]] & 1) : 0.f;
+  const float cu = (S.nsym_site[1] >= 0) ? (float)(crow[S.nsym_site[1]] & 1) : 0.f;
+  float* Pr = Pm + row * pw;
+  if (gru) {
+    const float4 g = S.gates[((long long)S.q * S.R + row) * S.Gp + j];  // (u, ht, m, -)
+    const float ds = dhp * g.x * (1.f - g.y * g.y);
+    const float dg = dhp * (g.y - g.z) * g.x * (1.f - g.x);
+    const float dm = dhp * (1.f - g.x);
+    dp0[idx] = ds; dp1[idx] = dg; dp2[idx] = dm;
+    Pr[j] = ds; Pr[S.nh + j] = cl * ds; Pr[2 * S.nh + j] = cu * ds;
+    Pr[3 * S.nh + j] = dg; Pr[4 * S.nh + j] = cl * dg; Pr[5 * S.nh + j] = cu * dg;
+    Pr[6 * S.nh + j] = dm;
+  } else {
+    const float hv = S.hist[((long long)S.q * S.R + row) * S.nhp + j];
+    const float ds = dhp * (1.f - hv * hv);
+    dp0[idx] = ds;
+    Pr[j] = ds; Pr[S.nh + j] = cl * ds; Pr[2 * S.nh + j] = cu * ds;
+  }
+}
+
+// WstackT[variant][i (2nh)][c (nblk*nh)], K-contiguous for the gemm "nt" form.  variant: 0 both neighbours,
+// 1 horizontal only, 2 vertical only (same definitions as pack_tc_kernel).
+__global__ void pack_wstack_kernel(const float* __restrict__ W, const float* __restrict__ Wg, const float* __restrict__ Wmerge,
+                                   int nh, int gru, float* __restrict__ out) {
+  const int nblk = gru ? 7 : 3, pw = nblk * nh;
+  const long long total = 3LL * 2 * nh * pw;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(idx % pw);
+    const int i = (int)((idx / pw) % (2 * nh));
+    const int variant = (int)(idx / ((long long)pw * 2 * nh));
+    const int blk = c / nh, j = c - blk * nh;
+    float v;
+    if (blk == 6) {
+      v = Wmerge[(long long)i * nh + j];
+    } else {
+      const float* w = ((blk < 3) ? W : Wg) + ((long long)j * 2 * nh + i) * 4;
+      const int kind = blk % 3;
+      if (variant == 0) v = (kind == 0) ? (w[0] + w[2]) : (kind == 1 ? (w[1] - w[0]) : (w[3] - w[2]));
+      else if (variant == 1) v = (kind == 0) ? w[0] : (kind == 1 ? (w[1] - w[0]) : 0.f);
+      else v = (kind == 0) ? w[2] : (kind == 1 ? 0.f : (w[3] - w[2]));
+    }
+    out[idx] = v;
+  }
+}
+
+// dh[neighbour s][row][k] += dhc[row][s*nh + k]
+__global__ void scatter_hc_kernel(const BwdStep S, const float* __restrict__ dhc) {
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int nh2 = 2 * S.nh;
+  if (idx >= S.R * nh2) return;
+  const long long row = idx / nh2;
+  const int i = (int)(idx - row * nh2);
+  const int slot = i / S.nh, k = i - slot * S.nh;
+  if (S.nbr[slot] < 0) return;
+  S.dh[((long long)S.nbr[slot] * S.R + row) * S.nhp + k] += dhc[idx];
+}
+
 // tensorized cells: T[row][i*4+k] = hc_i * xc_k and hc[row][i]
 __global__ void build_tens_kernel(const BwdStep S, float* __restrict__ T, float* __restrict__ hc) {
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -349,10 +418,10 @@ __global__ void build_onehot_kernel(const BwdStep S, int nslots, float* __restri
 // orchestration
 // ------------------------------------------------------------------------------------------------
 inline cudaError_t backward_init() {
-  return cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * GT_TILE_BYTES);
+  return cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GT_STAGES * 2 * GT_TILE_BYTES);
 }
 
-struct BwdLayout { long long off_dh, off_dp, off_Z, off_dZ, off_hc, off_dhc, off_dlog, off_X, total; long long dpw; int Kz; bool batched; };
+struct BwdLayout { long long off_dh, off_dp, off_Z, off_dZ, off_hc, off_dhc, off_dlog, off_X, off_wstack, total; long long dpw; int Kz; bool batched; };
 
 inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   auto al = [](long long x) { return (x + 255) & ~255LL; };
@@ -369,11 +438,12 @@ inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   L.off_dh = o;   o += al((long long)m.Q * R * m.nhp * 4);
   L.off_dp = o;   o += al(nb * R * L.dpw * 4);
   L.off_Z = o;    o += al(nb * R * (long long)L.Kz * 4);
-  L.off_dZ = o;   o += al(R * (long long)L.Kz * 4);
+  L.off_dZ = o;   o += al(R * (long long)L.Kz * 4);   // tensorized cells: the per-step linearised operand P [R][7nh] lives here
   L.off_hc = o;   o += al(nb * R * 2 * nh * 4);
   L.off_dhc = o;  o += al(R * 2 * nh * 4);
   L.off_dlog = o; o += al(nb * R * 8 * 4);
   L.off_X = o;    o += al(R * 8 * 4);
+  L.off_wstack = o; o += al(L.batched ? 3LL * 2 * nh * 7 * nh * 4 : 0);
   L.total = o;
   return L;
 }
@@ -439,6 +509,12 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
   const int nh = m.nh, nhp = m.nhp;
   Gemm G{st};
   G.tc = (m.precision == 1);
+  float* wstack = reinterpret_cast<float*>(ws + L.off_wstack);
+  if (L.batched) {
+    const bool gru0 = m.cell == CELL_TENSGRU2D;
+    RNNWF_COUNT_LAUNCH(); pack_wstack_kernel<<<512, 256, 0, st>>>(params + m.tensor("W")->offset, gru0 ? params + m.tensor("Wg")->offset : nullptr,
+                                                     gru0 ? params + m.tensor("Wmerge")->offset : nullptr, nh, gru0 ? 1 : 0, wstack);
+  }
 
   cudaError_t e = cudaMemsetAsync(dh, 0, (size_t)m.Q * R * nhp * 4, st);
   if (e == cudaSuccess) e = cudaMemsetAsync(grad, 0, (size_t)m.num_params * 4, st);
@@ -484,7 +560,8 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
     float* dp2 = batched ? dp + (2LL * m.Q + q) * R * nh : dp1 + R * nh;
     float* Z = batched ? Z_base + (long long)q * R * L.Kz : Z_base;
     float* hc = batched ? hc_base + (long long)q * R * 2 * nh : hc_base;
-    RNNWF_COUNT_LAUNCH(); cell_bwd_kernel<<<nblk(R * nh), tpb, 0, st>>>(S, dp0, dp1, dp2);
+    if (batched) { RNNWF_COUNT_LAUNCH(); cell_bwd_tens_kernel<<<nblk(R * nh), tpb, 0, st>>>(S, m.cell == CELL_TENSGRU2D ? 1 : 0, dp0, dp1, dp2, dZ); }
+    else { RNNWF_COUNT_LAUNCH(); cell_bwd_kernel<<<nblk(R * nh), tpb, 0, st>>>(S, dp0, dp1, dp2); }
 
     switch (m.cell) {
       case CELL_TENS2D:
@@ -492,13 +569,17 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
         const bool gru = m.cell == CELL_TENSGRU2D;
         const int K8 = 8 * nh;
         if (sm.nbr[0] < 0 && sm.nbr[1] < 0) break;  // first site: no inputs (its bias gradient is in the batched sums)
-        RNNWF_COUNT_LAUNCH(); build_tens_kernel<<<nblk(R * 2 * nh), tpb, 0, st>>>(S, Z, hc);
-        G.nn(dp0, nh, P("W"), K8, dZ, K8, R, K8, nh, 0);                 // dT  = ds W2
-        if (gru) {
-          G.nn(dp1, nh, P("Wg"), K8, dZ, K8, R, K8, nh, 1);              // dT += dg Wg2
-          G.nt(dp2, nh, P("Wmerge"), nh, dhc, 2 * nh, R, 2 * nh, nh, 0);  // dhc = dm Wmerge^T
+        RNNWF_COUNT_LAUNCH(); build_tens_kernel<<<nblk(R * 2 * nh), tpb, 0, st>>>(S, Z, hc);   // operands of the batched dW GEMMs
+        {
+          // d[h_h ; h_v] = P * Wstack(variant): one GEMM instead of dT = ds W2 (+ dg Wg2) over the expanded h (x) x
+          const int pw = (gru ? 7 : 3) * nh;
+          const int variant = (sm.nbr[0] >= 0 && sm.nbr[1] >= 0) ? 0 : (sm.nbr[0] >= 0 ? 1 : 2);
+          const float* WsT = wstack + (long long)variant * 2 * nh * pw;
+          if (!(G.tc && gemm_tc_launch(st, dZ, pw, 1, WsT, pw, 1, dhc, 2 * nh, R, 2 * nh, pw, 0)))
+            G.nt(dZ, pw, WsT, pw, dhc, 2 * nh, R, 2 * nh, pw, 0);
+          RNNWF_COUNT_LAUNCH(); scatter_hc_kernel<<<nblk(R * 2 * nh), tpb, 0, st>>>(S, dhc);
         }
-        RNNWF_COUNT_LAUNCH(); scatter_tens_kernel<<<nblk(R * 2 * nh), tpb, 0, st>>>(S, dZ, gru ? dhc : nullptr);
+        (void)K8;
         break;
       }
       case CELL_GRU4: {

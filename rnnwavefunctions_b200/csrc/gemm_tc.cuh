@@ -8,8 +8,8 @@
 //      dX = dY W^T   (A = dY K-contig, B = W   K-contig)          gemm "nt"
 //      dX = dY W     (A = dY K-contig, B = W   N-contig)          gemm "nn"
 //      dW += X^T dY  (A = X  M-contig, B = dY  N-contig, split over the batch, atomics)   gemm "tn"
-// One elected thread issues tcgen05.mma (kind::tf32, M=128, N=128, K=8); two shared-memory stages overlap the next
-// tile's loads with the current MMAs; the epilogue reads TMEM with tcgen05.ld (one thread per accumulator row).
+// One elected thread issues tcgen05.mma (kind::tf32, M=128, N=128, K=8); a 3-stage cp.async pipeline keeps two tiles
+// of loads in flight behind the MMAs; the epilogue reads TMEM with tcgen05.ld (one thread per accumulator row).
 #pragma once
 #include "common.cuh"
 #include "sweep_tc.cuh"
@@ -36,36 +36,30 @@ __device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uin
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 
-// Copy a [128 (mn) x 32 (k)] FP32 tile into shared memory as core matrices.
-//   kc = 1 (contiguous along k):  K-major,  offset = (k/4)*2048 + (mn/8)*128 + (mn%8)*16 + (k%4)*4
-//   kc = 0 (contiguous along mn): same K-major image, transposed while staging (MN-major TF32 operands need the
-//                                 special 128B/32B-base swizzle, so the transposition is done by the copy instead)
+// Stage a [128 (mn) x 32 (k)] FP32 tile into shared memory as K-major core matrices:
+//   offset = (k/4)*2048 + (mn/8)*128 + (mn%8)*16 + (k%4)*4
+//   kc = 1 (contiguous along k):  each 16-byte core row is one cp.async (zero-filled past the edges) -- asynchronous;
+//   kc = 0 (contiguous along mn): coalesced scalar loads along mn, transposed in registers (MN-major TF32 operands
+//                                 would need the special 128B/32B-base swizzle, so the copy does the transposition).
+__device__ __forceinline__ void cp_async16_zfill(void* smem_dst, const void* gmem_src, int src_bytes) {
+  unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d), "l"(gmem_src), "r"(src_bytes));
+}
 __device__ __forceinline__ void gt_load_tile(unsigned char* smem, const float* __restrict__ G, long long ld, int kc,
                                              long long mn0, long long mn_lim, long long k0, long long k_lim, int tid) {
+  const long long mn = mn0 + tid;
+  const uint32_t base = (uint32_t)(tid >> 3) * 128 + (uint32_t)(tid & 7) * 16;
+  const bool ok = mn < mn_lim;
   if (kc) {
-    const long long mn = mn0 + tid;
-    const float* src = G + mn * ld + k0;
-    const uint32_t base = (uint32_t)(tid >> 3) * 128 + (uint32_t)(tid & 7) * 16;
+    const float* src = G + (ok ? mn : 0) * ld + k0;
 #pragma unroll
     for (int c = 0; c < GT_BK / 4; ++c) {
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      const long long k = k0 + 4 * c;
-      if (mn < mn_lim) {
-        if (k + 3 < k_lim) v = __ldg(reinterpret_cast<const float4*>(src + 4 * c));
-        else {
-          if (k < k_lim) v.x = src[4 * c];
-          if (k + 1 < k_lim) v.y = src[4 * c + 1];
-          if (k + 2 < k_lim) v.z = src[4 * c + 2];
-        }
-      }
-      *reinterpret_cast<float4*>(smem + (uint32_t)c * 2048 + base) = v;
+      const long long rem = k_lim - (k0 + 4 * c);
+      const int bytes = (!ok || rem <= 0) ? 0 : (rem >= 4 ? 16 : (int)rem * 4);
+      cp_async16_zfill(smem + (uint32_t)c * 2048 + base, bytes ? (const void*)(src + 4 * c) : (const void*)G, bytes);
     }
   } else {
-    // contiguous along mn: thread = one mn, coalesced scalar loads along mn, transposed into K-major 16-byte rows
-    const long long mn = mn0 + tid;
     const float* src = G + k0 * ld + mn;
-    const uint32_t base = (uint32_t)(tid >> 3) * 128 + (uint32_t)(tid & 7) * 16;
-    const bool ok = mn < mn_lim;
 #pragma unroll
     for (int c = 0; c < GT_BK / 4; ++c) {
       const long long k = k0 + 4 * c;
@@ -79,19 +73,20 @@ __device__ __forceinline__ void gt_load_tile(unsigned char* smem, const float* _
   }
 }
 
+constexpr int GT_STAGES = 3;
+
 __global__ void __launch_bounds__(128, 2) gemm_tc_kernel(const GemmTcArgs g) {
-  extern __shared__ __align__(128) unsigned char gt_smem[];
-  unsigned char (*As)[GT_TILE_BYTES] = reinterpret_cast<unsigned char (*)[GT_TILE_BYTES]>(gt_smem);
-  unsigned char (*Bs)[GT_TILE_BYTES] = reinterpret_cast<unsigned char (*)[GT_TILE_BYTES]>(gt_smem + 2 * GT_TILE_BYTES);
-  __shared__ __align__(8) uint64_t bars[2];
+  extern __shared__ __align__(128) unsigned char gt_smem[];   // [stage][A tile | B tile]
+  __shared__ __align__(8) uint64_t bars[GT_STAGES];
   __shared__ uint32_t tmem_slot;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const long long m0 = (long long)blockIdx.y * GT_BM;
   const long long n0 = (long long)blockIdx.x * GT_BN;
   const long long kbeg = (long long)blockIdx.z * g.kchunk;
   const long long kend = (kbeg + g.kchunk < g.K) ? kbeg + g.kchunk : g.K;
+  const int niter = (kend > kbeg) ? (int)((kend - kbeg + GT_BK - 1) / GT_BK) : 0;
 
-  if (tid == 0) { mbar_init(bars + 0, 1); mbar_init(bars + 1, 1); fence_mbar_init(); }
+  if (tid == 0) { for (int i = 0; i < GT_STAGES; ++i) mbar_init(bars + i, 1); fence_mbar_init(); }
   if (warp == 0) tc_alloc(&tmem_slot, GT_BN);
   tc_fence_before();
   __syncthreads();
@@ -100,22 +95,35 @@ __global__ void __launch_bounds__(128, 2) gemm_tc_kernel(const GemmTcArgs g) {
 
   // instruction descriptor: D=F32, A=B=TF32 (format 2), both K-major
   const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(GT_BN >> 3) << 17) | ((uint32_t)(GT_BM >> 4) << 24);
-  // per-MMA (K = 8) descriptor: two k-groups of 4 (LBO = 2048), 8-row groups SBO = 128, advance 4096 bytes per MMA
-  const uint32_t a_lbo = 2048u, b_lbo = 2048u;
 
-  uint32_t nwait[2] = {0, 0};
-  int it = 0;
-  for (long long k0 = kbeg; k0 < kend; k0 += GT_BK, ++it) {
-    const int s = it & 1;
-    if (it >= 2) { mbar_wait(bars + s, nwait[s] & 1); ++nwait[s]; }   // MMAs that read this stage are done
-    gt_load_tile(As[s], g.A, g.lda, g.a_kc, m0, g.M, k0, kend, tid);
-    gt_load_tile(Bs[s], g.B, g.ldb, g.b_kc, n0, (long long)g.N, k0, kend, tid);
+  auto stage_A = [&](int s) { return gt_smem + (size_t)s * 2 * GT_TILE_BYTES; };
+  auto stage_B = [&](int s) { return gt_smem + (size_t)s * 2 * GT_TILE_BYTES + GT_TILE_BYTES; };
+  auto issue_loads = [&](int it) {       // tile `it` -> stage it % GT_STAGES ; always commits one cp.async group
+    if (it < niter) {
+      const int s = it % GT_STAGES;
+      const long long k0 = kbeg + (long long)it * GT_BK;
+      gt_load_tile(stage_A(s), g.A, g.lda, g.a_kc, m0, g.M, k0, kend, tid);
+      gt_load_tile(stage_B(s), g.B, g.ldb, g.b_kc, n0, (long long)g.N, k0, kend, tid);
+    }
+    asm volatile("cp.async.commit_group;\n" ::);
+  };
+
+  uint32_t nwait[GT_STAGES];
+#pragma unroll
+  for (int i = 0; i < GT_STAGES; ++i) nwait[i] = 0;
+#pragma unroll
+  for (int it = 0; it < GT_STAGES - 1; ++it) issue_loads(it);
+
+  for (int it = 0; it < niter; ++it) {
+    const int s = it % GT_STAGES;
+    asm volatile("cp.async.wait_group %0;\n" ::"n"(GT_STAGES - 2) : "memory");   // this thread's copies of tile `it` landed
     fence_proxy_async_smem();
     __syncthreads();
     if (warp == 0) {
       tc_fence_after();
       if (elect_one()) {
-        const uint64_t ad = tc_desc(smem_u32(As[s]), a_lbo, 128), bd = tc_desc(smem_u32(Bs[s]), b_lbo, 128);
+        // per-MMA (K = 8) descriptor: two k-groups of 4 (LBO = 2048), 8-row groups SBO = 128, advance 4096 bytes per MMA
+        const uint64_t ad = tc_desc(smem_u32(stage_A(s)), 2048u, 128u), bd = tc_desc(smem_u32(stage_B(s)), 2048u, 128u);
 #pragma unroll
         for (int ks = 0; ks < GT_BK / 8; ++ks)
           tc_mma_tf32(tmem_d, ad + (uint64_t)(ks * 4096 >> 4), bd + (uint64_t)(ks * 4096 >> 4), idesc, (it > 0 || ks > 0) ? 1u : 0u);
@@ -123,20 +131,21 @@ __global__ void __launch_bounds__(128, 2) gemm_tc_kernel(const GemmTcArgs g) {
       }
       __syncwarp();
     }
+    // refill the stage that tile it-1 used (its MMAs were committed one iteration ago) with tile it + STAGES - 1
+    if (it >= 1) { const int sp = (it - 1) % GT_STAGES; mbar_wait(bars + sp, nwait[sp] & 1); ++nwait[sp]; }
+    issue_loads(it + GT_STAGES - 1);
   }
-  // drain: wait for the last commit of each stage that was used
-  for (int s = 0; s < 2; ++s) {
-    const int uses = (it + 1 - s) / 2;   // number of commits on stage s
-    while ((int)nwait[s] < uses) { mbar_wait(bars + s, nwait[s] & 1); ++nwait[s]; }
-  }
+  if (niter > 0) { const int sl = (niter - 1) % GT_STAGES; mbar_wait(bars + sl, nwait[sl] & 1); ++nwait[sl]; }
+  asm volatile("cp.async.wait_group 0;\n" ::: "memory");
   __syncwarp();
   tc_fence_after();
 
   // epilogue: thread = accumulator row (TMEM lane)
   const long long m = m0 + warp * 32 + lane;
-  if (it > 0) {
+  if (niter > 0) {
 #pragma unroll 1
     for (int c0 = 0; c0 < GT_BN; c0 += 16) {
+      if (n0 + c0 >= g.N) break;
       uint32_t d[16];
       tc_ld16(tmem_d + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, d);
       tc_wait_ld();
@@ -179,7 +188,7 @@ inline bool gemm_tc_launch(cudaStream_t st, const float* A, long long lda, int a
   g.kchunk = ((K + split - 1) / split + GT_BK - 1) / GT_BK * GT_BK;
   split = (K + g.kchunk - 1) / g.kchunk;
   dim3 grid((unsigned)((N + GT_BN - 1) / GT_BN), (unsigned)((M + GT_BM - 1) / GT_BM), (unsigned)split);
-  RNNWF_COUNT_LAUNCH(); gemm_tc_kernel<<<grid, 128, 4 * GT_TILE_BYTES, st>>>(g);
+  RNNWF_COUNT_LAUNCH(); gemm_tc_kernel<<<grid, 128, GT_STAGES * 2 * GT_TILE_BYTES, st>>>(g);
   return true;
 }
 

@@ -826,7 +826,7 @@ long long rnnwf_launch_count(void) { return rnnwf::launch_counter(); }
 // debug hook (not declared in the public header): run the tcgen05 TF32 GEMM on raw FP32 device matrices
 int rnnwf_debug_gemm_tc(const float* A, long long lda, int a_kc, const float* B, long long ldb, int b_kc, float* C, long long ldc,
                         long long M, int N, long long K, int mode, void* stream) {
-  cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * GT_TILE_BYTES);
+  cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GT_STAGES * 2 * GT_TILE_BYTES);
   if (!gemm_tc_launch(static_cast<cudaStream_t>(stream), A, lda, a_kc, B, ldb, b_kc, C, ldc, M, N, K, mode)) return fail(RNNWF_EINVAL, "gemm_tc: unaligned operands");
   CUDA_TRY(cudaGetLastError());
   return RNNWF_OK;
