@@ -290,6 +290,19 @@ int build_model(rnnwf_model& m) {
 // ------------------------------------------------------------------------------------------------
 struct LaunchShape { int WR, Mp, Mr, threads, smem, grid; };
 
+const void* sweep_fn(const rnnwf_model& m) {
+  if (m.NTU == 3 && m.TJ == 5) return reinterpret_cast<const void*>(&sweep_kernel<5, 3>);
+  if (m.NTU == 3 && m.TJ == 4) return reinterpret_cast<const void*>(&sweep_kernel<4, 3>);
+  return reinterpret_cast<const void*>(&sweep_kernel<4, 4>);
+}
+// persistent CTAs the scratch ring is sized for, in units of 128-row tiles: up to 4 per SM when shared memory allows
+int max_ctas(const rnnwf_model& m) {
+  if (m.tc_enabled) return m.num_sms;
+  SmemLayout L(m.ncls_max, m.Gblk, 128, m.ldH, m.nhp, m.ND, m.Tsym);
+  const int occ = std::max(1, std::min(4, (227 * 1024) / std::max(1, L.total)));
+  return m.num_sms * occ;
+}
+
 int pick_shape(const rnnwf_model& m, long long rows, LaunchShape& s) {
   if (m.tc_enabled) {
     const TcSmem ts(m.nhp, m.Tsym, m.Q);
@@ -309,7 +322,11 @@ int pick_shape(const rnnwf_model& m, long long rows, LaunchShape& s) {
     // prefer the tallest tile that still gives every SM a tile
     if (wr == 1 || tiles >= m.num_sms) {
       s.WR = wr; s.Mp = Mp; s.Mr = Mr; s.threads = 32 * wr * m.WC; s.smem = L.total;
-      s.grid = (int)std::max(1LL, std::min<long long>(tiles, m.num_sms));
+      int occ = 1;
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sweep_fn(m), s.threads, s.smem) != cudaSuccess) { occ = 1; cudaGetLastError(); }
+      occ = std::max(1, std::min(4, occ));
+      const long long cap = (long long)max_ctas(m) * 128 / Mp;     // what the scratch ring was sized for
+      s.grid = (int)std::max(1LL, std::min<long long>(tiles, std::min<long long>((long long)m.num_sms * occ, cap)));
       return RNNWF_OK;
     }
   }
@@ -548,7 +565,7 @@ int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
 
 int64_t rnnwf_workspace_bytes(rnnwf_handle h) {
   if (h == nullptr) return 0;
-  return align256(ring_bytes(*h, h->num_sms, 128));
+  return align256(ring_bytes(*h, max_ctas(*h), 128));
 }
 
 int64_t rnnwf_saved_bytes(rnnwf_handle h, int64_t rows) { return h ? h->saved_layout(rows).total : 0; }
@@ -618,7 +635,7 @@ ElocLayout eloc_layout(const rnnwf_model& m, int ham, long long rows) {
   L.off_nchild = o;   o += 256;
   L.max_children = max_children_per_sample(m, ham) * rows;
   L.off_children = o; o += align256(L.max_children * (long long)sizeof(Child));
-  L.off_ring = o;     o += align256(ring_bytes(m, m.num_sms, 128));
+  L.off_ring = o;     o += align256(ring_bytes(m, max_ctas(m), 128));
   L.total = o;
   return L;
 }
