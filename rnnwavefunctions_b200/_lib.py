@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librnnwf.so")
+# RNNWF_LIB_PATH selects another build of the same library (e.g. the cycle-counter variant used by tools/tc_cycles.py)
+LIB_PATH = os.environ.get("RNNWF_LIB_PATH") or os.path.join(_HERE, "librnnwf.so")
 
 CELL_GRU1D, CELL_VANILLA2D, CELL_TENS2D, CELL_TENSGRU2D, CELL_GRU4 = range(5)
 HAM_TFIM1D, HAM_TFIM2D, HAM_J1J2, HAM_HEIS2D, HAM_RYDBERG = range(5)

@@ -101,6 +101,7 @@ struct SweepParams {
   const float* tc_bias;        // [2][nhp]: b, bg
   int tc_np;
   unsigned long long* tc_prof;  // optional per-CTA cycle counters (debug)
+  int debug_flags;                    // tensor-core sweep timing experiments (RNNWF_TC_DEBUG), 0 in production
   // ---- scratch
   float* ring;              // [gridDim.x][ring_len][Mp][nhp]
 };

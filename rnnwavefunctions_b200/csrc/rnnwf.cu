@@ -4,6 +4,7 @@
 #include <cstdio>
 #include <cstring>
 #include <mutex>
+#include <cstdlib>
 #include <string>
 #include <vector>
 
@@ -279,6 +280,11 @@ int build_model(rnnwf_model& m) {
   m.tc_enabled = (m.precision == 1 && m.cell == CELL_TENSGRU2D);
   if (m.precision == 1 && !m.tc_enabled) return fail(RNNWF_EINVAL, "the tensor-core regime is implemented for the tensorized 2D GRU cell");
   m.tc_np = (m.nh + TC_JP - 1) / TC_JP;
+  if (m.tc_enabled) {
+    const TcSmem ts(m.nhp, m.Tsym, m.Q);
+    if (ts.total > 227 * 1024 || 2 * TC_N + 2 * m.nhp > TC_TMEM_COLS || m.tc_np > 7)
+      return fail(RNNWF_EINVAL, "the tensor-core regime needs num_units <= 104 (weight stages in shared memory, operand in TMEM)");
+  }
   m.wpack_float4 = std::max(1LL, woff);
   m.xtab_float4 = std::max(1LL, xoff);
   m.bias_float4 = std::max(1LL, boff);
@@ -343,6 +349,7 @@ void fill_model_params(const rnnwf_model& m, const LaunchShape& s, SweepParams& 
   P.steps = m.d_steps; P.variants = m.d_variants; P.Wpack = m.d_wpack; P.Xtab = m.d_xtab; P.bias = m.d_bias;
   P.head_w = m.d_head_w; P.head_b = m.d_head_b;
   P.tc_B = m.d_tcB; P.tc_bias = m.d_tcbias; P.tc_np = m.tc_np; P.tc_prof = g_tc_prof;
+  { const char* dbg = std::getenv("RNNWF_TC_DEBUG"); P.debug_flags = dbg ? std::atoi(dbg) : 0; }
 }
 
 template <int TJ, int NTU>
@@ -354,7 +361,10 @@ cudaError_t launch_inst(const SweepParams& P, const LaunchShape& s, cudaStream_t
 int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& s, cudaStream_t st) {
   cudaError_t e;
   if (m.tc_enabled) {
-    RNNWF_COUNT_LAUNCH(); sweep_tc_kernel<<<s.grid, s.threads, s.smem, st>>>(P);
+    RNNWF_COUNT_LAUNCH();
+    if (P.mode == MODE_SAMPLE) sweep_tc_kernel<MODE_SAMPLE><<<s.grid, s.threads, s.smem, st>>>(P);
+    else if (P.mode == MODE_CHILD) sweep_tc_kernel<MODE_CHILD><<<s.grid, s.threads, s.smem, st>>>(P);
+    else sweep_tc_kernel<MODE_EVAL><<<s.grid, s.threads, s.smem, st>>>(P);
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("tensor-core sweep launch: ") + cudaGetErrorString(e));
     return RNNWF_OK;
@@ -468,7 +478,9 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
     if (ts.total > 227 * 1024) { rnnwf_destroy(m); return fail(RNNWF_ENOMEM, "tensor-core sweep does not fit in shared memory for this lattice / width"); }
     CREATE_TRY(cudaMalloc(&m->d_tcB, (size_t)3 * m->tc_np * ts.b_bytes));
     CREATE_TRY(cudaMalloc(&m->d_tcbias, (size_t)2 * m->nhp * 4));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
   }
   CREATE_TRY(backward_init());
 #undef CREATE_TRY

@@ -10,12 +10,18 @@
 // the weights O(0.1), so the range is no issue and the 11-bit mantissa keeps E_loc within ~2e-4 of the FP32 path
 // (measured on the oracle: BF16 activations give 2.4e-3, which misses the 1e-3 bound of the reduced-precision mode).
 //
-//   warp 0, lane 0 : control -- cp.async.bulk of the pre-packed weight images (UMMA K-major core-matrix layout,
-//                    mbarrier complete_tx), tcgen05.mma issue, tcgen05.commit
-//   warps 1..16    : four threads per row (row == TMEM lane; the four share the 16 units of every column pass).
-//                    They build the row's A operand (hi/lo) in shared memory from the FP32 history ring, read the
-//                    accumulators with tcgen05.ld, apply the gates; one of the four then evaluates the heads /
-//                    U(1) mask / draw / log-probability of the row (4 warps per scheduler hide the latencies).
+//   warp 0       : MMA issue -- tcgen05.mma with the A operand in TMEM and the weights in shared memory (UMMA K-major
+//                  core-matrix layout), K loop fully unrolled, tcgen05.commit to the epilogue and to the loader.
+//                  Executes at the tensor-core floor (128 x 112 / 256 = 56 cycles per K=16 step).
+//   warp 19      : loader -- cp.async.bulk of the pre-packed weight images (mbarrier complete_tx) through 4 stages,
+//                  up to 4 column passes ahead, across sites and tiles.
+//   warps 1..16  : epilogue, four threads per row (row == TMEM lane; the four share the 16 units of every column pass).
+//                  They read their 28 accumulators with tcgen05.ld, apply the gates, and write the new hidden state as
+//                  FP16 straight into the next site's A operand in TMEM (tcgen05.st) and into the L2-resident
+//                  history ring; the older neighbour half of the next operand is prefetched from the ring one site
+//                  ahead.  No block barrier in the site loop.
+//   warps 17..18 : heads, two rows per thread: softmax / U(1) mask / draw / log-probability / phase, one site behind
+//                  the epilogue warps (partial head sums handed over in shared memory), off the critical path.
 // Everything is synchronised by mbarriers; every wait is bounded and traps instead of hanging.
 //
 // Same reference behaviour as sweep.cuh for 2DHeisenberg/MDTensorizedGRUcell.py:49-61 and MDComplexRNN.py:69-286.
@@ -32,26 +38,27 @@ constexpr int TC_NB = 7;                // column blocks per unit: Wa_s Wb_s Wc_
 constexpr int TC_N = TC_JP * TC_NB;     // 112 MMA columns per pass
 constexpr int TC_SUB = 4;                // threads per row: each handles 4 of the 16 units of a pass
 constexpr int TC_EPI_THREADS = TC_ROWS * TC_SUB;
-constexpr int TC_THREADS = 32 + TC_EPI_THREADS;   // warp 0: control, warps 1..16: epilogue
-constexpr int TC_TMEM_COLS = 256;
+constexpr int TC_HEAD_THREADS = 64;     // two rows per head thread
+constexpr int TC_THREADS = 32 + TC_EPI_THREADS + TC_HEAD_THREADS + 32;   // warp 0: MMA, 1..16: epilogue, 17..18: heads, 19: loader
+constexpr int TC_TPS = TC_NB * 4;       // accumulator columns one epilogue thread owns per pass (28, contiguous)
+constexpr int TC_TMEM_COLS = 512;         // 2 x 112 accumulator columns + 2 x (nhp) A-operand columns
+constexpr int TC_STAGES = 4;              // weight stages in shared memory
 constexpr uint32_t TC_SPIN_LIMIT = 1u << 26;
 
 struct TcSmem {
-  int off_A, off_B, off_headw, off_headb, off_bias, off_part, off_meta, off_sym, off_bar, off_tmem, total;
-  int a_bytes, b_bytes, kc;
+  int off_B, off_headw, off_headb, off_bias, off_part, off_meta, off_sym, off_bar, off_tmem, total;
+  int b_bytes, kc;
   __host__ __device__ TcSmem(int nhp, int Tsym, int Q = 0) {
     kc = 2 * (nhp / 8);                       // 16-byte k-cores of the concatenated [h_h ; h_v] operand
-    a_bytes = kc * (TC_ROWS / 8) * 128;
     b_bytes = kc * (TC_N / 8) * 128;
     int o = 0;
-    off_A = o; o += 2 * a_bytes;               // double-buffered operand tiles
-    off_B = o;   o += 2 * b_bytes;
-    off_headw = o; o += ((nhp * 4 * 4) + 15) & ~15;
+    off_B = o;   o += TC_STAGES * b_bytes;     // weight stages (the A operand lives in TMEM)
+    off_headw = o; o += (nhp + TC_JP) * 16;     // head weights [unit][4], zero rows up to the last pass's end
     off_headb = o; o += 16;
     off_bias = o;  o += ((2 * (nhp + TC_JP) * 4) + 15) & ~15;
-    off_part = o;  o += TC_ROWS * 4 * 16;      // partial head sums [128][TC_SUB] float4
+    off_part = o;  o += 2 * TC_ROWS * TC_SUB * 16;   // partial head sums [2][128][TC_SUB] float4
     off_meta = o;  o += ((Q > 0 ? Q : Tsym) * 8 + 15) & ~15;   // per step: nbr0, nbr1, site, pad (int16 x 4)
-    off_bar = o;   o += 128;
+    off_bar = o;   o += 256;
     off_tmem = o;  o += 16;
     off_sym = o;   o += ((Tsym * TC_ROWS) + 15) & ~15;
     total = o + 1024;                          // slack for the 1024-byte alignment of the base
@@ -78,10 +85,55 @@ __device__ __forceinline__ uint32_t mbar_try_wait(uint64_t* bar, uint32_t parity
       : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
   return ok;
 }
+__device__ __forceinline__ uint32_t mbar_test_wait(uint64_t* bar, uint32_t parity) {   // non-blocking poll
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  return ok;
+}
 __device__ __forceinline__ long long tc_clock() { long long c; asm volatile("mov.u64 %0, %%clock64;" : "=l"(c)); return c; }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   for (uint32_t spin = 0; !mbar_try_wait(bar, parity); ++spin)
     if (spin > TC_SPIN_LIMIT) { asm volatile("trap;"); }
+}
+// the same on a precomputed shared-space address
+__device__ __forceinline__ void mbar_arrive_a(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  if (ok) return;
+  for (uint32_t spin = 0;; ++spin) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    if (ok) return;
+    if (spin > TC_SPIN_LIMIT) { asm volatile("trap;"); }
+  }
+}
+// wait of a role that is off the critical path: let the hardware suspend the warp for up to ~4 us per poll instead of
+// spinning on the issue slots the epilogue warps need
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
+  for (uint32_t spin = 0;; ++spin) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity), "r"(4000u) : "memory");
+    if (ok) return;
+    if (spin > TC_SPIN_LIMIT) { asm volatile("trap;"); }
+  }
 }
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -115,12 +167,31 @@ __device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t adesc, uint
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// D[tmem] (+)= A[tmem] * B[smem]^T ; A: lane = row, 32-bit column = two consecutive K halves; B K-major, no swizzle
+__device__ __forceinline__ void tc_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_st4(uint32_t taddr, const uint4& v) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void tc_st2(uint32_t taddr, const uint2& v) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(taddr), "r"(v.x), "r"(v.y) : "memory");
+}
+__device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&d)[16]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
       : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]), "=r"(d[7]), "=r"(d[8]),
         "=r"(d[9]), "=r"(d[10]), "=r"(d[11]), "=r"(d[12]), "=r"(d[13]), "=r"(d[14]), "=r"(d[15])
       : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tc_ld8(uint32_t taddr, uint32_t* d) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]), "=r"(d[7]) : "r"(taddr) : "memory");
 }
 __device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
@@ -147,57 +218,97 @@ __device__ __forceinline__ void tc_ld4(uint32_t taddr, uint32_t (&d)[4]) {
 }
 // the four warps that share a TMEM lane quarter (= the four threads of each of its 32 rows)
 __device__ __forceinline__ void quarter_barrier(int quarter) { asm volatile("bar.sync %0, 128;" ::"r"(1 + quarter) : "memory"); }
-// 1e-3 regime: exp2-based sigmoid / tanh (abs. error ~1e-6, far below the BF16 operand rounding)
-__device__ __forceinline__ float fast_sigmoid(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
-__device__ __forceinline__ float fast_tanh(float x) { return 2.0f * fast_sigmoid(2.0f * x) - 1.0f; }
+// Gate non-linearities of the reduced-precision regime: one MUFU.TANH each (tanh.approx.f32, relative error 2^-11, the
+// same size as the FP16 rounding of the operands; tools/tc_accuracy.py shows no measurable difference against exact
+// gates).  sigmoid(g) = 1/2 + 1/2 tanh(g/2): the factor 1/2 is folded into the packed update-gate weights and biases
+// (pack_tc_kernel; exact in FP16).  The special-function unit issues 16 ops/clk/SM, so the two MUFU per unit
+// (instead of four with ex2 + rcp) matter: 512 threads x 4 units x 2 = 256 cycles per column pass.
+constexpr float TC_SCALE_CAND = 1.0f, TC_SCALE_GATE = 0.5f;
+__device__ __forceinline__ float mufu_tanh(float x) { float y; asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float sigmoid_prescaled(float x) { return fmaf(0.5f, mufu_tanh(x), 0.5f); }
+__device__ __forceinline__ float tanh_prescaled(float x) { return mufu_tanh(x); }
 
+// K loop of one column pass.  HC > 0: fully unrolled, every operand address is base + immediate; HC == 0: generic.
+template <int HC>
+__device__ __forceinline__ void tc_issue_pass(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, int hc = HC) {
+  constexpr uint64_t B_KSTEP = (2ull * (TC_N / 8) * 128) >> 4;   // two k-cores of the weight image per K=16 step
+  if constexpr (HC > 0) {
+#pragma unroll
+    for (int ks = 0; ks < HC; ++ks) tc_mma_f16_ts(tmem_d, tmem_a + (uint32_t)ks * 8u, bdesc + (uint64_t)ks * B_KSTEP, idesc, ks > 0 ? 1u : 0u);
+  } else {
+#pragma unroll 1
+    for (int ks = 0; ks < hc; ++ks) tc_mma_f16_ts(tmem_d, tmem_a + (uint32_t)ks * 8u, bdesc + (uint64_t)ks * B_KSTEP, idesc, ks > 0 ? 1u : 0u);
+  }
+}
+// the 28 accumulator columns of one epilogue thread (contiguous in TMEM, see pack_tc_kernel): three loads
+__device__ __forceinline__ void tc_ld28(uint32_t taddr, uint32_t (&d)[TC_TPS]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3]), "=r"(d[4]), "=r"(d[5]), "=r"(d[6]), "=r"(d[7]), "=r"(d[8]),
+        "=r"(d[9]), "=r"(d[10]), "=r"(d[11]), "=r"(d[12]), "=r"(d[13]), "=r"(d[14]), "=r"(d[15])
+      : "r"(taddr) : "memory");
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(d[16]), "=r"(d[17]), "=r"(d[18]), "=r"(d[19]), "=r"(d[20]), "=r"(d[21]), "=r"(d[22]), "=r"(d[23])
+               : "r"(taddr + 16u) : "memory");
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(d[24]), "=r"(d[25]), "=r"(d[26]), "=r"(d[27]) : "r"(taddr + 24u) : "memory");
+}
+
+template <int MODE>
 __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepParams P) {
-  extern __shared__ unsigned char smem_raw[];
-  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  extern __shared__ __align__(128) unsigned char tc_smem[];   // no swizzle anywhere: 16-byte alignment is all the hardware needs
+  unsigned char* const smem = tc_smem;
   const TcSmem L(P.nhp, P.Tsym, P.Q);
-  unsigned char* const Abuf = smem + L.off_A;          // [2][a_bytes]: operand of step q lives in buffer q & 1
-  unsigned char* const Bst = smem + L.off_B;
-  float* const headW = reinterpret_cast<float*>(smem + L.off_headw);
+  unsigned char* const Bst = smem + L.off_B;                              // [TC_STAGES][b_bytes] weight stages
+  float* const headW = reinterpret_cast<float*>(smem + L.off_headw);      // [nhp + 16][4], zero rows past num_units
   float* const headB = reinterpret_cast<float*>(smem + L.off_headb);
-  float* const biasS = reinterpret_cast<float*>(smem + L.off_bias);       // [2][nhp + 16]: b, bg
+  float* const biasS = reinterpret_cast<float*>(smem + L.off_bias);       // [2][nhp + 16]: b, bg (zero past num_units)
   float4* const partS = reinterpret_cast<float4*>(smem + L.off_part);     // [2][128][TC_SUB] partial head sums
   short4* const metaS = reinterpret_cast<short4*>(smem + L.off_meta);     // per step: (nbr0, nbr1, site, -)
   uint8_t* const symS = smem + L.off_sym;                                 // [Tsym][128]
   uint64_t* const bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
   uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(smem + L.off_tmem);
-  uint64_t* const bar_A = bars + 0;
-  uint64_t* const bar_B = bars + 1;      // [2]
-  uint64_t* const bar_mma = bars + 3;    // [2]
-  uint64_t* const bar_free = bars + 5;   // [2]
+  uint64_t* const bar_A = bars + 0;                   // next operand written to TMEM (512 arrivals)
+  uint64_t* const bar_mma = bars + 1;                 // [2] accumulator buffer full (tcgen05.commit)
+  uint64_t* const bar_free = bars + 3;                // [2] accumulator buffer drained (512 arrivals)
+  uint64_t* const bar_part = bars + 5;                // [2] partial head sums of a step written (512 arrivals)
+  uint64_t* const bar_pfree = bars + 7;               // [2] partial head sums consumed (64 arrivals)
+  uint64_t* const bar_sym = bars + 9;                 // sampling: the step's symbols are drawn (64 arrivals)
+  uint64_t* const bar_tile = bars + 10;               // head warps are done with the tile's symbol table (64 arrivals)
+  uint64_t* const bar_B = bars + 11;                  // [TC_STAGES] weight stage landed (complete_tx)
+  uint64_t* const bar_Bfree = bars + 11 + TC_STAGES;  // [TC_STAGES] weight stage consumed (tcgen05.commit)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const bool is_ctrl = (tid == 0);
-  const bool is_epi = (warp >= 1);
-  const int quarter = warp & 3;                       // TMEM lane quarter this warp may access
-  const int sub = (warp - 1) >> 2;                    // which 4 of the 16 units of a pass this thread handles
-  const int row = (quarter << 5) + lane;              // tile row == TMEM lane
   const int nhp = P.nhp, nh = P.nh, ldb = nhp + TC_JP;
-  const int NP = P.tc_np, hc = L.kc / 2;   // k-cores of the whole operand / of one neighbour half
-  const uint32_t A_LBO = (TC_ROWS / 8) * 128, B_LBO = (TC_N / 8) * 128, SBO = 128;
+  const int NP = P.tc_np, hc = L.kc / 2;              // column passes per site; k-cores (= K16 steps) per neighbour half
+  const uint32_t B_LBO = (TC_N / 8) * 128, SBO = 128;
   const uint32_t idesc = tc_idesc(TC_ROWS, TC_N);
-  const uint32_t roff = (uint32_t)(row >> 3) * 128 + (uint32_t)(row & 7) * 16;   // this row inside a k-core
-  // history ring of this CTA, stored as FP16 operand images [slot][k-core][row/8][row%8][8 halves] (L2-resident)
-  const uint32_t img_bytes = (uint32_t)hc * A_LBO;
-  unsigned char* const ring = reinterpret_cast<unsigned char*>(P.ring) + (size_t)blockIdx.x * P.ring_len * img_bytes;
+  // The last column pass holds only num_units - 16 (NP - 1) real units: issue it just wide enough for the epilogue
+  // threads that own them (28 columns each, rounded up to the MMA's N granularity of 16).
+  const int subs_last = (nh - (NP - 1) * TC_JP + 3) / 4;
+  const uint32_t idesc_last = tc_idesc(TC_ROWS, ((subs_last * TC_TPS + 15) / 16) * 16);
+  // TMEM map: [0, 224) two accumulator buffers; then two A operands of 8*hc columns each (2 halves per 32-bit column)
+  const uint32_t acols = 8u * (uint32_t)hc;           // columns of one A operand ([h_h ; h_v], 16*hc halves)
 
   if (tid == 0) {
     mbar_init(bar_A, TC_EPI_THREADS);
-    mbar_init(bar_B + 0, 1); mbar_init(bar_B + 1, 1);
-    mbar_init(bar_mma + 0, 1); mbar_init(bar_mma + 1, 1);
-    mbar_init(bar_free + 0, TC_EPI_THREADS); mbar_init(bar_free + 1, TC_EPI_THREADS);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar_mma + i, 1);
+      mbar_init(bar_free + i, TC_EPI_THREADS);
+      mbar_init(bar_part + i, TC_EPI_THREADS);
+      mbar_init(bar_pfree + i, TC_HEAD_THREADS);
+    }
+    mbar_init(bar_sym, TC_HEAD_THREADS);
+    mbar_init(bar_tile, TC_HEAD_THREADS);
+    for (int i = 0; i < TC_STAGES; ++i) { mbar_init(bar_B + i, 1); mbar_init(bar_Bfree + i, 1); }
     fence_mbar_init();
   }
   if (warp == 0) tc_alloc(tmem_slot, TC_TMEM_COLS);
-  for (int i = tid; i < nhp * 4; i += TC_THREADS) headW[i] = P.head_w[i];
+  for (int i = tid; i < (nhp + TC_JP) * 4; i += TC_THREADS) headW[i] = (i < nh * 4) ? P.head_w[i] : 0.f;
   if (tid < 4) headB[tid] = P.head_b[tid];
   for (int i = tid; i < 2 * ldb; i += TC_THREADS) {
     const int which = i / ldb, j = i - which * ldb;
-    biasS[i] = (j < nh) ? P.tc_bias[which * nhp + j] : 0.f;
+    biasS[i] = (j < nh) ? P.tc_bias[which * nhp + j] * (which == 0 ? TC_SCALE_CAND : TC_SCALE_GATE) : 0.f;
   }
   for (int i = tid; i < P.Q; i += TC_THREADS) {
     const StepMeta* m = P.steps + i;
@@ -207,279 +318,371 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_A0 = tmem_base + 2u * TC_N;     // first A operand buffer
 
-  const uint64_t adesc0 = tc_desc(smem_u32(Abuf), A_LBO, SBO);
-  const uint64_t bdesc0 = tc_desc(smem_u32(Bst), B_LBO, SBO);
-  const uint64_t a_kstep = (2 * A_LBO) >> 4, b_kstep = (2 * B_LBO) >> 4;
-
-  // consumed-completion counters (parity = count & 1)
-  uint32_t nA = 0, nB[2] = {0, 0}, nMc[2] = {0, 0}, nF[2] = {0, 0};   // control thread
-  uint32_t nMe[2] = {0, 0};                                             // epilogue threads
-  bool b_prefetched = false;
-  // optional cycle accounting (debug builds of the bench only): [0] bar_A [1] bar_B [2] bar_free [3] mma issue [4] bar_mma(ctrl)
-  // [5] total ctrl; [8] epi bar_mma wait [9] epi pass compute [10] epi build_half [11] epi finalize+barriers [12] epi total
+  // optional cycle accounting (-DRNNWF_TC_PROF builds only; tools/tc_cycles.py): MMA warp [0] bar_A [1] bar_B
+  // [2] bar_free [3] mma issue [5] total; loader warp [4] stage wait [6] copy issue; epilogue thread 32: [8] bar_mma
+  // [9] pass compute [10] next-operand half [11] step tail [12] total; head thread: [13] wait for partial sums [14] heads
+#ifdef RNNWF_TC_PROF
   long long prof[16];
+#pragma unroll
   for (int i = 0; i < 16; ++i) prof[i] = 0;
-  const bool do_prof = (P.tc_prof != nullptr) && (tid == 0 || tid == 32);
+  const bool do_prof = (P.tc_prof != nullptr) && (tid == 0 || tid == 32 || tid == 32 + TC_EPI_THREADS || tid == TC_THREADS - 32);
+  const long long kstart = tc_clock();
 #define TC_T0() long long t0__ = do_prof ? tc_clock() : 0
 #define TC_ACC(k) do { if (do_prof) { const long long t1__ = tc_clock(); prof[k] += t1__ - t0__; t0__ = t1__; } } while (0)
-  const long long kstart = do_prof ? tc_clock() : 0;
+#define TC_TOTAL(k) do { if (do_prof) prof[k] = tc_clock() - kstart; } while (0)
+  // event trace of CTA 0: [role 8][TC_TRACE_LEN] words (tag << 40 | cycles since kernel start), after the counters
+  constexpr int TC_TRACE_LEN = 1024;
+  const int trole = (warp == 0) ? 0 : (warp == TC_THREADS / 32 - 1) ? 1 : (warp == 1) ? 2 : (warp == 16) ? 3 : (warp == 8) ? 4 : (warp == 17) ? 5 : -1;
+  const bool do_trace = (P.tc_prof != nullptr) && blockIdx.x == 0 && lane == 0 && trole >= 0;
+  unsigned long long* const tbuf = do_trace ? P.tc_prof + (size_t)gridDim.x * 16 + (size_t)trole * TC_TRACE_LEN : nullptr;
+  int nev = 0;
+#define TC_EV(tag) do { if (do_trace && nev < TC_TRACE_LEN) tbuf[nev++] = ((unsigned long long)(tag) << 40) | (unsigned long long)(tc_clock() - kstart); } while (0)
+#else
+#define TC_EV(tag) do { } while (0)
+#define TC_T0() do { } while (0)
+#define TC_ACC(k) do { } while (0)
+#define TC_TOTAL(k) do { } while (0)
+#endif
 
   const long long total_rows = (P.rows_dev != nullptr) ? (long long)(*P.rows_dev) : P.rows;
   const long long ntiles = (total_rows + TC_ROWS - 1) / TC_ROWS;
-  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    const long long row0 = tile * TC_ROWS;
-    const int nrows = (int)((total_rows - row0 < (long long)TC_ROWS) ? (total_rows - row0) : (long long)TC_ROWS);
+  // first sweep step of a tile: under prefix reuse the tile restarts where its first child departs from its parent
+  auto tile_q0 = [&](long long row0) -> int {
     int ts0 = 0;
-    if (P.mode == MODE_CHILD && P.par_hist != nullptr) {
+    if (MODE == MODE_CHILD && P.par_hist != nullptr) {
       const Child c0 = P.children[row0];
       ts0 = (c0.tb >= 0 && c0.tb < c0.ta) ? c0.tb : c0.ta;
     }
-    const int q0 = ts0 * P.symL;
-    const bool live = is_epi && row < nrows;
-    const bool fin = live && sub == 0;                // the thread that owns the row's heads / running sums
+    return ts0;
+  };
+  // Every site goes through the tensor core, the first one included (its operand is all zeros): no special cases.
 
-    // ---- per-row state
-    double rlogp = 0.0, rphase = 0.0;                 // (fin thread only)
-    int rnup = 0, rparent = 0;
-    float rcoef = 0.f;
-    if (is_epi) {
-      Child ch;
-      ch.parent = 0; ch.ta = 0; ch.tb = -1; ch.coef = 0.f; ch.ka = ch.kb = 0;
-      if (live && P.mode == MODE_CHILD) { ch = P.children[row0 + row]; rparent = ch.parent; rcoef = ch.coef; }
-      if (live && P.mode != MODE_SAMPLE) {
-        const long long src = (P.mode == MODE_CHILD) ? (long long)ch.parent : row0 + row;
-        const int8_t* c = P.cfg_in + src * P.nsites;
-        for (int t = sub; t < P.Tsym; t += TC_SUB) {
-          int sy = c[metaS[t].z] & 1;
-          if (P.mode == MODE_CHILD && (t == ch.ta || t == ch.tb)) sy ^= 1;
-          symS[t * TC_ROWS + row] = (uint8_t)sy;
-        }
-      } else {
-        for (int t = sub; t < P.Tsym; t += TC_SUB) symS[t * TC_ROWS + row] = 0;
-      }
-      quarter_barrier(quarter);
-      if (fin && P.mode == MODE_CHILD)
-        for (int t = 0; t < ts0; ++t) rnup += symS[t * TC_ROWS + row];
-    }
-    // One neighbour half of an A operand: this row's hidden state of step qn (zeros if absent) in the core-matrix
-    // layout [k-core][row/8][row%8][8 halves]; the row's four threads take every 4th k-core.  Source: the FP16 ring
-    // image (straight 16-byte copies) or, before the tile's first step under prefix reuse, the parent's FP32 history.
-    auto build_half = [&](unsigned char* A, int half, int qn) {
-      const bool have = (qn >= 0) && live;
-      const bool from_parent = have && (P.par_hist != nullptr) && (qn < q0);
-      const float* psrc = from_parent ? P.par_hist + ((size_t)qn * (size_t)P.par_rows + (size_t)rparent) * nhp : nullptr;
-      const unsigned char* isrc = (have && !from_parent) ? ring + (size_t)(qn % P.ring_len) * img_bytes + roff : nullptr;
-      for (int cbase = 0; cbase < hc; cbase += 4 * TC_SUB) {
-        uint4 o[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int c = cbase + sub + i * TC_SUB;
-          o[i] = make_uint4(0u, 0u, 0u, 0u);
-          if (c < hc) {
-            if (isrc != nullptr) {
-              o[i] = __ldcg(reinterpret_cast<const uint4*>(isrc + (uint32_t)c * A_LBO));
-            } else if (psrc != nullptr) {
-              const float4 v0 = __ldg(reinterpret_cast<const float4*>(psrc + c * 8));
-              const float4 v1 = __ldg(reinterpret_cast<const float4*>(psrc + c * 8 + 4));
-              o[i].x = pack_f16x2(v0.x, v0.y); o[i].y = pack_f16x2(v0.z, v0.w);
-              o[i].z = pack_f16x2(v1.x, v1.y); o[i].w = pack_f16x2(v1.z, v1.w);
-            }
-          }
-        }
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int c = cbase + sub + i * TC_SUB;
-          if (c < hc) *reinterpret_cast<uint4*>(A + (uint32_t)(half * hc + c) * A_LBO + roff) = o[i];
-        }
-      }
-    };
-
-    // operand of the tile's first step: both halves from the history (parent's saved history under prefix reuse)
-    if (is_epi) {
-      const short4 s0 = metaS[q0];
-      if (s0.x >= 0 || s0.y >= 0) {
-        build_half(Abuf + (q0 & 1) * L.a_bytes, 0, s0.x);
-        build_half(Abuf + (q0 & 1) * L.a_bytes, 1, s0.y);
-        fence_proxy_async_smem();
-        mbar_arrive(bar_A);
-      }
-    }
-
-    for (int q = q0; q < P.Q; ++q) {
-      const short4 sm = metaS[q];
-      const int nb0 = sm.x, nb1 = sm.y;      // history index == symbol index of the two neighbours (2D cells)
-      const int variant = (nb0 >= 0 && nb1 >= 0) ? 0 : (nb0 >= 0 ? 1 : (nb1 >= 0 ? 2 : 3));
-      const int t = q;
-
-      if (warp == 0 && variant != 3) {
-        // ================= control warp: weight stream + MMA issue =================
-        // The whole warp walks this path convergently (so descriptors and addresses stay in uniform registers);
-        // only the instructions that must be issued once are predicated on one elected lane.
-        const unsigned char* Bsrc = P.tc_B + (size_t)variant * NP * L.b_bytes;
-        const bool leader = elect_one();
-        if (!b_prefetched && leader) {
-          for (int p = 0; p < 2 && p < NP; ++p) {
-            mbar_expect_tx(bar_B + p, L.b_bytes);
-            bulk_g2s(Bst + p * L.b_bytes, Bsrc + (size_t)p * L.b_bytes, L.b_bytes, bar_B + p);
-          }
-        }
+  if (warp == 0) {
+    // ======================= MMA warp =======================
+    // Warp-uniform code (descriptors stay in uniform registers); the single-issue instructions are predicated on one
+    // elected lane.  Per column pass: wait for the weight stage and a drained accumulator buffer, issue the K loop
+    // (fully unrolled: every descriptor is base + immediate), commit to the epilogue and to the loader.
+    const bool leader = elect_one();
+    const uint64_t bdesc0 = tc_desc(smem_u32(Bst), B_LBO, SBO);
+    uint32_t phA = 0, phF = 0, phBw = 0, it = 0;      // parity bits: operand / accumulator buffers / weight stages; pass counter
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const int q0 = tile_q0(tile * TC_ROWS) * P.symL;
+      for (int q = q0; q < P.Q; ++q) {
         TC_T0();
-        mbar_wait(bar_A, nA & 1); ++nA;
-        TC_ACC(0);
-        const uint64_t ad0 = adesc0 + (uint64_t)(((q & 1) * L.a_bytes) >> 4);
-        for (int p = 0; p < NP; ++p) {
-          const int s = p & 1;
-          mbar_wait(bar_B + s, nB[s] & 1); ++nB[s];
-          TC_ACC(1);
-          mbar_wait(bar_free + s, (nF[s] & 1) ^ 1); ++nF[s];
-          TC_ACC(2);
+        mbar_wait(bar_A, phA); phA ^= 1u;
+        TC_ACC(0); TC_EV(1);
+        const uint32_t tmem_a = tmem_A0 + (uint32_t)(q & 1) * acols;
+        for (int p = 0; p < NP; ++p, ++it) {
+          const uint32_t s = it % TC_STAGES, tb = (uint32_t)p & 1u;
+          mbar_wait(bar_B + s, (phBw >> s) & 1u); phBw ^= 1u << s;
+          TC_ACC(1); TC_EV(2);
+          mbar_wait(bar_free + tb, ((phF >> tb) & 1u) ^ 1u); phF ^= 1u << tb;
+          TC_ACC(2); TC_EV(3);
           tc_fence_after();
-          const uint32_t tmem_d = tmem_base + (uint32_t)(s * TC_N);
-          // descriptors differ between k-steps only in the 14-bit start-address field: one add per MMA
-          const uint64_t bd0 = bdesc0 + (uint64_t)((s * L.b_bytes) >> 4);
+          const uint32_t tmem_d = tmem_base + tb * (uint32_t)TC_N;
+          const uint64_t bd0 = bdesc0 + (uint64_t)((s * (uint32_t)L.b_bytes) >> 4);
           if (leader) {
-#pragma unroll 1
-            for (int ks = 0; ks < hc; ++ks)
-              tc_mma_f16(tmem_d, ad0 + (uint64_t)ks * a_kstep, bd0 + (uint64_t)ks * b_kstep, idesc, ks > 0 ? 1u : 0u);
-            tc_commit(bar_mma + s);
+            const uint32_t id = (p == NP - 1) ? idesc_last : idesc;
+            if (hc == 13) tc_issue_pass<13>(tmem_d, tmem_a, bd0, id);
+            else tc_issue_pass<0>(tmem_d, tmem_a, bd0, id, hc);
+            tc_commit(bar_mma + tb);
+            tc_commit(bar_Bfree + s);
           }
           __syncwarp();
-          TC_ACC(3);
-          if (p >= 1) {   // pass p-1 has finished reading its weight stage -> refill it with pass p+1
-            const int s1 = (p - 1) & 1;
-            mbar_wait(bar_mma + s1, nMc[s1] & 1); ++nMc[s1];
-            if (p + 1 < NP && leader) {
-              mbar_expect_tx(bar_B + s1, L.b_bytes);
-              bulk_g2s(Bst + s1 * L.b_bytes, Bsrc + (size_t)(p + 1) * L.b_bytes, L.b_bytes, bar_B + s1);
-            }
-            TC_ACC(4);
-          }
+          TC_ACC(3); TC_EV(4);
         }
-        { const int s1 = (NP - 1) & 1; mbar_wait(bar_mma + s1, nMc[s1] & 1); ++nMc[s1]; }
-        TC_ACC(4);
-        // both weight stages are free again: start streaming the first two passes of the next step
-        b_prefetched = false;
-        if (q + 1 < P.Q) {
-          const short4 sn = metaS[q + 1];
-          const int vn = (sn.x >= 0 && sn.y >= 0) ? 0 : (sn.x >= 0 ? 1 : 2);
-          const unsigned char* Bn = P.tc_B + (size_t)vn * NP * L.b_bytes;
+      }
+    }
+    TC_TOTAL(5);
+  } else if (warp == TC_THREADS / 32 - 1) {
+    // ======================= loader warp: weight stream =======================
+    // One flat sequence of (site, pass) weight images through TC_STAGES shared-memory stages; runs ahead of the MMA
+    // warp across sites and tiles, gated only by the stages' "consumed" barriers.
+    const bool leader = elect_one();
+    // debug_flags bit 0 (RNNWF_TC_DEBUG=1, timing experiments only, wrong results): copy half of every weight image
+    const uint32_t load_bytes = (P.debug_flags & 1) ? (uint32_t)L.b_bytes / 2 : (uint32_t)L.b_bytes;
+    uint32_t phBf = 0, n = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const int q0 = tile_q0(tile * TC_ROWS) * P.symL;
+      for (int q = q0; q < P.Q; ++q) {
+        const short4 sm = metaS[q];
+        const int v = (sm.x >= 0 && sm.y < 0) ? 1 : ((sm.x < 0 && sm.y >= 0) ? 2 : 0);   // first site: any image (operand is zero)
+        const unsigned char* src = P.tc_B + (size_t)v * NP * L.b_bytes;
+        for (int p = 0; p < NP; ++p, ++n) {
+          const uint32_t s = n % TC_STAGES;
+          TC_T0();
+          if (n >= TC_STAGES) { mbar_wait_relaxed(bar_Bfree + s, (phBf >> s) & 1u); phBf ^= 1u << s; }
+          TC_ACC(4); TC_EV(5);
           if (leader) {
-            for (int p = 0; p < 2 && p < NP; ++p) {
-              mbar_expect_tx(bar_B + p, L.b_bytes);
-              bulk_g2s(Bst + p * L.b_bytes, Bn + (size_t)p * L.b_bytes, L.b_bytes, bar_B + p);
+            mbar_expect_tx(bar_B + s, load_bytes);
+            bulk_g2s(Bst + (size_t)s * L.b_bytes, src + (size_t)p * L.b_bytes, load_bytes, bar_B + s);
+          }
+          __syncwarp();
+          TC_ACC(6); TC_EV(6);
+        }
+      }
+    }
+  } else if (warp <= TC_EPI_THREADS / 32) {
+    // ======================= epilogue warps: 4 threads per row =======================
+    // Thread (row, sub) owns units 16 p + 4 sub .. + 3 of every column pass p: it reads those accumulators (28
+    // contiguous TMEM columns), applies the gates, and writes the 4 new hidden values (FP16) to the next operand in
+    // TMEM and to its private pieces of the history ring (only this thread ever reads those 8 bytes back, so the ring
+    // needs no barrier).  The partial head sums go to the head warps through shared memory; no block-wide barrier in
+    // the step loop.
+    const int quarter = warp & 3;                       // TMEM lane quarter this warp may access
+    const int sub = (warp - 1) >> 2;                    // which 4 of the 16 units of a pass this thread handles
+    const int row = (quarter << 5) + lane;              // tile row == TMEM lane
+    const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
+    constexpr uint32_t CORE = (TC_ROWS / 8) * 128;      // bytes of one k-core (8 halves x 128 rows) in the ring image
+    const uint32_t img_bytes = (uint32_t)hc * CORE;
+    // this thread's 8-byte piece of pass p inside a ring image: piece0 + p * 2 CORE
+    const uint32_t piece0 = (uint32_t)(row >> 3) * 128 + (uint32_t)(row & 7) * 16 + (uint32_t)(sub >> 1) * CORE + (uint32_t)(sub & 1) * 8u;
+    unsigned char* const ring_base = reinterpret_cast<unsigned char*>(P.ring);
+    const uint32_t ring_off0 = (uint32_t)blockIdx.x * (uint32_t)P.ring_len * img_bytes + piece0;   // (the whole ring is < 4 GB)
+    const uint32_t bar_mma_a = smem_u32(bar_mma), bar_free_a = smem_u32(bar_free);
+    const uint32_t acc0 = tmem_base + lane_base + (uint32_t)(sub * TC_TPS);      // this thread's accumulators, buffer 0
+    const uint32_t aop0 = tmem_A0 + lane_base + (uint32_t)(sub * 2);             // this thread's operand columns, buffer 0
+    const float* const bS = biasS + sub * 4;
+    const float* const hW = headW + sub * 16;
+    constexpr int MAXP = 7;                             // column passes (num_units <= 104, checked at create time)
+    uint32_t phM = 0;                                   // parity bits of the two accumulator-full barriers
+    uint32_t hs = 0, ntile = 0;                         // steps / tiles processed so far by this CTA
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++ntile) {
+      const long long row0 = tile * TC_ROWS;
+      const int nrows = (int)((total_rows - row0 < (long long)TC_ROWS) ? (total_rows - row0) : (long long)TC_ROWS);
+      const int q0 = tile_q0(row0) * P.symL;
+      const bool live = row < nrows;
+      int rparent = 0;
+      // ---- symbol table of the tile (teacher forcing); the head warps must be done with the previous tile's
+      if (ntile > 0) mbar_wait(bar_tile, (ntile - 1) & 1);
+      {
+        Child ch;
+        ch.parent = 0; ch.ta = 0; ch.tb = -1; ch.coef = 0.f; ch.ka = ch.kb = 0;
+        if (live && MODE == MODE_CHILD) { ch = P.children[row0 + row]; rparent = ch.parent; }
+        if (live && MODE != MODE_SAMPLE) {
+          const long long src = (MODE == MODE_CHILD) ? (long long)ch.parent : row0 + row;
+          const int8_t* c = P.cfg_in + src * P.nsites;
+          for (int t = sub; t < P.Tsym; t += TC_SUB) {
+            int sy = c[metaS[t].z] & 1;
+            if (MODE == MODE_CHILD && (t == ch.ta || t == ch.tb)) sy ^= 1;
+            symS[t * TC_ROWS + row] = (uint8_t)sy;
+          }
+        } else {
+          for (int t = sub; t < P.Tsym; t += TC_SUB) symS[t * TC_ROWS + row] = 0;
+        }
+        quarter_barrier(quarter);
+      }
+      // One neighbour half of an A operand: this row's hidden state of step qn (zeros if absent) as FP16 pieces, from
+      // the ring image or, before the tile's first step under prefix reuse, from the parent's saved FP32 history.
+      auto load_half = [&](uint2 (&o)[MAXP], int qn) {
+        const bool have = (qn >= 0) && live;
+        const bool from_parent = have && (P.par_hist != nullptr) && (qn < q0);
+        const float* psrc = from_parent ? P.par_hist + ((size_t)qn * (size_t)P.par_rows + (size_t)rparent) * nhp + sub * 4 : nullptr;
+        const unsigned char* isrc = (have && !from_parent) ? ring_base + (ring_off0 + (uint32_t)(qn % P.ring_len) * img_bytes) : nullptr;
+#pragma unroll
+        for (int i = 0; i < MAXP; ++i) {
+          o[i] = make_uint2(0u, 0u);
+          if (i < NP && i * TC_JP + sub * 4 < nhp) {
+            if (isrc != nullptr) {
+              o[i] = __ldcg(reinterpret_cast<const uint2*>(isrc + (uint32_t)i * (2u * CORE)));
+            } else if (psrc != nullptr) {
+              const float4 v = __ldg(reinterpret_cast<const float4*>(psrc + i * TC_JP));
+              o[i].x = pack_f16x2(v.x, v.y); o[i].y = pack_f16x2(v.z, v.w);
             }
           }
-          b_prefetched = true;
         }
+      };
+      // TMEM lane == row, 32-bit column c of an operand holds halves (2c, 2c+1) of the K axis [h_h ; h_v].  All 32
+      // lanes execute the (warp-collective) tcgen05.st; rows past the end of the batch store zeros.
+      auto store_half = [&](const uint2 (&o)[MAXP], uint32_t a_thr, int half) {
         __syncwarp();
+        const uint32_t base = a_thr + (uint32_t)(half * hc) * 4u;
+#pragma unroll
+        for (int i = 0; i < MAXP; ++i)
+          if (i < NP && i * TC_JP + sub * 4 < nhp) tc_st2(base + (uint32_t)(i * (TC_JP / 2)), o[i]);   // warp-uniform guard
+      };
+      // the neighbour of step qq that is NOT the step right before it (that one is written as it is computed)
+      auto other_nbr = [&](int qq, int& carry_half) -> int {
+        const short4 sn = metaS[qq];
+        carry_half = (sn.x == qq - 1) ? 0 : 1;
+        return (carry_half == 0) ? sn.y : sn.x;
+      };
+
+      // operand of the tile's first step: both halves from the history (parent's saved history under prefix reuse;
+      // zeros for the very first site), then prefetch the older-neighbour half of the second step's operand
+      uint2 onext[MAXP];
+      {
+        const short4 s0 = metaS[q0];
+        const uint32_t a0 = aop0 + (uint32_t)(q0 & 1) * acols;
+        load_half(onext, s0.x);
+        store_half(onext, a0, 0);
+        load_half(onext, s0.y);
+        store_half(onext, a0, 1);
+        tc_wait_st();
+        tc_fence_before();
+        mbar_arrive(bar_A);
+        if (q0 + 1 < P.Q) { int ch_; load_half(onext, other_nbr(q0 + 1, ch_)); }
       }
 
-      if (is_epi) {
-        // ================= 4 threads per row (one per 4-unit slice of every pass) =================
-        // The operand of step q+1 is produced here: the half that is this step's own output is written slice by
-        // slice as the gates are evaluated; the other half (an older neighbour, or nothing) is fetched first, while
-        // the tensor core is still busy with this step.
+      for (int q = q0; q < P.Q; ++q, ++hs) {
+        // The operand of step q+1 is produced here: its older-neighbour half was prefetched at the end of the previous
+        // step and goes to TMEM first; the half that is this step's own output is written pass by pass.
+        const short4 sm = metaS[q];
+        const int nb0 = sm.x, nb1 = sm.y;      // history index == symbol index of the two neighbours (2D cells)
         TC_T0();
-        unsigned char* Anext = nullptr;
+        const bool has_next = (q + 1 < P.Q);
         int carry_half = 0;
-        if (q + 1 < P.Q) {
-          const short4 sn = metaS[q + 1];
-          if (sn.x >= 0 || sn.y >= 0) {
-            Anext = Abuf + ((q + 1) & 1) * L.a_bytes;
-            carry_half = (sn.x == q) ? 0 : 1;
-            build_half(Anext, 1 - carry_half, (carry_half == 0) ? sn.y : sn.x);
-          }
-        }
-        TC_ACC(10);
+        if (has_next) other_nbr(q + 1, carry_half);
+        const uint32_t a_next = aop0 + (uint32_t)((q + 1) & 1) * acols;
+        if (has_next) store_half(onext, a_next, 1 - carry_half);
+        TC_ACC(10); TC_EV(11);
+        // sampling: the neighbours' symbols are drawn by the head warps (completion number hs covers steps < hs)
+        if (MODE == MODE_SAMPLE && hs > 0) mbar_wait(bar_sym, (hs - 1) & 1);
         const float cl = (nb0 >= 0) ? (float)symS[nb0 * TC_ROWS + row] : 0.f;
         const float cu = (nb1 >= 0) ? (float)symS[nb1 * TC_ROWS + row] : 0.f;
         float lg[4] = {0.f, 0.f, 0.f, 0.f};
-        unsigned char* ring_img = ring + (size_t)(q % P.ring_len) * img_bytes + roff;
-        float4* const part = partS;
+        // 32-bit offsets from kernel-uniform bases (the ring and the saved tensors are far below 4 GB per launch... the
+        // saved tensors are not: they keep 64-bit pointers, advanced per pass)
+        uint32_t ring_off = ring_off0 + (uint32_t)(q % P.ring_len) * img_bytes;
+        const bool save = (MODE != MODE_CHILD) && live && (P.sv_hist != nullptr);
+        float* sv_h = save ? P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + sub * 4 : nullptr;
+        float4* sv_g = save ? P.sv_gates + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * P.Gp + sub * 4 : nullptr;
+        uint32_t a_carry = a_next + (uint32_t)(carry_half * hc) * 4u;
+        const float* bSp = bS;
+        const float* hWp = hW;
+#pragma unroll 1
         for (int p = 0; p < NP; ++p) {
-          const int s = p & 1;
-          uint32_t d[TC_NB][4];
-          if (variant != 3) {
-            mbar_wait(bar_mma + s, nMe[s] & 1); ++nMe[s];
-            TC_ACC(8);
+          const uint32_t s = (uint32_t)p & 1u;
+          const bool active = (p < NP - 1) || (sub < subs_last);     // warp-uniform: does this thread own real units?
+          mbar_wait_a(bar_mma_a + s * 8u, (phM >> s) & 1u); phM ^= 1u << s;
+          TC_ACC(8); TC_EV(12);
+          uint2 o = make_uint2(0u, 0u);
+          if (active) {
+            uint32_t d[TC_TPS];
             __syncwarp();
             tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(s * TC_N + sub * 4);
-#pragma unroll
-            for (int b = 0; b < TC_NB; ++b) tc_ld4(taddr + b * TC_JP, d[b]);
+            tc_ld28(acc0 + s * (uint32_t)TC_N, d);
             tc_wait_ld();
             tc_fence_before();
-            mbar_arrive(bar_free + s);
-          } else {
+            mbar_arrive_a(bar_free_a + s * 8u);
+            TC_EV(13);
+            const float4 bs = *reinterpret_cast<const float4*>(bSp);
+            const float4 bg = *reinterpret_cast<const float4*>(bSp + ldb);
+            const float bsv[4] = {bs.x, bs.y, bs.z, bs.w}, bgv[4] = {bg.x, bg.y, bg.z, bg.w};
+            float hnew[4];
 #pragma unroll
-            for (int b = 0; b < TC_NB; ++b)
-#pragma unroll
-              for (int e = 0; e < 4; ++e) d[b][e] = 0u;
-          }
-          const int j0 = p * TC_JP + sub * 4;
-          float hnew[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int j = j0 + e;
-            const float sv = __uint_as_float(d[0][e]) + cl * __uint_as_float(d[1][e]) + cu * __uint_as_float(d[2][e]) + biasS[j];
-            const float gv = __uint_as_float(d[3][e]) + cl * __uint_as_float(d[4][e]) + cu * __uint_as_float(d[5][e]) + biasS[ldb + j];
-            const float mv = __uint_as_float(d[6][e]);
-            const float u = fast_sigmoid(gv);
-            const float ht = fast_tanh(sv);
-            const float hv = (j < nh) ? (u * ht + (1.f - u) * mv) : 0.f;
-            hnew[e] = hv;
-            if (j < nh) {
-              const float4 w = *reinterpret_cast<const float4*>(headW + j * 4);
+            for (int e = 0; e < 4; ++e) {
+              // blocks: 0..2 = Wa, Wb, Wc of the candidate; 3..5 of the gate; 6 = Wmerge
+              const float sv = fmaf(cu, __uint_as_float(d[8 + e]), fmaf(cl, __uint_as_float(d[4 + e]), __uint_as_float(d[e]))) + bsv[e];
+              const float gv = fmaf(cu, __uint_as_float(d[20 + e]), fmaf(cl, __uint_as_float(d[16 + e]), __uint_as_float(d[12 + e]))) + bgv[e];
+              const float mv = __uint_as_float(d[24 + e]);
+              const float u = sigmoid_prescaled(gv);
+              const float ht = tanh_prescaled(sv);
+              // u ht + (1 - u) m.  Padding units (>= num_units) have zero weights and biases: u = 1/2, ht = m = 0 -> 0.
+              const float hv = fmaf(u, ht - mv, mv);
+              hnew[e] = hv;
+              const float4 w = *reinterpret_cast<const float4*>(hWp + e * 4);
               lg[0] = fmaf(hv, w.x, lg[0]); lg[1] = fmaf(hv, w.y, lg[1]); lg[2] = fmaf(hv, w.z, lg[2]); lg[3] = fmaf(hv, w.w, lg[3]);
-              if (live && P.sv_gates != nullptr && P.mode != MODE_CHILD)
-                P.sv_gates[((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * P.Gp + j] = make_float4(u, ht, mv, 0.f);
+              if (save && p * TC_JP + sub * 4 + e < nh) sv_g[e] = make_float4(u, ht, mv, 0.f);
             }
-          }
-          if (j0 < nhp) {
-            // 4 halves = half a k-core row: into the next operand's carry half and into the ring image
-            uint2 o;
-            o.x = pack_f16x2(hnew[0], hnew[1]); o.y = pack_f16x2(hnew[2], hnew[3]);
-            const uint32_t coff = (uint32_t)(j0 >> 3) * A_LBO + (uint32_t)(j0 & 7) * 2;
-            if (Anext != nullptr) *reinterpret_cast<uint2*>(Anext + (uint32_t)(carry_half * hc) * A_LBO + coff + roff) = o;
             if (live) {
-              *reinterpret_cast<uint2*>(ring_img + coff) = o;
-              if (P.sv_hist != nullptr && P.mode != MODE_CHILD)
-                *reinterpret_cast<float4*>(P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + j0) =
-                    make_float4(hnew[0], hnew[1], hnew[2], hnew[3]);
+              o.x = pack_f16x2(hnew[0], hnew[1]);
+              o.y = pack_f16x2(hnew[2], hnew[3]);
+              if (save) *reinterpret_cast<float4*>(sv_h) = make_float4(hnew[0], hnew[1], hnew[2], hnew[3]);
             }
+          } else {
+            mbar_arrive_a(bar_free_a + s * 8u);   // nothing to read: its columns of the narrow last pass are padding
           }
+          if (p * TC_JP + sub * 4 < nhp) {
+            // 4 halves = 2 TMEM columns of the next operand's carry half; the same 8 bytes go to the ring image
+            // (zeros for padding units and for rows past the end of the batch)
+            __syncwarp();
+            if (has_next) tc_st2(a_carry, o);
+            if (live) *reinterpret_cast<uint2*>(ring_base + ring_off) = o;
+          }
+          ring_off += 2u * CORE; a_carry += TC_JP / 2; bSp += TC_JP; hWp += TC_JP * 4; sv_h += TC_JP; sv_g += TC_JP;
         }
-        TC_ACC(9);
-        if (Anext != nullptr) {       // next step's operand complete: release the tensor core before the heads
-          fence_proxy_async_smem();
+        TC_ACC(9); TC_EV(14);
+        __syncwarp();
+        if (has_next) {               // next step's operand complete: release the tensor core
+          tc_wait_st();
+          tc_fence_before();
           mbar_arrive(bar_A);
         }
-        part[row * TC_SUB + sub] = make_float4(lg[0], lg[1], lg[2], lg[3]);
-        quarter_barrier(quarter);   // partial head sums and this step's ring rows are visible to the row's other threads
-
-        // ---- heads for this row (softmax, U(1) mask, draw / teacher forcing, log psi)
-        if (fin) {
-          float l4[4] = {0.f, 0.f, 0.f, 0.f};
+        TC_EV(15);
+        // prefetch the older-neighbour half of the operand after next (its latency hides behind the hand-over below
+        // and the wait for the next step's first accumulators)
+        if (q + 2 < P.Q) { int ch_; load_half(onext, other_nbr(q + 2, ch_)); }
+        // partial head sums of this step -> head warps (buffer hs & 1; wait until the step before last was consumed)
+        const uint32_t pb = hs & 1u;
+        mbar_wait(bar_pfree + pb, ((hs >> 1) & 1u) ^ 1u);
+        partS[(pb * TC_ROWS + row) * TC_SUB + sub] = make_float4(lg[0], lg[1], lg[2], lg[3]);
+        mbar_arrive(bar_part + pb);
+        TC_ACC(11); TC_EV(16);
+      }  // steps
+    }  // tiles
+    TC_TOTAL(12);
+  } else {
+    // ======================= head warps: two rows per thread =======================
+    // Softmax / U(1) mask / draw or teacher forcing / running log-probability and phase of the rows, off the
+    // tensor-core critical path: they consume the partial head sums one step behind the epilogue warps.  Transcendental
+    // math in FP32 (this regime's tolerance is 1e-3), running sums in FP64.
+    const int hrow = tid - 32 - TC_EPI_THREADS;          // rows hrow and hrow + 64
+    uint32_t hs = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const long long row0 = tile * TC_ROWS;
+      const int nrows = (int)((total_rows - row0 < (long long)TC_ROWS) ? (total_rows - row0) : (long long)TC_ROWS);
+      const int ts0 = tile_q0(row0), q0 = ts0 * P.symL;
+      double rlogp[2] = {0.0, 0.0}, rphase[2] = {0.0, 0.0};
+      int rnup[2] = {0, 0}, rparent[2] = {0, 0};
+      float rcoef[2] = {0.f, 0.f};
+      bool live[2];
 #pragma unroll
-          for (int k = 0; k < TC_SUB; ++k) {
-            const float4 v = part[row * TC_SUB + k];
-            l4[0] += v.x; l4[1] += v.y; l4[2] += v.z; l4[3] += v.w;
+      for (int k = 0; k < 2; ++k) {
+        const int row = hrow + k * TC_HEAD_THREADS;
+        live[k] = row < nrows;
+        if (live[k] && MODE == MODE_CHILD) { const Child ch = P.children[row0 + row]; rparent[k] = ch.parent; rcoef[k] = ch.coef; }
+      }
+      for (int q = q0; q < P.Q; ++q, ++hs) {
+        const int t = q;
+        const uint32_t pb = hs & 1u;
+        TC_T0();
+        mbar_wait_relaxed(bar_part + pb, (hs >> 1) & 1u);
+        TC_ACC(13); TC_EV(20);
+        float l4[2][4];
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          const int row = hrow + k * TC_HEAD_THREADS;
+          if (q == q0 && MODE == MODE_CHILD)            // the tile's symbol table is complete once its first step arrived
+            for (int tt = 0; tt < ts0; ++tt) rnup[k] += symS[tt * TC_ROWS + row];
+          l4[k][0] = headB[0]; l4[k][1] = headB[1]; l4[k][2] = headB[2]; l4[k][3] = headB[3];
+#pragma unroll
+          for (int i = 0; i < TC_SUB; ++i) {
+            const float4 v = partS[(pb * TC_ROWS + row) * TC_SUB + i];
+            l4[k][0] += v.x; l4[k][1] += v.y; l4[k][2] += v.z; l4[k][3] += v.w;
           }
-          float p0 = l4[0] + headB[0], p1 = l4[1] + headB[1];
+        }
+        mbar_arrive(bar_pfree + pb);
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          const int row = hrow + k * TC_HEAD_THREADS;
+          if (!live[k]) continue;
+          float p0 = l4[k][0], p1 = l4[k][1];
           const float mx = fmaxf(p0, p1);
-          p0 = expf(p0 - mx); p1 = expf(p1 - mx);
+          p0 = __expf(p0 - mx); p1 = __expf(p1 - mx);
           const float ssum = p0 + p1;
-          p0 /= ssum; p1 /= ssum;
+          p0 = __fdividef(p0, ssum); p1 = __fdividef(p1, ssum);
           if (P.u1) {
-            const int ndn = t - rnup;
+            const int ndn = t - rnup[k];
             p0 *= (P.cap_dn - ndn >= 0) ? 1.f : 0.f;
-            p1 *= (P.cap_up - rnup >= 0) ? 1.f : 0.f;
+            p1 *= (P.cap_up - rnup[k] >= 0) ? 1.f : 0.f;
             const float nrm = p0 + p1;
-            p0 /= nrm; p1 /= nrm;
+            p0 = __fdividef(p0, nrm); p1 = __fdividef(p1, nrm);
           }
           int sy;
-          if (P.mode == MODE_SAMPLE) {
+          if (MODE == MODE_SAMPLE) {
             const float u = (P.uniforms != nullptr)
                                 ? P.uniforms[(size_t)(row0 + row) * P.Tsym + t]
                                 : philox_uniform(P.seed, P.row_offset + (unsigned long long)(row0 + row), (uint32_t)t);
@@ -490,61 +693,71 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           } else {
             sy = symS[t * TC_ROWS + row];
           }
-          rlogp += log((double)(sy ? p1 : p0));
+          rlogp[k] += (double)__logf(sy ? p1 : p0);
           if (P.complex_head) {
-            const double xs = (double)((sy ? l4[3] : l4[2]) + (sy ? headB[3] : headB[2]));
-            rphase += 3.14159265358979323846 * (xs / (1.0 + fabs(xs)));
+            const float xs = sy ? l4[k][3] : l4[k][2];
+            rphase[k] += (double)(3.14159265358979323846f * __fdividef(xs, 1.0f + fabsf(xs)));
           }
-          rnup += sy;
-          if (P.sv_cum != nullptr && P.mode != MODE_CHILD)
-            P.sv_cum[(size_t)t * (size_t)P.sv_rows + (size_t)(row0 + row)] = make_double2(rlogp, rphase);
+          rnup[k] += sy;
+          if (P.sv_cum != nullptr && MODE != MODE_CHILD)
+            P.sv_cum[(size_t)t * (size_t)P.sv_rows + (size_t)(row0 + row)] = make_double2(rlogp[k], rphase[k]);
         }
-        quarter_barrier(quarter);   // the drawn symbol (sampling) is visible to the row's other threads; partS reusable
-        TC_ACC(11);
-      }
-    }  // steps
+        if (MODE == MODE_SAMPLE) mbar_arrive(bar_sym);
+        TC_ACC(14); TC_EV(21);
+      }  // steps
 
-    // ---- tile results
-    if (fin) {
-      if (P.mode == MODE_CHILD) {
-        double base_lp = P.par_logp[rparent], base_ph = (P.par_phase != nullptr) ? P.par_phase[rparent] : 0.0;
-        if (ts0 > 0 && P.par_cum != nullptr) {
-          const double2 c = P.par_cum[(size_t)(ts0 - 1) * (size_t)P.par_rows + rparent];
-          base_lp -= c.x;
-          base_ph -= c.y;
-        }
-        const double amp = exp(0.5 * (rlogp - base_lp)) * (double)rcoef;
-        if (P.complex_head) {
-          double sn, cs;
-          sincos(rphase - base_ph, &sn, &cs);
-          atomicAdd(P.eloc + 2 * (size_t)rparent, amp * cs);
-          atomicAdd(P.eloc + 2 * (size_t)rparent + 1, amp * sn);
+      // ---- tile results
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int row = hrow + k * TC_HEAD_THREADS;
+        if (!live[k]) continue;
+        if (MODE == MODE_CHILD) {
+          const int par = rparent[k];
+          double base_lp = P.par_logp[par], base_ph = (P.par_phase != nullptr) ? P.par_phase[par] : 0.0;
+          if (ts0 > 0 && P.par_cum != nullptr) {
+            const double2 c = P.par_cum[(size_t)(ts0 - 1) * (size_t)P.par_rows + par];
+            base_lp -= c.x;
+            base_ph -= c.y;
+          }
+          const double amp = exp(0.5 * (rlogp[k] - base_lp)) * (double)rcoef[k];
+          if (P.complex_head) {
+            double sn, cs;
+            sincos(rphase[k] - base_ph, &sn, &cs);
+            atomicAdd(P.eloc + 2 * (size_t)par, amp * cs);
+            atomicAdd(P.eloc + 2 * (size_t)par + 1, amp * sn);
+          } else {
+            atomicAdd(P.eloc + 2 * (size_t)par, amp);
+          }
         } else {
-          atomicAdd(P.eloc + 2 * (size_t)rparent, amp);
-        }
-      } else {
-        if (P.out_logp != nullptr) P.out_logp[row0 + row] = rlogp;
-        if (P.out_phase != nullptr) P.out_phase[row0 + row] = rphase;
-        if (P.mode == MODE_SAMPLE && P.cfg_out != nullptr) {
-          int8_t* c = P.cfg_out + (size_t)(row0 + row) * P.nsites;
-          for (int t = 0; t < P.Tsym; ++t) c[metaS[t].z] = (int8_t)symS[t * TC_ROWS + row];
+          if (P.out_logp != nullptr) P.out_logp[row0 + row] = rlogp[k];
+          if (P.out_phase != nullptr) P.out_phase[row0 + row] = rphase[k];
+          if (MODE == MODE_SAMPLE && P.cfg_out != nullptr) {
+            int8_t* c = P.cfg_out + (size_t)(row0 + row) * P.nsites;
+            for (int tt = 0; tt < P.Tsym; ++tt) c[metaS[tt].z] = (int8_t)symS[tt * TC_ROWS + row];
+          }
         }
       }
-    }
-    if (is_epi) quarter_barrier(quarter);   // symS is rewritten by the next tile's set-up
-  }  // tiles
-
-  if (do_prof) {
-    prof[tid == 0 ? 5 : 12] = tc_clock() - kstart;
-    for (int i = (tid == 0 ? 0 : 8); i < (tid == 0 ? 8 : 16); ++i) P.tc_prof[(size_t)blockIdx.x * 16 + i] = (unsigned long long)prof[i];
+      mbar_arrive(bar_tile);          // the epilogue warps may rewrite the symbol table
+    }  // tiles
   }
+
+#ifdef RNNWF_TC_PROF
+  if (do_prof) {
+    const int role = (tid == 0) ? 0 : (tid == 32 ? 1 : (tid == TC_THREADS - 32 ? 3 : 2));
+    for (int i = 0; i < 16; ++i) {
+      const int owner = (i == 4 || i == 6) ? 3 : (i < 8 ? 0 : (i < 13 ? 1 : 2));
+      if (owner == role) P.tc_prof[(size_t)blockIdx.x * 16 + i] = (unsigned long long)prof[i];
+    }
+  }
+#endif
   tc_fence_before();
   __syncthreads();
   if (warp == 0) { __syncwarp(); tc_dealloc(tmem_base, TC_TMEM_COLS); }
 }
 
 // ---- weight image for the tensor-core sweep --------------------------------------------------------------
-// [variant 3][pass NP][k-core kc][n-core 14][8 rows][8 halves]:  B[n][k] of the pass, K-major core matrices.
+// [variant 3][pass NP][k-core kc][n-core 14][8 rows][8 halves]:  B[n][k] of the pass, K-major core matrices
+// (n ordered thread-major, see below).
 // variants: 0 both neighbours, 1 horizontal only, 2 vertical only.
 __global__ void pack_tc_kernel(const float* __restrict__ W, const float* __restrict__ Wg, const float* __restrict__ Wmerge,
                                int nh, int nhp, int NP, __half* __restrict__ out) {
@@ -560,7 +773,9 @@ __global__ void pack_tc_kernel(const float* __restrict__ W, const float* __restr
     const int p = (int)(r % NP); r /= NP;
     const int variant = (int)r;
     const int n = ni * 8 + r8, k = ki * 8 + e;
-    const int blk = n / TC_JP, j = p * TC_JP + (n % TC_JP);
+    // MMA column n = sub * 28 + blk * 4 + e  <->  block blk of unit j = 16 p + 4 sub + e: the 28 accumulators an
+    // epilogue thread needs are contiguous TMEM columns
+    const int sub = n / TC_TPS, blk = (n % TC_TPS) / 4, j = p * TC_JP + sub * 4 + (n % 4);
     const int slot = k / nhp, unit = k - slot * nhp;
     float v = 0.f;
     if (unit < nh && j < nh) {
@@ -576,7 +791,7 @@ __global__ void pack_tc_kernel(const float* __restrict__ W, const float* __restr
         else v = (kind == 0) ? w[2] : (kind == 1 ? 0.f : (w[3] - w[2]));
       }
     }
-    out[idx] = __float2half_rn(v);
+    out[idx] = __float2half_rn(v * (blk < 3 ? TC_SCALE_CAND : (blk < 6 ? TC_SCALE_GATE : 1.0f)));
   }
 }
 
