@@ -410,6 +410,56 @@ __global__ void scan_kernel(const int* __restrict__ in, int* __restrict__ out, l
   for (long long i = lo; i < hi; ++i) { const int v = in[i]; out[i] = run; run += v; }
 }
 
+// three-launch exclusive scan for long inputs: per-block sums, scan of the (<= 1024) sums, per-block scan with offset
+constexpr int SCAN_TPB = 256;
+__global__ void __launch_bounds__(SCAN_TPB) scan_reduce_kernel(const int* __restrict__ in, int* __restrict__ bsum, long long n, long long chunk) {
+  __shared__ int red[SCAN_TPB / 32];
+  const long long lo = blockIdx.x * chunk, hi = (lo + chunk < n) ? lo + chunk : n;
+  int s = 0;
+  for (long long i = lo + threadIdx.x; i < hi; i += SCAN_TPB) s += in[i];
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int w = 0; w < SCAN_TPB / 32; ++w) t += red[w];
+    bsum[blockIdx.x] = t;
+  }
+}
+__global__ void __launch_bounds__(SCAN_TPB) scan_apply_kernel(const int* __restrict__ in, const int* __restrict__ boff, int* __restrict__ out,
+                                                             long long n, long long chunk) {
+  __shared__ int wsum[SCAN_TPB / 32];
+  __shared__ int carry_s;
+  const long long lo = blockIdx.x * chunk, hi = (lo + chunk < n) ? lo + chunk : n;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry_s = boff[blockIdx.x];
+  __syncthreads();
+  for (long long base = lo; base < hi; base += SCAN_TPB) {
+    const long long i = base + threadIdx.x;
+    const int v = (i < hi) ? in[i] : 0;
+    int x = v;                                   // inclusive scan inside the warp
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) wsum[w] = x;
+    __syncthreads();
+    int woff = 0;
+    for (int k = 0; k < w; ++k) woff += wsum[k];
+    const int carry = carry_s;
+    if (i < hi) out[i] = carry + woff + x - v;
+    __syncthreads();
+    if (threadIdx.x == SCAN_TPB - 1) carry_s = carry + woff + x;
+    __syncthreads();
+  }
+}
+// exclusive scan of n int32 counts on stream st; tmp holds 2048 ints
+void exclusive_scan(const int* in, int* out, long long n, int* tmp, cudaStream_t st) {
+  if (n <= 8192) { RNNWF_COUNT_LAUNCH(); scan_kernel<<<1, 1024, 0, st>>>(in, out, n); return; }
+  const int nblk = (int)std::min<long long>(1024, (n + 4095) / 4096);
+  const long long chunk = (n + nblk - 1) / nblk;
+  RNNWF_COUNT_LAUNCH(); scan_reduce_kernel<<<nblk, SCAN_TPB, 0, st>>>(in, tmp, n, chunk);
+  RNNWF_COUNT_LAUNCH(); scan_kernel<<<1, 1024, 0, st>>>(tmp, tmp + 1024, nblk);
+  RNNWF_COUNT_LAUNCH(); scan_apply_kernel<<<nblk, SCAN_TPB, 0, st>>>(in, tmp + 1024, out, n, chunk);
+}
+
 __global__ void count_children_kernel(const int* rows_dev, long long fixed, long long* out) {
   if (threadIdx.x == 0 && blockIdx.x == 0) *out = (rows_dev != nullptr) ? (long long)(*rows_dev) : fixed;
 }
@@ -644,7 +694,7 @@ ElocLayout eloc_layout(const rnnwf_model& m, int ham, long long rows) {
   const long long ncnt = variable ? (long long)m.Tsym * rows + 1 : 0;
   L.off_counts = o;   o += align256(ncnt * 4);
   L.off_offsets = o;  o += align256(ncnt * 4);
-  L.off_nchild = o;   o += 256;
+  L.off_nchild = o;   o += 2 * 1024 * 4;     // scratch of the multi-block scan
   L.max_children = max_children_per_sample(m, ham) * rows;
   L.off_children = o; o += align256(L.max_children * (long long)sizeof(Child));
   L.off_ring = o;     o += align256(ring_bytes(m, max_ctas(m), 128));
@@ -795,7 +845,7 @@ int rnnwf_local_energies(rnnwf_handle h, int hamiltonian, const double* ham, int
       RNNWF_COUNT_LAUNCH(); bond_diag_kernel<<<gsamp, tpb, 0, st>>>(samples_dev, rows, m.nsites, m.d_site_of_t, d_bonds, (int)bonds.size(), d_ham, (int)Bz.size(), eloc_dev);
       const long long ncnt = (long long)T * rows;
       RNNWF_COUNT_LAUNCH(); bond_count_kernel<<<std::min(8192, cdiv(ncnt + 1, tpb)), tpb, 0, st>>>(samples_dev, rows, m.nsites, T, m.d_site_of_t, d_bonds, d_bstart, d_counts);
-      RNNWF_COUNT_LAUNCH(); scan_kernel<<<1, 1024, 0, st>>>(d_counts, d_offsets, ncnt + 1);
+      exclusive_scan(d_counts, d_offsets, ncnt + 1, reinterpret_cast<int*>(ws + L.off_nchild), st);
       RNNWF_COUNT_LAUNCH(); bond_fill_kernel<<<std::min(8192, cdiv(ncnt, tpb)), tpb, 0, st>>>(samples_dev, rows, m.nsites, T, m.d_site_of_t, d_bonds, d_bstart, d_offsets, d_children);
       rows_dev = d_offsets + ncnt;
       nchild_fixed = L.max_children;

@@ -41,12 +41,29 @@ constexpr int TC_EPI_THREADS = TC_ROWS * TC_SUB;
 constexpr int TC_HEAD_THREADS = 64;     // two rows per head thread
 constexpr int TC_THREADS = 32 + TC_EPI_THREADS + TC_HEAD_THREADS + 32;   // warp 0: MMA, 1..16: epilogue, 17..18: heads, 19: loader
 constexpr int TC_TPS = TC_NB * 4;       // accumulator columns one epilogue thread owns per pass (28, contiguous)
+// one step's FP16 history image: [sub 4][quad 4][row 128][16 bytes]; quad i of thread (row, sub) holds its pieces 2i, 2i+1
+// (a warp's 16-byte accesses are contiguous: fully coalesced)
+constexpr uint32_t TC_RING_SLOT = TC_SUB * 4 * TC_ROWS * 16;
+constexpr uint32_t TC_RING_QUAD = TC_ROWS * 16;
+
+// Thread-major order of the K axis inside one neighbour half (nhp units): epilogue thread `sub` owns units
+// 16 p + 4 sub + e; its units occupy the contiguous positions tc_koff(sub) + 4 p + e.  Used identically by the operand
+// in TMEM, the ring image and the packed weights.
+__host__ __device__ inline int tc_kcnt(int nhp, int sub) { return (4 * sub < nhp) ? 4 * ((nhp - 4 * sub + 15) / 16) : 0; }
+__host__ __device__ inline int tc_koff(int nhp, int sub) { int o = 0; for (int s = 0; s < sub; ++s) o += tc_kcnt(nhp, s); return o; }
+// unit index of position kp (0 <= kp < nhp)
+__host__ __device__ inline int tc_kunit(int nhp, int kp) {
+  int sub = 0, off = 0;
+  while (sub < TC_SUB - 1 && kp >= off + tc_kcnt(nhp, sub)) { off += tc_kcnt(nhp, sub); ++sub; }
+  const int r = kp - off;
+  return 16 * (r / 4) + 4 * sub + (r % 4);
+}
 constexpr int TC_TMEM_COLS = 512;         // 2 x 112 accumulator columns + 2 x (nhp) A-operand columns
 constexpr int TC_STAGES = 4;              // weight stages in shared memory
 constexpr uint32_t TC_SPIN_LIMIT = 1u << 26;
 
 struct TcSmem {
-  int off_B, off_headw, off_headb, off_bias, off_part, off_meta, off_sym, off_bar, off_tmem, total;
+  int off_B, off_headw, off_headb, off_bias, off_part, off_meta, off_step, off_sym, off_bar, off_tmem, total;
   int b_bytes, kc;
   __host__ __device__ TcSmem(int nhp, int Tsym, int Q = 0) {
     kc = 2 * (nhp / 8);                       // 16-byte k-cores of the concatenated [h_h ; h_v] operand
@@ -58,6 +75,7 @@ struct TcSmem {
     off_bias = o;  o += ((2 * (nhp + TC_JP) * 4) + 15) & ~15;
     off_part = o;  o += 2 * TC_ROWS * TC_SUB * 16;   // partial head sums [2][128][TC_SUB] float4
     off_meta = o;  o += ((Q > 0 ? Q : Tsym) * 8 + 15) & ~15;   // per step: nbr0, nbr1, site, pad (int16 x 4)
+    off_step = o;  o += (Q > 0 ? Q : Tsym) * 16;                // per step: neighbours, carry half, ring slots (int4)
     off_bar = o;   o += 256;
     off_tmem = o;  o += 16;
     off_sym = o;   o += ((Tsym * TC_ROWS) + 15) & ~15;
@@ -181,6 +199,10 @@ __device__ __forceinline__ void tc_st4(uint32_t taddr, const uint4& v) {
 __device__ __forceinline__ void tc_st2(uint32_t taddr, const uint2& v) {
   asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(taddr), "r"(v.x), "r"(v.y) : "memory");
 }
+__device__ __forceinline__ void tc_st8(uint32_t taddr, uint32_t a, uint32_t b, uint32_t c, uint32_t d, uint32_t e, uint32_t f, uint32_t g, uint32_t h) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+               ::"r"(taddr), "r"(a), "r"(b), "r"(c), "r"(d), "r"(e), "r"(f), "r"(g), "r"(h) : "memory");
+}
 __device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&d)[16]) {
   asm volatile(
@@ -265,6 +287,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
   float* const biasS = reinterpret_cast<float*>(smem + L.off_bias);       // [2][nhp + 16]: b, bg (zero past num_units)
   float4* const partS = reinterpret_cast<float4*>(smem + L.off_part);     // [2][128][TC_SUB] partial head sums
   short4* const metaS = reinterpret_cast<short4*>(smem + L.off_meta);     // per step: (nbr0, nbr1, site, -)
+  int4* const stepT = reinterpret_cast<int4*>(smem + L.off_step);         // per step: see the set-up loop below
   uint8_t* const symS = smem + L.off_sym;                                 // [Tsym][128]
   uint64_t* const bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
   uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(smem + L.off_tmem);
@@ -313,6 +336,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
   for (int i = tid; i < P.Q; i += TC_THREADS) {
     const StepMeta* m = P.steps + i;
     metaS[i] = make_short4(m->nbr[0], m->nbr[1], m->site, 0);
+    // operand of step i: the half that holds the step right before it ("carry", written as that step is computed) and
+    // the other neighbour (copied from the ring); ring slots as byte offsets
+    const int nb0 = m->nbr[0], nb1 = m->nbr[1];
+    const int carry = (nb0 == i - 1) ? 0 : 1;
+    const int other = (carry == 0) ? nb1 : nb0;
+    stepT[i] = make_int4((nb0 & 0xffff) | (nb1 << 16), (other & 0xffff) | (carry << 16),
+                         (int)((uint32_t)(i % P.ring_len) * TC_RING_SLOT), other >= 0 ? (int)((uint32_t)(other % P.ring_len) * TC_RING_SLOT) : 0);
   }
   tc_fence_before();
   __syncthreads();
@@ -428,25 +458,25 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
     // ======================= epilogue warps: 4 threads per row =======================
     // Thread (row, sub) owns units 16 p + 4 sub .. + 3 of every column pass p: it reads those accumulators (28
     // contiguous TMEM columns), applies the gates, and writes the 4 new hidden values (FP16) to the next operand in
-    // TMEM and to its private pieces of the history ring (only this thread ever reads those 8 bytes back, so the ring
-    // needs no barrier).  The partial head sums go to the head warps through shared memory; no block-wide barrier in
-    // the step loop.
+    // TMEM and to the history ring.  The K axis of the operand is ordered thread-major (tc_kpos), so everything a
+    // thread owns of a neighbour half is one contiguous run of TMEM columns and one 64-byte chunk of the ring image:
+    // only this thread ever reads those bytes back, so the ring needs no barrier.  The partial head sums go to the head
+    // warps through shared memory; no block-wide barrier in the step loop.
     const int quarter = warp & 3;                       // TMEM lane quarter this warp may access
     const int sub = (warp - 1) >> 2;                    // which 4 of the 16 units of a pass this thread handles
     const int row = (quarter << 5) + lane;              // tile row == TMEM lane
     const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
-    constexpr uint32_t CORE = (TC_ROWS / 8) * 128;      // bytes of one k-core (8 halves x 128 rows) in the ring image
-    const uint32_t img_bytes = (uint32_t)hc * CORE;
-    // this thread's 8-byte piece of pass p inside a ring image: piece0 + p * 2 CORE
-    const uint32_t piece0 = (uint32_t)(row >> 3) * 128 + (uint32_t)(row & 7) * 16 + (uint32_t)(sub >> 1) * CORE + (uint32_t)(sub & 1) * 8u;
+    const int np_own = tc_kcnt(nhp, sub) / 4;           // column passes in which this thread owns units (7 or 6 at 104)
+    const uint32_t hcols = (uint32_t)nhp / 2;           // TMEM columns of one neighbour half
     unsigned char* const ring_base = reinterpret_cast<unsigned char*>(P.ring);
-    const uint32_t ring_off0 = (uint32_t)blockIdx.x * (uint32_t)P.ring_len * img_bytes + piece0;   // (the whole ring is < 4 GB)
+    // this thread's first quad inside a step's ring image   (the whole ring is < 4 GB: 32-bit offsets)
+    const uint32_t ring_off0 = (uint32_t)blockIdx.x * (uint32_t)P.ring_len * TC_RING_SLOT + (uint32_t)sub * (4u * TC_RING_QUAD) + (uint32_t)row * 16u;
     const uint32_t bar_mma_a = smem_u32(bar_mma), bar_free_a = smem_u32(bar_free);
-    const uint32_t acc0 = tmem_base + lane_base + (uint32_t)(sub * TC_TPS);      // this thread's accumulators, buffer 0
-    const uint32_t aop0 = tmem_A0 + lane_base + (uint32_t)(sub * 2);             // this thread's operand columns, buffer 0
+    const uint32_t bar_part_a = smem_u32(bar_part), bar_pfree_a = smem_u32(bar_pfree);
+    const uint32_t acc0 = tmem_base + lane_base + (uint32_t)(sub * TC_TPS);               // this thread's accumulators, buffer 0
+    const uint32_t aop0 = tmem_A0 + lane_base + (uint32_t)tc_koff(nhp, sub) / 2;          // its operand columns, buffer 0, half 0
     const float* const bS = biasS + sub * 4;
     const float* const hW = headW + sub * 16;
-    constexpr int MAXP = 7;                             // column passes (num_units <= 104, checked at create time)
     uint32_t phM = 0;                                   // parity bits of the two accumulator-full barriers
     uint32_t hs = 0, ntile = 0;                         // steps / tiles processed so far by this CTA
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++ntile) {
@@ -474,82 +504,90 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         }
         quarter_barrier(quarter);
       }
-      // One neighbour half of an A operand: this row's hidden state of step qn (zeros if absent) as FP16 pieces, from
-      // the ring image or, before the tile's first step under prefix reuse, from the parent's saved FP32 history.
-      auto load_half = [&](uint2 (&o)[MAXP], int qn) {
-        const bool have = (qn >= 0) && live;
-        const bool from_parent = have && (P.par_hist != nullptr) && (qn < q0);
-        const float* psrc = from_parent ? P.par_hist + ((size_t)qn * (size_t)P.par_rows + (size_t)rparent) * nhp + sub * 4 : nullptr;
-        const unsigned char* isrc = (have && !from_parent) ? ring_base + (ring_off0 + (uint32_t)(qn % P.ring_len) * img_bytes) : nullptr;
+      // Everything this thread owns of one neighbour half: the hidden state of step `other` (zeros if absent) as 14 (12)
+      // packed FP16 words, from the ring image or, before the tile's first step under prefix reuse, from the parent's
+      // saved FP32 history.  All branches are warp-uniform.
+      auto load_half = [&](uint32_t (&w)[16], int other, uint32_t other_slot) {
+        if (other < 0) {
 #pragma unroll
-        for (int i = 0; i < MAXP; ++i) {
-          o[i] = make_uint2(0u, 0u);
-          if (i < NP && i * TC_JP + sub * 4 < nhp) {
-            if (isrc != nullptr) {
-              o[i] = __ldcg(reinterpret_cast<const uint2*>(isrc + (uint32_t)i * (2u * CORE)));
-            } else if (psrc != nullptr) {
+          for (int i = 0; i < 16; ++i) w[i] = 0u;
+        } else if (other >= q0 || P.par_hist == nullptr) {
+          const unsigned char* src = ring_base + (ring_off0 + other_slot);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const uint4 v = __ldcg(reinterpret_cast<const uint4*>(src + i * TC_RING_QUAD));
+            w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
+          }
+        } else {
+          const float* psrc = P.par_hist + ((size_t)other * (size_t)P.par_rows + (size_t)rparent) * nhp + sub * 4;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            w[2 * i] = 0u; w[2 * i + 1] = 0u;
+            if (i < np_own) {
               const float4 v = __ldg(reinterpret_cast<const float4*>(psrc + i * TC_JP));
-              o[i].x = pack_f16x2(v.x, v.y); o[i].y = pack_f16x2(v.z, v.w);
+              w[2 * i] = pack_f16x2(v.x, v.y); w[2 * i + 1] = pack_f16x2(v.z, v.w);
             }
           }
         }
       };
-      // TMEM lane == row, 32-bit column c of an operand holds halves (2c, 2c+1) of the K axis [h_h ; h_v].  All 32
-      // lanes execute the (warp-collective) tcgen05.st; rows past the end of the batch store zeros.
-      auto store_half = [&](const uint2 (&o)[MAXP], uint32_t a_thr, int half) {
+      // TMEM lane == row; the thread's run of 2 np_own columns inside the half that starts at column a_half.  All 32
+      // lanes execute the (warp-collective) tcgen05.st.
+      auto store_half = [&](const uint32_t (&w)[16], uint32_t a_half) {
         __syncwarp();
-        const uint32_t base = a_thr + (uint32_t)(half * hc) * 4u;
-#pragma unroll
-        for (int i = 0; i < MAXP; ++i)
-          if (i < NP && i * TC_JP + sub * 4 < nhp) tc_st2(base + (uint32_t)(i * (TC_JP / 2)), o[i]);   // warp-uniform guard
-      };
-      // the neighbour of step qq that is NOT the step right before it (that one is written as it is computed)
-      auto other_nbr = [&](int qq, int& carry_half) -> int {
-        const short4 sn = metaS[qq];
-        carry_half = (sn.x == qq - 1) ? 0 : 1;
-        return (carry_half == 0) ? sn.y : sn.x;
+        // 2 np_own columns, decomposed into x8 / x4 / x2 stores (register indices must be static)
+        if (np_own & 4) tc_st8(a_half, w[0], w[1], w[2], w[3], w[4], w[5], w[6], w[7]);
+        if (np_own & 2) {
+          if (np_own & 4) tc_st4(a_half + 8u, make_uint4(w[8], w[9], w[10], w[11]));
+          else tc_st4(a_half, make_uint4(w[0], w[1], w[2], w[3]));
+        }
+        if (np_own & 1) {
+          switch (np_own & 6) {
+            case 0: tc_st2(a_half, make_uint2(w[0], w[1])); break;
+            case 2: tc_st2(a_half + 4u, make_uint2(w[4], w[5])); break;
+            case 4: tc_st2(a_half + 8u, make_uint2(w[8], w[9])); break;
+            default: tc_st2(a_half + 12u, make_uint2(w[12], w[13])); break;
+          }
+        }
       };
 
       // operand of the tile's first step: both halves from the history (parent's saved history under prefix reuse;
       // zeros for the very first site), then prefetch the older-neighbour half of the second step's operand
-      uint2 onext[MAXP];
+      uint32_t onext[16];
       {
-        const short4 s0 = metaS[q0];
+        const int4 e0 = stepT[q0];
+        const int nb0 = (int)(short)(e0.x & 0xffff), nb1 = (int)(short)((unsigned)e0.x >> 16);
         const uint32_t a0 = aop0 + (uint32_t)(q0 & 1) * acols;
-        load_half(onext, s0.x);
-        store_half(onext, a0, 0);
-        load_half(onext, s0.y);
-        store_half(onext, a0, 1);
+        load_half(onext, nb0, nb0 >= 0 ? (uint32_t)(nb0 % P.ring_len) * TC_RING_SLOT : 0u);
+        store_half(onext, a0);
+        load_half(onext, nb1, nb1 >= 0 ? (uint32_t)(nb1 % P.ring_len) * TC_RING_SLOT : 0u);
+        store_half(onext, a0 + hcols);
         tc_wait_st();
         tc_fence_before();
         mbar_arrive(bar_A);
-        if (q0 + 1 < P.Q) { int ch_; load_half(onext, other_nbr(q0 + 1, ch_)); }
+        if (q0 + 1 < P.Q) { const int4 e1 = stepT[q0 + 1]; load_half(onext, (int)(short)(e1.y & 0xffff), (uint32_t)e1.w); }
       }
 
       for (int q = q0; q < P.Q; ++q, ++hs) {
         // The operand of step q+1 is produced here: its older-neighbour half was prefetched at the end of the previous
         // step and goes to TMEM first; the half that is this step's own output is written pass by pass.
-        const short4 sm = metaS[q];
-        const int nb0 = sm.x, nb1 = sm.y;      // history index == symbol index of the two neighbours (2D cells)
+        const int4 eq = stepT[q];
+        const int nb0 = (int)(short)(eq.x & 0xffff), nb1 = (int)(short)((unsigned)eq.x >> 16);
         TC_T0();
         const bool has_next = (q + 1 < P.Q);
-        int carry_half = 0;
-        if (has_next) other_nbr(q + 1, carry_half);
+        const int carry_half = has_next ? (stepT[q + 1].y >> 16) : 0;
         const uint32_t a_next = aop0 + (uint32_t)((q + 1) & 1) * acols;
-        if (has_next) store_half(onext, a_next, 1 - carry_half);
+        if (has_next) store_half(onext, a_next + (uint32_t)(1 - carry_half) * hcols);
         TC_ACC(10); TC_EV(11);
         // sampling: the neighbours' symbols are drawn by the head warps (completion number hs covers steps < hs)
         if (MODE == MODE_SAMPLE && hs > 0) mbar_wait(bar_sym, (hs - 1) & 1);
         const float cl = (nb0 >= 0) ? (float)symS[nb0 * TC_ROWS + row] : 0.f;
         const float cu = (nb1 >= 0) ? (float)symS[nb1 * TC_ROWS + row] : 0.f;
         float lg[4] = {0.f, 0.f, 0.f, 0.f};
-        // 32-bit offsets from kernel-uniform bases (the ring and the saved tensors are far below 4 GB per launch... the
-        // saved tensors are not: they keep 64-bit pointers, advanced per pass)
-        uint32_t ring_off = ring_off0 + (uint32_t)(q % P.ring_len) * img_bytes;
+        unsigned char* const ring_w = ring_base + (ring_off0 + (uint32_t)eq.z);  // this thread's first quad of this step's image
         const bool save = (MODE != MODE_CHILD) && live && (P.sv_hist != nullptr);
         float* sv_h = save ? P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + sub * 4 : nullptr;
         float4* sv_g = save ? P.sv_gates + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * P.Gp + sub * 4 : nullptr;
-        uint32_t a_carry = a_next + (uint32_t)(carry_half * hc) * 4u;
+        uint32_t a_carry = a_next + (uint32_t)carry_half * hcols;
         const float* bSp = bS;
         const float* hWp = hW;
 #pragma unroll 1
@@ -595,16 +633,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           } else {
             mbar_arrive_a(bar_free_a + s * 8u);   // nothing to read: its columns of the narrow last pass are padding
           }
-          if (p * TC_JP + sub * 4 < nhp) {
+          if (p < np_own) {
             // 4 halves = 2 TMEM columns of the next operand's carry half; the same 8 bytes go to the ring image
             // (zeros for padding units and for rows past the end of the batch)
             __syncwarp();
             if (has_next) tc_st2(a_carry, o);
-            if (live) *reinterpret_cast<uint2*>(ring_base + ring_off) = o;
+            *reinterpret_cast<uint2*>(ring_w + (uint32_t)(p >> 1) * TC_RING_QUAD + (uint32_t)(p & 1) * 8u) = o;
           }
-          ring_off += 2u * CORE; a_carry += TC_JP / 2; bSp += TC_JP; hWp += TC_JP * 4; sv_h += TC_JP; sv_g += TC_JP;
+          a_carry += 2u; bSp += TC_JP; hWp += TC_JP * 4; sv_h += TC_JP; sv_g += TC_JP;
+          TC_ACC(9);
         }
-        TC_ACC(9); TC_EV(14);
+        TC_EV(14);
         __syncwarp();
         if (has_next) {               // next step's operand complete: release the tensor core
           tc_wait_st();
@@ -612,14 +651,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           mbar_arrive(bar_A);
         }
         TC_EV(15);
-        // prefetch the older-neighbour half of the operand after next (its latency hides behind the hand-over below
-        // and the wait for the next step's first accumulators)
-        if (q + 2 < P.Q) { int ch_; load_half(onext, other_nbr(q + 2, ch_)); }
         // partial head sums of this step -> head warps (buffer hs & 1; wait until the step before last was consumed)
         const uint32_t pb = hs & 1u;
-        mbar_wait(bar_pfree + pb, ((hs >> 1) & 1u) ^ 1u);
+        mbar_wait_a(bar_pfree_a + pb * 8u, ((hs >> 1) & 1u) ^ 1u);
         partS[(pb * TC_ROWS + row) * TC_SUB + sub] = make_float4(lg[0], lg[1], lg[2], lg[3]);
-        mbar_arrive(bar_part + pb);
+        mbar_arrive_a(bar_part_a + pb * 8u);
+        // prefetch the older-neighbour half of the operand after next (its latency hides behind the wait for the next
+        // step's first accumulators)
+        if (q + 2 < P.Q) { const int4 e2 = stepT[q + 2]; load_half(onext, (int)(short)(e2.y & 0xffff), (uint32_t)e2.w); }
         TC_ACC(11); TC_EV(16);
       }  // steps
     }  // tiles
@@ -776,7 +815,7 @@ __global__ void pack_tc_kernel(const float* __restrict__ W, const float* __restr
     // MMA column n = sub * 28 + blk * 4 + e  <->  block blk of unit j = 16 p + 4 sub + e: the 28 accumulators an
     // epilogue thread needs are contiguous TMEM columns
     const int sub = n / TC_TPS, blk = (n % TC_TPS) / 4, j = p * TC_JP + sub * 4 + (n % 4);
-    const int slot = k / nhp, unit = k - slot * nhp;
+    const int slot = k / nhp, unit = tc_kunit(nhp, k - slot * nhp);   // K axis in thread-major order
     float v = 0.f;
     if (unit < nh && j < nh) {
       const int i = slot * nh + unit;
