@@ -16,6 +16,7 @@
 #include <string>
 
 #include "model.h"
+#include "bwd_tc.cuh"
 
 namespace rnnwf {
 
@@ -420,8 +421,11 @@ __global__ void build_onehot_kernel(const BwdStep S, int nslots, float* __restri
 inline cudaError_t backward_init() {
   return cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GT_STAGES * 2 * GT_TILE_BYTES);
 }
+inline cudaError_t backward_init_tc(const rnnwf_model_impl& m) {
+  return cudaFuncSetAttribute(bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BtSmem(m.nhp, m.Tsym, m.Q).total);
+}
 
-struct BwdLayout { long long off_dh, off_dp, off_Z, off_dZ, off_hc, off_dhc, off_dlog, off_X, off_wstack, total; long long dpw; int Kz; bool batched; };
+struct BwdLayout { long long off_dh, off_dp, off_Z, off_dZ, off_hc, off_dhc, off_dlog, off_X, off_wstack, off_wimg, total; long long dpw; int Kz; bool batched; };
 
 inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   auto al = [](long long x) { return (x + 255) & ~255LL; };
@@ -435,7 +439,7 @@ inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   L.batched = (m.cell == CELL_TENS2D || m.cell == CELL_TENSGRU2D);
   const long long nb = L.batched ? m.Q : 1;
   long long o = 0;
-  L.off_dh = o;   o += al((long long)m.Q * R * m.nhp * 4);
+  L.off_dh = o;   o += al(std::max((long long)m.Q * R * m.nhp * 4, m.tc_enabled ? tc_dh_bytes(m.Q, R, m.tc_np) : 0LL));
   L.off_dp = o;   o += al(nb * R * L.dpw * 4);
   L.off_Z = o;    o += al(nb * R * (long long)L.Kz * 4);
   L.off_dZ = o;   o += al(R * (long long)L.Kz * 4);   // tensorized cells: the per-step linearised operand P [R][7nh] lives here
@@ -444,6 +448,7 @@ inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   L.off_dlog = o; o += al(nb * R * 8 * 4);
   L.off_X = o;    o += al(R * 8 * 4);
   L.off_wstack = o; o += al(L.batched ? 3LL * 2 * nh * 7 * nh * 4 : 0);
+  L.off_wimg = o;   o += al(m.tc_enabled ? 3LL * m.tc_np * BtSmem(m.nhp, m.Tsym, m.Q).b_bytes : 0);   // Wstack^T chunks of the reverse sweep
   L.total = o;
   return L;
 }
@@ -516,7 +521,7 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
                                                      gru0 ? params + m.tensor("Wmerge")->offset : nullptr, nh, gru0 ? 1 : 0, wstack);
   }
 
-  cudaError_t e = cudaMemsetAsync(dh, 0, (size_t)m.Q * R * nhp * 4, st);
+  cudaError_t e = (m.tc_enabled && m.cell == CELL_TENSGRU2D) ? cudaSuccess : cudaMemsetAsync(dh, 0, (size_t)m.Q * R * nhp * 4, st);
   if (e == cudaSuccess) e = cudaMemsetAsync(grad, 0, (size_t)m.num_params * 4, st);
   if (e != cudaSuccess) { err = std::string("rnnwf_backward memset: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
 
@@ -527,7 +532,44 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
   auto hrow = [&](int q) { return hist + (long long)q * R * nhp; };
   auto dhrow = [&](int q) { return dh + (long long)q * R * nhp; };
 
-  for (int q = m.Q - 1; q >= 0; --q) {
+  // Reduced-precision regime, tensorized GRU: the whole recurrence (heads' push into d h, gate derivatives, input
+  // gradients, scatter to the neighbours) is one persistent tensor-core kernel (bwd_tc.cuh) after one batched
+  // d(logits) kernel; only the operands of the batched weight-gradient GEMMs below are still built per site.
+  const bool tc_sweep = m.tc_enabled && m.cell == CELL_TENSGRU2D;
+  if (tc_sweep) {
+    e = cudaMemsetAsync(dh, 0, (size_t)tc_dh_bytes(m.Q, R, m.tc_np), st);
+    if (e != cudaSuccess) { err = std::string("rnnwf_backward memset: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
+    float* wimg = reinterpret_cast<float*>(ws + L.off_wimg);
+    RNNWF_COUNT_LAUNCH(); pack_bwd_tc_kernel<<<512, 256, 0, st>>>(P("W"), P("Wg"), P("Wmerge"), nh, nhp, m.tc_np, wimg);
+    HeadAllParams H;
+    H.Q = m.Q; H.nh = nh; H.nhp = nhp; H.ND = m.ND; H.D = m.D; H.nsites = m.nsites; H.complex_head = m.complex_head;
+    H.u1 = m.u1; H.cap_up = m.cap_up; H.cap_dn = m.cap_dn; H.R = R; H.hist = hist; H.cfg = cfg; H.site_of_t = m.d_site_of_t;
+    H.head_w = m.d_head_w; H.head_b = m.d_head_b; H.seed_logp = seed_logp; H.seed_phase = seed_phase; H.dlog = dlog_base;
+    RNNWF_COUNT_LAUNCH(); head_bwd_all_kernel<<<(unsigned)(((long long)m.Q * R + 7) / 8), 256, 0, st>>>(H);
+    BwdTcParams B;
+    B.steps = m.d_steps; B.Q = m.Q; B.Tsym = m.Tsym; B.nsites = m.nsites; B.nh = nh; B.nhp = nhp; B.np = m.tc_np; B.ND = m.ND;
+    B.rows = R; B.cfg = cfg; B.gates = gates; B.dlog = dlog_base; B.dh = reinterpret_cast<float4*>(dh);
+    B.dp0 = dp; B.dp1 = dp + (long long)m.Q * R * nh; B.dp2 = dp + 2LL * m.Q * R * nh;
+    B.wimg = wimg; B.head_w = m.d_head_w;
+    const long long tiles = (R + TC_ROWS - 1) / TC_ROWS;
+    const BtSmem bs(nhp, m.Tsym, m.Q);
+    RNNWF_COUNT_LAUNCH(); bwd_tc_kernel<<<(unsigned)std::min<long long>(tiles, m.num_sms), BT_THREADS, bs.total, st>>>(B);
+    for (int q = m.Q - 1; q >= 1; --q) {     // operands T = hc (x) x and hc of the batched dW / dWmerge GEMMs
+      const StepMeta& sm = m.steps[q];
+      BwdStep S;
+      std::memset(&S, 0, sizeof(S));
+      S.q = q; S.t = sm.sym; S.cell = m.cell; S.nh = nh; S.nhp = nhp; S.Gp = m.Gp; S.D = m.D; S.ND = m.ND;
+      S.bits = m.bits; S.nsites = m.nsites; S.Tsym = m.Tsym; S.L = m.symL; S.R = R; S.cfg = cfg; S.hist = hist;
+      for (int k = 0; k < MAX_SLOTS; ++k) {
+        S.nbr[k] = sm.nbr[k];
+        S.nsym_site[k] = (sm.nsym[k] >= 0) ? m.site_of_t[sm.nsym[k]] : -1;
+      }
+      S.sym_site = sm.site;
+      RNNWF_COUNT_LAUNCH(); build_tens_kernel<<<nblk(R * 2 * nh), tpb, 0, st>>>(S, Z_base + (long long)q * R * L.Kz, hc_base + (long long)q * R * 2 * nh);
+    }
+  }
+
+  for (int q = tc_sweep ? -1 : m.Q - 1; q >= 0; --q) {
     const StepMeta& sm = m.steps[q];
     BwdStep S;
     std::memset(&S, 0, sizeof(S));

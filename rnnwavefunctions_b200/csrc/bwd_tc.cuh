@@ -1,0 +1,404 @@
+// Tensor-core reverse sweep of the tensorized 2D GRU (reduced-precision regime): the recurrence part of the backward
+// pass of  sum_b seed_b * log psi(sigma_b)  as ONE persistent kernel instead of ~5 launches per lattice site.
+//
+// Per 128-row tile the sites are walked backwards.  For site q the tile's threads turn d h_q (accumulated from the
+// sites that consumed h_q, plus the heads' contribution) into the pre-activation gradients (ds, dg, dm) with the gates
+// saved by the sampling sweep, and form the linearised operand
+//        P = [ds, cl ds, cu ds, dg, cl dg, cu dg, dm]            (cl, cu: the neighbours' spins, 0 if absent)
+// so that  d[h_h ; h_v] = P * Wstack^T  with the same pre-summed weight blocks as the forward sweep (sweep_tc.cuh):
+// one [128 x 784] x [784 x 208] contraction per site on the tensor cores (tcgen05.mma kind::tf32 -- gradients need the
+// FP32 exponent range -- A operand written straight into TMEM by the threads that computed it, weights streamed from
+// L2 in 7 chunks of 16 units, FP32 accumulator [128 x 208] in TMEM).  The K axis of a chunk is ordered exactly like the
+// forward sweep's accumulator columns (thread-major: sub * 28 + block * 4 + e), the N axis like its operand (tc_kunit),
+// so every thread only ever touches its own columns and its own pieces of d h: no atomics, no barriers on d h.
+//
+// Warp roles: warp 0 MMA issue, warps 1..16 four threads per row (thread (row, sub) owns units 16 p + 4 sub + e),
+// warp 17 weight loader.  Everything is synchronised by mbarriers; waits are bounded and trap instead of hanging.
+//
+// Outputs: ds, dg, dm of every site ([Q][R][nh] each, for the batched weight-gradient GEMMs) -- the parameter
+// gradients themselves are long-K GEMMs over these (backward.cuh).
+// Reference behaviour: tf.gradients of the cost in 2DHeisenberg/Training2DRNN_Heisenberg.py through
+// MDTensorizedGRUcell.py:49-61 / MDComplexRNN.py:69-286 (same math as cell_bwd_tens_kernel + gemm + scatter_hc_kernel).
+#pragma once
+#include "sweep_tc.cuh"
+
+namespace rnnwf {
+
+constexpr int BT_K = TC_TPS * TC_SUB;                 // 112 K elements per chunk (16 units x 7 blocks)
+constexpr int BT_THREADS = 32 + TC_EPI_THREADS + 32;  // warp 0: MMA, warps 1..16: rows, warp 17: loader
+constexpr int BT_NK8 = BT_K / 8;                      // tf32 MMAs (K = 8) per chunk
+
+struct BtSmem {
+  int off_B, off_headw, off_step, off_sym, off_bar, off_tmem, total;
+  int b_bytes, ncores;
+  __host__ __device__ BtSmem(int nhp, int Tsym, int Q) {
+    ncores = 2 * nhp / 8;                             // 8-row groups of the N axis [d h_h ; d h_v]
+    b_bytes = (BT_K / 4) * ncores * 128;              // one chunk of Wstack^T: [k-core 28][n-core][8 rows][4 tf32]
+    int o = 0;
+    off_B = o;     o += 2 * b_bytes;
+    off_headw = o; o += (nhp + TC_JP) * 16;           // head weights [unit][4], zero rows past num_units
+    off_step = o;  o += Q * 8;                        // per site: neighbours (int16 x 2), flags
+    off_bar = o;   o += 128;
+    off_tmem = o;  o += 16;
+    off_sym = o;   o += ((Tsym * TC_ROWS) + 15) & ~15;
+    total = o;
+  }
+};
+
+struct BwdTcParams {
+  const StepMeta* steps;
+  int Q, Tsym, nsites, nh, nhp, np, ND;
+  long long rows;
+  const int8_t* cfg;            // [rows][nsites]
+  const float4* gates;          // saved by the sampling sweep, tile-blocked (tc_gate_index)
+  const float* dlog;            // [Q][rows][ND]  d(logits) of every site (head_bwd_all_kernel)
+  float4* dh;                   // [Q][tiles][sub 4][pass np][row 128] float4, zero-initialised
+  float* dp0; float* dp1; float* dp2;   // [Q][rows][nh] each
+  const float* wimg;            // [variant 3][chunk np][b_bytes / 4]
+  const float* head_w;          // [nh][4]
+};
+
+// tile-blocked layouts shared with the sampling sweep: everything a thread (row, sub) touches for column pass p is
+// one float4 per quantity, and a warp's 32 rows are contiguous (fully coalesced)
+__host__ __device__ inline size_t tc_gate_index(int q, long long tile, long long ntiles, int np, int sub, int p, int c, int row) {
+  return ((((size_t)q * (size_t)ntiles + (size_t)tile) * TC_SUB + sub) * np + p) * 3 * TC_ROWS + (size_t)c * TC_ROWS + row;
+}
+__host__ __device__ inline size_t tc_dh_index(int q, long long tile, long long ntiles, int np, int sub, int p, int row) {
+  return ((((size_t)q * (size_t)ntiles + (size_t)tile) * TC_SUB + sub) * np + p) * TC_ROWS + row;
+}
+__host__ __device__ inline long long tc_gate_bytes(int Q, long long rows, int np) {
+  return (long long)Q * ((rows + TC_ROWS - 1) / TC_ROWS) * TC_SUB * np * 3 * TC_ROWS * 16;
+}
+__host__ __device__ inline long long tc_dh_bytes(int Q, long long rows, int np) {
+  return (long long)Q * ((rows + TC_ROWS - 1) / TC_ROWS) * TC_SUB * np * TC_ROWS * 16;
+}
+
+// D[tmem] (+)= A[tmem] * B[smem]^T, tf32 operands (one 32-bit TMEM column per A element, K = 8 per instruction)
+__device__ __forceinline__ void tc_mma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// instruction descriptor: D = F32 (bit 4), A = B = TF32 (format 2 at bits 7 and 10), K-major, N >> 3 at 17, M >> 4 at 24
+__host__ __device__ constexpr uint32_t tc_idesc_tf32(int M, int N) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void tc_st28(uint32_t taddr, const uint32_t (&d)[TC_TPS]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+      ::"r"(taddr), "r"(d[0]), "r"(d[1]), "r"(d[2]), "r"(d[3]), "r"(d[4]), "r"(d[5]), "r"(d[6]), "r"(d[7]), "r"(d[8]), "r"(d[9]),
+        "r"(d[10]), "r"(d[11]), "r"(d[12]), "r"(d[13]), "r"(d[14]), "r"(d[15]) : "memory");
+  tc_st8(taddr + 16u, d[16], d[17], d[18], d[19], d[20], d[21], d[22], d[23]);
+  tc_st4(taddr + 24u, make_uint4(d[24], d[25], d[26], d[27]));
+}
+
+// ---- weight images: Wstack^T per variant and chunk ------------------------------------------------------------
+// out[variant 3][chunk p][k-core 28][n-core][8 rows][4]:  element (n, k) of chunk p is the derivative of pre-activation
+// block blk of unit j = 16 p + 4 sub + e  (k = sub * 28 + blk * 4 + e) with respect to input i of [h_h ; h_v]
+// (n = half * nhp + position, unit of the half = tc_kunit(position)).  Same variants as pack_tc_kernel.
+__global__ void pack_bwd_tc_kernel(const float* __restrict__ W, const float* __restrict__ Wg, const float* __restrict__ Wmerge,
+                                   int nh, int nhp, int NP, float* __restrict__ out) {
+  const int ncores = 2 * nhp / 8;
+  const long long per_chunk = (long long)(BT_K / 4) * ncores * 32;
+  const long long total = 3LL * NP * per_chunk;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    long long r = idx;
+    const int ek = (int)(r % 4); r /= 4;
+    const int en = (int)(r % 8); r /= 8;
+    const int nn = (int)(r % ncores); r /= ncores;
+    const int kk = (int)(r % (BT_K / 4)); r /= (BT_K / 4);
+    const int p = (int)(r % NP); r /= NP;
+    const int variant = (int)r;
+    const int k = kk * 4 + ek, n = nn * 8 + en;
+    const int sub = k / TC_TPS, blk = (k % TC_TPS) / 4, j = p * TC_JP + sub * 4 + (k % 4);
+    const int half = n / nhp, unit = tc_kunit(nhp, n - half * nhp);
+    float v = 0.f;
+    if (unit < nh && j < nh) {
+      const int i = half * nh + unit;
+      if (blk == 6) {
+        v = Wmerge[(long long)i * nh + j];
+      } else {
+        const float* w = ((blk < 3) ? W : Wg) + ((long long)j * 2 * nh + i) * 4;
+        const int kind = blk % 3;
+        if (variant == 0) v = (kind == 0) ? (w[0] + w[2]) : (kind == 1 ? (w[1] - w[0]) : (w[3] - w[2]));
+        else if (variant == 1) v = (kind == 0) ? w[0] : (kind == 1 ? (w[1] - w[0]) : 0.f);
+        else v = (kind == 0) ? w[2] : (kind == 1 ? 0.f : (w[3] - w[2]));
+      }
+    }
+    out[idx] = v;
+  }
+}
+
+// ---- d(logits) of every site in one launch --------------------------------------------------------------------
+// One warp per (site, row): recompute the heads from the saved hidden state and form d(logits) for the given seeds
+// (same math as head_bwd_kernel; the push into d h happens inside the reverse sweep).  2D cells: site q <-> symbol q.
+struct HeadAllParams {
+  int Q, nh, nhp, ND, D, nsites, complex_head, u1, cap_up, cap_dn;
+  long long R;
+  const float* hist; const int8_t* cfg; const int16_t* site_of_t;
+  const float* head_w; const float* head_b; const double* seed_logp; const double* seed_phase;
+  float* dlog;
+};
+__global__ void __launch_bounds__(256) head_bwd_all_kernel(const HeadAllParams S) {
+  const int lane = threadIdx.x & 31;
+  const long long w = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (w >= (long long)S.Q * S.R) return;
+  const int q = (int)(w / S.R);
+  const long long row = w - (long long)q * S.R;
+  const float* h = S.hist + ((long long)q * S.R + row) * S.nhp;
+  float part[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int j = lane; j < S.nh; j += 32) {
+    const float hv = h[j];
+#pragma unroll
+    for (int d = 0; d < 4; ++d) if (d < S.ND) part[d] = fmaf(hv, S.head_w[j * S.ND + d], part[d]);
+  }
+#pragma unroll
+  for (int d = 0; d < 4; ++d)
+    for (int o = 16; o > 0; o >>= 1) part[d] += __shfl_xor_sync(0xffffffffu, part[d], o);
+  const int8_t* crow = S.cfg + row * S.nsites;
+  const int s = crow[S.site_of_t[q]] & 1;
+  float p0 = part[0] + S.head_b[0], p1 = part[1] + S.head_b[1];
+  const float mx = fmaxf(p0, p1);
+  p0 = expf(p0 - mx); p1 = expf(p1 - mx);
+  const float ssum = p0 + p1;
+  p0 /= ssum; p1 /= ssum;
+  if (S.u1) {
+    int nup = 0;
+    for (int tt = lane; tt < q; tt += 32) nup += crow[S.site_of_t[tt]] & 1;
+    for (int o = 16; o > 0; o >>= 1) nup += __shfl_xor_sync(0xffffffffu, nup, o);
+    const int ndn = q - nup;
+    p0 *= (S.cap_dn - ndn >= 0) ? 1.f : 0.f;
+    p1 *= (S.cap_up - nup >= 0) ? 1.f : 0.f;
+    const float nrm = p0 + p1;
+    p0 /= nrm; p1 /= nrm;
+  }
+  const float sl = (float)S.seed_logp[row];
+  float dl[4] = {sl * ((s == 0 ? 1.f : 0.f) - p0), sl * ((s == 1 ? 1.f : 0.f) - p1), 0.f, 0.f};
+  if (S.complex_head) {
+    const float sp = (S.seed_phase != nullptr) ? (float)S.seed_phase[row] : 0.f;
+    const float x = ((s == 0) ? part[2] : part[3]) + ((s == 0) ? S.head_b[2] : S.head_b[3]);
+    const float den = 1.f + fabsf(x);
+    const float g = sp * 3.14159265358979f / (den * den);
+    dl[2] = (s == 0) ? g : 0.f;
+    dl[3] = (s == 1) ? g : 0.f;
+  }
+  if (lane < S.ND) S.dlog[((long long)q * S.R + row) * S.ND + lane] = dl[lane];
+}
+
+// ---- the reverse sweep ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams P) {
+  extern __shared__ __align__(128) unsigned char bt_smem[];
+  unsigned char* const smem = bt_smem;
+  const BtSmem L(P.nhp, P.Tsym, P.Q);
+  unsigned char* const Bst = smem + L.off_B;                              // [2][b_bytes] weight chunk stages
+  float* const headW = reinterpret_cast<float*>(smem + L.off_headw);      // [nhp + 16][4], zero past num_units / ND
+  short4* const stepS = reinterpret_cast<short4*>(smem + L.off_step);     // per site: (nbr0, nbr1, site, has_inputs)
+  uint8_t* const symS = smem + L.off_sym;                                 // [Tsym][128]
+  uint64_t* const bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
+  uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(smem + L.off_tmem);
+  uint64_t* const bar_A = bars + 0;       // [2] operand chunk written to TMEM (512 arrivals)
+  uint64_t* const bar_B = bars + 2;       // [2] weight chunk landed (complete_tx)
+  uint64_t* const bar_free = bars + 4;    // [2] chunk consumed: operand buffer and weight stage reusable (tcgen05.commit)
+  uint64_t* const bar_D = bars + 6;       // accumulator of the site complete (tcgen05.commit)
+  uint64_t* const bar_Dfree = bars + 7;   // accumulator drained (512 arrivals)
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nh = P.nh, nhp = P.nhp, NP = P.np;
+  const uint32_t ncols = 2u * (uint32_t)nhp;          // accumulator columns: [d h_h ; d h_v]
+  // TMEM map: [0, ncols) accumulator; then two operand chunks of 112 columns (one tf32 per column)
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_A + i, TC_EPI_THREADS); mbar_init(bar_B + i, 1); mbar_init(bar_free + i, 1); }
+    mbar_init(bar_D, 1);
+    mbar_init(bar_Dfree, TC_EPI_THREADS);
+    fence_mbar_init();
+  }
+  if (warp == 0) tc_alloc(tmem_slot, TC_TMEM_COLS);
+  for (int i = tid; i < (nhp + TC_JP) * 4; i += BT_THREADS) {
+    const int j = i >> 2, d = i & 3;
+    headW[i] = (j < nh && d < P.ND) ? P.head_w[j * P.ND + d] : 0.f;
+  }
+  for (int i = tid; i < P.Q; i += BT_THREADS) {
+    const StepMeta* m = P.steps + i;
+    stepS[i] = make_short4(m->nbr[0], m->nbr[1], m->site, (m->nbr[0] >= 0 || m->nbr[1] >= 0) ? 1 : 0);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_A0 = tmem_base + ((ncols + 15u) & ~15u);
+  const long long ntiles = (P.rows + TC_ROWS - 1) / TC_ROWS;
+
+  if (warp == 0) {
+    // ======================= MMA warp =======================
+    const bool leader = elect_one();
+    const uint32_t B_LBO = (uint32_t)L.ncores * 128u, SBO = 128u;
+    const uint64_t bdesc0 = tc_desc(smem_u32(Bst), B_LBO, SBO);
+    const uint64_t kstep = (uint64_t)((2u * B_LBO) >> 4);           // two k-cores (8 tf32) per MMA
+    const uint32_t idesc = tc_idesc_tf32(TC_ROWS, (int)ncols);
+    uint32_t phA = 0, phB = 0, c = 0, nsite = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      for (int q = P.Q - 1; q >= 0; --q) {
+        if (!stepS[q].w) continue;                                  // first site: no inputs to differentiate
+        for (int p = 0; p < NP; ++p, ++c) {
+          const uint32_t s = c & 1u;
+          mbar_wait(bar_B + s, (phB >> s) & 1u); phB ^= 1u << s;
+          mbar_wait(bar_A + s, (phA >> s) & 1u); phA ^= 1u << s;
+          if (p == 0 && nsite > 0) mbar_wait(bar_Dfree, (nsite - 1) & 1u);
+          tc_fence_after();
+          const uint32_t tmem_a = tmem_A0 + s * (uint32_t)BT_K;
+          const uint64_t bd = bdesc0 + (uint64_t)((s * (uint32_t)L.b_bytes) >> 4);
+          if (leader) {
+#pragma unroll
+            for (int ks = 0; ks < BT_NK8; ++ks)
+              tc_mma_tf32_ts(tmem_base, tmem_a + (uint32_t)ks * 8u, bd + (uint64_t)ks * kstep, idesc, (p > 0 || ks > 0) ? 1u : 0u);
+            tc_commit(bar_free + s);
+            if (p == NP - 1) tc_commit(bar_D);
+          }
+          __syncwarp();
+        }
+        ++nsite;
+      }
+    }
+  } else if (warp == BT_THREADS / 32 - 1) {
+    // ======================= loader warp: weight chunks =======================
+    const bool leader = elect_one();
+    uint32_t phF = 0, c = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      for (int q = P.Q - 1; q >= 0; --q) {
+        const short4 sm = stepS[q];
+        if (!sm.w) continue;
+        const int v = (sm.x >= 0 && sm.y >= 0) ? 0 : (sm.x >= 0 ? 1 : 2);
+        const unsigned char* src = reinterpret_cast<const unsigned char*>(P.wimg) + (size_t)v * NP * L.b_bytes;
+        for (int p = 0; p < NP; ++p, ++c) {
+          const uint32_t s = c & 1u;
+          if (c >= 2) { mbar_wait_relaxed(bar_free + s, (phF >> s) & 1u); phF ^= 1u << s; }
+          if (leader) {
+            mbar_expect_tx(bar_B + s, L.b_bytes);
+            bulk_g2s(Bst + (size_t)s * L.b_bytes, src + (size_t)p * L.b_bytes, L.b_bytes, bar_B + s);
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else {
+    // ======================= row warps: 4 threads per row =======================
+    const int quarter = warp & 3;
+    const int sub = (warp - 1) >> 2;
+    const int row = (quarter << 5) + lane;
+    const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
+    const int np_own = tc_kcnt(nhp, sub) / 4;                       // column passes in which this thread owns units
+    const uint32_t kcol = (uint32_t)tc_koff(nhp, sub);              // its first column inside a neighbour half of D
+    const uint32_t a_thr = tmem_A0 + lane_base + (uint32_t)(sub * TC_TPS);   // its 28 columns of operand buffer 0
+    const float* const hW = headW + sub * 16;
+    uint32_t phF = 0, c = 0, nsite = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const long long row0 = tile * TC_ROWS;
+      const bool live = row0 + row < P.rows;
+      // ---- symbol table of the tile
+      {
+        const int8_t* cf = P.cfg + (row0 + row) * P.nsites;
+        for (int t = sub; t < P.Tsym; t += TC_SUB) symS[t * TC_ROWS + row] = live ? (uint8_t)(cf[stepS[t].z] & 1) : (uint8_t)0;
+        quarter_barrier(quarter);
+      }
+      for (int q = P.Q - 1; q >= 0; --q) {
+        const short4 sm = stepS[q];
+        const int nb0 = sm.x, nb1 = sm.y;
+        const bool has_in = sm.w != 0;
+        const float cl = (nb0 >= 0) ? (float)symS[nb0 * TC_ROWS + row] : 0.f;
+        const float cu = (nb1 >= 0) ? (float)symS[nb1 * TC_ROWS + row] : 0.f;
+        float dl[4] = {0.f, 0.f, 0.f, 0.f};
+        if (live) {
+          const float* dlp = P.dlog + ((size_t)q * (size_t)P.rows + (size_t)(row0 + row)) * P.ND;
+          if (P.ND == 4) { const float4 v = *reinterpret_cast<const float4*>(dlp); dl[0] = v.x; dl[1] = v.y; dl[2] = v.z; dl[3] = v.w; }
+          else { const float2 v = *reinterpret_cast<const float2*>(dlp); dl[0] = v.x; dl[1] = v.y; }
+        }
+        const float4* gq = P.gates + tc_gate_index(q, tile, ntiles, NP, sub, 0, 0, row);
+        const float4* dhq = P.dh + tc_dh_index(q, tile, ntiles, NP, sub, 0, row);
+        const size_t orow = ((size_t)q * (size_t)P.rows + (size_t)(row0 + row)) * nh + sub * 4;
+#pragma unroll 1
+        for (int p = 0; p < NP; ++p) {
+          uint32_t d[TC_TPS];
+#pragma unroll
+          for (int i = 0; i < TC_TPS; ++i) d[i] = 0u;
+          if (p < np_own && live) {
+            const float4 dh4 = __ldcg(dhq + (size_t)p * TC_ROWS);
+            const float4 u4 = __ldg(gq + (size_t)p * 3 * TC_ROWS);
+            const float4 t4 = __ldg(gq + (size_t)p * 3 * TC_ROWS + TC_ROWS);
+            const float4 m4 = __ldg(gq + (size_t)p * 3 * TC_ROWS + 2 * TC_ROWS);
+            const float dhv[4] = {dh4.x, dh4.y, dh4.z, dh4.w}, uv[4] = {u4.x, u4.y, u4.z, u4.w};
+            const float tv[4] = {t4.x, t4.y, t4.z, t4.w}, mv[4] = {m4.x, m4.y, m4.z, m4.w};
+            float ds[4], dg[4], dm[4];
+            const int j0 = p * TC_JP + sub * 4;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float4 w = *reinterpret_cast<const float4*>(hW + p * (TC_JP * 4) + e * 4);
+              const float g = dhv[e] + dl[0] * w.x + dl[1] * w.y + dl[2] * w.z + dl[3] * w.w;   // heads' contribution
+              const bool real = (j0 + e < nh);                       // padding units carry nothing (their saved gates are unset)
+              ds[e] = real ? g * uv[e] * (1.f - tv[e] * tv[e]) : 0.f;
+              dg[e] = real ? g * (tv[e] - mv[e]) * uv[e] * (1.f - uv[e]) : 0.f;
+              dm[e] = real ? g * (1.f - uv[e]) : 0.f;
+              d[e] = __float_as_uint(ds[e]); d[4 + e] = __float_as_uint(cl * ds[e]); d[8 + e] = __float_as_uint(cu * ds[e]);
+              d[12 + e] = __float_as_uint(dg[e]); d[16 + e] = __float_as_uint(cl * dg[e]); d[20 + e] = __float_as_uint(cu * dg[e]);
+              d[24 + e] = __float_as_uint(dm[e]);
+            }
+            if (j0 + 3 < nh) {
+              *reinterpret_cast<float4*>(P.dp0 + orow + p * TC_JP) = make_float4(ds[0], ds[1], ds[2], ds[3]);
+              *reinterpret_cast<float4*>(P.dp1 + orow + p * TC_JP) = make_float4(dg[0], dg[1], dg[2], dg[3]);
+              *reinterpret_cast<float4*>(P.dp2 + orow + p * TC_JP) = make_float4(dm[0], dm[1], dm[2], dm[3]);
+            } else {
+              for (int e = 0; e < 4; ++e)
+                if (j0 + e < nh) { P.dp0[orow + p * TC_JP + e] = ds[e]; P.dp1[orow + p * TC_JP + e] = dg[e]; P.dp2[orow + p * TC_JP + e] = dm[e]; }
+            }
+          }
+          if (has_in) {
+            const uint32_t s = c & 1u;
+            if (c >= 2) { mbar_wait(bar_free + s, (phF >> s) & 1u); phF ^= 1u << s; }
+            __syncwarp();
+            tc_st28(a_thr + s * (uint32_t)BT_K, d);
+            tc_wait_st();
+            tc_fence_before();
+            mbar_arrive(bar_A + s);
+            ++c;
+          }
+        }
+        if (has_in) {
+          // ---- d[h_h ; h_v] of this row: add this thread's columns to the d h of the two neighbour sites
+          mbar_wait(bar_D, nsite & 1u);
+          ++nsite;
+          __syncwarp();
+          tc_fence_after();
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            const int nb = half ? nb1 : nb0;                         // warp-uniform
+            if (nb < 0) continue;
+            uint32_t d[TC_TPS];
+            tc_ld28(tmem_base + lane_base + (uint32_t)half * (uint32_t)nhp + kcol, d);
+            tc_wait_ld();
+            if (live) {
+              float4* dst = P.dh + tc_dh_index(nb, tile, ntiles, NP, sub, 0, row);
+#pragma unroll
+              for (int p = 0; p < TC_TPS / 4; ++p) {
+                if (p < np_own) {
+                  float4 v = __ldcg(dst + (size_t)p * TC_ROWS);
+                  v.x += __uint_as_float(d[4 * p]); v.y += __uint_as_float(d[4 * p + 1]);
+                  v.z += __uint_as_float(d[4 * p + 2]); v.w += __uint_as_float(d[4 * p + 3]);
+                  __stcg(dst + (size_t)p * TC_ROWS, v);
+                }
+              }
+            }
+          }
+          tc_fence_before();
+          mbar_arrive(bar_Dfree);
+        }
+      }  // sites
+      quarter_barrier(quarter);   // symS is rewritten by the next tile's set-up
+    }  // tiles
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) { __syncwarp(); tc_dealloc(tmem_base, TC_TMEM_COLS); }
+}
+
+}  // namespace rnnwf

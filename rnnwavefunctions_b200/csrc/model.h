@@ -70,7 +70,10 @@ struct rnnwf_model_impl {
     Saved s;
     s.off_hist = 0;
     s.off_gates = al((long long)Q * rows * nhp * 4);
-    s.off_cum = s.off_gates + al(gru_type ? (long long)Q * rows * Gp * 16 : 0);
+    // tensor-core regime: gates are saved tile-blocked, three float4 per (row, 4 units) (bwd_tc.cuh: tc_gate_index)
+    const long long gate_bytes = tc_enabled ? (long long)Q * ((rows + 127) / 128) * 4 * tc_np * 3 * 128 * 16
+                                            : (gru_type ? (long long)Q * rows * Gp * 16 : 0);
+    s.off_cum = s.off_gates + al(gate_bytes);
     s.total = s.off_cum + al((long long)Tsym * rows * 16);
     return s;
   }

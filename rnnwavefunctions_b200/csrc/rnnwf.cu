@@ -533,6 +533,7 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
   }
   CREATE_TRY(backward_init());
+  if (m->tc_enabled) CREATE_TRY(backward_init_tc(*m));
 #undef CREATE_TRY
   *out = m;
   return RNNWF_OK;

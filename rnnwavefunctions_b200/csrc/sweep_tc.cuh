@@ -484,6 +484,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
       const int nrows = (int)((total_rows - row0 < (long long)TC_ROWS) ? (total_rows - row0) : (long long)TC_ROWS);
       const int q0 = tile_q0(row0) * P.symL;
       const bool live = row < nrows;
+      const long long sv_tiles = ((long long)P.sv_rows + TC_ROWS - 1) / TC_ROWS;
       int rparent = 0;
       // ---- symbol table of the tile (teacher forcing); the head warps must be done with the previous tile's
       if (ntile > 0) mbar_wait(bar_tile, (ntile - 1) & 1);
@@ -586,7 +587,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         unsigned char* const ring_w = ring_base + (ring_off0 + (uint32_t)eq.z);  // this thread's first quad of this step's image
         const bool save = (MODE != MODE_CHILD) && live && (P.sv_hist != nullptr);
         float* sv_h = save ? P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + sub * 4 : nullptr;
-        float4* sv_g = save ? P.sv_gates + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * P.Gp + sub * 4 : nullptr;
+        // saved gates, tile-blocked for the reverse sweep (bwd_tc.cuh: tc_gate_index): one float4 (4 units) per quantity
+        float4* sv_g = save ? P.sv_gates + ((((size_t)q * (size_t)sv_tiles + (size_t)tile) * TC_SUB + sub) * NP) * 3 * TC_ROWS + row : nullptr;
         uint32_t a_carry = a_next + (uint32_t)carry_half * hcols;
         const float* bSp = bS;
         const float* hWp = hW;
@@ -609,7 +611,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
             const float4 bs = *reinterpret_cast<const float4*>(bSp);
             const float4 bg = *reinterpret_cast<const float4*>(bSp + ldb);
             const float bsv[4] = {bs.x, bs.y, bs.z, bs.w}, bgv[4] = {bg.x, bg.y, bg.z, bg.w};
-            float hnew[4];
+            float hnew[4], gu[4], gt[4], gm[4];
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
               // blocks: 0..2 = Wa, Wb, Wc of the candidate; 3..5 of the gate; 6 = Wmerge
@@ -623,12 +625,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
               hnew[e] = hv;
               const float4 w = *reinterpret_cast<const float4*>(hWp + e * 4);
               lg[0] = fmaf(hv, w.x, lg[0]); lg[1] = fmaf(hv, w.y, lg[1]); lg[2] = fmaf(hv, w.z, lg[2]); lg[3] = fmaf(hv, w.w, lg[3]);
-              if (save && p * TC_JP + sub * 4 + e < nh) sv_g[e] = make_float4(u, ht, mv, 0.f);
+              gu[e] = u; gt[e] = ht; gm[e] = mv;
             }
             if (live) {
               o.x = pack_f16x2(hnew[0], hnew[1]);
               o.y = pack_f16x2(hnew[2], hnew[3]);
-              if (save) *reinterpret_cast<float4*>(sv_h) = make_float4(hnew[0], hnew[1], hnew[2], hnew[3]);
+              if (save) {
+                *reinterpret_cast<float4*>(sv_h) = make_float4(hnew[0], hnew[1], hnew[2], hnew[3]);
+                sv_g[0] = make_float4(gu[0], gu[1], gu[2], gu[3]);
+                sv_g[TC_ROWS] = make_float4(gt[0], gt[1], gt[2], gt[3]);
+                sv_g[2 * TC_ROWS] = make_float4(gm[0], gm[1], gm[2], gm[3]);
+              }
             }
           } else {
             mbar_arrive_a(bar_free_a + s * 8u);   // nothing to read: its columns of the narrow last pass are padding
@@ -640,7 +647,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
             if (has_next) tc_st2(a_carry, o);
             *reinterpret_cast<uint2*>(ring_w + (uint32_t)(p >> 1) * TC_RING_QUAD + (uint32_t)(p & 1) * 8u) = o;
           }
-          a_carry += 2u; bSp += TC_JP; hWp += TC_JP * 4; sv_h += TC_JP; sv_g += TC_JP;
+          a_carry += 2u; bSp += TC_JP; hWp += TC_JP * 4; sv_h += TC_JP; sv_g += 3 * TC_ROWS;
           TC_ACC(9);
         }
         TC_EV(14);
