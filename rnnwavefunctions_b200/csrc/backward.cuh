@@ -17,6 +17,7 @@
 
 #include "model.h"
 #include "bwd_tc.cuh"
+#include "dw_tc.cuh"
 
 namespace rnnwf {
 
@@ -421,11 +422,14 @@ __global__ void build_onehot_kernel(const BwdStep S, int nslots, float* __restri
 inline cudaError_t backward_init() {
   return cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GT_STAGES * 2 * GT_TILE_BYTES);
 }
+inline int dw_smem_bytes(int nhp) { return 2 * tc_himg_floats(nhp) * 4 + 256; }
 inline cudaError_t backward_init_tc(const rnnwf_model_impl& m) {
-  return cudaFuncSetAttribute(bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BtSmem(m.nhp, m.Tsym, m.Q).total);
+  cudaError_t e = cudaFuncSetAttribute(bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BtSmem(m.nhp, m.Tsym, m.Q).total);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(dw_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dw_smem_bytes(m.nhp));
 }
 
-struct BwdLayout { long long off_dh, off_dp, off_Z, off_dZ, off_hc, off_dhc, off_dlog, off_X, off_wstack, off_wimg, total; long long dpw; int Kz; bool batched; };
+struct BwdLayout { long long off_dh, off_dp, off_Z, off_dZ, off_hc, off_dhc, off_dlog, off_X, off_wstack, off_wimg, off_dpT, off_jobs, off_cls, total; long long dpw; int Kz; bool batched; };
 
 inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   auto al = [](long long x) { return (x + 255) & ~255LL; };
@@ -449,8 +453,47 @@ inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   L.off_X = o;    o += al(R * 8 * 4);
   L.off_wstack = o; o += al(L.batched ? 3LL * 2 * nh * 7 * nh * 4 : 0);
   L.off_wimg = o;   o += al(m.tc_enabled ? 3LL * m.tc_np * BtSmem(m.nhp, m.Tsym, m.Q).b_bytes : 0);   // Wstack^T chunks of the reverse sweep
+  L.off_dpT = o;    o += al(m.tc_enabled ? tc_dpt_bytes(m.Q, R, m.nhp) : 0);
+  L.off_jobs = o;   o += al(m.tc_enabled ? 1024LL * (long long)sizeof(DwJob) : 0);
+  L.off_cls = o;    o += al(m.tc_enabled ? 3LL * m.Q * 4 : 0);
   L.total = o;
   return L;
+}
+
+// Work split of the weight-gradient kernel: one job per CTA, each a contiguous range of (site, tile) items of one
+// (source, neighbour half, neighbour class); about one job per SM, sized by cost (Wmerge jobs skip the masked blocks).
+inline void dw_plan(const rnnwf_model_impl& m, long long R, std::vector<DwJob>& jobs, std::vector<int>& cls_steps, int cls_count[3]) {
+  const long long tiles = (R + TC_ROWS - 1) / TC_ROWS;
+  cls_steps.assign(3 * (size_t)m.Q, 0);
+  cls_count[0] = cls_count[1] = cls_count[2] = 0;
+  for (int q = 0; q < m.Q; ++q) {
+    const bool h = m.steps[q].nbr[0] >= 0, u = m.steps[q].nbr[1] >= 0;
+    const int c = (h && u) ? 0 : (h ? 1 : (u ? 2 : -1));
+    if (c >= 0) cls_steps[(size_t)c * m.Q + cls_count[c]++] = q;
+  }
+  struct Group { int src, half, cls; long long items; double w; };
+  std::vector<Group> groups;
+  double total = 0;
+  for (int src = 0; src < 3; ++src)
+    for (int half = 0; half < 2; ++half)
+      for (int cls = 0; cls < 3; ++cls) {
+        if ((half == 0 && cls == 2) || (half == 1 && cls == 1)) continue;   // that neighbour is absent in this class
+        const long long items = (long long)cls_count[cls] * tiles;
+        if (items == 0) continue;
+        const double w = (src == 2) ? 0.5 : 1.0;
+        groups.push_back({src, half, cls, items, w});
+        total += items * w;
+      }
+  jobs.clear();
+  const double target = total / std::max(1, m.num_sms);
+  for (const Group& g : groups) {
+    long long n = (long long)(g.items * g.w / std::max(1e-9, target) + 0.5);
+    n = std::max(1LL, std::min(n, g.items));
+    for (long long k = 0; k < n; ++k) {
+      const long long b = g.items * k / n, e = g.items * (k + 1) / n;
+      jobs.push_back({g.src, g.half, g.cls, (int)b, (int)(e - b)});
+    }
+  }
 }
 
 inline long long backward_workspace_bytes(const rnnwf_model_impl& m, long long R) { return backward_layout(m, R).total; }
@@ -549,27 +592,43 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
     BwdTcParams B;
     B.steps = m.d_steps; B.Q = m.Q; B.Tsym = m.Tsym; B.nsites = m.nsites; B.nh = nh; B.nhp = nhp; B.np = m.tc_np; B.ND = m.ND;
     B.rows = R; B.cfg = cfg; B.gates = gates; B.dlog = dlog_base; B.dh = reinterpret_cast<float4*>(dh);
-    B.dp0 = dp; B.dp1 = dp + (long long)m.Q * R * nh; B.dp2 = dp + 2LL * m.Q * R * nh;
+    B.dpT = reinterpret_cast<float*>(ws + L.off_dpT);
     B.wimg = wimg; B.head_w = m.d_head_w;
     const long long tiles = (R + TC_ROWS - 1) / TC_ROWS;
     const BtSmem bs(nhp, m.Tsym, m.Q);
     RNNWF_COUNT_LAUNCH(); bwd_tc_kernel<<<(unsigned)std::min<long long>(tiles, m.num_sms), BT_THREADS, bs.total, st>>>(B);
-    for (int q = m.Q - 1; q >= 1; --q) {     // operands T = hc (x) x and hc of the batched dW / dWmerge GEMMs
-      const StepMeta& sm = m.steps[q];
-      BwdStep S;
-      std::memset(&S, 0, sizeof(S));
-      S.q = q; S.t = sm.sym; S.cell = m.cell; S.nh = nh; S.nhp = nhp; S.Gp = m.Gp; S.D = m.D; S.ND = m.ND;
-      S.bits = m.bits; S.nsites = m.nsites; S.Tsym = m.Tsym; S.L = m.symL; S.R = R; S.cfg = cfg; S.hist = hist;
-      for (int k = 0; k < MAX_SLOTS; ++k) {
-        S.nbr[k] = sm.nbr[k];
-        S.nsym_site[k] = (sm.nsym[k] >= 0) ? m.site_of_t[sm.nsym[k]] : -1;
-      }
-      S.sym_site = sm.site;
-      RNNWF_COUNT_LAUNCH(); build_tens_kernel<<<nblk(R * 2 * nh), tpb, 0, st>>>(S, Z_base + (long long)q * R * L.Kz, hc_base + (long long)q * R * 2 * nh);
+    // ---- parameter gradients: weights on the tensor cores (dw_tc.cuh), biases and heads as reductions
+    {
+      std::vector<DwJob> jobs;
+      std::vector<int> cls_steps;
+      DwParams D;
+      dw_plan(m, R, jobs, cls_steps, D.cls_count);
+      if (jobs.size() > 1024) { err = "rnnwf_backward: too many weight-gradient jobs"; return RNNWF_EINVAL; }
+      DwJob* d_jobs = reinterpret_cast<DwJob*>(ws + L.off_jobs);
+      int* d_cls = reinterpret_cast<int*>(ws + L.off_cls);
+      e = cudaMemcpyAsync(d_jobs, jobs.data(), jobs.size() * sizeof(DwJob), cudaMemcpyHostToDevice, st);
+      if (e == cudaSuccess) e = cudaMemcpyAsync(d_cls, cls_steps.data(), cls_steps.size() * sizeof(int), cudaMemcpyHostToDevice, st);
+      if (e != cudaSuccess) { err = std::string("rnnwf_backward plan upload: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
+      const float* himg = reinterpret_cast<const float*>(sb + sv.off_himg);
+      D.jobs = d_jobs; D.cls_steps = d_cls; D.steps = m.d_steps; D.Q = m.Q; D.nh = nh; D.nhp = nhp; D.nsites = m.nsites;
+      D.rows = R; D.tiles = tiles; D.cfg = cfg; D.site_of_t = m.d_site_of_t; D.dpT = B.dpT; D.himg = himg;
+      D.gW = Gd("W"); D.gWg = Gd("Wg"); D.gWmerge = Gd("Wmerge");
+      RNNWF_COUNT_LAUNCH(); dw_tc_kernel<<<(unsigned)jobs.size(), DW_THREADS, dw_smem_bytes(nhp), st>>>(D);
+      const int nsplit = 16;
+      RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, 0, m.Q, tiles, nhp, nsplit, Gd("b"));
+      RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, 1, m.Q, tiles, nhp, nsplit, Gd("bg"));
+      RNNWF_COUNT_LAUNCH(); head_grad_himg_kernel<<<std::min<long long>((long long)m.Q * tiles, 4LL * m.num_sms), 128, 0, st>>>(
+          himg, dlog_base, m.Q, tiles, R, nh, nhp, m.ND, Gd("dense.W"), m.complex_head ? Gd("dense_phase.W") : nullptr);
+      const long long RQ = (long long)m.Q * R;
+      G.colsum(dlog_base, m.ND, RQ, m.D, Gd("dense.b"));
+      if (m.complex_head) G.colsum(dlog_base + m.D, m.ND, RQ, 2, Gd("dense_phase.b"));
     }
+    e = cudaGetLastError();
+    if (e != cudaSuccess) { err = std::string("rnnwf_backward kernels: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
+    return RNNWF_OK;
   }
 
-  for (int q = tc_sweep ? -1 : m.Q - 1; q >= 0; --q) {
+  for (int q = m.Q - 1; q >= 0; --q) {
     const StepMeta& sm = m.steps[q];
     BwdStep S;
     std::memset(&S, 0, sizeof(S));

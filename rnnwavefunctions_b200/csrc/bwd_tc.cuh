@@ -53,7 +53,7 @@ struct BwdTcParams {
   const float4* gates;          // saved by the sampling sweep, tile-blocked (tc_gate_index)
   const float* dlog;            // [Q][rows][ND]  d(logits) of every site (head_bwd_all_kernel)
   float4* dh;                   // [Q][tiles][sub 4][pass np][row 128] float4, zero-initialised
-  float* dp0; float* dp1; float* dp2;   // [Q][rows][nh] each
+  float* dpT;                   // [src 3: ds, dg, dm][Q][tiles][unit nhp][row 128]  (feature-major tiles for dw_tc.cuh)
   const float* wimg;            // [variant 3][chunk np][b_bytes / 4]
   const float* head_w;          // [nh][4]
 };
@@ -316,40 +316,40 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
         }
         const float4* gq = P.gates + tc_gate_index(q, tile, ntiles, NP, sub, 0, 0, row);
         const float4* dhq = P.dh + tc_dh_index(q, tile, ntiles, NP, sub, 0, row);
-        const size_t orow = ((size_t)q * (size_t)P.rows + (size_t)(row0 + row)) * nh + sub * 4;
 #pragma unroll 1
         for (int p = 0; p < NP; ++p) {
           uint32_t d[TC_TPS];
 #pragma unroll
           for (int i = 0; i < TC_TPS; ++i) d[i] = 0u;
-          if (p < np_own && live) {
-            const float4 dh4 = __ldcg(dhq + (size_t)p * TC_ROWS);
-            const float4 u4 = __ldg(gq + (size_t)p * 3 * TC_ROWS);
-            const float4 t4 = __ldg(gq + (size_t)p * 3 * TC_ROWS + TC_ROWS);
-            const float4 m4 = __ldg(gq + (size_t)p * 3 * TC_ROWS + 2 * TC_ROWS);
-            const float dhv[4] = {dh4.x, dh4.y, dh4.z, dh4.w}, uv[4] = {u4.x, u4.y, u4.z, u4.w};
-            const float tv[4] = {t4.x, t4.y, t4.z, t4.w}, mv[4] = {m4.x, m4.y, m4.z, m4.w};
-            float ds[4], dg[4], dm[4];
+          if (p < np_own) {
+            float ds[4] = {0.f, 0.f, 0.f, 0.f}, dg[4] = {0.f, 0.f, 0.f, 0.f}, dm[4] = {0.f, 0.f, 0.f, 0.f};
             const int j0 = p * TC_JP + sub * 4;
+            if (live) {
+              const float4 dh4 = __ldcg(dhq + (size_t)p * TC_ROWS);
+              const float4 u4 = __ldg(gq + (size_t)p * 3 * TC_ROWS);
+              const float4 t4 = __ldg(gq + (size_t)p * 3 * TC_ROWS + TC_ROWS);
+              const float4 m4 = __ldg(gq + (size_t)p * 3 * TC_ROWS + 2 * TC_ROWS);
+              const float dhv[4] = {dh4.x, dh4.y, dh4.z, dh4.w}, uv[4] = {u4.x, u4.y, u4.z, u4.w};
+              const float tv[4] = {t4.x, t4.y, t4.z, t4.w}, mv[4] = {m4.x, m4.y, m4.z, m4.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float4 w = *reinterpret_cast<const float4*>(hW + p * (TC_JP * 4) + e * 4);
+                const float g = dhv[e] + dl[0] * w.x + dl[1] * w.y + dl[2] * w.z + dl[3] * w.w;   // heads' contribution
+                const bool real = (j0 + e < nh);                     // padding units carry nothing (their saved gates are unset)
+                ds[e] = real ? g * uv[e] * (1.f - tv[e] * tv[e]) : 0.f;
+                dg[e] = real ? g * (tv[e] - mv[e]) * uv[e] * (1.f - uv[e]) : 0.f;
+                dm[e] = real ? g * (1.f - uv[e]) : 0.f;
+                d[e] = __float_as_uint(ds[e]); d[4 + e] = __float_as_uint(cl * ds[e]); d[8 + e] = __float_as_uint(cu * ds[e]);
+                d[12 + e] = __float_as_uint(dg[e]); d[16 + e] = __float_as_uint(cl * dg[e]); d[20 + e] = __float_as_uint(cu * dg[e]);
+                d[24 + e] = __float_as_uint(dm[e]);
+              }
+            }
+            // feature-major tiles for the weight-gradient kernel (zeros for rows past the end of the batch)
+            float* o0 = P.dpT + (((size_t)q * (size_t)ntiles + (size_t)tile) * nhp + j0) * TC_ROWS + row;
+            const size_t sstride = (size_t)P.Q * (size_t)ntiles * nhp * TC_ROWS;
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-              const float4 w = *reinterpret_cast<const float4*>(hW + p * (TC_JP * 4) + e * 4);
-              const float g = dhv[e] + dl[0] * w.x + dl[1] * w.y + dl[2] * w.z + dl[3] * w.w;   // heads' contribution
-              const bool real = (j0 + e < nh);                       // padding units carry nothing (their saved gates are unset)
-              ds[e] = real ? g * uv[e] * (1.f - tv[e] * tv[e]) : 0.f;
-              dg[e] = real ? g * (tv[e] - mv[e]) * uv[e] * (1.f - uv[e]) : 0.f;
-              dm[e] = real ? g * (1.f - uv[e]) : 0.f;
-              d[e] = __float_as_uint(ds[e]); d[4 + e] = __float_as_uint(cl * ds[e]); d[8 + e] = __float_as_uint(cu * ds[e]);
-              d[12 + e] = __float_as_uint(dg[e]); d[16 + e] = __float_as_uint(cl * dg[e]); d[20 + e] = __float_as_uint(cu * dg[e]);
-              d[24 + e] = __float_as_uint(dm[e]);
-            }
-            if (j0 + 3 < nh) {
-              *reinterpret_cast<float4*>(P.dp0 + orow + p * TC_JP) = make_float4(ds[0], ds[1], ds[2], ds[3]);
-              *reinterpret_cast<float4*>(P.dp1 + orow + p * TC_JP) = make_float4(dg[0], dg[1], dg[2], dg[3]);
-              *reinterpret_cast<float4*>(P.dp2 + orow + p * TC_JP) = make_float4(dm[0], dm[1], dm[2], dm[3]);
-            } else {
-              for (int e = 0; e < 4; ++e)
-                if (j0 + e < nh) { P.dp0[orow + p * TC_JP + e] = ds[e]; P.dp1[orow + p * TC_JP + e] = dg[e]; P.dp2[orow + p * TC_JP + e] = dm[e]; }
+              if (j0 + e < nhp) { o0[(size_t)e * TC_ROWS] = ds[e]; o0[sstride + (size_t)e * TC_ROWS] = dg[e]; o0[2 * sstride + (size_t)e * TC_ROWS] = dm[e]; }
             }
           }
           if (has_in) {

@@ -1,0 +1,290 @@
+// Weight gradients of the tensorized 2D GRU on the tensor cores (reduced-precision regime).
+//
+//   dW [j][i][c]   = sum_{sites q, rows b} ds_j  hc_i  x_c        x = (1 - sl, sl, 1 - su, su)   (0 for an absent neighbour)
+//   dWg[j][i][c]   = same with dg,         dWmerge[i][j] = sum dm_j hc_i,        hc = [h_h ; h_v]
+// The one-hot factors are {0,1} masks over the rows, so for each source s in {ds, dg, dm} and each neighbour half the
+// kernel accumulates three [128 x 112] FP32 tiles in TMEM over all (site, 128-row tile) items it is given:
+//        S = s^T h,    Cl = (sl . s)^T h,    Cu = (su . s)^T h              (contraction over the rows)
+// with tcgen05.mma kind::tf32: the A operand (units x rows) is written into TMEM by the threads that load the
+// feature-major (ds, dg, dm) tiles of the reverse sweep and apply the row masks in registers; the B operand is the
+// hidden-state tile image the sampling sweep saved in UMMA core-matrix order, fetched with one bulk copy per item.
+// Items of one CTA all belong to one neighbour class (both / horizontal only / vertical only), so at the end
+//        dW[..,0] += S - Cl, dW[..,1] += Cl   (horizontal neighbour present),   dW[..,2] += S - Cu, dW[..,3] += Cu   (vertical)
+// go to the gradient with atomicAdd.  Replaces the expanded operand h (x) x (3.2 GB at the benchmark size) and three
+// long-K GEMMs with transposing loads.
+// Reference behaviour: tf.gradients w.r.t. MDTensorizedGRUcell.py:35-47 parameters (W, Wg, Wmerge).
+#pragma once
+#include "bwd_tc.cuh"
+
+namespace rnnwf {
+
+constexpr int DW_THREADS = 32 + 128 + 32;   // warp 0: MMA, warps 1..4: operand writers (lane <-> unit), warp 5: loader
+constexpr int DW_KC = 16;                   // rows per operand chunk
+constexpr int DW_CHUNKS = TC_ROWS / DW_KC;  // 8 chunks per item
+
+// hidden-state tile image of one (site, 128-row tile): B operand [unit n][row k], K-major core matrices
+//   float index = ((k / 4) * ncores + n / 8) * 32 + (n % 8) * 4 + (k % 4),     ncores = ceil(nhp / 16) * 2
+__host__ __device__ inline int tc_himg_ncores(int nhp) { return ((nhp + 15) / 16) * 2; }
+__host__ __device__ inline int tc_himg_floats(int nhp) { return (TC_ROWS / 4) * tc_himg_ncores(nhp) * 32; }
+__host__ __device__ inline long long tc_himg_bytes(int Q, long long rows, int nhp) {
+  return (long long)Q * ((rows + TC_ROWS - 1) / TC_ROWS) * tc_himg_floats(nhp) * 4;
+}
+// feature-major tiles of the reverse sweep: [src 3][site][tile][unit nhp][row 128]
+__host__ __device__ inline long long tc_dpt_bytes(int Q, long long rows, int nhp) {
+  return 3LL * Q * ((rows + TC_ROWS - 1) / TC_ROWS) * nhp * TC_ROWS * 4;
+}
+
+struct DwJob {            // one CTA's share: a contiguous range of items of one (source, half, class)
+  int src;                // 0 ds -> W, 1 dg -> Wg, 2 dm -> Wmerge
+  int half;               // neighbour half of hc: 0 horizontal, 1 vertical
+  int cls;                // 0 both neighbours present, 1 horizontal only, 2 vertical only
+  int begin, count;       // items [begin, begin + count) of the class: item = step_index * tiles + tile
+};
+
+struct DwParams {
+  const DwJob* jobs;
+  const int* cls_steps;   // [3][Q] sites of each class, cls_count[3]
+  int cls_count[3];
+  const StepMeta* steps;
+  int Q, nh, nhp, nsites;
+  long long rows, tiles;
+  const int8_t* cfg;
+  const int16_t* site_of_t;
+  const float* dpT;       // feature-major (ds, dg, dm)
+  const float* himg;      // hidden-state tile images
+  float* gW; float* gWg; float* gWmerge;
+};
+
+__global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) {
+  extern __shared__ __align__(128) unsigned char dw_smem[];
+  const int ncores = tc_himg_ncores(P.nhp);
+  const uint32_t img_bytes = (uint32_t)tc_himg_floats(P.nhp) * 4u;
+  unsigned char* const Bst = dw_smem;                                       // [2][img_bytes]
+  uint64_t* const bars = reinterpret_cast<uint64_t*>(dw_smem + 2 * img_bytes);
+  uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(dw_smem + 2 * img_bytes + 64);
+  uint32_t* const maskS = reinterpret_cast<uint32_t*>(dw_smem + 2 * img_bytes + 128);   // [2 items][2 masks][4 words]
+  uint64_t* const bar_A = bars + 0;       // [2] operand chunk written (128 arrivals)
+  uint64_t* const bar_Afree = bars + 2;   // [2] operand chunk consumed (commit)
+  uint64_t* const bar_B = bars + 4;       // [2] hidden-state tile landed (complete_tx)
+  uint64_t* const bar_Bfree = bars + 6;   // [2] hidden-state tile consumed (commit)
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const DwJob job = P.jobs[blockIdx.x];
+  const int N = ncores * 8;                                   // MMA N (units padded to a multiple of 16)
+  const bool masks = job.src != 2;                            // Wmerge has no one-hot factor
+  const int nacc = masks ? 3 : 1;
+  // TMEM map: accumulators [0, 3 N); operand chunks at 3 N: [2 buffers][3 blocks][16 columns]
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_A + i, 128); mbar_init(bar_Afree + i, 1); mbar_init(bar_B + i, 1); mbar_init(bar_Bfree + i, 1); }
+    fence_mbar_init();
+  }
+  if (warp == 0) tc_alloc(tmem_slot, TC_TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_A0 = tmem_base + 3u * (uint32_t)N;
+  const int* steps_of_cls = P.cls_steps + job.cls * P.Q;
+
+  if (job.count > 0) {
+    if (warp == 0) {
+      // ======================= MMA warp =======================
+      const bool leader = elect_one();
+      const uint32_t LBO = (uint32_t)ncores * 128u, SBO = 128u;
+      const uint64_t bdesc0 = tc_desc(smem_u32(Bst), LBO, SBO);
+      const uint32_t idesc = tc_idesc_tf32(TC_ROWS, N);
+      uint32_t phA = 0, phB = 0, c = 0;
+      for (int it = 0; it < job.count; ++it) {
+        const uint32_t st = (uint32_t)it & 1u;
+        mbar_wait(bar_B + st, (phB >> st) & 1u); phB ^= 1u << st;
+        for (int kc = 0; kc < DW_CHUNKS; ++kc, ++c) {
+          const uint32_t s = c & 1u;
+          mbar_wait(bar_A + s, (phA >> s) & 1u); phA ^= 1u << s;
+          tc_fence_after();
+          if (leader) {
+            const uint32_t a0 = tmem_A0 + s * 48u;
+            // rows 16 kc .. + 15 of the tile = k-cores 4 kc .. + 3 of the image
+            const uint64_t bd = bdesc0 + (uint64_t)((st * img_bytes + (uint32_t)(kc * 4) * LBO) >> 4);
+            for (int b = 0; b < nacc; ++b) {
+#pragma unroll
+              for (int ks = 0; ks < 2; ++ks)
+                tc_mma_tf32_ts(tmem_base + (uint32_t)(b * N), a0 + (uint32_t)(b * 16 + ks * 8), bd + (uint64_t)((ks * 2u * LBO) >> 4), idesc,
+                               (it > 0 || kc > 0 || ks > 0) ? 1u : 0u);
+            }
+            tc_commit(bar_Afree + s);
+            if (kc == DW_CHUNKS - 1) tc_commit(bar_Bfree + st);
+          }
+          __syncwarp();
+        }
+      }
+    } else if (warp == DW_THREADS / 32 - 1) {
+      // ======================= loader warp: one bulk copy per item =======================
+      const bool leader = elect_one();
+      uint32_t phF = 0;
+      for (int it = 0; it < job.count; ++it) {
+        const uint32_t st = (uint32_t)it & 1u;
+        const int item = job.begin + it;
+        const int q = steps_of_cls[item / (int)P.tiles];
+        const long long tile = item % (int)P.tiles;
+        const int nb = P.steps[q].nbr[job.half];
+        if (it >= 2) { mbar_wait_relaxed(bar_Bfree + st, (phF >> st) & 1u); phF ^= 1u << st; }
+        if (leader) {
+          const unsigned char* src = reinterpret_cast<const unsigned char*>(P.himg) + ((size_t)nb * (size_t)P.tiles + (size_t)tile) * img_bytes;
+          mbar_expect_tx(bar_B + st, img_bytes);
+          bulk_g2s(Bst + (size_t)st * img_bytes, src, img_bytes, bar_B + st);
+        }
+        __syncwarp();
+      }
+    } else {
+      // ======================= operand writers: lane <-> unit =======================
+      const int quarter = warp & 3;
+      const int unit = (quarter << 5) + lane;                      // TMEM lane == M index == unit j
+      const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
+      const bool real = unit < P.nh;
+      uint32_t phF = 0, c = 0;
+      for (int it = 0; it < job.count; ++it) {
+        const int item = job.begin + it;
+        const int q = steps_of_cls[item / (int)P.tiles];
+        const long long tile = item % (int)P.tiles;
+        // row masks of the item: bit k of word w <-> row 32 w + k has its horizontal / vertical neighbour spin up
+        if (masks) {
+          const StepMeta* sm = P.steps + q;
+          const long long r = tile * TC_ROWS + (warp - 1) * 32 + lane;
+          int sl = 0, su = 0;
+          if (r < P.rows) {
+            const int8_t* cf = P.cfg + r * P.nsites;
+            if (sm->nbr[0] >= 0) sl = cf[P.site_of_t[sm->nbr[0]]] & 1;
+            if (sm->nbr[1] >= 0) su = cf[P.site_of_t[sm->nbr[1]]] & 1;
+          }
+          const uint32_t bl = __ballot_sync(0xffffffffu, sl), bu = __ballot_sync(0xffffffffu, su);
+          if (lane == 0) { maskS[((it & 1) * 2 + 0) * 4 + (warp - 1)] = bl; maskS[((it & 1) * 2 + 1) * 4 + (warp - 1)] = bu; }
+          asm volatile("bar.sync 1, 128;" ::: "memory");           // the four writer warps
+        }
+        const float* src = P.dpT + ((((size_t)job.src * P.Q + q) * (size_t)P.tiles + (size_t)tile) * P.nhp + (real ? unit : 0)) * TC_ROWS;
+        float4 nxt[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) nxt[i] = real ? __ldg(reinterpret_cast<const float4*>(src) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int kc = 0; kc < DW_CHUNKS; ++kc, ++c) {
+          float v[16];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) { v[4 * i] = nxt[i].x; v[4 * i + 1] = nxt[i].y; v[4 * i + 2] = nxt[i].z; v[4 * i + 3] = nxt[i].w; }
+          if (kc + 1 < DW_CHUNKS) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) nxt[i] = real ? __ldg(reinterpret_cast<const float4*>(src) + (kc + 1) * 4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+          const uint32_t s = c & 1u;
+          if (c >= 2) { mbar_wait(bar_Afree + s, (phF >> s) & 1u); phF ^= 1u << s; }
+          const uint32_t a0 = tmem_A0 + lane_base + s * 48u;
+          uint32_t w[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) w[i] = __float_as_uint(v[i]);
+          __syncwarp();
+          tc_st16(a0, w);
+          if (masks) {
+            const uint32_t ml = (maskS[((it & 1) * 2 + 0) * 4 + (kc >> 1)] >> ((kc & 1) * 16)) & 0xffffu;
+            const uint32_t mu = (maskS[((it & 1) * 2 + 1) * 4 + (kc >> 1)] >> ((kc & 1) * 16)) & 0xffffu;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) w[i] = ((ml >> i) & 1u) ? __float_as_uint(v[i]) : 0u;
+            tc_st16(a0 + 16u, w);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) w[i] = ((mu >> i) & 1u) ? __float_as_uint(v[i]) : 0u;
+            tc_st16(a0 + 32u, w);
+          }
+          tc_wait_st();
+          tc_fence_before();
+          mbar_arrive(bar_A + s);
+        }
+      }
+      // ---- flush: wait for the last MMAs, then add this unit's accumulator rows to the gradient
+      {
+        // commits complete in order: the last chunk's completion on its buffer is the phase this thread would wait for next
+        const uint32_t last = (c - 1) & 1u;
+        mbar_wait(bar_Afree + last, (phF >> last) & 1u);
+        tc_fence_after();
+        const bool has_h = job.cls != 2, has_u = job.cls != 1;
+        const int nh = P.nh;
+        for (int n0 = 0; n0 < N; n0 += 16) {
+          uint32_t S[16], Cl[16], Cu[16];
+          __syncwarp();
+          tc_ld16(tmem_base + lane_base + (uint32_t)n0, S);
+          if (masks) { tc_ld16(tmem_base + lane_base + (uint32_t)(N + n0), Cl); tc_ld16(tmem_base + lane_base + (uint32_t)(2 * N + n0), Cu); }
+          tc_wait_ld();
+          if (real) {
+#pragma unroll
+            for (int e = 0; e < 16; ++e) {
+              const int i = n0 + e;
+              if (i >= nh) continue;
+              const float s = __uint_as_float(S[e]);
+              if (!masks) {
+                atomicAdd(P.gWmerge + (size_t)(job.half * nh + i) * nh + unit, s);
+              } else {
+                float* g = (job.src == 0 ? P.gW : P.gWg) + ((size_t)unit * 2 * nh + (size_t)(job.half * nh + i)) * 4;
+                const float cl = __uint_as_float(Cl[e]), cu = __uint_as_float(Cu[e]);
+                if (has_h) { atomicAdd(g + 0, s - cl); atomicAdd(g + 1, cl); }
+                if (has_u) { atomicAdd(g + 2, s - cu); atomicAdd(g + 3, cu); }
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) { __syncwarp(); tc_dealloc(tmem_base, TC_TMEM_COLS); }
+}
+
+// bias gradients from the feature-major tiles: out[j] += sum over all (site, tile, row) of src[j]
+__global__ void __launch_bounds__(128) dpt_rowsum_kernel(const float* __restrict__ dpT, int src, int Q, long long tiles, int nhp,
+                                                         int nsplit, float* __restrict__ out) {
+  __shared__ float red[4];
+  const int j = blockIdx.x;
+  const long long nitems = (long long)Q * tiles;
+  const float* base = dpT + (size_t)src * Q * tiles * nhp * TC_ROWS + (size_t)j * TC_ROWS + threadIdx.x;
+  float s = 0.f;
+  for (long long it = blockIdx.y; it < nitems; it += nsplit) s += base[(size_t)it * nhp * TC_ROWS];
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) atomicAdd(out + j, red[0] + red[1] + red[2] + red[3]);
+}
+
+// head weight gradients from the hidden-state tile images: gH[j][d] += sum_rows h_j dlog_d
+__global__ void __launch_bounds__(128) head_grad_himg_kernel(const float* __restrict__ himg, const float* __restrict__ dlog, int Q,
+                                                             long long tiles, long long rows, int nh, int nhp, int ND,
+                                                             float* __restrict__ gW, float* __restrict__ gWp) {
+  __shared__ float dl[TC_ROWS * 4];
+  const int ncores = tc_himg_ncores(nhp);
+  const int j = threadIdx.x;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  const long long nitems = (long long)Q * tiles;
+  for (long long it = blockIdx.x; it < nitems; it += gridDim.x) {
+    const int q = (int)(it / tiles);
+    const long long tile = it % tiles;
+    __syncthreads();
+    for (int i = threadIdx.x; i < TC_ROWS * 4; i += 128) {
+      const long long r = tile * TC_ROWS + (i >> 2);
+      const int d = i & 3;
+      dl[i] = (r < rows && d < ND) ? dlog[((size_t)q * rows + r) * ND + d] : 0.f;
+    }
+    __syncthreads();
+    if (j < nh) {
+      const float4* img = reinterpret_cast<const float4*>(himg + (size_t)it * tc_himg_floats(nhp)) + (size_t)(j >> 3) * 8 + (j & 7);
+      for (int kc = 0; kc < TC_ROWS / 4; ++kc) {
+        const float4 h = __ldg(img + (size_t)kc * ncores * 8);
+        const float hv[4] = {h.x, h.y, h.z, h.w};
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+          for (int d = 0; d < 4; ++d) acc[d] = fmaf(hv[r], dl[(kc * 4 + r) * 4 + d], acc[d]);
+      }
+    }
+  }
+  if (j < nh) {
+    // dense.W is [nh][D = 2], dense_phase.W is [nh][2]
+    atomicAdd(gW + j * 2 + 0, acc[0]); atomicAdd(gW + j * 2 + 1, acc[1]);
+    if (gWp != nullptr) { atomicAdd(gWp + j * 2 + 0, acc[2]); atomicAdd(gWp + j * 2 + 1, acc[3]); }
+  }
+}
+
+}  // namespace rnnwf

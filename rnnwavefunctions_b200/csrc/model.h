@@ -25,7 +25,7 @@ struct HostVariant {
 };
 
 struct Saved {   // byte offsets inside a caller-provided saved-state buffer for `rows` rows
-  long long off_hist, off_gates, off_cum, total;
+  long long off_hist, off_gates, off_cum, off_himg, total;
 };
 
 struct rnnwf_model_impl {
@@ -74,7 +74,10 @@ struct rnnwf_model_impl {
     const long long gate_bytes = tc_enabled ? (long long)Q * ((rows + 127) / 128) * 4 * tc_np * 3 * 128 * 16
                                             : (gru_type ? (long long)Q * rows * Gp * 16 : 0);
     s.off_cum = s.off_gates + al(gate_bytes);
-    s.total = s.off_cum + al((long long)Tsym * rows * 16);
+    s.off_himg = s.off_cum + al((long long)Tsym * rows * 16);
+    // tensor-core regime: hidden states once more as ready-made B operand tiles of the weight-gradient kernel
+    const long long himg_bytes = tc_enabled ? (long long)Q * ((rows + 127) / 128) * (32LL * (((nhp + 15) / 16) * 2) * 32) * 4 : 0;
+    s.total = s.off_himg + al(himg_bytes);
     return s;
   }
 };

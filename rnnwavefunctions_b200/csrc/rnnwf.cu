@@ -385,6 +385,7 @@ int set_saved(const rnnwf_model& m, SweepParams& P, void* saved, long long rows)
   P.sv_hist = reinterpret_cast<float*>(b + sv.off_hist);
   P.sv_gates = m.gru_type ? reinterpret_cast<float4*>(b + sv.off_gates) : nullptr;
   P.sv_cum = reinterpret_cast<double2*>(b + sv.off_cum);
+  P.sv_himg = m.tc_enabled ? reinterpret_cast<float*>(b + sv.off_himg) : nullptr;
   P.sv_rows = rows;
   return RNNWF_OK;
 }

@@ -203,6 +203,12 @@ __device__ __forceinline__ void tc_st8(uint32_t taddr, uint32_t a, uint32_t b, u
   asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
                ::"r"(taddr), "r"(a), "r"(b), "r"(c), "r"(d), "r"(e), "r"(f), "r"(g), "r"(h) : "memory");
 }
+__device__ __forceinline__ void tc_st16(uint32_t taddr, const uint32_t (&d)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+      ::"r"(taddr), "r"(d[0]), "r"(d[1]), "r"(d[2]), "r"(d[3]), "r"(d[4]), "r"(d[5]), "r"(d[6]), "r"(d[7]), "r"(d[8]), "r"(d[9]),
+        "r"(d[10]), "r"(d[11]), "r"(d[12]), "r"(d[13]), "r"(d[14]), "r"(d[15]) : "memory");
+}
 __device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&d)[16]) {
   asm volatile(
@@ -590,6 +596,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         // saved gates, tile-blocked for the reverse sweep (bwd_tc.cuh: tc_gate_index): one float4 (4 units) per quantity
         float4* sv_g = save ? P.sv_gates + ((((size_t)q * (size_t)sv_tiles + (size_t)tile) * TC_SUB + sub) * NP) * 3 * TC_ROWS + row : nullptr;
         uint32_t a_carry = a_next + (uint32_t)carry_half * hcols;
+        // hidden-state tile image for the weight-gradient kernel (dw_tc.cuh: [row / 4][unit / 8][unit % 8][row % 4]);
+        // rows past the end of the batch and padding units are written as zeros
+        const int hnc = ((nhp + 15) / 16) * 2;
+        float* sv_i = (MODE != MODE_CHILD && P.sv_himg != nullptr)
+            ? P.sv_himg + ((size_t)q * (size_t)sv_tiles + (size_t)tile) * (size_t)(32 * hnc * 32) + (size_t)(row >> 2) * hnc * 32 + (row & 3) : nullptr;
         const float* bSp = bS;
         const float* hWp = hW;
 #pragma unroll 1
@@ -599,6 +610,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           mbar_wait_a(bar_mma_a + s * 8u, (phM >> s) & 1u); phM ^= 1u << s;
           TC_ACC(8); TC_EV(12);
           uint2 o = make_uint2(0u, 0u);
+          float hsave[4] = {0.f, 0.f, 0.f, 0.f};
           if (active) {
             uint32_t d[TC_TPS];
             __syncwarp();
@@ -628,6 +640,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
               gu[e] = u; gt[e] = ht; gm[e] = mv;
             }
             if (live) {
+              hsave[0] = hnew[0]; hsave[1] = hnew[1]; hsave[2] = hnew[2]; hsave[3] = hnew[3];
               o.x = pack_f16x2(hnew[0], hnew[1]);
               o.y = pack_f16x2(hnew[2], hnew[3]);
               if (save) {
@@ -646,6 +659,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
             __syncwarp();
             if (has_next) tc_st2(a_carry, o);
             *reinterpret_cast<uint2*>(ring_w + (uint32_t)(p >> 1) * TC_RING_QUAD + (uint32_t)(p & 1) * 8u) = o;
+          }
+          if (sv_i != nullptr) {
+            const int j0 = p * TC_JP + sub * 4;
+            if (j0 < hnc * 8) {
+#pragma unroll
+              for (int e = 0; e < 4; ++e) sv_i[((j0 + e) >> 3) * 32 + ((j0 + e) & 7) * 4] = hsave[e];
+            }
           }
           a_carry += 2u; bSp += TC_JP; hWp += TC_JP * 4; sv_h += TC_JP; sv_g += 3 * TC_ROWS;
           TC_ACC(9);
