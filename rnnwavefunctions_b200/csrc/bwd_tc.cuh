@@ -316,6 +316,8 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
         }
         const float4* gq = P.gates + tc_gate_index(q, tile, ntiles, NP, sub, 0, 0, row);
         const float4* dhq = P.dh + tc_dh_index(q, tile, ntiles, NP, sub, 0, row);
+        float4 n_dh = make_float4(0.f, 0.f, 0.f, 0.f), n_u = n_dh, n_t = n_dh, n_m = n_dh;
+        if (live && np_own > 0) { n_dh = __ldcg(dhq); n_u = __ldg(gq); n_t = __ldg(gq + TC_ROWS); n_m = __ldg(gq + 2 * TC_ROWS); }
 #pragma unroll 1
         for (int p = 0; p < NP; ++p) {
           uint32_t d[TC_TPS];
@@ -325,10 +327,13 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
             float ds[4] = {0.f, 0.f, 0.f, 0.f}, dg[4] = {0.f, 0.f, 0.f, 0.f}, dm[4] = {0.f, 0.f, 0.f, 0.f};
             const int j0 = p * TC_JP + sub * 4;
             if (live) {
-              const float4 dh4 = __ldcg(dhq + (size_t)p * TC_ROWS);
-              const float4 u4 = __ldg(gq + (size_t)p * 3 * TC_ROWS);
-              const float4 t4 = __ldg(gq + (size_t)p * 3 * TC_ROWS + TC_ROWS);
-              const float4 m4 = __ldg(gq + (size_t)p * 3 * TC_ROWS + 2 * TC_ROWS);
+              const float4 dh4 = n_dh, u4 = n_u, t4 = n_t, m4 = n_m;      // loaded one pass ahead
+              if (p + 1 < np_own) {
+                n_dh = __ldcg(dhq + (size_t)(p + 1) * TC_ROWS);
+                n_u = __ldg(gq + (size_t)(p + 1) * 3 * TC_ROWS);
+                n_t = __ldg(gq + (size_t)(p + 1) * 3 * TC_ROWS + TC_ROWS);
+                n_m = __ldg(gq + (size_t)(p + 1) * 3 * TC_ROWS + 2 * TC_ROWS);
+              }
               const float dhv[4] = {dh4.x, dh4.y, dh4.z, dh4.w}, uv[4] = {u4.x, u4.y, u4.z, u4.w};
               const float tv[4] = {t4.x, t4.y, t4.z, t4.w}, mv[4] = {m4.x, m4.y, m4.z, m4.w};
 #pragma unroll

@@ -21,6 +21,8 @@ namespace rnnwf {
 constexpr int DW_THREADS = 32 + 128 + 32;   // warp 0: MMA, warps 1..4: operand writers (lane <-> unit), warp 5: loader
 constexpr int DW_KC = 16;                   // rows per operand chunk
 constexpr int DW_CHUNKS = TC_ROWS / DW_KC;  // 8 chunks per item
+constexpr int DW_ABUF = 3;                  // operand chunk buffers in TMEM
+constexpr int DW_PF = 4;                    // operand chunks loaded ahead (registers)
 
 // hidden-state tile image of one (site, 128-row tile): B operand [unit n][row k], K-major core matrices
 //   float index = ((k / 4) * ncores + n / 8) * 32 + (n % 8) * 4 + (k % 4),     ncores = ceil(nhp / 16) * 2
@@ -61,21 +63,22 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
   const uint32_t img_bytes = (uint32_t)tc_himg_floats(P.nhp) * 4u;
   unsigned char* const Bst = dw_smem;                                       // [2][img_bytes]
   uint64_t* const bars = reinterpret_cast<uint64_t*>(dw_smem + 2 * img_bytes);
-  uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(dw_smem + 2 * img_bytes + 64);
+  uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(dw_smem + 2 * img_bytes + 96);
   uint32_t* const maskS = reinterpret_cast<uint32_t*>(dw_smem + 2 * img_bytes + 128);   // [2 items][2 masks][4 words]
-  uint64_t* const bar_A = bars + 0;       // [2] operand chunk written (128 arrivals)
-  uint64_t* const bar_Afree = bars + 2;   // [2] operand chunk consumed (commit)
-  uint64_t* const bar_B = bars + 4;       // [2] hidden-state tile landed (complete_tx)
-  uint64_t* const bar_Bfree = bars + 6;   // [2] hidden-state tile consumed (commit)
+  uint64_t* const bar_A = bars + 0;       // [DW_ABUF] operand chunk written (128 arrivals)
+  uint64_t* const bar_Afree = bars + 3;   // [DW_ABUF] operand chunk consumed (commit)
+  uint64_t* const bar_B = bars + 6;       // [2] hidden-state tile landed (complete_tx)
+  uint64_t* const bar_Bfree = bars + 8;   // [2] hidden-state tile consumed (commit)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const DwJob job = P.jobs[blockIdx.x];
   const int N = ncores * 8;                                   // MMA N (units padded to a multiple of 16)
   const bool masks = job.src != 2;                            // Wmerge has no one-hot factor
   const int nacc = masks ? 3 : 1;
-  // TMEM map: accumulators [0, 3 N); operand chunks at 3 N: [2 buffers][3 blocks][16 columns]
+  // TMEM map: accumulators [0, 3 N); operand chunks at 3 N: [DW_ABUF buffers][3 blocks][16 columns]
   if (tid == 0) {
-    for (int i = 0; i < 2; ++i) { mbar_init(bar_A + i, 128); mbar_init(bar_Afree + i, 1); mbar_init(bar_B + i, 1); mbar_init(bar_Bfree + i, 1); }
+    for (int i = 0; i < DW_ABUF; ++i) { mbar_init(bar_A + i, 128); mbar_init(bar_Afree + i, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_B + i, 1); mbar_init(bar_Bfree + i, 1); }
     fence_mbar_init();
   }
   if (warp == 0) tc_alloc(tmem_slot, TC_TMEM_COLS);
@@ -98,7 +101,7 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
         const uint32_t st = (uint32_t)it & 1u;
         mbar_wait(bar_B + st, (phB >> st) & 1u); phB ^= 1u << st;
         for (int kc = 0; kc < DW_CHUNKS; ++kc, ++c) {
-          const uint32_t s = c & 1u;
+          const uint32_t s = c % DW_ABUF;
           mbar_wait(bar_A + s, (phA >> s) & 1u); phA ^= 1u << s;
           tc_fence_after();
           if (leader) {
@@ -142,6 +145,7 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
       const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
       const bool real = unit < P.nh;
       uint32_t phF = 0, c = 0;
+      float4 pf[DW_PF][4];
       for (int it = 0; it < job.count; ++it) {
         const int item = job.begin + it;
         const int q = steps_of_cls[item / (int)P.tiles];
@@ -160,20 +164,40 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
           if (lane == 0) { maskS[((it & 1) * 2 + 0) * 4 + (warp - 1)] = bl; maskS[((it & 1) * 2 + 1) * 4 + (warp - 1)] = bu; }
           asm volatile("bar.sync 1, 128;" ::: "memory");           // the four writer warps
         }
-        const float* src = P.dpT + ((((size_t)job.src * P.Q + q) * (size_t)P.tiles + (size_t)tile) * P.nhp + (real ? unit : 0)) * TC_ROWS;
-        float4 nxt[4];
+        // operand rows of this unit: DW_PF chunks (16 rows each) are in flight in registers, across item boundaries
+        if (it == 0) {
+          const float* src = P.dpT + ((((size_t)job.src * P.Q + q) * (size_t)P.tiles + (size_t)tile) * P.nhp + (real ? unit : 0)) * TC_ROWS;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) nxt[i] = real ? __ldg(reinterpret_cast<const float4*>(src) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int k = 0; k < DW_PF; ++k)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) pf[k][i] = real ? __ldg(reinterpret_cast<const float4*>(src) + k * 4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        // source of the chunks that will be loaded while this item is processed: its own second half, then the next item
+        const float* src_cur = P.dpT + ((((size_t)job.src * P.Q + q) * (size_t)P.tiles + (size_t)tile) * P.nhp + (real ? unit : 0)) * TC_ROWS;
+        const float* src_nxt = src_cur;
+        if (it + 1 < job.count) {
+          const int item2 = item + 1;
+          const int q2 = steps_of_cls[item2 / (int)P.tiles];
+          const long long tile2 = item2 % (int)P.tiles;
+          src_nxt = P.dpT + ((((size_t)job.src * P.Q + q2) * (size_t)P.tiles + (size_t)tile2) * P.nhp + (real ? unit : 0)) * TC_ROWS;
+        }
+#pragma unroll
         for (int kc = 0; kc < DW_CHUNKS; ++kc, ++c) {
           float v[16];
 #pragma unroll
-          for (int i = 0; i < 4; ++i) { v[4 * i] = nxt[i].x; v[4 * i + 1] = nxt[i].y; v[4 * i + 2] = nxt[i].z; v[4 * i + 3] = nxt[i].w; }
-          if (kc + 1 < DW_CHUNKS) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) nxt[i] = real ? __ldg(reinterpret_cast<const float4*>(src) + (kc + 1) * 4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int i = 0; i < 4; ++i) {
+            const float4 t = pf[kc % DW_PF][i];
+            v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
           }
-          const uint32_t s = c & 1u;
-          if (c >= 2) { mbar_wait(bar_Afree + s, (phF >> s) & 1u); phF ^= 1u << s; }
+          {
+            const int kn = kc + DW_PF;                               // chunk to fetch into the slot just freed
+            const bool more = (kn < DW_CHUNKS) || (it + 1 < job.count);
+            const float4* s4 = reinterpret_cast<const float4*>(kn < DW_CHUNKS ? src_cur : src_nxt) + (kn % DW_CHUNKS) * 4;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) pf[kc % DW_PF][i] = (real && more) ? __ldg(s4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+          const uint32_t s = c % DW_ABUF;
+          if (c >= DW_ABUF) { mbar_wait(bar_Afree + s, (phF >> s) & 1u); phF ^= 1u << s; }
           const uint32_t a0 = tmem_A0 + lane_base + s * 48u;
           uint32_t w[16];
 #pragma unroll
@@ -198,7 +222,7 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
       // ---- flush: wait for the last MMAs, then add this unit's accumulator rows to the gradient
       {
         // commits complete in order: the last chunk's completion on its buffer is the phase this thread would wait for next
-        const uint32_t last = (c - 1) & 1u;
+        const uint32_t last = (c - 1) % DW_ABUF;
         mbar_wait(bar_Afree + last, (phF >> last) & 1u);
         tc_fence_after();
         const bool has_h = job.cls != 2, has_u = job.cls != 1;
