@@ -403,19 +403,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
     const bool leader = elect_one();
     const uint64_t bdesc0 = tc_desc(smem_u32(Bst), B_LBO, SBO);
     uint32_t phA = 0, phF = 0, phBw = 0, it = 0;      // parity bits: operand / accumulator buffers / weight stages; pass counter
+    const uint32_t barA_a = smem_u32(bar_A), barB_a = smem_u32(bar_B), barF_a = smem_u32(bar_free);
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const int q0 = tile_q0(tile * TC_ROWS) * P.symL;
       for (int q = q0; q < P.Q; ++q) {
         TC_T0();
-        mbar_wait(bar_A, phA); phA ^= 1u;
-        TC_ACC(0); TC_EV(1);
         const uint32_t tmem_a = tmem_A0 + (uint32_t)(q & 1) * acols;
         for (int p = 0; p < NP; ++p, ++it) {
           const uint32_t s = it % TC_STAGES, tb = (uint32_t)p & 1u;
-          mbar_wait(bar_B + s, (phBw >> s) & 1u); phBw ^= 1u << s;
+          // weights and accumulator buffer first (ready long before); the site's operand is the critical one: last
+          mbar_wait_a(barB_a + s * 8u, (phBw >> s) & 1u); phBw ^= 1u << s;
           TC_ACC(1); TC_EV(2);
-          mbar_wait(bar_free + tb, ((phF >> tb) & 1u) ^ 1u); phF ^= 1u << tb;
+          mbar_wait_a(barF_a + tb * 8u, ((phF >> tb) & 1u) ^ 1u); phF ^= 1u << tb;
           TC_ACC(2); TC_EV(3);
+          if (p == 0) {
+            mbar_wait_a(barA_a, phA); phA ^= 1u;
+            TC_ACC(0); TC_EV(1);
+          }
           tc_fence_after();
           const uint32_t tmem_d = tmem_base + tb * (uint32_t)TC_N;
           const uint64_t bd0 = bdesc0 + (uint64_t)((s * (uint32_t)L.b_bytes) >> 4);
