@@ -362,9 +362,13 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
   cudaError_t e;
   if (m.tc_enabled) {
     RNNWF_COUNT_LAUNCH();
-    if (P.mode == MODE_SAMPLE) sweep_tc_kernel<MODE_SAMPLE><<<s.grid, s.threads, s.smem, st>>>(P);
-    else if (P.mode == MODE_CHILD) sweep_tc_kernel<MODE_CHILD><<<s.grid, s.threads, s.smem, st>>>(P);
-    else sweep_tc_kernel<MODE_EVAL><<<s.grid, s.threads, s.smem, st>>>(P);
+    const bool bm = m.nh < m.nhp;     // biases through the tensor core when the operand has a free padding position
+#define RNNWF_TC_LAUNCH(MODE_) do { if (bm) sweep_tc_kernel<MODE_, true><<<s.grid, s.threads, s.smem, st>>>(P); \
+                                     else sweep_tc_kernel<MODE_, false><<<s.grid, s.threads, s.smem, st>>>(P); } while (0)
+    if (P.mode == MODE_SAMPLE) RNNWF_TC_LAUNCH(MODE_SAMPLE);
+    else if (P.mode == MODE_CHILD) RNNWF_TC_LAUNCH(MODE_CHILD);
+    else RNNWF_TC_LAUNCH(MODE_EVAL);
+#undef RNNWF_TC_LAUNCH
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("tensor-core sweep launch: ") + cudaGetErrorString(e));
     return RNNWF_OK;
@@ -529,9 +533,12 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
     if (ts.total > 227 * 1024) { rnnwf_destroy(m); return fail(RNNWF_ENOMEM, "tensor-core sweep does not fit in shared memory for this lattice / width"); }
     CREATE_TRY(cudaMalloc(&m->d_tcB, (size_t)3 * m->tc_np * ts.b_bytes));
     CREATE_TRY(cudaMalloc(&m->d_tcbias, (size_t)2 * m->nhp * 4));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
   }
   CREATE_TRY(backward_init());
   if (m->tc_enabled) CREATE_TRY(backward_init_tc(*m));
@@ -618,6 +625,7 @@ int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
     const long long n = 3LL * h->tc_np * (ts.b_bytes / 2);
     RNNWF_COUNT_LAUNCH(); pack_tc_kernel<<<std::min(2048, cdiv(n, 256)), 256, 0, st>>>(
         params_dev + h->tensor("W")->offset, params_dev + h->tensor("Wg")->offset, params_dev + h->tensor("Wmerge")->offset,
+        params_dev + h->tensor("b")->offset, params_dev + h->tensor("bg")->offset,
         h->nh, h->nhp, h->tc_np, reinterpret_cast<__half*>(h->d_tcB));
     RNNWF_COUNT_LAUNCH(); pack_tc_bias_kernel<<<1, 256, 0, st>>>(params_dev + h->tensor("b")->offset, params_dev + h->tensor("bg")->offset, h->nh, h->nhp, h->d_tcbias);
   }

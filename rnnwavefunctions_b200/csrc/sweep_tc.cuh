@@ -38,8 +38,11 @@ constexpr int TC_NB = 7;                // column blocks per unit: Wa_s Wb_s Wc_
 constexpr int TC_N = TC_JP * TC_NB;     // 112 MMA columns per pass
 constexpr int TC_SUB = 4;                // threads per row: each handles 4 of the 16 units of a pass
 constexpr int TC_EPI_THREADS = TC_ROWS * TC_SUB;
-constexpr int TC_HEAD_THREADS = 64;     // two rows per head thread
-constexpr int TC_THREADS = 32 + TC_EPI_THREADS + TC_HEAD_THREADS + 32;   // warp 0: MMA, 1..16: epilogue, 17..18: heads, 19: loader
+constexpr int TC_HEAD_THREADS = 32;     // four rows per head thread
+constexpr int TC_HEAD_ROWS = TC_ROWS / TC_HEAD_THREADS;
+constexpr int TC_MMA2_WARP = 18;        // second MMA-issue warp
+// warp 0: MMA issue (even passes), 1..16: epilogue, 17: heads, 18: MMA issue (odd passes), 19: loader
+constexpr int TC_THREADS = 32 + TC_EPI_THREADS + TC_HEAD_THREADS + 32 + 32;
 constexpr int TC_TPS = TC_NB * 4;       // accumulator columns one epilogue thread owns per pass (28, contiguous)
 // one step's FP16 history image: [sub 4][quad 4][row 128][16 bytes]; quad i of thread (row, sub) holds its pieces 2i, 2i+1
 // (a warp's 16-byte accesses are contiguous: fully coalesced)
@@ -282,7 +285,9 @@ __device__ __forceinline__ void tc_ld28(uint32_t taddr, uint32_t (&d)[TC_TPS]) {
                : "=r"(d[24]), "=r"(d[25]), "=r"(d[26]), "=r"(d[27]) : "r"(taddr + 24u) : "memory");
 }
 
-template <int MODE>
+// BIASMMA: the biases ride on the tensor core (num_units < padded width): position `num_units` of the horizontal
+// neighbour half of every operand is a constant 1 and that K row of the weight images holds the biases.
+template <int MODE, bool BIASMMA>
 __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepParams P) {
   extern __shared__ __align__(128) unsigned char tc_smem[];   // no swizzle anywhere: 16-byte alignment is all the hardware needs
   unsigned char* const smem = tc_smem;
@@ -395,39 +400,43 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
   };
   // Every site goes through the tensor core, the first one included (its operand is all zeros): no special cases.
 
-  if (warp == 0) {
-    // ======================= MMA warp =======================
+  if (warp == 0 || warp == TC_MMA2_WARP) {
+    // ======================= two MMA warps: one per accumulator buffer =======================
+    // A warp's instructions after its tcgen05.mma's (even a barrier poll) only return once those MMAs have executed,
+    // so a single issuer cannot check the next pass's barriers while its MMAs are in flight and the tensor core idles
+    // between passes.  Two issuers alternate: warp 0 takes the even column passes (accumulator buffer 0), warp 18 the
+    // odd ones (buffer 1); each is only ever blocked behind its own pass, and the other one's MMAs queue up behind.
     // Warp-uniform code (descriptors stay in uniform registers); the single-issue instructions are predicated on one
-    // elected lane.  Per column pass: wait for the weight stage and a drained accumulator buffer, issue the K loop
-    // (fully unrolled: every descriptor is base + immediate), commit to the epilogue and to the loader.
+    // elected lane; the K loop is fully unrolled (every descriptor is base + immediate).
+    const int me = (warp == 0) ? 0 : 1;
     const bool leader = elect_one();
     const uint64_t bdesc0 = tc_desc(smem_u32(Bst), B_LBO, SBO);
-    uint32_t phA = 0, phF = 0, phBw = 0, it = 0;      // parity bits: operand / accumulator buffers / weight stages; pass counter
-    const uint32_t barA_a = smem_u32(bar_A), barB_a = smem_u32(bar_B), barF_a = smem_u32(bar_free);
+    const uint32_t barA_a = smem_u32(bar_A), barB_a = smem_u32(bar_B), barF_a = smem_u32(bar_free + me);
+    const uint32_t tmem_d = tmem_base + (uint32_t)me * (uint32_t)TC_N;
+    uint32_t phA = 0, nuse = 0, it0 = 0;              // operand parity; uses of this warp's buffer; passes before this site
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const int q0 = tile_q0(tile * TC_ROWS) * P.symL;
-      for (int q = q0; q < P.Q; ++q) {
+      for (int q = q0; q < P.Q; ++q, it0 += (uint32_t)NP) {
         TC_T0();
         const uint32_t tmem_a = tmem_A0 + (uint32_t)(q & 1) * acols;
-        for (int p = 0; p < NP; ++p, ++it) {
-          const uint32_t s = it % TC_STAGES, tb = (uint32_t)p & 1u;
+        for (int p = me; p < NP; p += 2) {
+          const uint32_t it = it0 + (uint32_t)p, s = it % TC_STAGES;
           // weights and accumulator buffer first (ready long before); the site's operand is the critical one: last
-          mbar_wait_a(barB_a + s * 8u, (phBw >> s) & 1u); phBw ^= 1u << s;
+          mbar_wait_a(barB_a + s * 8u, (it / TC_STAGES) & 1u);   // the stage's (it / stages)-th use, by either warp
           TC_ACC(1); TC_EV(2);
-          mbar_wait_a(barF_a + tb * 8u, ((phF >> tb) & 1u) ^ 1u); phF ^= 1u << tb;
+          mbar_wait_a(barF_a, (nuse & 1u) ^ 1u); ++nuse;
           TC_ACC(2); TC_EV(3);
-          if (p == 0) {
+          if (p == me) {
             mbar_wait_a(barA_a, phA); phA ^= 1u;
             TC_ACC(0); TC_EV(1);
           }
           tc_fence_after();
-          const uint32_t tmem_d = tmem_base + tb * (uint32_t)TC_N;
           const uint64_t bd0 = bdesc0 + (uint64_t)((s * (uint32_t)L.b_bytes) >> 4);
           if (leader) {
             const uint32_t id = (p == NP - 1) ? idesc_last : idesc;
             if (hc == 13) tc_issue_pass<13>(tmem_d, tmem_a, bd0, id);
             else tc_issue_pass<0>(tmem_d, tmem_a, bd0, id, hc);
-            tc_commit(bar_mma + tb);
+            tc_commit(bar_mma + me);
             tc_commit(bar_Bfree + s);
           }
           __syncwarp();
@@ -435,7 +444,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         }
       }
     }
-    TC_TOTAL(5);
+    if (me == 0) { TC_TOTAL(5); }
   } else if (warp == TC_THREADS / 32 - 1) {
     // ======================= loader warp: weight stream =======================
     // One flat sequence of (site, pass) weight images through TC_STAGES shared-memory stages; runs ahead of the MMA
@@ -478,6 +487,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
     const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
     const int np_own = tc_kcnt(nhp, sub) / 4;           // column passes in which this thread owns units (7 or 6 at 104)
     const uint32_t hcols = (uint32_t)nhp / 2;           // TMEM columns of one neighbour half
+    // constant-1 position (unit index num_units, a padding unit) of the horizontal half: owned by one sub of each row
+    const bool one_mine = BIASMMA && sub == ((nh & 15) >> 2);
+    const int one_p = nh >> 4;                          // its column pass == piece index
+    const uint32_t one_bits = 0x3C00u << (16 * (nh & 1));               // FP16 1.0 in the low / high half of the word
+    const int one_word = 2 * one_p + ((nh & 3) >> 1);                   // word inside the thread's run
     unsigned char* const ring_base = reinterpret_cast<unsigned char*>(P.ring);
     // this thread's first quad inside a step's ring image   (the whole ring is < 4 GB: 32-bit offsets)
     const uint32_t ring_off0 = (uint32_t)blockIdx.x * (uint32_t)P.ring_len * TC_RING_SLOT + (uint32_t)sub * (4u * TC_RING_QUAD) + (uint32_t)row * 16u;
@@ -561,6 +575,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         }
       };
 
+      auto set_one = [&](uint32_t (&w)[16]) {
+        if (one_mine) {
+#pragma unroll
+          for (int i = 0; i < 14; ++i) if (i == one_word) w[i] |= one_bits;
+        }
+      };
+
       // operand of the tile's first step: both halves from the history (parent's saved history under prefix reuse;
       // zeros for the very first site), then prefetch the older-neighbour half of the second step's operand
       uint32_t onext[16];
@@ -569,6 +590,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         const int nb0 = (int)(short)(e0.x & 0xffff), nb1 = (int)(short)((unsigned)e0.x >> 16);
         const uint32_t a0 = aop0 + (uint32_t)(q0 & 1) * acols;
         load_half(onext, nb0, nb0 >= 0 ? (uint32_t)(nb0 % P.ring_len) * TC_RING_SLOT : 0u);
+        set_one(onext);
         store_half(onext, a0);
         load_half(onext, nb1, nb1 >= 0 ? (uint32_t)(nb1 % P.ring_len) * TC_RING_SLOT : 0u);
         store_half(onext, a0 + hcols);
@@ -587,7 +609,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         const bool has_next = (q + 1 < P.Q);
         const int carry_half = has_next ? (stepT[q + 1].y >> 16) : 0;
         const uint32_t a_next = aop0 + (uint32_t)((q + 1) & 1) * acols;
-        if (has_next) store_half(onext, a_next + (uint32_t)(1 - carry_half) * hcols);
+        if (has_next) {
+          if (carry_half == 1) set_one(onext);          // the prefetched half is the horizontal one
+          store_half(onext, a_next + (uint32_t)(1 - carry_half) * hcols);
+        }
         TC_ACC(10); TC_EV(11);
         // sampling: the neighbours' symbols are drawn by the head warps (completion number hs covers steps < hs)
         if (MODE == MODE_SAMPLE && hs > 0) mbar_wait(bar_sym, (hs - 1) & 1);
@@ -624,15 +649,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
             tc_fence_before();
             mbar_arrive_a(bar_free_a + s * 8u);
             TC_EV(13);
-            const float4 bs = *reinterpret_cast<const float4*>(bSp);
-            const float4 bg = *reinterpret_cast<const float4*>(bSp + ldb);
-            const float bsv[4] = {bs.x, bs.y, bs.z, bs.w}, bgv[4] = {bg.x, bg.y, bg.z, bg.w};
+            float bsv[4] = {0.f, 0.f, 0.f, 0.f}, bgv[4] = {0.f, 0.f, 0.f, 0.f};
+            if (!BIASMMA) {
+              const float4 bs = *reinterpret_cast<const float4*>(bSp);
+              const float4 bg = *reinterpret_cast<const float4*>(bSp + ldb);
+              bsv[0] = bs.x; bsv[1] = bs.y; bsv[2] = bs.z; bsv[3] = bs.w;
+              bgv[0] = bg.x; bgv[1] = bg.y; bgv[2] = bg.z; bgv[3] = bg.w;
+            }
             float hnew[4], gu[4], gt[4], gm[4];
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
               // blocks: 0..2 = Wa, Wb, Wc of the candidate; 3..5 of the gate; 6 = Wmerge
-              const float sv = fmaf(cu, __uint_as_float(d[8 + e]), fmaf(cl, __uint_as_float(d[4 + e]), __uint_as_float(d[e]))) + bsv[e];
-              const float gv = fmaf(cu, __uint_as_float(d[20 + e]), fmaf(cl, __uint_as_float(d[16 + e]), __uint_as_float(d[12 + e]))) + bgv[e];
+              float sv = fmaf(cu, __uint_as_float(d[8 + e]), fmaf(cl, __uint_as_float(d[4 + e]), __uint_as_float(d[e])));
+              float gv = fmaf(cu, __uint_as_float(d[20 + e]), fmaf(cl, __uint_as_float(d[16 + e]), __uint_as_float(d[12 + e])));
+              if (!BIASMMA) { sv += bsv[e]; gv += bgv[e]; }
               const float mv = __uint_as_float(d[24 + e]);
               const float u = sigmoid_prescaled(gv);
               const float ht = tanh_prescaled(sv);
@@ -661,7 +691,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
             // 4 halves = 2 TMEM columns of the next operand's carry half; the same 8 bytes go to the ring image
             // (zeros for padding units and for rows past the end of the batch)
             __syncwarp();
-            if (has_next) tc_st2(a_carry, o);
+            uint2 ot = o;                                 // TMEM copy carries the constant 1 of the horizontal half
+            if (one_mine && p == one_p && carry_half == 0) { if (nh & 2) ot.y |= one_bits; else ot.x |= one_bits; }
+            if (has_next) tc_st2(a_carry, ot);
             *reinterpret_cast<uint2*>(ring_w + (uint32_t)(p >> 1) * TC_RING_QUAD + (uint32_t)(p & 1) * 8u) = o;
           }
           if (sv_i != nullptr) {
@@ -694,24 +726,25 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
       }  // steps
     }  // tiles
     TC_TOTAL(12);
-  } else {
-    // ======================= head warps: two rows per thread =======================
+  } else if (warp == TC_EPI_THREADS / 32 + 1) {
+    // ======================= head warp: four rows per thread =======================
     // Softmax / U(1) mask / draw or teacher forcing / running log-probability and phase of the rows, off the
     // tensor-core critical path: they consume the partial head sums one step behind the epilogue warps.  Transcendental
     // math in FP32 (this regime's tolerance is 1e-3), running sums in FP64.
-    const int hrow = tid - 32 - TC_EPI_THREADS;          // rows hrow and hrow + 64
+    const int hrow = tid - 32 - TC_EPI_THREADS;          // rows hrow + 32 k
     uint32_t hs = 0;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const long long row0 = tile * TC_ROWS;
       const int nrows = (int)((total_rows - row0 < (long long)TC_ROWS) ? (total_rows - row0) : (long long)TC_ROWS);
       const int ts0 = tile_q0(row0), q0 = ts0 * P.symL;
-      double rlogp[2] = {0.0, 0.0}, rphase[2] = {0.0, 0.0};
-      int rnup[2] = {0, 0}, rparent[2] = {0, 0};
-      float rcoef[2] = {0.f, 0.f};
-      bool live[2];
+      double rlogp[TC_HEAD_ROWS], rphase[TC_HEAD_ROWS];
+      int rnup[TC_HEAD_ROWS], rparent[TC_HEAD_ROWS];
+      float rcoef[TC_HEAD_ROWS];
+      bool live[TC_HEAD_ROWS];
 #pragma unroll
-      for (int k = 0; k < 2; ++k) {
+      for (int k = 0; k < TC_HEAD_ROWS; ++k) {
         const int row = hrow + k * TC_HEAD_THREADS;
+        rlogp[k] = 0.0; rphase[k] = 0.0; rnup[k] = 0; rparent[k] = 0; rcoef[k] = 0.f;
         live[k] = row < nrows;
         if (live[k] && MODE == MODE_CHILD) { const Child ch = P.children[row0 + row]; rparent[k] = ch.parent; rcoef[k] = ch.coef; }
       }
@@ -721,9 +754,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         TC_T0();
         mbar_wait_relaxed(bar_part + pb, (hs >> 1) & 1u);
         TC_ACC(13); TC_EV(20);
-        float l4[2][4];
+        float l4[TC_HEAD_ROWS][4];
 #pragma unroll
-        for (int k = 0; k < 2; ++k) {
+        for (int k = 0; k < TC_HEAD_ROWS; ++k) {
           const int row = hrow + k * TC_HEAD_THREADS;
           if (q == q0 && MODE == MODE_CHILD)            // the tile's symbol table is complete once its first step arrived
             for (int tt = 0; tt < ts0; ++tt) rnup[k] += symS[tt * TC_ROWS + row];
@@ -736,7 +769,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         }
         mbar_arrive(bar_pfree + pb);
 #pragma unroll
-        for (int k = 0; k < 2; ++k) {
+        for (int k = 0; k < TC_HEAD_ROWS; ++k) {
           const int row = hrow + k * TC_HEAD_THREADS;
           if (!live[k]) continue;
           float p0 = l4[k][0], p1 = l4[k][1];
@@ -778,7 +811,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
 
       // ---- tile results
 #pragma unroll
-      for (int k = 0; k < 2; ++k) {
+      for (int k = 0; k < TC_HEAD_ROWS; ++k) {
         const int row = hrow + k * TC_HEAD_THREADS;
         if (!live[k]) continue;
         if (MODE == MODE_CHILD) {
@@ -830,6 +863,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
 // (n ordered thread-major, see below).
 // variants: 0 both neighbours, 1 horizontal only, 2 vertical only.
 __global__ void pack_tc_kernel(const float* __restrict__ W, const float* __restrict__ Wg, const float* __restrict__ Wmerge,
+                               const float* __restrict__ b, const float* __restrict__ bg,
                                int nh, int nhp, int NP, __half* __restrict__ out) {
   const int kc = 2 * (nhp / 8);
   const long long per_pass = (long long)kc * (TC_N / 8) * 64;
@@ -848,7 +882,10 @@ __global__ void pack_tc_kernel(const float* __restrict__ W, const float* __restr
     const int sub = n / TC_TPS, blk = (n % TC_TPS) / 4, j = p * TC_JP + sub * 4 + (n % 4);
     const int slot = k / nhp, unit = tc_kunit(nhp, k - slot * nhp);   // K axis in thread-major order
     float v = 0.f;
-    if (unit < nh && j < nh) {
+    if (nh < nhp && slot == 0 && unit == nh && j < nh) {
+      // bias row: the operand carries a constant 1 at position num_units of the horizontal half (all variants)
+      v = (blk == 0) ? b[j] : (blk == 3 ? bg[j] : 0.f);
+    } else if (unit < nh && j < nh) {
       const int i = slot * nh + unit;
       if (blk == 6) {
         v = Wmerge[(long long)i * nh + j];
