@@ -128,3 +128,41 @@ class VMC:
         self.it += 1
         self.last = dict(samples=s, logp=lp, phase=ph, eloc=e, nconn=cnt, grad=grad)
         return mean_e, var
+
+
+def estimate_energy(engine, ham, ham_params, numsamples_estimation, numbatches, nsites, seed=111, row_offset=0,
+                    prefix_reuse=True, return_samples=False):
+    """Final-estimate pass: `numsamples_estimation` fresh samples in batches of `numbatches`, their
+    local energies, and  meanE/N, sqrt(var/n)/N  exactly as 2DHeisenberg/Run_RNNWF_2DHeis.py:356-387 and
+    RydbergKagome_2DGRU/Run_RNNWF_Rydberg.py:299-322 compute them (population variance, n = all samples of all ranks).
+    Pure reuse of the sampling and E_loc kernels; under torch.distributed every rank draws disjoint Philox rows and the
+    moments are all-reduced.  Returns dict(mean, err, var, n[, eloc, samples]) with per-site mean / error."""
+    nb = int(numsamples_estimation) // int(numbatches)
+    rank = dist.get_rank() if _dist_on() else 0
+    world = dist.get_world_size() if _dist_on() else 1
+    saved = engine.new_saved(numbatches) if prefix_reuse else None
+    elocs, samples = [], []
+    for i in range(nb):
+        off = row_offset + (i * world + rank) * int(numbatches)
+        s, lp, ph = engine.sample(numbatches, seed=seed, row_offset=off, saved=saved)
+        elocs.append(engine.local_energies(ham, ham_params, s, lp, ph, saved=saved))
+        if return_samples:
+            samples.append(s)
+    e = torch.cat(elocs)
+    n, mean_e, var, _ = energy_moments(e)
+    out = dict(mean=float(mean_e.real) / nsites,
+               err=math.sqrt(float(var) / float(n)) / nsites, var=float(var), n=int(n), eloc=e)
+    if return_samples:
+        out["samples"] = torch.cat(samples)
+    return out
+
+
+def site_densities(samples):
+    """Rydberg ground-state densities of the final-estimate pass (Run_RNNWF_Rydberg.py:331-336): per-site mean and
+    standard error, overall mean density and its error (std of the per-sample mean density / sqrt(n))."""
+    x = samples.to(torch.float64)
+    n = x.shape[0]
+    dens = x.mean(0)
+    dens_err = x.std(0, unbiased=False) / math.sqrt(n)
+    per_sample = x.reshape(n, -1).mean(1)
+    return dens, dens_err, float(x.mean()), float(per_sample.std(unbiased=False)) / math.sqrt(n)
