@@ -599,21 +599,27 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
     RNNWF_COUNT_LAUNCH(); bwd_tc_kernel<<<(unsigned)std::min<long long>(tiles, m.num_sms), BT_THREADS, bs.total, st>>>(B);
     // ---- parameter gradients: weights on the tensor cores (dw_tc.cuh), biases and heads as reductions
     {
-      std::vector<DwJob> jobs;
-      std::vector<int> cls_steps;
       DwParams D;
-      dw_plan(m, R, jobs, cls_steps, D.cls_count);
-      if (jobs.size() > 1024) { err = "rnnwf_backward: too many weight-gradient jobs"; return RNNWF_EINVAL; }
-      DwJob* d_jobs = reinterpret_cast<DwJob*>(ws + L.off_jobs);
-      int* d_cls = reinterpret_cast<int*>(ws + L.off_cls);
-      e = cudaMemcpyAsync(d_jobs, jobs.data(), jobs.size() * sizeof(DwJob), cudaMemcpyHostToDevice, st);
-      if (e == cudaSuccess) e = cudaMemcpyAsync(d_cls, cls_steps.data(), cls_steps.size() * sizeof(int), cudaMemcpyHostToDevice, st);
-      if (e != cudaSuccess) { err = std::string("rnnwf_backward plan upload: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
+      if (m.dw_rows != R) {             // plan depends on the row count only: build and upload once (blocking copy)
+        std::vector<DwJob> jobs;
+        std::vector<int> cls_steps;
+        dw_plan(m, R, jobs, cls_steps, m.dw_cls_count);
+        if (jobs.size() > 1024) { err = "rnnwf_backward: too many weight-gradient jobs"; return RNNWF_EINVAL; }
+        e = cudaMemcpy(m.d_dw_jobs, jobs.data(), jobs.size() * sizeof(DwJob), cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMemcpy(m.d_dw_cls, cls_steps.data(), cls_steps.size() * sizeof(int), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) { err = std::string("rnnwf_backward plan upload: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
+        m.dw_njobs = (int)jobs.size();
+        m.dw_rows = R;
+      }
+      for (int k = 0; k < 3; ++k) D.cls_count[k] = m.dw_cls_count[k];
+      const DwJob* d_jobs = reinterpret_cast<const DwJob*>(m.d_dw_jobs);
+      const int* d_cls = m.d_dw_cls;
+      const int njobs = m.dw_njobs;
       const float* himg = reinterpret_cast<const float*>(sb + sv.off_himg);
       D.jobs = d_jobs; D.cls_steps = d_cls; D.steps = m.d_steps; D.Q = m.Q; D.nh = nh; D.nhp = nhp; D.nsites = m.nsites;
       D.rows = R; D.tiles = tiles; D.cfg = cfg; D.site_of_t = m.d_site_of_t; D.dpT = B.dpT; D.himg = himg;
       D.gW = Gd("W"); D.gWg = Gd("Wg"); D.gWmerge = Gd("Wmerge");
-      RNNWF_COUNT_LAUNCH(); dw_tc_kernel<<<(unsigned)jobs.size(), DW_THREADS, dw_smem_bytes(nhp), st>>>(D);
+      RNNWF_COUNT_LAUNCH(); dw_tc_kernel<<<(unsigned)njobs, DW_THREADS, dw_smem_bytes(nhp), st>>>(D);
       const int nsplit = 16;
       RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, 0, m.Q, tiles, nhp, nsplit, Gd("b"));
       RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, 1, m.Q, tiles, nhp, nsplit, Gd("bg"));

@@ -58,6 +58,12 @@ struct rnnwf_model_impl {
   int tc_np = 0;
   unsigned char* d_tcB = nullptr;
   float* d_tcbias = nullptr;
+  // weight-gradient kernel work plan (dw_tc.cuh), cached on the device for the last row count it was built for
+  mutable long long dw_rows = -1;
+  mutable int dw_njobs = 0;
+  mutable int dw_cls_count[3] = {0, 0, 0};
+  void* d_dw_jobs = nullptr;        // [1024] DwJob
+  int* d_dw_cls = nullptr;          // [3][Q]
   const float* d_params = nullptr;  // last parameter vector handed to set_weights (caller-owned)
   bool weights_set = false;
 

@@ -541,7 +541,11 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
   }
   CREATE_TRY(backward_init());
-  if (m->tc_enabled) CREATE_TRY(backward_init_tc(*m));
+  if (m->tc_enabled) {
+    CREATE_TRY(backward_init_tc(*m));
+    CREATE_TRY(cudaMalloc(&m->d_dw_jobs, 1024 * sizeof(DwJob)));
+    CREATE_TRY(cudaMalloc(&m->d_dw_cls, (size_t)3 * m->Q * sizeof(int)));
+  }
 #undef CREATE_TRY
   *out = m;
   return RNNWF_OK;
@@ -551,7 +555,7 @@ int rnnwf_destroy(rnnwf_handle h) {
   if (h == nullptr) return RNNWF_OK;
   cudaFree(h->d_steps); cudaFree(h->d_variants); cudaFree(h->d_site_of_t); cudaFree(h->d_wpack);
   cudaFree(h->d_xtab); cudaFree(h->d_bias); cudaFree(h->d_head_w); cudaFree(h->d_head_b);
-  cudaFree(h->d_tcB); cudaFree(h->d_tcbias);
+  cudaFree(h->d_tcB); cudaFree(h->d_tcbias); cudaFree(h->d_dw_jobs); cudaFree(h->d_dw_cls);
   delete h;
   return RNNWF_OK;
 }
