@@ -10,9 +10,10 @@
 // the weights O(0.1), so the range is no issue and the 11-bit mantissa keeps E_loc within ~2e-4 of the FP32 path
 // (measured on the oracle: BF16 activations give 2.4e-3, which misses the 1e-3 bound of the reduced-precision mode).
 //
-//   warp 0       : MMA issue -- tcgen05.mma with the A operand in TMEM and the weights in shared memory (UMMA K-major
-//                  core-matrix layout), K loop fully unrolled, tcgen05.commit to the epilogue and to the loader.
-//                  Executes at the tensor-core floor (128 x 112 / 256 = 56 cycles per K=16 step).
+//   warps 0, 18  : MMA issue, one warp per accumulator buffer (even / odd column passes) -- tcgen05.mma with the A operand
+//                  in TMEM and the weights in shared memory (UMMA K-major core-matrix layout), K loop fully unrolled,
+//                  tcgen05.commit to the epilogue and to the loader.  Two issuers because a warp's waits after its own
+//                  MMAs only return once they have executed.  Biases ride on a constant-1 operand position.
 //   warp 19      : loader -- cp.async.bulk of the pre-packed weight images (mbarrier complete_tx) through 4 stages,
 //                  up to 4 column passes ahead, across sites and tiles.
 //   warps 1..16  : epilogue, four threads per row (row == TMEM lane; the four share the 16 units of every column pass).
@@ -20,7 +21,7 @@
 //                  FP16 straight into the next site's A operand in TMEM (tcgen05.st) and into the L2-resident
 //                  history ring; the older neighbour half of the next operand is prefetched from the ring one site
 //                  ahead.  No block barrier in the site loop.
-//   warps 17..18 : heads, two rows per thread: softmax / U(1) mask / draw / log-probability / phase, one site behind
+//   warp 17      : heads, four rows per thread: softmax / U(1) mask / draw / log-probability / phase, one site behind
 //                  the epilogue warps (partial head sums handed over in shared memory), off the critical path.
 // Everything is synchronised by mbarriers; every wait is bounded and traps instead of hanging.
 //
