@@ -442,20 +442,22 @@ inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   // after the reverse sweep instead of ~10 small launches per lattice site.
   L.batched = (m.cell == CELL_TENS2D || m.cell == CELL_TENSGRU2D);
   const long long nb = L.batched ? m.Q : 1;
+  // tensor-core regime of the tensorized GRU: the reverse sweep / weight-gradient kernels have their own layouts
+  // (d h tile-blocked, feature-major ds/dg/dm); none of the per-site FFMA-regime operands below is needed
+  const bool tcs = m.tc_enabled && m.cell == CELL_TENSGRU2D;
   long long o = 0;
-  L.off_dh = o;   o += al(std::max((long long)m.Q * R * m.nhp * 4, m.tc_enabled ? tc_dh_bytes(m.Q, R, m.tc_np) : 0LL));
-  L.off_dp = o;   o += al(nb * R * L.dpw * 4);
-  L.off_Z = o;    o += al(nb * R * (long long)L.Kz * 4);
-  L.off_dZ = o;   o += al(R * (long long)L.Kz * 4);   // tensorized cells: the per-step linearised operand P [R][7nh] lives here
-  L.off_hc = o;   o += al(nb * R * 2 * nh * 4);
-  L.off_dhc = o;  o += al(R * 2 * nh * 4);
+  L.off_dh = o;   o += al(tcs ? tc_dh_bytes(m.Q, R, m.tc_np) : (long long)m.Q * R * m.nhp * 4);
+  L.off_dp = o;   o += al(tcs ? 0 : nb * R * L.dpw * 4);
+  L.off_Z = o;    o += al(tcs ? 0 : nb * R * (long long)L.Kz * 4);
+  L.off_dZ = o;   o += al(tcs ? 0 : R * (long long)L.Kz * 4);   // tensorized cells: the per-step linearised operand P [R][7nh] lives here
+  L.off_hc = o;   o += al(tcs ? 0 : nb * R * 2 * nh * 4);
+  L.off_dhc = o;  o += al(tcs ? 0 : R * 2 * nh * 4);
   L.off_dlog = o; o += al(nb * R * 8 * 4);
   L.off_X = o;    o += al(R * 8 * 4);
   L.off_wstack = o; o += al(L.batched ? 3LL * 2 * nh * 7 * nh * 4 : 0);
   L.off_wimg = o;   o += al(m.tc_enabled ? 3LL * m.tc_np * BtSmem(m.nhp, m.Tsym, m.Q).b_bytes : 0);   // Wstack^T chunks of the reverse sweep
   L.off_dpT = o;    o += al(m.tc_enabled ? tc_dpt_bytes(m.Q, R, m.nhp) : 0);
-  L.off_jobs = o;   o += al(m.tc_enabled ? 1024LL * (long long)sizeof(DwJob) : 0);
-  L.off_cls = o;    o += al(m.tc_enabled ? 3LL * m.Q * 4 : 0);
+  L.off_jobs = o; L.off_cls = o;   // (the work plan lives in the handle)
   L.total = o;
   return L;
 }
@@ -558,7 +560,7 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
   Gemm G{st};
   G.tc = (m.precision == 1);
   float* wstack = reinterpret_cast<float*>(ws + L.off_wstack);
-  if (L.batched) {
+  if (L.batched && !(m.tc_enabled && m.cell == CELL_TENSGRU2D)) {
     const bool gru0 = m.cell == CELL_TENSGRU2D;
     RNNWF_COUNT_LAUNCH(); pack_wstack_kernel<<<512, 256, 0, st>>>(params + m.tensor("W")->offset, gru0 ? params + m.tensor("Wg")->offset : nullptr,
                                                      gru0 ? params + m.tensor("Wmerge")->offset : nullptr, nh, gru0 ? 1 : 0, wstack);
