@@ -380,7 +380,11 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
   return RNNWF_OK;
 }
 
-long long ring_bytes(const rnnwf_model& m, int grid, int Mp) { return (long long)grid * m.ring_len * Mp * m.nhp * 4; }
+long long ring_bytes(const rnnwf_model& m, int grid, int Mp) {
+  // tensor-core regime: one FP16 history image per slot in the fixed quad layout of sweep_tc.cuh (TC_RING_SLOT bytes)
+  const long long slot = m.tc_enabled ? std::max<long long>((long long)TC_RING_SLOT, (long long)Mp * m.nhp * 4) : (long long)Mp * m.nhp * 4;
+  return (long long)grid * m.ring_len * slot;
+}
 
 int set_saved(const rnnwf_model& m, SweepParams& P, void* saved, long long rows) {
   if (saved == nullptr) return RNNWF_OK;

@@ -620,7 +620,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         const float cl = (nb0 >= 0) ? (float)symS[nb0 * TC_ROWS + row] : 0.f;
         const float cu = (nb1 >= 0) ? (float)symS[nb1 * TC_ROWS + row] : 0.f;
         float lg[4] = {0.f, 0.f, 0.f, 0.f};
-        unsigned char* const ring_w = ring_base + (ring_off0 + (uint32_t)eq.z);  // this thread's first quad of this step's image
+        unsigned char* ring_p = ring_base + (ring_off0 + (uint32_t)eq.z);   // this thread's pieces of this step's image, in pass order
+        uint2 o_one = make_uint2(0u, 0u);
+        const uint32_t acc1 = acc0 + (uint32_t)TC_N;
+        const int p_act = (sub < subs_last) ? NP : NP - 1;                  // passes in which this thread owns real units
         const bool save = (MODE != MODE_CHILD) && live && (P.sv_hist != nullptr);
         float* sv_h = save ? P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + sub * 4 : nullptr;
         // saved gates, tile-blocked for the reverse sweep (bwd_tc.cuh: tc_gate_index): one float4 (4 units) per quantity
@@ -636,7 +639,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
 #pragma unroll 1
         for (int p = 0; p < NP; ++p) {
           const uint32_t s = (uint32_t)p & 1u;
-          const bool active = (p < NP - 1) || (sub < subs_last);     // warp-uniform: does this thread own real units?
+          const bool active = p < p_act;                              // warp-uniform
           mbar_wait_a(bar_mma_a + s * 8u, (phM >> s) & 1u); phM ^= 1u << s;
           TC_ACC(8); TC_EV(12);
           uint2 o = make_uint2(0u, 0u);
@@ -645,7 +648,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
             uint32_t d[TC_TPS];
             __syncwarp();
             tc_fence_after();
-            tc_ld28(acc0 + s * (uint32_t)TC_N, d);
+            tc_ld28(s ? acc1 : acc0, d);
             tc_wait_ld();
             tc_fence_before();
             mbar_arrive_a(bar_free_a + s * 8u);
@@ -692,11 +695,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
             // 4 halves = 2 TMEM columns of the next operand's carry half; the same 8 bytes go to the ring image
             // (zeros for padding units and for rows past the end of the batch)
             __syncwarp();
-            uint2 ot = o;                                 // TMEM copy carries the constant 1 of the horizontal half
-            if (one_mine && p == one_p && carry_half == 0) { if (nh & 2) ot.y |= one_bits; else ot.x |= one_bits; }
-            if (has_next) tc_st2(a_carry, ot);
-            *reinterpret_cast<uint2*>(ring_w + (uint32_t)(p >> 1) * TC_RING_QUAD + (uint32_t)(p & 1) * 8u) = o;
+            if (has_next) tc_st2(a_carry, o);
+            *reinterpret_cast<uint2*>(ring_p) = o;
+            if (p == one_p) o_one = o;                    // (kept for the constant-1 store after the loop)
           }
+          ring_p += (p & 1) ? (TC_RING_QUAD - 8u) : 8u;
           if (sv_i != nullptr) {
             const int j0 = p * TC_JP + sub * 4;
             if (j0 < hnc * 8) {
@@ -709,6 +712,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         }
         TC_EV(14);
         __syncwarp();
+        if (one_mine && has_next && carry_half == 0) {
+          // the TMEM copy of the horizontal half carries the constant 1 of the bias row: rewrite that piece (warp-uniform)
+          if (nh & 2) o_one.y |= one_bits; else o_one.x |= one_bits;
+          tc_st2(a_next + (uint32_t)(2 * one_p), o_one);
+        }
         if (has_next) {               // next step's operand complete: release the tensor core
           tc_wait_st();
           tc_fence_before();

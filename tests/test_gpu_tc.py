@@ -93,3 +93,31 @@ def test_tc_matches_fp32_regime_and_feeds_backward(cuda):
         gr = P[n].grad
         scale = float(gr.abs().max()) + 1e-30
         assert float((v.double() - gr).abs().max()) / scale < 1e-2, n
+
+
+@pytest.mark.gpu
+def test_tc_persistent_tiles_are_row_independent(cuda):
+    """More 128-row tiles than SMs (every CTA walks several tiles, the last one ragged): each row's result must not
+    depend on the batch it was evaluated in, and the backward of a big batch must equal the sum over its halves."""
+    eng = _mk(4, 4, 20, seed=91)
+    nsm = torch.cuda.get_device_properties(0).multi_processor_count
+    ns = nsm * 128 * 2 + 77
+    s, lp, ph = eng.sample(ns, seed=5)
+    saved = eng.new_saved(ns)
+    lp2, ph2 = eng.logpsi(s, saved=saved)
+    np.testing.assert_allclose(lp2.cpu().numpy(), lp.cpu().numpy(), rtol=1e-12, atol=1e-12)
+    cut = 128 * 37 + 5                                   # a split that is not tile-aligned
+    for lo, hi in ((0, cut), (cut, ns)):
+        l3, p3 = eng.logpsi(s[lo:hi])
+        assert torch.equal(l3, lp2[lo:hi]) and torch.equal(p3, ph2[lo:hi])
+    g = torch.Generator().manual_seed(3)
+    sl = (torch.randn(ns, generator=g, dtype=torch.float64) / ns).cuda()
+    sp = (torch.randn(ns, generator=g, dtype=torch.float64) / ns).cuda()
+    grad = eng.backward(s, saved, sl, sp).double()
+    parts = torch.zeros_like(grad)
+    for lo, hi in ((0, cut), (cut, ns)):
+        sv = eng.new_saved(hi - lo)
+        eng.logpsi(s[lo:hi], saved=sv)
+        parts += eng.backward(s[lo:hi], sv, sl[lo:hi], sp[lo:hi]).double()
+    scale = float(grad.abs().max())
+    assert float((grad - parts).abs().max()) < 2e-4 * scale    # same terms, different (atomic / split) summation order
