@@ -339,8 +339,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
     fence_mbar_init();
   }
   if (warp == 0) tc_alloc(tmem_slot, TC_TMEM_COLS);
-  for (int i = tid; i < (nhp + TC_JP) * 4; i += TC_THREADS) headW[i] = (i < nh * 4) ? P.head_w[i] : 0.f;
-  if (tid < 4) headB[tid] = P.head_b[tid];
+  for (int i = tid; i < (nhp + TC_JP) * 4; i += TC_THREADS) {     // packed heads are [unit][ND], ND = 2 (real) or 4 (complex)
+    const int j = i >> 2, d = i & 3;
+    headW[i] = (j < nh && d < P.ND) ? P.head_w[j * P.ND + d] : 0.f;
+  }
+  if (tid < 4) headB[tid] = (tid < P.ND) ? P.head_b[tid] : 0.f;
   for (int i = tid; i < 2 * ldb; i += TC_THREADS) {
     const int which = i / ldb, j = i - which * ldb;
     biasS[i] = (j < nh) ? P.tc_bias[which * nhp + j] * (which == 0 ? TC_SCALE_CAND : TC_SCALE_GATE) : 0.f;

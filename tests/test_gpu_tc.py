@@ -121,3 +121,34 @@ def test_tc_persistent_tiles_are_row_independent(cuda):
         parts += eng.backward(s[lo:hi], sv, sl[lo:hi], sp[lo:hi]).double()
     scale = float(grad.abs().max())
     assert float((grad - parts).abs().max()) < 2e-4 * scale    # same terms, different (atomic / split) summation order
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("complex_head,ns", [(False, 130), (True, 1), (True, 3)])
+def test_tc_real_head_and_tiny_batches(cuda, complex_head, ns):
+    """Real-valued heads (two logits per unit in the packed layout) and batches smaller than one tile, against the
+    FP32 regime on the same weights: sample with shared uniforms, log psi, local energies, gradient."""
+    kw = dict(cell=_lib.CELL_TENSGRU2D, nx=4, ny=4, num_units=20, complex_head=complex_head, u1=True, seed=17)
+    e32, e16 = Engine(precision="fp32", **kw), Engine(precision="tc", **kw)
+    g = torch.Generator().manual_seed(18)
+    p = e32.params.cpu() + 0.15 * (torch.rand(e32.params.shape, generator=g) - 0.5)
+    e32.set_weights(p)
+    e16.set_weights(p)
+    u = torch.rand(ns, 16, generator=g, dtype=torch.float32)
+    s, lp32, ph32 = e32.sample(ns, uniforms=u)
+    saved = e16.new_saved(ns)
+    lp16, ph16 = e16.logpsi(s, saved=saved)
+    np.testing.assert_allclose(lp16.cpu().numpy(), lp32.cpu().numpy(), rtol=RTOL, atol=1e-3)
+    np.testing.assert_allclose(ph16.cpu().numpy(), ph32.cpu().numpy(), rtol=RTOL, atol=1e-2)
+    ea = e32.local_energies(_lib.HAM_HEIS2D, [1.0], s, lp32, ph32).cpu().numpy()
+    eb = e16.local_energies(_lib.HAM_HEIS2D, [1.0], s, lp16, ph16, saved=saved).cpu().numpy()
+    np.testing.assert_allclose(eb, ea, rtol=5 * RTOL, atol=5 * RTOL * np.abs(ea).max())
+    sl = torch.randn(ns, generator=g, dtype=torch.float64) / ns
+    sp = torch.randn(ns, generator=g, dtype=torch.float64) / ns if complex_head else None
+    sv32 = e32.new_saved(ns)
+    e32.logpsi(s, saved=sv32)
+    ga = e32.backward(s, sv32, sl, sp).cpu().double()
+    gb = e16.backward(s, saved, sl, sp).cpu().double()
+    for n, v in e16.views(gb).items():
+        ref = e32.views(ga)[n]
+        assert float((v - ref).abs().max()) <= 1e-2 * (float(ref.abs().max()) + 1e-30), n
