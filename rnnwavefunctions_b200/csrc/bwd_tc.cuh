@@ -40,7 +40,7 @@ struct BtSmem {
     off_step = o;  o += Q * 8;                        // per site: neighbours (int16 x 2), flags
     off_bar = o;   o += 128;
     off_tmem = o;  o += 16;
-    off_sym = o;   o += ((Tsym * TC_ROWS) + 15) & ~15;
+    off_sym = o;   o += Tsym * 16;                    // symbols, one bit per (site, row)
     total = o;
   }
 };
@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
   unsigned char* const Bst = smem + L.off_B;                              // [2][b_bytes] weight chunk stages
   float* const headW = reinterpret_cast<float*>(smem + L.off_headw);      // [nhp + 16][4], zero past num_units / ND
   short4* const stepS = reinterpret_cast<short4*>(smem + L.off_step);     // per site: (nbr0, nbr1, site, has_inputs)
-  uint8_t* const symS = smem + L.off_sym;                                 // [Tsym][128]
+  uint32_t* const symS = reinterpret_cast<uint32_t*>(smem + L.off_sym);   // [Tsym][4] ballot words (tc_sym)
   uint64_t* const bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
   uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(smem + L.off_tmem);
   uint64_t* const bar_A = bars + 0;       // [2] operand chunk written to TMEM (512 arrivals)
@@ -299,15 +299,18 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
       // ---- symbol table of the tile
       {
         const int8_t* cf = P.cfg + (row0 + row) * P.nsites;
-        for (int t = sub; t < P.Tsym; t += TC_SUB) symS[t * TC_ROWS + row] = live ? (uint8_t)(cf[stepS[t].z] & 1) : (uint8_t)0;
+        for (int t = sub; t < P.Tsym; t += TC_SUB) {
+          const uint32_t w = __ballot_sync(0xffffffffu, live ? (cf[stepS[t].z] & 1) : 0);
+          if (lane == 0) symS[t * 4 + quarter] = w;
+        }
         quarter_barrier(quarter);
       }
       for (int q = P.Q - 1; q >= 0; --q) {
         const short4 sm = stepS[q];
         const int nb0 = sm.x, nb1 = sm.y;
         const bool has_in = sm.w != 0;
-        const float cl = (nb0 >= 0) ? (float)symS[nb0 * TC_ROWS + row] : 0.f;
-        const float cu = (nb1 >= 0) ? (float)symS[nb1 * TC_ROWS + row] : 0.f;
+        const float cl = (nb0 >= 0) ? (float)tc_sym(symS, nb0, row) : 0.f;
+        const float cu = (nb1 >= 0) ? (float)tc_sym(symS, nb1, row) : 0.f;
         float dl[4] = {0.f, 0.f, 0.f, 0.f};
         if (live) {
           const float* dlp = P.dlog + ((size_t)q * (size_t)P.rows + (size_t)(row0 + row)) * P.ND;

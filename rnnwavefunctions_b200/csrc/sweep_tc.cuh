@@ -82,7 +82,7 @@ struct TcSmem {
     off_step = o;  o += (Q > 0 ? Q : Tsym) * 16;                // per step: neighbours, carry half, ring slots (int4)
     off_bar = o;   o += 256;
     off_tmem = o;  o += 16;
-    off_sym = o;   o += ((Tsym * TC_ROWS) + 15) & ~15;
+    off_sym = o;   o += Tsym * 16;               // symbols, one bit per (site, row): 4 ballot words per site
     total = o + 1024;                          // slack for the 1024-byte alignment of the base
   }
 };
@@ -260,6 +260,9 @@ __device__ __forceinline__ float mufu_tanh(float x) { float y; asm("tanh.approx.
 __device__ __forceinline__ float sigmoid_prescaled(float x) { return fmaf(0.5f, mufu_tanh(x), 0.5f); }
 __device__ __forceinline__ float tanh_prescaled(float x) { return mufu_tanh(x); }
 
+// symbol of (site t, tile row) in the bit-packed table
+__device__ __forceinline__ int tc_sym(const uint32_t* symS, int t, int row) { return (int)((symS[t * 4 + (row >> 5)] >> (row & 31)) & 1u); }
+
 // K loop of one column pass.  HC > 0: fully unrolled, every operand address is base + immediate; HC == 0: generic.
 template <int HC>
 __device__ __forceinline__ void tc_issue_pass(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, int hc = HC) {
@@ -300,7 +303,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
   float4* const partS = reinterpret_cast<float4*>(smem + L.off_part);     // [2][128][TC_SUB] partial head sums
   short4* const metaS = reinterpret_cast<short4*>(smem + L.off_meta);     // per step: (nbr0, nbr1, site, -)
   int4* const stepT = reinterpret_cast<int4*>(smem + L.off_step);         // per step: see the set-up loop below
-  uint8_t* const symS = smem + L.off_sym;                                 // [Tsym][128]
+  uint32_t* const symS = reinterpret_cast<uint32_t*>(smem + L.off_sym);   // [Tsym][4]: bit (row & 31) of word row >> 5
   uint64_t* const bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
   uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(smem + L.off_tmem);
   uint64_t* const bar_A = bars + 0;                   // next operand written to TMEM (512 arrivals)
@@ -520,16 +523,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         Child ch;
         ch.parent = 0; ch.ta = 0; ch.tb = -1; ch.coef = 0.f; ch.ka = ch.kb = 0;
         if (live && MODE == MODE_CHILD) { ch = P.children[row0 + row]; rparent = ch.parent; }
-        if (live && MODE != MODE_SAMPLE) {
-          const long long src = (MODE == MODE_CHILD) ? (long long)ch.parent : row0 + row;
-          const int8_t* c = P.cfg_in + src * P.nsites;
-          for (int t = sub; t < P.Tsym; t += TC_SUB) {
-            int sy = c[metaS[t].z] & 1;
+        const long long src = (MODE == MODE_CHILD) ? (long long)ch.parent : row0 + row;
+        const int8_t* c = P.cfg_in + src * P.nsites;
+        for (int t = sub; t < P.Tsym; t += TC_SUB) {        // warp-uniform trip count: one ballot word per (site, 32 rows)
+          int sy = 0;
+          if (live && MODE != MODE_SAMPLE) {
+            sy = c[metaS[t].z] & 1;
             if (MODE == MODE_CHILD && (t == ch.ta || t == ch.tb)) sy ^= 1;
-            symS[t * TC_ROWS + row] = (uint8_t)sy;
           }
-        } else {
-          for (int t = sub; t < P.Tsym; t += TC_SUB) symS[t * TC_ROWS + row] = 0;
+          const uint32_t w = __ballot_sync(0xffffffffu, sy);
+          if (lane == 0) symS[t * 4 + quarter] = w;
         }
         quarter_barrier(quarter);
       }
@@ -553,7 +556,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           for (int i = 0; i < 8; ++i) {
             w[2 * i] = 0u; w[2 * i + 1] = 0u;
             if (i < np_own) {
-              const float4 v = __ldg(reinterpret_cast<const float4*>(psrc + i * TC_JP));
+              float4 v = __ldg(reinterpret_cast<const float4*>(psrc + i * TC_JP));
+              const int j = i * TC_JP + sub * 4;                   // padding units must be exact zeros in the operand
+              if (j + 0 >= nh) v.x = 0.f;
+              if (j + 1 >= nh) v.y = 0.f;
+              if (j + 2 >= nh) v.z = 0.f;
+              if (j + 3 >= nh) v.w = 0.f;
               w[2 * i] = pack_f16x2(v.x, v.y); w[2 * i + 1] = pack_f16x2(v.z, v.w);
             }
           }
@@ -620,8 +628,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         TC_ACC(10); TC_EV(11);
         // sampling: the neighbours' symbols are drawn by the head warps (completion number hs covers steps < hs)
         if (MODE == MODE_SAMPLE && hs > 0) mbar_wait(bar_sym, (hs - 1) & 1);
-        const float cl = (nb0 >= 0) ? (float)symS[nb0 * TC_ROWS + row] : 0.f;
-        const float cu = (nb1 >= 0) ? (float)symS[nb1 * TC_ROWS + row] : 0.f;
+        const float cl = (nb0 >= 0) ? (float)tc_sym(symS, nb0, row) : 0.f;
+        const float cu = (nb1 >= 0) ? (float)tc_sym(symS, nb1, row) : 0.f;
         float lg[4] = {0.f, 0.f, 0.f, 0.f};
         unsigned char* ring_p = ring_base + (ring_off0 + (uint32_t)eq.z);   // this thread's pieces of this step's image, in pass order
         uint2 o_one = make_uint2(0u, 0u);
@@ -685,7 +693,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
               o.x = pack_f16x2(hnew[0], hnew[1]);
               o.y = pack_f16x2(hnew[2], hnew[3]);
               if (save) {
-                *reinterpret_cast<float4*>(sv_h) = make_float4(hnew[0], hnew[1], hnew[2], hnew[3]);
                 sv_g[0] = make_float4(gu[0], gu[1], gu[2], gu[3]);
                 sv_g[TC_ROWS] = make_float4(gt[0], gt[1], gt[2], gt[3]);
                 sv_g[2 * TC_ROWS] = make_float4(gm[0], gm[1], gm[2], gm[3]);
@@ -694,6 +701,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           } else {
             mbar_arrive_a(bar_free_a + s * 8u);   // nothing to read: its columns of the narrow last pass are padding
           }
+          // saved history (FP32, row-major): padding units are written too (as zeros) -- prefix reuse reads whole pieces
+          if (save && p < np_own) *reinterpret_cast<float4*>(sv_h) = make_float4(hsave[0], hsave[1], hsave[2], hsave[3]);
           if (p < np_own) {
             // 4 halves = 2 TMEM columns of the next operand's carry half; the same 8 bytes go to the ring image
             // (zeros for padding units and for rows past the end of the batch)
@@ -771,7 +780,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         for (int k = 0; k < TC_HEAD_ROWS; ++k) {
           const int row = hrow + k * TC_HEAD_THREADS;
           if (q == q0 && MODE == MODE_CHILD)            // the tile's symbol table is complete once its first step arrived
-            for (int tt = 0; tt < ts0; ++tt) rnup[k] += symS[tt * TC_ROWS + row];
+            for (int tt = 0; tt < ts0; ++tt) rnup[k] += tc_sym(symS, tt, row);
           l4[k][0] = headB[0]; l4[k][1] = headB[1]; l4[k][2] = headB[2]; l4[k][3] = headB[3];
 #pragma unroll
           for (int i = 0; i < TC_SUB; ++i) {
@@ -783,7 +792,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
 #pragma unroll
         for (int k = 0; k < TC_HEAD_ROWS; ++k) {
           const int row = hrow + k * TC_HEAD_THREADS;
-          if (!live[k]) continue;
+          int sy = 0;
+          if (live[k]) {
           float p0 = l4[k][0], p1 = l4[k][1];
           const float mx = fmaxf(p0, p1);
           p0 = __expf(p0 - mx); p1 = __expf(p1 - mx);
@@ -796,7 +806,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
             const float nrm = p0 + p1;
             p0 = __fdividef(p0, nrm); p1 = __fdividef(p1, nrm);
           }
-          int sy;
           if (MODE == MODE_SAMPLE) {
             const float u = (P.uniforms != nullptr)
                                 ? P.uniforms[(size_t)(row0 + row) * P.Tsym + t]
@@ -804,9 +813,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
             const double tot = (double)p0 + (double)p1;
             const double target = (double)u * tot;
             sy = ((double)p0 <= target) ? 1 : 0;   // # of CDF entries <= target, clamped to the last class
-            symS[t * TC_ROWS + row] = (uint8_t)sy;
           } else {
-            sy = symS[t * TC_ROWS + row];
+            sy = tc_sym(symS, t, row);
           }
           rlogp[k] += (double)__logf(sy ? p1 : p0);
           if (P.complex_head) {
@@ -816,6 +824,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           rnup[k] += sy;
           if (P.sv_cum != nullptr && MODE != MODE_CHILD)
             P.sv_cum[(size_t)t * (size_t)P.sv_rows + (size_t)(row0 + row)] = make_double2(rlogp[k], rphase[k]);
+          }
+          if (MODE == MODE_SAMPLE) {      // drawn symbols of rows 32 k .. 32 k + 31: one ballot word (the head warp's lane == row & 31)
+            const uint32_t w = __ballot_sync(0xffffffffu, sy);
+            if (lane == 0) symS[t * 4 + k] = w;
+          }
         }
         if (MODE == MODE_SAMPLE) mbar_arrive(bar_sym);
         TC_ACC(14); TC_EV(21);
@@ -848,7 +861,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           if (P.out_phase != nullptr) P.out_phase[row0 + row] = rphase[k];
           if (MODE == MODE_SAMPLE && P.cfg_out != nullptr) {
             int8_t* c = P.cfg_out + (size_t)(row0 + row) * P.nsites;
-            for (int tt = 0; tt < P.Tsym; ++tt) c[metaS[tt].z] = (int8_t)symS[tt * TC_ROWS + row];
+            for (int tt = 0; tt < P.Tsym; ++tt) c[metaS[tt].z] = (int8_t)tc_sym(symS, tt, row);
           }
         }
       }

