@@ -152,3 +152,28 @@ def test_tc_real_head_and_tiny_batches(cuda, complex_head, ns):
     for n, v in e16.views(gb).items():
         ref = e32.views(ga)[n]
         assert float((v - ref).abs().max()) <= 1e-2 * (float(ref.abs().max()) + 1e-30), n
+
+
+@pytest.mark.gpu
+def test_tc_training_tracks_the_fp32_regime(cuda):
+    """End to end (north_star: 'variational energies agree within statistical error after equal training steps'):
+    the same VMC run -- 4x4 Heisenberg, Sz = 0, same Philox seeds, TF-Adam -- in both precision regimes.  The first
+    step sees identical weights (energies agree to 1e-3); afterwards the trajectories are statistically equivalent
+    and both move towards the exact ground state (-9.1892 for the 4x4 open square lattice)."""
+    from rnnwavefunctions_b200 import vmc
+    out = {}
+    for prec in ("fp32", "tc"):
+        eng = Engine(_lib.CELL_TENSGRU2D, 4, 4, num_units=20, complex_head=True, u1=True, seed=5, precision=prec)
+        eng.init_params(seed=5)
+        v = vmc.VMC(eng, _lib.HAM_HEIS2D, [0.0], 512, lr=5e-3, seed=21)
+        es = []
+        for it in range(80):
+            mean_e, var = v.step()
+            es.append(float(mean_e.real))
+        out[prec] = np.array(es)
+    a, b = out["fp32"], out["tc"]
+    assert abs(a[0] - b[0]) < 1e-3 * abs(a[0])
+    assert np.isfinite(b).all()
+    assert a[-10:].mean() < a[:3].mean() - 1.0 and b[-10:].mean() < b[:3].mean() - 1.0
+    assert abs(a[-10:].mean() - b[-10:].mean()) < 0.25
+    assert -9.2 < b[-10:].mean() < -5.0
