@@ -324,7 +324,7 @@ def main():
     ek["cell"] = getattr(_lib, "CELL_" + ek["cell"])
     precision = args.precision
     if precision == "auto":
-        precision = "tc" if w["eng"]["cell"] == "TENSGRU2D" else "fp32"
+        precision = "tc" if w["eng"]["cell"] in ("TENSGRU2D", "VANILLA2D") else "fp32"
     eng = Engine(seed=111, precision=precision, **ek)
     ham = getattr(_lib, "HAM_" + w["ham"])
     ns = w["ns"]
@@ -423,6 +423,8 @@ def main():
         npass = (w["eng"]["num_units"] + 15) // 16
         subs_last = (w["eng"]["num_units"] - 16 * (npass - 1) + 3) // 4       # the last column pass is issued only as wide as its real units
         ncols = 112 * (npass - 1) + (28 * subs_last + 15) // 16 * 16
+        if w["eng"]["cell"] == "VANILLA2D":
+            ncols = 112                                                       # one pass per site: 7 unit pieces x 4 threads x 4 units
         exec_flops = exec_sites * (2 * (2 * nhp) * ncols + 2 * w["eng"]["num_units"] * 4)
         achieved = exec_flops / (eloc_ms * 1e-3) / 1e12
         roofline = {"bound": "tensor", "kernel": "sweep_tc_kernel (MODE_CHILD)", "achieved": achieved, "peak": bf16_peak, "unit": "TFLOP/s",

@@ -455,8 +455,8 @@ inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   L.off_dlog = o; o += al(nb * R * 8 * 4);
   L.off_X = o;    o += al(R * 8 * 4);
   L.off_wstack = o; o += al(L.batched ? 3LL * 2 * nh * 7 * nh * 4 : 0);
-  L.off_wimg = o;   o += al(m.tc_enabled ? 3LL * m.tc_np * BtSmem(m.nhp, m.Tsym, m.Q).b_bytes : 0);   // Wstack^T chunks of the reverse sweep
-  L.off_dpT = o;    o += al(m.tc_enabled ? tc_dpt_bytes(m.Q, R, m.nhp) : 0);
+  L.off_wimg = o;   o += al(tcs ? 3LL * m.tc_np * BtSmem(m.nhp, m.Tsym, m.Q).b_bytes : 0);   // Wstack^T chunks of the reverse sweep
+  L.off_dpT = o;    o += al(tcs ? tc_dpt_bytes(m.Q, R, m.nhp) : 0);
   L.off_jobs = o; L.off_cls = o;   // (the work plan lives in the handle)
   L.total = o;
   return L;

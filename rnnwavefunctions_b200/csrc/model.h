@@ -77,12 +77,13 @@ struct rnnwf_model_impl {
     s.off_hist = 0;
     s.off_gates = al((long long)Q * rows * nhp * 4);
     // tensor-core regime: gates are saved tile-blocked, three float4 per (row, 4 units) (bwd_tc.cuh: tc_gate_index)
-    const long long gate_bytes = tc_enabled ? (long long)Q * ((rows + 127) / 128) * 4 * tc_np * 3 * 128 * 16
+    const bool tcs = tc_enabled && cell == CELL_TENSGRU2D;   // (the vanilla cell has no gates and no tensor-core backward)
+    const long long gate_bytes = tcs ? (long long)Q * ((rows + 127) / 128) * 4 * tc_np * 3 * 128 * 16
                                             : (gru_type ? (long long)Q * rows * Gp * 16 : 0);
     s.off_cum = s.off_gates + al(gate_bytes);
     s.off_himg = s.off_cum + al((long long)Tsym * rows * 16);
     // tensor-core regime: hidden states once more as ready-made B operand tiles of the weight-gradient kernel
-    const long long himg_bytes = tc_enabled ? (long long)Q * ((rows + 127) / 128) * (32LL * (((nhp + 15) / 16) * 2) * 32) * 4 : 0;
+    const long long himg_bytes = tcs ? (long long)Q * ((rows + 127) / 128) * (32LL * (((nhp + 15) / 16) * 2) * 32) * 4 : 0;
     s.total = s.off_himg + al(himg_bytes);
     return s;
   }

@@ -277,12 +277,14 @@ int build_model(rnnwf_model& m) {
     v.meta.b_off = (uint32_t)boff;
     boff += m.Gp;
   }
-  m.tc_enabled = (m.precision == 1 && m.cell == CELL_TENSGRU2D);
-  if (m.precision == 1 && !m.tc_enabled) return fail(RNNWF_EINVAL, "the tensor-core regime is implemented for the tensorized 2D GRU cell");
-  m.tc_np = (m.nh + TC_JP - 1) / TC_JP;
+  m.tc_enabled = (m.precision == 1 && (m.cell == CELL_TENSGRU2D || m.cell == CELL_VANILLA2D));
+  if (m.precision == 1 && !m.tc_enabled)
+    return fail(RNNWF_EINVAL, "the tensor-core regime is implemented for the tensorized 2D GRU and the vanilla 2D RNN cells");
+  // column passes per site: 16 units x 7 blocks each for the tensorized GRU; the vanilla cell needs one (7 unit pieces)
+  m.tc_np = (m.cell == CELL_VANILLA2D) ? 1 : (m.nh + TC_JP - 1) / TC_JP;
   if (m.tc_enabled) {
     const TcSmem ts(m.nhp, m.Tsym, m.Q);
-    if (ts.total > 227 * 1024 || 2 * TC_N + 2 * m.nhp > TC_TMEM_COLS || m.tc_np > 7)
+    if (ts.total > 227 * 1024 || 2 * TC_N + 2 * m.nhp > TC_TMEM_COLS || (m.nhp + TC_JP - 1) / TC_JP > 7)
       return fail(RNNWF_EINVAL, "the tensor-core regime needs num_units <= 104 (weight stages in shared memory, operand in TMEM)");
   }
   m.wpack_float4 = std::max(1LL, woff);
@@ -363,8 +365,10 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
   if (m.tc_enabled) {
     RNNWF_COUNT_LAUNCH();
     const bool bm = m.nh < m.nhp;     // biases through the tensor core when the operand has a free padding position
-#define RNNWF_TC_LAUNCH(MODE_) do { if (bm) sweep_tc_kernel<MODE_, true><<<s.grid, s.threads, s.smem, st>>>(P); \
-                                     else sweep_tc_kernel<MODE_, false><<<s.grid, s.threads, s.smem, st>>>(P); } while (0)
+    const bool van = m.cell == CELL_VANILLA2D;
+#define RNNWF_TC_LAUNCH(MODE_) do { if (van) sweep_tc_kernel<MODE_, false, 1><<<s.grid, s.threads, s.smem, st>>>(P); \
+                                     else if (bm) sweep_tc_kernel<MODE_, true, 0><<<s.grid, s.threads, s.smem, st>>>(P); \
+                                     else sweep_tc_kernel<MODE_, false, 0><<<s.grid, s.threads, s.smem, st>>>(P); } while (0)
     if (P.mode == MODE_SAMPLE) RNNWF_TC_LAUNCH(MODE_SAMPLE);
     else if (P.mode == MODE_CHILD) RNNWF_TC_LAUNCH(MODE_CHILD);
     else RNNWF_TC_LAUNCH(MODE_EVAL);
@@ -393,7 +397,7 @@ int set_saved(const rnnwf_model& m, SweepParams& P, void* saved, long long rows)
   P.sv_hist = reinterpret_cast<float*>(b + sv.off_hist);
   P.sv_gates = m.gru_type ? reinterpret_cast<float4*>(b + sv.off_gates) : nullptr;
   P.sv_cum = reinterpret_cast<double2*>(b + sv.off_cum);
-  P.sv_himg = m.tc_enabled ? reinterpret_cast<float*>(b + sv.off_himg) : nullptr;
+  P.sv_himg = (m.tc_enabled && m.cell == CELL_TENSGRU2D) ? reinterpret_cast<float*>(b + sv.off_himg) : nullptr;
   P.sv_rows = rows;
   return RNNWF_OK;
 }
@@ -536,16 +540,19 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
     const TcSmem ts(m->nhp, m->Tsym, m->Q);
     if (ts.total > 227 * 1024) { rnnwf_destroy(m); return fail(RNNWF_ENOMEM, "tensor-core sweep does not fit in shared memory for this lattice / width"); }
     CREATE_TRY(cudaMalloc(&m->d_tcB, (size_t)3 * m->tc_np * ts.b_bytes));
-    CREATE_TRY(cudaMalloc(&m->d_tcbias, (size_t)2 * m->nhp * 4));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaMalloc(&m->d_tcbias, (size_t)6 * m->nhp * 4));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE, true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL, true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
   }
   CREATE_TRY(backward_init());
-  if (m->tc_enabled) {
+  if (m->tc_enabled && m->cell == CELL_TENSGRU2D) {
     CREATE_TRY(backward_init_tc(*m));
     CREATE_TRY(cudaMalloc(&m->d_dw_jobs, 1024 * sizeof(DwJob)));
     CREATE_TRY(cudaMalloc(&m->d_dw_cls, (size_t)3 * m->Q * sizeof(int)));
@@ -630,12 +637,19 @@ int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
       bp ? params_dev + bp->offset : nullptr, h->nh, h->nhp, h->D, h->ND, h->d_head_w, h->d_head_b);
   if (h->tc_enabled) {
     const TcSmem ts(h->nhp, h->Tsym, h->Q);
-    const long long n = 3LL * h->tc_np * (ts.b_bytes / 2);
-    RNNWF_COUNT_LAUNCH(); pack_tc_kernel<<<std::min(2048, cdiv(n, 256)), 256, 0, st>>>(
-        params_dev + h->tensor("W")->offset, params_dev + h->tensor("Wg")->offset, params_dev + h->tensor("Wmerge")->offset,
-        params_dev + h->tensor("b")->offset, params_dev + h->tensor("bg")->offset,
-        h->nh, h->nhp, h->tc_np, reinterpret_cast<__half*>(h->d_tcB));
-    RNNWF_COUNT_LAUNCH(); pack_tc_bias_kernel<<<1, 256, 0, st>>>(params_dev + h->tensor("b")->offset, params_dev + h->tensor("bg")->offset, h->nh, h->nhp, h->d_tcbias);
+    if (h->cell == CELL_VANILLA2D) {
+      RNNWF_COUNT_LAUNCH(); pack_tc_vanilla_kernel<<<std::min(2048, cdiv((long long)ts.b_bytes / 2, 256)), 256, 0, st>>>(
+          params_dev + h->tensor("Wh")->offset, params_dev + h->tensor("Wv")->offset, h->nh, h->nhp, reinterpret_cast<__half*>(h->d_tcB));
+      RNNWF_COUNT_LAUNCH(); pack_tc_vanilla_bias_kernel<<<4, 256, 0, st>>>(params_dev + h->tensor("Uh")->offset, params_dev + h->tensor("Uv")->offset,
+                                                                           params_dev + h->tensor("b")->offset, h->nh, h->nhp, h->d_tcbias);
+    } else {
+      const long long n = 3LL * h->tc_np * (ts.b_bytes / 2);
+      RNNWF_COUNT_LAUNCH(); pack_tc_kernel<<<std::min(2048, cdiv(n, 256)), 256, 0, st>>>(
+          params_dev + h->tensor("W")->offset, params_dev + h->tensor("Wg")->offset, params_dev + h->tensor("Wmerge")->offset,
+          params_dev + h->tensor("b")->offset, params_dev + h->tensor("bg")->offset,
+          h->nh, h->nhp, h->tc_np, reinterpret_cast<__half*>(h->d_tcB));
+      RNNWF_COUNT_LAUNCH(); pack_tc_bias_kernel<<<1, 256, 0, st>>>(params_dev + h->tensor("b")->offset, params_dev + h->tensor("bg")->offset, h->nh, h->nhp, h->d_tcbias);
+    }
   }
   CUDA_TRY(cudaGetLastError());
   h->d_params = params_dev;

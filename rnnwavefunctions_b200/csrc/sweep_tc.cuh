@@ -76,7 +76,7 @@ struct TcSmem {
     off_B = o;   o += TC_STAGES * b_bytes;     // weight stages (the A operand lives in TMEM)
     off_headw = o; o += (nhp + TC_JP) * 16;     // head weights [unit][4], zero rows up to the last pass's end
     off_headb = o; o += 16;
-    off_bias = o;  o += ((2 * (nhp + TC_JP) * 4) + 15) & ~15;
+    off_bias = o;  o += 6 * (nhp + TC_JP) * 4;    // tGRU: b, bg; vanilla: b' of the 4 neighbour variants, dUh, dUv
     off_part = o;  o += 2 * TC_ROWS * TC_SUB * 16;   // partial head sums [2][128][TC_SUB] float4
     off_meta = o;  o += ((Q > 0 ? Q : Tsym) * 8 + 15) & ~15;   // per step: nbr0, nbr1, site, pad (int16 x 4)
     off_step = o;  o += (Q > 0 ? Q : Tsym) * 16;                // per step: neighbours, carry half, ring slots (int4)
@@ -291,7 +291,11 @@ __device__ __forceinline__ void tc_ld28(uint32_t taddr, uint32_t (&d)[TC_TPS]) {
 
 // BIASMMA: the biases ride on the tensor core (num_units < padded width): position `num_units` of the horizontal
 // neighbour half of every operand is a constant 1 and that K row of the weight images holds the biases.
-template <int MODE, bool BIASMMA>
+// CELLK: 0 = tensorized GRU (7 accumulator blocks per unit, 16 units per column pass); 1 = vanilla 2D RNN
+// (2DTFIM_2DRNN/MDRNNcell.py:21-35: elu(x_h Uh + h_h Wh + x_v Uv + h_v Wv + b)): one pass per site whose 7 "blocks" are
+// the 7 unit pieces a thread owns (unit = 16 blk + 4 sub + e); the neighbours are separable, so one weight image serves
+// every site, and the one-hot inputs / bias are added in the epilogue from small shared-memory tables.
+template <int MODE, bool BIASMMA, int CELLK>
 __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepParams P) {
   extern __shared__ __align__(128) unsigned char tc_smem[];   // no swizzle anywhere: 16-byte alignment is all the hardware needs
   unsigned char* const smem = tc_smem;
@@ -324,7 +328,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
   // The last column pass holds only num_units - 16 (NP - 1) real units: issue it just wide enough for the epilogue
   // threads that own them (28 columns each, rounded up to the MMA's N granularity of 16).
   const int subs_last = (nh - (NP - 1) * TC_JP + 3) / 4;
-  const uint32_t idesc_last = tc_idesc(TC_ROWS, ((subs_last * TC_TPS + 15) / 16) * 16);
+  const uint32_t idesc_last = (CELLK == 1) ? idesc : tc_idesc(TC_ROWS, ((subs_last * TC_TPS + 15) / 16) * 16);
   // TMEM map: [0, 224) two accumulator buffers; then two A operands of 8*hc columns each (2 halves per 32-bit column)
   const uint32_t acols = 8u * (uint32_t)hc;           // columns of one A operand ([h_h ; h_v], 16*hc halves)
 
@@ -347,9 +351,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
     headW[i] = (j < nh && d < P.ND) ? P.head_w[j * P.ND + d] : 0.f;
   }
   if (tid < 4) headB[tid] = (tid < P.ND) ? P.head_b[tid] : 0.f;
-  for (int i = tid; i < 2 * ldb; i += TC_THREADS) {
+  for (int i = tid; i < (CELLK == 1 ? 6 : 2) * ldb; i += TC_THREADS) {
     const int which = i / ldb, j = i - which * ldb;
-    biasS[i] = (j < nh) ? P.tc_bias[which * nhp + j] * (which == 0 ? TC_SCALE_CAND : TC_SCALE_GATE) : 0.f;
+    const float sc = (CELLK == 1) ? 1.0f : (which == 0 ? TC_SCALE_CAND : TC_SCALE_GATE);
+    biasS[i] = (j < nh) ? P.tc_bias[which * nhp + j] * sc : 0.f;
   }
   for (int i = tid; i < P.Q; i += TC_THREADS) {
     const StepMeta* m = P.steps + i;
@@ -464,7 +469,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
       const int q0 = tile_q0(tile * TC_ROWS) * P.symL;
       for (int q = q0; q < P.Q; ++q) {
         const short4 sm = metaS[q];
-        const int v = (sm.x >= 0 && sm.y < 0) ? 1 : ((sm.x < 0 && sm.y >= 0) ? 2 : 0);   // first site: any image (operand is zero)
+        const int v = (CELLK == 1) ? 0 : ((sm.x >= 0 && sm.y < 0) ? 1 : ((sm.x < 0 && sm.y >= 0) ? 2 : 0));   // first site: any image (operand is zero)
         const unsigned char* src = P.tc_B + (size_t)v * NP * L.b_bytes;
         for (int p = 0; p < NP; ++p, ++n) {
           const uint32_t s = n % TC_STAGES;
@@ -631,96 +636,145 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         const float cl = (nb0 >= 0) ? (float)tc_sym(symS, nb0, row) : 0.f;
         const float cu = (nb1 >= 0) ? (float)tc_sym(symS, nb1, row) : 0.f;
         float lg[4] = {0.f, 0.f, 0.f, 0.f};
-        unsigned char* ring_p = ring_base + (ring_off0 + (uint32_t)eq.z);   // this thread's pieces of this step's image, in pass order
         uint2 o_one = make_uint2(0u, 0u);
-        const uint32_t acc1 = acc0 + (uint32_t)TC_N;
-        const int p_act = (sub < subs_last) ? NP : NP - 1;                  // passes in which this thread owns real units
-        const bool save = (MODE != MODE_CHILD) && live && (P.sv_hist != nullptr);
-        float* sv_h = save ? P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + sub * 4 : nullptr;
-        // saved gates, tile-blocked for the reverse sweep (bwd_tc.cuh: tc_gate_index): one float4 (4 units) per quantity
-        float4* sv_g = save ? P.sv_gates + ((((size_t)q * (size_t)sv_tiles + (size_t)tile) * TC_SUB + sub) * NP) * 3 * TC_ROWS + row : nullptr;
-        uint32_t a_carry = a_next + (uint32_t)carry_half * hcols;
-        // hidden-state tile image for the weight-gradient kernel (dw_tc.cuh: [row / 4][unit / 8][unit % 8][row % 4]);
-        // rows past the end of the batch and padding units are written as zeros
-        const int hnc = ((nhp + 15) / 16) * 2;
-        float* sv_i = (MODE != MODE_CHILD && P.sv_himg != nullptr)
-            ? P.sv_himg + ((size_t)q * (size_t)sv_tiles + (size_t)tile) * (size_t)(32 * hnc * 32) + (size_t)(row >> 2) * hnc * 32 + (row & 3) : nullptr;
-        const float* bSp = bS;
-        const float* hWp = hW;
-#pragma unroll 1
-        for (int p = 0; p < NP; ++p) {
-          const uint32_t s = (uint32_t)p & 1u;
-          const bool active = p < p_act;                              // warp-uniform
-          mbar_wait_a(bar_mma_a + s * 8u, (phM >> s) & 1u); phM ^= 1u << s;
+        if constexpr (CELLK == 1) {
+          // ---- vanilla 2D RNN: one 112-column pass, accumulator block blk = this thread's unit piece blk
+          unsigned char* ring_p = ring_base + (ring_off0 + (uint32_t)eq.z);
+          const bool save = (MODE != MODE_CHILD) && live && (P.sv_hist != nullptr);
+          float* sv_h = save ? P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + sub * 4 : nullptr;
+          uint32_t a_carry = a_next + (uint32_t)carry_half * hcols;
+          // b' = b + Uh[0] (horizontal neighbour present) + Uv[0] (vertical present); dUh = Uh[1] - Uh[0], dUv likewise
+          const float* bv = biasS + (((nb0 >= 0) ? 1 : 0) + ((nb1 >= 0) ? 2 : 0)) * ldb + sub * 4;
+          const float* duh = biasS + 4 * ldb + sub * 4;
+          const float* duv = biasS + 5 * ldb + sub * 4;
+          mbar_wait_a(bar_mma_a, phM & 1u); phM ^= 1u;
           TC_ACC(8); TC_EV(12);
-          uint2 o = make_uint2(0u, 0u);
-          float hsave[4] = {0.f, 0.f, 0.f, 0.f};
-          if (active) {
-            uint32_t d[TC_TPS];
-            __syncwarp();
-            tc_fence_after();
-            tc_ld28(s ? acc1 : acc0, d);
-            tc_wait_ld();
-            tc_fence_before();
-            mbar_arrive_a(bar_free_a + s * 8u);
-            TC_EV(13);
-            float bsv[4] = {0.f, 0.f, 0.f, 0.f}, bgv[4] = {0.f, 0.f, 0.f, 0.f};
-            if (!BIASMMA) {
-              const float4 bs = *reinterpret_cast<const float4*>(bSp);
-              const float4 bg = *reinterpret_cast<const float4*>(bSp + ldb);
-              bsv[0] = bs.x; bsv[1] = bs.y; bsv[2] = bs.z; bsv[3] = bs.w;
-              bgv[0] = bg.x; bgv[1] = bg.y; bgv[2] = bg.z; bgv[3] = bg.w;
-            }
-            float hnew[4], gu[4], gt[4], gm[4];
+          uint32_t d[TC_TPS];
+          __syncwarp();
+          tc_fence_after();
+          tc_ld28(acc0, d);
+          tc_wait_ld();
+          tc_fence_before();
+          mbar_arrive_a(bar_free_a);
+          TC_EV(13);
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              // blocks: 0..2 = Wa, Wb, Wc of the candidate; 3..5 of the gate; 6 = Wmerge
-              float sv = fmaf(cu, __uint_as_float(d[8 + e]), fmaf(cl, __uint_as_float(d[4 + e]), __uint_as_float(d[e])));
-              float gv = fmaf(cu, __uint_as_float(d[20 + e]), fmaf(cl, __uint_as_float(d[16 + e]), __uint_as_float(d[12 + e])));
-              if (!BIASMMA) { sv += bsv[e]; gv += bgv[e]; }
-              const float mv = __uint_as_float(d[24 + e]);
-              const float u = sigmoid_prescaled(gv);
-              const float ht = tanh_prescaled(sv);
-              // u ht + (1 - u) m.  Padding units (>= num_units) have zero weights and biases: u = 1/2, ht = m = 0 -> 0.
-              const float hv = fmaf(u, ht - mv, mv);
-              hnew[e] = hv;
-              const float4 w = *reinterpret_cast<const float4*>(hWp + e * 4);
-              lg[0] = fmaf(hv, w.x, lg[0]); lg[1] = fmaf(hv, w.y, lg[1]); lg[2] = fmaf(hv, w.z, lg[2]); lg[3] = fmaf(hv, w.w, lg[3]);
-              gu[e] = u; gt[e] = ht; gm[e] = mv;
-            }
-            if (live) {
-              hsave[0] = hnew[0]; hsave[1] = hnew[1]; hsave[2] = hnew[2]; hsave[3] = hnew[3];
+          for (int blk = 0; blk < TC_NB; ++blk) {
+            if (blk < np_own) {                                     // warp-uniform
+              const float4 b4 = *reinterpret_cast<const float4*>(bv + blk * TC_JP);
+              const float4 h4 = *reinterpret_cast<const float4*>(duh + blk * TC_JP);
+              const float4 v4 = *reinterpret_cast<const float4*>(duv + blk * TC_JP);
+              const float bb[4] = {b4.x, b4.y, b4.z, b4.w}, hh[4] = {h4.x, h4.y, h4.z, h4.w}, vv[4] = {v4.x, v4.y, v4.z, v4.w};
+              float hnew[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float x = fmaf(cu, vv[e], fmaf(cl, hh[e], __uint_as_float(d[blk * 4 + e]) + bb[e]));
+                const float hv = (x > 0.f) ? x : (__expf(x) - 1.0f);      // elu; padding units: x = 0 -> 0
+                hnew[e] = live ? hv : 0.f;
+                const float4 w = *reinterpret_cast<const float4*>(hW + blk * (TC_JP * 4) + e * 4);
+                lg[0] = fmaf(hv, w.x, lg[0]); lg[1] = fmaf(hv, w.y, lg[1]); lg[2] = fmaf(hv, w.z, lg[2]); lg[3] = fmaf(hv, w.w, lg[3]);
+              }
+              uint2 o;
               o.x = pack_f16x2(hnew[0], hnew[1]);
               o.y = pack_f16x2(hnew[2], hnew[3]);
-              if (save) {
-                sv_g[0] = make_float4(gu[0], gu[1], gu[2], gu[3]);
-                sv_g[TC_ROWS] = make_float4(gt[0], gt[1], gt[2], gt[3]);
-                sv_g[2 * TC_ROWS] = make_float4(gm[0], gm[1], gm[2], gm[3]);
+              if (save) *reinterpret_cast<float4*>(sv_h + blk * TC_JP) = make_float4(hnew[0], hnew[1], hnew[2], hnew[3]);
+              __syncwarp();
+              if (has_next) tc_st2(a_carry + (uint32_t)(2 * blk), o);
+              *reinterpret_cast<uint2*>(ring_p) = o;
+              ring_p += (blk & 1) ? (TC_RING_QUAD - 8u) : 8u;
+            }
+          }
+          TC_ACC(9);
+        } else {
+          unsigned char* ring_p = ring_base + (ring_off0 + (uint32_t)eq.z);   // this thread's pieces of this step's image, in pass order
+          const uint32_t acc1 = acc0 + (uint32_t)TC_N;
+          const int p_act = (sub < subs_last) ? NP : NP - 1;                  // passes in which this thread owns real units
+          const bool save = (MODE != MODE_CHILD) && live && (P.sv_hist != nullptr);
+          float* sv_h = save ? P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + sub * 4 : nullptr;
+          // saved gates, tile-blocked for the reverse sweep (bwd_tc.cuh: tc_gate_index): one float4 (4 units) per quantity
+          float4* sv_g = save ? P.sv_gates + ((((size_t)q * (size_t)sv_tiles + (size_t)tile) * TC_SUB + sub) * NP) * 3 * TC_ROWS + row : nullptr;
+          uint32_t a_carry = a_next + (uint32_t)carry_half * hcols;
+          // hidden-state tile image for the weight-gradient kernel (dw_tc.cuh: [row / 4][unit / 8][unit % 8][row % 4]);
+          // rows past the end of the batch and padding units are written as zeros
+          const int hnc = ((nhp + 15) / 16) * 2;
+          float* sv_i = (MODE != MODE_CHILD && P.sv_himg != nullptr)
+              ? P.sv_himg + ((size_t)q * (size_t)sv_tiles + (size_t)tile) * (size_t)(32 * hnc * 32) + (size_t)(row >> 2) * hnc * 32 + (row & 3) : nullptr;
+          const float* bSp = bS;
+          const float* hWp = hW;
+  #pragma unroll 1
+          for (int p = 0; p < NP; ++p) {
+            const uint32_t s = (uint32_t)p & 1u;
+            const bool active = p < p_act;                              // warp-uniform
+            mbar_wait_a(bar_mma_a + s * 8u, (phM >> s) & 1u); phM ^= 1u << s;
+            TC_ACC(8); TC_EV(12);
+            uint2 o = make_uint2(0u, 0u);
+            float hsave[4] = {0.f, 0.f, 0.f, 0.f};
+            if (active) {
+              uint32_t d[TC_TPS];
+              __syncwarp();
+              tc_fence_after();
+              tc_ld28(s ? acc1 : acc0, d);
+              tc_wait_ld();
+              tc_fence_before();
+              mbar_arrive_a(bar_free_a + s * 8u);
+              TC_EV(13);
+              float bsv[4] = {0.f, 0.f, 0.f, 0.f}, bgv[4] = {0.f, 0.f, 0.f, 0.f};
+              if (!BIASMMA) {
+                const float4 bs = *reinterpret_cast<const float4*>(bSp);
+                const float4 bg = *reinterpret_cast<const float4*>(bSp + ldb);
+                bsv[0] = bs.x; bsv[1] = bs.y; bsv[2] = bs.z; bsv[3] = bs.w;
+                bgv[0] = bg.x; bgv[1] = bg.y; bgv[2] = bg.z; bgv[3] = bg.w;
+              }
+              float hnew[4], gu[4], gt[4], gm[4];
+  #pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                // blocks: 0..2 = Wa, Wb, Wc of the candidate; 3..5 of the gate; 6 = Wmerge
+                float sv = fmaf(cu, __uint_as_float(d[8 + e]), fmaf(cl, __uint_as_float(d[4 + e]), __uint_as_float(d[e])));
+                float gv = fmaf(cu, __uint_as_float(d[20 + e]), fmaf(cl, __uint_as_float(d[16 + e]), __uint_as_float(d[12 + e])));
+                if (!BIASMMA) { sv += bsv[e]; gv += bgv[e]; }
+                const float mv = __uint_as_float(d[24 + e]);
+                const float u = sigmoid_prescaled(gv);
+                const float ht = tanh_prescaled(sv);
+                // u ht + (1 - u) m.  Padding units (>= num_units) have zero weights and biases: u = 1/2, ht = m = 0 -> 0.
+                const float hv = fmaf(u, ht - mv, mv);
+                hnew[e] = hv;
+                const float4 w = *reinterpret_cast<const float4*>(hWp + e * 4);
+                lg[0] = fmaf(hv, w.x, lg[0]); lg[1] = fmaf(hv, w.y, lg[1]); lg[2] = fmaf(hv, w.z, lg[2]); lg[3] = fmaf(hv, w.w, lg[3]);
+                gu[e] = u; gt[e] = ht; gm[e] = mv;
+              }
+              if (live) {
+                hsave[0] = hnew[0]; hsave[1] = hnew[1]; hsave[2] = hnew[2]; hsave[3] = hnew[3];
+                o.x = pack_f16x2(hnew[0], hnew[1]);
+                o.y = pack_f16x2(hnew[2], hnew[3]);
+                if (save) {
+                  sv_g[0] = make_float4(gu[0], gu[1], gu[2], gu[3]);
+                  sv_g[TC_ROWS] = make_float4(gt[0], gt[1], gt[2], gt[3]);
+                  sv_g[2 * TC_ROWS] = make_float4(gm[0], gm[1], gm[2], gm[3]);
+                }
+              }
+            } else {
+              mbar_arrive_a(bar_free_a + s * 8u);   // nothing to read: its columns of the narrow last pass are padding
+            }
+            // saved history (FP32, row-major): padding units are written too (as zeros) -- prefix reuse reads whole pieces
+            if (save && p < np_own) *reinterpret_cast<float4*>(sv_h) = make_float4(hsave[0], hsave[1], hsave[2], hsave[3]);
+            if (p < np_own) {
+              // 4 halves = 2 TMEM columns of the next operand's carry half; the same 8 bytes go to the ring image
+              // (zeros for padding units and for rows past the end of the batch)
+              __syncwarp();
+              if (has_next) tc_st2(a_carry, o);
+              *reinterpret_cast<uint2*>(ring_p) = o;
+              if (p == one_p) o_one = o;                    // (kept for the constant-1 store after the loop)
+            }
+            ring_p += (p & 1) ? (TC_RING_QUAD - 8u) : 8u;
+            if (sv_i != nullptr) {
+              const int j0 = p * TC_JP + sub * 4;
+              if (j0 < hnc * 8) {
+  #pragma unroll
+                for (int e = 0; e < 4; ++e) sv_i[((j0 + e) >> 3) * 32 + ((j0 + e) & 7) * 4] = hsave[e];
               }
             }
-          } else {
-            mbar_arrive_a(bar_free_a + s * 8u);   // nothing to read: its columns of the narrow last pass are padding
+            a_carry += 2u; bSp += TC_JP; hWp += TC_JP * 4; sv_h += TC_JP; sv_g += 3 * TC_ROWS;
+            TC_ACC(9);
           }
-          // saved history (FP32, row-major): padding units are written too (as zeros) -- prefix reuse reads whole pieces
-          if (save && p < np_own) *reinterpret_cast<float4*>(sv_h) = make_float4(hsave[0], hsave[1], hsave[2], hsave[3]);
-          if (p < np_own) {
-            // 4 halves = 2 TMEM columns of the next operand's carry half; the same 8 bytes go to the ring image
-            // (zeros for padding units and for rows past the end of the batch)
-            __syncwarp();
-            if (has_next) tc_st2(a_carry, o);
-            *reinterpret_cast<uint2*>(ring_p) = o;
-            if (p == one_p) o_one = o;                    // (kept for the constant-1 store after the loop)
-          }
-          ring_p += (p & 1) ? (TC_RING_QUAD - 8u) : 8u;
-          if (sv_i != nullptr) {
-            const int j0 = p * TC_JP + sub * 4;
-            if (j0 < hnc * 8) {
-#pragma unroll
-              for (int e = 0; e < 4; ++e) sv_i[((j0 + e) >> 3) * 32 + ((j0 + e) & 7) * 4] = hsave[e];
-            }
-          }
-          a_carry += 2u; bSp += TC_JP; hWp += TC_JP * 4; sv_h += TC_JP; sv_g += 3 * TC_ROWS;
-          TC_ACC(9);
         }
         TC_EV(14);
         __syncwarp();
@@ -931,6 +985,41 @@ __global__ void pack_tc_bias_kernel(const float* __restrict__ b, const float* __
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * nhp; i += gridDim.x * blockDim.x) {
     const int which = i / nhp, j = i - which * nhp;
     out[i] = (j < nh) ? (which == 0 ? b[j] : bg[j]) : 0.f;
+  }
+}
+
+// ---- vanilla 2D RNN (CELLK = 1): one image [k-core kc][n-core 14][8 rows][8 halves], B[n][k] = W_half[unit(k)][unit(n)]
+// with n = sub * 28 + blk * 4 + e  <->  output unit 16 blk + 4 sub + e, k in the thread-major order of the operand.
+__global__ void pack_tc_vanilla_kernel(const float* __restrict__ Wh, const float* __restrict__ Wv, int nh, int nhp, __half* __restrict__ out) {
+  const int kc = 2 * (nhp / 8);
+  const long long total = (long long)kc * (TC_N / 8) * 64;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    long long r = idx;
+    const int e = (int)(r % 8); r /= 8;
+    const int r8 = (int)(r % 8); r /= 8;
+    const int ni = (int)(r % (TC_N / 8)); r /= (TC_N / 8);
+    const int ki = (int)r;
+    const int n = ni * 8 + r8, k = ki * 8 + e;
+    const int sub = n / TC_TPS, blk = (n % TC_TPS) / 4, j = blk * TC_JP + sub * 4 + (n % 4);
+    const int slot = k / nhp, unit = tc_kunit(nhp, k - slot * nhp);
+    float v = 0.f;
+    if (unit < nh && j < nh) v = (slot == 0 ? Wh : Wv)[(long long)unit * nh + j];
+    out[idx] = __float2half_rn(v);
+  }
+}
+// bias / input tables [6][nhp]: b' of the four neighbour variants (bit 0: horizontal present, bit 1: vertical present),
+// then dUh = Uh[1] - Uh[0], dUv = Uv[1] - Uv[0]   (one-hot inputs: x U = U[0] + sigma (U[1] - U[0]); absent neighbour: 0)
+__global__ void pack_tc_vanilla_bias_kernel(const float* __restrict__ Uh, const float* __restrict__ Uv, const float* __restrict__ b,
+                                            int nh, int nhp, float* __restrict__ out) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 6 * nhp; i += gridDim.x * blockDim.x) {
+    const int which = i / nhp, j = i - which * nhp;
+    float v = 0.f;
+    if (j < nh) {
+      if (which < 4) v = b[j] + ((which & 1) ? Uh[j] : 0.f) + ((which & 2) ? Uv[j] : 0.f);
+      else if (which == 4) v = Uh[nh + j] - Uh[j];
+      else v = Uv[nh + j] - Uv[j];
+    }
+    out[i] = v;
   }
 }
 

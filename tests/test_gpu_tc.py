@@ -177,3 +177,61 @@ def test_tc_training_tracks_the_fp32_regime(cuda):
     assert a[-10:].mean() < a[:3].mean() - 1.0 and b[-10:].mean() < b[:3].mean() - 1.0
     assert abs(a[-10:].mean() - b[-10:].mean()) < 0.25
     assert -9.2 < b[-10:].mean() < -5.0
+
+
+def _mk_vanilla(nx, ny, nh, seed=31, precision="tc"):
+    eng = Engine(_lib.CELL_VANILLA2D, nx, ny, num_units=nh, seed=seed, precision=precision)
+    g = torch.Generator().manual_seed(seed + 1)
+    p = eng.params.cpu()
+    eng.set_weights(p + 0.15 * (torch.rand(p.shape, generator=g) - 0.5))
+    return eng
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nx,ny,nh,ns", [(5, 4, 50, 300), (12, 12, 50, 130), (3, 3, 10, 40), (4, 4, 64, 129)])
+def test_tc_vanilla_sample_and_logpsi(cuda, nx, ny, nh, ns):
+    """2DTFIM_2DRNN vanilla cell in the tensor-core regime against the float64 oracle (same bounds as the tGRU)."""
+    eng = _mk_vanilla(nx, ny, nh)
+    assert "tcgen05" in eng.describe()
+    u = torch.rand(ns, eng.nsteps, generator=torch.Generator().manual_seed(ns), dtype=torch.float32)
+    s, lp, ph = eng.sample(ns, uniforms=u)
+    P = oracle_params(eng)
+    with torch.no_grad():
+        ref = oracle_run(eng, P, uniforms=u, numsamples=ns)
+    ok = (ref["margin"].min(dim=1).values > 1e-3).numpy()
+    assert ok.mean() > 0.4
+    s_cpu = s.cpu().long().numpy()
+    assert (s_cpu[ok] == ref["samples"].numpy()[ok]).all()
+    scale = np.abs(ref["logp"].numpy()).max()
+    np.testing.assert_allclose(lp.cpu().numpy()[ok], ref["logp"].numpy()[ok], rtol=RTOL, atol=RTOL * scale * 0.1)
+    lp2, _ = eng.logpsi(s)
+    np.testing.assert_allclose(lp2.cpu().numpy(), lp.cpu().numpy(), rtol=1e-12, atol=1e-12)
+    with torch.no_grad():
+        ref2 = oracle_run(eng, P, samples=s_cpu)
+    np.testing.assert_allclose(lp2.cpu().numpy(), ref2["logp"].numpy(), rtol=RTOL, atol=RTOL * scale * 0.1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("reuse", [False, True])
+def test_tc_vanilla_tfim2d_local_energies_and_gradient(cuda, reuse):
+    Nx, Ny, ns = 5, 4, 300
+    eng = _mk_vanilla(Nx, Ny, 50, seed=41)
+    e32 = Engine(_lib.CELL_VANILLA2D, Nx, Ny, num_units=50, seed=41, precision="fp32")
+    e32.set_weights(eng.params)
+    saved = eng.new_saved(ns)
+    s, lp, ph = eng.sample(ns, seed=6, saved=saved)
+    Jz = np.random.RandomState(0).uniform(0.5, 1.5, (Nx, Ny))
+    hp = np.concatenate([[3.0], Jz.reshape(-1)])
+    e = eng.local_energies(_lib.HAM_TFIM2D, hp, s, lp, ph, saved=saved if reuse else None).cpu().numpy()
+    ref = ole.ising2d_local_energies(Jz, 3.0, s.cpu().numpy().astype(np.int64), oracle_logpsi_fn(eng, oracle_params(eng)))
+    np.testing.assert_allclose(e.real, ref, rtol=RTOL, atol=RTOL * np.abs(ref).max())
+    # gradient: generic backward over the history the tensor-core sweep saved, against the FP32 regime
+    g = torch.Generator().manual_seed(3)
+    sl = torch.randn(ns, generator=g, dtype=torch.float64) / ns
+    sv32 = e32.new_saved(ns)
+    e32.logpsi(s, saved=sv32)
+    ga = e32.backward(s, sv32, sl).cpu().double()
+    gb = eng.backward(s, saved, sl).cpu().double()
+    for n, v in eng.views(gb).items():
+        r = e32.views(ga)[n]
+        assert float((v - r).abs().max()) <= 1e-2 * (float(r.abs().max()) + 1e-30), n
