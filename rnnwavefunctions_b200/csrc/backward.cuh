@@ -424,7 +424,9 @@ inline cudaError_t backward_init() {
 }
 inline int dw_smem_bytes(int nhp) { return 2 * tc_himg_floats(nhp) * 4 + 256; }
 inline cudaError_t backward_init_tc(const rnnwf_model_impl& m) {
-  cudaError_t e = cudaFuncSetAttribute(bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BtSmem(m.nhp, m.Tsym, m.Q).total);
+  cudaError_t e = cudaFuncSetAttribute(bwd_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, BtSmem(m.nhp, m.Tsym, m.Q).total);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(bwd_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, BtSmem(m.nhp, m.Tsym, m.Q).total);
   if (e != cudaSuccess) return e;
   return cudaFuncSetAttribute(dw_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dw_smem_bytes(m.nhp));
 }
@@ -444,18 +446,18 @@ inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   const long long nb = L.batched ? m.Q : 1;
   // tensor-core regime of the tensorized GRU: the reverse sweep / weight-gradient kernels have their own layouts
   // (d h tile-blocked, feature-major ds/dg/dm); none of the per-site FFMA-regime operands below is needed
-  const bool tcs = m.tc_enabled && m.cell == CELL_TENSGRU2D;
+  const bool tcs = m.tc_enabled;   // (tensorized GRU and vanilla 2D RNN both have the tensor-core backward)
   long long o = 0;
-  L.off_dh = o;   o += al(tcs ? tc_dh_bytes(m.Q, R, m.tc_np) : (long long)m.Q * R * m.nhp * 4);
+  L.off_dh = o;   o += al(tcs ? tc_dh_bytes(m.Q, R, (m.nhp + TC_JP - 1) / TC_JP) : (long long)m.Q * R * m.nhp * 4);
   L.off_dp = o;   o += al(tcs ? 0 : nb * R * L.dpw * 4);
   L.off_Z = o;    o += al(tcs ? 0 : nb * R * (long long)L.Kz * 4);
   L.off_dZ = o;   o += al(tcs ? 0 : R * (long long)L.Kz * 4);   // tensorized cells: the per-step linearised operand P [R][7nh] lives here
   L.off_hc = o;   o += al(tcs ? 0 : nb * R * 2 * nh * 4);
   L.off_dhc = o;  o += al(tcs ? 0 : R * 2 * nh * 4);
-  L.off_dlog = o; o += al(nb * R * 8 * 4);
+  L.off_dlog = o; o += al(((L.batched || tcs) ? (long long)m.Q : 1LL) * R * 8 * 4);   // d(logits) of all sites in the batched / tensor-core paths
   L.off_X = o;    o += al(R * 8 * 4);
   L.off_wstack = o; o += al(L.batched ? 3LL * 2 * nh * 7 * nh * 4 : 0);
-  L.off_wimg = o;   o += al(tcs ? 3LL * m.tc_np * BtSmem(m.nhp, m.Tsym, m.Q).b_bytes : 0);   // Wstack^T chunks of the reverse sweep
+  L.off_wimg = o;   o += al(tcs ? 3LL * ((m.nhp + TC_JP - 1) / TC_JP) * BtSmem(m.nhp, m.Tsym, m.Q).b_bytes : 0);   // Wstack^T chunks of the reverse sweep
   L.off_dpT = o;    o += al(tcs ? tc_dpt_bytes(m.Q, R, m.nhp) : 0);
   L.off_jobs = o; L.off_cls = o;   // (the work plan lives in the handle)
   L.total = o;
@@ -476,13 +478,13 @@ inline void dw_plan(const rnnwf_model_impl& m, long long R, std::vector<DwJob>& 
   struct Group { int src, half, cls; long long items; double w; };
   std::vector<Group> groups;
   double total = 0;
-  for (int src = 0; src < 3; ++src)
+  for (int src = (m.cell == CELL_VANILLA2D ? 2 : 0); src < 3; ++src)   // vanilla cell: one unmasked source (d pre -> Wh, Wv)
     for (int half = 0; half < 2; ++half)
       for (int cls = 0; cls < 3; ++cls) {
         if ((half == 0 && cls == 2) || (half == 1 && cls == 1)) continue;   // that neighbour is absent in this class
         const long long items = (long long)cls_count[cls] * tiles;
         if (items == 0) continue;
-        const double w = (src == 2) ? 0.5 : 1.0;
+        const double w = (src == 2 && m.cell != CELL_VANILLA2D) ? 0.5 : 1.0;
         groups.push_back({src, half, cls, items, w});
         total += items * w;
       }
@@ -560,13 +562,13 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
   Gemm G{st};
   G.tc = (m.precision == 1);
   float* wstack = reinterpret_cast<float*>(ws + L.off_wstack);
-  if (L.batched && !(m.tc_enabled && m.cell == CELL_TENSGRU2D)) {
+  if (L.batched && !m.tc_enabled) {
     const bool gru0 = m.cell == CELL_TENSGRU2D;
     RNNWF_COUNT_LAUNCH(); pack_wstack_kernel<<<512, 256, 0, st>>>(params + m.tensor("W")->offset, gru0 ? params + m.tensor("Wg")->offset : nullptr,
                                                      gru0 ? params + m.tensor("Wmerge")->offset : nullptr, nh, gru0 ? 1 : 0, wstack);
   }
 
-  cudaError_t e = (m.tc_enabled && m.cell == CELL_TENSGRU2D) ? cudaSuccess : cudaMemsetAsync(dh, 0, (size_t)m.Q * R * nhp * 4, st);
+  cudaError_t e = m.tc_enabled ? cudaSuccess : cudaMemsetAsync(dh, 0, (size_t)m.Q * R * nhp * 4, st);
   if (e == cudaSuccess) e = cudaMemsetAsync(grad, 0, (size_t)m.num_params * 4, st);
   if (e != cudaSuccess) { err = std::string("rnnwf_backward memset: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
 
@@ -580,25 +582,30 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
   // Reduced-precision regime, tensorized GRU: the whole recurrence (heads' push into d h, gate derivatives, input
   // gradients, scatter to the neighbours) is one persistent tensor-core kernel (bwd_tc.cuh) after one batched
   // d(logits) kernel; only the operands of the batched weight-gradient GEMMs below are still built per site.
-  const bool tc_sweep = m.tc_enabled && m.cell == CELL_TENSGRU2D;
+  const bool tc_sweep = m.tc_enabled;
   if (tc_sweep) {
-    e = cudaMemsetAsync(dh, 0, (size_t)tc_dh_bytes(m.Q, R, m.tc_np), st);
+    const bool van = m.cell == CELL_VANILLA2D;
+    const int pieces = (nhp + TC_JP - 1) / TC_JP;      // unit pieces per thread layout (== column passes of the tensorized GRU)
+    e = cudaMemsetAsync(dh, 0, (size_t)tc_dh_bytes(m.Q, R, pieces), st);
     if (e != cudaSuccess) { err = std::string("rnnwf_backward memset: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
     float* wimg = reinterpret_cast<float*>(ws + L.off_wimg);
-    RNNWF_COUNT_LAUNCH(); pack_bwd_tc_kernel<<<512, 256, 0, st>>>(P("W"), P("Wg"), P("Wmerge"), nh, nhp, m.tc_np, wimg);
+    if (van) { RNNWF_COUNT_LAUNCH(); pack_bwd_tc_vanilla_kernel<<<256, 256, 0, st>>>(P("Wh"), P("Wv"), nh, nhp, wimg); }
+    else { RNNWF_COUNT_LAUNCH(); pack_bwd_tc_kernel<<<512, 256, 0, st>>>(P("W"), P("Wg"), P("Wmerge"), nh, nhp, m.tc_np, wimg); }
     HeadAllParams H;
     H.Q = m.Q; H.nh = nh; H.nhp = nhp; H.ND = m.ND; H.D = m.D; H.nsites = m.nsites; H.complex_head = m.complex_head;
     H.u1 = m.u1; H.cap_up = m.cap_up; H.cap_dn = m.cap_dn; H.R = R; H.hist = hist; H.cfg = cfg; H.site_of_t = m.d_site_of_t;
     H.head_w = m.d_head_w; H.head_b = m.d_head_b; H.seed_logp = seed_logp; H.seed_phase = seed_phase; H.dlog = dlog_base;
     RNNWF_COUNT_LAUNCH(); head_bwd_all_kernel<<<(unsigned)(((long long)m.Q * R + 7) / 8), 256, 0, st>>>(H);
     BwdTcParams B;
-    B.steps = m.d_steps; B.Q = m.Q; B.Tsym = m.Tsym; B.nsites = m.nsites; B.nh = nh; B.nhp = nhp; B.np = m.tc_np; B.ND = m.ND;
+    B.steps = m.d_steps; B.Q = m.Q; B.Tsym = m.Tsym; B.nsites = m.nsites; B.nh = nh; B.nhp = nhp; B.np = pieces; B.ND = m.ND;
     B.rows = R; B.cfg = cfg; B.gates = gates; B.dlog = dlog_base; B.dh = reinterpret_cast<float4*>(dh);
     B.dpT = reinterpret_cast<float*>(ws + L.off_dpT);
-    B.wimg = wimg; B.head_w = m.d_head_w;
+    B.wimg = wimg; B.head_w = m.d_head_w; B.hist = hist;
     const long long tiles = (R + TC_ROWS - 1) / TC_ROWS;
     const BtSmem bs(nhp, m.Tsym, m.Q);
-    RNNWF_COUNT_LAUNCH(); bwd_tc_kernel<<<(unsigned)std::min<long long>(tiles, m.num_sms), BT_THREADS, bs.total, st>>>(B);
+    RNNWF_COUNT_LAUNCH();
+    if (van) bwd_tc_kernel<1><<<(unsigned)std::min<long long>(tiles, m.num_sms), BT_THREADS, bs.total, st>>>(B);
+    else bwd_tc_kernel<0><<<(unsigned)std::min<long long>(tiles, m.num_sms), BT_THREADS, bs.total, st>>>(B);
     // ---- parameter gradients: weights on the tensor cores (dw_tc.cuh), biases and heads as reductions
     {
       DwParams D;
@@ -620,11 +627,20 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
       const float* himg = reinterpret_cast<const float*>(sb + sv.off_himg);
       D.jobs = d_jobs; D.cls_steps = d_cls; D.steps = m.d_steps; D.Q = m.Q; D.nh = nh; D.nhp = nhp; D.nsites = m.nsites;
       D.rows = R; D.tiles = tiles; D.cfg = cfg; D.site_of_t = m.d_site_of_t; D.dpT = B.dpT; D.himg = himg;
-      D.gW = Gd("W"); D.gWg = Gd("Wg"); D.gWmerge = Gd("Wmerge");
-      RNNWF_COUNT_LAUNCH(); dw_tc_kernel<<<(unsigned)njobs, DW_THREADS, dw_smem_bytes(nhp), st>>>(D);
       const int nsplit = 16;
-      RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, 0, m.Q, tiles, nhp, nsplit, Gd("b"));
-      RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, 1, m.Q, tiles, nhp, nsplit, Gd("bg"));
+      if (van) {
+        D.gW = nullptr; D.gWg = nullptr; D.gM0 = Gd("Wh"); D.gM1 = Gd("Wv");
+        D.slab[0] = D.slab[1] = D.slab[2] = 0;
+        RNNWF_COUNT_LAUNCH(); dw_tc_kernel<<<(unsigned)njobs, DW_THREADS, dw_smem_bytes(nhp), st>>>(D);
+        RNNWF_COUNT_LAUNCH(); vanilla_input_grads_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, m.d_steps, m.d_site_of_t, cfg, m.Q, tiles, R, nh, nhp,
+                                                                                          m.nsites, Gd("b"), Gd("Uh"), Gd("Uv"));
+      } else {
+        D.gW = Gd("W"); D.gWg = Gd("Wg"); D.gM0 = Gd("Wmerge"); D.gM1 = Gd("Wmerge") + (long long)nh * nh;
+        D.slab[0] = 0; D.slab[1] = 1; D.slab[2] = 2;
+        RNNWF_COUNT_LAUNCH(); dw_tc_kernel<<<(unsigned)njobs, DW_THREADS, dw_smem_bytes(nhp), st>>>(D);
+        RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, 0, m.Q, tiles, nhp, nsplit, Gd("b"));
+        RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, 1, m.Q, tiles, nhp, nsplit, Gd("bg"));
+      }
       RNNWF_COUNT_LAUNCH(); head_grad_himg_kernel<<<std::min<long long>((long long)m.Q * tiles, 4LL * m.num_sms), 128, 0, st>>>(
           himg, dlog_base, m.Q, tiles, R, nh, nhp, m.ND, Gd("dense.W"), m.complex_head ? Gd("dense_phase.W") : nullptr);
       const long long RQ = (long long)m.Q * R;

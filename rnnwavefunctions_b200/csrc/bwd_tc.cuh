@@ -55,7 +55,8 @@ struct BwdTcParams {
   float4* dh;                   // [Q][tiles][sub 4][pass np][row 128] float4, zero-initialised
   float* dpT;                   // [src 3: ds, dg, dm][Q][tiles][unit nhp][row 128]  (feature-major tiles for dw_tc.cuh)
   const float* wimg;            // [variant 3][chunk np][b_bytes / 4]
-  const float* head_w;          // [nh][4]
+  const float* head_w;          // [nh][ND]
+  const float* hist;            // vanilla cell: saved hidden states [Q][rows][nhp] (elu' = h > 0 ? 1 : h + 1)
 };
 
 // tile-blocked layouts shared with the sampling sweep: everything a thread (row, sub) touches for column pass p is
@@ -131,6 +132,59 @@ __global__ void pack_bwd_tc_kernel(const float* __restrict__ W, const float* __r
   }
 }
 
+// ---- vanilla 2D RNN: one chunk, element (n, k) = d pre_j / d h_{half, i} = W_half[i][j]   (k <-> unit j, n <-> (half, unit i))
+__global__ void pack_bwd_tc_vanilla_kernel(const float* __restrict__ Wh, const float* __restrict__ Wv, int nh, int nhp, float* __restrict__ out) {
+  const int ncores = 2 * nhp / 8;
+  const long long total = (long long)(BT_K / 4) * ncores * 32;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+    long long r = idx;
+    const int ek = (int)(r % 4); r /= 4;
+    const int en = (int)(r % 8); r /= 8;
+    const int nn = (int)(r % ncores); r /= ncores;
+    const int kk = (int)r;
+    const int k = kk * 4 + ek, n = nn * 8 + en;
+    const int sub = k / TC_TPS, blk = (k % TC_TPS) / 4, j = blk * TC_JP + sub * 4 + (k % 4);
+    const int half = n / nhp, unit = tc_kunit(nhp, n - half * nhp);
+    out[idx] = (unit < nh && j < nh) ? (half == 0 ? Wh : Wv)[(long long)unit * nh + j] : 0.f;
+  }
+}
+
+// vanilla 2D RNN: gradients of the one-hot input kernels and the bias from the feature-major d(pre) tiles:
+//   db[j] = sum d pre_j,   dUh[c][j] = sum [horizontal neighbour present and sigma_l == c] d pre_j,   dUv likewise.
+// grid (nh, nsplit), 128 threads = the rows of a tile.
+__global__ void __launch_bounds__(128) vanilla_input_grads_kernel(const float* __restrict__ dpT, const StepMeta* __restrict__ steps,
+                                                                  const int16_t* __restrict__ site_of_t, const int8_t* __restrict__ cfg,
+                                                                  int Q, long long tiles, long long rows, int nh, int nhp, int nsites,
+                                                                  float* __restrict__ gb, float* __restrict__ gUh, float* __restrict__ gUv) {
+  __shared__ float red[4][5];
+  const int j = blockIdx.x, r = threadIdx.x;
+  float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+  const long long nitems = (long long)Q * tiles;
+  for (long long it = blockIdx.y; it < nitems; it += gridDim.y) {
+    const int q = (int)(it / tiles);
+    const long long row = (it % tiles) * TC_ROWS + r;
+    const float v = dpT[((size_t)it * nhp + j) * TC_ROWS + r];
+    if (row >= rows) continue;
+    const int n0 = steps[q].nbr[0], n1 = steps[q].nbr[1];
+    const int8_t* cf = cfg + row * nsites;
+    acc[0] += v;
+    if (n0 >= 0) { if (cf[site_of_t[n0]] & 1) acc[2] += v; else acc[1] += v; }
+    if (n1 >= 0) { if (cf[site_of_t[n1]] & 1) acc[4] += v; else acc[3] += v; }
+  }
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    float x = acc[k];
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if ((r & 31) == 0) red[r >> 5][k] = x;
+  }
+  __syncthreads();
+  if (r < 5) {
+    const float x = red[0][r] + red[1][r] + red[2][r] + red[3][r];
+    float* dst = (r == 0) ? gb + j : (r <= 2 ? gUh + (r - 1) * nh + j : gUv + (r - 3) * nh + j);
+    atomicAdd(dst, x);
+  }
+}
+
 // ---- d(logits) of every site in one launch --------------------------------------------------------------------
 // One warp per (site, row): recompute the heads from the saved hidden state and form d(logits) for the given seeds
 // (same math as head_bwd_kernel; the push into d h happens inside the reverse sweep).  2D cells: site q <-> symbol q.
@@ -188,6 +242,9 @@ __global__ void __launch_bounds__(256) head_bwd_all_kernel(const HeadAllParams S
 }
 
 // ---- the reverse sweep ------------------------------------------------------------------------------------------
+// CELLK: 0 = tensorized GRU (np chunks of 16 units x 7 blocks per site); 1 = vanilla 2D RNN (one chunk per site: the
+// K axis holds d(pre-activation) of all units, position sub * 28 + piece * 4 + e; P.np = unit pieces of the layouts)
+template <int CELLK>
 __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams P) {
   extern __shared__ __align__(128) unsigned char bt_smem[];
   unsigned char* const smem = bt_smem;
@@ -206,6 +263,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int nh = P.nh, nhp = P.nhp, NP = P.np;
+  const int NCH = (CELLK == 1) ? 1 : NP;              // operand chunks (MMA K groups) per site
   const uint32_t ncols = 2u * (uint32_t)nhp;          // accumulator columns: [d h_h ; d h_v]
   // TMEM map: [0, ncols) accumulator; then two operand chunks of 112 columns (one tf32 per column)
   if (tid == 0) {
@@ -241,7 +299,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       for (int q = P.Q - 1; q >= 0; --q) {
         if (!stepS[q].w) continue;                                  // first site: no inputs to differentiate
-        for (int p = 0; p < NP; ++p, ++c) {
+        for (int p = 0; p < NCH; ++p, ++c) {
           const uint32_t s = c & 1u;
           mbar_wait(bar_B + s, (phB >> s) & 1u); phB ^= 1u << s;
           mbar_wait(bar_A + s, (phA >> s) & 1u); phA ^= 1u << s;
@@ -254,7 +312,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
             for (int ks = 0; ks < BT_NK8; ++ks)
               tc_mma_tf32_ts(tmem_base, tmem_a + (uint32_t)ks * 8u, bd + (uint64_t)ks * kstep, idesc, (p > 0 || ks > 0) ? 1u : 0u);
             tc_commit(bar_free + s);
-            if (p == NP - 1) tc_commit(bar_D);
+            if (p == NCH - 1) tc_commit(bar_D);
           }
           __syncwarp();
         }
@@ -269,9 +327,9 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
       for (int q = P.Q - 1; q >= 0; --q) {
         const short4 sm = stepS[q];
         if (!sm.w) continue;
-        const int v = (sm.x >= 0 && sm.y >= 0) ? 0 : (sm.x >= 0 ? 1 : 2);
-        const unsigned char* src = reinterpret_cast<const unsigned char*>(P.wimg) + (size_t)v * NP * L.b_bytes;
-        for (int p = 0; p < NP; ++p, ++c) {
+        const int v = (CELLK == 1) ? 0 : ((sm.x >= 0 && sm.y >= 0) ? 0 : (sm.x >= 0 ? 1 : 2));   // vanilla: one image
+        const unsigned char* src = reinterpret_cast<const unsigned char*>(P.wimg) + (size_t)v * NCH * L.b_bytes;
+        for (int p = 0; p < NCH; ++p, ++c) {
           const uint32_t s = c & 1u;
           if (c >= 2) { mbar_wait_relaxed(bar_free + s, (phF >> s) & 1u); phF ^= 1u << s; }
           if (leader) {
@@ -317,47 +375,34 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
           if (P.ND == 4) { const float4 v = *reinterpret_cast<const float4*>(dlp); dl[0] = v.x; dl[1] = v.y; dl[2] = v.z; dl[3] = v.w; }
           else { const float2 v = *reinterpret_cast<const float2*>(dlp); dl[0] = v.x; dl[1] = v.y; }
         }
-        const float4* gq = P.gates + tc_gate_index(q, tile, ntiles, NP, sub, 0, 0, row);
-        const float4* dhq = P.dh + tc_dh_index(q, tile, ntiles, NP, sub, 0, row);
-        float4 n_dh = make_float4(0.f, 0.f, 0.f, 0.f), n_u = n_dh, n_t = n_dh, n_m = n_dh;
-        if (live && np_own > 0) { n_dh = __ldcg(dhq); n_u = __ldg(gq); n_t = __ldg(gq + TC_ROWS); n_m = __ldg(gq + 2 * TC_ROWS); }
-#pragma unroll 1
-        for (int p = 0; p < NP; ++p) {
+        if constexpr (CELLK == 1) {
+          // ---- vanilla cell: d(pre) = (d h + heads' push) * elu'(pre), elu' = 1 for h > 0 else h + 1; one chunk per site
+          const float4* dhq = P.dh + tc_dh_index(q, tile, ntiles, NP, sub, 0, row);
+          const float* hq = P.hist + ((size_t)q * (size_t)P.rows + (size_t)(row0 + row)) * nhp + sub * 4;
           uint32_t d[TC_TPS];
 #pragma unroll
           for (int i = 0; i < TC_TPS; ++i) d[i] = 0u;
-          if (p < np_own) {
-            float ds[4] = {0.f, 0.f, 0.f, 0.f}, dg[4] = {0.f, 0.f, 0.f, 0.f}, dm[4] = {0.f, 0.f, 0.f, 0.f};
-            const int j0 = p * TC_JP + sub * 4;
-            if (live) {
-              const float4 dh4 = n_dh, u4 = n_u, t4 = n_t, m4 = n_m;      // loaded one pass ahead
-              if (p + 1 < np_own) {
-                n_dh = __ldcg(dhq + (size_t)(p + 1) * TC_ROWS);
-                n_u = __ldg(gq + (size_t)(p + 1) * 3 * TC_ROWS);
-                n_t = __ldg(gq + (size_t)(p + 1) * 3 * TC_ROWS + TC_ROWS);
-                n_m = __ldg(gq + (size_t)(p + 1) * 3 * TC_ROWS + 2 * TC_ROWS);
-              }
-              const float dhv[4] = {dh4.x, dh4.y, dh4.z, dh4.w}, uv[4] = {u4.x, u4.y, u4.z, u4.w};
-              const float tv[4] = {t4.x, t4.y, t4.z, t4.w}, mv[4] = {m4.x, m4.y, m4.z, m4.w};
 #pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float4 w = *reinterpret_cast<const float4*>(hW + p * (TC_JP * 4) + e * 4);
-                const float g = dhv[e] + dl[0] * w.x + dl[1] * w.y + dl[2] * w.z + dl[3] * w.w;   // heads' contribution
-                const bool real = (j0 + e < nh);                     // padding units carry nothing (their saved gates are unset)
-                ds[e] = real ? g * uv[e] * (1.f - tv[e] * tv[e]) : 0.f;
-                dg[e] = real ? g * (tv[e] - mv[e]) * uv[e] * (1.f - uv[e]) : 0.f;
-                dm[e] = real ? g * (1.f - uv[e]) : 0.f;
-                d[e] = __float_as_uint(ds[e]); d[4 + e] = __float_as_uint(cl * ds[e]); d[8 + e] = __float_as_uint(cu * ds[e]);
-                d[12 + e] = __float_as_uint(dg[e]); d[16 + e] = __float_as_uint(cl * dg[e]); d[20 + e] = __float_as_uint(cu * dg[e]);
-                d[24 + e] = __float_as_uint(dm[e]);
-              }
-            }
-            // feature-major tiles for the weight-gradient kernel (zeros for rows past the end of the batch)
-            float* o0 = P.dpT + (((size_t)q * (size_t)ntiles + (size_t)tile) * nhp + j0) * TC_ROWS + row;
-            const size_t sstride = (size_t)P.Q * (size_t)ntiles * nhp * TC_ROWS;
+          for (int blk = 0; blk < TC_NB; ++blk) {
+            if (blk < np_own) {                                       // warp-uniform
+              float dp[4] = {0.f, 0.f, 0.f, 0.f};
+              const int j0 = blk * TC_JP + sub * 4;
+              if (live) {
+                const float4 dh4 = __ldcg(dhq + (size_t)blk * TC_ROWS);
+                const float4 h4 = __ldg(reinterpret_cast<const float4*>(hq + blk * TC_JP));
+                const float dhv[4] = {dh4.x, dh4.y, dh4.z, dh4.w}, hv[4] = {h4.x, h4.y, h4.z, h4.w};
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              if (j0 + e < nhp) { o0[(size_t)e * TC_ROWS] = ds[e]; o0[sstride + (size_t)e * TC_ROWS] = dg[e]; o0[2 * sstride + (size_t)e * TC_ROWS] = dm[e]; }
+                for (int e = 0; e < 4; ++e) {
+                  const float4 w = *reinterpret_cast<const float4*>(hW + blk * (TC_JP * 4) + e * 4);
+                  const float g = dhv[e] + dl[0] * w.x + dl[1] * w.y + dl[2] * w.z + dl[3] * w.w;
+                  dp[e] = (j0 + e < nh) ? g * (hv[e] > 0.f ? 1.f : hv[e] + 1.f) : 0.f;
+                  d[blk * 4 + e] = __float_as_uint(dp[e]);
+                }
+              }
+              float* o0 = P.dpT + (((size_t)q * (size_t)ntiles + (size_t)tile) * nhp + j0) * TC_ROWS + row;
+#pragma unroll
+              for (int e = 0; e < 4; ++e)
+                if (j0 + e < nhp) o0[(size_t)e * TC_ROWS] = dp[e];
             }
           }
           if (has_in) {
@@ -369,6 +414,61 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
             tc_fence_before();
             mbar_arrive(bar_A + s);
             ++c;
+          }
+        } else {
+          const float4* gq = P.gates + tc_gate_index(q, tile, ntiles, NP, sub, 0, 0, row);
+          const float4* dhq = P.dh + tc_dh_index(q, tile, ntiles, NP, sub, 0, row);
+          float4 n_dh = make_float4(0.f, 0.f, 0.f, 0.f), n_u = n_dh, n_t = n_dh, n_m = n_dh;
+          if (live && np_own > 0) { n_dh = __ldcg(dhq); n_u = __ldg(gq); n_t = __ldg(gq + TC_ROWS); n_m = __ldg(gq + 2 * TC_ROWS); }
+  #pragma unroll 1
+          for (int p = 0; p < NP; ++p) {
+            uint32_t d[TC_TPS];
+  #pragma unroll
+            for (int i = 0; i < TC_TPS; ++i) d[i] = 0u;
+            if (p < np_own) {
+              float ds[4] = {0.f, 0.f, 0.f, 0.f}, dg[4] = {0.f, 0.f, 0.f, 0.f}, dm[4] = {0.f, 0.f, 0.f, 0.f};
+              const int j0 = p * TC_JP + sub * 4;
+              if (live) {
+                const float4 dh4 = n_dh, u4 = n_u, t4 = n_t, m4 = n_m;      // loaded one pass ahead
+                if (p + 1 < np_own) {
+                  n_dh = __ldcg(dhq + (size_t)(p + 1) * TC_ROWS);
+                  n_u = __ldg(gq + (size_t)(p + 1) * 3 * TC_ROWS);
+                  n_t = __ldg(gq + (size_t)(p + 1) * 3 * TC_ROWS + TC_ROWS);
+                  n_m = __ldg(gq + (size_t)(p + 1) * 3 * TC_ROWS + 2 * TC_ROWS);
+                }
+                const float dhv[4] = {dh4.x, dh4.y, dh4.z, dh4.w}, uv[4] = {u4.x, u4.y, u4.z, u4.w};
+                const float tv[4] = {t4.x, t4.y, t4.z, t4.w}, mv[4] = {m4.x, m4.y, m4.z, m4.w};
+  #pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const float4 w = *reinterpret_cast<const float4*>(hW + p * (TC_JP * 4) + e * 4);
+                  const float g = dhv[e] + dl[0] * w.x + dl[1] * w.y + dl[2] * w.z + dl[3] * w.w;   // heads' contribution
+                  const bool real = (j0 + e < nh);                     // padding units carry nothing (their saved gates are unset)
+                  ds[e] = real ? g * uv[e] * (1.f - tv[e] * tv[e]) : 0.f;
+                  dg[e] = real ? g * (tv[e] - mv[e]) * uv[e] * (1.f - uv[e]) : 0.f;
+                  dm[e] = real ? g * (1.f - uv[e]) : 0.f;
+                  d[e] = __float_as_uint(ds[e]); d[4 + e] = __float_as_uint(cl * ds[e]); d[8 + e] = __float_as_uint(cu * ds[e]);
+                  d[12 + e] = __float_as_uint(dg[e]); d[16 + e] = __float_as_uint(cl * dg[e]); d[20 + e] = __float_as_uint(cu * dg[e]);
+                  d[24 + e] = __float_as_uint(dm[e]);
+                }
+              }
+              // feature-major tiles for the weight-gradient kernel (zeros for rows past the end of the batch)
+              float* o0 = P.dpT + (((size_t)q * (size_t)ntiles + (size_t)tile) * nhp + j0) * TC_ROWS + row;
+              const size_t sstride = (size_t)P.Q * (size_t)ntiles * nhp * TC_ROWS;
+  #pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                if (j0 + e < nhp) { o0[(size_t)e * TC_ROWS] = ds[e]; o0[sstride + (size_t)e * TC_ROWS] = dg[e]; o0[2 * sstride + (size_t)e * TC_ROWS] = dm[e]; }
+              }
+            }
+            if (has_in) {
+              const uint32_t s = c & 1u;
+              if (c >= 2) { mbar_wait(bar_free + s, (phF >> s) & 1u); phF ^= 1u << s; }
+              __syncwarp();
+              tc_st28(a_thr + s * (uint32_t)BT_K, d);
+              tc_wait_st();
+              tc_fence_before();
+              mbar_arrive(bar_A + s);
+              ++c;
+            }
           }
         }
         if (has_in) {

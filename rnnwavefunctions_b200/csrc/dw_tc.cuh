@@ -54,7 +54,9 @@ struct DwParams {
   const int16_t* site_of_t;
   const float* dpT;       // feature-major (ds, dg, dm)
   const float* himg;      // hidden-state tile images
-  float* gW; float* gWg; float* gWmerge;
+  float* gW; float* gWg;
+  float* gM0; float* gM1;   // unmasked source (src 2): [unit i][unit j] targets of the horizontal / vertical half
+  int slab[3];              // which feature-major slab of dpT holds source 0, 1, 2
 };
 
 __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) {
@@ -166,20 +168,20 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
         }
         // operand rows of this unit: DW_PF chunks (16 rows each) are in flight in registers, across item boundaries
         if (it == 0) {
-          const float* src = P.dpT + ((((size_t)job.src * P.Q + q) * (size_t)P.tiles + (size_t)tile) * P.nhp + (real ? unit : 0)) * TC_ROWS;
+          const float* src = P.dpT + ((((size_t)P.slab[job.src] * P.Q + q) * (size_t)P.tiles + (size_t)tile) * P.nhp + (real ? unit : 0)) * TC_ROWS;
 #pragma unroll
           for (int k = 0; k < DW_PF; ++k)
 #pragma unroll
             for (int i = 0; i < 4; ++i) pf[k][i] = real ? __ldg(reinterpret_cast<const float4*>(src) + k * 4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
         // source of the chunks that will be loaded while this item is processed: its own second half, then the next item
-        const float* src_cur = P.dpT + ((((size_t)job.src * P.Q + q) * (size_t)P.tiles + (size_t)tile) * P.nhp + (real ? unit : 0)) * TC_ROWS;
+        const float* src_cur = P.dpT + ((((size_t)P.slab[job.src] * P.Q + q) * (size_t)P.tiles + (size_t)tile) * P.nhp + (real ? unit : 0)) * TC_ROWS;
         const float* src_nxt = src_cur;
         if (it + 1 < job.count) {
           const int item2 = item + 1;
           const int q2 = steps_of_cls[item2 / (int)P.tiles];
           const long long tile2 = item2 % (int)P.tiles;
-          src_nxt = P.dpT + ((((size_t)job.src * P.Q + q2) * (size_t)P.tiles + (size_t)tile2) * P.nhp + (real ? unit : 0)) * TC_ROWS;
+          src_nxt = P.dpT + ((((size_t)P.slab[job.src] * P.Q + q2) * (size_t)P.tiles + (size_t)tile2) * P.nhp + (real ? unit : 0)) * TC_ROWS;
         }
 #pragma unroll
         for (int kc = 0; kc < DW_CHUNKS; ++kc, ++c) {
@@ -240,7 +242,7 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
               if (i >= nh) continue;
               const float s = __uint_as_float(S[e]);
               if (!masks) {
-                atomicAdd(P.gWmerge + (size_t)(job.half * nh + i) * nh + unit, s);
+                atomicAdd((job.half ? P.gM1 : P.gM0) + (size_t)i * nh + unit, s);
               } else {
                 float* g = (job.src == 0 ? P.gW : P.gWg) + ((size_t)unit * 2 * nh + (size_t)(job.half * nh + i)) * 4;
                 const float cl = __uint_as_float(Cl[e]), cu = __uint_as_float(Cu[e]);

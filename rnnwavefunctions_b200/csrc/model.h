@@ -83,7 +83,7 @@ struct rnnwf_model_impl {
     s.off_cum = s.off_gates + al(gate_bytes);
     s.off_himg = s.off_cum + al((long long)Tsym * rows * 16);
     // tensor-core regime: hidden states once more as ready-made B operand tiles of the weight-gradient kernel
-    const long long himg_bytes = tcs ? (long long)Q * ((rows + 127) / 128) * (32LL * (((nhp + 15) / 16) * 2) * 32) * 4 : 0;
+    const long long himg_bytes = tc_enabled ? (long long)Q * ((rows + 127) / 128) * (32LL * (((nhp + 15) / 16) * 2) * 32) * 4 : 0;
     s.total = s.off_himg + al(himg_bytes);
     return s;
   }

@@ -397,7 +397,7 @@ int set_saved(const rnnwf_model& m, SweepParams& P, void* saved, long long rows)
   P.sv_hist = reinterpret_cast<float*>(b + sv.off_hist);
   P.sv_gates = m.gru_type ? reinterpret_cast<float4*>(b + sv.off_gates) : nullptr;
   P.sv_cum = reinterpret_cast<double2*>(b + sv.off_cum);
-  P.sv_himg = (m.tc_enabled && m.cell == CELL_TENSGRU2D) ? reinterpret_cast<float*>(b + sv.off_himg) : nullptr;
+  P.sv_himg = m.tc_enabled ? reinterpret_cast<float*>(b + sv.off_himg) : nullptr;
   P.sv_rows = rows;
   return RNNWF_OK;
 }
@@ -552,7 +552,7 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
   }
   CREATE_TRY(backward_init());
-  if (m->tc_enabled && m->cell == CELL_TENSGRU2D) {
+  if (m->tc_enabled) {
     CREATE_TRY(backward_init_tc(*m));
     CREATE_TRY(cudaMalloc(&m->d_dw_jobs, 1024 * sizeof(DwJob)));
     CREATE_TRY(cudaMalloc(&m->d_dw_cls, (size_t)3 * m->Q * sizeof(int)));

@@ -683,6 +683,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
               ring_p += (blk & 1) ? (TC_RING_QUAD - 8u) : 8u;
             }
           }
+          if (MODE != MODE_CHILD && P.sv_himg != nullptr) {
+            // hidden-state tile image for the weight-gradient kernel (zeros for padding units / rows past the batch)
+            const int hnc = ((nhp + 15) / 16) * 2;
+            float* sv_i = P.sv_himg + ((size_t)q * (size_t)sv_tiles + (size_t)tile) * (size_t)(32 * hnc * 32) + (size_t)(row >> 2) * hnc * 32 + (row & 3);
+            const float* hsrc = P.sv_hist != nullptr ? P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp : nullptr;
+#pragma unroll
+            for (int blk = 0; blk < TC_NB; ++blk) {
+              const int j0 = blk * TC_JP + sub * 4;
+              if (j0 < hnc * 8) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                  sv_i[((j0 + e) >> 3) * 32 + ((j0 + e) & 7) * 4] = (live && hsrc != nullptr && j0 + e < nhp) ? hsrc[j0 + e] : 0.f;
+              }
+            }
+          }
           TC_ACC(9);
         } else {
           unsigned char* ring_p = ring_base + (ring_off0 + (uint32_t)eq.z);   // this thread's pieces of this step's image, in pass order
