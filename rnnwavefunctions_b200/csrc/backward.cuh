@@ -478,7 +478,9 @@ inline void dw_plan(const rnnwf_model_impl& m, long long R, std::vector<DwJob>& 
   struct Group { int src, half, cls; long long items; double w; };
   std::vector<Group> groups;
   double total = 0;
-  for (int src = (m.cell == CELL_VANILLA2D ? 2 : 0); src < 3; ++src)   // vanilla cell: one unmasked source (d pre -> Wh, Wv)
+  const int src_lo = (m.cell == CELL_VANILLA2D) ? 2 : 0;                // vanilla cell: one unmasked source (d pre -> Wh, Wv)
+  const int src_hi = (m.cell == CELL_TENS2D) ? 1 : 3;                   // un-gated tensorized cell: ds -> W only
+  for (int src = src_lo; src < src_hi; ++src)
     for (int half = 0; half < 2; ++half)
       for (int cls = 0; cls < 3; ++cls) {
         if ((half == 0 && cls == 2) || (half == 1 && cls == 1)) continue;   // that neighbour is absent in this class
@@ -590,7 +592,10 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
     if (e != cudaSuccess) { err = std::string("rnnwf_backward memset: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
     float* wimg = reinterpret_cast<float*>(ws + L.off_wimg);
     if (van) { RNNWF_COUNT_LAUNCH(); pack_bwd_tc_vanilla_kernel<<<256, 256, 0, st>>>(P("Wh"), P("Wv"), nh, nhp, wimg); }
-    else { RNNWF_COUNT_LAUNCH(); pack_bwd_tc_kernel<<<512, 256, 0, st>>>(P("W"), P("Wg"), P("Wmerge"), nh, nhp, m.tc_np, wimg); }
+    else {
+      const bool gated = m.cell == CELL_TENSGRU2D;
+      RNNWF_COUNT_LAUNCH(); pack_bwd_tc_kernel<<<512, 256, 0, st>>>(P("W"), gated ? P("Wg") : nullptr, gated ? P("Wmerge") : nullptr, nh, nhp, m.tc_np, wimg);
+    }
     HeadAllParams H;
     H.Q = m.Q; H.nh = nh; H.nhp = nhp; H.ND = m.ND; H.D = m.D; H.nsites = m.nsites; H.complex_head = m.complex_head;
     H.u1 = m.u1; H.cap_up = m.cap_up; H.cap_dn = m.cap_dn; H.R = R; H.hist = hist; H.cfg = cfg; H.site_of_t = m.d_site_of_t;
@@ -635,11 +640,13 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
         RNNWF_COUNT_LAUNCH(); vanilla_input_grads_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, m.d_steps, m.d_site_of_t, cfg, m.Q, tiles, R, nh, nhp,
                                                                                           m.nsites, Gd("b"), Gd("Uh"), Gd("Uv"));
       } else {
-        D.gW = Gd("W"); D.gWg = Gd("Wg"); D.gM0 = Gd("Wmerge"); D.gM1 = Gd("Wmerge") + (long long)nh * nh;
+        const bool gated = m.cell == CELL_TENSGRU2D;
+        D.gW = Gd("W"); D.gWg = gated ? Gd("Wg") : nullptr;
+        D.gM0 = gated ? Gd("Wmerge") : nullptr; D.gM1 = gated ? Gd("Wmerge") + (long long)nh * nh : nullptr;
         D.slab[0] = 0; D.slab[1] = 1; D.slab[2] = 2;
         RNNWF_COUNT_LAUNCH(); dw_tc_kernel<<<(unsigned)njobs, DW_THREADS, dw_smem_bytes(nhp), st>>>(D);
         RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, 0, m.Q, tiles, nhp, nsplit, Gd("b"));
-        RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, 1, m.Q, tiles, nhp, nsplit, Gd("bg"));
+        if (gated) { RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, 1, m.Q, tiles, nhp, nsplit, Gd("bg")); }
       }
       RNNWF_COUNT_LAUNCH(); head_grad_himg_kernel<<<std::min<long long>((long long)m.Q * tiles, 4LL * m.num_sms), 128, 0, st>>>(
           himg, dlog_base, m.Q, tiles, R, nh, nhp, m.ND, Gd("dense.W"), m.complex_head ? Gd("dense_phase.W") : nullptr);

@@ -119,7 +119,9 @@ __global__ void pack_bwd_tc_kernel(const float* __restrict__ W, const float* __r
     if (unit < nh && j < nh) {
       const int i = half * nh + unit;
       if (blk == 6) {
-        v = Wmerge[(long long)i * nh + j];
+        v = (Wmerge != nullptr) ? Wmerge[(long long)i * nh + j] : 0.f;
+      } else if (blk >= 3 && Wg == nullptr) {
+        v = 0.f;                                   // un-gated tensorized cell
       } else {
         const float* w = ((blk < 3) ? W : Wg) + ((long long)j * 2 * nh + i) * 4;
         const int kind = blk % 3;

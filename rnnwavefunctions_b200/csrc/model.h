@@ -77,7 +77,7 @@ struct rnnwf_model_impl {
     s.off_hist = 0;
     s.off_gates = al((long long)Q * rows * nhp * 4);
     // tensor-core regime: gates are saved tile-blocked, three float4 per (row, 4 units) (bwd_tc.cuh: tc_gate_index)
-    const bool tcs = tc_enabled && cell == CELL_TENSGRU2D;   // (the vanilla cell has no gates and no tensor-core backward)
+    const bool tcs = tc_enabled && (cell == CELL_TENSGRU2D || cell == CELL_TENS2D);   // tile-blocked (u, h~, m); the vanilla cell saves none
     const long long gate_bytes = tcs ? (long long)Q * ((rows + 127) / 128) * 4 * tc_np * 3 * 128 * 16
                                             : (gru_type ? (long long)Q * rows * Gp * 16 : 0);
     s.off_cum = s.off_gates + al(gate_bytes);

@@ -277,9 +277,9 @@ int build_model(rnnwf_model& m) {
     v.meta.b_off = (uint32_t)boff;
     boff += m.Gp;
   }
-  m.tc_enabled = (m.precision == 1 && (m.cell == CELL_TENSGRU2D || m.cell == CELL_VANILLA2D));
+  m.tc_enabled = (m.precision == 1 && (m.cell == CELL_TENSGRU2D || m.cell == CELL_TENS2D || m.cell == CELL_VANILLA2D));
   if (m.precision == 1 && !m.tc_enabled)
-    return fail(RNNWF_EINVAL, "the tensor-core regime is implemented for the tensorized 2D GRU and the vanilla 2D RNN cells");
+    return fail(RNNWF_EINVAL, "the tensor-core regime is implemented for the 2D cells (tensorized GRU, tensorized, vanilla RNN)");
   // column passes per site: 16 units x 7 blocks each for the tensorized GRU; the vanilla cell needs one (7 unit pieces)
   m.tc_np = (m.cell == CELL_VANILLA2D) ? 1 : (m.nh + TC_JP - 1) / TC_JP;
   if (m.tc_enabled) {
@@ -366,7 +366,10 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
     RNNWF_COUNT_LAUNCH();
     const bool bm = m.nh < m.nhp;     // biases through the tensor core when the operand has a free padding position
     const bool van = m.cell == CELL_VANILLA2D;
+    const bool ung = m.cell == CELL_TENS2D;
 #define RNNWF_TC_LAUNCH(MODE_) do { if (van) sweep_tc_kernel<MODE_, false, 1><<<s.grid, s.threads, s.smem, st>>>(P); \
+                                     else if (ung && bm) sweep_tc_kernel<MODE_, true, 2><<<s.grid, s.threads, s.smem, st>>>(P); \
+                                     else if (ung) sweep_tc_kernel<MODE_, false, 2><<<s.grid, s.threads, s.smem, st>>>(P); \
                                      else if (bm) sweep_tc_kernel<MODE_, true, 0><<<s.grid, s.threads, s.smem, st>>>(P); \
                                      else sweep_tc_kernel<MODE_, false, 0><<<s.grid, s.threads, s.smem, st>>>(P); } while (0)
     if (P.mode == MODE_SAMPLE) RNNWF_TC_LAUNCH(MODE_SAMPLE);
@@ -395,7 +398,7 @@ int set_saved(const rnnwf_model& m, SweepParams& P, void* saved, long long rows)
   const Saved sv = m.saved_layout(rows);
   char* b = static_cast<char*>(saved);
   P.sv_hist = reinterpret_cast<float*>(b + sv.off_hist);
-  P.sv_gates = m.gru_type ? reinterpret_cast<float4*>(b + sv.off_gates) : nullptr;
+  P.sv_gates = (m.gru_type || (m.tc_enabled && m.cell == CELL_TENS2D)) ? reinterpret_cast<float4*>(b + sv.off_gates) : nullptr;
   P.sv_cum = reinterpret_cast<double2*>(b + sv.off_cum);
   P.sv_himg = m.tc_enabled ? reinterpret_cast<float*>(b + sv.off_himg) : nullptr;
   P.sv_rows = rows;
@@ -547,6 +550,12 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
@@ -644,11 +653,11 @@ int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
                                                                            params_dev + h->tensor("b")->offset, h->nh, h->nhp, h->d_tcbias);
     } else {
       const long long n = 3LL * h->tc_np * (ts.b_bytes / 2);
+      auto opt = [&](const char* nm) -> const float* { const TensorInfo* t = h->tensor(nm); return t ? params_dev + t->offset : nullptr; };
       RNNWF_COUNT_LAUNCH(); pack_tc_kernel<<<std::min(2048, cdiv(n, 256)), 256, 0, st>>>(
-          params_dev + h->tensor("W")->offset, params_dev + h->tensor("Wg")->offset, params_dev + h->tensor("Wmerge")->offset,
-          params_dev + h->tensor("b")->offset, params_dev + h->tensor("bg")->offset,
+          params_dev + h->tensor("W")->offset, opt("Wg"), opt("Wmerge"), params_dev + h->tensor("b")->offset, opt("bg"),
           h->nh, h->nhp, h->tc_np, reinterpret_cast<__half*>(h->d_tcB));
-      RNNWF_COUNT_LAUNCH(); pack_tc_bias_kernel<<<1, 256, 0, st>>>(params_dev + h->tensor("b")->offset, params_dev + h->tensor("bg")->offset, h->nh, h->nhp, h->d_tcbias);
+      RNNWF_COUNT_LAUNCH(); pack_tc_bias_kernel<<<1, 256, 0, st>>>(params_dev + h->tensor("b")->offset, opt("bg"), h->nh, h->nhp, h->d_tcbias);
     }
   }
   CUDA_TRY(cudaGetLastError());

@@ -291,7 +291,8 @@ __device__ __forceinline__ void tc_ld28(uint32_t taddr, uint32_t (&d)[TC_TPS]) {
 
 // BIASMMA: the biases ride on the tensor core (num_units < padded width): position `num_units` of the horizontal
 // neighbour half of every operand is a constant 1 and that K row of the weight images holds the biases.
-// CELLK: 0 = tensorized GRU (7 accumulator blocks per unit, 16 units per column pass); 1 = vanilla 2D RNN
+// CELLK: 0 = tensorized GRU (7 accumulator blocks per unit, 16 units per column pass); 2 = un-gated tensorized cell
+// (2DHeisenberg/MDTensorizedcell.py: tanh(T:W + b)) = the same with u == 1 and zero gate / merge images; 1 = vanilla 2D RNN
 // (2DTFIM_2DRNN/MDRNNcell.py:21-35: elu(x_h Uh + h_h Wh + x_v Uv + h_v Wv + b)): one pass per site whose 7 "blocks" are
 // the 7 unit pieces a thread owns (unit = 16 blk + 4 sub + e); the neighbours are separable, so one weight image serves
 // every site, and the one-hot inputs / bias are added in the epilogue from small shared-memory tables.
@@ -747,7 +748,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
                 float gv = fmaf(cu, __uint_as_float(d[20 + e]), fmaf(cl, __uint_as_float(d[16 + e]), __uint_as_float(d[12 + e])));
                 if (!BIASMMA) { sv += bsv[e]; gv += bgv[e]; }
                 const float mv = __uint_as_float(d[24 + e]);
-                const float u = sigmoid_prescaled(gv);
+                const float u = (CELLK == 2) ? 1.0f : sigmoid_prescaled(gv);   // CELLK 2: un-gated tensorized cell, h = tanh(s)
                 const float ht = tanh_prescaled(sv);
                 // u ht + (1 - u) m.  Padding units (>= num_units) have zero weights and biases: u = 1/2, ht = m = 0 -> 0.
                 const float hv = fmaf(u, ht - mv, mv);
@@ -978,11 +979,13 @@ __global__ void pack_tc_kernel(const float* __restrict__ W, const float* __restr
     float v = 0.f;
     if (nh < nhp && slot == 0 && unit == nh && j < nh) {
       // bias row: the operand carries a constant 1 at position num_units of the horizontal half (all variants)
-      v = (blk == 0) ? b[j] : (blk == 3 ? bg[j] : 0.f);
+      v = (blk == 0) ? b[j] : ((blk == 3 && bg != nullptr) ? bg[j] : 0.f);
     } else if (unit < nh && j < nh) {
       const int i = slot * nh + unit;
       if (blk == 6) {
-        v = Wmerge[(long long)i * nh + j];
+        v = (Wmerge != nullptr) ? Wmerge[(long long)i * nh + j] : 0.f;
+      } else if (blk >= 3 && Wg == nullptr) {
+        v = 0.f;                                   // un-gated cell: no update gate
       } else {
         const float* T = (blk < 3) ? W : Wg;
         const float* w = T + ((long long)j * 2 * nh + i) * 4;
@@ -999,7 +1002,7 @@ __global__ void pack_tc_kernel(const float* __restrict__ W, const float* __restr
 __global__ void pack_tc_bias_kernel(const float* __restrict__ b, const float* __restrict__ bg, int nh, int nhp, float* __restrict__ out) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * nhp; i += gridDim.x * blockDim.x) {
     const int which = i / nhp, j = i - which * nhp;
-    out[i] = (j < nh) ? (which == 0 ? b[j] : bg[j]) : 0.f;
+    out[i] = (j < nh) ? (which == 0 ? b[j] : (bg != nullptr ? bg[j] : 0.f)) : 0.f;
   }
 }
 

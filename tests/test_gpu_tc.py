@@ -235,3 +235,41 @@ def test_tc_vanilla_tfim2d_local_energies_and_gradient(cuda, reuse):
     for n, v in eng.views(gb).items():
         r = e32.views(ga)[n]
         assert float((v - r).abs().max()) <= 1e-2 * (float(r.abs().max()) + 1e-30), n
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nh", [20, 24])
+def test_tc_ungated_tensorized_cell(cuda, nh):
+    """2DHeisenberg/MDTensorizedcell.py (tanh(T:W + b)) in the tensor-core regime: samples / log psi / E_loc against the
+    oracle, gradient against the oracle's autograd (both the bias-in-MMA and the plain variants: nh = 20 / 24)."""
+    eng = Engine(_lib.CELL_TENS2D, 4, 4, num_units=nh, complex_head=True, u1=True, seed=77, precision="tc")
+    g = torch.Generator().manual_seed(78)
+    p = eng.params.cpu()
+    eng.set_weights(p + 0.15 * (torch.rand(p.shape, generator=g) - 0.5))
+    assert "tcgen05" in eng.describe()
+    ns = 257
+    u = torch.rand(ns, 16, generator=g, dtype=torch.float32)
+    saved = eng.new_saved(ns)
+    s, lp, ph = eng.sample(ns, uniforms=u, saved=saved)
+    P = oracle_params(eng)
+    with torch.no_grad():
+        ref = oracle_run(eng, P, uniforms=u, numsamples=ns)
+    ok = (ref["margin"].min(dim=1).values > 1e-3).numpy()
+    s_cpu = s.cpu().long().numpy()
+    assert ok.mean() > 0.4 and (s_cpu[ok] == ref["samples"].numpy()[ok]).all()
+    scale = np.abs(ref["logp"].numpy()).max()
+    np.testing.assert_allclose(lp.cpu().numpy()[ok], ref["logp"].numpy()[ok], rtol=RTOL, atol=RTOL * scale * 0.1)
+    np.testing.assert_allclose(ph.cpu().numpy()[ok], ref["phase"].numpy()[ok], rtol=RTOL, atol=RTOL * 0.5 * scale)
+    e = eng.local_energies(_lib.HAM_HEIS2D, [1.0], s, lp, ph, saved=saved).cpu().numpy()
+    eref, _ = ole.heis2d_local_energies(1.0, s_cpu, oracle_logpsi_fn(eng, P))
+    np.testing.assert_allclose(e, eref, rtol=RTOL, atol=RTOL * np.abs(eref).max())
+    Er = torch.randn(ns, generator=g, dtype=torch.float64)
+    Ei = torch.randn(ns, generator=g, dtype=torch.float64)
+    Pg = oracle_params(eng, requires_grad=True)
+    r = oracle_run(eng, Pg, samples=s_cpu)
+    costs.cost_complex(r["logp"], r["phase"], torch.complex(Er, Ei)).backward()
+    sl, sp = costs.seeds_complex(lp.cpu(), torch.complex(Er, Ei))
+    grad = eng.backward(s, saved, sl, sp).cpu()
+    for n, v in eng.views(grad).items():
+        gr = Pg[n].grad
+        assert float((v.double() - gr).abs().max()) / (float(gr.abs().max()) + 1e-30) < 1e-2, n
