@@ -55,6 +55,7 @@ struct rnnwf_model_impl {
   // tensor-core regime
   int precision = 0;            // 0: FP32 FFMA, 1: BF16 tensor cores (tcgen05), hi+lo split activations
   bool tc_enabled = false;
+  bool tc4 = false;             // tensor-core sweep of the four-neighbour GRU (sweep_tc4.cuh); saved state and backward as in the FFMA regime
   int tc_np = 0;
   unsigned char* d_tcB = nullptr;
   float* d_tcbias = nullptr;

@@ -11,6 +11,7 @@
 #include "model.h"
 #include "sweep.cuh"
 #include "sweep_tc.cuh"
+#include "sweep_tc4.cuh"
 #include "pack.cuh"
 #include "eloc.cuh"
 #include "gemm_tc.cuh"
@@ -278,14 +279,21 @@ int build_model(rnnwf_model& m) {
     boff += m.Gp;
   }
   m.tc_enabled = (m.precision == 1 && (m.cell == CELL_TENSGRU2D || m.cell == CELL_TENS2D || m.cell == CELL_VANILLA2D));
-  if (m.precision == 1 && !m.tc_enabled)
-    return fail(RNNWF_EINVAL, "the tensor-core regime is implemented for the 2D cells (tensorized GRU, tensorized, vanilla RNN)");
+  m.tc4 = (m.precision == 1 && m.cell == CELL_GRU4);
+  if (m.precision == 1 && !m.tc_enabled && !m.tc4)
+    return fail(RNNWF_EINVAL, "the tensor-core regime is implemented for the 2D cells (tensorized GRU, tensorized, vanilla RNN, four-neighbour GRU)");
   // column passes per site: 16 units x 7 blocks each for the tensorized GRU; the vanilla cell needs one (7 unit pieces)
   m.tc_np = (m.cell == CELL_VANILLA2D) ? 1 : (m.nh + TC_JP - 1) / TC_JP;
   if (m.tc_enabled) {
     const TcSmem ts(m.nhp, m.Tsym, m.Q);
     if (ts.total > 227 * 1024 || 2 * TC_N + 2 * m.nhp > TC_TMEM_COLS || (m.nhp + TC_JP - 1) / TC_JP > 7)
       return fail(RNNWF_EINVAL, "the tensor-core regime needs num_units <= 104 (weight stages in shared memory, operand in TMEM)");
+  }
+  if (m.tc4) {
+    m.tc_np = (m.nh + T4_UP - 1) / T4_UP;      // column passes of 64 units; the hidden axis is padded to 64 tc_np
+    if (m.tc_np > T4_MAXNP) return fail(RNNWF_EINVAL, "the tensor-core regime of the four-neighbour GRU needs num_units <= 256");
+    if (T4Smem(m.tc_np, m.Q).total > 227 * 1024) return fail(RNNWF_EINVAL, "the tensor-core regime of the four-neighbour GRU: lattice too large for shared memory");
+    m.ring_len = m.Q;
   }
   m.wpack_float4 = std::max(1LL, woff);
   m.xtab_float4 = std::max(1LL, xoff);
@@ -305,7 +313,7 @@ const void* sweep_fn(const rnnwf_model& m) {
 }
 // persistent CTAs the scratch ring is sized for, in units of 128-row tiles: up to 4 per SM when shared memory allows
 int max_ctas(const rnnwf_model& m) {
-  if (m.tc_enabled) return m.num_sms;
+  if (m.tc_enabled || m.tc4) return m.num_sms;
   SmemLayout L(m.ncls_max, m.Gblk, 128, m.ldH, m.nhp, m.ND, m.Tsym);
   const int occ = std::max(1, std::min(4, (227 * 1024) / std::max(1, L.total)));
   return m.num_sms * occ;
@@ -316,6 +324,12 @@ int pick_shape(const rnnwf_model& m, long long rows, LaunchShape& s) {
     const TcSmem ts(m.nhp, m.Tsym, m.Q);
     const long long tiles = (rows + TC_ROWS - 1) / TC_ROWS;
     s.WR = 4; s.Mp = TC_ROWS; s.Mr = TC_ROWS; s.threads = TC_THREADS; s.smem = ts.total;
+    s.grid = (int)std::max(1LL, std::min<long long>(tiles, m.num_sms));
+    return RNNWF_OK;
+  }
+  if (m.tc4) {
+    const long long tiles = (rows + T4_ROWS - 1) / T4_ROWS;
+    s.WR = 4; s.Mp = T4_ROWS; s.Mr = T4_ROWS; s.threads = T4_THREADS; s.smem = T4Smem(m.tc_np, m.Q).total;
     s.grid = (int)std::max(1LL, std::min<long long>(tiles, m.num_sms));
     return RNNWF_OK;
   }
@@ -380,6 +394,15 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
     if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("tensor-core sweep launch: ") + cudaGetErrorString(e));
     return RNNWF_OK;
   }
+  if (m.tc4) {
+    RNNWF_COUNT_LAUNCH();
+    if (P.mode == MODE_SAMPLE) sweep_tc4_kernel<MODE_SAMPLE><<<s.grid, s.threads, s.smem, st>>>(P);
+    else if (P.mode == MODE_CHILD) sweep_tc4_kernel<MODE_CHILD><<<s.grid, s.threads, s.smem, st>>>(P);
+    else sweep_tc4_kernel<MODE_EVAL><<<s.grid, s.threads, s.smem, st>>>(P);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("tensor-core sweep (four-neighbour GRU) launch: ") + cudaGetErrorString(e));
+    return RNNWF_OK;
+  }
   if (m.NTU == 3 && m.TJ == 5) e = launch_inst<5, 3>(P, s, st);
   else if (m.NTU == 3 && m.TJ == 4) e = launch_inst<4, 3>(P, s, st);
   else e = launch_inst<4, 4>(P, s, st);
@@ -388,6 +411,7 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
 }
 
 long long ring_bytes(const rnnwf_model& m, int grid, int Mp) {
+  if (m.tc4) return (long long)grid * m.Q * t4_step_bytes(m.tc_np);   // FP16 chunk images of every site, per persistent CTA
   // tensor-core regime: one FP16 history image per slot in the fixed quad layout of sweep_tc.cuh (TC_RING_SLOT bytes)
   const long long slot = m.tc_enabled ? std::max<long long>((long long)TC_RING_SLOT, (long long)Mp * m.nhp * 4) : (long long)Mp * m.nhp * 4;
   return (long long)grid * m.ring_len * slot;
@@ -560,6 +584,13 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
   }
+  if (m->tc4) {
+    const int t4s = T4Smem(m->tc_np, m->Q).total;
+    CREATE_TRY(cudaMalloc(&m->d_tcB, (size_t)m->tc_np * (size_t)t4_pass_bytes(m->tc_np)));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc4_kernel<MODE_SAMPLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, t4s));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc4_kernel<MODE_EVAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, t4s));
+    CREATE_TRY(cudaFuncSetAttribute(sweep_tc4_kernel<MODE_CHILD>, cudaFuncAttributeMaxDynamicSharedMemorySize, t4s));
+  }
   CREATE_TRY(backward_init());
   if (m->tc_enabled) {
     CREATE_TRY(backward_init_tc(*m));
@@ -659,6 +690,12 @@ int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
           h->nh, h->nhp, h->tc_np, reinterpret_cast<__half*>(h->d_tcB));
       RNNWF_COUNT_LAUNCH(); pack_tc_bias_kernel<<<1, 256, 0, st>>>(params_dev + h->tensor("b")->offset, opt("bg"), h->nh, h->nhp, h->d_tcbias);
     }
+  }
+  if (h->tc4) {
+    const long long n = (long long)h->tc_np * (t4_pass_bytes(h->tc_np) / 2);
+    RNNWF_COUNT_LAUNCH(); pack_tc4_kernel<<<std::min(2048, cdiv(n, 256)), 256, 0, st>>>(
+        params_dev + h->tensor("W")->offset, params_dev + h->tensor("Wg")->offset, params_dev + h->tensor("Wmerge")->offset,
+        params_dev + h->tensor("b")->offset, params_dev + h->tensor("bg")->offset, h->nh, h->tc_np, reinterpret_cast<__half*>(h->d_tcB));
   }
   CUDA_TRY(cudaGetLastError());
   h->d_params = params_dev;
@@ -984,7 +1021,8 @@ int rnnwf_describe(rnnwf_handle h, char* buf, int cap) {
                 "cell=%d nh=%d (padded %d) steps=%d symbols=%d slots=%d classes=%d | pipe=%s, tile=128 rows x %d col-groups "
                 "(TJ=%d NTU=%d WC=%d passes=%d), k-chunk=%d, ring=%d steps, params=%lld",
                 h->cell, h->nh, h->nhp, h->Q, h->Tsym, h->nslots, h->ncls_max,
-                h->tc_enabled ? "tcgen05 FP16 operands, FP32 accumulate in TMEM (column passes of 112, double-buffered)" : "FFMA fp32", h->Gblk, h->TJ, h->NTU, h->WC, h->ncb, KC,
+                h->tc_enabled ? "tcgen05 FP16 operands, FP32 accumulate in TMEM (column passes of 112, double-buffered)"
+                              : (h->tc4 ? "tcgen05 FP16 operands streamed from the L2 ring (A) and the weight image (B), FP32 accumulate in TMEM (column passes of 192, double-buffered)" : "FFMA fp32"), h->Gblk, h->TJ, h->NTU, h->WC, h->ncb, KC,
                 h->ring_len, (long long)h->num_params);
   return RNNWF_OK;
 }

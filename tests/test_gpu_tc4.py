@@ -1,0 +1,90 @@
+"""GPU parity of the tensor-core (tcgen05, FP16 operands) regime of the four-neighbour 2D GRU of the Rydberg Kagome
+wavefunction (csrc/sweep_tc4.cuh) against the float64 oracle.  Tolerance: 1e-3 relative on log-probabilities and E_loc
+(the reduced-precision bound of BASELINE.json's north_star); samples must agree with the oracle wherever no draw falls
+within 1e-3 of a CDF threshold; the gradient (FFMA backward fed with the saved state this sweep wrote) within 1e-2 per
+tensor of the oracle's autograd."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import local_energies as ole
+from oracle import costs
+from rnnwavefunctions_b200 import _lib
+from rnnwavefunctions_b200.engine import Engine
+from helpers import oracle_params, oracle_run, oracle_logpsi_fn
+
+RTOL = 1e-3
+HAM = [1.7 ** 6, 3.3, 1.0, 2.001]
+
+
+def _mk(nx, ny, nh, seed=71, precision="tc"):
+    eng = Engine(_lib.CELL_GRU4, nx, ny, num_units=nh, seed=seed, precision=precision)
+    g = torch.Generator().manual_seed(seed + 1)
+    p = eng.params.cpu()
+    eng.set_weights(p + 0.1 * (torch.rand(p.shape, generator=g) - 0.5))
+    return eng
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nx,ny,nh,ns", [(3, 3, 40, 120), (2, 3, 64, 37), (4, 4, 256, 300), (5, 3, 100, 200), (4, 5, 130, 20000)])
+def test_tc4_sample_and_logpsi(cuda, nx, ny, nh, ns):
+    eng = _mk(nx, ny, nh)
+    assert "tcgen05" in eng.describe()
+    nref = min(ns, 300)                      # the oracle checks the first rows; the rest through the FP32 regime below
+    u = torch.rand(ns, eng.nsteps, generator=torch.Generator().manual_seed(ns), dtype=torch.float32)
+    s, lp, _ = eng.sample(ns, uniforms=u)
+    P = oracle_params(eng)
+    with torch.no_grad():
+        ref = oracle_run(eng, P, uniforms=u[:nref], numsamples=nref)
+    ok = (ref["margin"].min(dim=1).values > 1e-3).numpy()
+    assert ok.mean() > 0.5
+    s_cpu = s.cpu().long().numpy()
+    assert (s_cpu[:nref][ok] == ref["samples"].numpy()[ok]).all()
+    scale = np.abs(ref["logp"].numpy()).max()
+    np.testing.assert_allclose(lp.cpu().numpy()[:nref][ok], ref["logp"].numpy()[ok], rtol=RTOL, atol=RTOL * scale * 0.1)
+    # teacher forcing reproduces the sampling pass bit for bit, and agrees with the oracle on the drawn configurations
+    lp2, _ = eng.logpsi(s)
+    np.testing.assert_allclose(lp2.cpu().numpy(), lp.cpu().numpy(), rtol=1e-12, atol=1e-12)
+    with torch.no_grad():
+        ref2 = oracle_run(eng, P, samples=s_cpu[:nref])
+    np.testing.assert_allclose(lp2.cpu().numpy()[:nref], ref2["logp"].numpy(), rtol=RTOL, atol=RTOL * scale * 0.1)
+    if ns > nref:                            # more tiles than SMs: every row against the FP32 regime on the same weights
+        f32 = Engine(_lib.CELL_GRU4, nx, ny, num_units=nh, seed=71)
+        f32.set_weights(eng.params)
+        lp3, _ = f32.logpsi(s)
+        np.testing.assert_allclose(lp2.cpu().numpy(), lp3.cpu().numpy(), rtol=RTOL, atol=RTOL * scale * 0.1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("reuse", [False, True])
+@pytest.mark.parametrize("nx,ny,nh", [(3, 3, 40), (4, 3, 256)])
+def test_tc4_rydberg_local_energies(cuda, reuse, nx, ny, nh):
+    eng = _mk(nx, ny, nh, seed=81)
+    ns = 150
+    saved = eng.new_saved(ns) if reuse else None
+    u = torch.rand(ns, eng.nsteps, generator=torch.Generator().manual_seed(5), dtype=torch.float32)
+    s, lp, ph = eng.sample(ns, uniforms=u, saved=saved)
+    e = eng.local_energies(_lib.HAM_RYDBERG, HAM, s, lp, ph, saved=saved).cpu().numpy()
+    pos = ole.generate_kagome(nx, ny)
+    nb, dist = ole.neighbouring_atoms(pos, HAM[3], nx, ny)
+    ref = ole.rydberg_local_energies(HAM[0], HAM[1], HAM[2], nb, dist, s.cpu().numpy().astype(np.int64),
+                                     oracle_logpsi_fn(eng, oracle_params(eng)))
+    np.testing.assert_allclose(e.real, ref, rtol=RTOL, atol=RTOL * np.abs(ref).max())
+
+
+@pytest.mark.gpu
+def test_tc4_saved_state_feeds_the_backward(cuda):
+    """The FFMA backward consumes the hidden states and gates the tensor-core sweep saved."""
+    nx, ny, nh, ns = 3, 3, 72, 200
+    eng = _mk(nx, ny, nh, seed=91)
+    saved = eng.new_saved(ns)
+    u = torch.rand(ns, eng.nsteps, generator=torch.Generator().manual_seed(9), dtype=torch.float32)
+    s, lp, ph = eng.sample(ns, uniforms=u, saved=saved)
+    E = torch.randn(ns, generator=torch.Generator().manual_seed(10), dtype=torch.float64)
+    Pg = oracle_params(eng, requires_grad=True)
+    r = oracle_run(eng, Pg, samples=s.cpu().long().numpy())
+    costs.cost_real(r["logp"], E).backward()
+    grad = eng.backward(s, saved, costs.seeds_real(E)).cpu()
+    for n, v in eng.views(grad).items():
+        gr = Pg[n].grad
+        assert float((v.double() - gr).abs().max()) <= 1e-2 * float(gr.abs().max()) + 1e-30, f"gradient of {n} differs"
