@@ -324,7 +324,7 @@ def main():
     ek["cell"] = getattr(_lib, "CELL_" + ek["cell"])
     precision = args.precision
     if precision == "auto":
-        precision = "tc" if w["eng"]["cell"] in ("TENSGRU2D", "VANILLA2D") else "fp32"
+        precision = "tc" if w["eng"]["cell"] in ("TENSGRU2D", "VANILLA2D", "GRU4") else "fp32"
     eng = Engine(seed=111, precision=precision, **ek)
     ham = getattr(_lib, "HAM_" + w["ham"])
     ns = w["ns"]
@@ -417,7 +417,35 @@ def main():
     except Exception:
         pass
     bf16_peak = peaks.get("bf16_tflops_sustained", 1400.0)
-    if precision == "tc":
+    if precision == "tc" and w["eng"]["cell"] == "GRU4":
+        # sweep_tc4_kernel: per row and unit cell the dense [(live neighbours)*nhq + 32] x [3*nhq] contraction, nhq = 64*passes;
+        # a child flipped in cell t re-runs cells t..T-1 (prefix reuse), three children per cell and sample
+        nx, ny, nh = w["eng"]["nx"], w["eng"]["ny"], w["eng"]["num_units"]
+        nhq = (nh + 63) // 64 * 64
+        step = lambda ix, iy: iy * nx + (ix if iy % 2 == 0 else nx - 1 - ix)
+        site_flops = []
+        for iy in range(ny):
+            for k in range(nx):
+                ix = k if iy % 2 == 0 else nx - 1 - k
+                d = 1 if iy % 2 == 0 else -1
+                t = iy * nx + k
+                keys = [(ix - d, iy), (ix, iy - 1), ((ix + d) % nx, iy), (ix, (iy + 1) % ny)]
+                live = sum(1 for (a, b) in keys if 0 <= a < nx and 0 <= b < ny and step(a, b) < t)
+                site_flops.append(2 * (live * nhq + 32) * 3 * nhq + 2 * nh * 8)
+        suffix = np.cumsum(site_flops[::-1])[::-1]
+        per_sample = 3 * float(suffix.sum()) if V.prefix_reuse else 3 * T * float(suffix[0])
+        exec_flops = ns * per_sample
+        achieved = exec_flops / (eloc_ms * 1e-3) / 1e12
+        roofline = {"bound": "tensor", "kernel": "sweep_tc4_kernel (MODE_CHILD)", "achieved": achieved, "peak": bf16_peak, "unit": "TFLOP/s",
+                    "frac": achieved / bf16_peak, "traffic": None,
+                    "peak_source": ("MEASURED_PEAKS.json bf16_tflops_sustained (16-bit tensor peak, kernel timed inside a long step)"
+                                    if peaks else "fallback 1400 (B200_PROFILING.md)"),
+                    "executed_flops_per_launch": exec_flops, "algorithmic_flops_per_launch": alg_flops,
+                    "algorithmic_tflops": alg_flops / (eloc_ms * 1e-3) / 1e12, "ffma_peak_tflops_measured": best,
+                    "launch_ms": eloc_ms, "mma_columns_per_row_site": 3 * nhq,
+                    "note": "executed = MMA flops issued per row (absent neighbours skipped, hidden axis padded to 64 per pass, K=32 input/bias "
+                            "job, prefix reuse counted per row); launch_ms brackets rnnwf_local_energies (enumeration kernels + sweep)"}
+    elif precision == "tc":
         # the tensor-core sweep executes, per row and site, the dense [2*nhp] x [7*16*passes] contraction
         nhp = (w["eng"]["num_units"] + 7) // 8 * 8
         npass = (w["eng"]["num_units"] + 15) // 16

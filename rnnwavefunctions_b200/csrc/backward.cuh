@@ -517,6 +517,11 @@ struct Gemm {
     dim3 g((N + GB - 1) / GB, (unsigned)((M + GB - 1) / GB));
     RNNWF_COUNT_LAUNCH(); gemm_nt_kernel<<<g, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, N, K, beta);
   }
+  // C[M,N] (+)= A[M,K] B[N,K]^T; reduced-precision regime: TF32 tensor cores when the operands are aligned for it
+  void nt_fast(const float* A, int lda, const float* B, int ldb, float* C, int ldc, long long M, int N, int K, int beta) const {
+    if (tc && N >= 16 && K >= 16 && gemm_tc_launch(st, A, lda, 1, B, ldb, 1, C, ldc, M, N, K, beta ? 1 : 0)) return;
+    nt(A, lda, B, ldb, C, ldc, M, N, K, beta);
+  }
   void nn(const float* A, int lda, const float* B, int ldb, float* C, int ldc, long long M, int N, int K, int beta) const {
     if (M <= 0 || N <= 0 || K <= 0) return;
     dim3 g((N + GB - 1) / GB, (unsigned)((M + GB - 1) / GB));
@@ -717,12 +722,13 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
       case CELL_GRU4: {
         const int Kz = 24 + 4 * nh;
         RNNWF_COUNT_LAUNCH(); build_gru4_kernel<<<nblk(R * Kz), tpb, 0, st>>>(S, Z);
-        G.nt(dp0, nh, P("W"), nh, dZ, Kz, R, Kz, nh, 0);                  // dz  = ds W^T
-        G.nt(dp1, nh, P("Wg"), nh, dZ, Kz, R, Kz, nh, 1);                 // dz += dg Wg^T
-        G.nt(dp2, nh, P("Wmerge"), nh, dZ + 24, Kz, R, 4 * nh, nh, 1);    // dz[:,24:] += dm Wmerge^T
-        G.tn(Z, Kz, dp0, nh, Gd("W"), nh, R, Kz, nh);
-        G.tn(Z, Kz, dp1, nh, Gd("Wg"), nh, R, Kz, nh);
-        G.tn(Z + 24, Kz, dp2, nh, Gd("Wmerge"), nh, R, 4 * nh, nh);
+        // (reduced-precision regime: these six GEMMs run on the tensor cores in TF32, gemm_tc.cuh)
+        G.nt_fast(dp0, nh, P("W"), nh, dZ, Kz, R, Kz, nh, 0);                  // dz  = ds W^T
+        G.nt_fast(dp1, nh, P("Wg"), nh, dZ, Kz, R, Kz, nh, 1);                 // dz += dg Wg^T
+        G.nt_fast(dp2, nh, P("Wmerge"), nh, dZ + 24, Kz, R, 4 * nh, nh, 1);    // dz[:,24:] += dm Wmerge^T
+        G.tn_long(Z, Kz, dp0, nh, Gd("W"), nh, R, Kz, nh);
+        G.tn_long(Z, Kz, dp1, nh, Gd("Wg"), nh, R, Kz, nh);
+        G.tn_long(Z + 24, Kz, dp2, nh, Gd("Wmerge"), nh, R, 4 * nh, nh);
         G.colsum(dp0, nh, R, nh, Gd("b"));
         G.colsum(dp1, nh, R, nh, Gd("bg"));
         RNNWF_COUNT_LAUNCH(); scatter_gru4_kernel<<<nblk(R * 4 * nh), tpb, 0, st>>>(S, dZ);
