@@ -18,6 +18,7 @@
 #include "model.h"
 #include "bwd_tc.cuh"
 #include "dw_tc.cuh"
+#include "bwd_tc4.cuh"
 
 namespace rnnwf {
 
@@ -431,7 +432,11 @@ inline cudaError_t backward_init_tc(const rnnwf_model_impl& m) {
   return cudaFuncSetAttribute(dw_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dw_smem_bytes(m.nhp));
 }
 
-struct BwdLayout { long long off_dh, off_dp, off_Z, off_dZ, off_hc, off_dhc, off_dlog, off_X, off_wstack, off_wimg, off_dpT, off_jobs, off_cls, total; long long dpw; int Kz; bool batched; };
+struct BwdLayout { long long off_dh, off_dp, off_Z, off_dZ, off_hc, off_dhc, off_dlog, off_X, off_wstack, off_wimg, off_dpT, off_jobs, off_cls,
+                   off_t4_wt, off_t4_dimg, off_t4_himg, off_t4_ximg, total; long long dpw; int Kz; bool batched; };
+inline cudaError_t backward_init_tc4(const rnnwf_model_impl& m) {
+  return cudaFuncSetAttribute(bwd4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, B4Smem(m.tc_np, m.Q).total);
+}
 
 inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   auto al = [](long long x) { return (x + 255) & ~255LL; };
@@ -443,7 +448,7 @@ inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   // ALL steps, so that dW, dWg, dWmerge, the head kernels and every bias come out of one long-K GEMM / reduction each
   // after the reverse sweep instead of ~10 small launches per lattice site.
   L.batched = (m.cell == CELL_TENS2D || m.cell == CELL_TENSGRU2D);
-  const long long nb = L.batched ? m.Q : 1;
+  const long long nb = (L.batched || m.tc4) ? m.Q : 1;   // (four-neighbour GRU, tensor-core regime: ds, dg, dm of all cells)
   // tensor-core regime of the tensorized GRU: the reverse sweep / weight-gradient kernels have their own layouts
   // (d h tile-blocked, feature-major ds/dg/dm); none of the per-site FFMA-regime operands below is needed
   const bool tcs = m.tc_enabled;   // (tensorized GRU and vanilla 2D RNN both have the tensor-core backward)
@@ -454,12 +459,20 @@ inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   L.off_dZ = o;   o += al(tcs ? 0 : R * (long long)L.Kz * 4);   // tensorized cells: the per-step linearised operand P [R][7nh] lives here
   L.off_hc = o;   o += al(tcs ? 0 : nb * R * 2 * nh * 4);
   L.off_dhc = o;  o += al(tcs ? 0 : R * 2 * nh * 4);
-  L.off_dlog = o; o += al(((L.batched || tcs) ? (long long)m.Q : 1LL) * R * 8 * 4);   // d(logits) of all sites in the batched / tensor-core paths
+  L.off_dlog = o; o += al(((L.batched || tcs || m.tc4) ? (long long)m.Q : 1LL) * R * 8 * 4);   // d(logits) of all sites in the batched / tensor-core paths
   L.off_X = o;    o += al(R * 8 * 4);
   L.off_wstack = o; o += al(L.batched ? 3LL * 2 * nh * 7 * nh * 4 : 0);
   L.off_wimg = o;   o += al(tcs ? 3LL * ((m.nhp + TC_JP - 1) / TC_JP) * BtSmem(m.nhp, m.Tsym, m.Q).b_bytes : 0);   // Wstack^T chunks of the reverse sweep
   L.off_dpT = o;    o += al(tcs ? tc_dpt_bytes(m.Q, R, m.nhp) : 0);
   L.off_jobs = o; L.off_cls = o;   // (the work plan lives in the handle)
+  {
+    // four-neighbour GRU, tensor-core regime (bwd_tc4.cuh): transposed weight image and the BF16 images of every (cell, tile)
+    const long long t4 = m.tc4 ? 1 : 0, tiles = (R + 127) / 128, NP = m.tc_np;
+    L.off_t4_wt = o;   o += al(t4 * 4 * 3 * NP * (64 * NP) * 128);
+    L.off_t4_dimg = o; o += al(t4 * m.Q * tiles * 3 * NP * (long long)B4_A_BYTES);
+    L.off_t4_himg = o; o += al(t4 * m.Q * tiles * NP * (long long)B4_A_BYTES);
+    L.off_t4_ximg = o; o += al(t4 * m.Q * tiles * 4 * 128 * 16);
+  }
   L.total = o;
   return L;
 }
@@ -659,6 +672,44 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
       G.colsum(dlog_base, m.ND, RQ, m.D, Gd("dense.b"));
       if (m.complex_head) G.colsum(dlog_base + m.D, m.ND, RQ, 2, Gd("dense_phase.b"));
     }
+    e = cudaGetLastError();
+    if (e != cudaSuccess) { err = std::string("rnnwf_backward kernels: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
+    return RNNWF_OK;
+  }
+
+  if (m.tc4) {
+    // Four-neighbour GRU, tensor-core regime: the whole recurrence is one persistent kernel (bwd_tc4.cuh); the weight
+    // gradients follow from the (ds, dg, dm) and d(logits) of all cells it leaves behind.
+    const long long tiles = (R + 127) / 128, RQ = (long long)m.Q * R;
+    unsigned char* wt = reinterpret_cast<unsigned char*>(ws + L.off_t4_wt);
+    RNNWF_COUNT_LAUNCH(); pack_bwd4_kernel<<<512, 256, 0, st>>>(P("W"), P("Wg"), P("Wmerge"), nh, m.tc_np, reinterpret_cast<__nv_bfloat16*>(wt));
+    Bwd4Params B;
+    B.Q = m.Q; B.nh = nh; B.nhp = nhp; B.NP = m.tc_np; B.Gp = m.Gp; B.nsites = m.nsites; B.R = R;
+    B.steps = m.d_steps; B.cfg = cfg; B.hist = hist; B.gates = gates; B.dh = dh; B.dp = dp; B.dlog = dlog_base;
+    B.seed = seed_logp; B.head_w = m.d_head_w; B.head_b = m.d_head_b; B.Wt = wt;
+    B.dimg = reinterpret_cast<unsigned char*>(ws + L.off_t4_dimg);
+    B.himg = reinterpret_cast<unsigned char*>(ws + L.off_t4_himg);
+    B.ximg = reinterpret_cast<unsigned char*>(ws + L.off_t4_ximg);
+    RNNWF_COUNT_LAUNCH(); bwd4_kernel<<<(unsigned)std::min<long long>(tiles, m.num_sms), B4_THREADS, B4Smem(m.tc_np, m.Q).total, st>>>(B);
+    float* dsA = dp;
+    float* dgA = dp + RQ * nh;
+    float* dmA = dp + 2 * RQ * nh;
+    const int Kz = 24 + 4 * nh;
+    for (int q = 0; q < m.Q; ++q) {
+      const StepMeta& sm = m.steps[q];
+      BwdStep S;
+      std::memset(&S, 0, sizeof(S));
+      S.q = q; S.nh = nh; S.nhp = nhp; S.nsites = m.nsites; S.R = R; S.cfg = cfg; S.hist = hist; S.bits = m.bits;
+      for (int k = 0; k < MAX_SLOTS; ++k) { S.nbr[k] = sm.nbr[k]; S.nsym_site[k] = (sm.nsym[k] >= 0) ? m.site_of_t[sm.nsym[k]] : -1; }
+      RNNWF_COUNT_LAUNCH(); build_gru4_kernel<<<nblk(R * Kz), tpb, 0, st>>>(S, Z_base);
+      G.tn_long(Z_base, Kz, dsA + (long long)q * R * nh, nh, Gd("W"), nh, R, Kz, nh);
+      G.tn_long(Z_base, Kz, dgA + (long long)q * R * nh, nh, Gd("Wg"), nh, R, Kz, nh);
+      G.tn_long(Z_base + 24, Kz, dmA + (long long)q * R * nh, nh, Gd("Wmerge"), nh, R, 4 * nh, nh);
+    }
+    G.colsum(dsA, nh, RQ, nh, Gd("b"));
+    G.colsum(dgA, nh, RQ, nh, Gd("bg"));
+    G.tn(hist, nhp, dlog_base, m.ND, Gd("dense.W"), m.D, RQ, nh, m.D);
+    G.colsum(dlog_base, m.ND, RQ, m.D, Gd("dense.b"));
     e = cudaGetLastError();
     if (e != cudaSuccess) { err = std::string("rnnwf_backward kernels: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
     return RNNWF_OK;

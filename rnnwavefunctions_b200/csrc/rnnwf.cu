@@ -592,6 +592,7 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc4_kernel<MODE_CHILD>, cudaFuncAttributeMaxDynamicSharedMemorySize, t4s));
   }
   CREATE_TRY(backward_init());
+  if (m->tc4) CREATE_TRY(backward_init_tc4(*m));
   if (m->tc_enabled) {
     CREATE_TRY(backward_init_tc(*m));
     CREATE_TRY(cudaMalloc(&m->d_dw_jobs, 1024 * sizeof(DwJob)));
