@@ -435,7 +435,36 @@ inline cudaError_t backward_init_tc(const rnnwf_model_impl& m) {
 struct BwdLayout { long long off_dh, off_dp, off_Z, off_dZ, off_hc, off_dhc, off_dlog, off_X, off_wstack, off_wimg, off_dpT, off_jobs, off_cls,
                    off_t4_wt, off_t4_dimg, off_t4_himg, off_t4_ximg, total; long long dpw; int Kz; bool batched; };
 inline cudaError_t backward_init_tc4(const rnnwf_model_impl& m) {
-  return cudaFuncSetAttribute(bwd4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, B4Smem(m.tc_np, m.Q).total);
+  cudaError_t e = cudaFuncSetAttribute(bwd4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, B4Smem(m.tc_np, m.Q).total);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(dw4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DW4_SMEM);
+}
+// Work plan of dw4_kernel: every output tile's (cell, tile) items split into contiguous ranges, ~3 jobs per SM in total.
+inline void dw4_plan(const rnnwf_model_impl& m, long long R, std::vector<Dw4Job>& jobs, std::vector<int>& sites, int sites_n[5]) {
+  const int tiles = (int)((R + 127) / 128), N4 = 64 * m.tc_np;
+  sites.assign((size_t)5 * m.Q, 0);
+  for (int s = 0; s < 5; ++s) {
+    sites_n[s] = 0;
+    for (int q = 0; q < m.Q; ++q)
+      if (s == 4 || m.steps[q].nbr[s] >= 0) sites[(size_t)s * m.Q + sites_n[s]++] = q;
+  }
+  struct Out { int kind, slot, m0, blk; long long items; };
+  std::vector<Out> outs;
+  long long total = 0;
+  for (int s = 0; s < 4; ++s)
+    for (int m0 = 0; m0 < N4 && m0 < m.nh; m0 += 128)
+      for (int blk = 0; blk < 3; ++blk) { outs.push_back({0, s, m0, blk, (long long)sites_n[s] * tiles}); total += outs.back().items; }
+  for (int blk = 0; blk < 2; ++blk) { outs.push_back({1, 0, 0, blk, (long long)m.Q * tiles}); total += outs.back().items; }
+  const long long target = std::max<long long>(8, (total + 3LL * m.num_sms - 1) / (3LL * m.num_sms));   // items per job
+  jobs.clear();
+  for (auto& o : outs) {
+    if (o.items <= 0) continue;
+    const long long parts = (o.items + target - 1) / target;
+    for (long long p = 0; p < parts && jobs.size() < 4096; ++p) {
+      const long long b = o.items * p / parts, e = o.items * (p + 1) / parts;
+      if (e > b) jobs.push_back({(int16_t)o.kind, (int16_t)o.slot, (int16_t)o.m0, (int16_t)o.blk, (int32_t)b, (int32_t)(e - b)});
+    }
+  }
 }
 
 inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
@@ -448,7 +477,7 @@ inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   // ALL steps, so that dW, dWg, dWmerge, the head kernels and every bias come out of one long-K GEMM / reduction each
   // after the reverse sweep instead of ~10 small launches per lattice site.
   L.batched = (m.cell == CELL_TENS2D || m.cell == CELL_TENSGRU2D);
-  const long long nb = (L.batched || m.tc4) ? m.Q : 1;   // (four-neighbour GRU, tensor-core regime: ds, dg, dm of all cells)
+  const long long nb = L.batched ? m.Q : 1;
   // tensor-core regime of the tensorized GRU: the reverse sweep / weight-gradient kernels have their own layouts
   // (d h tile-blocked, feature-major ds/dg/dm); none of the per-site FFMA-regime operands below is needed
   const bool tcs = m.tc_enabled;   // (tensorized GRU and vanilla 2D RNN both have the tensor-core backward)
@@ -685,29 +714,33 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
     RNNWF_COUNT_LAUNCH(); pack_bwd4_kernel<<<512, 256, 0, st>>>(P("W"), P("Wg"), P("Wmerge"), nh, m.tc_np, reinterpret_cast<__nv_bfloat16*>(wt));
     Bwd4Params B;
     B.Q = m.Q; B.nh = nh; B.nhp = nhp; B.NP = m.tc_np; B.Gp = m.Gp; B.nsites = m.nsites; B.R = R;
-    B.steps = m.d_steps; B.cfg = cfg; B.hist = hist; B.gates = gates; B.dh = dh; B.dp = dp; B.dlog = dlog_base;
+    B.steps = m.d_steps; B.cfg = cfg; B.hist = hist; B.gates = gates; B.dh = dh; B.dp = nullptr; B.dlog = dlog_base;
     B.seed = seed_logp; B.head_w = m.d_head_w; B.head_b = m.d_head_b; B.Wt = wt;
     B.dimg = reinterpret_cast<unsigned char*>(ws + L.off_t4_dimg);
     B.himg = reinterpret_cast<unsigned char*>(ws + L.off_t4_himg);
     B.ximg = reinterpret_cast<unsigned char*>(ws + L.off_t4_ximg);
     RNNWF_COUNT_LAUNCH(); bwd4_kernel<<<(unsigned)std::min<long long>(tiles, m.num_sms), B4_THREADS, B4Smem(m.tc_np, m.Q).total, st>>>(B);
-    float* dsA = dp;
-    float* dgA = dp + RQ * nh;
-    float* dmA = dp + 2 * RQ * nh;
-    const int Kz = 24 + 4 * nh;
-    for (int q = 0; q < m.Q; ++q) {
-      const StepMeta& sm = m.steps[q];
-      BwdStep S;
-      std::memset(&S, 0, sizeof(S));
-      S.q = q; S.nh = nh; S.nhp = nhp; S.nsites = m.nsites; S.R = R; S.cfg = cfg; S.hist = hist; S.bits = m.bits;
-      for (int k = 0; k < MAX_SLOTS; ++k) { S.nbr[k] = sm.nbr[k]; S.nsym_site[k] = (sm.nsym[k] >= 0) ? m.site_of_t[sm.nsym[k]] : -1; }
-      RNNWF_COUNT_LAUNCH(); build_gru4_kernel<<<nblk(R * Kz), tpb, 0, st>>>(S, Z_base);
-      G.tn_long(Z_base, Kz, dsA + (long long)q * R * nh, nh, Gd("W"), nh, R, Kz, nh);
-      G.tn_long(Z_base, Kz, dgA + (long long)q * R * nh, nh, Gd("Wg"), nh, R, Kz, nh);
-      G.tn_long(Z_base + 24, Kz, dmA + (long long)q * R * nh, nh, Gd("Wmerge"), nh, R, 4 * nh, nh);
+    {
+      // weight gradients: grouped GEMM over the images the reverse sweep left behind (work plan cached per row count)
+      if (m.dw4_rows != R) {
+        std::vector<Dw4Job> jobs;
+        std::vector<int> sites;
+        dw4_plan(m, R, jobs, sites, m.dw4_sites_n);
+        e = cudaMemcpyAsync(m.d_dw4_jobs, jobs.data(), jobs.size() * sizeof(Dw4Job), cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(m.d_dw4_sites, sites.data(), sites.size() * sizeof(int), cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);     // the host vectors go out of scope
+        if (e != cudaSuccess) { err = std::string("rnnwf_backward plan upload: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
+        m.dw4_njobs = (int)jobs.size();
+        m.dw4_rows = R;
+      }
+      Dw4Params D;
+      D.Q = m.Q; D.nh = nh; D.NP = m.tc_np; D.tiles = (int)tiles; D.steps = m.d_steps;
+      D.jobs = static_cast<const Dw4Job*>(m.d_dw4_jobs); D.sites = m.d_dw4_sites;
+      for (int k = 0; k < 5; ++k) D.sites_n[k] = m.dw4_sites_n[k];
+      D.dimg = B.dimg; D.himg = B.himg; D.ximg = B.ximg;
+      D.gW = Gd("W"); D.gWg = Gd("Wg"); D.gWmerge = Gd("Wmerge"); D.gb = Gd("b"); D.gbg = Gd("bg");
+      if (m.dw4_njobs > 0) { RNNWF_COUNT_LAUNCH(); dw4_kernel<<<(unsigned)m.dw4_njobs, DW4_THREADS, DW4_SMEM, st>>>(D); }
     }
-    G.colsum(dsA, nh, RQ, nh, Gd("b"));
-    G.colsum(dgA, nh, RQ, nh, Gd("bg"));
     G.tn(hist, nhp, dlog_base, m.ND, Gd("dense.W"), m.D, RQ, nh, m.D);
     G.colsum(dlog_base, m.ND, RQ, m.D, Gd("dense.b"));
     e = cudaGetLastError();

@@ -157,6 +157,9 @@ __global__ void __launch_bounds__(B4_THREADS, 1) bwd4_kernel(const Bwd4Params P)
         const int4 e = stepT[q];
         const int nact = (e.x >> 16) & 0xff;
         const unsigned char* asrc = P.dimg + ((size_t)q * (size_t)ntiles + (size_t)tile) * dimg_tile;
+        // every cell's phase of bar_ready is observed, also when the cell has no neighbour to push into (a skipped phase
+        // would alias the parity of the next one)
+        if (nact == 0) mbar_wait(bar_ready, hs & 1u);
         for (int a = 0; a < nact; ++a) {
           const int slot = (e.x >> (4 * a)) & 15;
           for (int c = 0; c < NJ; ++c, ++n) {
@@ -356,6 +359,131 @@ __global__ void pack_bwd4_kernel(const float* __restrict__ W, const float* __res
     }
     out[idx] = __float2bfloat16_rn(v);
   }
+}
+
+// ---- weight gradients of the four-neighbour GRU: grouped GEMM over (cell, tile) items ------------------------------------
+// One job = one [128 x N4] output tile -- (neighbour slot, 128 input units, block s|g|m) or (the 32 one-hot input positions,
+// block s|g) -- accumulated in TMEM over a contiguous range of (cell, tile) items and flushed with atomics.  Per item the
+// contraction runs over the tile's 128 rows: A = hidden-state (or one-hot) image, B = d(pre-activation) image of the block, both
+// MN-major (8 units contiguous per row, rows 16 bytes apart, 8-row groups 128 bytes apart, 8-unit groups 2048 bytes apart).
+struct Dw4Job { int16_t kind, slot, m0, blk; int32_t item_begin, item_count; };   // kind 0: hidden-state rows, 1: one-hot input rows
+static_assert(sizeof(Dw4Job) == 16, "Dw4Job layout");
+
+struct Dw4Params {
+  int Q, nh, NP, tiles;
+  const StepMeta* steps;
+  const Dw4Job* jobs;
+  const int* sites;           // [5][Q]: cells in which neighbour slot s is live (s = 4: every cell); counts in sites_n
+  int sites_n[5];
+  const unsigned char* dimg;
+  const unsigned char* himg;
+  const unsigned char* ximg;
+  float* gW; float* gWg; float* gWmerge; float* gb; float* gbg;
+};
+
+constexpr int DW4_THREADS = 128;
+constexpr uint32_t DW4_A_MAX = 32768, DW4_B_MAX = 65536, DW4_STAGE = DW4_A_MAX + DW4_B_MAX;
+constexpr int DW4_SMEM = 2 * (int)DW4_STAGE + 256;
+
+__global__ void __launch_bounds__(DW4_THREADS, 1) dw4_kernel(const Dw4Params P) {
+  extern __shared__ __align__(128) unsigned char d4_smem[];
+  unsigned char* const stage0 = d4_smem;
+  uint64_t* const bars = reinterpret_cast<uint64_t*>(d4_smem + 2 * DW4_STAGE);
+  uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(d4_smem + 2 * DW4_STAGE + 64);
+  uint64_t* const bar_full = bars + 0;     // [2]
+  uint64_t* const bar_empty = bars + 2;    // [2]
+  uint64_t* const bar_done = bars + 4;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int NP = P.NP, N4 = 64 * NP, nh = P.nh;
+  const Dw4Job job = P.jobs[blockIdx.x];
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_full + i, 1); mbar_init(bar_empty + i, 1); }
+    mbar_init(bar_done, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) tc_alloc(tmem_slot, 256);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_d = *tmem_slot;
+  const uint32_t a_bytes = (job.kind == 0) ? (uint32_t)((N4 - job.m0 < 128 ? N4 - job.m0 : 128) / 8) * 2048u : 4u * 2048u;
+  const uint32_t b_bytes = (uint32_t)NP * B4_A_BYTES;
+  const size_t dimg_tile = (size_t)3 * NP * B4_A_BYTES, himg_tile = (size_t)NP * B4_A_BYTES, ximg_tile = 4 * 2048;
+  const int* sites = P.sites + (job.kind == 0 ? job.slot : 4) * P.Q;
+
+  if (warp == 0) {
+    const bool leader = elect_one();
+    for (int i = 0; i < job.item_count; ++i) {
+      const int item = job.item_begin + i, q = sites[item / P.tiles], tile = item % P.tiles;
+      const uint32_t s = (uint32_t)i & 1u;
+      if (i >= 2) mbar_wait_relaxed(bar_empty + s, ((uint32_t)(i >> 1) - 1u) & 1u);
+      if (leader) {
+        unsigned char* dst = stage0 + (size_t)s * DW4_STAGE;
+        const unsigned char* asrc = (job.kind == 0)
+            ? P.himg + ((size_t)P.steps[q].nbr[job.slot] * (size_t)P.tiles + (size_t)tile) * himg_tile + (size_t)(job.m0 / 8) * 2048
+            : P.ximg + ((size_t)q * (size_t)P.tiles + (size_t)tile) * ximg_tile;
+        mbar_expect_tx(bar_full + s, a_bytes + b_bytes);
+        bulk_g2s(dst, asrc, a_bytes, bar_full + s);
+        bulk_g2s(dst + DW4_A_MAX, P.dimg + ((size_t)q * (size_t)P.tiles + (size_t)tile) * dimg_tile + (size_t)job.blk * b_bytes, b_bytes, bar_full + s);
+      }
+      __syncwarp();
+    }
+  } else if (warp == 1) {
+    const bool leader = elect_one();
+    const uint32_t idesc = b4_idesc_bf16(128, N4, 1, 1);
+    for (int i = 0; i < job.item_count; ++i) {
+      const uint32_t s = (uint32_t)i & 1u;
+      mbar_wait(bar_full + s, (uint32_t)(i >> 1) & 1u);
+      tc_fence_after();
+      if (leader) {
+        const uint32_t sa = smem_u32(stage0 + (size_t)s * DW4_STAGE);
+        // MN-major, no swizzle: "leading" offset = stride between 8-row (K) groups, "stride" offset = between 8-unit (MN) groups
+        const uint64_t adesc = tc_desc(sa, 128u, 2048u), bdesc = tc_desc(sa + DW4_A_MAX, 128u, 2048u);
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          tc_mma_f16(tmem_d, adesc + (uint64_t)((ks * 256) >> 4), bdesc + (uint64_t)((ks * 256) >> 4), idesc, (i > 0 || ks > 0) ? 1u : 0u);
+        tc_commit(bar_empty + s);
+        if (i == job.item_count - 1) tc_commit(bar_done);
+      }
+      __syncwarp();
+    }
+  }
+  __syncwarp();
+  if (job.item_count > 0) {
+    mbar_wait(bar_done, 0u);
+    tc_fence_after();
+    // flush: thread = accumulator row m (TMEM lane)
+    const int m = warp * 32 + lane;
+    float* dst = nullptr;          // row of the gradient tensor this accumulator row belongs to
+    if (job.kind == 0) {
+      const int k = job.m0 + m;
+      if (k < nh) {
+        if (job.blk == 2) dst = P.gWmerge + (size_t)(job.slot * nh + k) * nh;
+        else dst = (job.blk == 0 ? P.gW : P.gWg) + (size_t)(24 + job.slot * nh + k) * nh;
+      }
+    } else if (m < 32) {
+      const int slot = m >> 3, i = m & 7;
+      if (i < 6) dst = (job.blk == 0 ? P.gW : P.gWg) + (size_t)(slot * 6 + i) * nh;
+      else if (i == 6 && slot == 0) dst = (job.blk == 0 ? P.gb : P.gbg);
+    }
+#pragma unroll 1
+    for (int c0 = 0; c0 < N4; c0 += 16) {
+      uint32_t d[16];
+      __syncwarp();
+      tc_ld16(tmem_d + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, d);
+      tc_wait_ld();
+      if (dst != nullptr) {
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const float v = __uint_as_float(d[e]);
+          if (c0 + e < nh && v != 0.f) atomicAdd(dst + c0 + e, v);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) { __syncwarp(); tc_dealloc(tmem_d, 256); }
 }
 
 }  // namespace rnnwf

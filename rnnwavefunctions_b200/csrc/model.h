@@ -65,6 +65,12 @@ struct rnnwf_model_impl {
   mutable int dw_cls_count[3] = {0, 0, 0};
   void* d_dw_jobs = nullptr;        // [1024] DwJob
   int* d_dw_cls = nullptr;          // [3][Q]
+  // work plan of the four-neighbour GRU's weight-gradient kernel (bwd_tc4.cuh), cached per row count
+  mutable long long dw4_rows = -1;
+  mutable int dw4_njobs = 0;
+  mutable int dw4_sites_n[5] = {0, 0, 0, 0, 0};
+  void* d_dw4_jobs = nullptr;       // [4096] Dw4Job
+  int* d_dw4_sites = nullptr;       // [5][Q]
   const float* d_params = nullptr;  // last parameter vector handed to set_weights (caller-owned)
   bool weights_set = false;
 

@@ -592,7 +592,11 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc4_kernel<MODE_CHILD>, cudaFuncAttributeMaxDynamicSharedMemorySize, t4s));
   }
   CREATE_TRY(backward_init());
-  if (m->tc4) CREATE_TRY(backward_init_tc4(*m));
+  if (m->tc4) {
+    CREATE_TRY(backward_init_tc4(*m));
+    CREATE_TRY(cudaMalloc(&m->d_dw4_jobs, 4096 * sizeof(Dw4Job)));
+    CREATE_TRY(cudaMalloc(&m->d_dw4_sites, (size_t)5 * m->Q * sizeof(int)));
+  }
   if (m->tc_enabled) {
     CREATE_TRY(backward_init_tc(*m));
     CREATE_TRY(cudaMalloc(&m->d_dw_jobs, 1024 * sizeof(DwJob)));
@@ -607,7 +611,7 @@ int rnnwf_destroy(rnnwf_handle h) {
   if (h == nullptr) return RNNWF_OK;
   cudaFree(h->d_steps); cudaFree(h->d_variants); cudaFree(h->d_site_of_t); cudaFree(h->d_wpack);
   cudaFree(h->d_xtab); cudaFree(h->d_bias); cudaFree(h->d_head_w); cudaFree(h->d_head_b);
-  cudaFree(h->d_tcB); cudaFree(h->d_tcbias); cudaFree(h->d_dw_jobs); cudaFree(h->d_dw_cls);
+  cudaFree(h->d_tcB); cudaFree(h->d_tcbias); cudaFree(h->d_dw_jobs); cudaFree(h->d_dw_cls); cudaFree(h->d_dw4_jobs); cudaFree(h->d_dw4_sites);
   delete h;
   return RNNWF_OK;
 }

@@ -91,3 +91,13 @@ def test_tc4_backward(cuda, nx, ny, nh, ns):
     for n, v in eng.views(grad).items():
         gr = Pg[n].grad
         assert float((v.double() - gr).abs().max()) <= 1e-2 * float(gr.abs().max()) + 1e-30, f"gradient of {n} differs"
+    if ns > nref:
+        # every tile carries weight now (more tiles than persistent CTAs): against the FP32 regime on the same samples
+        f32 = Engine(_lib.CELL_GRU4, nx, ny, num_units=nh, seed=91)
+        f32.set_weights(eng.params)
+        sv2 = f32.new_saved(ns)
+        f32.logpsi(s, saved=sv2)
+        seeds = costs.seeds_real(torch.randn(ns, generator=torch.Generator().manual_seed(11), dtype=torch.float64))
+        ga, gb = eng.backward(s, saved, seeds).cpu(), f32.backward(s, sv2, seeds).cpu()
+        for (n, a), (_, b) in zip(eng.views(ga).items(), f32.views(gb).items()):
+            assert float((a - b).abs().max()) <= 1e-2 * float(b.abs().max()) + 1e-30, f"gradient of {n} differs from the FP32 regime"
