@@ -49,6 +49,9 @@ WORKLOADS = {
     "rydberg_4x4_gru256": dict(eng=dict(cell="GRU4", nx=4, ny=4, num_units=256), ham="RYDBERG",
                                hp=[1.7 ** 6, 3.3, 1.0, 2.001], ns=12500,
                                desc="Rydberg Kagome 4x4 cells (48 atoms) 2D GRU 256 units, 12500 samples/step/GPU"),
+    "rydberg_8x8_gru256": dict(eng=dict(cell="GRU4", nx=8, ny=8, num_units=256), ham="RYDBERG",
+                               hp=[1.7 ** 6, 3.3, 1.0, 2.001], ns=12500,
+                               desc="Rydberg Kagome 8x8 cells (192 atoms) 2D GRU 256 units, 12500 samples/step/GPU"),
 }
 DEFAULT_WORKLOAD = "heis10x10_tri_tgru100"
 
