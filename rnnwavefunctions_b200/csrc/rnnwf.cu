@@ -292,7 +292,7 @@ int build_model(rnnwf_model& m) {
   if (m.tc4) {
     m.tc_np = (m.nh + T4_UP - 1) / T4_UP;      // column passes of 64 units; the hidden axis is padded to 64 tc_np
     if (m.tc_np > T4_MAXNP) return fail(RNNWF_EINVAL, "the tensor-core regime of the four-neighbour GRU needs num_units <= 256");
-    if (T4Smem(m.tc_np, m.Q).total > 227 * 1024) return fail(RNNWF_EINVAL, "the tensor-core regime of the four-neighbour GRU: lattice too large for shared memory");
+    if (T4Smem(4, m.Q).total > 227 * 1024) return fail(RNNWF_EINVAL, "the tensor-core regime of the four-neighbour GRU: lattice too large for shared memory");
     m.ring_len = m.Q;
   }
   m.wpack_float4 = std::max(1LL, woff);
@@ -329,7 +329,7 @@ int pick_shape(const rnnwf_model& m, long long rows, LaunchShape& s) {
   }
   if (m.tc4) {
     const long long tiles = (rows + T4_ROWS - 1) / T4_ROWS;
-    s.WR = 4; s.Mp = T4_ROWS; s.Mr = T4_ROWS; s.threads = T4_THREADS; s.smem = T4Smem(m.tc_np, m.Q).total;
+    s.WR = 4; s.Mp = T4_ROWS; s.Mr = T4_ROWS; s.threads = T4_THREADS; s.smem = T4Smem(t4_stages(m.Q), m.Q).total;
     s.grid = (int)std::max(1LL, std::min<long long>(tiles, m.num_sms));
     return RNNWF_OK;
   }
@@ -374,6 +374,16 @@ cudaError_t launch_inst(const SweepParams& P, const LaunchShape& s, cudaStream_t
   return cudaGetLastError();
 }
 
+// the FP32 FFMA sweep (its weight packs are kept up to date in every regime)
+int launch_sweep_ffma(const rnnwf_model& m, const SweepParams& P, const LaunchShape& s, cudaStream_t st) {
+  cudaError_t e;
+  if (m.NTU == 3 && m.TJ == 5) e = launch_inst<5, 3>(P, s, st);
+  else if (m.NTU == 3 && m.TJ == 4) e = launch_inst<4, 3>(P, s, st);
+  else e = launch_inst<4, 4>(P, s, st);
+  if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("sweep kernel launch: ") + cudaGetErrorString(e));
+  return RNNWF_OK;
+}
+
 int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& s, cudaStream_t st) {
   cudaError_t e;
   if (m.tc_enabled) {
@@ -403,11 +413,7 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
     if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("tensor-core sweep (four-neighbour GRU) launch: ") + cudaGetErrorString(e));
     return RNNWF_OK;
   }
-  if (m.NTU == 3 && m.TJ == 5) e = launch_inst<5, 3>(P, s, st);
-  else if (m.NTU == 3 && m.TJ == 4) e = launch_inst<4, 3>(P, s, st);
-  else e = launch_inst<4, 4>(P, s, st);
-  if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("sweep kernel launch: ") + cudaGetErrorString(e));
-  return RNNWF_OK;
+  return launch_sweep_ffma(m, P, s, st);
 }
 
 long long ring_bytes(const rnnwf_model& m, int grid, int Mp) {
@@ -551,7 +557,11 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
   CREATE_TRY(cudaMalloc(&m->d_wpack, m->wpack_float4 * 16));
   CREATE_TRY(cudaMalloc(&m->d_xtab, m->xtab_float4 * 16));
   CREATE_TRY(cudaMalloc(&m->d_bias, m->bias_float4 * 16));
-  CREATE_TRY(cudaMalloc(&m->d_head_w, (size_t)m->nhp * m->ND * 4));
+  {   // (rows padded to a multiple of 64 and zero-filled: the four-neighbour tensor-core sweep reads whole 64-unit passes)
+    const size_t hw_bytes = (size_t)((m->nhp + 63) / 64 * 64) * m->ND * 4;
+    CREATE_TRY(cudaMalloc(&m->d_head_w, hw_bytes));
+    CREATE_TRY(cudaMemset(m->d_head_w, 0, hw_bytes));
+  }
   CREATE_TRY(cudaMalloc(&m->d_head_b, 64));
   CREATE_TRY(cudaMemcpy(m->d_steps, m->steps.data(), m->steps.size() * sizeof(StepMeta), cudaMemcpyHostToDevice));
   CREATE_TRY(cudaMemcpy(m->d_variants, vmeta.data(), vmeta.size() * sizeof(VariantMeta), cudaMemcpyHostToDevice));
@@ -585,7 +595,7 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
   }
   if (m->tc4) {
-    const int t4s = T4Smem(m->tc_np, m->Q).total;
+    const int t4s = T4Smem(t4_stages(m->Q), m->Q).total;
     CREATE_TRY(cudaMalloc(&m->d_tcB, (size_t)m->tc_np * (size_t)t4_pass_bytes(m->tc_np)));
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc4_kernel<MODE_SAMPLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, t4s));
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc4_kernel<MODE_EVAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, t4s));
@@ -1093,7 +1103,7 @@ extern "C" int rnnwf_logpsi_static(rnnwf_handle h, int64_t rows, const int8_t* s
     if (Mr <= 0) continue;
     SmemLayout L(m.ncls_max, m.Gblk, Mp, m.ldH, m.nhp, m.ND, m.Tsym);
     if (L.total > 227 * 1024) continue;
-    const long long per_cta = ring_bytes(m, 1, Mp);
+    const long long per_cta = (long long)m.ring_len * Mp * m.nhp * 4;      // FP32 history ring of the FFMA sweep
     smallest = per_cta;
     const long long tiles = (rows + Mr - 1) / Mr;
     if (per_cta > (long long)RNNWF_STATIC_SCRATCH_BYTES) continue;
@@ -1118,5 +1128,6 @@ extern "C" int rnnwf_logpsi_static(rnnwf_handle h, int64_t rows, const int8_t* s
   fill_model_params(m, s, P);
   P.mode = MODE_EVAL; P.rows = rows; P.cfg_in = samples_dev; P.out_logp = logp_dev; P.out_phase = phase_dev;
   P.ring = ring;
-  return launch_sweep(m, P, s, static_cast<cudaStream_t>(stream));
+  // always the FP32 FFMA sweep, whatever the precision regime of the handle (the tensor-core sweeps size their ring differently)
+  return launch_sweep_ffma(m, P, s, static_cast<cudaStream_t>(stream));
 }

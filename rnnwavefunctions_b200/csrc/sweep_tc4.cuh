@@ -19,7 +19,8 @@
 //   warps 1..16  : epilogue, four threads per row (row == TMEM lane); thread (row, sub) owns units 64 p + 16 sub + [0,16) of
 //                  pass p: 48 accumulators -> gates -> FP16 ring chunk (two 16-byte k-core rows), FP32 saved state, head partials
 //   warp 17      : heads, four rows per thread: 8-way softmax, inverse-CDF draw or teacher forcing, running log P (FP64)
-//   warp 18      : loader: cp.async.bulk of A and B chunks (mbarrier complete_tx)
+//   warp 18, 19  : loaders: cp.async.bulk of the B chunk (weights; no dependencies) and of the A chunk (ring; gated by the
+//                  epilogue's chunk counters) of every stage -- two issuers because one thread issues a bulk copy per ~300 cycles
 // Ring writes (generic proxy) are published to the loader's bulk copies (async proxy) by fence.proxy.async on both
 // sides of a shared-memory counter.  Every wait is bounded and traps instead of hanging.
 #pragma once
@@ -31,15 +32,15 @@ constexpr int T4_ROWS = 128;
 constexpr int T4_UP = 64;                         // units per column pass == hidden units per K job
 constexpr int T4_N = 3 * T4_UP;                   // 192 MMA columns per pass: (s, g, m) of 64 units
 constexpr int T4_TPS = T4_N / 4;                  // 48 accumulator columns per epilogue thread
-constexpr int T4_STAGES = 4;
+constexpr int T4_MAX_STAGES = 4;                  // stages of 40 KB (A chunk + B chunk)
 constexpr uint32_t T4_A_BYTES = T4_ROWS * T4_UP * 2;      // 16 KB: [k-core 8][row 128][8 halves]
 constexpr uint32_t T4_B_BYTES = T4_N * T4_UP * 2;         // 24 KB: [k-core 8][n 192][8 halves]
 constexpr uint32_t T4_STAGE = T4_A_BYTES + T4_B_BYTES;
 constexpr uint32_t T4_XA_BYTES = 4 * T4_ROWS * 16;        // input chunk: [k-core = neighbour 4][row 128][8 halves]
 constexpr uint32_t T4_XB_BYTES = 4 * T4_N * 16;           // its weights: [k-core 4][n 192][8 halves]
 constexpr int T4_EPI_THREADS = 512;
-constexpr int T4_HEAD_WARP = 17, T4_LOAD_WARP = 18;
-constexpr int T4_THREADS = 32 * 19;
+constexpr int T4_HEAD_WARP = 17, T4_LOADB_WARP = 18, T4_LOAD_WARP = 19;   // (T4_LOAD_WARP: the hidden-state loader)
+constexpr int T4_THREADS = 32 * 20;
 constexpr int T4_HEAD_ROWS = 4;
 constexpr int T4_MAXNP = 4;                       // num_units <= 256
 constexpr uint32_t T4_TMEM_COLS = 512;
@@ -49,12 +50,12 @@ __host__ __device__ inline long long t4_step_bytes(int NP) { return (long long)N
 
 struct T4Smem {
   int off_stage, off_xa, off_part, off_headw, off_headb, off_step, off_last, off_sym, off_bar, off_cnt, off_tmem, total;
-  __host__ __device__ T4Smem(int NP, int Q) {
+  __host__ __device__ T4Smem(int stages, int Q) {
     int o = 0;
-    off_stage = o; o += T4_STAGES * (int)T4_STAGE;
+    off_stage = o; o += stages * (int)T4_STAGE;
     off_xa = o;    o += (int)T4_XA_BYTES;
     off_part = o;  o += T4_ROWS * 4 * 32;           // partial head sums [row][sub][8]
-    off_headw = o; o += NP * T4_UP * 32;            // head weights [unit][8], zero rows past num_units
+    off_headw = o; o += T4_MAXNP * T4_UP * 32;      // head weights [unit][8], zero rows past num_units
     off_headb = o; o += 32;
     off_step = o;  o += Q * 16;
     off_last = o;  o += (Q * 2 + 15) & ~15;         // per step: last step that reads it as a neighbour
@@ -66,7 +67,15 @@ struct T4Smem {
   }
 };
 
+// stages of the operand ring.  (Measured dead ends, tools/tc4_cycles.py: a fifth stage at the price of reading the head weights
+// from global memory, streaming loads for the parent-history gather, separate A / B rings -- the stream is bound by
+// bytes in flight per SM x ~3k cycles of L2 latency under load, tools/ubench/bulk_rate.cu.)
+__host__ __device__ inline int t4_stages(int Q) { (void)Q; return T4_MAX_STAGES; }
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+// generic-proxy writes to global memory -> later async-proxy (bulk copy) reads of them; executed by the WRITER before it
+// signals.  The full fence.proxy.async costs ~1000 cycles here (event trace, tools/tc4_cycles.py), so the reader side
+// relies on the writers' fence + the release/acquire chain of the counter, as TMA-store epilogues do.
+__device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
 __device__ __forceinline__ uint32_t ld_volatile_shared(const uint32_t* p) {
   uint32_t v;
   asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
@@ -75,8 +84,8 @@ __device__ __forceinline__ uint32_t ld_volatile_shared(const uint32_t* p) {
 // poll a shared-memory counter (one warp, off the critical path of everything but itself)
 __device__ __forceinline__ void t4_wait_count(const uint32_t* cnt, uint32_t target) {
   for (uint32_t spin = 0; (int32_t)(ld_volatile_shared(cnt) - target) < 0; ++spin) {
-    __nanosleep(32);
-    if (spin > (1u << 24)) { asm volatile("trap;"); }
+    if (spin > 64) __nanosleep(20);                 // the chunk it waits for is usually a few hundred cycles away
+    if (spin > (1u << 25)) { asm volatile("trap;"); }
   }
   __threadfence_block();
 }
@@ -85,7 +94,8 @@ template <int MODE>
 __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepParams P) {
   extern __shared__ __align__(128) unsigned char t4_smem[];
   const int NP = P.tc_np;
-  const T4Smem L(NP, P.Q);
+  const uint32_t NS = (uint32_t)t4_stages(P.Q);
+  const T4Smem L((int)NS, P.Q);
   unsigned char* const smem = t4_smem;
   unsigned char* const stage0 = smem + L.off_stage;
   unsigned char* const xa = smem + L.off_xa;
@@ -98,15 +108,15 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
   uint64_t* const bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
   uint32_t* const cnt = reinterpret_cast<uint32_t*>(smem + L.off_cnt);      // [0..3] ring chunk c written (warps), [4] prologues (warps)
   uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(smem + L.off_tmem);
-  uint64_t* const bar_full = bars + 0;                 // [4] stage landed (complete_tx)
-  uint64_t* const bar_empty = bars + 4;                // [4] stage consumed (tcgen05.commit)
-  uint64_t* const bar_acc_full = bars + 8;             // [2] accumulator buffer complete (tcgen05.commit)
-  uint64_t* const bar_acc_free = bars + 10;            // [2] accumulator buffer drained (512 arrivals)
-  uint64_t* const bar_x = bars + 12;                   // input chunk of a step written (512 arrivals)
-  uint64_t* const bar_part = bars + 13;                // partial head sums written (512 arrivals)
-  uint64_t* const bar_pfree = bars + 14;               // partial head sums consumed (32 arrivals)
-  uint64_t* const bar_sym = bars + 15;                 // sampling: the step's symbols are drawn (32 arrivals)
-  uint64_t* const bar_tile = bars + 16;                // head warp is done with the tile's symbol table (32 arrivals)
+  uint64_t* const bar_full = bars + 0;                 // [<= 5] stage landed (complete_tx, two producers)
+  uint64_t* const bar_empty = bars + 5;                // [<= 5] stage consumed (tcgen05.commit)
+  uint64_t* const bar_acc_full = bars + 10;            // [2] accumulator buffer complete (tcgen05.commit)
+  uint64_t* const bar_acc_free = bars + 12;            // [2] accumulator buffer drained (512 arrivals)
+  uint64_t* const bar_x = bars + 14;                   // input chunk of a step written (512 arrivals)
+  uint64_t* const bar_part = bars + 15;                // partial head sums written (512 arrivals)
+  uint64_t* const bar_pfree = bars + 16;               // partial head sums consumed (32 arrivals)
+  uint64_t* const bar_sym = bars + 17;                 // sampling: the step's symbols are drawn (32 arrivals)
+  uint64_t* const bar_tile = bars + 18;                // head warp is done with the tile's symbol table (32 arrivals)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int nh = P.nh, nhp = P.nhp;
@@ -114,7 +124,7 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
   const long long step_bytes = t4_step_bytes(NP);
 
   if (tid == 0) {
-    for (int i = 0; i < T4_STAGES; ++i) { mbar_init(bar_full + i, 1); mbar_init(bar_empty + i, 1); }
+    for (int i = 0; i < T4_MAX_STAGES; ++i) { mbar_init(bar_full + i, 2); mbar_init(bar_empty + i, 1); }   // two producers per stage
     for (int i = 0; i < 2; ++i) { mbar_init(bar_acc_full + i, 1); mbar_init(bar_acc_free + i, T4_EPI_THREADS); }
     mbar_init(bar_x, T4_EPI_THREADS);
     mbar_init(bar_part, T4_EPI_THREADS);
@@ -156,6 +166,31 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // optional cycle accounting (-DRNNWF_TC_PROF builds only; tools/tc4_cycles.py).  MMA warp: [0] accumulator-free wait
+  // [1] stage-full wait [2] input-chunk wait [3] issue [5] total; loader: [4] stage-empty wait [6] ring-chunk wait [7] total;
+  // epilogue thread 32: [8] accumulator-full wait [9] pass compute [10] step tail (head hand-off, next input chunk) [12] total
+#ifdef RNNWF_TC_PROF
+  long long prof4[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) prof4[i] = 0;
+  const bool do_prof4 = (P.tc_prof != nullptr) && (tid == 0 || tid == 32 || tid == 32 * T4_LOAD_WARP);
+  const long long kstart4 = tc_clock();
+#define T4_T0() long long t0__ = do_prof4 ? tc_clock() : 0
+#define T4_ACC(k) do { if (do_prof4) { const long long t1__ = tc_clock(); prof4[k] += t1__ - t0__; t0__ = t1__; } } while (0)
+#define T4_TOTAL(k) do { if (do_prof4) prof4[k] = tc_clock() - kstart4; } while (0)
+  // event trace of CTA 0: [role 3][T4_TRACE_LEN] words (tag << 40 | cycles since kernel start) after the counters
+  constexpr int T4_TRACE_LEN = 4096;
+  const int trole4 = (tid == 0) ? 0 : (tid == 32 * T4_LOAD_WARP ? 1 : (tid == 32 ? 2 : -1));
+  const bool do_trace4 = (P.tc_prof != nullptr) && blockIdx.x == 0 && trole4 >= 0;
+  unsigned long long* const tbuf4 = do_trace4 ? P.tc_prof + (size_t)gridDim.x * 16 + (size_t)trole4 * T4_TRACE_LEN : nullptr;
+  int nev4 = 0;
+#define T4_EV(tag) do { if (do_trace4 && nev4 < T4_TRACE_LEN) tbuf4[nev4++] = ((unsigned long long)(tag) << 40) | (unsigned long long)(tc_clock() - kstart4); } while (0)
+#else
+#define T4_EV(tag) do { } while (0)
+#define T4_T0() do { } while (0)
+#define T4_ACC(k) do { } while (0)
+#define T4_TOTAL(k) do { } while (0)
+#endif
   const long long total_rows = (P.rows_dev != nullptr) ? (long long)(*P.rows_dev) : P.rows;
   const long long ntiles = (total_rows + T4_ROWS - 1) / T4_ROWS;
   auto tile_q0 = [&](long long row0) -> int {
@@ -186,13 +221,17 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
         const int njobs = nact * NP;
         for (int p = 0; p < NP; ++p, ++it) {
           const uint32_t buf = it & 1u;
+          T4_T0();
           mbar_wait(bar_acc_free + buf, ((it >> 1) & 1u) ^ 1u);
+          T4_ACC(0); T4_EV(1);
           const uint32_t tmem_d = tmem_base + buf * (uint32_t)T4_N;
           for (int j = 0; j <= njobs; ++j, ++n) {
-            const uint32_t s = n % T4_STAGES;
-            mbar_wait(bar_full + s, (n / T4_STAGES) & 1u);
+            const uint32_t s = n % NS;
+            mbar_wait(bar_full + s, (n / NS) & 1u);
+            T4_ACC(1);
             const bool xjob = (j == njobs);
             if (xjob && p == 0) mbar_wait(bar_x, hs & 1u);
+            T4_ACC(2);
             tc_fence_after();
             if (leader) {
               const uint32_t sa = smem_u32(stage0 + (size_t)s * T4_STAGE);
@@ -211,15 +250,48 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
               if (xjob) tc_commit(bar_acc_full + buf);
             }
             __syncwarp();
+            T4_ACC(3);
+            if (xjob) T4_EV(2);
+          }
+        }
+      }
+    }
+    T4_TOTAL(5);
+  } else if (warp == T4_LOADB_WARP) {
+    // ======================= weight loader (no dependencies): B chunk of every job =======================
+    // A single thread issues one bulk copy per ~300 cycles whatever its size (measured, tools/ubench/bulk_rate.cu), which is
+    // about the tensor-core time of a job: the two operands of a stage are therefore issued by two warps.
+    const bool leader = elect_one();
+    uint32_t n = 0;
+    const uint32_t bB = (P.debug_flags & 1) ? T4_B_BYTES / 2 : T4_B_BYTES;   // (RNNWF_TC_DEBUG bit 0: timing experiment)
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const int q0 = tile_q0(tile * T4_ROWS);
+      for (int q = q0; q < P.Q; ++q) {
+        const int4 e = stepT[q];
+        const int nact = (e.x >> 16) & 0xff;
+        for (int p = 0; p < NP; ++p) {
+          const unsigned char* bsrc = P.tc_B + (size_t)p * (size_t)pass_bytes;
+          for (int j = 0; j <= nact * NP; ++j, ++n) {
+            const bool xjob = (j == nact * NP);
+            const uint32_t s = n % NS;
+            if (n >= NS) mbar_wait_relaxed(bar_empty + s, ((n / NS) - 1u) & 1u);
+            if (leader) {
+              const uint32_t bytes = xjob ? T4_XB_BYTES : bB;
+              const size_t off = xjob ? (size_t)4 * NP * T4_B_BYTES : (size_t)(((e.x >> (4 * (j / NP))) & 15) * NP + (j % NP)) * T4_B_BYTES;
+              mbar_expect_tx(bar_full + s, bytes);
+              bulk_g2s(stage0 + (size_t)s * T4_STAGE + T4_A_BYTES, bsrc + off, bytes, bar_full + s);
+            }
+            __syncwarp();
           }
         }
       }
     }
   } else if (warp == T4_LOAD_WARP) {
-    // ======================= loader =======================
+    // ======================= hidden-state loader: A chunk of every job, gated by the epilogue's chunk counters ===========
     const bool leader = elect_one();
     uint32_t n = 0, hs = 0, nt = 0;
     uint32_t seen[T4_MAXNP] = {0u, 0u, 0u, 0u};     // ring chunk c: writer warps already waited for
+    const uint32_t bA = (P.debug_flags & 2) ? T4_A_BYTES / 2 : T4_A_BYTES;   // (RNNWF_TC_DEBUG bit 1: timing experiment)
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++nt) {
       const int q0 = tile_q0(tile * T4_ROWS);
       const uint32_t hs0 = hs;
@@ -231,42 +303,40 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
         const int4 e = stepT[q];
         const int nact = (e.x >> 16) & 0xff;
         for (int p = 0; p < NP; ++p) {
-          const unsigned char* bsrc = P.tc_B + (size_t)p * (size_t)pass_bytes;
           for (int a = 0; a < nact; ++a) {
             const int slot = (e.x >> (4 * a)) & 15;
             const int nb = nbr_of(e, slot);
             for (int c = 0; c < NP; ++c, ++n) {
-              const uint32_t s = n % T4_STAGES;
-              if (n >= T4_STAGES) mbar_wait_relaxed(bar_empty + s, ((n / T4_STAGES) - 1u) & 1u);
-              unsigned char* dst = stage0 + (size_t)s * T4_STAGE;
-              if (leader) {
-                mbar_expect_tx(bar_full + s, T4_STAGE);
-                bulk_g2s(dst + T4_A_BYTES, bsrc + (size_t)(slot * NP + c) * T4_B_BYTES, T4_B_BYTES, bar_full + s);
-              }
+              const uint32_t s = n % NS;
+              T4_T0();
+              if (n >= NS) mbar_wait_relaxed(bar_empty + s, ((n / NS) - 1u) & 1u);
+              T4_ACC(4);
               if (nb >= q0) {
                 // written by this tile's epilogue at local step hs0 + (nb - q0): 16 warps per (step, chunk)
                 const uint32_t target = 16u * (hs0 + (uint32_t)(nb - q0) + 1u);
 #pragma unroll
                 for (int cc = 0; cc < T4_MAXNP; ++cc)
-                  if (cc == c && (int32_t)(seen[cc] - target) < 0) { t4_wait_count(cnt + cc, target); seen[cc] = target; fence_proxy_async_all(); }
+                  if (cc == c && (int32_t)(seen[cc] - target) < 0) { T4_EV(10 + 4 * cc); t4_wait_count(cnt + cc, target); seen[cc] = target; T4_EV(11 + 4 * cc); }
               }
-              if (leader) bulk_g2s(dst, ring_cta + (size_t)nb * (size_t)step_bytes + (size_t)c * T4_A_BYTES, T4_A_BYTES, bar_full + s);
+              T4_ACC(6);
+              if (leader) {
+                mbar_expect_tx(bar_full + s, bA);
+                bulk_g2s(stage0 + (size_t)s * T4_STAGE, ring_cta + (size_t)nb * (size_t)step_bytes + (size_t)c * T4_A_BYTES, bA, bar_full + s);
+              }
               __syncwarp();
             }
           }
-          {   // input / bias job: only its weights are streamed
-            const uint32_t s = n % T4_STAGES;
-            if (n >= T4_STAGES) mbar_wait_relaxed(bar_empty + s, ((n / T4_STAGES) - 1u) & 1u);
-            if (leader) {
-              mbar_expect_tx(bar_full + s, T4_XB_BYTES);
-              bulk_g2s(stage0 + (size_t)s * T4_STAGE + T4_A_BYTES, bsrc + (size_t)4 * NP * T4_B_BYTES, T4_XB_BYTES, bar_full + s);
-            }
+          {   // input / bias job: its A chunk is the shared-memory input chunk; this producer only arrives
+            const uint32_t s = n % NS;
+            if (n >= NS) mbar_wait_relaxed(bar_empty + s, ((n / NS) - 1u) & 1u);
+            if (leader) mbar_arrive(bar_full + s);
             __syncwarp();
             ++n;
           }
         }
       }
     }
+    T4_TOTAL(7);
   } else if (warp <= T4_EPI_THREADS / 32) {
     // ======================= epilogue warps: 4 threads per row =======================
     const int quarter = warp & 3;
@@ -281,7 +351,9 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
       const int q0 = tile_q0(row0);
       const bool live = row < nrows;
       int rparent = 0;
+      T4_T0();
       if (ntile > 0) mbar_wait(bar_tile, (ntile - 1) & 1);
+      T4_ACC(11);
       // ---- symbol table of the tile (teacher forcing)
       {
         Child ch;
@@ -302,27 +374,38 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
           symS[t * T4_ROWS + row] = (uint8_t)sy;
         }
       }
+      T4_ACC(13);
       // ---- prefix reuse: the parents' saved FP32 history of every earlier step some step >= q0 looks back to,
       //      converted into this CTA's ring (FP16 chunk images)
       if (MODE == MODE_CHILD && q0 > 0) {
+        // (all 16 loads of a step are issued before the first conversion: the gather is latency-bound)
+        const float* pbase = P.par_hist + (size_t)rparent * nhp + sub * 16;
+        unsigned char* dbase = ring_cta + (size_t)(2 * sub) * (T4_ROWS * 16) + (size_t)row * 16;
+#pragma unroll 1
         for (int j = 0; j < q0; ++j) {
           if ((int)lastS[j] < q0) continue;           // no step of this tile looks back to it (uniform over the CTA)
-          const float* psrc = P.par_hist + ((size_t)j * (size_t)P.par_rows + (size_t)rparent) * nhp;
-          unsigned char* dst = ring_cta + (size_t)j * (size_t)step_bytes + (size_t)(2 * sub) * (T4_ROWS * 16) + (size_t)row * 16;
-          for (int p = 0; p < NP; ++p) {
-            const int j0 = p * T4_UP + sub * 16;
-            uint32_t w[8];
+          const float* psrc = pbase + (size_t)j * (size_t)P.par_rows * nhp;
+          unsigned char* dst = dbase + (size_t)j * (size_t)step_bytes;
+          float4 v[T4_MAXNP][4];
+#pragma unroll
+          for (int p = 0; p < T4_MAXNP; ++p)
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-              float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (live && j0 + 4 * i < nhp) v = __ldg(reinterpret_cast<const float4*>(psrc + j0 + 4 * i));
-              w[2 * i] = pack_f16x2(v.x, v.y); w[2 * i + 1] = pack_f16x2(v.z, v.w);
+              v[p][i] = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (p < NP && live && p * T4_UP + sub * 16 + 4 * i < nhp) v[p][i] = __ldg(reinterpret_cast<const float4*>(psrc + p * T4_UP + 4 * i));
             }
-            *reinterpret_cast<uint4*>(dst + (size_t)p * T4_A_BYTES) = make_uint4(w[0], w[1], w[2], w[3]);
-            *reinterpret_cast<uint4*>(dst + (size_t)p * T4_A_BYTES + T4_ROWS * 16) = make_uint4(w[4], w[5], w[6], w[7]);
+#pragma unroll
+          for (int p = 0; p < T4_MAXNP; ++p) {
+            if (p < NP) {
+              *reinterpret_cast<uint4*>(dst + (size_t)p * T4_A_BYTES) =
+                  make_uint4(pack_f16x2(v[p][0].x, v[p][0].y), pack_f16x2(v[p][0].z, v[p][0].w), pack_f16x2(v[p][1].x, v[p][1].y), pack_f16x2(v[p][1].z, v[p][1].w));
+              *reinterpret_cast<uint4*>(dst + (size_t)p * T4_A_BYTES + T4_ROWS * 16) =
+                  make_uint4(pack_f16x2(v[p][2].x, v[p][2].y), pack_f16x2(v[p][2].z, v[p][2].w), pack_f16x2(v[p][3].x, v[p][3].y), pack_f16x2(v[p][3].z, v[p][3].w));
+            }
           }
         }
       }
+      T4_ACC(14);
       // symbols of the other sub-threads are needed below: the four warps of a lane quarter hold one row's four threads
       quarter_barrier(quarter);
       // input chunk of step q: k-core `sub` = neighbour slot `sub`: one-hot pairs of the neighbour cell's three bits; the
@@ -345,6 +428,7 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
       fence_proxy_async_all();
       __syncwarp();
       if (lane == 0) { __threadfence_block(); atomicAdd(cnt + 4, 1u); }
+      T4_ACC(15);
 
       for (int q = q0; q < P.Q; ++q, ++hs) {
         const bool save = (MODE != MODE_CHILD) && live && (P.sv_hist != nullptr);
@@ -355,7 +439,9 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
 #pragma unroll 1
         for (int p = 0; p < NP; ++p, ++it) {
           const uint32_t buf = it & 1u;
+          T4_T0();
           mbar_wait(bar_acc_full + buf, (it >> 1) & 1u);
+          T4_ACC(8); T4_EV(20 + p);
           uint32_t ds[16], dg[16], dm[16];
           __syncwarp();
           tc_fence_after();
@@ -368,34 +454,41 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
           mbar_arrive(bar_acc_free + buf);
           const int j0 = p * T4_UP + sub * 16;
           const float* hW = headW + j0 * 8;
-          uint32_t w[8];
-          float hprev = 0.f;
+          // The new hidden states go out first (the next site's MMAs wait for this chunk); the head partial sums and the
+          // saved state follow, off the site-to-site critical path.
+          float hv[16];
 #pragma unroll
           for (int e = 0; e < 16; ++e) {
             const float u = sigmoid_prescaled(__uint_as_float(dg[e]));
             const float ht = tanh_prescaled(__uint_as_float(ds[e]));
             const float mv = __uint_as_float(dm[e]);
             // u ht + (1 - u) m; padding units have zero weights and biases: u = 1/2, ht = m = 0 -> 0
-            float hv = fmaf(u, ht - mv, mv);
-            if (!live) hv = 0.f;
-            const float4 wa = *reinterpret_cast<const float4*>(hW + e * 8);
-            const float4 wb = *reinterpret_cast<const float4*>(hW + e * 8 + 4);
-            lg[0] = fmaf(hv, wa.x, lg[0]); lg[1] = fmaf(hv, wa.y, lg[1]); lg[2] = fmaf(hv, wa.z, lg[2]); lg[3] = fmaf(hv, wa.w, lg[3]);
-            lg[4] = fmaf(hv, wb.x, lg[4]); lg[5] = fmaf(hv, wb.y, lg[5]); lg[6] = fmaf(hv, wb.z, lg[6]); lg[7] = fmaf(hv, wb.w, lg[7]);
+            hv[e] = live ? fmaf(u, ht - mv, mv) : 0.f;
             if (save) {
               const int j = j0 + e;
               if (j < nh) P.sv_gates[((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * P.Gp + j] = make_float4(u, ht, mv, 0.f);
-              if (j < nhp) P.sv_hist[((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + j] = hv;
+              if (j < nhp) P.sv_hist[((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + j] = hv[e];
             }
-            if (e & 1) w[e >> 1] = pack_f16x2(hprev, hv); else hprev = hv;
           }
-          *reinterpret_cast<uint4*>(ring_q + (size_t)p * T4_A_BYTES) = make_uint4(w[0], w[1], w[2], w[3]);
-          *reinterpret_cast<uint4*>(ring_q + (size_t)p * T4_A_BYTES + T4_ROWS * 16) = make_uint4(w[4], w[5], w[6], w[7]);
+          *reinterpret_cast<uint4*>(ring_q + (size_t)p * T4_A_BYTES) =
+              make_uint4(pack_f16x2(hv[0], hv[1]), pack_f16x2(hv[2], hv[3]), pack_f16x2(hv[4], hv[5]), pack_f16x2(hv[6], hv[7]));
+          *reinterpret_cast<uint4*>(ring_q + (size_t)p * T4_A_BYTES + T4_ROWS * 16) =
+              make_uint4(pack_f16x2(hv[8], hv[9]), pack_f16x2(hv[10], hv[11]), pack_f16x2(hv[12], hv[13]), pack_f16x2(hv[14], hv[15]));
           // chunk p of this step is written: release it to the loader
-          fence_proxy_async_all();
+          fence_proxy_async_global();
           __syncwarp();
           if (lane == 0) { __threadfence_block(); atomicAdd(cnt + p, 1u); }
+          T4_EV(30 + p);
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {
+            const float4 wa = *reinterpret_cast<const float4*>(hW + e * 8);
+            const float4 wb = *reinterpret_cast<const float4*>(hW + e * 8 + 4);
+            lg[0] = fmaf(hv[e], wa.x, lg[0]); lg[1] = fmaf(hv[e], wa.y, lg[1]); lg[2] = fmaf(hv[e], wa.z, lg[2]); lg[3] = fmaf(hv[e], wa.w, lg[3]);
+            lg[4] = fmaf(hv[e], wb.x, lg[4]); lg[5] = fmaf(hv[e], wb.y, lg[5]); lg[6] = fmaf(hv[e], wb.z, lg[6]); lg[7] = fmaf(hv[e], wb.w, lg[7]);
+          }
+          T4_ACC(9); T4_EV(40);
         }
+        T4_T0();
         // partial head sums of this step -> head warp
         mbar_wait(bar_pfree, (hs & 1u) ^ 1u);
         partS[(row * 4 + sub) * 2] = make_float4(lg[0], lg[1], lg[2], lg[3]);
@@ -406,8 +499,10 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
           if (MODE == MODE_SAMPLE) mbar_wait(bar_sym, hs & 1u);
           write_x(q + 1);
         }
+        T4_ACC(10);
       }  // steps
     }  // tiles
+    T4_TOTAL(12);
   } else if (warp == T4_HEAD_WARP) {
     // ======================= head warp: four rows per thread =======================
     const int hrow = lane;
@@ -510,6 +605,15 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
     }  // tiles
   }
 
+#ifdef RNNWF_TC_PROF
+  if (do_prof4) {
+    const int role = (tid == 0) ? 0 : (tid == 32 ? 2 : 1);
+    for (int i = 0; i < 16; ++i) {
+      const int owner = (i == 4 || i == 6 || i == 7) ? 1 : (i < 8 ? 0 : 2);
+      if (owner == role) P.tc_prof[(size_t)blockIdx.x * 16 + i] = (unsigned long long)prof4[i];
+    }
+  }
+#endif
   tc_fence_before();
   __syncthreads();
   if (warp == 0) { __syncwarp(); tc_dealloc(tmem_base, T4_TMEM_COLS); }

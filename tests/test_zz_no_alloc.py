@@ -61,3 +61,25 @@ def test_static_scratch_refuses_models_that_do_not_fit(cuda):
     # the regular entry point still serves the same model
     lp, _ = eng.logpsi(samples)
     assert torch.isfinite(lp).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cfg", [
+    dict(cell=_lib.CELL_TENSGRU2D, nx=6, ny=6, num_units=48, complex_head=True, u1=True),
+    dict(cell=_lib.CELL_GRU4, nx=3, ny=3, num_units=72),
+])
+def test_static_scratch_on_a_tensor_core_handle_runs_the_fp32_sweep(cuda, cfg):
+    """A handle created in the reduced-precision regime sizes its workspace ring for the tensor-core kernels; the
+    entry point without a workspace must not inherit that shape: it always runs the FP32 sweep on the same weights."""
+    tc = Engine(seed=43, precision="tc", **cfg)
+    f32 = Engine(seed=43, **cfg)
+    f32.set_weights(tc.params)
+    u = torch.rand(700, tc.nsteps, generator=torch.Generator().manual_seed(44), dtype=torch.float32)
+    samples, _, _ = f32.sample(700, uniforms=u)
+    want_lp, want_ph = f32.logpsi(samples)
+    for call in range(2):
+        rc, lp, ph = _static_logpsi(tc, samples)
+        assert rc == 0, _lib.lib.rnnwf_last_error().decode()
+        torch.cuda.synchronize()
+        np.testing.assert_allclose(lp.cpu().numpy(), want_lp.cpu().numpy(), rtol=RTOL, atol=1e-6, err_msg=f"call {call}")
+        np.testing.assert_allclose(ph.cpu().numpy(), want_ph.cpu().numpy(), rtol=RTOL, atol=1e-5, err_msg=f"call {call}")
