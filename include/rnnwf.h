@@ -147,6 +147,30 @@ int rnnwf_backward(rnnwf_handle h, int64_t rows, const int8_t* samples_dev, cons
 int rnnwf_logpsi_static(rnnwf_handle h, int64_t rows, const int8_t* samples_dev, double* logp_dev, double* phase_dev,
                         void* stream);
 
+/* Optimiser step right after the gradient all-reduce: tf.train.AdamOptimizer.apply_gradients as the training scripts
+ * use it (1DTFIM/TrainingRNN_1DTFIM.py:163-165, 2DHeisenberg/Run_RNNWF_2DHeis.py:201-217,
+ * RydbergKagome_2DGRU/Run_RNNWF_Rydberg.py:161-177), one fused pass over the flat parameter vector:
+ *   g <- clip_by_value(g, -clip, clip) if clip > 0;  m <- b1 m + (1-b1) g;  v <- b2 v + (1-b2) g^2;
+ *   theta <- theta - lr sqrt(1-b2^t)/(1-b1^t) * m / (sqrt(v) + eps),   t = 1, 2, ... the step number.
+ * All arrays float32 [n] on the device; m and v are the caller's optimiser state (zero before the first step).
+ * Call rnnwf_set_weights afterwards to repack. */
+int rnnwf_adam_step(float* params_dev, const float* grad_dev, float* m_dev, float* v_dev, int64_t n, double lr,
+                    double beta1, double beta2, double eps, int64_t t, double clip, void* stream);
+
+/* Symmetry-projected amplitudes (2DHeisenberg/MDComplexRNN.py:290-316 log_amplitudes_fromsymmetrygroup and the rotsym /
+ * c2v / c4v ... variants :320-577 built on it; RydbergKagome_2DGRU/MDRNNWavefunction.py:242-279 log_probability_symmetry):
+ * the caller evaluates the G transformed copies of its `rows` configurations in one rnnwf_logpsi batch (copy-major:
+ * logp[g*rows + b]); the epilogue returns  out_logp[b] = log(mean_g P_g)  and  out_phase[b] = arg(reg(Re) + i Im) of
+ * sum_g e^{i phi_g} / chi_g,  reg(x) = sign(x) sqrt(x^2 + 1e-8).  chi: G host doubles (the group characters; NULL = all 1).
+ * phase_dev / out_phase_dev may be NULL (positive wavefunctions).  rnnwf_symmetry_seeds is its backward: given
+ * d cost / d out_logp and d cost / d out_phase per row it fills the per-copy seeds rnnwf_backward takes for the G*rows batch
+ * (the sign inside reg is under stop-gradient, as in the reference). */
+int rnnwf_symmetry_epilogue(int G, int64_t rows, const double* logp_dev, const double* phase_dev, const double* chi,
+                            double* out_logp_dev, double* out_phase_dev, void* stream);
+int rnnwf_symmetry_seeds(int G, int64_t rows, const double* logp_dev, const double* phase_dev, const double* chi,
+                         const double* s_logp_dev, const double* s_phase_dev, double* seed_logp_dev, double* seed_phase_dev,
+                         void* stream);
+
 /* Kernel-regime report for the profiler notes: fills `buf` with a one-line description of the tile
  * shape / pipe (FFMA or tcgen05) the handle's sweeps run in. */
 int rnnwf_describe(rnnwf_handle h, char* buf, int cap);

@@ -88,12 +88,8 @@ class RNNwavefunction:
         G = len(list_samples)
         allc = torch.cat([torch.as_tensor(s).reshape(-1, self.Nx, self.Ny) for s in list_samples], dim=0)
         lp, ph = self.engine.logpsi(allc)
-        lp, ph = lp.view(G, -1), ph.view(G, -1)
-        ch = torch.as_tensor(np.asarray(group_character_signs, dtype=np.float64), device=lp.device).view(G, 1)
-        re = (torch.cos(ph) / ch).sum(0)
-        im = (torch.sin(ph) / ch).sum(0)
-        logp = torch.log(torch.exp(lp).sum(0) / G)
-        return torch.complex(0.5 * logp, torch.atan2(im, regularized_identity(re)))
+        logp, phase = self.engine.symmetrize(lp.view(G, -1), ph.view(G, -1), list(group_character_signs))   # fused device epilogue
+        return torch.complex(0.5 * logp, phase)
 
     def _sym(self, name, samples, inputdim, group_character, spinparity_value=None):
         if isinstance(samples, Placeholder):

@@ -83,7 +83,7 @@ class MDRNNWavefunction:
             raise ValueError(symmetry)
         G = len(lst)
         lp = self.engine.logpsi(torch.cat(lst, dim=0))[0].view(G, -1)
-        return torch.logsumexp(lp, dim=0) - math.log(G)
+        return self.engine.symmetrize(lp)[0]             # fused device epilogue: log(mean_g P_g)
 
 
 def generate_kagome(Nx, Ny):

@@ -47,6 +47,9 @@ def _load():
         "rnnwf_backward_workspace_bytes": (i64, [vp, i64]),
         "rnnwf_backward": (C.c_int, [vp, i64, vp, vp, vp, vp, vp, vp, i64, vp]),
         "rnnwf_logpsi_static": (C.c_int, [vp, i64, vp, vp, vp, vp]),
+        "rnnwf_adam_step": (C.c_int, [vp, vp, vp, vp, i64, C.c_double, C.c_double, C.c_double, C.c_double, i64, C.c_double, vp]),
+        "rnnwf_symmetry_epilogue": (C.c_int, [C.c_int, i64, vp, vp, C.POINTER(C.c_double), vp, vp, vp]),
+        "rnnwf_symmetry_seeds": (C.c_int, [C.c_int, i64, vp, vp, C.POINTER(C.c_double), vp, vp, vp, vp, vp]),
         "rnnwf_describe": (C.c_int, [vp, C.c_char_p, C.c_int]),
         "rnnwf_launch_count": (C.c_longlong, []),
         "rnnwf_ffma_probe": (C.c_int, [vp, C.c_int, C.c_int, vp]),

@@ -16,6 +16,7 @@
 #include "eloc.cuh"
 #include "gemm_tc.cuh"
 #include "backward.cuh"
+#include "symmetry.cuh"
 
 using namespace rnnwf;
 
@@ -1026,6 +1027,69 @@ __global__ void __launch_bounds__(512) ffma_probe_kernel(float* out, int iters, 
 
 int rnnwf_ffma_probe(float* out_dev, int blocks, int iters, void* stream) {
   RNNWF_COUNT_LAUNCH(); ffma_probe_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(out_dev, iters, 1.0f);
+  CUDA_TRY(cudaGetLastError());
+  return RNNWF_OK;
+}
+
+// ---- fused optimiser step ---------------------------------------------------------------------------
+// tf.train.AdamOptimizer.apply_gradients in one pass over the flat parameter vector (TF 1.13 semantics, SURVEY App. B:
+// m <- b1 m + (1-b1) g, v <- b2 v + (1-b2) g^2, theta <- theta - lr_t m / (sqrt(v) + eps), lr_t = lr sqrt(1-b2^t)/(1-b1^t)),
+// with the optional clip-by-value the Heisenberg / Rydberg scripts apply to the gradient first.
+__global__ void __launch_bounds__(256) adam_step_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                                        float* __restrict__ v, long long n, float lr_t, float b1, float b2, float eps,
+                                                        float clip) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    float gi = g[i];
+    if (clip > 0.f) gi = fminf(fmaxf(gi, -clip), clip);
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] -= lr_t * mi / (sqrtf(vi) + eps);
+  }
+}
+
+int rnnwf_adam_step(float* params_dev, const float* grad_dev, float* m_dev, float* v_dev, int64_t n, double lr, double beta1,
+                    double beta2, double eps, int64_t t, double clip, void* stream) {
+  if (params_dev == nullptr || grad_dev == nullptr || m_dev == nullptr || v_dev == nullptr || n <= 0 || t < 1)
+    return fail(RNNWF_EINVAL, "rnnwf_adam_step: null argument, n <= 0 or t < 1");
+  const double lr_t = lr * std::sqrt(1.0 - std::pow(beta2, (double)t)) / (1.0 - std::pow(beta1, (double)t));
+  RNNWF_COUNT_LAUNCH();
+  adam_step_kernel<<<std::min(1184, cdiv(n, 256)), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      params_dev, grad_dev, m_dev, v_dev, n, (float)lr_t, (float)beta1, (float)beta2, (float)eps, (float)clip);
+  CUDA_TRY(cudaGetLastError());
+  return RNNWF_OK;
+}
+
+// ---- symmetry-projected amplitudes --------------------------------------------------------------------
+static int sym_chars(int G, const double* chi, SymChars& ch) {
+  if (G < 1 || G > SYM_MAX_G) return fail(RNNWF_EINVAL, "symmetry epilogue: the group must have 1..64 elements");
+  for (int g = 0; g < SYM_MAX_G; ++g) ch.inv_chi[g] = (g < G) ? ((chi != nullptr) ? 1.0 / chi[g] : 1.0) : 0.0;
+  return RNNWF_OK;
+}
+
+int rnnwf_symmetry_epilogue(int G, int64_t rows, const double* logp_dev, const double* phase_dev, const double* chi,
+                            double* out_logp_dev, double* out_phase_dev, void* stream) {
+  if (rows <= 0 || logp_dev == nullptr || out_logp_dev == nullptr) return fail(RNNWF_EINVAL, "rnnwf_symmetry_epilogue: null argument or rows <= 0");
+  SymChars ch;
+  int rc = sym_chars(G, chi, ch);
+  if (rc) return rc;
+  RNNWF_COUNT_LAUNCH();
+  symmetry_epilogue_kernel<<<std::min(1184, cdiv(rows, 256)), 256, 0, static_cast<cudaStream_t>(stream)>>>(G, rows, logp_dev, phase_dev, ch, out_logp_dev, out_phase_dev);
+  CUDA_TRY(cudaGetLastError());
+  return RNNWF_OK;
+}
+
+int rnnwf_symmetry_seeds(int G, int64_t rows, const double* logp_dev, const double* phase_dev, const double* chi,
+                         const double* s_logp_dev, const double* s_phase_dev, double* seed_logp_dev, double* seed_phase_dev, void* stream) {
+  if (rows <= 0 || logp_dev == nullptr || s_logp_dev == nullptr || seed_logp_dev == nullptr)
+    return fail(RNNWF_EINVAL, "rnnwf_symmetry_seeds: null argument or rows <= 0");
+  SymChars ch;
+  int rc = sym_chars(G, chi, ch);
+  if (rc) return rc;
+  RNNWF_COUNT_LAUNCH();
+  symmetry_seeds_kernel<<<std::min(1184, cdiv(rows, 256)), 256, 0, static_cast<cudaStream_t>(stream)>>>(G, rows, logp_dev, phase_dev, ch, s_logp_dev, s_phase_dev,
+                                                                                                      seed_logp_dev, seed_phase_dev);
   CUDA_TRY(cudaGetLastError());
   return RNNWF_OK;
 }

@@ -196,6 +196,33 @@ class Engine:
                                  self._bwd_ws.numel(), _stream()), "rnnwf_backward")
         return grad
 
+    def symmetrize(self, logp, phase=None, characters=None):
+        """Symmetry epilogue on the device (rnnwf_symmetry_epilogue): logp / phase are [G, rows] float64 (copy-major);
+        -> (log mean_g P_g, arg of the character-weighted phase sum or None)."""
+        G, rows = logp.shape
+        lp = logp.to(device=self.device, dtype=torch.float64).contiguous()
+        ph = None if phase is None else phase.to(device=self.device, dtype=torch.float64).contiguous()
+        chi = None if characters is None else (C.c_double * G)(*[float(c) for c in characters])
+        out_lp = torch.empty(rows, dtype=torch.float64, device=self.device)
+        out_ph = None if ph is None else torch.empty(rows, dtype=torch.float64, device=self.device)
+        check(lib.rnnwf_symmetry_epilogue(G, rows, _ptr(lp), _ptr(ph), chi, _ptr(out_lp), _ptr(out_ph), _stream()),
+              "rnnwf_symmetry_epilogue")
+        return out_lp, out_ph
+
+    def symmetry_seeds(self, logp, phase, characters, s_logp, s_phase=None):
+        """Backward of `symmetrize`: per-copy seeds [G, rows] for `backward` on the G*rows batch."""
+        G, rows = logp.shape
+        lp = logp.to(device=self.device, dtype=torch.float64).contiguous()
+        ph = None if phase is None else phase.to(device=self.device, dtype=torch.float64).contiguous()
+        chi = None if characters is None else (C.c_double * G)(*[float(c) for c in characters])
+        sl = s_logp.to(device=self.device, dtype=torch.float64).contiguous()
+        sp = None if s_phase is None else s_phase.to(device=self.device, dtype=torch.float64).contiguous()
+        seed_lp = torch.empty(G, rows, dtype=torch.float64, device=self.device)
+        seed_ph = None if ph is None else torch.empty(G, rows, dtype=torch.float64, device=self.device)
+        check(lib.rnnwf_symmetry_seeds(G, rows, _ptr(lp), _ptr(ph), chi, _ptr(sl), _ptr(sp), _ptr(seed_lp), _ptr(seed_ph), _stream()),
+              "rnnwf_symmetry_seeds")
+        return seed_lp, seed_ph
+
     def describe(self):
         buf = C.create_string_buffer(512)
         check(lib.rnnwf_describe(self._h, buf, 512), "rnnwf_describe")

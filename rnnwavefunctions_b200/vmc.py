@@ -76,8 +76,21 @@ class TFAdam:
         self.v = torch.zeros(numel, dtype=torch.float32, device=device)
         self.b1, self.b2, self.eps, self.t = beta1, beta2, eps, 0
 
-    def step(self, params, grad, lr):
+    def step(self, params, grad, lr, clip=0.0):
         self.t += 1
+        if params.is_cuda:
+            # device parameters: one fused kernel of the C-ABI library (rnnwf_adam_step)
+            import ctypes as C
+            from ._lib import lib, check
+            g = grad if (grad.dtype == torch.float32 and grad.is_contiguous()) else grad.float().contiguous()
+            check(lib.rnnwf_adam_step(C.c_void_p(params.data_ptr()), C.c_void_p(g.data_ptr()), C.c_void_p(self.m.data_ptr()),
+                                      C.c_void_p(self.v.data_ptr()), params.numel(), float(lr), self.b1, self.b2, self.eps,
+                                      self.t, float(clip or 0.0), C.c_void_p(torch.cuda.current_stream().cuda_stream)),
+                  "rnnwf_adam_step")
+            return
+        # host tensors (the gloo tests of the data-parallel logic): the same arithmetic as torch ops
+        if clip:
+            grad = grad.clamp(-clip, clip)
         self.m.mul_(self.b1).add_(grad, alpha=1 - self.b1)
         self.v.mul_(self.b2).addcmul_(grad, grad, value=1 - self.b2)
         lr_t = lr * math.sqrt(1 - self.b2 ** self.t) / (1 - self.b1 ** self.t)

@@ -111,3 +111,62 @@ def test_final_estimate_pass(cuda):
     x = out["samples"].cpu().numpy()
     np.testing.assert_allclose(dens.cpu().numpy(), x.mean(0), rtol=1e-12)
     assert avg == pytest.approx(x.mean()) and avg_err == pytest.approx(np.std(x.mean(axis=(1, 2))) / math.sqrt(600))
+
+
+@pytest.mark.gpu
+def test_fused_adam_step_matches_tf_adam_semantics(cuda):
+    """rnnwf_adam_step (one fused kernel) against the TF-Adam formulas of SURVEY App. B written out in float64,
+    several steps in a row, with and without clip-by-value; called through the C-ABI by vmc.TFAdam."""
+    import math
+    from rnnwavefunctions_b200 import vmc
+    n = 180604
+    g = torch.Generator().manual_seed(5)
+    for clip in (0.0, 0.3):
+        p0 = torch.randn(n, generator=g)
+        p = p0.clone().to(cuda)
+        opt = vmc.TFAdam(n, cuda)
+        m = torch.zeros(n, dtype=torch.float64)
+        v = torch.zeros(n, dtype=torch.float64)
+        ref = p0.double()
+        for t in range(1, 6):
+            grad = torch.randn(n, generator=g)
+            lr = 1e-2 / t
+            opt.step(p, grad.to(cuda), lr, clip=clip)
+            gd = grad.double().clamp(-clip, clip) if clip else grad.double()
+            m = 0.9 * m + 0.1 * gd
+            v = 0.999 * v + 0.001 * gd * gd
+            ref = ref - lr * math.sqrt(1 - 0.999 ** t) / (1 - 0.9 ** t) * m / (v.sqrt() + 1e-8)
+            torch.testing.assert_close(p.cpu().double(), ref, rtol=2e-6, atol=2e-6)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("G,with_phase", [(4, True), (16, True), (6, False), (1, True)])
+def test_symmetry_epilogue_and_seeds_match_the_reference_formulas(cuda, G, with_phase):
+    """rnnwf_symmetry_epilogue / rnnwf_symmetry_seeds against 2DHeisenberg/MDComplexRNN.py:23-25,290-316 written in torch
+    float64 (regularised real part with the sign under stop-gradient) and its autograd."""
+    from rnnwavefunctions_b200 import _lib
+    from rnnwavefunctions_b200.engine import Engine
+    eng = Engine(_lib.CELL_TENSGRU2D, 2, 2, num_units=4, complex_head=True, u1=True, seed=1)
+    g = torch.Generator().manual_seed(G)
+    rows = 1037
+    lp = (-30 * torch.rand(G, rows, generator=g, dtype=torch.float64)).requires_grad_(True)
+    ph = (6 * torch.rand(G, rows, generator=g, dtype=torch.float64) - 3).requires_grad_(True)
+    chi = [1.0 if (k % 3) else -1.0 for k in range(G)]
+    out_lp, out_ph = eng.symmetrize(lp.detach(), ph.detach() if with_phase else None, chi)
+    ref_lp = torch.log(torch.exp(lp).sum(0) / G)
+    torch.testing.assert_close(out_lp.cpu(), ref_lp.detach(), rtol=1e-12, atol=1e-12)
+    s_lp = torch.randn(rows, generator=g, dtype=torch.float64)
+    s_ph = torch.randn(rows, generator=g, dtype=torch.float64)
+    cost = (ref_lp * s_lp).sum()
+    if with_phase:
+        c = torch.tensor(chi, dtype=torch.float64).view(G, 1)
+        re, im = (torch.cos(ph) / c).sum(0), (torch.sin(ph) / c).sum(0)
+        sign = torch.where(re >= 0, torch.ones_like(re), -torch.ones_like(re)).detach()
+        ref_ph = torch.atan2(im, sign * torch.sqrt(re * re + 1e-8))
+        torch.testing.assert_close(out_ph.cpu(), ref_ph.detach(), rtol=1e-11, atol=1e-11)
+        cost = cost + (ref_ph * s_ph).sum()
+    cost.backward()
+    seed_lp, seed_ph = eng.symmetry_seeds(lp.detach(), ph.detach() if with_phase else None, chi, s_lp, s_ph if with_phase else None)
+    torch.testing.assert_close(seed_lp.cpu(), lp.grad, rtol=1e-10, atol=1e-12)
+    if with_phase:
+        torch.testing.assert_close(seed_ph.cpu(), ph.grad, rtol=1e-8, atol=1e-10)
