@@ -101,16 +101,61 @@ def executed_flops_per_step_site(w):
 # clocks
 # ------------------------------------------------------------------------------------------------------
 class ClockSampler:
+    """SM clock and throttle reasons of one GPU, sampled every 25 ms during the timed region.
+
+    NVML in a background thread (per-device queries, microseconds each).  An `nvidia-smi -lms` child process is only the
+    fallback: on an 8-GPU box it enumerates every GPU per poll and serialises on the driver, which stalled this process's own
+    kernel launches (C4 backward phase 7 -> 24 ms with one poller, 33 -> 43 ms/step with one poller per rank)."""
     FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
               "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu_index):
         self.gpu = gpu_index
-        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         self.p = None
+        self.f = None
+        self.thread = None
+        self.samples = []          # (sm_mhz, max_mhz, reasons bitmask)
+        self.nvml = None
+        self.handle = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            pr = torch.cuda.get_device_properties(gpu_index)
+            try:
+                bus = "%08X:%02X:%02X.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+                self.handle = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+            except Exception:
+                vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+                phys = int(vis.split(",")[gpu_index]) if vis and vis.split(",")[gpu_index].strip().isdigit() else gpu_index
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
+
+    def _poll(self):
+        nv = self.nvml
+        while not self._stop:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM)
+                mx = nv.nvmlDeviceGetMaxClockInfo(self.handle, nv.NVML_CLOCK_SM)
+                try:
+                    rs = nv.nvmlDeviceGetCurrentClocksEventReasons(self.handle)
+                except Exception:
+                    rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+                self.samples.append((float(sm), float(mx), int(rs)))
+            except Exception:
+                pass
+            time.sleep(0.025)
 
     def start(self):
+        if self.nvml is not None:
+            import threading
+            self._stop = False
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+            return
         try:
+            self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.FIELDS}",
                                        "--format=csv,noheader,nounits", "-lms", "25"], stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
@@ -118,6 +163,20 @@ class ClockSampler:
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.thread is not None:
+            self._stop = True
+            self.thread.join(timeout=2)
+            nv = self.nvml
+            bits = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
+            reasons = set()
+            for _, _, rs in self.samples:
+                for name, bit in bits.items():
+                    if rs & bit:
+                        reasons.add(name)
+            if self.samples:
+                out.update(sm_mhz=float(np.median([x[0] for x in self.samples])), sm_max_mhz=float(max(x[1] for x in self.samples)),
+                           reasons=sorted(reasons), samples=len(self.samples), source="nvml")
+            return out
         if self.p is None:
             return out
         self.p.terminate()
@@ -145,7 +204,7 @@ class ClockSampler:
         except OSError:
             pass
         if sm:
-            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm), source="nvidia-smi")
         return out
 
 
@@ -361,8 +420,10 @@ def main():
         step_resident(False)
     barrier()
     launches0 = _lib.lib.rnnwf_launch_count()
-    clocks = ClockSampler(local_rank)
-    clocks.start()
+    # rank 0 alone samples the clocks (of its own GPU)
+    clocks = ClockSampler(local_rank) if rank == 0 else None
+    if clocks is not None:
+        clocks.start()
     t_start, t_end = ev(), ev()
     recs = []
     barrier()
@@ -371,7 +432,7 @@ def main():
         recs.append(step_resident(True))
     t_end.record()
     barrier()
-    clk = clocks.stop()
+    clk = clocks.stop() if clocks is not None else {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
     launches = _lib.lib.rnnwf_launch_count() - launches0
     elapsed_ms = t_start.elapsed_time(t_end)
     nconf_local = 0

@@ -68,7 +68,8 @@ struct T4Smem {
 };
 
 // stages of the operand ring.  (Measured dead ends, tools/tc4_cycles.py: a fifth stage at the price of reading the head weights
-// from global memory, streaming loads for the parent-history gather, separate A / B rings -- the stream is bound by
+// from global memory, streaming loads for the parent-history gather, an L2 prefetch of the next tile's parent history,
+// separate A / B rings -- the stream is bound by
 // bytes in flight per SM x ~3k cycles of L2 latency under load, tools/ubench/bulk_rate.cu.)
 __host__ __device__ inline int t4_stages(int Q) { (void)Q; return T4_MAX_STAGES; }
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
