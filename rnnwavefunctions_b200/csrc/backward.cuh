@@ -433,7 +433,7 @@ inline cudaError_t backward_init_tc(const rnnwf_model_impl& m) {
 }
 
 struct BwdLayout { long long off_dh, off_dp, off_Z, off_dZ, off_hc, off_dhc, off_dlog, off_X, off_wstack, off_wimg, off_dpT, off_jobs, off_cls,
-                   off_t4_wt, off_t4_dimg, off_t4_himg, off_t4_ximg, total; long long dpw; int Kz; bool batched; };
+                   off_t4_wt, off_t4_dimg, off_t4_himg, off_t4_ximg, total; long long dpw; int Kz; bool batched; bool batched1d; };
 inline cudaError_t backward_init_tc4(const rnnwf_model_impl& m) {
   cudaError_t e = cudaFuncSetAttribute(bwd4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, B4Smem(m.tc_np, m.Q).total);
   if (e != cudaSuccess) return e;
@@ -477,7 +477,10 @@ inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   // ALL steps, so that dW, dWg, dWmerge, the head kernels and every bias come out of one long-K GEMM / reduction each
   // after the reverse sweep instead of ~10 small launches per lattice site.
   L.batched = (m.cell == CELL_TENS2D || m.cell == CELL_TENSGRU2D);
-  const long long nb = L.batched ? m.Q : 1;
+  // Single-layer 1D GRU: the same idea -- d(pre-activations), d(logits) and the one-hot inputs of ALL sites are kept, so every
+  // weight / bias gradient is one launch after the reverse recurrence (4 launches per site instead of 15).
+  L.batched1d = (m.cell == CELL_GRU1D && m.symL == 1);
+  const long long nb = (L.batched || L.batched1d) ? m.Q : 1;
   // tensor-core regime of the tensorized GRU: the reverse sweep / weight-gradient kernels have their own layouts
   // (d h tile-blocked, feature-major ds/dg/dm); none of the per-site FFMA-regime operands below is needed
   const bool tcs = m.tc_enabled;   // (tensorized GRU and vanilla 2D RNN both have the tensor-core backward)
@@ -488,8 +491,8 @@ inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   L.off_dZ = o;   o += al(tcs ? 0 : R * (long long)L.Kz * 4);   // tensorized cells: the per-step linearised operand P [R][7nh] lives here
   L.off_hc = o;   o += al(tcs ? 0 : nb * R * 2 * nh * 4);
   L.off_dhc = o;  o += al(tcs ? 0 : R * 2 * nh * 4);
-  L.off_dlog = o; o += al(((L.batched || tcs || m.tc4) ? (long long)m.Q : 1LL) * R * 8 * 4);   // d(logits) of all sites in the batched / tensor-core paths
-  L.off_X = o;    o += al(R * 8 * 4);
+  L.off_dlog = o; o += al(((L.batched || L.batched1d || tcs || m.tc4) ? (long long)m.Q : 1LL) * R * 8 * 4);   // d(logits) of all sites in the batched / tensor-core paths
+  L.off_X = o;    o += al((L.batched1d ? (long long)m.Q : 1LL) * R * 8 * 4);
   L.off_wstack = o; o += al(L.batched ? 3LL * 2 * nh * 7 * nh * 4 : 0);
   L.off_wimg = o;   o += al(tcs ? 3LL * ((m.nhp + TC_JP - 1) / TC_JP) * BtSmem(m.nhp, m.Tsym, m.Q).b_bytes : 0);   // Wstack^T chunks of the reverse sweep
   L.off_dpT = o;    o += al(tcs ? tc_dpt_bytes(m.Q, R, m.nhp) : 0);
@@ -762,11 +765,12 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
     S.sym_site = sm.site;
 
     const bool batched = L.batched;
-    float* dlog = batched ? dlog_base + (long long)q * R * m.ND : dlog_base;
+    const bool b1d = L.batched1d;
+    float* dlog = (batched || b1d) ? dlog_base + (long long)q * R * m.ND : dlog_base;
     if (sm.head) {
       const int wpb = 8;
       RNNWF_COUNT_LAUNCH(); head_bwd_kernel<<<(unsigned)((R + wpb - 1) / wpb), wpb * 32, 0, st>>>(S, m.d_site_of_t, m.d_head_w, m.d_head_b, seed_logp, seed_phase, dlog);
-      if (!batched) {
+      if (!batched && !b1d) {
         G.tn(hrow(q), nhp, dlog, m.ND, Gd("dense.W"), m.D, R, nh, m.D);
         G.colsum(dlog, m.ND, R, m.D, Gd("dense.b"));
         if (m.complex_head) {
@@ -779,6 +783,11 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
     float* dp0 = batched ? dp + (long long)q * R * nh : dp;
     float* dp1 = batched ? dp + ((long long)m.Q + q) * R * nh : dp + ((m.cell == CELL_GRU1D) ? 2 * R * nh : R * nh);
     float* dp2 = batched ? dp + (2LL * m.Q + q) * R * nh : dp1 + R * nh;
+    if (b1d) {   // three arrays over all sites: [Q][R][2nh] (d r_pre, d u_pre), [Q][R][nh] (d candidate input), [Q][R][nh] (d candidate hidden)
+      dp0 = dp + (long long)q * R * 2 * nh;
+      dp1 = dp + (long long)m.Q * R * 2 * nh + (long long)q * R * nh;
+      dp2 = dp + (long long)m.Q * R * 3 * nh + (long long)q * R * nh;
+    }
     float* Z = batched ? Z_base + (long long)q * R * L.Kz : Z_base;
     float* hc = batched ? hc_base + (long long)q * R * 2 * nh : hc_base;
     if (batched) { RNNWF_COUNT_LAUNCH(); cell_bwd_tens_kernel<<<nblk(R * nh), tpb, 0, st>>>(S, m.cell == CELL_TENSGRU2D ? 1 : 0, dp0, dp1, dp2, dZ); }
@@ -839,6 +848,16 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
         const std::string p = "gru" + std::to_string(l) + ".";
         const float* Wg = P(p + "Wg");
         float* dWg = Gd(p + "Wg");
+        if (b1d) {
+          // single layer: only the recurrence stays in the loop (d h_{q-1} += d gates Wg_h^T + d candidate Wch^T); the
+          // one-hot inputs of this site are kept for the batched weight gradients below
+          if (sm.nsym[0] >= 0) { RNNWF_COUNT_LAUNCH(); build_onehot_kernel<<<nblk(R), tpb, 0, st>>>(S, 1, X + (long long)q * R * 2); }
+          if (sm.nbr[0] >= 0) {
+            G.nt(dp0, 2 * nh, Wg + (long long)din * 2 * nh, 2 * nh, dhrow(sm.nbr[0]), nhp, R, nh, 2 * nh, 1);
+            G.nt(dp2, nh, P(p + "Wch"), nh, dhrow(sm.nbr[0]), nhp, R, nh, nh, 1);
+          }
+          break;
+        }
         G.colsum(dp0, 2 * nh, R, 2 * nh, Gd(p + "bg"));
         G.colsum(dp1, nh, R, nh, Gd(p + "bci"));
         G.colsum(dp2, nh, R, nh, Gd(p + "bch"));
@@ -863,6 +882,30 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
         }
         break;
       }
+    }
+  }
+  if (L.batched1d) {
+    // Single-layer 1D GRU: weight and bias gradients over all sites at once.  Site 0 has neither a previous state nor a
+    // one-hot input (the first input is the zero vector); sites 1..Q-1 are contiguous in every array.
+    const long long RQ = (long long)m.Q * R, R1 = (long long)(m.Q - 1) * R;
+    float* dgA = dp;                                          // [Q][R][2nh]
+    float* dciA = dp + (long long)m.Q * R * 2 * nh;           // [Q][R][nh]
+    float* dchA = dp + (long long)m.Q * R * 3 * nh;           // [Q][R][nh]
+    float* dWg = Gd("gru0.Wg");
+    G.colsum(dgA, 2 * nh, RQ, 2 * nh, Gd("gru0.bg"));
+    G.colsum(dciA, nh, RQ, nh, Gd("gru0.bci"));
+    G.colsum(dchA, nh, RQ, nh, Gd("gru0.bch"));
+    if (m.Q > 1) {
+      G.tn(hist, nhp, dgA + R * 2LL * nh, 2 * nh, dWg + 2LL * 2 * nh, 2 * nh, R1, nh, 2 * nh);     // rows of Wg fed by h_{q-1}
+      G.tn(hist, nhp, dchA + R * (long long)nh, nh, Gd("gru0.Wch"), nh, R1, nh, nh);
+      G.tn(X + R * 2LL, 2, dgA + R * 2LL * nh, 2 * nh, dWg, 2 * nh, R1, 2, 2 * nh);               // rows fed by the one-hot input
+      G.tn(X + R * 2LL, 2, dciA + R * (long long)nh, nh, Gd("gru0.Wci"), nh, R1, 2, nh);
+    }
+    G.tn(hist, nhp, dlog_base, m.ND, Gd("dense.W"), m.D, RQ, nh, m.D);
+    G.colsum(dlog_base, m.ND, RQ, m.D, Gd("dense.b"));
+    if (m.complex_head) {
+      G.tn(hist, nhp, dlog_base + m.D, m.ND, Gd("dense_phase.W"), 2, RQ, nh, 2);
+      G.colsum(dlog_base + m.D, m.ND, RQ, 2, Gd("dense_phase.b"));
     }
   }
   if (L.batched) {
