@@ -342,9 +342,8 @@ int pick_shape(const rnnwf_model& m, long long rows, LaunchShape& s) {
     const long long tiles = (rows + Mr - 1) / Mr;
     const bool fits = L.total <= 227 * 1024;
     if (!fits) continue;
-    // prefer the tallest tile that still gives every SM two tiles (the small models are latency-bound: two resident CTAs per
-    // SM hide each other's per-site round trips)
-    if (wr == 1 || tiles >= 2LL * m.num_sms) {
+    // prefer the tallest tile that still gives every SM a tile
+    if (wr == 1 || tiles >= m.num_sms) {
       s.WR = wr; s.Mp = Mp; s.Mr = Mr; s.threads = 32 * wr * m.WC; s.smem = L.total;
       int occ = 1;
       if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sweep_fn(m), s.threads, s.smem) != cudaSuccess) { occ = 1; cudaGetLastError(); }
