@@ -101,3 +101,25 @@ def test_tc4_backward(cuda, nx, ny, nh, ns):
         ga, gb = eng.backward(s, saved, seeds).cpu(), f32.backward(s, sv2, seeds).cpu()
         for (n, a), (_, b) in zip(eng.views(ga).items(), f32.views(gb).items()):
             assert float((a - b).abs().max()) <= 1e-2 * float(b.abs().max()) + 1e-30, f"gradient of {n} differs from the FP32 regime"
+
+
+@pytest.mark.gpu
+def test_tc4_large_lattice_matches_fp32_regime(cuda):
+    """8x8 unit cells (192 atoms, the primary C5 size): log P and the prefix-reuse local energies of the tensor-core regime
+    against the FP32 regime on the same weights and samples (the float64 oracle is too slow at this size); the
+    periodic look-back spans the whole lattice here (ring of 64 cells, row 0 feeds the last row)."""
+    nx = ny = 8
+    nh, ns = 96, 300
+    eng = _mk(nx, ny, nh, seed=101)
+    f32 = Engine(_lib.CELL_GRU4, nx, ny, num_units=nh, seed=101)
+    f32.set_weights(eng.params)
+    saved = eng.new_saved(ns)
+    s, lp, ph = eng.sample(ns, seed=7, row_offset=0, saved=saved)
+    lp32, ph32 = f32.logpsi(s)
+    scale = float(lp32.abs().max())
+    np.testing.assert_allclose(lp.cpu().numpy(), lp32.cpu().numpy(), rtol=RTOL, atol=RTOL * scale * 0.1)
+    e = eng.local_energies(_lib.HAM_RYDBERG, HAM, s, lp, ph, saved=saved).cpu().numpy().real
+    e_noreuse = eng.local_energies(_lib.HAM_RYDBERG, HAM, s, lp, ph).cpu().numpy().real
+    e32 = f32.local_energies(_lib.HAM_RYDBERG, HAM, s, lp32, ph32).cpu().numpy().real
+    np.testing.assert_allclose(e, e32, rtol=2e-3, atol=2e-3 * np.abs(e32).max())
+    np.testing.assert_allclose(e_noreuse, e, rtol=1e-4, atol=1e-4 * np.abs(e).max())
