@@ -110,25 +110,33 @@ __global__ void bond_fill_kernel(const int8_t* __restrict__ cfg, long long ns, i
 }
 
 // ---- Rydberg diagonal part -------------------------------------------------------------------------
+// one warp per sample: lanes over (unit cell, neighbour-table entry) pairs, float64 shuffle reduction
 __global__ void rydberg_diag_kernel(const int8_t* __restrict__ cfg, long long ns, int Lx, int Ly, const RydNb* __restrict__ nb,
                                     int nnb, double delta, double* __restrict__ eloc) {
-  for (long long n = blockIdx.x * (long long)blockDim.x + threadIdx.x; n < ns; n += (long long)gridDim.x * blockDim.x) {
-    const int8_t* row = cfg + n * Lx * Ly * 3;
+  const int lane = threadIdx.x & 31;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  const int cells = Lx * Ly;
+  for (long long n = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; n < ns; n += nwarps) {
+    const int8_t* row = cfg + n * cells * 3;
     double e = 0.0;
-    for (int i = 0; i < Lx; ++i)
-      for (int j = 0; j < Ly; ++j) {
-        const int8_t* cell = row + (i * Ly + j) * 3;
-        e -= delta * (double)((cell[0] & 1) + (cell[1] & 1) + (cell[2] & 1));
-        for (int m = 0; m < nnb; ++m) {
-          const RydNb q = nb[m];
-          if (cell[q.kc] & 1) {
-            const int ii = ((i + q.di) % Lx + Lx) % Lx, jj = ((j + q.dj) % Ly + Ly) % Ly;
-            if (row[(ii * Ly + jj) * 3 + q.k] & 1) e += (double)q.w;
-          }
-        }
+    for (int c = lane; c < cells; c += 32) {
+      const int8_t* cell = row + c * 3;
+      e -= delta * (double)((cell[0] & 1) + (cell[1] & 1) + (cell[2] & 1));
+    }
+    for (int idx = lane; idx < cells * nnb; idx += 32) {
+      const int c = idx / nnb, m = idx - c * nnb;
+      const int i = c / Ly, j = c - i * Ly;
+      const RydNb q = nb[m];
+      if (row[c * 3 + q.kc] & 1) {
+        const int ii = ((i + q.di) % Lx + Lx) % Lx, jj = ((j + q.dj) % Ly + Ly) % Ly;
+        if (row[(ii * Ly + jj) * 3 + q.k] & 1) e += (double)q.w;
       }
-    eloc[2 * n] = e;
-    eloc[2 * n + 1] = 0.0;
+    }
+    for (int o = 16; o > 0; o >>= 1) e += __shfl_xor_sync(0xffffffffu, e, o);
+    if (lane == 0) {
+      eloc[2 * n] = e;
+      eloc[2 * n + 1] = 0.0;
+    }
   }
 }
 

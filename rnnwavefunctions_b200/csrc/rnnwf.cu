@@ -884,7 +884,7 @@ int rnnwf_local_energies(rnnwf_handle h, int hamiltonian, const double* ham, int
             }
       if (nb.size() > 256) return fail(RNNWF_EINVAL, "Rydberg: too many neighbours within Rcutoff (max 256)");
       if (!nb.empty()) CUDA_TRY(cudaMemcpyAsync(d_nb, nb.data(), nb.size() * sizeof(RydNb), cudaMemcpyHostToDevice, st));
-      RNNWF_COUNT_LAUNCH(); rydberg_diag_kernel<<<gsamp, tpb, 0, st>>>(samples_dev, rows, Nx, Ny, d_nb, (int)nb.size(), delta, eloc_dev);
+      RNNWF_COUNT_LAUNCH(); rydberg_diag_kernel<<<std::min(8192, cdiv(rows * 32, tpb)), tpb, 0, st>>>(samples_dev, rows, Nx, Ny, d_nb, (int)nb.size(), delta, eloc_dev);
       if (Omega == 0.0) have_children = false;
       else {
         nchild_fixed = 3LL * T * rows;
