@@ -433,7 +433,7 @@ inline cudaError_t backward_init_tc(const rnnwf_model_impl& m) {
 }
 
 struct BwdLayout { long long off_dh, off_dp, off_Z, off_dZ, off_hc, off_dhc, off_dlog, off_X, off_wstack, off_wimg, off_dpT, off_jobs, off_cls,
-                   off_t4_wt, off_t4_dimg, off_t4_himg, off_t4_ximg, total; long long dpw; int Kz; bool batched; bool batched1d; };
+                   off_t4_wt, off_t4_dimg, off_t4_himg, off_t4_ximg, off_t4_dlimg, total; long long dpw; int Kz; bool batched; bool batched1d; };
 inline cudaError_t backward_init_tc4(const rnnwf_model_impl& m) {
   cudaError_t e = cudaFuncSetAttribute(bwd4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, B4Smem(m.tc_np, m.Q).total);
   if (e != cudaSuccess) return e;
@@ -455,6 +455,7 @@ inline void dw4_plan(const rnnwf_model_impl& m, long long R, std::vector<Dw4Job>
     for (int m0 = 0; m0 < N4 && m0 < m.nh; m0 += 128)
       for (int blk = 0; blk < 3; ++blk) { outs.push_back({0, s, m0, blk, (long long)sites_n[s] * tiles}); total += outs.back().items; }
   for (int blk = 0; blk < 2; ++blk) { outs.push_back({1, 0, 0, blk, (long long)m.Q * tiles}); total += outs.back().items; }
+  for (int m0 = 0; m0 < N4 && m0 < m.nh; m0 += 128) { outs.push_back({2, 0, m0, 0, (long long)m.Q * tiles}); total += outs.back().items; }   // head weights
   const long long target = std::max<long long>(8, (total + 3LL * m.num_sms - 1) / (3LL * m.num_sms));   // items per job
   jobs.clear();
   for (auto& o : outs) {
@@ -504,6 +505,7 @@ inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
     L.off_t4_dimg = o; o += al(t4 * m.Q * tiles * 3 * NP * (long long)B4_A_BYTES);
     L.off_t4_himg = o; o += al(t4 * m.Q * tiles * NP * (long long)B4_A_BYTES);
     L.off_t4_ximg = o; o += al(t4 * m.Q * tiles * 4 * 128 * 16);
+    L.off_t4_dlimg = o; o += al(t4 * m.Q * tiles * 4096);
   }
   L.total = o;
   return L;
@@ -722,6 +724,7 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
     B.dimg = reinterpret_cast<unsigned char*>(ws + L.off_t4_dimg);
     B.himg = reinterpret_cast<unsigned char*>(ws + L.off_t4_himg);
     B.ximg = reinterpret_cast<unsigned char*>(ws + L.off_t4_ximg);
+    B.dlimg = reinterpret_cast<unsigned char*>(ws + L.off_t4_dlimg);
     RNNWF_COUNT_LAUNCH(); bwd4_kernel<<<(unsigned)std::min<long long>(tiles, m.num_sms), B4_THREADS, B4Smem(m.tc_np, m.Q).total, st>>>(B);
     {
       // weight gradients: grouped GEMM over the images the reverse sweep left behind (work plan cached per row count)
@@ -740,12 +743,11 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
       D.Q = m.Q; D.nh = nh; D.NP = m.tc_np; D.tiles = (int)tiles; D.steps = m.d_steps;
       D.jobs = static_cast<const Dw4Job*>(m.d_dw4_jobs); D.sites = m.d_dw4_sites;
       for (int k = 0; k < 5; ++k) D.sites_n[k] = m.dw4_sites_n[k];
-      D.dimg = B.dimg; D.himg = B.himg; D.ximg = B.ximg;
+      D.dimg = B.dimg; D.himg = B.himg; D.ximg = B.ximg; D.dlimg = B.dlimg; D.gDense = Gd("dense.W");
       D.gW = Gd("W"); D.gWg = Gd("Wg"); D.gWmerge = Gd("Wmerge"); D.gb = Gd("b"); D.gbg = Gd("bg");
       if (m.dw4_njobs > 0) { RNNWF_COUNT_LAUNCH(); dw4_kernel<<<(unsigned)m.dw4_njobs, DW4_THREADS, DW4_SMEM, st>>>(D); }
     }
-    G.tn(hist, nhp, dlog_base, m.ND, Gd("dense.W"), m.D, RQ, nh, m.D);
-    G.colsum(dlog_base, m.ND, RQ, m.D, Gd("dense.b"));
+    G.colsum(dlog_base, m.ND, RQ, m.D, Gd("dense.b"));      // (dense.W is one more job type of dw4_kernel)
     e = cudaGetLastError();
     if (e != cudaSuccess) { err = std::string("rnnwf_backward kernels: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
     return RNNWF_OK;

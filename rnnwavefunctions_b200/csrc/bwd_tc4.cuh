@@ -43,6 +43,7 @@ struct Bwd4Params {
   unsigned char* dimg;      // BF16 [Q][tiles][chunk 3 NP][k-core 8][row 128][8]
   unsigned char* himg;      // BF16 [Q][tiles][k-core 8 NP][row 128][8]
   unsigned char* ximg;      // BF16 [Q][tiles][k-core 4][row 128][8]
+  unsigned char* dlimg;     // BF16 [Q][tiles][k-core 2][row 128][8]: d(logits) (second k-core zero: the MMA needs N >= 16)
 };
 
 struct B4Smem {
@@ -250,6 +251,11 @@ __global__ void __launch_bounds__(B4_THREADS, 1) bwd4_kernel(const Bwd4Params P)
             o[0] = make_float4(dl[0], dl[1], dl[2], dl[3]);
             o[1] = make_float4(dl[4], dl[5], dl[6], dl[7]);
           }
+          if (sub == 0) {     // image for the head weight gradient (dead rows: seed = 0 -> zeros)
+            unsigned char* o = P.dlimg + ((size_t)q * (size_t)ntiles + (size_t)tile) * 4096 + (size_t)row * 16;
+            *reinterpret_cast<uint4*>(o) = make_uint4(pack_bf16x2(dl[0], dl[1]), pack_bf16x2(dl[2], dl[3]), pack_bf16x2(dl[4], dl[5]), pack_bf16x2(dl[6], dl[7]));
+            *reinterpret_cast<uint4*>(o + 2048) = make_uint4(0u, 0u, 0u, 0u);
+          }
         }
         // ---- one-hot input image (k-core = neighbour slot = sub): pairs of the neighbour cell's three bits, constant 1 at
         //      position 6 of slot 0 (its weight-gradient row is the bias gradient)
@@ -366,7 +372,7 @@ __global__ void pack_bwd4_kernel(const float* __restrict__ W, const float* __res
 // block s|g) -- accumulated in TMEM over a contiguous range of (cell, tile) items and flushed with atomics.  Per item the
 // contraction runs over the tile's 128 rows: A = hidden-state (or one-hot) image, B = d(pre-activation) image of the block, both
 // MN-major (8 units contiguous per row, rows 16 bytes apart, 8-row groups 128 bytes apart, 8-unit groups 2048 bytes apart).
-struct Dw4Job { int16_t kind, slot, m0, blk; int32_t item_begin, item_count; };   // kind 0: hidden-state rows, 1: one-hot input rows
+struct Dw4Job { int16_t kind, slot, m0, blk; int32_t item_begin, item_count; };   // kind 0: hidden-state rows, 1: one-hot input rows, 2: head weights
 static_assert(sizeof(Dw4Job) == 16, "Dw4Job layout");
 
 struct Dw4Params {
@@ -378,7 +384,8 @@ struct Dw4Params {
   const unsigned char* dimg;
   const unsigned char* himg;
   const unsigned char* ximg;
-  float* gW; float* gWg; float* gWmerge; float* gb; float* gbg;
+  const unsigned char* dlimg;
+  float* gW; float* gWg; float* gWmerge; float* gb; float* gbg; float* gDense;
 };
 
 constexpr int DW4_THREADS = 128;
@@ -406,10 +413,11 @@ __global__ void __launch_bounds__(DW4_THREADS, 1) dw4_kernel(const Dw4Params P) 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_d = *tmem_slot;
-  const uint32_t a_bytes = (job.kind == 0) ? (uint32_t)((N4 - job.m0 < 128 ? N4 - job.m0 : 128) / 8) * 2048u : 4u * 2048u;
-  const uint32_t b_bytes = (uint32_t)NP * B4_A_BYTES;
+  const uint32_t a_bytes = (job.kind != 1) ? (uint32_t)((N4 - job.m0 < 128 ? N4 - job.m0 : 128) / 8) * 2048u : 4u * 2048u;
+  const uint32_t b_bytes = (job.kind == 2) ? 4096u : (uint32_t)NP * B4_A_BYTES;
+  const int Nk = (job.kind == 2) ? 16 : N4;          // MMA columns: head job = 8 logits padded to 16
   const size_t dimg_tile = (size_t)3 * NP * B4_A_BYTES, himg_tile = (size_t)NP * B4_A_BYTES, ximg_tile = 4 * 2048;
-  const int* sites = P.sites + (job.kind == 0 ? job.slot : 4) * P.Q;
+  const int* sites = P.sites + (job.kind == 0 ? job.slot : 4) * P.Q;     // (input and head jobs: every cell)
 
   if (warp == 0) {
     const bool leader = elect_one();
@@ -419,18 +427,20 @@ __global__ void __launch_bounds__(DW4_THREADS, 1) dw4_kernel(const Dw4Params P) 
       if (i >= 2) mbar_wait_relaxed(bar_empty + s, ((uint32_t)(i >> 1) - 1u) & 1u);
       if (leader) {
         unsigned char* dst = stage0 + (size_t)s * DW4_STAGE;
+        const size_t qt = (size_t)q * (size_t)P.tiles + (size_t)tile;
         const unsigned char* asrc = (job.kind == 0)
             ? P.himg + ((size_t)P.steps[q].nbr[job.slot] * (size_t)P.tiles + (size_t)tile) * himg_tile + (size_t)(job.m0 / 8) * 2048
-            : P.ximg + ((size_t)q * (size_t)P.tiles + (size_t)tile) * ximg_tile;
+            : (job.kind == 2 ? P.himg + qt * himg_tile + (size_t)(job.m0 / 8) * 2048 : P.ximg + qt * ximg_tile);
+        const unsigned char* bsrc = (job.kind == 2) ? P.dlimg + qt * 4096 : P.dimg + qt * dimg_tile + (size_t)job.blk * b_bytes;
         mbar_expect_tx(bar_full + s, a_bytes + b_bytes);
         bulk_g2s(dst, asrc, a_bytes, bar_full + s);
-        bulk_g2s(dst + DW4_A_MAX, P.dimg + ((size_t)q * (size_t)P.tiles + (size_t)tile) * dimg_tile + (size_t)job.blk * b_bytes, b_bytes, bar_full + s);
+        bulk_g2s(dst + DW4_A_MAX, bsrc, b_bytes, bar_full + s);
       }
       __syncwarp();
     }
   } else if (warp == 1) {
     const bool leader = elect_one();
-    const uint32_t idesc = b4_idesc_bf16(128, N4, 1, 1);
+    const uint32_t idesc = b4_idesc_bf16(128, Nk, 1, 1);
     for (int i = 0; i < job.item_count; ++i) {
       const uint32_t s = (uint32_t)i & 1u;
       mbar_wait(bar_full + s, (uint32_t)(i >> 1) & 1u);
@@ -455,19 +465,24 @@ __global__ void __launch_bounds__(DW4_THREADS, 1) dw4_kernel(const Dw4Params P) 
     // flush: thread = accumulator row m (TMEM lane)
     const int m = warp * 32 + lane;
     float* dst = nullptr;          // row of the gradient tensor this accumulator row belongs to
+    int ncol = nh;                 // real columns of this job's output rows
     if (job.kind == 0) {
       const int k = job.m0 + m;
       if (k < nh) {
         if (job.blk == 2) dst = P.gWmerge + (size_t)(job.slot * nh + k) * nh;
         else dst = (job.blk == 0 ? P.gW : P.gWg) + (size_t)(24 + job.slot * nh + k) * nh;
       }
+    } else if (job.kind == 2) {
+      const int k = job.m0 + m;
+      if (k < nh) dst = P.gDense + (size_t)k * 8;
+      ncol = 8;
     } else if (m < 32) {
       const int slot = m >> 3, i = m & 7;
       if (i < 6) dst = (job.blk == 0 ? P.gW : P.gWg) + (size_t)(slot * 6 + i) * nh;
       else if (i == 6 && slot == 0) dst = (job.blk == 0 ? P.gb : P.gbg);
     }
 #pragma unroll 1
-    for (int c0 = 0; c0 < N4; c0 += 16) {
+    for (int c0 = 0; c0 < Nk; c0 += 16) {
       uint32_t d[16];
       __syncwarp();
       tc_ld16(tmem_d + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, d);
@@ -476,7 +491,7 @@ __global__ void __launch_bounds__(DW4_THREADS, 1) dw4_kernel(const Dw4Params P) 
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
           const float v = __uint_as_float(d[e]);
-          if (c0 + e < nh && v != 0.f) atomicAdd(dst + c0 + e, v);
+          if (c0 + e < ncol && v != 0.f) atomicAdd(dst + c0 + e, v);
         }
       }
     }
