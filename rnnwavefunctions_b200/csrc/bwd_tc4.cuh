@@ -32,7 +32,7 @@ struct Bwd4Params {
   const StepMeta* steps;
   const int8_t* cfg;
   const float* hist;        // [Q][R][nhp]
-  const float4* gates;      // [Q][R][Gp]  (u, h~, m, -)
+  const float4* gates;      // tile-blocked [Q][tiles][Gp][row 128]  (u, h~, m, -)
   float* dh;                // [Q][R][nhp], zero on entry
   float* dp;                // optional FP32 copy of (ds, dg, dm): [3][Q][R][nh]
   float* dlog;              // [Q][R][8]
@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(B4_THREADS, 1) bwd4_kernel(const Bwd4Params P)
         // ---- d h_q (+ the head's push) -> (ds, dg, dm): BF16 chunk images (+ optional FP32 copies)
         if (active) {
           const float* dhq = P.dh + ((size_t)q * (size_t)P.R + (size_t)(live ? grow : 0)) * nhp;
-          const float4* gq = P.gates + ((size_t)q * (size_t)P.R + (size_t)(live ? grow : 0)) * P.Gp;
+          const float4* gq = P.gates + qt * (size_t)P.Gp * 128 + row;         // unit j at gq[j * 128]
           unsigned char* ddst = P.dimg + qt * dimg_tile + (size_t)sub * B4_A_BYTES + (size_t)row * 16;
 #pragma unroll 1
           for (int kc = 0; kc < 8; ++kc) {
@@ -289,7 +289,7 @@ __global__ void __launch_bounds__(B4_THREADS, 1) bwd4_kernel(const Bwd4Params P)
                 float d = dhq[j];
                 d = fmaf(wa.x, dl[0], d); d = fmaf(wa.y, dl[1], d); d = fmaf(wa.z, dl[2], d); d = fmaf(wa.w, dl[3], d);
                 d = fmaf(wb.x, dl[4], d); d = fmaf(wb.y, dl[5], d); d = fmaf(wb.z, dl[6], d); d = fmaf(wb.w, dl[7], d);
-                const float4 g = __ldg(gq + j);                      // (u, h~, m, -)
+                const float4 g = __ldg(gq + (size_t)j * 128);        // (u, h~, m, -)
                 dsv[i] = d * g.x * (1.f - g.y * g.y);
                 dgv[i] = d * (g.y - g.z) * g.x * (1.f - g.x);
                 dmv[i] = d * (1.f - g.x);

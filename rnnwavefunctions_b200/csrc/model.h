@@ -86,7 +86,8 @@ struct rnnwf_model_impl {
     // tensor-core regime: gates are saved tile-blocked, three float4 per (row, 4 units) (bwd_tc.cuh: tc_gate_index)
     const bool tcs = tc_enabled && (cell == CELL_TENSGRU2D || cell == CELL_TENS2D);   // tile-blocked (u, h~, m); the vanilla cell saves none
     const long long gate_bytes = tcs ? (long long)Q * ((rows + 127) / 128) * 4 * tc_np * 3 * 128 * 16
-                                            : (gru_type ? (long long)Q * rows * Gp * 16 : 0);
+                                     : (tc4 ? (long long)Q * ((rows + 127) / 128) * Gp * 128 * 16      // tile-blocked [cell][tile][unit][row 128]
+                                            : (gru_type ? (long long)Q * rows * Gp * 16 : 0));
     s.off_cum = s.off_gates + al(gate_bytes);
     s.off_himg = s.off_cum + al((long long)Tsym * rows * 16);
     // tensor-core regime: hidden states once more as ready-made B operand tiles of the weight-gradient kernel

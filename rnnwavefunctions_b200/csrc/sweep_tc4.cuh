@@ -467,7 +467,8 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
             hv[e] = live ? fmaf(u, ht - mv, mv) : 0.f;
             if (save) {
               const int j = j0 + e;
-              if (j < nh) P.sv_gates[((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * P.Gp + j] = make_float4(u, ht, mv, 0.f);
+              // tile-blocked [cell][tile][unit][row 128]: a warp's 32 rows are 512 contiguous bytes (read back the same way by bwd4_kernel)
+              if (j < nh) P.sv_gates[(((size_t)q * (size_t)((P.sv_rows + T4_ROWS - 1) / T4_ROWS) + (size_t)tile) * P.Gp + j) * T4_ROWS + row] = make_float4(u, ht, mv, 0.f);
               if (j < nhp) P.sv_hist[((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + j] = hv[e];
             }
           }
