@@ -469,8 +469,13 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
               const int j = j0 + e;
               // tile-blocked [cell][tile][unit][row 128]: a warp's 32 rows are 512 contiguous bytes (read back the same way by bwd4_kernel)
               if (j < nh) P.sv_gates[(((size_t)q * (size_t)((P.sv_rows + T4_ROWS - 1) / T4_ROWS) + (size_t)tile) * P.Gp + j) * T4_ROWS + row] = make_float4(u, ht, mv, 0.f);
-              if (j < nhp) P.sv_hist[((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + j] = hv[e];
             }
+          }
+          if (save) {        // saved history (row-major, prefix reuse gathers whole rows): four 16-byte stores per pass
+            float* hrow = P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + j0;
+#pragma unroll
+            for (int e = 0; e < 16; e += 4)
+              if (j0 + e < nhp) *reinterpret_cast<float4*>(hrow + e) = make_float4(hv[e], hv[e + 1], hv[e + 2], hv[e + 3]);
           }
           *reinterpret_cast<uint4*>(ring_q + (size_t)p * T4_A_BYTES) =
               make_uint4(pack_f16x2(hv[0], hv[1]), pack_f16x2(hv[2], hv[3]), pack_f16x2(hv[4], hv[5]), pack_f16x2(hv[6], hv[7]));
