@@ -33,6 +33,7 @@ def main():
     ap.add_argument("--trace", type=int, default=0, help="print this many events of CTA 0's timeline (M: MMA 1 pass start / 2 pass "
                     "issued; L: loader 10+4c wait for ring chunk c / 11+4c got it; E: epilogue 20+p accumulators ready / 30+p chunk released / 40 pass done)")
     ap.add_argument("--trace-from", type=int, default=300000)
+    ap.add_argument("--debug-flags", type=int, nargs="*", default=[], help="also time E_loc with RNNWF_TC_DEBUG set to each of these")
     a = ap.parse_args()
     eng = Engine(_lib.CELL_GRU4, a.nx, a.ny, num_units=a.nh, precision="tc")
     saved = eng.new_saved(a.ns)
@@ -48,7 +49,7 @@ def main():
     e1.record()
     torch.cuda.synchronize()
     print(f"eloc {e0.elapsed_time(e1) / 3:.3f} ms")
-    for flags in ():          # timing experiments: halve the weight stream / the hidden-state stream / both
+    for flags in a.debug_flags:          # timing experiments (results invalid): bit 0 halves the weight stream, bit 1 the hidden-state stream
         os.environ["RNNWF_TC_DEBUG"] = str(flags)
         eloc()
         torch.cuda.synchronize()
