@@ -500,8 +500,11 @@ def main():
         per_sample = 3 * float(suffix.sum()) if V.prefix_reuse else 3 * T * float(suffix[0])
         exec_flops = ns * per_sample
         achieved = exec_flops / (eloc_ms * 1e-3) / 1e12
+        # traffic: dram__bytes_read.sum + dram__bytes_write.sum of this kernel from the committed ncu --set full capture
+        # (profiles/r1h_c5_summary.md), valid for the 4x4-cell / 12 500-sample workload it was taken on
+        traffic = 8.31e9 if (nx == 4 and ny == 4 and nh == 256 and ns == 12500) else None
         roofline = {"bound": "tensor", "kernel": "sweep_tc4_kernel (MODE_CHILD)", "achieved": achieved, "peak": bf16_peak, "unit": "TFLOP/s",
-                    "frac": achieved / bf16_peak, "traffic": None,
+                    "frac": achieved / bf16_peak, "traffic": traffic, "traffic_source": "profiles/r1h_c5_summary.md (ncu --set full, one launch)" if traffic else None,
                     "peak_source": ("MEASURED_PEAKS.json bf16_tflops_sustained (16-bit tensor peak, kernel timed inside a long step)"
                                     if peaks else "fallback 1400 (B200_PROFILING.md)"),
                     "executed_flops_per_launch": exec_flops, "algorithmic_flops_per_launch": alg_flops,
@@ -519,8 +522,11 @@ def main():
             ncols = 112                                                       # one pass per site: 7 unit pieces x 4 threads x 4 units
         exec_flops = exec_sites * (2 * (2 * nhp) * ncols + 2 * w["eng"]["num_units"] * 4)
         achieved = exec_flops / (eloc_ms * 1e-3) / 1e12
+        # traffic: dram bytes read + written by this kernel in the committed ncu --set full capture (profiles/r1e_summary.md:
+        # 5.17 GB + 12.33 GB, write-back of the history ring), valid for the C4 triangular workload it was taken on
+        traffic = 17.5e9 if args.workload == DEFAULT_WORKLOAD else None
         roofline = {"bound": "tensor", "kernel": "sweep_tc_kernel (MODE_CHILD)", "achieved": achieved, "peak": bf16_peak, "unit": "TFLOP/s",
-                    "frac": achieved / bf16_peak, "traffic": None,
+                    "frac": achieved / bf16_peak, "traffic": traffic, "traffic_source": "profiles/r1e_summary.md (ncu --set full, one launch)" if traffic else None,
                     "peak_source": ("MEASURED_PEAKS.json bf16_tflops_sustained (16-bit tensor peak, kernel timed inside a long step)"
                                     if peaks else "fallback 1400 (B200_PROFILING.md)"),
                     "executed_flops_per_launch": exec_flops, "algorithmic_flops_per_launch": alg_flops,
