@@ -402,7 +402,9 @@ __global__ void scatter_gru4_kernel(const BwdStep S, const float* __restrict__ d
   const int i = (int)(idx - row * nh4);
   const int slot = i / S.nh, k = i - slot * S.nh;
   if (S.nbr[slot] < 0) return;
-  S.dh[((long long)S.nbr[slot] * S.R + row) * S.nhp + k] += dz[row * Kz + 24 + i];
+  // atomic: on lattices with Lx <= 2 or Ly <= 2 two slots of a cell name the same neighbour (its periodic successor is its
+  // predecessor), i.e. two threads add into the same element
+  atomicAdd(&S.dh[((long long)S.nbr[slot] * S.R + row) * S.nhp + k], dz[row * Kz + 24 + i]);
 }
 
 // one-hot inputs of the two-neighbour / chain models: X[row][2*slot + v]

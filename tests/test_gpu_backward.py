@@ -19,6 +19,10 @@ MODELS = {
     "tensgru2d_u1": dict(cell=_lib.CELL_TENSGRU2D, nx=4, ny=4, num_units=20, complex_head=True, u1=True),
     "tensgru2d_free": dict(cell=_lib.CELL_TENSGRU2D, nx=3, ny=4, num_units=9, complex_head=True),
     "rydberg": dict(cell=_lib.CELL_GRU4, nx=3, ny=3, num_units=24),
+    # periodic lattices two cells wide: a cell's successor is its predecessor, two neighbour slots name the same cell and
+    # both push their input gradient into it (a non-atomic scatter lost one of the two)
+    "rydberg_2x2": dict(cell=_lib.CELL_GRU4, nx=2, ny=2, num_units=24),
+    "rydberg_1x2": dict(cell=_lib.CELL_GRU4, nx=1, ny=2, num_units=16),
 }
 
 

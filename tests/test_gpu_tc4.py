@@ -123,3 +123,33 @@ def test_tc4_large_lattice_matches_fp32_regime(cuda):
     e32 = f32.local_energies(_lib.HAM_RYDBERG, HAM, s, lp32, ph32).cpu().numpy().real
     np.testing.assert_allclose(e, e32, rtol=2e-3, atol=2e-3 * np.abs(e32).max())
     np.testing.assert_allclose(e_noreuse, e, rtol=1e-4, atol=1e-4 * np.abs(e).max())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nx,ny", [(1, 1), (1, 2), (2, 1), (1, 5)])
+def test_tc4_degenerate_lattices(cuda, nx, ny):
+    """Single cells and chains of cells: sites with no neighbour at all (only the input / bias job runs) and lattices whose
+    periodic successor is the predecessor; sampling, teacher forcing, prefix-reuse local energies and the gradient from a
+    teacher-forced saved state, against the FP32 regime on the same weights."""
+    nh, ns = 40, 200
+    eng = _mk(nx, ny, nh, seed=111)
+    f32 = Engine(_lib.CELL_GRU4, nx, ny, num_units=nh, seed=111)
+    f32.set_weights(eng.params)
+    u = torch.rand(ns, eng.nsteps, generator=torch.Generator().manual_seed(3), dtype=torch.float32)
+    s, lp, ph = eng.sample(ns, uniforms=u)
+    s32, lp32, ph32 = f32.sample(ns, uniforms=u)
+    same = (s == s32).reshape(ns, -1).all(dim=1).cpu().numpy()
+    assert same.mean() > 0.9
+    np.testing.assert_allclose(lp.cpu().numpy()[same], lp32.cpu().numpy()[same], rtol=RTOL, atol=1e-3)
+    saved = eng.new_saved(ns)
+    lp2, ph2 = eng.logpsi(s, saved=saved)           # teacher forcing writes the saved state the backward consumes
+    np.testing.assert_allclose(lp2.cpu().numpy(), lp.cpu().numpy(), rtol=1e-12, atol=1e-12)
+    e = eng.local_energies(_lib.HAM_RYDBERG, HAM, s, lp2, ph2, saved=saved).cpu().numpy().real
+    sv32 = f32.new_saved(ns)
+    lp3, ph3 = f32.logpsi(s, saved=sv32)
+    e32 = f32.local_energies(_lib.HAM_RYDBERG, HAM, s, lp3, ph3, saved=sv32).cpu().numpy().real
+    np.testing.assert_allclose(e, e32, rtol=2e-3, atol=2e-3 * np.abs(e32).max())
+    seeds = costs.seeds_real(torch.randn(ns, generator=torch.Generator().manual_seed(4), dtype=torch.float64))
+    ga, gb = eng.backward(s, saved, seeds).cpu(), f32.backward(s, sv32, seeds).cpu()
+    for (n, a), (_, b) in zip(eng.views(ga).items(), f32.views(gb).items()):
+        assert float((a - b).abs().max()) <= 1e-2 * float(b.abs().max()) + 1e-30, f"gradient of {n} differs from the FP32 regime"
