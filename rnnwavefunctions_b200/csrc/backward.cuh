@@ -690,7 +690,7 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
       if (van) {
         D.gW = nullptr; D.gWg = nullptr; D.gM0 = Gd("Wh"); D.gM1 = Gd("Wv");
         D.slab[0] = D.slab[1] = D.slab[2] = 0;
-        RNNWF_COUNT_LAUNCH(); dw_tc_kernel<<<(unsigned)njobs, DW_THREADS, dw_smem_bytes(nhp), st>>>(D);
+        if (njobs > 0) { RNNWF_COUNT_LAUNCH(); dw_tc_kernel<<<(unsigned)njobs, DW_THREADS, dw_smem_bytes(nhp), st>>>(D); }   // (a single-site lattice has no neighbour weights)
         RNNWF_COUNT_LAUNCH(); vanilla_input_grads_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, m.d_steps, m.d_site_of_t, cfg, m.Q, tiles, R, nh, nhp,
                                                                                           m.nsites, Gd("b"), Gd("Uh"), Gd("Uv"));
       } else {
@@ -698,7 +698,7 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
         D.gW = Gd("W"); D.gWg = gated ? Gd("Wg") : nullptr;
         D.gM0 = gated ? Gd("Wmerge") : nullptr; D.gM1 = gated ? Gd("Wmerge") + (long long)nh * nh : nullptr;
         D.slab[0] = 0; D.slab[1] = 1; D.slab[2] = 2;
-        RNNWF_COUNT_LAUNCH(); dw_tc_kernel<<<(unsigned)njobs, DW_THREADS, dw_smem_bytes(nhp), st>>>(D);
+        if (njobs > 0) { RNNWF_COUNT_LAUNCH(); dw_tc_kernel<<<(unsigned)njobs, DW_THREADS, dw_smem_bytes(nhp), st>>>(D); }   // (a single-site lattice has no neighbour weights)
         RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, 0, m.Q, tiles, nhp, nsplit, Gd("b"));
         if (gated) { RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, 1, m.Q, tiles, nhp, nsplit, Gd("bg")); }
       }
