@@ -153,3 +153,21 @@ def test_tc4_degenerate_lattices(cuda, nx, ny):
     ga, gb = eng.backward(s, saved, seeds).cpu(), f32.backward(s, sv32, seeds).cpu()
     for (n, a), (_, b) in zip(eng.views(ga).items(), f32.views(gb).items()):
         assert float((a - b).abs().max()) <= 1e-2 * float(b.abs().max()) + 1e-30, f"gradient of {n} differs from the FP32 regime"
+
+
+@pytest.mark.gpu
+def test_tc4_local_energies_more_tiles_than_sms(cuda):
+    """Every persistent CTA walks several tiles of connected configurations (317 tiles of 128 rows), each restarting from
+    its parents' saved history at a different cell: against the FP32 regime on the same samples."""
+    nx, ny, nh, ns = 3, 3, 64, 1500
+    eng = _mk(nx, ny, nh, seed=121)
+    f32 = Engine(_lib.CELL_GRU4, nx, ny, num_units=nh, seed=121)
+    f32.set_weights(eng.params)
+    saved = eng.new_saved(ns)
+    s, lp, ph = eng.sample(ns, seed=11, row_offset=0, saved=saved)
+    e = eng.local_energies(_lib.HAM_RYDBERG, HAM, s, lp, ph, saved=saved).cpu().numpy().real
+    sv32 = f32.new_saved(ns)
+    lp32, ph32 = f32.logpsi(s, saved=sv32)
+    e32 = f32.local_energies(_lib.HAM_RYDBERG, HAM, s, lp32, ph32, saved=sv32).cpu().numpy().real
+    np.testing.assert_allclose(e, e32, rtol=2e-3, atol=2e-3 * np.abs(e32).max())
+    assert abs(e.mean() - e32.mean()) < 2e-4 * abs(e32.mean())
