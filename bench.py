@@ -129,6 +129,14 @@ class ClockSampler:
                 phys = int(vis.split(",")[gpu_index]) if vis and vis.split(",")[gpu_index].strip().isdigit() else gpu_index
                 self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
             self.nvml = pynvml
+            # the first queries initialise NVML lazily (hundreds of ms, under a driver lock that kernel launches also take):
+            # make them here, before the warm-up steps, not inside the timed region
+            pynvml.nvmlDeviceGetClockInfo(self.handle, pynvml.NVML_CLOCK_SM)
+            pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM)
+            try:
+                pynvml.nvmlDeviceGetCurrentClocksEventReasons(self.handle)
+            except Exception:
+                pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
         except Exception:
             self.nvml = None
 
@@ -416,12 +424,12 @@ def main():
         V.it += 1
         return (e0, e1, e2, e3), cnt, s
 
+    # rank 0 alone samples the clocks (of its own GPU); the sampler is set up (NVML initialised) before the warm-up steps
+    clocks = ClockSampler(local_rank) if rank == 0 else None
     for _ in range(args.warmup):
         step_resident(False)
     barrier()
     launches0 = _lib.lib.rnnwf_launch_count()
-    # rank 0 alone samples the clocks (of its own GPU)
-    clocks = ClockSampler(local_rank) if rank == 0 else None
     if clocks is not None:
         clocks.start()
     t_start, t_end = ev(), ev()
