@@ -171,3 +171,27 @@ def test_tc4_local_energies_more_tiles_than_sms(cuda):
     e32 = f32.local_energies(_lib.HAM_RYDBERG, HAM, s, lp32, ph32, saved=sv32).cpu().numpy().real
     np.testing.assert_allclose(e, e32, rtol=2e-3, atol=2e-3 * np.abs(e32).max())
     assert abs(e.mean() - e32.mean()) < 2e-4 * abs(e32.mean())
+
+
+@pytest.mark.gpu
+def test_tc4_training_tracks_the_fp32_regime(cuda):
+    """End to end (north_star: 'variational energies agree within statistical error after equal training steps'): the same
+    VMC run -- 3x3 Kagome cells, same Philox seeds, TF-Adam -- in both precision regimes.  The first step sees identical
+    weights (energies agree to 1e-3); afterwards both trajectories descend and stay statistically equivalent."""
+    from rnnwavefunctions_b200 import vmc
+    out = {}
+    for prec in ("fp32", "tc"):
+        eng = Engine(_lib.CELL_GRU4, 3, 3, num_units=32, seed=5, precision=prec)
+        eng.init_params(seed=5)
+        v = vmc.VMC(eng, _lib.HAM_RYDBERG, HAM, 512, lr=5e-3, seed=21)
+        es = []
+        for it in range(60):
+            mean_e, var = v.step()
+            es.append(float(mean_e.real))
+        out[prec] = np.array(es)
+    a, b = out["fp32"], out["tc"]
+    assert abs(a[0] - b[0]) < 1e-3 * abs(a[0])
+    assert np.isfinite(b).all()
+    assert a[-10:].mean() < a[:3].mean() and b[-10:].mean() < b[:3].mean()
+    spread = max(a[-10:].std(), b[-10:].std(), 1e-3 * abs(a[-10:].mean()))
+    assert abs(a[-10:].mean() - b[-10:].mean()) < 4 * spread + 0.02 * abs(a[-10:].mean())
