@@ -271,13 +271,15 @@ def regularized_identity(x, eps=1e-4):
 
 
 def log_amplitudes_from_symmetry_group(logp_g, phase_g, characters):
-    """2DHeisenberg/MDComplexRNN.py:290-316. logp_g, phase_g: [G,B]; characters: [G] of +-1.
-    Returns complex log-amplitude [B]."""
+    """2DHeisenberg/MDComplexRNN.py:290-316. logp_g, phase_g: [G,B]; characters: list of +-1.
+    Returns complex log-amplitude [B].  As upstream (:313), the phase sum runs over range(len(characters)) -- normally G;
+    see `heis_symmetry_copies(legacy_list_bug=True)` for the one case where the reference passes fewer."""
     G = logp_g.shape[0]
-    ch = torch.as_tensor(characters, dtype=F64).reshape(G, 1)
+    Gc = len(characters)
+    ch = torch.as_tensor(characters, dtype=F64).reshape(Gc, 1)
     logp = torch.log(torch.exp(logp_g).sum(0) / G)
-    re = (torch.cos(phase_g) / ch).sum(0)
-    im = (torch.sin(phase_g) / ch).sum(0)
+    re = (torch.cos(phase_g[:Gc]) / ch).sum(0)
+    im = (torch.sin(phase_g[:Gc]) / ch).sum(0)
     ph = torch.atan2(im, regularized_identity(re))
     return torch.complex(0.5 * logp, ph)
 
@@ -292,3 +294,69 @@ def rotate60(samples):
             out[:, i, j, 1] = samples[:, (i + j) % Lx, (Ly - i) % Ly, 2]
             out[:, i, j, 2] = samples[:, (i + j + 1) % Lx, (Ly - (i + 1)) % Ly, 0]
     return out
+
+
+# group elements in the order the reference appends them to list_samples, and the character tables
+# (2DHeisenberg/MDComplexRNN.py: rotsym :320-333, rotsym_spinparity :335-356, rotreducedsym(_spinparity) :358-389,
+#  c2vsym :391-408, c2v_spinparity :410-435, c2sym(_spinparity) :438-469, c2dsym(_spinparity) :471-518,
+#  c4vsym(_spinparity) :520-577).  tf.image.rot90(k) on [b, Nx, Ny, 1] == np.rot90(k, axes=(1, 2)).
+def _rot(k):
+    return lambda s: torch.rot90(s, k, dims=(1, 2))
+
+
+HEIS_GROUP_OPS = {
+    "id": lambda s: s, "r1": _rot(-1), "r2": _rot(-2), "r3": _rot(-3),
+    "fx": lambda s: torch.flip(s, dims=[1]), "fy": lambda s: torch.flip(s, dims=[2]),
+    "t": lambda s: s.transpose(1, 2), "tr2": lambda s: torch.rot90(s, -2, dims=(1, 2)).transpose(1, 2),
+}
+_C2V_TABLE = {"A1": [1, 1, 1, 1], "A2": [1, 1, -1, -1], "B1": [1, -1, 1, -1], "B2": [1, -1, -1, 1]}
+HEIS_GROUPS = {
+    "rotsym": (["id", "r1", "r2", "r3"], {"A": [1, 1, 1, 1], "B": [1, -1, 1, -1]}),
+    "rotreducedsym": (["id", "r1"], {"A": [1, 1], "B": [1, -1]}),
+    "c2sym": (["id", "r2"], {"A": [1, 1], "B": [1, -1]}),
+    "c2vsym": (["id", "r2", "fx", "fy"], _C2V_TABLE),
+    "c2dsym": (["id", "r2", "t", "tr2"], _C2V_TABLE),
+    "c4vsym": (["id", "r1", "r2", "r3", "fx", "fy", "t", "tr2"],
+               {"A1": [1] * 8, "A2": [1, 1, 1, 1, -1, -1, -1, -1], "B1": [1, -1, 1, -1, 1, 1, -1, -1],
+                "B2": [1, -1, 1, -1, -1, -1, 1, 1]}),
+}
+
+
+def heis_symmetry_copies(samples, group, group_character, spinparity_value=None, legacy_list_bug=False):
+    """-> (list of transformed configurations [B,Nx,Ny], list of character signs).  With a spin parity the spin-flipped
+    copies 1 - s follow in the same order with signs spinparity_value * chi (e.g. :343-346, :354).
+
+    Reference defect reproduced only on request (`legacy_list_bug=True`, used to check the fixtures): every spin-parity
+    variant except c4vsym keeps chi as a Python *list*, so `spinparity_value*group_character_signs` (:354, :373, :433,
+    :453, :516) is list repetition -- for spinparity_value = -1 it is the empty list, and the phase sum of
+    log_amplitudes_fromsymmetrygroup then runs over the un-flipped copies only (the amplitude still averages all 2G).
+    c4vsym_spinparity uses np.array (:566-575) and multiplies as intended.  The product implements the intended signs."""
+    ops, table = HEIS_GROUPS[group]
+    lst = [HEIS_GROUP_OPS[o](samples) for o in ops]
+    signs = list(table[group_character])
+    if spinparity_value is not None:
+        lst += [HEIS_GROUP_OPS[o](1 - samples) for o in ops]
+        if legacy_list_bug and group != "c4vsym":
+            signs = signs + int(spinparity_value) * signs          # list repetition, as upstream
+        else:
+            signs = signs + [spinparity_value * c for c in signs]
+    return lst, signs
+
+
+def rydberg_symmetry_copies(samples, symmetry):
+    """RydbergKagome_2DGRU/MDRNNWavefunction.py:246-263: the six 60-degree rotations, or all Lx*Ly translations
+    (tf.roll by (rx, ry) along the cell axes, rx outer)."""
+    if symmetry == "c6sym":
+        lst = [samples]
+        for _ in range(5):
+            lst.append(rotate60(lst[-1]))
+        return lst
+    if symmetry == "translationsym":
+        _, Lx, Ly, _ = samples.shape
+        return [torch.roll(samples, shifts=(rx, ry), dims=(1, 2)) for rx in range(Lx) for ry in range(Ly)]
+    raise ValueError(symmetry)
+
+
+def log_probability_symmetry(logp_g):
+    """RydbergKagome_2DGRU/MDRNNWavefunction.py:275-279: log(mean_g P_g); logp_g [G,B]."""
+    return torch.log(torch.exp(logp_g).sum(0) / logp_g.shape[0])
