@@ -171,6 +171,32 @@ int rnnwf_symmetry_seeds(int G, int64_t rows, const double* logp_dev, const doub
                          const double* s_logp_dev, const double* s_phase_dev, double* seed_logp_dev, double* seed_phase_dev,
                          void* stream);
 
+/* The symmetry group as device-resident index-remap tables, built once per (wavefunction, group): element g maps a
+ * configuration s to  s_g[i] = s[perm[g][i]] ^ flip[g]  -- tf.image.rot90 / [:, ::-1] / transpose / abs(1 - s) of
+ * 2DHeisenberg/MDComplexRNN.py:320-577, rotate60 and tf.roll of RydbergKagome_2DGRU/MDRNNWavefunction.py:246-291, the chain
+ * reversal of 1DTFIM/RNNwavefunction_paritysym.py:125.  perm: host int32 [G][nsites] in the configuration's array layout
+ * (each row a permutation), flip: host int8 [G] or NULL, chi: host double [G] group characters or NULL (all 1; also used
+ * for the positive wavefunctions).  G <= 64. */
+typedef struct rnnwf_symmetry* rnnwf_symmetry_handle;
+int rnnwf_symmetry_create(rnnwf_handle h, int G, const int32_t* perm, const int8_t* flip, const double* chi, rnnwf_symmetry_handle* out);
+int rnnwf_symmetry_destroy(rnnwf_symmetry_handle s);
+int rnnwf_symmetry_order(rnnwf_symmetry_handle s);
+/* list_samples of the reference's symmetric methods, formed on the device: out_dev int8 [G][rows][nsites] (copy-major, the
+ * layout rnnwf_symmetry_epilogue / rnnwf_symmetry_seeds take after one rnnwf_logpsi over G*rows configurations). */
+int rnnwf_symmetry_apply(rnnwf_symmetry_handle s, int64_t rows, const int8_t* in_dev, int8_t* out_dev, void* stream);
+/* Local energies of a symmetry-projected wavefunction: Get_Elocs(..., RNN_symmetry != "nosym")
+ * (2DHeisenberg/Helper_Functions.py:131-144,158-177 with log_amps = wf.log_amplitude_<group>), Rydberg_local_energies with
+ * log_probability_symmetry (RydbergKagome_2DGRU/Run_RNNWF_Rydberg.py:155,262), Ising_local_energies with the parity-symmetric
+ * log_probability (1DTFIM/RNNwavefunction_paritysym.py:122-145).  Enumerates the connected configurations on the device,
+ * forms the G copies of the samples and of every connected configuration through the remap tables, evaluates all of them in
+ * one batched sweep (full sweeps: a transformed copy shares no prefix with its parent), combines each group of G and
+ * reduces E_loc.  Also returns the symmetrised log psi of the samples (out_logp, out_phase; phase NULL for positive
+ * wavefunctions).  Same `ham` blocks and eloc / nconn outputs as rnnwf_local_energies. */
+int64_t rnnwf_eloc_sym_workspace_bytes(rnnwf_handle h, rnnwf_symmetry_handle s, int hamiltonian, int64_t rows);
+int rnnwf_local_energies_sym(rnnwf_handle h, rnnwf_symmetry_handle s, int hamiltonian, const double* ham, int ham_len, int64_t rows,
+                             const int8_t* samples_dev, double* out_logp_dev, double* out_phase_dev, double* eloc_dev,
+                             int64_t* nconn_dev, void* workspace_dev, int64_t workspace_bytes, void* stream);
+
 /* Kernel-regime report for the profiler notes: fills `buf` with a one-line description of the tile
  * shape / pipe (FFMA or tcgen05) the handle's sweeps run in. */
 int rnnwf_describe(rnnwf_handle h, char* buf, int cap);

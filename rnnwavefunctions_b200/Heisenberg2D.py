@@ -5,8 +5,9 @@ import numpy as np
 import torch
 
 from . import _lib
-from .compat import Handle, Placeholder, Session, find_wf, to_numpy
+from .compat import Handle, Placeholder, Session, find_wf, find_symmetry, to_numpy
 from .engine import Engine
+from .symmetry import HEIS_GROUPS, heisenberg_tables
 
 
 class MDTensorizedcell:
@@ -22,22 +23,7 @@ class MDTensorizedGRUcell:
 
 MDRNNcell = MDTensorizedGRUcell
 
-# group elements in the order the reference builds its sample lists (MDComplexRNN.py:320-577)
-_ROT = lambda k: (lambda s: torch.rot90(s, k, dims=(1, 2)))          # tf.image.rot90(k) == np.rot90(axes=(1,2))
-_OPS = {
-    "id": lambda s: s, "r1": _ROT(-1), "r2": _ROT(-2), "r3": _ROT(-3),
-    "fx": lambda s: torch.flip(s, dims=[1]), "fy": lambda s: torch.flip(s, dims=[2]),
-    "t": lambda s: s.transpose(1, 2), "tr2": lambda s: torch.rot90(s, -2, dims=(1, 2)).transpose(1, 2),
-}
-_GROUPS = {
-    "rotsym": (["id", "r1", "r2", "r3"], {"A": [1, 1, 1, 1], "B": [1, -1, 1, -1]}),
-    "rotreducedsym": (["id", "r1"], {"A": [1, 1], "B": [1, -1]}),
-    "c2sym": (["id", "r2"], {"A": [1, 1], "B": [1, -1]}),
-    "c2vsym": (["id", "r2", "fx", "fy"], {"A1": [1, 1, 1, 1], "A2": [1, 1, -1, -1], "B1": [1, -1, 1, -1], "B2": [1, -1, -1, 1]}),
-    "c2dsym": (["id", "r2", "t", "tr2"], {"A1": [1, 1, 1, 1], "A2": [1, 1, -1, -1], "B1": [1, -1, 1, -1], "B2": [1, -1, -1, 1]}),
-    "c4vsym": (["id", "r1", "r2", "r3", "fx", "fy", "t", "tr2"],
-               {"A1": [1] * 8, "A2": [1, 1, 1, 1, -1, -1, -1, -1], "B1": [1, -1, 1, -1, 1, 1, -1, -1], "B2": [1, -1, 1, -1, -1, -1, 1, 1]}),
-}
+_GROUPS = HEIS_GROUPS      # group elements / character tables in the reference's order (symmetry.py)
 
 
 def regularized_identity(x, epsilon=1e-4):
@@ -57,6 +43,15 @@ class RNNwavefunction:
         self.engine = Engine(cid, systemsize_x, systemsize_y, num_units=units[0], complex_head=True, u1=bool(mag_fixed),
                              magnetization=int(magnetization), seed=seed)
         self._step = 0
+        self._groups = {}
+
+    def symmetry_group(self, name, group_character, spinparity_value=None):
+        """Device remap tables of one of the reference's groups (MDComplexRNN.py:320-577), built once and cached."""
+        key = (name, group_character, spinparity_value)
+        if key not in self._groups:
+            perm, flip, chi = heisenberg_tables(self.Nx, self.Ny, name, group_character, spinparity_value)
+            self._groups[key] = self.engine.symmetry_group(perm, flip, chi)
+        return self._groups[key]
 
     def sample(self, numsamples, inputdim, uniforms=None, philox=None):
         """MDComplexRNN.py:80-173 -> int64 [numsamples, Nx, Ny]."""
@@ -92,16 +87,13 @@ class RNNwavefunction:
         return torch.complex(0.5 * logp, phase)
 
     def _sym(self, name, samples, inputdim, group_character, spinparity_value=None):
+        grp = self.symmetry_group(name, group_character, spinparity_value)
         if isinstance(samples, Placeholder):
-            return Handle(self, lambda s: self._sym(name, s, inputdim, group_character, spinparity_value), samples)
-        ops, table = _GROUPS[name]
-        s = torch.as_tensor(samples).to(self.engine.device)
-        lst = [_OPS[o](s) for o in ops]
-        signs = list(table[group_character])
-        if spinparity_value is not None:
-            lst = lst + [_OPS[o](1 - s) for o in ops]
-            signs = signs + [spinparity_value * c for c in signs]
-        return self.log_amplitudes_fromsymmetrygroup(lst, inputdim, signs)
+            return Handle(self, lambda s: self._sym(name, s, inputdim, group_character, spinparity_value), samples, symmetry=grp)
+        # the G copies are formed on the device through the group's index-remap tables, swept in one batch, and combined
+        # by the fused epilogue (amplitude sqrt(mean_g P_g), regularised character-weighted phase)
+        logp, phase, _, _, _ = self.engine.logpsi_sym(grp, torch.as_tensor(samples))
+        return torch.complex(0.5 * logp, phase)
 
 
 def _add_symmetry_methods():
@@ -158,10 +150,25 @@ def Get_Elocs(J2, Nx, Ny, samples, sigmas=None, H=None, log_amplitudes=None, sig
     """2DHeisenberg/Helper_Functions.py:152-177 -> complex128 ndarray [numsamples].  ``log_amps`` is the wavefunction
     or a handle from ``wf.log_amplitude_nosym(placeholder, 2)``; the scratch arrays are not needed."""
     wf = find_wf(log_amps, sess, inputs)
-    if RNN_symmetry != "nosym":
-        raise NotImplementedError("fused E_loc with symmetry-projected amplitudes: P2 row, not built yet")
-    e = wf.engine.local_energies(_lib.HAM_HEIS2D, [float(J2)], torch.as_tensor(to_numpy(samples)))
+    grp = _group_for(wf, log_amps, RNN_symmetry)
+    smp = torch.as_tensor(to_numpy(samples))
+    if grp is not None:
+        e = wf.engine.local_energies_sym(grp, _lib.HAM_HEIS2D, [float(J2)], smp)[0]
+    else:
+        e = wf.engine.local_energies(_lib.HAM_HEIS2D, [float(J2)], smp)
     return e.cpu().numpy()
+
+
+def _group_for(wf, log_amps, RNN_symmetry):
+    """The symmetry group the local energies must use: the one behind the handle `log_amps` (the reference passes the
+    tensor of wf.log_amplitude_<RNN_symmetry>, Run_RNNWF_2DHeis.py:153-197), cross-checked against the flag."""
+    grp = find_symmetry(log_amps)
+    if RNN_symmetry != "nosym" and grp is None:
+        raise ValueError(f"RNN_symmetry={RNN_symmetry!r}: pass the handle returned by wf.log_amplitude_{RNN_symmetry}"
+                         "(placeholder, inputdim, group_character[, spinparity_value]) as log_amps")
+    if RNN_symmetry == "nosym" and grp is not None:
+        raise ValueError("log_amps is a symmetry-projected amplitude but RNN_symmetry='nosym'")
+    return grp
 
 
 def Get_Samples_and_Elocs(J2, Nx, Ny, samples=None, sigmas=None, H=None, log_amplitudes=None, sigmaH=None, matrixelements=None,
@@ -169,10 +176,14 @@ def Get_Samples_and_Elocs(J2, Nx, Ny, samples=None, sigmas=None, H=None, log_amp
     """2DHeisenberg/Helper_Functions.py:123-150 -> (samples int64 ndarray, local_energies complex128 ndarray).
     Sampling, the saved hidden states and the connected-configuration sweep stay on the device in between."""
     wf = find_wf(log_amps, samples_tensor, sess)
-    if RNN_symmetry != "nosym":
-        raise NotImplementedError("fused E_loc with symmetry-projected amplitudes: P2 row, not built yet")
+    grp = _group_for(wf, log_amps, RNN_symmetry)
     ns = samples.shape[0] if samples is not None else samples_tensor.numsamples
     eng = wf.engine
+    if grp is not None:
+        s, _, _ = eng.sample(ns, seed=wf.seed, row_offset=wf._step * ns)
+        wf._step += 1
+        e = eng.local_energies_sym(grp, _lib.HAM_HEIS2D, [float(J2)], s)[0]
+        return s.long().cpu().numpy(), e.cpu().numpy()
     saved = eng.new_saved(ns)
     s, lp, ph = eng.sample(ns, seed=wf.seed, row_offset=wf._step * ns, saved=saved)
     wf._step += 1

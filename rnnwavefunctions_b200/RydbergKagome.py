@@ -6,8 +6,9 @@ import numpy as np
 import torch
 
 from . import _lib
-from .compat import Handle, Placeholder, Session, find_wf, to_numpy
+from .compat import Handle, Placeholder, Session, find_wf, find_symmetry, to_numpy
 from .engine import Engine
+from .symmetry import rydberg_tables
 
 
 class MDRNNcell:
@@ -47,6 +48,14 @@ class MDRNNWavefunction:
         self.Nx, self.Ny, self.N, self.scope, self.seed = systemsize_x, systemsize_y, systemsize_x * systemsize_y, scope, seed
         self.engine = Engine(_lib.CELL_GRU4, systemsize_x, systemsize_y, num_units=units[0], seed=seed)
         self._step = 0
+        self._groups = {}
+
+    def symmetry_group(self, symmetry):
+        """Device remap tables of the six rotate60 copies / all translations (MDRNNWavefunction.py:246-263), cached."""
+        if symmetry not in self._groups:
+            perm, _, _ = rydberg_tables(self.Nx, self.Ny, symmetry)
+            self._groups[symmetry] = self.engine.symmetry_group(perm)
+        return self._groups[symmetry]
 
     def sample(self, numsamples, inputdim, uniforms=None, philox=None):
         """MDRNNWavefunction.py:73-153 -> int64 [numsamples, Nx, Ny, 3]."""
@@ -68,22 +77,15 @@ class MDRNNWavefunction:
     def log_probability_symmetry(self, samples, inputdim=2, symmetry="nosym"):
         """MDRNNWavefunction.py:242-279: log(mean_g P_g) over the C6 rotations or all translations; ``"nosym"``
         (missing upstream) is the plain log-probability."""
-        if isinstance(samples, Placeholder):
-            return Handle(self, lambda s: self.log_probability_symmetry(s, inputdim, symmetry), samples)
-        s = torch.as_tensor(samples).to(self.engine.device)
-        if symmetry == "nosym":
-            return self.log_probability(s, inputdim)
-        if symmetry == "c6sym":
-            lst = [s]
-            for _ in range(5):
-                lst.append(rotate60(lst[-1]))
-        elif symmetry == "translationsym":
-            lst = [torch.roll(s, shifts=(rx, ry), dims=(1, 2)) for rx in range(self.Nx) for ry in range(self.Ny)]
-        else:
+        if symmetry not in ("nosym", "c6sym", "translationsym"):
             raise ValueError(symmetry)
-        G = len(lst)
-        lp = self.engine.logpsi(torch.cat(lst, dim=0))[0].view(G, -1)
-        return self.engine.symmetrize(lp)[0]             # fused device epilogue: log(mean_g P_g)
+        grp = None if symmetry == "nosym" else self.symmetry_group(symmetry)
+        if isinstance(samples, Placeholder):
+            return Handle(self, lambda s: self.log_probability_symmetry(s, inputdim, symmetry), samples, symmetry=grp)
+        s = torch.as_tensor(samples).to(self.engine.device)
+        if grp is None:
+            return self.log_probability(s, inputdim)
+        return self.engine.logpsi_sym(grp, s)[0]     # copies through the remap tables, one sweep, fused log(mean_g P_g)
 
 
 def generate_kagome(Nx, Ny):
@@ -122,6 +124,11 @@ def Rydberg_local_energies(V, delta, Omega, neighbours, distances, binary_sample
     wf = find_wf(log_probs_tensor, sess, samples_placeholder)
     if Rcutoff is None:
         Rcutoff = max(max(d) for d in distances if len(d)) + 1e-9
-    e = wf.engine.local_energies(_lib.HAM_RYDBERG, [float(V), float(delta), float(Omega), float(Rcutoff)],
-                                 torch.as_tensor(to_numpy(binary_samples)))
+    ham = [float(V), float(delta), float(Omega), float(Rcutoff)]
+    smp = torch.as_tensor(to_numpy(binary_samples))
+    grp = find_symmetry(log_probs_tensor)       # handle of wf.log_probability_symmetry(..., symmetry=RNN_symmetry): Run_RNNWF_Rydberg.py:155,262
+    if grp is not None:
+        e = wf.engine.local_energies_sym(grp, _lib.HAM_RYDBERG, ham, smp)[0]
+    else:
+        e = wf.engine.local_energies(_lib.HAM_RYDBERG, ham, smp)
     return e.real.cpu().numpy()

@@ -10,6 +10,7 @@ import torch
 from . import _lib
 from .compat import Handle, Placeholder, Session, find_wf, to_numpy
 from .engine import Engine
+from .symmetry import parity_tables
 from .vmc import VMC
 
 
@@ -48,15 +49,19 @@ class RNNwavefunction:
 
 
 class RNNwavefunction_paritysym(RNNwavefunction):
-    """1DTFIM/RNNwavefunction_paritysym.py:80-145: log(0.5*(P(s) + P(reversed s)))."""
+    """1DTFIM/RNNwavefunction_paritysym.py:80-145: log(0.5*(P(s) + P(reversed s))).  The mirror image is formed on the
+    device through a two-element remap table; both copies go through one sweep and the fused epilogue."""
+
+    def symmetry_group(self):
+        if getattr(self, "_parity", None) is None:
+            self._parity = self.engine.symmetry_group(parity_tables(self.N)[0])
+        return self._parity
 
     def log_probability(self, samples, inputdim):
+        grp = self.symmetry_group()
         if isinstance(samples, Placeholder):
-            return Handle(self, lambda s: self.log_probability(s, inputdim), samples)
-        s = torch.as_tensor(samples)
-        lp1 = self.engine.logpsi(s)[0]
-        lp2 = self.engine.logpsi(torch.flip(s, dims=[1]))[0]
-        return torch.logaddexp(lp1, lp2) - math.log(2.0)
+            return Handle(self, lambda s: self.log_probability(s, inputdim), samples, symmetry=grp)
+        return self.engine.logpsi_sym(grp, torch.as_tensor(samples))[0]
 
 
 def Ising_local_energies(Jz, Bx, samples, queue_samples=None, log_probs_tensor=None, samples_placeholder=None,
@@ -65,11 +70,12 @@ def Ising_local_energies(Jz, Bx, samples, queue_samples=None, log_probs_tensor=N
     returned by ``wf.log_probability(placeholder, 2)``) as ``log_probs_tensor``; the queue / log_probs scratch arrays
     of the reference are not needed (the connected configurations are enumerated and reduced on the device)."""
     wf = find_wf(log_probs_tensor, sess, samples_placeholder)
-    if isinstance(wf, RNNwavefunction_paritysym):
-        raise NotImplementedError("fused E_loc of the parity-symmetrised ansatz: P2 row, not built yet")
     N = wf.N
     ham = np.concatenate([[float(Bx)], np.asarray(Jz, dtype=np.float64).reshape(-1)[:max(1, N - 1)]])
-    e = wf.engine.local_energies(_lib.HAM_TFIM1D, ham, torch.as_tensor(to_numpy(samples)))
+    if isinstance(wf, RNNwavefunction_paritysym):
+        e = wf.engine.local_energies_sym(wf.symmetry_group(), _lib.HAM_TFIM1D, ham, torch.as_tensor(to_numpy(samples)))[0]
+    else:
+        e = wf.engine.local_energies(_lib.HAM_TFIM1D, ham, torch.as_tensor(to_numpy(samples)))
     return e.real.cpu().numpy()
 
 

@@ -50,6 +50,12 @@ def _load():
         "rnnwf_adam_step": (C.c_int, [vp, vp, vp, vp, i64, C.c_double, C.c_double, C.c_double, C.c_double, i64, C.c_double, vp]),
         "rnnwf_symmetry_epilogue": (C.c_int, [C.c_int, i64, vp, vp, C.POINTER(C.c_double), vp, vp, vp]),
         "rnnwf_symmetry_seeds": (C.c_int, [C.c_int, i64, vp, vp, C.POINTER(C.c_double), vp, vp, vp, vp, vp]),
+        "rnnwf_symmetry_create": (C.c_int, [vp, C.c_int, C.POINTER(i32), C.POINTER(C.c_int8), C.POINTER(C.c_double), C.POINTER(vp)]),
+        "rnnwf_symmetry_destroy": (C.c_int, [vp]),
+        "rnnwf_symmetry_order": (C.c_int, [vp]),
+        "rnnwf_symmetry_apply": (C.c_int, [vp, i64, vp, vp, vp]),
+        "rnnwf_eloc_sym_workspace_bytes": (i64, [vp, vp, C.c_int, i64]),
+        "rnnwf_local_energies_sym": (C.c_int, [vp, vp, C.c_int, C.POINTER(C.c_double), C.c_int, i64, vp, vp, vp, vp, vp, vp, i64, vp]),
         "rnnwf_describe": (C.c_int, [vp, C.c_char_p, C.c_int]),
         "rnnwf_launch_count": (C.c_longlong, []),
         "rnnwf_ffma_probe": (C.c_int, [vp, C.c_int, C.c_int, vp]),

@@ -23,8 +23,9 @@ def placeholder(dtype=None, shape=None, name=None):
 class Handle:
     """A deferred wavefunction call: fn(samples) -> tensor."""
 
-    def __init__(self, wf, fn, placeholder=None, kind="log"):
+    def __init__(self, wf, fn, placeholder=None, kind="log", symmetry=None):
         self.wf, self.fn, self.placeholder, self.kind = wf, fn, placeholder, kind
+        self.symmetry = symmetry      # engine.SymmetryGroup when the call is a symmetry-projected amplitude, else None
 
     def __call__(self, samples):
         return self.fn(samples)
@@ -56,6 +57,16 @@ def find_wf(*candidates):
             return c
     raise TypeError("pass the wavefunction (or a handle returned by one of its methods) where the reference "
                     "takes log_probs_tensor / log_amps / sess")
+
+
+def find_symmetry(*candidates):
+    """The SymmetryGroup behind a handle of a symmetric wavefunction method (None for the plain amplitudes).  The
+    reference hands its local-energy functions the tensor of whichever method was chosen
+    (Run_RNNWF_2DHeis.py:153-197, Run_RNNWF_Rydberg.py:155); the handle carries the same choice here."""
+    for c in candidates:
+        if isinstance(c, Handle):
+            return c.symmetry
+    return None
 
 
 def to_numpy(x):

@@ -802,20 +802,14 @@ int64_t rnnwf_eloc_workspace_bytes(rnnwf_handle h, int hamiltonian, int64_t rows
   return eloc_layout(*h, hamiltonian, rows).total;
 }
 
-int rnnwf_local_energies(rnnwf_handle h, int hamiltonian, const double* ham, int ham_len, int64_t rows,
-                         const int8_t* samples_dev, const double* logp_dev, const double* phase_dev,
-                         const void* saved_dev, double* eloc_dev, int64_t* nconn_dev, void* workspace_dev,
-                         int64_t workspace_bytes, void* stream) {
-  int rc = check_ready(h);
-  if (rc) return rc;
-  if (rows <= 0 || samples_dev == nullptr || logp_dev == nullptr || eloc_dev == nullptr || ham == nullptr)
-    return fail(RNNWF_EINVAL, "rnnwf_local_energies: null argument or rows <= 0");
-  if (rows > 0x7fffffffLL) return fail(RNNWF_EINVAL, "rnnwf_local_energies: too many rows");
-  const rnnwf_model& m = *h;
-  const ElocLayout L = eloc_layout(m, hamiltonian, rows);
-  if (workspace_dev == nullptr || workspace_bytes < L.total) return fail(RNNWF_ENOMEM, "rnnwf_local_energies: workspace too small");
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  char* ws = static_cast<char*>(workspace_dev);
+namespace {
+struct EnumOut { long long nchild_fixed = 0; const int* rows_dev = nullptr; bool have_children = true; };
+
+// Diagonal matrix elements into eloc_dev and the list of connected configurations (Child records, ordered by first
+// changed generation step) into the workspace -- shared by rnnwf_local_energies and rnnwf_local_energies_sym.
+int enumerate_connected(const rnnwf_model& m, int hamiltonian, const double* ham, int ham_len, long long rows,
+                        const int8_t* samples_dev, double* eloc_dev, char* ws, const ElocLayout& L, cudaStream_t st, EnumOut& out) {
+  int rc;
   double* d_ham = reinterpret_cast<double*>(ws + L.off_ham);
   Bond* d_bonds = reinterpret_cast<Bond*>(ws + L.off_bonds);
   int* d_bstart = reinterpret_cast<int*>(ws + L.off_bstart);
@@ -949,17 +943,39 @@ int rnnwf_local_energies(rnnwf_handle h, int hamiltonian, const double* ham, int
       return fail(RNNWF_EINVAL, "unknown hamiltonian");
   }
   CUDA_TRY(cudaGetLastError());
+  out.nchild_fixed = nchild_fixed; out.rows_dev = rows_dev; out.have_children = have_children;
+  return RNNWF_OK;
+}
+}  // namespace
+
+int rnnwf_local_energies(rnnwf_handle h, int hamiltonian, const double* ham, int ham_len, int64_t rows,
+                         const int8_t* samples_dev, const double* logp_dev, const double* phase_dev,
+                         const void* saved_dev, double* eloc_dev, int64_t* nconn_dev, void* workspace_dev,
+                         int64_t workspace_bytes, void* stream) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (rows <= 0 || samples_dev == nullptr || logp_dev == nullptr || eloc_dev == nullptr || ham == nullptr)
+    return fail(RNNWF_EINVAL, "rnnwf_local_energies: null argument or rows <= 0");
+  if (rows > 0x7fffffffLL) return fail(RNNWF_EINVAL, "rnnwf_local_energies: too many rows");
+  const rnnwf_model& m = *h;
+  const ElocLayout L = eloc_layout(m, hamiltonian, rows);
+  if (workspace_dev == nullptr || workspace_bytes < L.total) return fail(RNNWF_ENOMEM, "rnnwf_local_energies: workspace too small");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  char* ws = static_cast<char*>(workspace_dev);
+  EnumOut en;
+  if ((rc = enumerate_connected(m, hamiltonian, ham, ham_len, rows, samples_dev, eloc_dev, ws, L, st, en))) return rc;
+  Child* d_children = reinterpret_cast<Child*>(ws + L.off_children);
   if (nconn_dev != nullptr) {
     // connected configurations evaluated (+ the diagonal one per sample, already known from `logp`)
-    RNNWF_COUNT_LAUNCH(); count_children_kernel<<<1, 32, 0, st>>>(have_children ? rows_dev : nullptr, have_children ? (rows_dev ? 0 : nchild_fixed) : 0, (long long*)nconn_dev);
+    RNNWF_COUNT_LAUNCH(); count_children_kernel<<<1, 32, 0, st>>>(en.have_children ? en.rows_dev : nullptr, en.have_children ? (en.rows_dev ? 0 : en.nchild_fixed) : 0, (long long*)nconn_dev);
   }
-  if (!have_children) return RNNWF_OK;
+  if (!en.have_children) return RNNWF_OK;
 
   LaunchShape s;
-  if ((rc = pick_shape(m, nchild_fixed, s))) return rc;
+  if ((rc = pick_shape(m, en.nchild_fixed, s))) return rc;
   SweepParams P;
   fill_model_params(m, s, P);
-  P.mode = MODE_CHILD; P.rows = nchild_fixed; P.rows_dev = rows_dev; P.cfg_in = samples_dev; P.children = d_children;
+  P.mode = MODE_CHILD; P.rows = en.nchild_fixed; P.rows_dev = en.rows_dev; P.cfg_in = samples_dev; P.children = d_children;
   P.par_logp = logp_dev; P.par_phase = phase_dev; P.eloc = eloc_dev;
   P.ring = reinterpret_cast<float*>(ws + L.off_ring);
   if (saved_dev != nullptr) {
@@ -1090,6 +1106,151 @@ int rnnwf_symmetry_seeds(int G, int64_t rows, const double* logp_dev, const doub
   RNNWF_COUNT_LAUNCH();
   symmetry_seeds_kernel<<<std::min(1184, cdiv(rows, 256)), 256, 0, static_cast<cudaStream_t>(stream)>>>(G, rows, logp_dev, phase_dev, ch, s_logp_dev, s_phase_dev,
                                                                                                       seed_logp_dev, seed_phase_dev);
+  CUDA_TRY(cudaGetLastError());
+  return RNNWF_OK;
+}
+
+// ---- symmetry groups as device-resident index-remap tables ------------------------------------------------
+}  // extern "C" (reopened below)
+
+struct rnnwf_symmetry {
+  int G = 0, nsites = 0, bits = 1, device = 0;
+  int32_t* d_perm = nullptr;
+  int8_t* d_flip = nullptr;
+  int16_t* d_site_of_t = nullptr;
+  bool has_chi = false;
+  SymChars ch;
+};
+
+namespace {
+struct SymElocLayout { ElocLayout e; long long off_cfg, off_logp, off_phase, off_total, off_ring2, total, Rmax; };
+SymElocLayout sym_eloc_layout(const rnnwf_model& m, int G, int ham, long long rows) {
+  SymElocLayout S;
+  S.e = eloc_layout(m, ham, rows);
+  S.Rmax = rows + S.e.max_children;
+  long long o = S.e.off_ring;                  // the plain E_loc sweep ring is not used: reuse its place and grow from there
+  S.off_cfg = o;    o += align256((long long)G * S.Rmax * m.nsites);
+  S.off_logp = o;   o += align256((long long)G * S.Rmax * 8);
+  S.off_phase = o;  o += align256((long long)G * S.Rmax * 8);
+  S.off_total = o;  o += 256;
+  S.off_ring2 = o;  o += align256(ring_bytes(m, max_ctas(m), 128));
+  S.total = o;
+  return S;
+}
+}  // namespace
+
+extern "C" {
+
+int rnnwf_symmetry_create(rnnwf_handle h, int G, const int32_t* perm, const int8_t* flip, const double* chi, rnnwf_symmetry_handle* out) {
+  if (h == nullptr || perm == nullptr || out == nullptr) return fail(RNNWF_EINVAL, "rnnwf_symmetry_create: null argument");
+  *out = nullptr;
+  if (G < 1 || G > SYM_MAX_G) return fail(RNNWF_EINVAL, "rnnwf_symmetry_create: the group must have 1..64 elements");
+  const int ns = h->nsites;
+  std::vector<char> seen(ns);
+  for (int g = 0; g < G; ++g) {
+    std::fill(seen.begin(), seen.end(), 0);
+    for (int i = 0; i < ns; ++i) {
+      const int j = perm[(size_t)g * ns + i];
+      if (j < 0 || j >= ns || seen[j]) return fail(RNNWF_EINVAL, "rnnwf_symmetry_create: every group element must be a permutation of the sites");
+      seen[j] = 1;
+    }
+  }
+  rnnwf_symmetry* s = new rnnwf_symmetry();
+  s->G = G; s->nsites = ns; s->bits = h->bits; s->device = h->device;
+  s->has_chi = chi != nullptr;
+  for (int g = 0; g < SYM_MAX_G; ++g) s->ch.inv_chi[g] = (g < G) ? ((chi != nullptr) ? 1.0 / chi[g] : 1.0) : 0.0;
+  std::vector<int8_t> fl(G, 0);
+  if (flip != nullptr) for (int g = 0; g < G; ++g) fl[g] = flip[g] ? 1 : 0;
+  cudaError_t e = cudaMalloc(&s->d_perm, (size_t)G * ns * 4);
+  if (e == cudaSuccess) e = cudaMalloc(&s->d_flip, (size_t)G);
+  if (e == cudaSuccess) e = cudaMalloc(&s->d_site_of_t, h->site_of_t.size() * sizeof(int16_t));
+  if (e == cudaSuccess) e = cudaMemcpy(s->d_perm, perm, (size_t)G * ns * 4, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(s->d_flip, fl.data(), (size_t)G, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(s->d_site_of_t, h->site_of_t.data(), h->site_of_t.size() * sizeof(int16_t), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) {
+    cudaFree(s->d_perm); cudaFree(s->d_flip); cudaFree(s->d_site_of_t); delete s;
+    return fail(RNNWF_ECUDA, std::string("rnnwf_symmetry_create: ") + cudaGetErrorString(e));
+  }
+  *out = s;
+  return RNNWF_OK;
+}
+
+int rnnwf_symmetry_destroy(rnnwf_symmetry_handle s) {
+  if (s == nullptr) return RNNWF_OK;
+  cudaFree(s->d_perm); cudaFree(s->d_flip); cudaFree(s->d_site_of_t);
+  delete s;
+  return RNNWF_OK;
+}
+
+int rnnwf_symmetry_order(rnnwf_symmetry_handle s) { return s ? s->G : 0; }
+
+int rnnwf_symmetry_apply(rnnwf_symmetry_handle s, int64_t rows, const int8_t* in_dev, int8_t* out_dev, void* stream) {
+  if (s == nullptr || rows <= 0 || in_dev == nullptr || out_dev == nullptr) return fail(RNNWF_EINVAL, "rnnwf_symmetry_apply: null argument or rows <= 0");
+  SymExpandParams P;
+  std::memset(&P, 0, sizeof(P));
+  P.G = s->G; P.nsites = s->nsites; P.bits = s->bits; P.rows = rows; P.perm = s->d_perm; P.flip = s->d_flip;
+  P.samples = in_dev; P.site_of_t = s->d_site_of_t; P.out = out_dev;
+  const long long total = (long long)rows * s->G * s->nsites;
+  RNNWF_COUNT_LAUNCH();
+  sym_expand_kernel<<<std::min(148 * 16, cdiv(total, 256)), 256, 0, static_cast<cudaStream_t>(stream)>>>(P);
+  CUDA_TRY(cudaGetLastError());
+  return RNNWF_OK;
+}
+
+int64_t rnnwf_eloc_sym_workspace_bytes(rnnwf_handle h, rnnwf_symmetry_handle s, int hamiltonian, int64_t rows) {
+  if (h == nullptr || s == nullptr || rows <= 0) return 0;
+  return sym_eloc_layout(*h, s->G, hamiltonian, rows).total;
+}
+
+int rnnwf_local_energies_sym(rnnwf_handle h, rnnwf_symmetry_handle s, int hamiltonian, const double* ham, int ham_len, int64_t rows,
+                             const int8_t* samples_dev, double* out_logp_dev, double* out_phase_dev, double* eloc_dev,
+                             int64_t* nconn_dev, void* workspace_dev, int64_t workspace_bytes, void* stream) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  if (s == nullptr || rows <= 0 || samples_dev == nullptr || out_logp_dev == nullptr || eloc_dev == nullptr || ham == nullptr)
+    return fail(RNNWF_EINVAL, "rnnwf_local_energies_sym: null argument or rows <= 0");
+  const rnnwf_model& m = *h;
+  if (s->nsites != m.nsites || s->bits != m.bits) return fail(RNNWF_EINVAL, "rnnwf_local_energies_sym: the symmetry table was built for another lattice");
+  if (m.complex_head && out_phase_dev == nullptr) return fail(RNNWF_EINVAL, "rnnwf_local_energies_sym: complex wavefunction needs out_phase");
+  const int G = s->G;
+  const SymElocLayout S = sym_eloc_layout(m, G, hamiltonian, rows);
+  if ((long long)G * S.Rmax > 0x7fffffffLL) return fail(RNNWF_EINVAL, "rnnwf_local_energies_sym: too many rows");
+  if (workspace_dev == nullptr || workspace_bytes < S.total) return fail(RNNWF_ENOMEM, "rnnwf_local_energies_sym: workspace too small");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  char* ws = static_cast<char*>(workspace_dev);
+  EnumOut en;
+  if ((rc = enumerate_connected(m, hamiltonian, ham, ham_len, rows, samples_dev, eloc_dev, ws, S.e, st, en))) return rc;
+  Child* d_children = reinterpret_cast<Child*>(ws + S.e.off_children);
+  if (nconn_dev != nullptr) {
+    RNNWF_COUNT_LAUNCH(); count_children_kernel<<<1, 32, 0, st>>>(en.have_children ? en.rows_dev : nullptr, en.have_children ? (en.rows_dev ? 0 : en.nchild_fixed) : 0, (long long*)nconn_dev);
+  }
+  int8_t* d_cfg = reinterpret_cast<int8_t*>(ws + S.off_cfg);
+  double* d_lp = reinterpret_cast<double*>(ws + S.off_logp);
+  double* d_ph = m.complex_head ? reinterpret_cast<double*>(ws + S.off_phase) : nullptr;
+  int* d_total = reinterpret_cast<int*>(ws + S.off_total);
+  const long long nfixed = en.have_children ? en.nchild_fixed : 0;
+  // 1. the G transformed copies of every sample and every connected configuration, formed through the remap tables
+  SymExpandParams X;
+  std::memset(&X, 0, sizeof(X));
+  X.G = G; X.nsites = m.nsites; X.bits = m.bits; X.rows = rows; X.nchild_fixed = nfixed; X.nchild_dev = en.have_children ? en.rows_dev : nullptr;
+  X.perm = s->d_perm; X.flip = s->d_flip; X.samples = samples_dev; X.children = en.have_children ? d_children : nullptr;
+  X.site_of_t = s->d_site_of_t; X.out = d_cfg; X.total_rows_out = d_total;
+  const long long upper = (long long)G * (rows + nfixed);
+  RNNWF_COUNT_LAUNCH(); sym_expand_kernel<<<std::min(148 * 16, cdiv(upper * m.nsites, 256)), 256, 0, st>>>(X);
+  // 2. one batched sweep over all of them
+  LaunchShape sh;
+  if ((rc = pick_shape(m, upper, sh))) return rc;
+  SweepParams P;
+  fill_model_params(m, sh, P);
+  P.mode = MODE_EVAL; P.rows = upper; P.rows_dev = d_total; P.cfg_in = d_cfg; P.out_logp = d_lp; P.out_phase = d_ph;
+  P.ring = reinterpret_cast<float*>(ws + S.off_ring2);
+  if ((rc = launch_sweep(m, P, sh, st))) return rc;
+  // 3. symmetrised log psi of the samples, then the ratios of the connected configurations reduced into E_loc
+  RNNWF_COUNT_LAUNCH(); sym_parent_kernel<<<std::min(1184, cdiv(rows, 256)), 256, 0, st>>>(G, rows, nfixed, X.nchild_dev, d_lp, d_ph, s->ch, out_logp_dev, out_phase_dev);
+  if (en.have_children) {
+    RNNWF_COUNT_LAUNCH(); sym_eloc_reduce_kernel<<<std::min(148 * 8, cdiv(nfixed, 256)), 256, 0, st>>>(G, rows, nfixed, X.nchild_dev, d_children, d_lp, d_ph, s->ch,
+                                                                                                       out_logp_dev, out_phase_dev, eloc_dev);
+  }
   CUDA_TRY(cudaGetLastError());
   return RNNWF_OK;
 }

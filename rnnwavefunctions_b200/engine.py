@@ -223,7 +223,75 @@ class Engine:
               "rnnwf_symmetry_seeds")
         return seed_lp, seed_ph
 
+    # ---------------------------------------------------------------- symmetry groups as device remap tables
+    def symmetry_group(self, perm, flip=None, characters=None):
+        """Device-resident index-remap tables of a symmetry group (rnnwf_symmetry_create): element g maps a configuration
+        s to s[perm[g]] ^ flip[g] (flat site indices in the configuration's array layout)."""
+        return SymmetryGroup(self, perm, flip, characters)
+
+    def symmetry_apply(self, group, samples):
+        """The G transformed copies of `samples`, copy-major: int8 [G * B, *cfg_shape]."""
+        s = self._as_cfg(samples)
+        out = torch.empty((group.G * s.shape[0],) + self.cfg_shape, dtype=torch.int8, device=self.device)
+        if s.shape[0]:
+            check(lib.rnnwf_symmetry_apply(group._h, s.shape[0], _ptr(s), _ptr(out), _stream()), "rnnwf_symmetry_apply")
+        return out
+
+    def logpsi_sym(self, group, samples, saved=None):
+        """Symmetry-projected log psi: -> (logp [B], phase [B] or None, per-copy logp [G,B], per-copy phase [G,B])."""
+        copies = self.symmetry_apply(group, samples)
+        lp, ph = self.logpsi(copies, saved=saved)
+        lp, ph = lp.view(group.G, -1), ph.view(group.G, -1)
+        out_lp, out_ph = self.symmetrize(lp, ph if self.complex_head else None, group.characters)
+        return out_lp, out_ph, lp, ph, copies
+
+    def local_energies_sym(self, group, ham, ham_params, samples, return_count=False):
+        """Local energies of the symmetry-projected wavefunction (rnnwf_local_energies_sym)
+        -> (eloc complex128 [B], logp [B], phase [B]) with logp / phase the symmetrised log psi of the samples."""
+        s = self._as_cfg(samples)
+        B = s.shape[0]
+        hp = np.ascontiguousarray(np.asarray(ham_params, dtype=np.float64).reshape(-1))
+        need = int(lib.rnnwf_eloc_sym_workspace_bytes(self._h, group._h, ham, B))
+        if self._eloc_ws is None or self._eloc_ws.numel() < need:
+            self._eloc_ws = None
+            self._eloc_ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        eloc = torch.empty(B, 2, dtype=torch.float64, device=self.device)
+        logp = torch.empty(B, dtype=torch.float64, device=self.device)
+        phase = torch.zeros(B, dtype=torch.float64, device=self.device)
+        ncount = torch.zeros(1, dtype=torch.int64, device=self.device)
+        check(lib.rnnwf_local_energies_sym(self._h, group._h, ham, hp.ctypes.data_as(C.POINTER(C.c_double)), hp.size, B, _ptr(s),
+                                           _ptr(logp), _ptr(phase if self.complex_head else None), _ptr(eloc), _ptr(ncount),
+                                           _ptr(self._eloc_ws), self._eloc_ws.numel(), _stream()), "rnnwf_local_energies_sym")
+        e = torch.view_as_complex(eloc)
+        return (e, logp, phase, ncount) if return_count else (e, logp, phase)
+
     def describe(self):
         buf = C.create_string_buffer(512)
         check(lib.rnnwf_describe(self._h, buf, 512), "rnnwf_describe")
         return buf.value.decode()
+
+
+class SymmetryGroup:
+    """Handle of rnnwf_symmetry_create: perm int [G, nsites] (flat source index of every site of the transformed
+    configuration), flip [G] (1: spins flipped, s -> 1 - s), characters [G] (+-1; None = trivial representation)."""
+
+    def __init__(self, engine, perm, flip=None, characters=None):
+        perm = np.ascontiguousarray(np.asarray(perm, dtype=np.int32))
+        self.G, nsites = perm.shape
+        self.perm = perm
+        self.flip = None if flip is None else np.ascontiguousarray(np.asarray(flip, dtype=np.int8))
+        self.characters = None if characters is None else [float(c) for c in characters]
+        chi = None if characters is None else (C.c_double * self.G)(*self.characters)
+        h = C.c_void_p()
+        check(lib.rnnwf_symmetry_create(engine._h, self.G, perm.ctypes.data_as(C.POINTER(C.c_int32)),
+                                        None if self.flip is None else self.flip.ctypes.data_as(C.POINTER(C.c_int8)),
+                                        chi, C.byref(h)), "rnnwf_symmetry_create")
+        self._h = h
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                lib.rnnwf_symmetry_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass

@@ -101,13 +101,16 @@ class VMC:
     """Sample -> E_loc -> gradient -> update for one engine and one Hamiltonian."""
 
     def __init__(self, engine, ham, ham_params, numsamples, lr=1e-3, seed=111, T=0.0, free_energy=False,
-                 prefix_reuse=True, clip=None):
+                 prefix_reuse=True, clip=None, symmetry=None):
         self.eng, self.ham, self.ham_params = engine, ham, ham_params
         self.ns = int(numsamples)
         self.rank = dist.get_rank() if _dist_on() else 0
         self.world = dist.get_world_size() if _dist_on() else 1
         self.seed, self.T, self.free_energy, self.lr, self.clip = seed, T, free_energy, lr, clip
-        self.saved = engine.new_saved(self.ns)
+        # symmetry: an engine.SymmetryGroup -> the wavefunction is the symmetry-projected one (local energies with
+        # rnnwf_local_energies_sym, gradient through the G copies of every sample and rnnwf_symmetry_seeds)
+        self.sym = symmetry
+        self.saved = engine.new_saved(self.ns * (symmetry.G if symmetry is not None else 1))
         self.prefix_reuse = prefix_reuse
         self.opt = TFAdam(engine.num_params, engine.device)
         self.it = 0
@@ -116,6 +119,10 @@ class VMC:
     def sample_and_energies(self, uniforms=None):
         eng = self.eng
         offset = (self.it * self.world + self.rank) * self.ns   # disjoint Philox rows per step and rank
+        if self.sym is not None:
+            s, _, _ = eng.sample(self.ns, uniforms=uniforms, seed=self.seed, row_offset=offset)
+            e, lp, ph, cnt = eng.local_energies_sym(self.sym, self.ham, self.ham_params, s, return_count=True)
+            return s, lp, ph, e, cnt
         s, lp, ph = eng.sample(self.ns, uniforms=uniforms, seed=self.seed, row_offset=offset, saved=self.saved)
         e, cnt = eng.local_energies(self.ham, self.ham_params, s, lp, ph,
                                     saved=self.saved if self.prefix_reuse else None, return_count=True)
@@ -126,7 +133,14 @@ class VMC:
         extra = lp if (self.T != 0.0) else None
         n, mean_e, var, mean_lp = energy_moments(e, extra)
         sl, sp = seeds(e, mean_e, n, eng.complex_head, logp=lp, mean_logp=mean_lp, T=self.T, free_energy=self.free_energy)
-        grad = eng.backward(s, self.saved, sl, sp)
+        if self.sym is not None:
+            # d cost / d (symmetrised log P, phase) -> seeds of the G copies -> one backward over the G * ns batch
+            _, _, lp_g, ph_g, copies = eng.logpsi_sym(self.sym, s, saved=self.saved)
+            cplx = eng.complex_head
+            sl_g, sp_g = eng.symmetry_seeds(lp_g, ph_g if cplx else None, self.sym.characters, sl, sp)
+            grad = eng.backward(copies, self.saved, sl_g.reshape(-1), None if sp_g is None else sp_g.reshape(-1))
+        else:
+            grad = eng.backward(s, self.saved, sl, sp)
         allreduce_(grad)
         return grad, mean_e, var
 

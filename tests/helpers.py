@@ -55,3 +55,20 @@ def philox_uniforms(seed, rows, nsteps, row_offset=0):
         c0, c1, c2, c3 = (hi1 ^ c1 ^ k0) & mask, lo1, (hi0 ^ c3 ^ k1) & mask, lo0
         k0, k1 = (k0 + np.uint64(W0)) & mask, (k1 + np.uint64(W1)) & mask
     return ((c0 >> np.uint64(8)).astype(np.float32) * np.float32(1.0 / 16777216.0)).astype(np.float32)
+
+
+def rel_err(x, ref):
+    """The one bound the parity tests use for log-amplitudes and local energies (north_star: 1e-5 relative in the FP32
+    regime, 1e-3 in the reduced-precision regime): per-sample relative error with a floor at the batch mean of |ref|,
+        err_b = |x_b - ref_b| / max(|ref_b|, <|ref|>).
+    Returns (max, rms) and prints them so the GPU log records the measured numbers."""
+    x, ref = np.asarray(x), np.asarray(ref)
+    floor = np.abs(ref).mean()
+    err = np.abs(x - ref) / np.maximum(np.abs(ref), floor)
+    return float(err.max()), float(np.sqrt((err ** 2).mean()))
+
+
+def assert_rel(x, ref, tol, what=""):
+    mx, rms = rel_err(x, ref)
+    print(f"[parity] {what}: max rel err {mx:.3e}, rms {rms:.3e} (bound {tol:g}, n={np.size(ref)})")
+    assert mx <= tol, f"{what}: max relative error {mx:.3e} > {tol:g} (rms {rms:.3e})"
