@@ -335,7 +335,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
     ap.add_argument("--numsamples", type=int, default=None)
-    ap.add_argument("--precision", default="auto", choices=["auto", "fp32", "tc"],
+    ap.add_argument("--precision", default="auto", choices=["auto", "fp32", "tc", "tc3"],
                     help="sweep regime: fp32 = FFMA (1e-5 parity), tc = tcgen05 FP16-operand tensor-core sweep (1e-3 bound); "
                          "auto = tc where it exists (tensorized 2D GRU), fp32 otherwise")
     ap.add_argument("--no-prefix-reuse", action="store_true")
@@ -520,7 +520,7 @@ def main():
                     "launch_ms": eloc_ms, "mma_columns_per_row_site": 3 * nhq,
                     "note": "executed = MMA flops issued per row (absent neighbours skipped, hidden axis padded to 64 per pass, K=32 input/bias "
                             "job, prefix reuse counted per row); launch_ms brackets rnnwf_local_energies (enumeration kernels + sweep)"}
-    elif precision == "tc":
+    elif precision in ("tc", "tc3"):
         # the tensor-core sweep executes, per row and site, the dense [2*nhp] x [7*16*passes] contraction
         nhp = (w["eng"]["num_units"] + 7) // 8 * 8
         npass = (w["eng"]["num_units"] + 15) // 16
@@ -528,11 +528,12 @@ def main():
         ncols = 112 * (npass - 1) + (28 * subs_last + 15) // 16 * 16
         if w["eng"]["cell"] == "VANILLA2D":
             ncols = 112                                                       # one pass per site: 7 unit pieces x 4 threads x 4 units
-        exec_flops = exec_sites * (2 * (2 * nhp) * ncols + 2 * w["eng"]["num_units"] * 4)
+        mma_per_kstep = 3 if precision == "tc3" else 1          # split precision: A_hi B_hi + A_lo B_hi + A_hi B_lo
+        exec_flops = exec_sites * (mma_per_kstep * 2 * (2 * nhp) * ncols + 2 * w["eng"]["num_units"] * 4)
         achieved = exec_flops / (eloc_ms * 1e-3) / 1e12
         # traffic: dram bytes read + written by this kernel in the committed ncu --set full capture (profiles/r1e_summary.md:
         # 5.17 GB + 12.33 GB, write-back of the history ring), valid for the C4 triangular workload it was taken on
-        traffic = 17.5e9 if args.workload == DEFAULT_WORKLOAD else None
+        traffic = 17.5e9 if (args.workload == DEFAULT_WORKLOAD and precision == "tc") else None
         roofline = {"bound": "tensor", "kernel": "sweep_tc_kernel (MODE_CHILD)", "achieved": achieved, "peak": bf16_peak, "unit": "TFLOP/s",
                     "frac": achieved / bf16_peak, "traffic": traffic, "traffic_source": "profiles/r1e_summary.md (ncu --set full, one launch)" if traffic else None,
                     "peak_source": ("MEASURED_PEAKS.json bf16_tflops_sustained (16-bit tensor peak, kernel timed inside a long step)"

@@ -17,8 +17,10 @@ _GRU = {"Wg": "gates/kernel", "bg": "gates/bias", "Wci": "candidate/input_projec
         "bch": "candidate/hidden_projection/bias"}
 
 
-def tf_variable_name(name, complex_head, scope="RNNwavefunction"):
-    """Engine tensor name -> TF variable name (without the ':0' suffix)."""
+def tf_variable_name(name, complex_head, scope="RNNwavefunction", gru1d=True):
+    """Engine tensor name -> TF variable name (without the ':0' suffix).  The amplitude head is 'wf_dense_ampl' only in
+    the 1D complex RNN (J1J2/ComplexRNNwavefunction.py:42); every other model -- the complex 2D Heisenberg one included
+    (2DHeisenberg/MDComplexRNN.py:63) -- calls it 'wf_dense'."""
     m = re.fullmatch(r"gru(\d+)\.(\w+)", name)
     if m:
         return f"{scope}/multi_rnn_cell/cell_{m.group(1)}/cudnn_compatible_gru_cell/{_GRU[m.group(2)]}"
@@ -27,14 +29,14 @@ def tf_variable_name(name, complex_head, scope="RNNwavefunction"):
         leaf = "kernel" if leaf == "W" else "bias"
         if head == "dense_phase":
             return f"{scope}/wf_dense_phase/{leaf}"
-        return f"{scope}/{'wf_dense_ampl' if complex_head else 'wf_dense'}/{leaf}"
+        return f"{scope}/{'wf_dense_ampl' if (complex_head and gru1d) else 'wf_dense'}/{leaf}"
     return f"{scope}/{name}_rnn_0"          # MD cells: Wh, Uh, Wv, Uv, b / W, b, Wg, bg, Wmerge
 
 
 def state_dict(engine, scope="RNNwavefunction"):
     """{tf_variable_name: float32 ndarray in TF layout} of the engine's current parameters."""
     views = engine.views()
-    return {tf_variable_name(n, engine.complex_head, scope): v.detach().cpu().numpy().copy() for n, v in views.items()}
+    return {tf_variable_name(n, engine.complex_head, scope, engine.cell == 0): v.detach().cpu().numpy().copy() for n, v in views.items()}
 
 
 def load_state_dict(engine, sd, scope="RNNwavefunction", strict=True):
@@ -46,7 +48,7 @@ def load_state_dict(engine, sd, scope="RNNwavefunction", strict=True):
     views = {n: flat[o:o + int(np.prod(s))].view(*s) for n, o, s in engine.tensors}
     missing = []
     for n, v in views.items():
-        key = tf_variable_name(n, engine.complex_head, scope)
+        key = tf_variable_name(n, engine.complex_head, scope, engine.cell == 0)
         if key not in sd:
             missing.append(key)
             continue

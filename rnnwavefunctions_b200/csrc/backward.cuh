@@ -668,13 +668,16 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
     // ---- parameter gradients: weights on the tensor cores (dw_tc.cuh), biases and heads as reductions
     {
       DwParams D;
-      if (m.dw_rows != R) {             // plan depends on the row count only: build and upload once (blocking copy)
+      if (m.dw_rows != R) {             // plan depends on the row count only: build and upload once, ordered on the caller's stream
         std::vector<DwJob> jobs;
         std::vector<int> cls_steps;
         dw_plan(m, R, jobs, cls_steps, m.dw_cls_count);
         if (jobs.size() > 1024) { err = "rnnwf_backward: too many weight-gradient jobs"; return RNNWF_EINVAL; }
-        e = cudaMemcpy(m.d_dw_jobs, jobs.data(), jobs.size() * sizeof(DwJob), cudaMemcpyHostToDevice);
-        if (e == cudaSuccess) e = cudaMemcpy(m.d_dw_cls, cls_steps.data(), cls_steps.size() * sizeof(int), cudaMemcpyHostToDevice);
+        // the host copies live in the handle until the next plan, so the stream-ordered upload never outlives its source
+        m.plan_host_a.assign(reinterpret_cast<const unsigned char*>(jobs.data()), reinterpret_cast<const unsigned char*>(jobs.data() + jobs.size()));
+        m.plan_host_b.assign(reinterpret_cast<const unsigned char*>(cls_steps.data()), reinterpret_cast<const unsigned char*>(cls_steps.data() + cls_steps.size()));
+        e = cudaMemcpyAsync(m.d_dw_jobs, m.plan_host_a.data(), m.plan_host_a.size(), cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(m.d_dw_cls, m.plan_host_b.data(), m.plan_host_b.size(), cudaMemcpyHostToDevice, st);
         if (e != cudaSuccess) { err = std::string("rnnwf_backward plan upload: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
         m.dw_njobs = (int)jobs.size();
         m.dw_rows = R;
@@ -734,9 +737,10 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
         std::vector<Dw4Job> jobs;
         std::vector<int> sites;
         dw4_plan(m, R, jobs, sites, m.dw4_sites_n);
-        e = cudaMemcpyAsync(m.d_dw4_jobs, jobs.data(), jobs.size() * sizeof(Dw4Job), cudaMemcpyHostToDevice, st);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(m.d_dw4_sites, sites.data(), sites.size() * sizeof(int), cudaMemcpyHostToDevice, st);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(st);     // the host vectors go out of scope
+        m.plan_host_a.assign(reinterpret_cast<const unsigned char*>(jobs.data()), reinterpret_cast<const unsigned char*>(jobs.data() + jobs.size()));
+        m.plan_host_b.assign(reinterpret_cast<const unsigned char*>(sites.data()), reinterpret_cast<const unsigned char*>(sites.data() + sites.size()));
+        e = cudaMemcpyAsync(m.d_dw4_jobs, m.plan_host_a.data(), m.plan_host_a.size(), cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(m.d_dw4_sites, m.plan_host_b.data(), m.plan_host_b.size(), cudaMemcpyHostToDevice, st);
         if (e != cudaSuccess) { err = std::string("rnnwf_backward plan upload: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
         m.dw4_njobs = (int)jobs.size();
         m.dw4_rows = R;

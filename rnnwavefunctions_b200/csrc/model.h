@@ -53,8 +53,9 @@ struct rnnwf_model_impl {
   float* d_head_w = nullptr;
   float* d_head_b = nullptr;
   // tensor-core regime
-  int precision = 0;            // 0: FP32 FFMA, 1: BF16 tensor cores (tcgen05), hi+lo split activations
+  int precision = 0;            // 0: FP32 FFMA sweep, 1: tcgen05 sweep (FP16 operands, FP32 accumulate in TMEM), 2: tcgen05 sweep, split precision
   bool tc_enabled = false;
+  bool tc_split = false;        // precision 2: split-precision operands (FP16 hi + lo, three MMAs per K step) -- the 1e-5 bound on the tensor cores
   bool tc4 = false;             // tensor-core sweep of the four-neighbour GRU (sweep_tc4.cuh); saved state and backward as in the FFMA regime
   int tc_np = 0;
   unsigned char* d_tcB = nullptr;
@@ -71,6 +72,7 @@ struct rnnwf_model_impl {
   mutable int dw4_sites_n[5] = {0, 0, 0, 0, 0};
   void* d_dw4_jobs = nullptr;       // [4096] Dw4Job
   int* d_dw4_sites = nullptr;       // [5][Q]
+  mutable std::vector<unsigned char> plan_host_a, plan_host_b;   // host images of the last uploaded work plan (source of the stream-ordered copies)
   const float* d_params = nullptr;  // last parameter vector handed to set_weights (caller-owned)
   bool weights_set = false;
 

@@ -11,6 +11,7 @@
 #include "model.h"
 #include "sweep.cuh"
 #include "sweep_tc.cuh"
+#include "pack_tc.cuh"
 #include "sweep_tc4.cuh"
 #include "pack.cuh"
 #include "eloc.cuh"
@@ -19,6 +20,11 @@
 #include "symmetry.cuh"
 
 using namespace rnnwf;
+
+namespace rnnwf {   // sweep_tc_inst.cu
+cudaError_t tc_sweep_set_smem(int cellk, bool biasmma, bool split, int smem_bytes);
+cudaError_t tc_sweep_launch(const SweepParams& P, int cellk, bool biasmma, bool split, int grid, int threads, int smem_bytes, cudaStream_t st);
+}
 
 struct rnnwf_model : rnnwf::rnnwf_model_impl {};
 
@@ -67,7 +73,8 @@ int build_model(rnnwf_model& m) {
   m.cps = m.nhp / KC;
   m.num_params = 0;
   m.precision = c.reserved[0];
-  if (m.precision != 0 && m.precision != 1) return fail(RNNWF_EINVAL, "precision must be 0 (fp32) or 1 (bf16 tensor cores)");
+  if (m.precision < 0 || m.precision > 2)
+    return fail(RNNWF_EINVAL, "precision must be 0 (FP32 FFMA sweep), 1 (tcgen05 sweep, FP16 operands) or 2 (tcgen05 sweep, split-precision FP16 hi+lo operands)");
   const int nh = m.nh, Nx = c.nx, Ny = c.ny;
   if (nh < 1 || nh > 1024 || Nx < 1 || Ny < 1) return fail(RNNWF_EINVAL, "bad lattice / num_units");
   if ((long long)Nx * Ny * std::max(1, c.num_layers) > 30000) return fail(RNNWF_EINVAL, "lattice too large for int16 step tables");
@@ -279,10 +286,13 @@ int build_model(rnnwf_model& m) {
     v.meta.b_off = (uint32_t)boff;
     boff += m.Gp;
   }
-  m.tc_enabled = (m.precision == 1 && (m.cell == CELL_TENSGRU2D || m.cell == CELL_TENS2D || m.cell == CELL_VANILLA2D));
+  m.tc_enabled = (m.precision >= 1 && (m.cell == CELL_TENSGRU2D || m.cell == CELL_TENS2D || m.cell == CELL_VANILLA2D));
+  m.tc_split = m.tc_enabled && m.precision == 2;
   m.tc4 = (m.precision == 1 && m.cell == CELL_GRU4);
   if (m.precision == 1 && !m.tc_enabled && !m.tc4)
     return fail(RNNWF_EINVAL, "the tensor-core regime is implemented for the 2D cells (tensorized GRU, tensorized, vanilla RNN, four-neighbour GRU)");
+  if (m.precision == 2 && !m.tc_enabled)
+    return fail(RNNWF_EINVAL, "the split-precision tensor-core regime is implemented for the two-neighbour 2D cells (tensorized GRU, tensorized, vanilla RNN)");
   // column passes per site: 16 units x 7 blocks each for the tensorized GRU; the vanilla cell needs one (7 unit pieces)
   m.tc_np = (m.cell == CELL_VANILLA2D) ? 1 : (m.nh + TC_JP - 1) / TC_JP;
   if (m.tc_enabled) {
@@ -389,19 +399,9 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
   cudaError_t e;
   if (m.tc_enabled) {
     RNNWF_COUNT_LAUNCH();
-    const bool bm = m.nh < m.nhp;     // biases through the tensor core when the operand has a free padding position
-    const bool van = m.cell == CELL_VANILLA2D;
-    const bool ung = m.cell == CELL_TENS2D;
-#define RNNWF_TC_LAUNCH(MODE_) do { if (van) sweep_tc_kernel<MODE_, false, 1><<<s.grid, s.threads, s.smem, st>>>(P); \
-                                     else if (ung && bm) sweep_tc_kernel<MODE_, true, 2><<<s.grid, s.threads, s.smem, st>>>(P); \
-                                     else if (ung) sweep_tc_kernel<MODE_, false, 2><<<s.grid, s.threads, s.smem, st>>>(P); \
-                                     else if (bm) sweep_tc_kernel<MODE_, true, 0><<<s.grid, s.threads, s.smem, st>>>(P); \
-                                     else sweep_tc_kernel<MODE_, false, 0><<<s.grid, s.threads, s.smem, st>>>(P); } while (0)
-    if (P.mode == MODE_SAMPLE) RNNWF_TC_LAUNCH(MODE_SAMPLE);
-    else if (P.mode == MODE_CHILD) RNNWF_TC_LAUNCH(MODE_CHILD);
-    else RNNWF_TC_LAUNCH(MODE_EVAL);
-#undef RNNWF_TC_LAUNCH
-    e = cudaGetLastError();
+    const int cellk = (m.cell == CELL_VANILLA2D) ? 1 : (m.cell == CELL_TENS2D ? 2 : 0);
+    const bool bm = cellk != 1 && m.nh < m.nhp;     // biases through the tensor core when the operand has a free padding position
+    e = tc_sweep_launch(P, cellk, bm, m.tc_split, s.grid, s.threads, s.smem, st);
     if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("tensor-core sweep launch: ") + cudaGetErrorString(e));
     return RNNWF_OK;
   }
@@ -420,7 +420,7 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
 long long ring_bytes(const rnnwf_model& m, int grid, int Mp) {
   if (m.tc4) return (long long)grid * m.Q * t4_step_bytes(m.tc_np);   // FP16 chunk images of every site, per persistent CTA
   // tensor-core regime: one FP16 history image per slot in the fixed quad layout of sweep_tc.cuh (TC_RING_SLOT bytes)
-  const long long slot = m.tc_enabled ? std::max<long long>((long long)TC_RING_SLOT, (long long)Mp * m.nhp * 4) : (long long)Mp * m.nhp * 4;
+  const long long slot = m.tc_enabled ? std::max<long long>((long long)TC_RING_SLOT * (m.tc_split ? 2 : 1), (long long)Mp * m.nhp * 4) : (long long)Mp * m.nhp * 4;
   return (long long)grid * m.ring_len * slot;
 }
 
@@ -577,23 +577,10 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
   if (m->tc_enabled) {
     const TcSmem ts(m->nhp, m->Tsym, m->Q);
     if (ts.total > 227 * 1024) { rnnwf_destroy(m); return fail(RNNWF_ENOMEM, "tensor-core sweep does not fit in shared memory for this lattice / width"); }
-    CREATE_TRY(cudaMalloc(&m->d_tcB, (size_t)3 * m->tc_np * ts.b_bytes));
+    CREATE_TRY(cudaMalloc(&m->d_tcB, (size_t)3 * m->tc_np * ts.b_bytes * (m->tc_split ? 2 : 1)));
     CREATE_TRY(cudaMalloc(&m->d_tcbias, (size_t)6 * m->nhp * 4));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE, true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL, true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_SAMPLE, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_EVAL, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc_kernel<MODE_CHILD, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ts.total));
+    const int cellk = (m->cell == CELL_VANILLA2D) ? 1 : (m->cell == CELL_TENS2D ? 2 : 0);
+    CREATE_TRY(tc_sweep_set_smem(cellk, cellk != 1 && m->nh < m->nhp, m->tc_split, ts.total));
   }
   if (m->tc4) {
     const int t4s = T4Smem(t4_stages(m->Q), m->Q).total;
@@ -695,15 +682,15 @@ int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
     const TcSmem ts(h->nhp, h->Tsym, h->Q);
     if (h->cell == CELL_VANILLA2D) {
       RNNWF_COUNT_LAUNCH(); pack_tc_vanilla_kernel<<<std::min(2048, cdiv((long long)ts.b_bytes / 2, 256)), 256, 0, st>>>(
-          params_dev + h->tensor("Wh")->offset, params_dev + h->tensor("Wv")->offset, h->nh, h->nhp, reinterpret_cast<__half*>(h->d_tcB));
+          params_dev + h->tensor("Wh")->offset, params_dev + h->tensor("Wv")->offset, h->nh, h->nhp, h->tc_split ? 1 : 0, reinterpret_cast<__half*>(h->d_tcB));
       RNNWF_COUNT_LAUNCH(); pack_tc_vanilla_bias_kernel<<<4, 256, 0, st>>>(params_dev + h->tensor("Uh")->offset, params_dev + h->tensor("Uv")->offset,
                                                                            params_dev + h->tensor("b")->offset, h->nh, h->nhp, h->d_tcbias);
     } else {
-      const long long n = 3LL * h->tc_np * (ts.b_bytes / 2);
+      const long long n = 3LL * h->tc_np * (ts.b_bytes / 2) * (h->tc_split ? 2 : 1);
       auto opt = [&](const char* nm) -> const float* { const TensorInfo* t = h->tensor(nm); return t ? params_dev + t->offset : nullptr; };
       RNNWF_COUNT_LAUNCH(); pack_tc_kernel<<<std::min(2048, cdiv(n, 256)), 256, 0, st>>>(
           params_dev + h->tensor("W")->offset, opt("Wg"), opt("Wmerge"), params_dev + h->tensor("b")->offset, opt("bg"),
-          h->nh, h->nhp, h->tc_np, reinterpret_cast<__half*>(h->d_tcB));
+          h->nh, h->nhp, h->tc_np, h->tc_split ? 1 : 0, reinterpret_cast<__half*>(h->d_tcB));
       RNNWF_COUNT_LAUNCH(); pack_tc_bias_kernel<<<1, 256, 0, st>>>(params_dev + h->tensor("b")->offset, opt("bg"), h->nh, h->nhp, h->d_tcbias);
     }
   }
@@ -1261,7 +1248,8 @@ int rnnwf_describe(rnnwf_handle h, char* buf, int cap) {
                 "cell=%d nh=%d (padded %d) steps=%d symbols=%d slots=%d classes=%d | pipe=%s, tile=128 rows x %d col-groups "
                 "(TJ=%d NTU=%d WC=%d passes=%d), k-chunk=%d, ring=%d steps, params=%lld",
                 h->cell, h->nh, h->nhp, h->Q, h->Tsym, h->nslots, h->ncls_max,
-                h->tc_enabled ? "tcgen05 FP16 operands, FP32 accumulate in TMEM (column passes of 112, double-buffered)"
+                h->tc_split ? "tcgen05 split precision: FP16 hi+lo operands, 3 MMAs per K step, FP32 accumulate in TMEM (column passes of 112, double-buffered)"
+                : h->tc_enabled ? "tcgen05 FP16 operands, FP32 accumulate in TMEM (column passes of 112, double-buffered)"
                               : (h->tc4 ? "tcgen05 FP16 operands streamed from the L2 ring (A) and the weight image (B), FP32 accumulate in TMEM (column passes of 192, double-buffered)" : "FFMA fp32"), h->Gblk, h->TJ, h->NTU, h->WC, h->ncb, KC,
                 h->ring_len, (long long)h->num_params);
   return RNNWF_OK;
@@ -1321,13 +1309,14 @@ extern "C" int rnnwf_logpsi_static(rnnwf_handle h, int64_t rows, const int8_t* s
   // tallest tile whose per-CTA ring fits; as many CTAs as the fixed array can serve
   const int pad = (m.ncls_max > 1) ? 3 * m.ncls_max : 0;
   LaunchShape s;
-  bool found = false;
+  bool found = false, fits_smem = false;
   long long smallest = 0;
   for (int wr = 4; wr >= 1 && !found; wr >>= 1) {
     const int Mp = 32 * wr, Mr = Mp - pad;
     if (Mr <= 0) continue;
     SmemLayout L(m.ncls_max, m.Gblk, Mp, m.ldH, m.nhp, m.ND, m.Tsym);
     if (L.total > 227 * 1024) continue;
+    fits_smem = true;
     const long long per_cta = (long long)m.ring_len * Mp * m.nhp * 4;      // FP32 history ring of the FFMA sweep
     smallest = per_cta;
     const long long tiles = (rows + Mr - 1) / Mr;
@@ -1339,6 +1328,7 @@ extern "C" int rnnwf_logpsi_static(rnnwf_handle h, int64_t rows, const int8_t* s
       found = true;
     }
   }
+  if (!fits_smem) return fail(RNNWF_ENOMEM, "rnnwf_logpsi_static: model does not fit in shared memory (lattice too long / too many units)");
   if (!found) {
     char msg[256];
     std::snprintf(msg, sizeof(msg),

@@ -35,15 +35,16 @@ class Engine:
         torch.cuda.set_device(self.device)
         # precision: "fp32" = FFMA sweep (1e-5 parity); "tc" = tcgen05 tensor-core sweep (FP16 operands, FP32
         # accumulate in TMEM), held to the 1e-3 bound BASELINE.json's north_star gives its reduced-precision mode
-        # ("bf16" / "fp16" are accepted as aliases).
+        # ("bf16" / "fp16" are accepted as aliases); "tc3" = tcgen05 sweep in split precision (FP16 hi+lo operands,
+        # three MMAs per K step, accurate gate / head functions): the 1e-5 bound on the tensor cores.
         if precision in ("bf16", "fp16"):
             precision = "tc"
-        if precision not in ("fp32", "tc"):
-            raise ValueError("precision must be 'fp32' or 'tc'")
+        if precision not in ("fp32", "tc", "tc3"):
+            raise ValueError("precision must be 'fp32', 'tc' or 'tc3'")
         self.precision = precision
         self.cfg = Config(cell=cell, complex_head=int(bool(complex_head)), nx=nx, ny=ny, num_units=num_units,
                           num_layers=num_layers, u1=int(bool(u1)), magnetization=magnetization)
-        self.cfg.reserved[0] = 1 if precision == "tc" else 0
+        self.cfg.reserved[0] = {"fp32": 0, "tc": 1, "tc3": 2}[precision]
         self.cell, self.nx, self.ny, self.nh, self.num_layers = cell, nx, ny, num_units, num_layers
         self.complex_head, self.u1 = bool(complex_head), bool(u1)
         h = C.c_void_p()

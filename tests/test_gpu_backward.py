@@ -69,3 +69,30 @@ def test_gradient_matches_oracle_autograd(cuda, name, from_sampling):
         if not err < 1e-4:
             bad.append((n, err, scale))
     assert not bad, f"gradient mismatch (tensor, rel err, scale): {bad}"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("precision", ["fp32", "tc"])
+def test_free_energy_cost_gradient(cuda, precision):
+    """G3: the Rydberg scripts minimise the free energy, F_loc = E_loc + T log P in place of E_loc
+    (RydbergKagome_2DGRU/Run_RNNWF_Rydberg.py:158-159).  The product forms the seeds in vmc.seeds(free_energy=True); the
+    oracle differentiates oracle/costs.py:cost_free_energy."""
+    from rnnwavefunctions_b200 import vmc
+    ns, T = 300, 0.7
+    eng = Engine(seed=41, precision=precision, cell=_lib.CELL_GRU4, nx=3, ny=3, num_units=40)
+    _randomize(eng, 42)
+    g = torch.Generator().manual_seed(43)
+    saved = eng.new_saved(ns)
+    s, lp, _ = eng.sample(ns, uniforms=torch.rand(ns, eng.nsteps, generator=g, dtype=torch.float32), saved=saved)
+    E = torch.randn(ns, generator=g, dtype=torch.float64)
+    Ec = torch.complex(E, torch.zeros_like(E)).cuda()
+    n, mean_e, var, mean_lp = vmc.energy_moments(Ec, lp)
+    sl, sp = vmc.seeds(Ec, mean_e, n, False, logp=lp, mean_logp=mean_lp, T=T, free_energy=True)
+    assert sp is None
+    grad = eng.backward(s, saved, sl).cpu()
+    P = oracle_params(eng, requires_grad=True)
+    costs.cost_free_energy(oracle_run(eng, P, samples=s.cpu().numpy())["logp"], E, T).backward()
+    tol = 1e-4 if precision == "fp32" else 1e-2
+    for name, v in eng.views(grad).items():
+        gr = P[name].grad
+        assert float((v.double() - gr).abs().max()) < tol * (float(gr.abs().max()) + 1e-30), name

@@ -35,7 +35,7 @@ def _oracle_eloc(eng, s, J2):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("precision,tol", [("tc", 1e-3), ("fp32", 1e-5)])
+@pytest.mark.parametrize("precision,tol", [("tc", 1e-3), ("tc3", 1e-5), ("fp32", 1e-5)])
 @pytest.mark.parametrize("J2", [0.0, 1.0])
 def test_c4_local_energies(cuda, precision, tol, J2):
     """E_loc of the 10x10 tensorized GRU, 100 units, square (J2=0) and triangular (J2=1) lattices, prefix reuse on and
@@ -63,7 +63,7 @@ def test_c4_tc_local_energies_random_init(cuda):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("precision,gtol", [("tc", 1e-2), ("fp32", 1e-4)])
+@pytest.mark.parametrize("precision,gtol", [("tc", 1e-2), ("tc3", 1e-2), ("fp32", 1e-4)])
 def test_c4_backward_vs_autograd(cuda, precision, gtol):
     """Backward at the benchmarked size (7 column passes / 7 K-chunks, 3 tiles): every parameter tensor against the
     oracle's autograd of the reference cost (complex cost + annealing term), within gtol of the tensor's largest entry."""
@@ -122,8 +122,8 @@ def test_c5_8x8_sample_and_logp_vs_oracle(cuda):
     with torch.no_grad():
         ref = oracle_run(eng, P, uniforms=u, numsamples=ns)
         ref2 = oracle_run(eng, P, samples=s.cpu().numpy())
-    ok = (ref["margin"].min(dim=1).values > 1e-3).numpy()
-    assert ok.mean() > 0.5
+    ok = (ref["margin"].min(dim=1).values > 1e-3).numpy()      # 64 eight-way draws per row: many rows come within 1e-3 of a threshold
+    assert ok.mean() > 0.25
     assert (s.cpu().long().numpy()[ok] == ref["samples"].numpy()[ok]).all()
     assert_rel(lp.cpu().numpy(), ref2["logp"].numpy(), 1e-3, "C5 8x8 logP tc")
     lp2, _ = eng.logpsi(s)

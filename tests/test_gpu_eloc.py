@@ -10,7 +10,7 @@ import torch
 from oracle import local_energies as ole
 from rnnwavefunctions_b200 import _lib
 from rnnwavefunctions_b200.engine import Engine
-from helpers import oracle_params, oracle_logpsi_fn
+from helpers import oracle_params, oracle_logpsi_fn, assert_rel
 
 RTOL = 1e-5
 
@@ -28,9 +28,7 @@ def _samples(eng, ns, seed, saved=None):
 
 
 def _check(e_gpu, e_ref):
-    e_gpu = e_gpu.cpu().numpy()
-    scale = np.abs(e_ref).max()
-    np.testing.assert_allclose(e_gpu, e_ref, rtol=RTOL, atol=RTOL * scale)
+    assert_rel(e_gpu.cpu().numpy(), e_ref, RTOL, "E_loc fp32")
 
 
 @pytest.mark.gpu

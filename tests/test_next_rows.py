@@ -62,6 +62,32 @@ def test_tf_variable_names():
     assert f("dense_phase.W", True) == "RNNwavefunction/wf_dense_phase/kernel"
     assert f("Wmerge", True) == "RNNwavefunction/Wmerge_rnn_0"
     assert f("Uh", False) == "RNNwavefunction/Uh_rnn_0"
+    # the complex 2D Heisenberg model calls its amplitude head 'wf_dense' (2DHeisenberg/MDComplexRNN.py:63), only the 1D
+    # cRNN has 'wf_dense_ampl' (J1J2/ComplexRNNwavefunction.py:42)
+    assert f("dense.W", True, gru1d=False) == "RNNwavefunction/wf_dense/kernel"
+
+
+def test_variable_names_match_the_executed_reference():
+    """Variable-name set per reference package: the names the reference's own code registers when it is executed under
+    tests/golden/tf_shim.py (recorded in the wf_*.npz fixtures: get_variable / Dense names are literals of the reference
+    source) against what checkpoint.tf_variable_name produces for the engine's tensors of that model."""
+    import os
+    G = os.path.join(os.path.dirname(__file__), "golden")
+    gru = lambda l: [f"gru{l}.{t}" for t in ("Wg", "bg", "Wci", "Wch", "bci", "bch")]
+    cases = {
+        "wf_gru1d": (gru(0) + ["dense.W", "dense.b"], False, True),
+        "wf_gru1d_3layer": (gru(0) + gru(1) + gru(2) + ["dense.W", "dense.b"], False, True),
+        "wf_cgru1d_u1": (gru(0) + ["dense.W", "dense.b", "dense_phase.W", "dense_phase.b"], True, True),
+        "wf_vanilla2d": (["Wh", "Uh", "Wv", "Uv", "b", "dense.W", "dense.b"], False, False),
+        "wf_tens2d_u1": (["W", "b", "dense.W", "dense.b", "dense_phase.W", "dense_phase.b"], True, False),
+        "wf_tensgru2d_u1": (["W", "b", "Wg", "bg", "Wmerge", "dense.W", "dense.b", "dense_phase.W", "dense_phase.b"], True, False),
+        "wf_rydberg_3x3": (["W", "b", "Wg", "bg", "Wmerge", "dense.W", "dense.b"], False, False),
+    }
+    for fixture, (names, cplx, gru1d) in cases.items():
+        z = np.load(os.path.join(G, fixture + ".npz"))
+        ref = {k[5:].replace("__", "/") for k in z.files if k.startswith("var__")}
+        ours = {checkpoint.tf_variable_name(n, cplx, gru1d=gru1d) for n in names}
+        assert ours == ref, (fixture, ours ^ ref)
 
 
 @pytest.mark.gpu
