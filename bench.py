@@ -11,11 +11,15 @@ metric  = E_loc configurations per second (1 diagonal + every connected configur
 value   : inputs resident in HBM (Philox uniforms generated in-kernel).
 e2e     : same step through the reference-facing API with HOST buffers: pinned uniforms H2D, samples and
           local energies D2H (as the reference's sess.run fetches), Eloc fed back H2D for the backward.
-roofline: the dominant kernel (connected-configuration sweep).  It runs FP32 FFMA in this round, so the bound
-          is the FP32-FFMA peak measured live by a probe kernel; the fraction of the measured bf16
-          tensor peak is given beside it for context.
+roofline: the dominant kernel (connected-configuration sweep).  The headline runs the tcgen05 tensor-core regime with
+          FP16 operands (north_star's reduced-precision mode, 1e-3 bound): tensor bound, executed MMA flops over the
+          measured sustained 16-bit peak of MEASURED_PEAKS.json.  The split-precision regime (tc3, 1e-5 bound) and the
+          FFMA regime (fp32, bound = FFMA peak measured live by a probe kernel) are reported under "workloads" together
+          with the other configurations of BASELINE.json (N = 1).
+scaling : "weak" (numsamples per GPU fixed) by default; at N > 1 the line also carries "strong_scaling" (the N = 1
+          batch sharded over the ranks); --scaling strong makes that the headline instead.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload NAME]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload NAME] [--precision P] [--scaling S]
 """
 import argparse
 import json
@@ -41,6 +45,8 @@ WORKLOADS = {
                                  desc="2DHeisenberg 10x10 square (J2=0) tensorized complex GRU, 100 units, U(1) Sz=0, 1e4 samples/step/GPU"),
     "tfim1d_n20_gru50": dict(eng=dict(cell="GRU1D", nx=20, ny=1, num_units=50, num_layers=1), ham="TFIM1D",
                              hp=[1.0] + [1.0] * 19, ns=500, desc="1DTFIM N=20 pRNN GRU 1x50, 500 samples/step/GPU"),
+    "tfim1d_n20_gru50x3": dict(eng=dict(cell="GRU1D", nx=20, ny=1, num_units=50, num_layers=3), ham="TFIM1D",
+                               hp=[1.0] + [1.0] * 19, ns=500, desc="1DTFIM N=20 pRNN GRU 3x50 (BASELINE.json config 1), 500 samples/step/GPU"),
     "j1j2_n20_cgru50": dict(eng=dict(cell="GRU1D", nx=20, ny=1, num_units=50, complex_head=True, u1=True), ham="J1J2",
                             hp=[0.0, 0.0] + [1.0] * 20 + [0.2] * 20 + [0.0] * 20, ns=500,
                             desc="J1J2 N=20 cRNN GRU 50, J2=0.2, U(1), 500 samples/step/GPU"),
@@ -327,95 +333,48 @@ def cpu_baseline(w, target_s=15.0):
 
 
 # ------------------------------------------------------------------------------------------------------
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
-    ap.add_argument("--numsamples", type=int, default=None)
-    ap.add_argument("--precision", default="auto", choices=["auto", "fp32", "tc", "tc3"],
-                    help="sweep regime: fp32 = FFMA (1e-5 parity), tc = tcgen05 FP16-operand tensor-core sweep (1e-3 bound); "
-                         "auto = tc where it exists (tensorized 2D GRU), fp32 otherwise")
-    ap.add_argument("--no-prefix-reuse", action="store_true")
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-e2e", action="store_true")
-    args = ap.parse_args()
-    w = dict(WORKLOADS[args.workload])
-    if args.numsamples:
-        w["ns"] = args.numsamples
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    metric, unit = "vmc_eloc_configs_per_s", "eloc_configs/s"
-    config = {"workload": f"{args.workload}: {w['desc']}", "numsamples_per_gpu": w["ns"],
-              "parallelism": f"dp{world} (samples sharded, weights replicated)",
-              "l2": "per-step working set (saved hidden states + gates of the samples, ~2 GB) exceeds the 126 MB L2; no explicit flush"}
+# measurement of one workload on this rank's GPU
+# ------------------------------------------------------------------------------------------------------
+DTYPE = {"tc": "f16 operands / f32 accumulate (tcgen05); heads, log psi, E_loc in f32/f64",
+         "tc3": "f16 hi+lo operand pairs (22 mantissa bits), 3 MMAs per K step, f32 accumulate (tcgen05); heads, log psi, E_loc in f32/f64",
+         "fp32": "f32"}
+# default regime per cell: the fast tensor-core regime (1e-3 bound) where it holds that bound at the benchmarked size
+# (tests/test_gpu_bench_size.py), the split-precision one for the vanilla 2D RNN (plain FP16 operands measure ~1e-2 at
+# 12x12, tools/cmp_regimes.py), FFMA for the 1D models
+AUTO_PRECISION = {"TENSGRU2D": "tc", "TENS2D": "tc", "GRU4": "tc", "VANILLA2D": "tc3", "GRU1D": "fp32"}
 
-    if args.impl == "reference":
-        # The reference's own implementation needs TensorFlow 1.13.1 (unavailable on this box): the timed arm is
-        # the oracle port of its algorithm on the host cores, on a bounded sample of the same workload.
-        if rank != 0:
-            return
-        cores = os.cpu_count() or 1
-        torch.set_num_threads(cores)
-        ns_ref = 48 if "heis" in args.workload else min(w["ns"], 64)
-        for _ in range(max(0, min(args.warmup, 1))):
-            oracle_step(w, 2)
-        tot_c, tot_t = 0, 0.0
-        for k in range(args.steps):
-            c, dt, br = oracle_step(w, ns_ref, seed=k)
-            tot_c += c
-            tot_t += dt
-        val = tot_c / tot_t
-        line = {"impl": "reference", "metric": metric, "value": val, "unit": unit, "n_gpus": args.gpus, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
-                "cpu_baseline": {"value": val, "unit": unit, "cores": cores, "kind": "port",
-                                 "sample": f"{ns_ref} samples/step of the same workload ({tot_c // args.steps} configurations/step), oracle port, torch float64, {cores} threads"},
-                "e2e": {"value": val, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line), flush=True)
-        return
 
-    import torch.distributed as dist
-    if local_rank == 0:
-        import __graft_entry__ as _g
-        _g.build()                      # no-op when librnnwf.so is newer than its sources
-    from rnnwavefunctions_b200 import _lib
-    from rnnwavefunctions_b200.engine import Engine
-    from rnnwavefunctions_b200 import vmc
+def ev():
+    return torch.cuda.Event(enable_timing=True)
 
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    ek = dict(w["eng"])
-    ek["cell"] = getattr(_lib, "CELL_" + ek["cell"])
-    precision = args.precision
-    if precision == "auto":
-        precision = "tc" if w["eng"]["cell"] in ("TENSGRU2D", "VANILLA2D", "GRU4") else "fp32"
-    eng = Engine(seed=111, precision=precision, **ek)
-    ham = getattr(_lib, "HAM_" + w["ham"])
-    ns = w["ns"]
-    V = vmc.VMC(eng, ham, w["hp"], ns, lr=5e-4, seed=111, prefix_reuse=not args.no_prefix_reuse)
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+class Bench:
+    """One workload in one precision regime on the current device: the resident step, its phases and its roofline."""
 
-    ev = lambda: torch.cuda.Event(enable_timing=True)
-    phase_ms = {"sample": 0.0, "eloc": 0.0, "backward": 0.0}
-    nconn_total = [0]
+    def __init__(self, name, precision, ns=None, prefix_reuse=True):
+        from rnnwavefunctions_b200 import _lib, vmc
+        from rnnwavefunctions_b200.engine import Engine
+        self._lib = _lib
+        self.name = name
+        self.w = dict(WORKLOADS[name])
+        if ns:
+            self.w["ns"] = int(ns)
+        self.ns = self.w["ns"]
+        ek = dict(self.w["eng"])
+        ek["cell"] = getattr(_lib, "CELL_" + ek["cell"])
+        self.precision = AUTO_PRECISION[self.w["eng"]["cell"]] if precision == "auto" else precision
+        self.eng = Engine(seed=111, precision=self.precision, **ek)
+        self.ham = getattr(_lib, "HAM_" + self.w["ham"])
+        self.V = vmc.VMC(self.eng, self.ham, self.w["hp"], self.ns, lr=5e-4, seed=111, prefix_reuse=prefix_reuse)
 
-    def step_resident(timed):
+    def step(self):
+        eng, V, ns = self.eng, self.V, self.ns
         e0, e1, e2, e3 = ev(), ev(), ev(), ev()
         offset = (V.it * V.world + V.rank) * ns
         e0.record()
         s, lp, ph = eng.sample(ns, seed=111, row_offset=offset, saved=V.saved)
         e1.record()
-        e, cnt = eng.local_energies(ham, w["hp"], s, lp, ph, saved=V.saved if V.prefix_reuse else None, return_count=True)
+        e, cnt = eng.local_energies(self.ham, self.w["hp"], s, lp, ph, saved=V.saved if V.prefix_reuse else None, return_count=True)
         e2.record()
         grad, mean_e, var = V.gradient(s, lp, ph, e)
         V.opt.step(eng.params, grad, V.lr)
@@ -424,148 +383,106 @@ def main():
         V.it += 1
         return (e0, e1, e2, e3), cnt, s
 
-    # rank 0 alone samples the clocks (of its own GPU); the sampler is set up (NVML initialised) before the warm-up steps
-    clocks = ClockSampler(local_rank) if rank == 0 else None
-    for _ in range(args.warmup):
-        step_resident(False)
-    barrier()
-    launches0 = _lib.lib.rnnwf_launch_count()
-    if clocks is not None:
-        clocks.start()
-    t_start, t_end = ev(), ev()
-    recs = []
-    barrier()
-    t_start.record()
-    for _ in range(args.steps):
-        recs.append(step_resident(True))
-    t_end.record()
-    barrier()
-    clk = clocks.stop() if clocks is not None else {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-    launches = _lib.lib.rnnwf_launch_count() - launches0
-    elapsed_ms = t_start.elapsed_time(t_end)
-    nconf_local = 0
-    for (e0, e1, e2, e3), cnt, s in recs:
-        phase_ms["sample"] += e0.elapsed_time(e1)
-        phase_ms["eloc"] += e1.elapsed_time(e2)
-        phase_ms["backward"] += e2.elapsed_time(e3)
-        nconf_local += int(cnt) + ns
-    tmax = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
-    tot = torch.tensor([float(nconf_local), float(ns * args.steps)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-    elapsed_ms = float(tmax)
-    value = float(tot[0]) / (elapsed_ms * 1e-3)
-    samples_per_s = float(tot[1]) / (elapsed_ms * 1e-3)
+    def run(self, steps, warmup, barrier, clocks=None):
+        """W untimed + K timed steps, CUDA events on the launching stream, barrier + synchronize on both sides."""
+        for _ in range(warmup):
+            self.step()
+        barrier()
+        launches0 = self._lib.lib.rnnwf_launch_count()
+        if clocks is not None:
+            clocks.start()
+        t_start, t_end = ev(), ev()
+        recs = []
+        barrier()
+        t_start.record()
+        for _ in range(steps):
+            recs.append(self.step())
+        t_end.record()
+        barrier()
+        clk = clocks.stop() if clocks is not None else None
+        out = {"elapsed_ms": t_start.elapsed_time(t_end), "launches": int(self._lib.lib.rnnwf_launch_count() - launches0),
+               "phase_ms": {"sample": 0.0, "eloc": 0.0, "backward": 0.0}, "nconf": 0, "clocks": clk, "steps": steps}
+        for (e0, e1, e2, e3), cnt, s in recs:
+            out["phase_ms"]["sample"] += e0.elapsed_time(e1) / steps
+            out["phase_ms"]["eloc"] += e1.elapsed_time(e2) / steps
+            out["phase_ms"]["backward"] += e2.elapsed_time(e3) / steps
+            out["nconf"] += int(cnt) + self.ns
+        out["s_last"], out["nchild"] = recs[-1][2], int(recs[-1][1])
+        return out
 
     # ---- roofline of the dominant kernel (the connected-configuration sweep inside local_energies)
-    s_last = recs[-1][2]
-    nchild = int(recs[-1][1])
-    eloc_ms = phase_ms["eloc"] / args.steps
-    fl_site = executed_flops_per_step_site(w)
-    T = eng.nsteps
-    if V.prefix_reuse:
-        # executed sites per child = T - (generation step of its first changed symbol); recomputed here from
-        # the samples exactly as the device enumeration orders them (measurement only, outside the timed region)
-        exec_sites = executed_sites(w, s_last.cpu().numpy(), eng)
-    else:
-        exec_sites = nchild * T
-    exec_flops = exec_sites * fl_site
-    alg_flops = (nchild) * T * flops_per_site(w)
-    probe_out = torch.zeros(4, dtype=torch.float32, device=dev)
-    import ctypes as C
-    best = 0.0
-    blocks, iters = 148 * 4, 20000
-    for _ in range(5):
-        a, b = ev(), ev()
-        a.record()
-        _lib.lib.rnnwf_ffma_probe(C.c_void_p(probe_out.data_ptr()), blocks, iters, C.c_void_p(torch.cuda.current_stream().cuda_stream))
-        b.record()
-        torch.cuda.synchronize()
-        best = max(best, blocks * 512 * iters * 16 * 2 / (a.elapsed_time(b) * 1e-3) / 1e12)
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    bf16_peak = peaks.get("bf16_tflops_sustained", 1400.0)
-    if precision == "tc" and w["eng"]["cell"] == "GRU4":
-        # sweep_tc4_kernel: per row and unit cell the dense [(live neighbours)*nhq + 32] x [3*nhq] contraction, nhq = 64*passes;
-        # a child flipped in cell t re-runs cells t..T-1 (prefix reuse), three children per cell and sample
-        nx, ny, nh = w["eng"]["nx"], w["eng"]["ny"], w["eng"]["num_units"]
-        nhq = (nh + 63) // 64 * 64
-        step = lambda ix, iy: iy * nx + (ix if iy % 2 == 0 else nx - 1 - ix)
-        site_flops = []
-        for iy in range(ny):
-            for k in range(nx):
-                ix = k if iy % 2 == 0 else nx - 1 - k
-                d = 1 if iy % 2 == 0 else -1
-                t = iy * nx + k
-                keys = [(ix - d, iy), (ix, iy - 1), ((ix + d) % nx, iy), (ix, (iy + 1) % ny)]
-                live = sum(1 for (a, b) in keys if 0 <= a < nx and 0 <= b < ny and step(a, b) < t)
-                site_flops.append(2 * (live * nhq + 32) * 3 * nhq + 2 * nh * 8)
-        suffix = np.cumsum(site_flops[::-1])[::-1]
-        per_sample = 3 * float(suffix.sum()) if V.prefix_reuse else 3 * T * float(suffix[0])
-        exec_flops = ns * per_sample
+    def roofline(self, res, peaks, ffma_peak):
+        w, eng, V, precision, ns = self.w, self.eng, self.V, self.precision, self.ns
+        eloc_ms = res["phase_ms"]["eloc"]
+        nchild = res["nchild"]
+        T = eng.nsteps
+        exec_sites = executed_sites(w, res["s_last"].cpu().numpy(), eng) if V.prefix_reuse else nchild * T
+        exec_flops = exec_sites * executed_flops_per_step_site(w)
+        alg_flops = nchild * T * flops_per_site(w)
+        bf16_peak = peaks.get("bf16_tflops_sustained", 1400.0)
+        peak_src = ("MEASURED_PEAKS.json bf16_tflops_sustained (16-bit tensor peak, kernel timed inside a long step)"
+                    if peaks else "fallback 1400 (B200_PROFILING.md)")
+        common = {"algorithmic_flops_per_launch": alg_flops, "algorithmic_tflops": alg_flops / (eloc_ms * 1e-3) / 1e12,
+                  "ffma_peak_tflops_measured": ffma_peak, "launch_ms": eloc_ms}
+        if precision == "tc" and w["eng"]["cell"] == "GRU4":
+            # sweep_tc4_kernel: per row and unit cell the dense [(live neighbours)*nhq + 32] x [3*nhq] contraction, nhq = 64*passes;
+            # a child flipped in cell t re-runs cells t..T-1 (prefix reuse), three children per cell and sample
+            nx, ny, nh = w["eng"]["nx"], w["eng"]["ny"], w["eng"]["num_units"]
+            nhq = (nh + 63) // 64 * 64
+            stepi = lambda ix, iy: iy * nx + (ix if iy % 2 == 0 else nx - 1 - ix)
+            site_flops = []
+            for iy in range(ny):
+                for k in range(nx):
+                    ix = k if iy % 2 == 0 else nx - 1 - k
+                    d = 1 if iy % 2 == 0 else -1
+                    t = iy * nx + k
+                    keys = [(ix - d, iy), (ix, iy - 1), ((ix + d) % nx, iy), (ix, (iy + 1) % ny)]
+                    live = sum(1 for (a, b) in keys if 0 <= a < nx and 0 <= b < ny and stepi(a, b) < t)
+                    site_flops.append(2 * (live * nhq + 32) * 3 * nhq + 2 * nh * 8)
+            suffix = np.cumsum(site_flops[::-1])[::-1]
+            per_sample = 3 * float(suffix.sum()) if V.prefix_reuse else 3 * T * float(suffix[0])
+            exec_flops = ns * per_sample
+            achieved = exec_flops / (eloc_ms * 1e-3) / 1e12
+            return dict(common, bound="tensor", kernel="sweep_tc4_kernel (MODE_CHILD)", achieved=achieved, peak=bf16_peak, unit="TFLOP/s",
+                        frac=achieved / bf16_peak, traffic=None, peak_source=peak_src, executed_flops_per_launch=exec_flops,
+                        mma_columns_per_row_site=3 * nhq,
+                        note="executed = MMA flops issued per row (absent neighbours skipped, hidden axis padded to 64 per pass, K=32 "
+                             "input/bias job, prefix reuse counted per row); launch_ms brackets rnnwf_local_energies (enumeration kernels + sweep)")
+        if precision in ("tc", "tc3"):
+            # the tensor-core sweep executes, per row and site, the dense [2*nhp] x [7*16*passes] contraction
+            nhp = (w["eng"]["num_units"] + 7) // 8 * 8
+            npass = (w["eng"]["num_units"] + 15) // 16
+            subs_last = (w["eng"]["num_units"] - 16 * (npass - 1) + 3) // 4       # the last column pass is issued only as wide as its real units
+            ncols = 112 * (npass - 1) + (28 * subs_last + 15) // 16 * 16
+            if w["eng"]["cell"] == "VANILLA2D":
+                ncols = 112                                                       # one pass per site: 7 unit pieces x 4 threads x 4 units
+            mma_per_kstep = 3 if precision == "tc3" else 1          # split precision: A_hi B_hi + A_lo B_hi + A_hi B_lo
+            exec_flops = exec_sites * (mma_per_kstep * 2 * (2 * nhp) * ncols + 2 * w["eng"]["num_units"] * 4)
+            achieved = exec_flops / (eloc_ms * 1e-3) / 1e12
+            return dict(common, bound="tensor", kernel=f"sweep_tc_kernel (MODE_CHILD{', split precision' if precision == 'tc3' else ''})",
+                        achieved=achieved, peak=bf16_peak, unit="TFLOP/s", frac=achieved / bf16_peak, traffic=None, peak_source=peak_src,
+                        executed_flops_per_launch=exec_flops, mma_columns_per_row_site=ncols,
+                        note="executed = MMA flops actually issued (linearised class trick: 7 accumulator blocks per unit, narrow last pass; "
+                             "split precision: three MMAs per K step, all counted; prefix reuse counted); launch_ms brackets "
+                             "rnnwf_local_energies (enumeration kernels + sweep; the sweep is >99%)")
         achieved = exec_flops / (eloc_ms * 1e-3) / 1e12
-        # traffic: dram__bytes_read.sum + dram__bytes_write.sum of this kernel from the committed ncu --set full capture
-        # (profiles/r1h_c5_summary.md), valid for the 4x4-cell / 12 500-sample workload it was taken on
-        traffic = 8.31e9 if (nx == 4 and ny == 4 and nh == 256 and ns == 12500) else None
-        roofline = {"bound": "tensor", "kernel": "sweep_tc4_kernel (MODE_CHILD)", "achieved": achieved, "peak": bf16_peak, "unit": "TFLOP/s",
-                    "frac": achieved / bf16_peak, "traffic": traffic, "traffic_source": "profiles/r1h_c5_summary.md (ncu --set full, one launch)" if traffic else None,
-                    "peak_source": ("MEASURED_PEAKS.json bf16_tflops_sustained (16-bit tensor peak, kernel timed inside a long step)"
-                                    if peaks else "fallback 1400 (B200_PROFILING.md)"),
-                    "executed_flops_per_launch": exec_flops, "algorithmic_flops_per_launch": alg_flops,
-                    "algorithmic_tflops": alg_flops / (eloc_ms * 1e-3) / 1e12, "ffma_peak_tflops_measured": best,
-                    "launch_ms": eloc_ms, "mma_columns_per_row_site": 3 * nhq,
-                    "note": "executed = MMA flops issued per row (absent neighbours skipped, hidden axis padded to 64 per pass, K=32 input/bias "
-                            "job, prefix reuse counted per row); launch_ms brackets rnnwf_local_energies (enumeration kernels + sweep)"}
-    elif precision in ("tc", "tc3"):
-        # the tensor-core sweep executes, per row and site, the dense [2*nhp] x [7*16*passes] contraction
-        nhp = (w["eng"]["num_units"] + 7) // 8 * 8
-        npass = (w["eng"]["num_units"] + 15) // 16
-        subs_last = (w["eng"]["num_units"] - 16 * (npass - 1) + 3) // 4       # the last column pass is issued only as wide as its real units
-        ncols = 112 * (npass - 1) + (28 * subs_last + 15) // 16 * 16
-        if w["eng"]["cell"] == "VANILLA2D":
-            ncols = 112                                                       # one pass per site: 7 unit pieces x 4 threads x 4 units
-        mma_per_kstep = 3 if precision == "tc3" else 1          # split precision: A_hi B_hi + A_lo B_hi + A_hi B_lo
-        exec_flops = exec_sites * (mma_per_kstep * 2 * (2 * nhp) * ncols + 2 * w["eng"]["num_units"] * 4)
-        achieved = exec_flops / (eloc_ms * 1e-3) / 1e12
-        # traffic: dram bytes read + written by this kernel in the committed ncu --set full capture (profiles/r1e_summary.md:
-        # 5.17 GB + 12.33 GB, write-back of the history ring), valid for the C4 triangular workload it was taken on
-        traffic = 17.5e9 if (args.workload == DEFAULT_WORKLOAD and precision == "tc") else None
-        roofline = {"bound": "tensor", "kernel": "sweep_tc_kernel (MODE_CHILD)", "achieved": achieved, "peak": bf16_peak, "unit": "TFLOP/s",
-                    "frac": achieved / bf16_peak, "traffic": traffic, "traffic_source": "profiles/r1e_summary.md (ncu --set full, one launch)" if traffic else None,
-                    "peak_source": ("MEASURED_PEAKS.json bf16_tflops_sustained (16-bit tensor peak, kernel timed inside a long step)"
-                                    if peaks else "fallback 1400 (B200_PROFILING.md)"),
-                    "executed_flops_per_launch": exec_flops, "algorithmic_flops_per_launch": alg_flops,
-                    "algorithmic_tflops": alg_flops / (eloc_ms * 1e-3) / 1e12, "ffma_peak_tflops_measured": best,
-                    "launch_ms": eloc_ms,
-                    "mma_columns_per_row_site": ncols,
-                    "note": "executed = MMA flops actually issued (linearised class trick: 7 accumulator blocks per unit, narrow last pass; "
-                            "prefix reuse counted); launch_ms brackets rnnwf_local_energies (enumeration kernels + sweep; the sweep is >99%)"}
-    else:
-        achieved = exec_flops / (eloc_ms * 1e-3) / 1e12
-        roofline = {"bound": "fp32-ffma", "kernel": "sweep_kernel (MODE_CHILD)", "achieved": achieved, "peak": best, "unit": "TFLOP/s",
-                    "frac": achieved / best if best > 0 else None, "traffic": None,
-                    "peak_source": "measured live: rnnwf_ffma_probe (16 FMA chains/thread, 592x512 threads), best of 5",
-                    "executed_flops_per_launch": exec_flops, "algorithmic_flops_per_launch": alg_flops,
-                    "algorithmic_tflops": alg_flops / (eloc_ms * 1e-3) / 1e12,
-                    "frac_of_bf16_tensor_peak": achieved / bf16_peak,
-                    "bf16_peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1400",
-                    "launch_ms": eloc_ms, "note": "launch_ms brackets rnnwf_local_energies (enumeration kernels + sweep; the sweep is >99% of it)"}
+        return dict(common, bound="fp32-ffma", kernel="sweep_kernel (MODE_CHILD)", achieved=achieved, peak=ffma_peak, unit="TFLOP/s",
+                    frac=achieved / ffma_peak if ffma_peak > 0 else None, traffic=None,
+                    peak_source="measured live: rnnwf_ffma_probe (16 FMA chains/thread, 592x512 threads), best of 5",
+                    executed_flops_per_launch=exec_flops, frac_of_bf16_tensor_peak=achieved / bf16_peak,
+                    note="launch_ms brackets rnnwf_local_energies (enumeration kernels + sweep; the sweep is >99% of it)")
 
     # ---- end to end through the reference-facing API with host buffers
-    e2e = None
-    if not args.no_e2e:
-        K = max(1, min(args.steps, 3))
+    def e2e(self, K, barrier, world, dev):
+        import torch.distributed as dist
+        eng, V, w, ns, ham = self.eng, self.V, self.w, self.ns, self.ham
         pinned_u = torch.rand(ns, eng.nsteps, dtype=torch.float32).pin_memory()
         host_s = torch.empty((ns,) + eng.cfg_shape, dtype=torch.int8).pin_memory()
         host_e = torch.empty(ns, dtype=torch.complex128).pin_memory()
         host_eloc_in = torch.empty(ns, dtype=torch.complex128).pin_memory()
         h2d = pinned_u.numel() * 4 + host_eloc_in.numel() * 16 + host_s.numel()
         d2h = host_s.numel() + host_e.numel() * 16 + 16
-        nconf_e2e = 0
+        nconf = 0
         barrier()
         a, b = ev(), ev()
         a.record()
@@ -577,38 +494,205 @@ def main():
             host_e.copy_(e, non_blocking=True)
             torch.cuda.synchronize()                       # the reference's sess.run returns numpy arrays here
             host_eloc_in.copy_(host_e)                     # meanE / varE on the host, Eloc fed back (optstep feed_dict)
-            mean_host = complex(host_e.mean())
+            _ = complex(host_e.mean())
             s_dev = host_s.to(dev, non_blocking=True)
             e_dev = host_eloc_in.to(dev, non_blocking=True)
             grad, mean_e, var = V.gradient(s_dev, lp, ph, e_dev)
             V.opt.step(eng.params, grad, V.lr)
             eng.set_weights()
             _ = complex(mean_e)                            # D2H of the step's result
-            nconf_e2e += int(cnt) + ns
+            nconf += int(cnt) + ns
         b.record()
         barrier()
         t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
-        c = torch.tensor([float(nconf_e2e)], dtype=torch.float64, device=dev)
+        c = torch.tensor([float(nconf)], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dist.all_reduce(c, op=dist.ReduceOp.SUM)
-        e2e = {"value": float(c) / (float(t) * 1e-3), "unit": unit, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-               "steps": K, "ms_per_step": float(t) / K}
+        return {"value": float(c) / (float(t) * 1e-3), "unit": "eloc_configs/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "steps": K, "ms_per_step": float(t) / K}
+
+
+def ffma_peak_probe(dev):
+    """FP32-FFMA throughput of this GPU, measured live (roofline denominator of the FFMA regime)."""
+    import ctypes as C
+    from rnnwavefunctions_b200 import _lib
+    probe_out = torch.zeros(4, dtype=torch.float32, device=dev)
+    best = 0.0
+    blocks, iters = 148 * 4, 20000
+    for _ in range(5):
+        a, b = ev(), ev()
+        a.record()
+        _lib.lib.rnnwf_ffma_probe(C.c_void_p(probe_out.data_ptr()), blocks, iters, C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        b.record()
+        torch.cuda.synchronize()
+        best = max(best, blocks * 512 * iters * 16 * 2 / (a.elapsed_time(b) * 1e-3) / 1e12)
+    return best
+
+
+# the other configurations of BASELINE.json and the other precision regimes of the headline one, measured in the same run
+# (N = 1 only; a few steps each) and reported under "workloads"
+EXTRA_WORKLOADS = [("tfim1d_n20_gru50", "auto"), ("tfim1d_n20_gru50x3", "auto"), ("j1j2_n20_cgru50", "auto"), ("tfim2d_12x12_rnn50", "auto"),
+                   ("heis10x10_sq_tgru100", "auto"), ("heis10x10_tri_tgru100", "tc3"), ("heis10x10_tri_tgru100", "fp32"),
+                   ("rydberg_4x4_gru256", "auto"), ("rydberg_8x8_gru256", "auto")]
+
+
+def reference_arm(args, w, config, metric, unit, rank):
+    """`--impl reference`: the reference's own implementation needs TensorFlow 1.13.1 (unavailable on this box), so the timed
+    arm is the oracle port of its algorithm on all host cores, each step a bounded sample of the same workload, large enough
+    that every chunked forward carries at least one full chunk of the reference's size (20 000 rows at C4)."""
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    ns_ref = 160 if "heis" in args.workload else min(w["ns"], 200 if "rydberg" in args.workload else 500)
+    for _ in range(max(0, min(args.warmup, 1))):
+        oracle_step(w, 2)
+    tot_c, tot_t = 0, 0.0
+    for k in range(args.steps):
+        c, dt, br = oracle_step(w, ns_ref, seed=k)
+        tot_c += c
+        tot_t += dt
+    val = tot_c / tot_t
+    line = {"impl": "reference", "metric": metric, "value": val, "unit": unit, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+            "cpu_baseline": {"value": val, "unit": unit, "cores": cores, "kind": "port",
+                             "sample": f"{ns_ref} samples/step of the same workload ({tot_c // args.steps} configurations/step), oracle port "
+                                       f"(oracle/: restated network forward + restated enumeration), torch float64, {cores} threads"},
+            "e2e": {"value": val, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+# ------------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
+    ap.add_argument("--numsamples", type=int, default=None)
+    ap.add_argument("--precision", default="auto", choices=["auto", "fp32", "tc", "tc3"],
+                    help="sweep regime: fp32 = FFMA (1e-5 parity), tc = tcgen05 FP16-operand sweep (1e-3 bound), tc3 = tcgen05 "
+                         "split-precision sweep (1e-5 parity); auto = the default regime of the cell (AUTO_PRECISION)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: numsamples per GPU fixed (default); strong: numsamples is the GLOBAL batch, sharded over the ranks")
+    ap.add_argument("--no-prefix-reuse", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the other workloads / regimes reported under 'workloads' (N = 1)")
+    args = ap.parse_args()
+    w = dict(WORKLOADS[args.workload])
+    if args.numsamples:
+        w["ns"] = args.numsamples
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    metric, unit = "vmc_eloc_configs_per_s", "eloc_configs/s"
+    ns_global = w["ns"] if args.scaling == "strong" else w["ns"] * world
+    ns_rank = w["ns"] // world if args.scaling == "strong" else w["ns"]
+    config = {"workload": f"{args.workload}: {w['desc']}", "numsamples_per_gpu": ns_rank, "numsamples_global": ns_global,
+              "parallelism": f"dp{world} (samples sharded, weights replicated)",
+              "l2": "per-step working set (saved hidden states + gates of the samples, ~2 GB) exceeds the 126 MB L2; no explicit flush"}
+
+    if args.impl == "reference":
+        reference_arm(args, w, config, metric, unit, rank)
+        return
+
+    import torch.distributed as dist
+    if local_rank == 0:
+        import __graft_entry__ as _g
+        _g.build()                      # no-op when librnnwf.so is newer than its sources
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    B = Bench(args.workload, args.precision, ns=ns_rank, prefix_reuse=not args.no_prefix_reuse)
+    precision = B.precision
+    # rank 0 alone samples the clocks (of its own GPU); the sampler is set up (NVML initialised) before the warm-up steps
+    clocks = ClockSampler(local_rank) if rank == 0 else None
+    res = B.run(args.steps, args.warmup, barrier, clocks)
+    clk = res["clocks"] or {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+    tmax = torch.tensor([res["elapsed_ms"]], dtype=torch.float64, device=dev)
+    tot = torch.tensor([float(res["nconf"]), float(ns_rank * args.steps)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    elapsed_ms = float(tmax)
+    value = float(tot[0]) / (elapsed_ms * 1e-3)
+    samples_per_s = float(tot[1]) / (elapsed_ms * 1e-3)
+
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    ffma_peak = ffma_peak_probe(dev)
+    roofline = B.roofline(res, peaks, ffma_peak)
+    if args.workload == DEFAULT_WORKLOAD and precision == "tc" and ns_rank == 10000:
+        roofline["traffic"] = NCU_TRAFFIC["bytes"]
+        roofline["traffic_source"] = NCU_TRAFFIC["source"]
+    e2e = None if args.no_e2e else B.e2e(max(1, min(args.steps, 3)), barrier, world, dev)
+
+    # strong scaling beside the weak number (N > 1, default mode): the same global batch as one GPU's, sharded over the ranks
+    strong = None
+    if world > 1 and args.scaling == "weak" and w["ns"] % world == 0:
+        Bs = Bench(args.workload, precision, ns=w["ns"] // world, prefix_reuse=not args.no_prefix_reuse)
+        rs = Bs.run(max(3, min(args.steps, 10)), 2, barrier)
+        t2 = torch.tensor([rs["elapsed_ms"]], dtype=torch.float64, device=dev)
+        c2 = torch.tensor([float(rs["nconf"])], dtype=torch.float64, device=dev)
+        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        dist.all_reduce(c2, op=dist.ReduceOp.SUM)
+        strong = {"numsamples_global": w["ns"], "numsamples_per_gpu": w["ns"] // world, "ms_per_step": float(t2) / rs["steps"],
+                  "value": float(c2) / (float(t2) * 1e-3), "unit": unit, "phase_ms_per_step": rs["phase_ms"],
+                  "note": "same global batch as the N=1 run, sharded; efficiency = value / (N * value at N=1)"}
+        del Bs
 
     if rank == 0:
         line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": ("f16 operands / f32 accumulate (tcgen05); heads, log psi, E_loc in f32/f64" if precision == "tc" else "f32"),
-                "precision_mode": precision, "data": "synthetic", "config": config, "samples_per_s": samples_per_s,
-                "phase_ms_per_step": {k: v / args.steps for k, v in phase_ms.items()},
-                "eloc_configs_per_step_per_gpu": nconf_local / args.steps, "gpu_launches": int(launches),
-                "clocks": clk, "roofline": roofline, "e2e": e2e, "engine": eng.describe(),
-                "prefix_reuse": V.prefix_reuse}
+                "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
+                "dtype": DTYPE[precision], "precision_mode": precision, "data": "synthetic", "config": config,
+                "samples_per_s": samples_per_s, "phase_ms_per_step": res["phase_ms"],
+                "eloc_configs_per_step_per_gpu": res["nconf"] / args.steps, "gpu_launches": res["launches"],
+                "clocks": clk, "roofline": roofline, "e2e": e2e, "engine": B.eng.describe(), "prefix_reuse": B.V.prefix_reuse}
+        if strong is not None:
+            line["strong_scaling"] = strong
+        if world == 1 and not args.no_extra and args.workload == DEFAULT_WORKLOAD and args.numsamples is None:
+            extra = {}
+            del B
+            torch.cuda.empty_cache()
+            for name, prec in EXTRA_WORKLOADS:
+                try:
+                    Bx = Bench(name, prec)
+                    rx = Bx.run(3, 2, barrier)
+                    rf = Bx.roofline(rx, peaks, ffma_peak)
+                    ms = rx["elapsed_ms"] / rx["steps"]
+                    extra[f"{name}:{Bx.precision}"] = {
+                        "desc": Bx.w["desc"], "precision_mode": Bx.precision, "dtype": DTYPE[Bx.precision], "ms_per_step": ms,
+                        "phase_ms_per_step": rx["phase_ms"], "eloc_configs_per_s": rx["nconf"] / (rx["elapsed_ms"] * 1e-3),
+                        "samples_per_s": Bx.ns * rx["steps"] / (rx["elapsed_ms"] * 1e-3), "gpu_launches_per_step": rx["launches"] / rx["steps"],
+                        "roofline": {k: rf[k] for k in ("bound", "kernel", "achieved", "peak", "unit", "frac")}, "steps": rx["steps"]}
+                    del Bx
+                    torch.cuda.empty_cache()
+                except Exception as exc:       # one workload failing must not lose the headline line
+                    extra[f"{name}:{prec}"] = {"error": f"{type(exc).__name__}: {exc}"}
+            line["workloads"] = extra
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(w)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum of one sweep_tc_kernel<MODE_CHILD> launch of the default workload, from the
+# committed `ncu --set full` capture named here (a constant of that capture, not a measurement of this run)
+NCU_TRAFFIC = {"bytes": 17.1e9, "source": "ncu --set full capture of commit 7ec878e (profiles/r1i_summary.md), one launch, 10^4 samples"}
 
 
 def executed_sites(w, samples, eng):

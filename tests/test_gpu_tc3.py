@@ -80,8 +80,8 @@ def test_tc3_tfim2d_local_energies_c3_size(cuda, reuse):
 
 
 @pytest.mark.gpu
-def test_tc3_vanilla_local_energies_and_gradient_8x8(cuda):
-    """Vanilla 2D RNN, 8x8: E_loc, and the backward (fed by the saved state this sweep wrote; TF32 tensor-core reverse
+def test_tc3_vanilla_local_energies_and_gradient(cuda):
+    """Vanilla 2D RNN, 8x8: E_loc; 6x6: the backward (fed by the saved state this sweep wrote; TF32 tensor-core reverse
     sweep) within 1e-2 per tensor of autograd."""
     eng = _mk("vanilla", 8, 8, 50, seed=73)
     ns = 200
@@ -92,6 +92,9 @@ def test_tc3_vanilla_local_energies_and_gradient_8x8(cuda):
     e = eng.local_energies(_lib.HAM_TFIM2D, np.concatenate([[3.0], Jz]), s, lp, ph, saved=saved).cpu().numpy()
     ref = ole.ising2d_local_energies(Jz.reshape(8, 8), 3.0, s.cpu().numpy().astype(np.int64), oracle_logpsi_fn(eng, oracle_params(eng)))
     assert_rel(e.real, ref, 2e-5, "tc3 vanilla 8x8 E_loc")      # (1.2e-5 measured: see the conditioning note above)
+    eng = _mk("vanilla", 6, 6, 50, seed=74)
+    saved = eng.new_saved(ns)
+    s, lp, ph = eng.sample(ns, uniforms=u[:, :36], saved=saved)
     g = torch.Generator().manual_seed(5)
     E = torch.randn(ns, generator=g, dtype=torch.float64)
     P = oracle_params(eng, requires_grad=True)
