@@ -103,6 +103,7 @@ struct SweepParams {
   int tc_np;
   unsigned long long* tc_prof;  // optional per-CTA cycle counters (debug)
   int debug_flags;                    // tensor-core sweep timing experiments (RNNWF_TC_DEBUG), 0 in production
+  const float* g1_pack;        // dedicated 1D-GRU kernels (gru1d.cuh): parameter image copied to shared memory
   // ---- scratch
   float* ring;              // [gridDim.x][ring_len][Mp][nhp]
 };

@@ -18,9 +18,16 @@
 #include "gemm_tc.cuh"
 #include "backward.cuh"
 #include "symmetry.cuh"
+#include "gru1d.cuh"
 
 using namespace rnnwf;
 
+namespace rnnwf {   // gru1d_inst.cu
+cudaError_t g1_set_smem(int smem_bytes);
+int g1_occupancy(int threads, int smem_bytes);
+cudaError_t g1_sweep_launch(const SweepParams& P, int grid, int threads, int smem_bytes, cudaStream_t st);
+cudaError_t g1_pack_launch(const G1PackSrc& S, int nh, int L, int N, int D, int ND, float* out, cudaStream_t st);
+}
 namespace rnnwf {   // sweep_tc_inst.cu
 cudaError_t tc_sweep_set_smem(int cellk, bool biasmma, bool split, int smem_bytes);
 cudaError_t tc_sweep_launch(const SweepParams& P, int cellk, bool biasmma, bool split, int grid, int threads, int smem_bytes, cudaStream_t st);
@@ -289,6 +296,8 @@ int build_model(rnnwf_model& m) {
   m.tc_enabled = (m.precision >= 1 && (m.cell == CELL_TENSGRU2D || m.cell == CELL_TENS2D || m.cell == CELL_VANILLA2D));
   m.tc_split = m.tc_enabled && m.precision == 2;
   m.tc4 = (m.precision == 1 && m.cell == CELL_GRU4);
+  // small 1D models in the FFMA regime: dedicated kernels with the whole weight set resident in shared memory (gru1d.cuh)
+  m.g1 = (m.precision == 0 && m.cell == CELL_GRU1D && g1_supported(m.nh, m.symL, m.Tsym) && std::getenv("RNNWF_NO_G1") == nullptr);
   if (m.precision == 1 && !m.tc_enabled && !m.tc4)
     return fail(RNNWF_EINVAL, "the tensor-core regime is implemented for the 2D cells (tensorized GRU, tensorized, vanilla RNN, four-neighbour GRU)");
   if (m.precision == 2 && !m.tc_enabled)
@@ -331,6 +340,12 @@ int max_ctas(const rnnwf_model& m) {
 }
 
 int pick_shape(const rnnwf_model& m, long long rows, LaunchShape& s) {
+  if (m.g1) {
+    const long long tiles = (rows + G1_ROWS - 1) / G1_ROWS;
+    s.WR = 2; s.Mp = G1_ROWS; s.Mr = G1_ROWS; s.threads = g1_threads(m.nh); s.smem = G1Layout(m.nh, m.symL, m.Tsym).total_bytes;
+    s.grid = (int)std::max(1LL, std::min<long long>(tiles, (long long)m.num_sms * m.g1_occ));
+    return RNNWF_OK;
+  }
   if (m.tc_enabled) {
     const TcSmem ts(m.nhp, m.Tsym, m.Q);
     const long long tiles = (rows + TC_ROWS - 1) / TC_ROWS;
@@ -375,7 +390,7 @@ void fill_model_params(const rnnwf_model& m, const LaunchShape& s, SweepParams& 
   P.ring_len = m.ring_len; P.WR = s.WR; P.WC = m.WC; P.Mp = s.Mp; P.Mr = s.Mr; P.ncls_max = m.ncls_max;
   P.steps = m.d_steps; P.variants = m.d_variants; P.Wpack = m.d_wpack; P.Xtab = m.d_xtab; P.bias = m.d_bias;
   P.head_w = m.d_head_w; P.head_b = m.d_head_b;
-  P.tc_B = m.d_tcB; P.tc_bias = m.d_tcbias; P.tc_np = m.tc_np; P.tc_prof = g_tc_prof;
+  P.tc_B = m.d_tcB; P.tc_bias = m.d_tcbias; P.tc_np = m.tc_np; P.tc_prof = g_tc_prof; P.g1_pack = m.d_g1pack;
   { const char* dbg = std::getenv("RNNWF_TC_DEBUG"); P.debug_flags = dbg ? std::atoi(dbg) : 0; }
 }
 
@@ -397,6 +412,12 @@ int launch_sweep_ffma(const rnnwf_model& m, const SweepParams& P, const LaunchSh
 
 int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& s, cudaStream_t st) {
   cudaError_t e;
+  if (m.g1) {
+    RNNWF_COUNT_LAUNCH();
+    e = g1_sweep_launch(P, s.grid, s.threads, s.smem, st);
+    if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("1D GRU sweep launch: ") + cudaGetErrorString(e));
+    return RNNWF_OK;
+  }
   if (m.tc_enabled) {
     RNNWF_COUNT_LAUNCH();
     const int cellk = (m.cell == CELL_VANILLA2D) ? 1 : (m.cell == CELL_TENS2D ? 2 : 0);
@@ -589,6 +610,12 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc4_kernel<MODE_EVAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, t4s));
     CREATE_TRY(cudaFuncSetAttribute(sweep_tc4_kernel<MODE_CHILD>, cudaFuncAttributeMaxDynamicSharedMemorySize, t4s));
   }
+  if (m->g1) {
+    const G1Layout Y(m->nh, m->symL, m->Tsym);
+    CREATE_TRY(cudaMalloc(&m->d_g1pack, (size_t)Y.pack_floats * 4));
+    CREATE_TRY(g1_set_smem(Y.total_bytes));
+    m->g1_occ = std::max(1, std::min(4, g1_occupancy(g1_threads(m->nh), Y.total_bytes)));
+  }
   CREATE_TRY(backward_init());
   if (m->tc4) {
     CREATE_TRY(backward_init_tc4(*m));
@@ -609,7 +636,7 @@ int rnnwf_destroy(rnnwf_handle h) {
   if (h == nullptr) return RNNWF_OK;
   cudaFree(h->d_steps); cudaFree(h->d_variants); cudaFree(h->d_site_of_t); cudaFree(h->d_wpack);
   cudaFree(h->d_xtab); cudaFree(h->d_bias); cudaFree(h->d_head_w); cudaFree(h->d_head_b);
-  cudaFree(h->d_tcB); cudaFree(h->d_tcbias); cudaFree(h->d_dw_jobs); cudaFree(h->d_dw_cls); cudaFree(h->d_dw4_jobs); cudaFree(h->d_dw4_sites);
+  cudaFree(h->d_g1pack); cudaFree(h->d_tcB); cudaFree(h->d_tcbias); cudaFree(h->d_dw_jobs); cudaFree(h->d_dw_cls); cudaFree(h->d_dw4_jobs); cudaFree(h->d_dw4_sites);
   delete h;
   return RNNWF_OK;
 }
@@ -678,6 +705,20 @@ int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
   RNNWF_COUNT_LAUNCH(); pack_head_kernel<<<cdiv((long long)h->nhp * h->ND, 256), 256, 0, st>>>(
       params_dev + wd->offset, params_dev + bd->offset, wp ? params_dev + wp->offset : nullptr,
       bp ? params_dev + bp->offset : nullptr, h->nh, h->nhp, h->D, h->ND, h->d_head_w, h->d_head_b);
+  if (h->g1) {
+    G1PackSrc S;
+    std::memset(&S, 0, sizeof(S));
+    for (int l = 0; l < h->symL; ++l) {
+      const std::string p = "gru" + std::to_string(l) + ".";
+      S.Wg[l] = params_dev + h->tensor(p + "Wg")->offset;   S.bg[l] = params_dev + h->tensor(p + "bg")->offset;
+      S.Wci[l] = params_dev + h->tensor(p + "Wci")->offset; S.Wch[l] = params_dev + h->tensor(p + "Wch")->offset;
+      S.bci[l] = params_dev + h->tensor(p + "bci")->offset; S.bch[l] = params_dev + h->tensor(p + "bch")->offset;
+    }
+    S.head_w = params_dev + wd->offset; S.head_b = params_dev + bd->offset;
+    S.phase_w = wp ? params_dev + wp->offset : nullptr; S.phase_b = bp ? params_dev + bp->offset : nullptr;
+    RNNWF_COUNT_LAUNCH();
+    CUDA_TRY(g1_pack_launch(S, h->nh, h->symL, h->Tsym, h->D, h->ND, h->d_g1pack, st));
+  }
   if (h->tc_enabled) {
     const TcSmem ts(h->nhp, h->Tsym, h->Q);
     if (h->cell == CELL_VANILLA2D) {
@@ -1249,6 +1290,7 @@ int rnnwf_describe(rnnwf_handle h, char* buf, int cap) {
                 "(TJ=%d NTU=%d WC=%d passes=%d), k-chunk=%d, ring=%d steps, params=%lld",
                 h->cell, h->nh, h->nhp, h->Q, h->Tsym, h->nslots, h->ncls_max,
                 h->tc_split ? "tcgen05 split precision: FP16 hi+lo operands, 3 MMAs per K step, FP32 accumulate in TMEM (column passes of 112, double-buffered)"
+                : h->g1 ? "FFMA fp32, dedicated 1D-GRU kernels: one launch per sweep, weights resident in shared memory"
                 : h->tc_enabled ? "tcgen05 FP16 operands, FP32 accumulate in TMEM (column passes of 112, double-buffered)"
                               : (h->tc4 ? "tcgen05 FP16 operands streamed from the L2 ring (A) and the weight image (B), FP32 accumulate in TMEM (column passes of 192, double-buffered)" : "FFMA fp32"), h->Gblk, h->TJ, h->NTU, h->WC, h->ncb, KC,
                 h->ring_len, (long long)h->num_params);
@@ -1343,6 +1385,6 @@ extern "C" int rnnwf_logpsi_static(rnnwf_handle h, int64_t rows, const int8_t* s
   fill_model_params(m, s, P);
   P.mode = MODE_EVAL; P.rows = rows; P.cfg_in = samples_dev; P.out_logp = logp_dev; P.out_phase = phase_dev;
   P.ring = ring;
-  // always the FP32 FFMA sweep, whatever the precision regime of the handle (the tensor-core sweeps size their ring differently)
+  // always the generic FP32 FFMA sweep, whatever the regime of the handle (the other sweeps size their scratch differently)
   return launch_sweep_ffma(m, P, s, static_cast<cudaStream_t>(stream));
 }
