@@ -13,6 +13,7 @@
 // weight gradients land directly in the TF parameter layout.  Backward runs on `numsamples` rows only,
 // i.e. ~1-3% of the rows a VMC step pushes through the forward sweep for its local energies.
 #pragma once
+#include "gru1d_bwd.cuh"
 #include <string>
 
 #include "model.h"
@@ -21,6 +22,7 @@
 #include "bwd_tc4.cuh"
 
 namespace rnnwf {
+cudaError_t g1_bwd_launch(const G1BwdParams& B, int grid, cudaStream_t st);     // gru1d_inst.cu
 
 // ------------------------------------------------------------------------------------------------
 // generic FP32 GEMM tiles (64x64x16, 256 threads, 4x4 per thread)
@@ -99,9 +101,11 @@ __global__ void __launch_bounds__(256) gemm_nn_kernel(const float* __restrict__ 
 }
 
 // C[K1,N] += A[M,K1]^T * B[M,N]; blockIdx.z splits the batch dimension M, partial tiles are added atomically
+// (rows of A may come in blocks: row m lives at A + (m / ablk) * astride + (m % ablk) * lda -- the saved history of one
+// layer of a stacked model is such a set; ablk >= M makes it an ordinary matrix)
 __global__ void __launch_bounds__(256) gemm_tn_atomic_kernel(const float* __restrict__ A, int lda, const float* __restrict__ B,
                                                              int ldb, float* __restrict__ C, int ldc, long long M, int K1, int N,
-                                                             long long mchunk) {
+                                                             long long mchunk, long long ablk, long long astride) {
   __shared__ float As[GK][GB + 4], Bs[GK][GB + 4];
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
   const int k0 = blockIdx.y * GB, n0 = blockIdx.x * GB;
@@ -112,7 +116,8 @@ __global__ void __launch_bounds__(256) gemm_tn_atomic_kernel(const float* __rest
     for (int i = threadIdx.x; i < GB * GK; i += 256) {
       const int mm = i / GB, c = i % GB;
       const bool mok = m0 + mm < mhi;
-      As[mm][c] = (mok && k0 + c < K1) ? A[(m0 + mm) * lda + k0 + c] : 0.f;
+      const long long ma = m0 + mm;
+      As[mm][c] = (mok && k0 + c < K1) ? A[(ma / ablk) * astride + (ma % ablk) * lda + k0 + c] : 0.f;
       Bs[mm][c] = (mok && n0 + c < N) ? B[(m0 + mm) * ldb + n0 + c] : 0.f;
     }
     __syncthreads();
@@ -482,7 +487,7 @@ inline BwdLayout backward_layout(const rnnwf_model_impl& m, long long R) {
   L.batched = (m.cell == CELL_TENS2D || m.cell == CELL_TENSGRU2D);
   // Single-layer 1D GRU: the same idea -- d(pre-activations), d(logits) and the one-hot inputs of ALL sites are kept, so every
   // weight / bias gradient is one launch after the reverse recurrence (4 launches per site instead of 15).
-  L.batched1d = (m.cell == CELL_GRU1D && m.symL == 1);
+  L.batched1d = (m.cell == CELL_GRU1D && (m.symL == 1 || m.g1_bwd));
   const long long nb = (L.batched || L.batched1d) ? m.Q : 1;
   // tensor-core regime of the tensorized GRU: the reverse sweep / weight-gradient kernels have their own layouts
   // (d h tile-blocked, feature-major ds/dg/dm); none of the per-site FFMA-regime operands below is needed
@@ -577,6 +582,10 @@ struct Gemm {
     RNNWF_COUNT_LAUNCH(); gemm_nn_kernel<<<g, 256, 0, st>>>(A, lda, B, ldb, C, ldc, (int)M, N, K, beta);
   }
   void tn(const float* A, int lda, const float* B, int ldb, float* C, int ldc, long long M, int K1, int N) const {
+    tn_blocked(A, lda, M > 0 ? M : 1, 0, B, ldb, C, ldc, M, K1, N);
+  }
+  // the same with A given as blocks of `ablk` rows, `astride` floats apart
+  void tn_blocked(const float* A, int lda, long long ablk, long long astride, const float* B, int ldb, float* C, int ldc, long long M, int K1, int N) const {
     if (M <= 0 || N <= 0 || K1 <= 0) return;
     const int tiles = ((N + GB - 1) / GB) * ((K1 + GB - 1) / GB);
     long long split = (592 + tiles - 1) / tiles;                 // ~4 CTAs per SM in flight
@@ -586,7 +595,7 @@ struct Gemm {
     long long mchunk = ((M + split - 1) / split + GK - 1) / GK * GK;
     split = (M + mchunk - 1) / mchunk;
     dim3 g((N + GB - 1) / GB, (K1 + GB - 1) / GB, (unsigned)split);
-    RNNWF_COUNT_LAUNCH(); gemm_tn_atomic_kernel<<<g, 256, 0, st>>>(A, lda, B, ldb, C, ldc, M, K1, N, mchunk);
+    RNNWF_COUNT_LAUNCH(); gemm_tn_atomic_kernel<<<g, 256, 0, st>>>(A, lda, B, ldb, C, ldc, M, K1, N, mchunk, ablk, astride);
   }
   void colsum(const float* X, int ldx, long long M, int N, float* out) const {
     if (M <= 0 || N <= 0) return;
@@ -624,7 +633,7 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
                                                      gru0 ? params + m.tensor("Wmerge")->offset : nullptr, nh, gru0 ? 1 : 0, wstack);
   }
 
-  cudaError_t e = m.tc_enabled ? cudaSuccess : cudaMemsetAsync(dh, 0, (size_t)m.Q * R * nhp * 4, st);
+  cudaError_t e = (m.tc_enabled || m.g1_bwd) ? cudaSuccess : cudaMemsetAsync(dh, 0, (size_t)m.Q * R * nhp * 4, st);
   if (e == cudaSuccess) e = cudaMemsetAsync(grad, 0, (size_t)m.num_params * 4, st);
   if (e != cudaSuccess) { err = std::string("rnnwf_backward memset: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
 
@@ -634,6 +643,62 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
   auto nblk = [&](long long n) { return (unsigned)((n + tpb - 1) / tpb); };
   auto hrow = [&](int q) { return hist + (long long)q * R * nhp; };
   auto dhrow = [&](int q) { return dh + (long long)q * R * nhp; };
+
+  if (m.g1_bwd) {
+    // Small 1D models: the whole reverse recurrence is one launch (gru1d_bwd.cuh); it leaves d(pre-activations), d(logits)
+    // and the one-hot inputs of every (layer, site, row) layer-major in the workspace, and every weight / bias gradient is
+    // one GEMM / reduction over all sites afterwards.
+    const int Ls = m.symL, Ns = m.Tsym;
+    const long long NR = (long long)Ns * R, N1R = (long long)(Ns - 1) * R;
+    G1BwdParams B;
+    std::memset(&B, 0, sizeof(B));
+    B.nh = nh; B.nhp = nhp; B.Gp = m.Gp; B.L = Ls; B.N = Ns; B.D = m.D; B.ND = m.ND; B.complex_head = m.complex_head; B.u1 = m.u1;
+    B.cap_up = m.cap_up; B.cap_dn = m.cap_dn; B.R = R; B.cfg = cfg; B.hist = hist; B.gates = gates; B.seed_logp = seed_logp;
+    B.seed_phase = seed_phase; B.packT = m.d_g1packT;
+    B.dpG = dp; B.dpCI = dp + (long long)m.Q * R * 2 * nh; B.dpCH = dp + (long long)m.Q * R * 3 * nh; B.dlog = dlog_base; B.X = X;
+    for (int l = Ls - 1; l >= 0; --l) {       // one launch per layer, top first; d h^{l-1}_t of all sites handed down through `dh`
+      B.layer = l;
+      B.dx_in = (l < Ls - 1) ? dh + (long long)((l + 1) & 1) * NR * nhp : nullptr;
+      B.dx_out = (l > 0) ? dh + (long long)(l & 1) * NR * nhp : nullptr;
+      RNNWF_COUNT_LAUNCH();
+      e = g1_bwd_launch(B, (int)std::min<long long>((R + G1_ROWS - 1) / G1_ROWS, (long long)m.num_sms), st);
+      if (e != cudaSuccess) { err = std::string("rnnwf_backward 1D GRU reverse sweep: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
+    }
+    const long long hstride = (long long)Ls * R * nhp;       // between consecutive sites of one layer in the saved history
+    for (int l = 0; l < Ls; ++l) {
+      const std::string p = "gru" + std::to_string(l) + ".";
+      const int din = (l == 0) ? 2 : nh;
+      const float* dG = B.dpG + (long long)l * NR * 2 * nh;
+      const float* dCI = B.dpCI + (long long)l * NR * nh;
+      const float* dCH = B.dpCH + (long long)l * NR * nh;
+      G.colsum(dG, 2 * nh, NR, 2 * nh, Gd(p + "bg"));
+      G.colsum(dCI, nh, NR, nh, Gd(p + "bci"));
+      G.colsum(dCH, nh, NR, nh, Gd(p + "bch"));
+      if (Ns > 1) {      // rows fed by the own previous state h^l_{t-1}, t >= 1
+        G.tn_blocked(hist + (long long)l * R * nhp, nhp, R, hstride, dG + R * 2LL * nh, 2 * nh, Gd(p + "Wg") + (long long)din * 2 * nh, 2 * nh, N1R, nh, 2 * nh);
+        G.tn_blocked(hist + (long long)l * R * nhp, nhp, R, hstride, dCH + R * (long long)nh, nh, Gd(p + "Wch"), nh, N1R, nh, nh);
+      }
+      if (l == 0) {      // rows fed by the one-hot of the previous symbol (zero vector at the first site)
+        if (Ns > 1) {
+          G.tn(X + R * 2LL, 2, dG + R * 2LL * nh, 2 * nh, Gd(p + "Wg"), 2 * nh, N1R, 2, 2 * nh);
+          G.tn(X + R * 2LL, 2, dCI + R * (long long)nh, nh, Gd(p + "Wci"), nh, N1R, 2, nh);
+        }
+      } else {           // rows fed by the layer below at the same site
+        G.tn_blocked(hist + (long long)(l - 1) * R * nhp, nhp, R, hstride, dG, 2 * nh, Gd(p + "Wg"), 2 * nh, NR, nh, 2 * nh);
+        G.tn_blocked(hist + (long long)(l - 1) * R * nhp, nhp, R, hstride, dCI, nh, Gd(p + "Wci"), nh, NR, nh, nh);
+      }
+    }
+    const float* htop = hist + (long long)(Ls - 1) * R * nhp;
+    G.tn_blocked(htop, nhp, R, hstride, dlog_base, m.ND, Gd("dense.W"), m.D, NR, nh, m.D);
+    G.colsum(dlog_base, m.ND, NR, m.D, Gd("dense.b"));
+    if (m.complex_head) {
+      G.tn_blocked(htop, nhp, R, hstride, dlog_base + m.D, m.ND, Gd("dense_phase.W"), 2, NR, nh, 2);
+      G.colsum(dlog_base + m.D, m.ND, NR, 2, Gd("dense_phase.b"));
+    }
+    e = cudaGetLastError();
+    if (e != cudaSuccess) { err = std::string("rnnwf_backward kernels: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
+    return RNNWF_OK;
+  }
 
   // Reduced-precision regime, tensorized GRU: the whole recurrence (heads' push into d h, gate derivatives, input
   // gradients, scatter to the neighbours) is one persistent tensor-core kernel (bwd_tc.cuh) after one batched

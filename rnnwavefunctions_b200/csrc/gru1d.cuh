@@ -51,7 +51,7 @@ struct G1Layout {
   }
 };
 inline int g1_threads(int nh) { const int t = 32 * ((((nh + 7) & ~7) / 2 + 3) / 4); return t < 2 * G1_ROWS ? 2 * G1_ROWS : t; }   // >= two head lanes per row
-inline bool g1_supported(int nh, int L, int N) { return nh <= 64 && L <= G1_MAXL && N <= 1024 && G1Layout(nh, L, N).total_bytes <= 200 * 1024; }
+inline bool g1_supported(int nh, int L, int N) { return nh <= 64 && L <= G1_MAXL && N <= 1024 && G1Layout(nh, L, N).total_bytes <= 227 * 1024; }
 
 // TF layout -> the image above.  Wg [din + nh, 2 nh] (rows [x; h], columns [r | u]), Wci [din, nh], Wch [nh, nh], bg [2 nh], bci, bch [nh]
 struct G1PackSrc { const float* Wg[G1_MAXL]; const float* bg[G1_MAXL]; const float* Wci[G1_MAXL]; const float* Wch[G1_MAXL];

@@ -30,4 +30,20 @@ cudaError_t g1_pack_launch(const G1PackSrc& S, int nh, int L, int N, int D, int 
   return cudaGetLastError();
 }
 
+cudaError_t g1_bwd_set_smem(int smem_bytes) {
+  return cudaFuncSetAttribute(gru1d_bwd_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+}
+
+cudaError_t g1_bwd_launch(const G1BwdParams& B, int grid, cudaStream_t st) {
+  const G1BwdLayout Y(B.nh, B.L);
+  gru1d_bwd_kernel<0><<<grid < 1 ? 1 : grid, g1_threads(B.nh), Y.total_bytes, st>>>(B);
+  return cudaGetLastError();
+}
+
+cudaError_t g1_pack_bwd_launch(const G1PackSrc& S, int nh, int L, int D, int ND, float* out, cudaStream_t st) {
+  const G1BwdLayout Y(nh, L);
+  gru1d_pack_bwd_kernel<0><<<(Y.pack_floats + 255) / 256, 256, 0, st>>>(S, nh, L, D, ND, out);
+  return cudaGetLastError();
+}
+
 }  // namespace rnnwf

@@ -27,6 +27,8 @@ cudaError_t g1_set_smem(int smem_bytes);
 int g1_occupancy(int threads, int smem_bytes);
 cudaError_t g1_sweep_launch(const SweepParams& P, int grid, int threads, int smem_bytes, cudaStream_t st);
 cudaError_t g1_pack_launch(const G1PackSrc& S, int nh, int L, int N, int D, int ND, float* out, cudaStream_t st);
+cudaError_t g1_bwd_set_smem(int smem_bytes);
+cudaError_t g1_pack_bwd_launch(const G1PackSrc& S, int nh, int L, int D, int ND, float* out, cudaStream_t st);
 }
 namespace rnnwf {   // sweep_tc_inst.cu
 cudaError_t tc_sweep_set_smem(int cellk, bool biasmma, bool split, int smem_bytes);
@@ -298,6 +300,7 @@ int build_model(rnnwf_model& m) {
   m.tc4 = (m.precision == 1 && m.cell == CELL_GRU4);
   // small 1D models in the FFMA regime: dedicated kernels with the whole weight set resident in shared memory (gru1d.cuh)
   m.g1 = (m.precision == 0 && m.cell == CELL_GRU1D && g1_supported(m.nh, m.symL, m.Tsym) && std::getenv("RNNWF_NO_G1") == nullptr);
+  m.g1_bwd = m.g1 && g1_bwd_supported(m.nh, m.symL) && std::getenv("RNNWF_NO_G1_BWD") == nullptr;
   if (m.precision == 1 && !m.tc_enabled && !m.tc4)
     return fail(RNNWF_EINVAL, "the tensor-core regime is implemented for the 2D cells (tensorized GRU, tensorized, vanilla RNN, four-neighbour GRU)");
   if (m.precision == 2 && !m.tc_enabled)
@@ -615,6 +618,11 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
     CREATE_TRY(cudaMalloc(&m->d_g1pack, (size_t)Y.pack_floats * 4));
     CREATE_TRY(g1_set_smem(Y.total_bytes));
     m->g1_occ = std::max(1, std::min(4, g1_occupancy(g1_threads(m->nh), Y.total_bytes)));
+    if (m->g1_bwd) {
+      const G1BwdLayout Yb(m->nh, m->symL);
+      CREATE_TRY(cudaMalloc(&m->d_g1packT, (size_t)Yb.pack_floats * 4));
+      CREATE_TRY(g1_bwd_set_smem(Yb.total_bytes));
+    }
   }
   CREATE_TRY(backward_init());
   if (m->tc4) {
@@ -636,7 +644,7 @@ int rnnwf_destroy(rnnwf_handle h) {
   if (h == nullptr) return RNNWF_OK;
   cudaFree(h->d_steps); cudaFree(h->d_variants); cudaFree(h->d_site_of_t); cudaFree(h->d_wpack);
   cudaFree(h->d_xtab); cudaFree(h->d_bias); cudaFree(h->d_head_w); cudaFree(h->d_head_b);
-  cudaFree(h->d_g1pack); cudaFree(h->d_tcB); cudaFree(h->d_tcbias); cudaFree(h->d_dw_jobs); cudaFree(h->d_dw_cls); cudaFree(h->d_dw4_jobs); cudaFree(h->d_dw4_sites);
+  cudaFree(h->d_g1pack); cudaFree(h->d_g1packT); cudaFree(h->d_tcB); cudaFree(h->d_tcbias); cudaFree(h->d_dw_jobs); cudaFree(h->d_dw_cls); cudaFree(h->d_dw4_jobs); cudaFree(h->d_dw4_sites);
   delete h;
   return RNNWF_OK;
 }
@@ -718,6 +726,7 @@ int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
     S.phase_w = wp ? params_dev + wp->offset : nullptr; S.phase_b = bp ? params_dev + bp->offset : nullptr;
     RNNWF_COUNT_LAUNCH();
     CUDA_TRY(g1_pack_launch(S, h->nh, h->symL, h->Tsym, h->D, h->ND, h->d_g1pack, st));
+    if (h->g1_bwd) { RNNWF_COUNT_LAUNCH(); CUDA_TRY(g1_pack_bwd_launch(S, h->nh, h->symL, h->D, h->ND, h->d_g1packT, st)); }
   }
   if (h->tc_enabled) {
     const TcSmem ts(h->nhp, h->Tsym, h->Q);

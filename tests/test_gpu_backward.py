@@ -66,7 +66,7 @@ def test_gradient_matches_oracle_autograd(cuda, name, from_sampling):
         gr = P[n].grad
         scale = float(gr.abs().max()) + 1e-30
         err = float((v.double() - gr).abs().max()) / scale
-        if not err < 1e-4:
+        if not err < 1e-4 + 1e-6 / scale:      # (absolute floor 1e-6: float atomics on a bias gradient that nearly cancels)
             bad.append((n, err, scale))
     assert not bad, f"gradient mismatch (tensor, rel err, scale): {bad}"
 
