@@ -157,6 +157,19 @@ int rnnwf_logpsi_static(rnnwf_handle h, int64_t rows, const int8_t* samples_dev,
 int rnnwf_adam_step(float* params_dev, const float* grad_dev, float* m_dev, float* v_dev, int64_t n, double lr,
                     double beta1, double beta2, double eps, int64_t t, double clip, void* stream);
 
+/* The step between the local energies and the backward: energy moments and the per-sample seeds of the reference's
+ * surrogate costs, on the device (replaces the np.mean / np.var of the training loops and the cost lines
+ * 1DTFIM/TrainingRNN_1DTFIM.py:157,207-208; J1J2/TrainingRNN_J1J2.py:197,281-282; 2DHeisenberg/Run_RNNWF_2DHeis.py:199,301-302;
+ * RydbergKagome_2DGRU/Run_RNNWF_Rydberg.py:158-159).
+ *   rnnwf_energy_moments: moments_dev[8] = {rows, sum Re E, sum Im E, sum (Re E)^2, sum (Im E)^2, sum logP, 0, 0} of this shard
+ *     (eloc_dev float64 [rows][2]; logp_dev may be NULL).  Under data parallelism the caller all-reduces the 8 doubles.
+ *   rnnwf_cost_seeds: from the (global) moments,  seed_logp[b] = (Re(E_b - <E>) + T (logP_b - <logP>)) / n  (the T term only for
+ *     the complex cost with annealing or the free-energy cost), seed_phase[b] = 2 Im(E_b - <E>) / n (complex models);
+ *     stats_dev[4] (optional) = {Re <E>, Im <E>, var E = var Re + var Im, <logP>}. */
+int rnnwf_energy_moments(int64_t rows, const double* eloc_dev, const double* logp_dev, double* moments_dev, void* stream);
+int rnnwf_cost_seeds(int64_t rows, const double* eloc_dev, const double* logp_dev, const double* moments_dev, int complex_head, double T,
+                     int free_energy, double* seed_logp_dev, double* seed_phase_dev, double* stats_dev, void* stream);
+
 /* Symmetry-projected amplitudes (2DHeisenberg/MDComplexRNN.py:290-316 log_amplitudes_fromsymmetrygroup and the rotsym /
  * c2v / c4v ... variants :320-577 built on it; RydbergKagome_2DGRU/MDRNNWavefunction.py:242-279 log_probability_symmetry):
  * the caller evaluates the G transformed copies of its `rows` configurations in one rnnwf_logpsi batch (copy-major:

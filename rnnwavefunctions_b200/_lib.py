@@ -48,6 +48,8 @@ def _load():
         "rnnwf_backward": (C.c_int, [vp, i64, vp, vp, vp, vp, vp, vp, i64, vp]),
         "rnnwf_logpsi_static": (C.c_int, [vp, i64, vp, vp, vp, vp]),
         "rnnwf_adam_step": (C.c_int, [vp, vp, vp, vp, i64, C.c_double, C.c_double, C.c_double, C.c_double, i64, C.c_double, vp]),
+        "rnnwf_energy_moments": (C.c_int, [i64, vp, vp, vp, vp]),
+        "rnnwf_cost_seeds": (C.c_int, [i64, vp, vp, vp, C.c_int, C.c_double, C.c_int, vp, vp, vp, vp]),
         "rnnwf_symmetry_epilogue": (C.c_int, [C.c_int, i64, vp, vp, C.POINTER(C.c_double), vp, vp, vp]),
         "rnnwf_symmetry_seeds": (C.c_int, [C.c_int, i64, vp, vp, C.POINTER(C.c_double), vp, vp, vp, vp, vp]),
         "rnnwf_symmetry_create": (C.c_int, [vp, C.c_int, C.POINTER(i32), C.POINTER(C.c_int8), C.POINTER(C.c_double), C.POINTER(vp)]),

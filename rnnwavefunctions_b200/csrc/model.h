@@ -80,6 +80,7 @@ struct rnnwf_model_impl {
   mutable std::vector<unsigned char> plan_host_a, plan_host_b;   // host images of the last uploaded work plan (source of the stream-ordered copies)
   const float* d_params = nullptr;  // last parameter vector handed to set_weights (caller-owned)
   bool weights_set = false;
+  bool ffma_stale = false;          // the generic FFMA packs lag behind d_params (repacked on demand by rnnwf_logpsi_static)
 
   const TensorInfo* tensor(const std::string& n) const {
     for (auto& t : tensors) if (t.name == n) return &t;

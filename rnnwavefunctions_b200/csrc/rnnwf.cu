@@ -696,9 +696,8 @@ static void make_pack_ctx(const rnnwf_model& m, const HostVariant& v, const floa
   }
 }
 
-int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
-  if (h == nullptr || params_dev == nullptr) return fail(RNNWF_EINVAL, "null argument");
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
+// weight packs of the generic FFMA sweep (sweep.cuh)
+static void pack_ffma(rnnwf_handle h, const float* params_dev, cudaStream_t st) {
   for (auto& v : h->variants) {
     PackCtx c;
     make_pack_ctx(*h, v, params_dev, nullptr, c);
@@ -706,6 +705,16 @@ int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
     if (v.meta.x_mask) { RNNWF_COUNT_LAUNCH(); pack_x_kernel<<<std::min(256, cdiv((long long)h->nslots * h->D * h->Gp, 256)), 256, 0, st>>>(c, h->nslots, h->d_xtab + v.meta.x_off); }
     RNNWF_COUNT_LAUNCH(); pack_b_kernel<<<cdiv(h->Gp, 256), 256, 0, st>>>(c, h->d_bias + v.meta.b_off);
   }
+  h->ffma_stale = false;
+}
+
+int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
+  if (h == nullptr || params_dev == nullptr) return fail(RNNWF_EINVAL, "null argument");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // handles whose sweeps run their own kernels (tensor-core regimes, dedicated 1D kernels) need the generic FFMA packs only
+  // for rnnwf_logpsi_static: packed there on demand instead of after every optimiser step
+  if (h->g1 || h->tc_enabled || h->tc4) h->ffma_stale = true;
+  else pack_ffma(h, params_dev, st);
   const TensorInfo* wd = h->tensor("dense.W");
   const TensorInfo* bd = h->tensor("dense.b");
   const TensorInfo* wp = h->tensor("dense_phase.W");
@@ -1114,6 +1123,72 @@ int rnnwf_adam_step(float* params_dev, const float* grad_dev, float* m_dev, floa
   return RNNWF_OK;
 }
 
+// ---- energy moments and the seeds of the reference's surrogate costs ---------------------------------------
+// moments[8] = {rows, sum Re E, sum Im E, sum (Re E)^2, sum (Im E)^2, sum logP, 0, 0}: one block, FP64, fixed order
+__global__ void __launch_bounds__(1024) energy_moments_kernel(long long rows, const double* __restrict__ eloc, const double* __restrict__ logp,
+                                                              double* __restrict__ out) {
+  __shared__ double red[5][32];
+  double a[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+  for (long long b = threadIdx.x; b < rows; b += blockDim.x) {
+    const double re = eloc[2 * b], im = eloc[2 * b + 1];
+    a[0] += re; a[1] += im; a[2] += re * re; a[3] += im * im;
+    if (logp != nullptr) a[4] += logp[b];
+  }
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    for (int o = 16; o > 0; o >>= 1) a[k] += __shfl_xor_sync(0xffffffffu, a[k], o);
+    if (lane == 0) red[k][w] = a[k];
+  }
+  __syncthreads();
+  if (w == 0) {
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      double v = (lane < (int)(blockDim.x >> 5)) ? red[k][lane] : 0.0;
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) out[1 + k] = v;
+    }
+    if (lane == 0) { out[0] = (double)rows; out[6] = 0.0; out[7] = 0.0; }
+  }
+}
+
+// seeds from the (all-reduced) moments; stats[4] = {mean Re E, mean Im E, var E, mean logP}
+__global__ void __launch_bounds__(256) cost_seeds_kernel(long long rows, const double* __restrict__ eloc, const double* __restrict__ logp,
+                                                         const double* __restrict__ mom, int complex_head, double T, int free_energy,
+                                                         double* __restrict__ seed_logp, double* __restrict__ seed_phase, double* __restrict__ stats) {
+  const double n = mom[0], mre = mom[1] / n, mim = mom[2] / n, mlp = mom[5] / n;
+  if (blockIdx.x == 0 && threadIdx.x == 0 && stats != nullptr) {
+    stats[0] = mre; stats[1] = mim; stats[2] = mom[3] / n - mre * mre + mom[4] / n - mim * mim; stats[3] = mlp;
+  }
+  for (long long b = blockIdx.x * (long long)blockDim.x + threadIdx.x; b < rows; b += (long long)gridDim.x * blockDim.x) {
+    const double dre = eloc[2 * b] - mre, dim_ = eloc[2 * b + 1] - mim;
+    double s = dre;
+    if (T != 0.0 && logp != nullptr && (complex_head || free_energy)) s += T * (logp[b] - mlp);
+    seed_logp[b] = s / n;
+    if (complex_head && seed_phase != nullptr) seed_phase[b] = 2.0 * dim_ / n;
+  }
+}
+
+int rnnwf_energy_moments(int64_t rows, const double* eloc_dev, const double* logp_dev, double* moments_dev, void* stream) {
+  if (rows <= 0 || eloc_dev == nullptr || moments_dev == nullptr) return fail(RNNWF_EINVAL, "rnnwf_energy_moments: null argument or rows <= 0");
+  RNNWF_COUNT_LAUNCH();
+  energy_moments_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(rows, eloc_dev, logp_dev, moments_dev);
+  CUDA_TRY(cudaGetLastError());
+  return RNNWF_OK;
+}
+
+int rnnwf_cost_seeds(int64_t rows, const double* eloc_dev, const double* logp_dev, const double* moments_dev, int complex_head, double T,
+                     int free_energy, double* seed_logp_dev, double* seed_phase_dev, double* stats_dev, void* stream) {
+  if (rows <= 0 || eloc_dev == nullptr || moments_dev == nullptr || seed_logp_dev == nullptr)
+    return fail(RNNWF_EINVAL, "rnnwf_cost_seeds: null argument or rows <= 0");
+  if (complex_head && seed_phase_dev == nullptr) return fail(RNNWF_EINVAL, "rnnwf_cost_seeds: complex cost needs seed_phase");
+  RNNWF_COUNT_LAUNCH();
+  cost_seeds_kernel<<<std::min(592, cdiv(rows, 256)), 256, 0, static_cast<cudaStream_t>(stream)>>>(rows, eloc_dev, logp_dev, moments_dev, complex_head, T,
+                                                                                                  free_energy, seed_logp_dev, seed_phase_dev, stats_dev);
+  CUDA_TRY(cudaGetLastError());
+  return RNNWF_OK;
+}
+
 // ---- symmetry-projected amplitudes --------------------------------------------------------------------
 static int sym_chars(int G, const double* chi, SymChars& ch) {
   if (G < 1 || G > SYM_MAX_G) return fail(RNNWF_EINVAL, "symmetry epilogue: the group must have 1..64 elements");
@@ -1395,5 +1470,6 @@ extern "C" int rnnwf_logpsi_static(rnnwf_handle h, int64_t rows, const int8_t* s
   P.mode = MODE_EVAL; P.rows = rows; P.cfg_in = samples_dev; P.out_logp = logp_dev; P.out_phase = phase_dev;
   P.ring = ring;
   // always the generic FP32 FFMA sweep, whatever the regime of the handle (the other sweeps size their scratch differently)
+  if (h->ffma_stale) pack_ffma(h, h->d_params, static_cast<cudaStream_t>(stream));
   return launch_sweep_ffma(m, P, s, static_cast<cudaStream_t>(stream));
 }

@@ -128,11 +128,36 @@ class VMC:
                                     saved=self.saved if self.prefix_reuse else None, return_count=True)
         return s, lp, ph, e, cnt
 
+    def _moments_and_seeds(self, lp, e):
+        """Energy moments (all-reduced) and the backward seeds: two library kernels around the one collective
+        (rnnwf_energy_moments, rnnwf_cost_seeds) instead of a chain of eager tensor ops."""
+        import ctypes as C
+        from ._lib import lib, check
+        eng = self.eng
+        ns = e.shape[0]
+        dev = eng.device
+        er = torch.view_as_real(e.to(torch.complex128)).contiguous() if e.is_complex() else torch.stack([e.double(), torch.zeros_like(e, dtype=torch.float64)], dim=-1).contiguous()
+        lpc = None if lp is None else lp.to(device=dev, dtype=torch.float64).contiguous()
+        mom = torch.empty(8, dtype=torch.float64, device=dev)
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        pt = lambda t: C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+        check(lib.rnnwf_energy_moments(ns, pt(er), pt(lpc), pt(mom), st), "rnnwf_energy_moments")
+        allreduce_(mom)
+        sl = torch.empty(ns, dtype=torch.float64, device=dev)
+        sp = torch.empty(ns, dtype=torch.float64, device=dev) if eng.complex_head else None
+        stats = torch.empty(4, dtype=torch.float64, device=dev)
+        check(lib.rnnwf_cost_seeds(ns, pt(er), pt(lpc), pt(mom), int(eng.complex_head), float(self.T), int(bool(self.free_energy)),
+                                   pt(sl), pt(sp), pt(stats), st), "rnnwf_cost_seeds")
+        return sl, sp, torch.view_as_complex(stats[0:2]), stats[2]
+
     def gradient(self, s, lp, ph, e):
         eng = self.eng
-        extra = lp if (self.T != 0.0) else None
-        n, mean_e, var, mean_lp = energy_moments(e, extra)
-        sl, sp = seeds(e, mean_e, n, eng.complex_head, logp=lp, mean_logp=mean_lp, T=self.T, free_energy=self.free_energy)
+        if e.is_cuda:
+            sl, sp, mean_e, var = self._moments_and_seeds(lp, e)
+        else:
+            extra = lp if (self.T != 0.0) else None
+            n, mean_e, var, mean_lp = energy_moments(e, extra)
+            sl, sp = seeds(e, mean_e, n, eng.complex_head, logp=lp, mean_logp=mean_lp, T=self.T, free_energy=self.free_energy)
         if self.sym is not None:
             # d cost / d (symmetrised log P, phase) -> seeds of the G copies -> one backward over the G * ns batch
             _, _, lp_g, ph_g, copies = eng.logpsi_sym(self.sym, s, saved=self.saved)
@@ -142,7 +167,7 @@ class VMC:
         else:
             grad = eng.backward(s, self.saved, sl, sp)
         allreduce_(grad)
-        return grad, mean_e, var
+        return grad, mean_e[0] if mean_e.dim() else mean_e, var
 
     def step(self, uniforms=None, lr=None, update=True):
         s, lp, ph, e, cnt = self.sample_and_energies(uniforms)
