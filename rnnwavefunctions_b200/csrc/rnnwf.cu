@@ -444,7 +444,7 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
 long long ring_bytes(const rnnwf_model& m, int grid, int Mp) {
   if (m.tc4) return (long long)grid * m.Q * t4_step_bytes(m.tc_np);   // FP16 chunk images of every site, per persistent CTA
   // tensor-core regime: one FP16 history image per slot in the fixed quad layout of sweep_tc.cuh (TC_RING_SLOT bytes)
-  const long long slot = m.tc_enabled ? std::max<long long>((long long)TC_RING_SLOT * (m.tc_split ? 2 : 1), (long long)Mp * m.nhp * 4) : (long long)Mp * m.nhp * 4;
+  const long long slot = m.tc_enabled ? (long long)tc_ring_slot(m.nhp) * (m.tc_split ? 2 : 1) : (long long)Mp * m.nhp * 4;
   return (long long)grid * m.ring_len * slot;
 }
 

@@ -45,10 +45,12 @@ constexpr int TC_MMA2_WARP = 18;        // second MMA-issue warp
 // warp 0: MMA issue (even passes), 1..16: epilogue, 17: heads, 18: MMA issue (odd passes), 19: loader
 constexpr int TC_THREADS = 32 + TC_EPI_THREADS + TC_HEAD_THREADS + 32 + 32;
 constexpr int TC_TPS = TC_NB * 4;       // accumulator columns one epilogue thread owns per pass (28, contiguous)
-// one step's FP16 history image: [sub 4][quad 4][row 128][16 bytes]; quad i of thread (row, sub) holds its pieces 2i, 2i+1
+// one step's FP16 history image: [sub 4][quad <= 4][row 128][16 bytes]; quad i of thread (row, sub) holds its pieces 2i, 2i+1
 // (a warp's 16-byte accesses are contiguous: fully coalesced)
-constexpr uint32_t TC_RING_SLOT = TC_SUB * 4 * TC_ROWS * 16;
 constexpr uint32_t TC_RING_QUAD = TC_ROWS * 16;
+// (only the quads that hold unit pieces are kept: 4 at 100 units, 2 at 50 -- the ring of C3 then fits the L2)
+__host__ __device__ inline int tc_ring_quads(int nhp) { return (((nhp + TC_JP - 1) / TC_JP) + 1) / 2; }
+__host__ __device__ inline uint32_t tc_ring_slot(int nhp) { return (uint32_t)(TC_SUB * tc_ring_quads(nhp)) * TC_RING_QUAD; }
 
 // Thread-major order of the K axis inside one neighbour half (nhp units): epilogue thread `sub` owns units
 // 16 p + 4 sub + e; its units occupy the contiguous positions tc_koff(sub) + 4 p + e.  Used identically by the operand

@@ -55,7 +55,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
   const uint32_t idesc_last = (CELLK == 1) ? idesc : tc_idesc(TC_ROWS, ((subs_last * TC_TPS + 15) / 16) * 16);
   // TMEM map: [0, 224) two accumulator buffers; then two A operands of 8*hc columns each (2 halves per 32-bit column)
   const uint32_t acols = 8u * (uint32_t)hc;           // columns of one A operand ([h_h ; h_v], 16*hc halves)
-  const uint32_t RSLOT = SPLIT ? 2u * TC_RING_SLOT : TC_RING_SLOT;   // one step's history image(s): hi [, lo]
+  const uint32_t NQ = (uint32_t)tc_ring_quads(P.nhp);              // quads (2 unit pieces each) a thread owns in a history image
+  const uint32_t SLOT1 = tc_ring_slot(P.nhp);                      // one history image
+  const uint32_t RSLOT = SPLIT ? 2u * SLOT1 : SLOT1;               // one step's history image(s): hi [, lo]
   constexpr uint32_t NPARTS = SPLIT ? 2u : 1u;        // weight images per column pass
   // split precision: operands are stored scaled by powers of two (TC_SPLIT_HS, TC_SPLIT_WS) so that their lo parts stay in
   // FP16's normal range; the accumulators are scaled back (exactly) as they are read
@@ -242,7 +244,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
     const int one_word = 2 * one_p + ((nh & 3) >> 1);                   // word inside the thread's run
     unsigned char* const ring_base = reinterpret_cast<unsigned char*>(P.ring);
     // this thread's first quad inside a step's ring image   (the whole ring is < 4 GB: 32-bit offsets)
-    const uint32_t ring_off0 = (uint32_t)blockIdx.x * (uint32_t)P.ring_len * RSLOT + (uint32_t)sub * (4u * TC_RING_QUAD) + (uint32_t)row * 16u;
+    const uint32_t ring_off0 = (uint32_t)blockIdx.x * (uint32_t)P.ring_len * RSLOT + (uint32_t)sub * (NQ * TC_RING_QUAD) + (uint32_t)row * 16u;
     const uint32_t bar_mma_a = smem_u32(bar_mma), bar_free_a = smem_u32(bar_free);
     const uint32_t bar_part_a = smem_u32(bar_part), bar_pfree_a = smem_u32(bar_pfree);
     const uint32_t acc0 = tmem_base + lane_base + (uint32_t)(sub * TC_TPS);               // this thread's accumulators, buffer 0
@@ -289,12 +291,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           const unsigned char* src = ring_base + (ring_off0 + other_slot);
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            const uint4 v = __ldcg(reinterpret_cast<const uint4*>(src + i * TC_RING_QUAD));
-            w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
-            if (SPLIT) {
-              const uint4 u = __ldcg(reinterpret_cast<const uint4*>(src + TC_RING_SLOT + i * TC_RING_QUAD));
-              wl[4 * i] = u.x; wl[4 * i + 1] = u.y; wl[4 * i + 2] = u.z; wl[4 * i + 3] = u.w;
+            uint4 v = make_uint4(0u, 0u, 0u, 0u), u = make_uint4(0u, 0u, 0u, 0u);
+            if ((uint32_t)i < NQ) {          // (narrow models keep fewer quads per image)
+              v = __ldcg(reinterpret_cast<const uint4*>(src + i * TC_RING_QUAD));
+              if (SPLIT) u = __ldcg(reinterpret_cast<const uint4*>(src + SLOT1 + i * TC_RING_QUAD));
             }
+            w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
+            if (SPLIT) { wl[4 * i] = u.x; wl[4 * i + 1] = u.y; wl[4 * i + 2] = u.z; wl[4 * i + 3] = u.w; }
           }
         } else {
           const float* psrc = P.par_hist + ((size_t)other * (size_t)P.par_rows + (size_t)rparent) * nhp + sub * 4;
@@ -378,6 +381,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           if (carry_half == 1) set_one(onext);          // the prefetched half is the horizontal one
           store_half(onext, a_next + (uint32_t)(1 - carry_half) * hcols);
         }
+        // split precision: the operand buffer is still being read by this site's MMAs; fetch the older-neighbour half of the
+        // next operand now (its latency hides behind the column passes) and collect this site's pieces in `chi` / `clo`
+        uint32_t chi[16], clo[16];
+        if (SPLIT) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) { chi[i] = 0u; clo[i] = 0u; }
+          if (has_next) { const int4 e1 = stepT[q + 1]; load_half(onext, onlo, (int)(short)(e1.y & 0xffff), (uint32_t)e1.w); }
+        }
         TC_ACC(10); TC_EV(11);
         // sampling: the neighbours' symbols are drawn by the head warps (completion number hs covers steps < hs)
         if (MODE == MODE_SAMPLE && hs > 0) mbar_wait(bar_sym, (hs - 1) & 1);
@@ -416,7 +427,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
                 const float x = fmaf(cu, vv[e], fmaf(cl, hh[e], fmaf(__uint_as_float(d[blk * 4 + e]), DS, bb[e])));
-                const float hv = (x > 0.f) ? x : (SPLIT ? expm1f(x) : (__expf(x) - 1.0f));      // elu; padding units: x = 0 -> 0
+                const float hv = (x > 0.f) ? x : (SPLIT ? (expf(x) - 1.0f) : (__expf(x) - 1.0f));   // elu (absolute error of exp(x) - 1 <= 1.2e-7: what FP32 h carries anyway); padding units: x = 0 -> 0
                 hnew[e] = live ? hv : 0.f;
                 const float4 w = *reinterpret_cast<const float4*>(hW + blk * (TC_JP * 4) + e * 4);
                 lg[0] = fmaf(hv, w.x, lg[0]); lg[1] = fmaf(hv, w.y, lg[1]); lg[2] = fmaf(hv, w.z, lg[2]); lg[3] = fmaf(hv, w.w, lg[3]);
@@ -428,7 +439,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
               __syncwarp();
               if (has_next && !SPLIT) tc_st2(a_carry + (uint32_t)(2 * blk), o);
               *reinterpret_cast<uint2*>(ring_p) = o;
-              if (SPLIT) *reinterpret_cast<uint2*>(ring_p + TC_RING_SLOT) = ol;
+              if (SPLIT) { *reinterpret_cast<uint2*>(ring_p + SLOT1) = ol; chi[2 * blk] = o.x; chi[2 * blk + 1] = o.y; clo[2 * blk] = ol.x; clo[2 * blk + 1] = ol.y; }
               ring_p += (blk & 1) ? (TC_RING_QUAD - 8u) : 8u;
             }
           }
@@ -527,7 +538,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
               __syncwarp();
               if (has_next && !SPLIT) tc_st2(a_carry, o);
               *reinterpret_cast<uint2*>(ring_p) = o;
-              if (SPLIT) *reinterpret_cast<uint2*>(ring_p + TC_RING_SLOT) = ol;
+              if (SPLIT) { *reinterpret_cast<uint2*>(ring_p + SLOT1) = ol; chi[2 * p] = o.x; chi[2 * p + 1] = o.y; clo[2 * p] = ol.x; clo[2 * p + 1] = ol.y; }
               if (p == one_p) o_one = o;                    // (kept for the constant-1 store after the loop)
             }
             ring_p += (p & 1) ? (TC_RING_QUAD - 8u) : 8u;
@@ -546,11 +557,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         __syncwarp();
         if (SPLIT) {
           // split-precision regime: all MMAs of this site have completed (the last pass's accumulators were read), so the
-          // single operand buffer can be rewritten: both neighbour halves of step q + 1 from the history ring (this thread's
-          // own earlier stores, this step's included -- same thread, same addresses: program order)
+          // single operand buffer can be rewritten: this site's pieces (carry half) and the prefetched older-neighbour half
           if (has_next) {
-            const int4 e1 = stepT[q + 1];
-            operand_from_history((int)(short)(e1.x & 0xffff), (int)(short)((unsigned)e1.x >> 16), aop0);
+            if (carry_half == 0) set_one(chi); else set_one(onext);       // the horizontal half carries the constant 1 of the bias row
+            store_half(chi, aop0 + (uint32_t)carry_half * hcols);
+            store_half(clo, aop0 + acols + (uint32_t)carry_half * hcols);
+            store_half(onext, aop0 + (uint32_t)(1 - carry_half) * hcols);
+            store_half(onlo, aop0 + acols + (uint32_t)(1 - carry_half) * hcols);
+            tc_wait_st();
+            tc_fence_before();
+            mbar_arrive(bar_A);
           }
         } else if (one_mine && has_next && carry_half == 0) {
           // the TMEM copy of the horizontal half carries the constant 1 of the bias row: rewrite that piece (warp-uniform)
