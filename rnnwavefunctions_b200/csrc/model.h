@@ -79,6 +79,12 @@ struct rnnwf_model_impl {
   int* d_dw4_sites = nullptr;       // [5][Q]
   mutable std::vector<unsigned char> plan_host_a, plan_host_b;   // host images of the last uploaded work plan (source of the stream-ordered copies)
   const float* d_params = nullptr;  // last parameter vector handed to set_weights (caller-owned)
+  // Hamiltonian tables of the local-energy front end, cached per `ham` block (rnnwf.cu: enumerate_connected)
+  void* d_hamtab = nullptr;
+  mutable int ham_kind = -1;
+  mutable std::vector<double> ham_block;
+  mutable std::vector<unsigned char> ham_host[3];
+  mutable int ham_n[2] = {0, 0};
   bool weights_set = false;
   bool ffma_stale = false;          // the generic FFMA packs lag behind d_params (repacked on demand by rnnwf_logpsi_static)
 

@@ -53,6 +53,10 @@ int fail(int code, const std::string& msg) { g_err = msg; return code; }
 
 inline long long align256(long long x) { return (x + 255) & ~255LL; }
 inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
+// the Hamiltonian tables of the local-energy front end (first four regions of ElocLayout; they live in the handle)
+inline long long hamtab_bytes(int T) {
+  return align256((3LL * T + 16) * 8) + align256(3LL * T * (long long)sizeof(Bond) + 64) + align256((T + 2) * 4LL) + align256(256 * (long long)sizeof(RydNb));
+}
 
 // ------------------------------------------------------------------------------------------------
 // model construction
@@ -588,6 +592,7 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
     CREATE_TRY(cudaMemset(m->d_head_w, 0, hw_bytes));
   }
   CREATE_TRY(cudaMalloc(&m->d_head_b, 64));
+  CREATE_TRY(cudaMalloc(&m->d_hamtab, (size_t)hamtab_bytes(m->Tsym)));     // couplings / bonds / neighbour table
   CREATE_TRY(cudaMemcpy(m->d_steps, m->steps.data(), m->steps.size() * sizeof(StepMeta), cudaMemcpyHostToDevice));
   CREATE_TRY(cudaMemcpy(m->d_variants, vmeta.data(), vmeta.size() * sizeof(VariantMeta), cudaMemcpyHostToDevice));
   CREATE_TRY(cudaMemcpy(m->d_site_of_t, m->site_of_t.data(), m->site_of_t.size() * sizeof(int16_t), cudaMemcpyHostToDevice));
@@ -644,7 +649,7 @@ int rnnwf_destroy(rnnwf_handle h) {
   if (h == nullptr) return RNNWF_OK;
   cudaFree(h->d_steps); cudaFree(h->d_variants); cudaFree(h->d_site_of_t); cudaFree(h->d_wpack);
   cudaFree(h->d_xtab); cudaFree(h->d_bias); cudaFree(h->d_head_w); cudaFree(h->d_head_b);
-  cudaFree(h->d_g1pack); cudaFree(h->d_g1packT); cudaFree(h->d_tcB); cudaFree(h->d_tcbias); cudaFree(h->d_dw_jobs); cudaFree(h->d_dw_cls); cudaFree(h->d_dw4_jobs); cudaFree(h->d_dw4_sites);
+  cudaFree(h->d_hamtab); cudaFree(h->d_g1pack); cudaFree(h->d_g1packT); cudaFree(h->d_tcB); cudaFree(h->d_tcbias); cudaFree(h->d_dw_jobs); cudaFree(h->d_dw_cls); cudaFree(h->d_dw4_jobs); cudaFree(h->d_dw4_sites);
   delete h;
   return RNNWF_OK;
 }
@@ -856,10 +861,19 @@ struct EnumOut { long long nchild_fixed = 0; const int* rows_dev = nullptr; bool
 int enumerate_connected(const rnnwf_model& m, int hamiltonian, const double* ham, int ham_len, long long rows,
                         const int8_t* samples_dev, double* eloc_dev, char* ws, const ElocLayout& L, cudaStream_t st, EnumOut& out) {
   int rc;
-  double* d_ham = reinterpret_cast<double*>(ws + L.off_ham);
-  Bond* d_bonds = reinterpret_cast<Bond*>(ws + L.off_bonds);
-  int* d_bstart = reinterpret_cast<int*>(ws + L.off_bstart);
-  RydNb* d_nb = reinterpret_cast<RydNb*>(ws + L.off_nb);
+  // Hamiltonian tables (couplings, bond list, neighbour table) live in the handle and are rebuilt / uploaded only when the
+  // `ham` block changes: a training loop passes the same block every step, so the hot call stages nothing from the host.
+  // The host images the uploads read from are kept in the handle, so the stream-ordered copies never outlive their source.
+  char* const tab = static_cast<char*>(m.d_hamtab);
+  double* d_ham = reinterpret_cast<double*>(tab + L.off_ham);
+  Bond* d_bonds = reinterpret_cast<Bond*>(tab + L.off_bonds);
+  int* d_bstart = reinterpret_cast<int*>(tab + L.off_bstart);
+  RydNb* d_nb = reinterpret_cast<RydNb*>(tab + L.off_nb);
+  const bool hit = (m.ham_kind == hamiltonian && (int)m.ham_block.size() == ham_len && std::equal(ham, ham + ham_len, m.ham_block.begin()));
+  auto upload = [&](void* dst, const void* src, size_t bytes, std::vector<unsigned char>& keep) -> cudaError_t {
+    keep.assign(static_cast<const unsigned char*>(src), static_cast<const unsigned char*>(src) + bytes);
+    return cudaMemcpyAsync(dst, keep.data(), bytes, cudaMemcpyHostToDevice, st);
+  };
   int* d_counts = reinterpret_cast<int*>(ws + L.off_counts);
   int* d_offsets = reinterpret_cast<int*>(ws + L.off_offsets);
   Child* d_children = reinterpret_cast<Child*>(ws + L.off_children);
@@ -880,9 +894,11 @@ int enumerate_connected(const rnnwf_model& m, int hamiltonian, const double* ham
       if (hamiltonian == RNNWF_HAM_TFIM1D && Ny != 1) return fail(RNNWF_EINVAL, "TFIM1D needs a chain");
       if (ham_len < 1 + nJ) return fail(RNNWF_EINVAL, "TFIM: ham = {Bx, Jz...} too short");
       // 1D: Jz[i] couples (i,i+1) == 2D kernel with Ny = 1 and Jz[i*1+0]
-      std::vector<double> J(Nx * Ny, 0.0);
-      for (int i = 0; i < nJ && i < Nx * Ny; ++i) J[i] = ham[1 + i];
-      CUDA_TRY(cudaMemcpyAsync(d_ham, J.data(), J.size() * 8, cudaMemcpyHostToDevice, st));
+      if (!hit) {
+        std::vector<double> J(Nx * Ny, 0.0);
+        for (int i = 0; i < nJ && i < Nx * Ny; ++i) J[i] = ham[1 + i];
+        CUDA_TRY(upload(d_ham, J.data(), J.size() * 8, m.ham_host[0]));
+      }
       RNNWF_COUNT_LAUNCH(); tfim_diag_kernel<<<gsamp, tpb, 0, st>>>(samples_dev, rows, Nx, Ny, d_ham, eloc_dev);
       const double Bx = ham[0];
       if (Bx == 0.0) have_children = false;
@@ -903,6 +919,7 @@ int enumerate_connected(const rnnwf_model& m, int hamiltonian, const double* ham
       };
       std::vector<RydNb> nb;
       const double a1x = 2.0, a1y = 0.0, a2x = 1.0, a2y = std::sqrt(3.0);
+      if (!hit)
       for (int i = 0; i < Nx; ++i)
         for (int j = 0; j < Ny; ++j)
           for (int k = 0; k < 3; ++k)
@@ -922,9 +939,12 @@ int enumerate_connected(const rnnwf_model& m, int hamiltonian, const double* ham
                 }
               }
             }
-      if (nb.size() > 256) return fail(RNNWF_EINVAL, "Rydberg: too many neighbours within Rcutoff (max 256)");
-      if (!nb.empty()) CUDA_TRY(cudaMemcpyAsync(d_nb, nb.data(), nb.size() * sizeof(RydNb), cudaMemcpyHostToDevice, st));
-      RNNWF_COUNT_LAUNCH(); rydberg_diag_kernel<<<std::min(8192, cdiv(rows * 32, tpb)), tpb, 0, st>>>(samples_dev, rows, Nx, Ny, d_nb, (int)nb.size(), delta, eloc_dev);
+      if (!hit) {
+        if (nb.size() > 256) return fail(RNNWF_EINVAL, "Rydberg: too many neighbours within Rcutoff (max 256)");
+        if (!nb.empty()) CUDA_TRY(upload(d_nb, nb.data(), nb.size() * sizeof(RydNb), m.ham_host[0]));
+        m.ham_n[0] = (int)nb.size();
+      }
+      RNNWF_COUNT_LAUNCH(); rydberg_diag_kernel<<<std::min(8192, cdiv(rows * 32, tpb)), tpb, 0, st>>>(samples_dev, rows, Nx, Ny, d_nb, m.ham_n[0], delta, eloc_dev);
       if (Omega == 0.0) have_children = false;
       else {
         nchild_fixed = 3LL * T * rows;
@@ -973,9 +993,11 @@ int enumerate_connected(const rnnwf_model& m, int hamiltonian, const double* ham
         bstart[hb[i].ta + 1]++;
       }
       for (int t = 0; t < T; ++t) bstart[t + 1] += bstart[t];
-      if (!bonds.empty()) CUDA_TRY(cudaMemcpyAsync(d_bonds, bonds.data(), bonds.size() * sizeof(Bond), cudaMemcpyHostToDevice, st));
-      CUDA_TRY(cudaMemcpyAsync(d_bstart, bstart.data(), bstart.size() * 4, cudaMemcpyHostToDevice, st));
-      if (!Bz.empty()) CUDA_TRY(cudaMemcpyAsync(d_ham, Bz.data(), Bz.size() * 8, cudaMemcpyHostToDevice, st));
+      if (!hit) {
+        if (!bonds.empty()) CUDA_TRY(upload(d_bonds, bonds.data(), bonds.size() * sizeof(Bond), m.ham_host[0]));
+        CUDA_TRY(upload(d_bstart, bstart.data(), bstart.size() * 4, m.ham_host[1]));
+        if (!Bz.empty()) CUDA_TRY(upload(d_ham, Bz.data(), Bz.size() * 8, m.ham_host[2]));
+      }
       RNNWF_COUNT_LAUNCH(); bond_diag_kernel<<<gsamp, tpb, 0, st>>>(samples_dev, rows, m.nsites, m.d_site_of_t, d_bonds, (int)bonds.size(), d_ham, (int)Bz.size(), eloc_dev);
       const long long ncnt = (long long)T * rows;
       RNNWF_COUNT_LAUNCH(); bond_count_kernel<<<std::min(8192, cdiv(ncnt + 1, tpb)), tpb, 0, st>>>(samples_dev, rows, m.nsites, T, m.d_site_of_t, d_bonds, d_bstart, d_counts);
@@ -989,6 +1011,7 @@ int enumerate_connected(const rnnwf_model& m, int hamiltonian, const double* ham
       return fail(RNNWF_EINVAL, "unknown hamiltonian");
   }
   CUDA_TRY(cudaGetLastError());
+  if (!hit) { m.ham_kind = hamiltonian; m.ham_block.assign(ham, ham + ham_len); }
   out.nchild_fixed = nchild_fixed; out.rows_dev = rows_dev; out.have_children = have_children;
   return RNNWF_OK;
 }

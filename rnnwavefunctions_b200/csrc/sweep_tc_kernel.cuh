@@ -521,7 +521,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
                 hsave[0] = hnew[0]; hsave[1] = hnew[1]; hsave[2] = hnew[2]; hsave[3] = hnew[3];
                 if (SPLIT) { split_f16x2(hnew[0] * HS, hnew[1] * HS, o.x, ol.x); split_f16x2(hnew[2] * HS, hnew[3] * HS, o.y, ol.y); }
                 else { o.x = pack_f16x2(hnew[0], hnew[1]); o.y = pack_f16x2(hnew[2], hnew[3]); }
-                if (save) {
+                if (save && !(P.debug_flags & 8)) {
                   sv_g[0] = make_float4(gu[0], gu[1], gu[2], gu[3]);
                   sv_g[TC_ROWS] = make_float4(gt[0], gt[1], gt[2], gt[3]);
                   sv_g[2 * TC_ROWS] = make_float4(gm[0], gm[1], gm[2], gm[3]);
@@ -531,7 +531,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
               mbar_arrive_a(bar_free_a + s * 8u);   // nothing to read: its columns of the narrow last pass are padding
             }
             // saved history (FP32, row-major): padding units are written too (as zeros) -- prefix reuse reads whole pieces
-            if (save && p < np_own) *reinterpret_cast<float4*>(sv_h) = make_float4(hsave[0], hsave[1], hsave[2], hsave[3]);
+            if (save && p < np_own && !(P.debug_flags & 4)) *reinterpret_cast<float4*>(sv_h) = make_float4(hsave[0], hsave[1], hsave[2], hsave[3]);
             if (p < np_own) {
               // 4 halves = 2 TMEM columns of the next operand's carry half; the same 8 bytes go to the ring image
               // (zeros for padding units and for rows past the end of the batch)
@@ -542,7 +542,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
               if (p == one_p) o_one = o;                    // (kept for the constant-1 store after the loop)
             }
             ring_p += (p & 1) ? (TC_RING_QUAD - 8u) : 8u;
-            if (sv_i != nullptr) {
+            if (sv_i != nullptr && !(P.debug_flags & 2)) {
               const int j0 = p * TC_JP + sub * 4;
               if (j0 < hnc * 8) {
   #pragma unroll

@@ -47,6 +47,7 @@ def main():
     ap.add_argument("--debug-flags", type=int, default=0, help="also time E_loc with RNNWF_TC_DEBUG set to this")
     ap.add_argument("--trace", type=int, default=0, help="print this many events of CTA 0's timeline")
     ap.add_argument("--trace-from", type=int, default=200000, help="first cycle of the printed window")
+    ap.add_argument("--what", default="eloc", choices=["eloc", "sample"], help="which launch carries the counters / the trace")
     args = ap.parse_args()
     eng = Engine(cell=_lib.CELL_TENSGRU2D, nx=args.nx, ny=args.ny, num_units=args.nh, complex_head=True, u1=True,
                  device="cuda:0", precision="tc")
@@ -73,7 +74,10 @@ def main():
     lib.rnnwf_debug_set_tc_prof.argtypes = [ctypes.c_void_p]
     lib.rnnwf_debug_set_tc_prof.restype = None
     lib.rnnwf_debug_set_tc_prof(ctypes.c_void_p(prof.data_ptr()))
-    eloc()
+    if args.what == "sample":
+        eng.sample(args.ns, saved=saved)
+    else:
+        eloc()
     torch.cuda.synchronize()
     lib.rnnwf_debug_set_tc_prof(ctypes.c_void_p(0))
     trace = prof[nsm * 16:].view(ROLES, TRACE_LEN).cpu().numpy()
