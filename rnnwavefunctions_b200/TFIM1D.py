@@ -1,5 +1,5 @@
-"""Drop-in for the reference package ``1DTFIM/`` (also serves ``2DTFIM_1DRNN/``: a 1D GRU raster-scanned over
-an Nx x Ny lattice is this class with systemsize = Nx*Ny).
+"""Drop-in for the reference package ``1DTFIM/`` (the twin ``2DTFIM_1DRNN/`` -- the same GRU raster-scanned over an
+Nx x Ny lattice with 2D Ising bonds -- is ``TFIM2D_1DRNN.py``).
 
 Reference: 1DTFIM/RNNwavefunction.py, RNNwavefunction_paritysym.py, TrainingRNN_1DTFIM.py, run_1dTFIM.py."""
 import math

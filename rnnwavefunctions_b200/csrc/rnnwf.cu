@@ -108,8 +108,9 @@ int build_model(rnnwf_model& m) {
 
   switch (c.cell) {
     case RNNWF_CELL_GRU1D: {
-      const int L = std::max(1, c.num_layers), N = Nx;
-      if (Ny != 1) return fail(RNNWF_EINVAL, "GRU1D needs ny == 1");
+      // ny > 1: the same chain raster-scanned over an Nx x Ny lattice, site (i, j) at flat index i * Ny + j
+      // (2DTFIM_1DRNN/RNNwavefunction.py:74-76,123; Training1DRNN_2DTFIM.py:27); configurations stay flat [B, Nx * Ny]
+      const int L = std::max(1, c.num_layers), N = Nx * Ny;
       m.nslots = 2; m.D = 2; m.bits = 1; m.Tsym = N; m.symL = L; m.Q = N * L; m.nsites = N;
       m.NTU = 4; m.Greal = nh; m.gru_type = true;
       for (int l = 0; l < L; ++l) {

@@ -59,8 +59,8 @@ class Engine:
             self.tensors.append((name.value.decode(), int(off.value), tuple(int(shp[k]) for k in range(nd.value))))
         if cell == _lib.CELL_GRU4:
             self.cfg_shape = (nx, ny, 3)
-        elif ny == 1 and cell == _lib.CELL_GRU1D:
-            self.cfg_shape = (nx,)
+        elif cell == _lib.CELL_GRU1D:
+            self.cfg_shape = (nx * ny,)        # chains; ny > 1: the chain raster-scanned over an nx x ny lattice (2DTFIM_1DRNN)
         else:
             self.cfg_shape = (nx, ny)
         self.nsteps = nx * ny  # symbols (= uniforms) per configuration

@@ -21,7 +21,7 @@ def oracle_run(eng, P, samples=None, uniforms=None, numsamples=None):
     if samples is not None:
         samples = torch.as_tensor(np.asarray(samples)).long()
     if eng.cell == _lib.CELL_GRU1D:
-        return owf.rnn1d(P, eng.nx, [eng.nh] * eng.num_layers, samples=samples, uniforms=uniforms,
+        return owf.rnn1d(P, eng.nx * eng.ny, [eng.nh] * eng.num_layers, samples=samples, uniforms=uniforms,
                          numsamples=numsamples, complex_=eng.complex_head, u1=eng.u1)
     if eng.cell == _lib.CELL_GRU4:
         return owf.rydberg2d(P, eng.nx, eng.ny, eng.nh, samples=samples, uniforms=uniforms, numsamples=numsamples)

@@ -118,3 +118,30 @@ def test_short_training_run_lowers_the_energy(cuda):
                                         learningrate=5e-3, seed=111)
     assert np.mean(meanE[:5]) > np.mean(meanE[-10:]) + 0.5
     assert -12.5 < np.mean(meanE[-10:]) < -11.0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("layers", [1, 2])
+def test_2dtfim_1drnn_twin(cuda, layers):
+    """2DTFIM_1DRNN/: the GRU chain raster-scanned over an Nx x Ny lattice with the 2D Ising bonds
+    (RNNwavefunction.py:40-130, Training1DRNN_2DTFIM.py:13-81), reference call sequence, against the oracle."""
+    from rnnwavefunctions_b200 import TFIM2D_1DRNN
+    from helpers import assert_rel
+    Nx, Ny, ns, nh = 4, 3, 60, 18
+    wf = TFIM2D_1DRNN.RNNwavefunction(Nx, Ny, units=[nh] * layers, seed=5)
+    g = torch.Generator().manual_seed(6)
+    p = wf.engine.params.cpu()
+    wf.engine.set_weights(p + 0.2 * (torch.rand(p.shape, generator=g) - 0.5))
+    samples_ = wf.sample(ns, 2)
+    assert tuple(samples_.shape) == (ns, Nx * Ny)
+    inputs = placeholder(dtype="int32", shape=[None, Nx * Ny])
+    lpt = wf.log_probability(inputs, 2)
+    Jz = np.random.RandomState(1).uniform(0.5, 1.5, (Nx, Ny))
+    samples = samples_.cpu().numpy()
+    E = TFIM2D_1DRNN.Ising2D_local_energies(Jz, 2.0, Nx, Ny, samples, None, lpt, inputs, None, Session())
+    P = oracle_params(wf.engine)
+    f = oracle_logpsi_fn(wf.engine, P)
+    ref = ole.ising2d_local_energies(Jz, 2.0, samples.reshape(ns, Nx, Ny), lambda c: f(c.reshape(c.shape[0], -1)))
+    assert_rel(E, ref, 1e-5, f"2DTFIM_1DRNN E_loc, {layers} layer(s)")
+    lp = Session().run(lpt, feed_dict={inputs: samples})
+    assert_rel(lp, oracle_run(wf.engine, P, samples=samples)["logp"].detach().numpy(), 1e-5, "2DTFIM_1DRNN log P")

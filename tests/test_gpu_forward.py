@@ -94,4 +94,9 @@ def test_errors_are_loud(cuda):
     with pytest.raises(ValueError):
         eng.logpsi(torch.zeros(4, 7, dtype=torch.int8))
     with pytest.raises(ValueError):
-        Engine(cell=_lib.CELL_GRU1D, nx=8, ny=2, num_units=4)
+        Engine(cell=_lib.CELL_TENSGRU2D, nx=8, ny=2, num_units=4, u1=True, magnetization=0, complex_head=False, precision="tc3", num_layers=1).local_energies(
+            _lib.HAM_TFIM1D, [1.0] * 8, torch.zeros(2, 8, 2, dtype=torch.int8))       # TFIM1D needs a chain
+    chain2d = Engine(cell=_lib.CELL_GRU1D, nx=4, ny=2, num_units=4)                    # the 2DTFIM_1DRNN twin: flat [B, 8] rows
+    assert chain2d.cfg_shape == (8,)
+    with pytest.raises(ValueError):
+        chain2d.local_energies(_lib.HAM_TFIM1D, [1.0] * 8, torch.zeros(2, 8, dtype=torch.int8))
