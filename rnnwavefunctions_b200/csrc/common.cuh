@@ -103,6 +103,8 @@ struct SweepParams {
   int tc_np;
   unsigned long long* tc_prof;  // optional per-CTA cycle counters (debug)
   int debug_flags;                    // tensor-core sweep timing experiments (RNNWF_TC_DEBUG), 0 in production
+  long long sched_ns;          // CHILD mode of single-flip Hamiltonians: samples per (step, bit) group of the regular child list
+  int sched_bits;              //   (child index (t bits + k) ns + n), 0 = no regular structure
   const float* g1_pack;        // dedicated 1D-GRU kernels (gru1d.cuh): parameter image copied to shared memory
   // ---- scratch
   float* ring;              // [gridDim.x][ring_len][Mp][nhp]

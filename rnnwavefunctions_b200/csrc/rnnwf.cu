@@ -1048,6 +1048,10 @@ int rnnwf_local_energies(rnnwf_handle h, int hamiltonian, const double* ham, int
   P.mode = MODE_CHILD; P.rows = en.nchild_fixed; P.rows_dev = en.rows_dev; P.cfg_in = samples_dev; P.children = d_children;
   P.par_logp = logp_dev; P.par_phase = phase_dev; P.eloc = eloc_dev;
   P.ring = reinterpret_cast<float*>(ws + L.off_ring);
+  if (en.rows_dev == nullptr) {      // single-flip Hamiltonians: the child list is regular (all_flips_kernel)
+    P.sched_ns = rows;
+    P.sched_bits = (hamiltonian == RNNWF_HAM_RYDBERG) ? 3 : 1;
+  }
   if (saved_dev != nullptr) {
     const Saved sv = m.saved_layout(rows);
     const char* b = static_cast<const char*>(saved_dev);

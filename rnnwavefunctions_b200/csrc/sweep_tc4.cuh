@@ -49,7 +49,7 @@ __host__ __device__ inline long long t4_pass_bytes(int NP) { return 4LL * NP * T
 __host__ __device__ inline long long t4_step_bytes(int NP) { return (long long)NP * T4_A_BYTES; }   // one site's ring image
 
 struct T4Smem {
-  int off_stage, off_xa, off_part, off_headw, off_headb, off_step, off_last, off_sym, off_bar, off_cnt, off_tmem, total;
+  int off_stage, off_xa, off_part, off_headw, off_headb, off_step, off_last, off_sym, off_bar, off_cnt, off_tmem, off_sched, total;
   __host__ __device__ T4Smem(int stages, int Q) {
     int o = 0;
     off_stage = o; o += stages * (int)T4_STAGE;
@@ -63,6 +63,7 @@ struct T4Smem {
     off_bar = o;   o += 256;
     off_cnt = o;   o += 32;                         // ring-chunk / prologue counters
     off_tmem = o;  o += 16;
+    off_sched = o; o += 32;                         // this CTA's tile range under the parent-block-major schedule
     total = o + 128;
   }
 };
@@ -162,6 +163,26 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
     }
     lastS[i] = (int16_t)last;
   }
+  // Parent-block-major schedule of the connected-configuration sweep (single-flip Hamiltonians: the child list is regular,
+  // child index (t bits + k) ns + n).  With prefix reuse every tile first converts its parents' saved history of the steps it
+  // looks back to into the CTA's ring -- on this periodic lattice nearly all earlier steps, ~q0 x 128 KB per tile.  Tiles of
+  // the SAME 128 parents restarting at increasing steps share that prefix: walked in that order by one CTA, each tile only
+  // has to restore the steps the previous tile overwrote.  The linear order L = block (T bits) + (t bits + k) is cut into
+  // gridDim.x contiguous ranges of equal cost (a tile costs T - t sites).
+  long long* const schedS = reinterpret_cast<long long*>(smem + L.off_sched);
+  const bool block_major = (MODE == MODE_CHILD) && P.par_hist != nullptr && P.sched_ns > 0 && P.rows_dev == nullptr;
+  if (tid == 0 && block_major) {
+    const long long T = P.Q, bits = P.sched_bits, G = T * bits, nb = (P.sched_ns + T4_ROWS - 1) / T4_ROWS;
+    const long long Cb = bits * T * (T + 1) / 2, totc = nb * Cb;
+    auto cut = [&](long long x) -> long long {
+      const long long b = x / Cb, rem = x % Cb;
+      long long acc = 0, r = 0;
+      while (acc < rem) { acc += T - r / bits; ++r; }
+      return b * G + r;
+    };
+    schedS[0] = cut(totc * (long long)blockIdx.x / (long long)gridDim.x);
+    schedS[1] = (blockIdx.x + 1 == gridDim.x) ? nb * G : cut(totc * (long long)(blockIdx.x + 1) / (long long)gridDim.x);
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -194,6 +215,18 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
 #endif
   const long long total_rows = (P.rows_dev != nullptr) ? (long long)(*P.rows_dev) : P.rows;
   const long long ntiles = (total_rows + T4_ROWS - 1) / T4_ROWS;
+  // tile iteration of this CTA: `ti` runs over the schedule above, or over the tiles blockIdx.x, + gridDim.x, ...
+  const long long ti_begin = block_major ? schedS[0] : (long long)blockIdx.x;
+  const long long ti_end = block_major ? schedS[1] : ntiles;
+  const long long ti_step = block_major ? 1 : (long long)gridDim.x;
+  const long long sched_G = (long long)P.Q * P.sched_bits;
+  auto tile_row0 = [&](long long ti) -> long long {
+    return block_major ? (ti % sched_G) * P.sched_ns + (ti / sched_G) * T4_ROWS : ti * T4_ROWS;
+  };
+  auto tile_rows = [&](long long ti, long long row0) -> int {
+    const long long left = block_major ? P.sched_ns - (ti / sched_G) * T4_ROWS : total_rows - row0;
+    return (int)(left < (long long)T4_ROWS ? left : (long long)T4_ROWS);
+  };
   auto tile_q0 = [&](long long row0) -> int {
     int ts0 = 0;
     if (MODE == MODE_CHILD && P.par_hist != nullptr) {
@@ -215,8 +248,8 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
     const uint32_t A_LBO = T4_ROWS * 16, B_LBO = T4_N * 16, SBO = 128;
     const uint64_t xdesc = tc_desc(smem_u32(xa), A_LBO, SBO);
     uint32_t n = 0, it = 0, hs = 0;
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-      const int q0 = tile_q0(tile * T4_ROWS);
+    for (long long ti = ti_begin; ti < ti_end; ti += ti_step) {
+      const int q0 = tile_q0(tile_row0(ti));
       for (int q = q0; q < P.Q; ++q, ++hs) {
         const int nact = (stepT[q].x >> 16) & 0xff;
         const int njobs = nact * NP;
@@ -265,8 +298,8 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
     const bool leader = elect_one();
     uint32_t n = 0;
     const uint32_t bB = (P.debug_flags & 1) ? T4_B_BYTES / 2 : T4_B_BYTES;   // (RNNWF_TC_DEBUG bit 0: timing experiment)
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-      const int q0 = tile_q0(tile * T4_ROWS);
+    for (long long ti = ti_begin; ti < ti_end; ti += ti_step) {
+      const int q0 = tile_q0(tile_row0(ti));
       for (int q = q0; q < P.Q; ++q) {
         const int4 e = stepT[q];
         const int nact = (e.x >> 16) & 0xff;
@@ -293,8 +326,8 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
     uint32_t n = 0, hs = 0, nt = 0;
     uint32_t seen[T4_MAXNP] = {0u, 0u, 0u, 0u};     // ring chunk c: writer warps already waited for
     const uint32_t bA = (P.debug_flags & 2) ? T4_A_BYTES / 2 : T4_A_BYTES;   // (RNNWF_TC_DEBUG bit 1: timing experiment)
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++nt) {
-      const int q0 = tile_q0(tile * T4_ROWS);
+    for (long long ti = ti_begin; ti < ti_end; ti += ti_step, ++nt) {
+      const int q0 = tile_q0(tile_row0(ti));
       const uint32_t hs0 = hs;
       // the tile's prologue (symbols, parent history -> ring) must be complete before any of its A chunks is read;
       // it only starts once the previous tile is finished, so every earlier ring write is covered as well
@@ -346,10 +379,17 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
     const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
     const uint32_t acc0 = tmem_base + lane_base + (uint32_t)(sub * T4_TPS);
     uint32_t it = 0, hs = 0, ntile = 0;
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++ntile) {
-      const long long row0 = tile * T4_ROWS;
-      const int nrows = (int)((total_rows - row0 < (long long)T4_ROWS) ? (total_rows - row0) : (long long)T4_ROWS);
+    long long prev_block = -1;
+    int prev_q0 = 0;
+    for (long long ti = ti_begin; ti < ti_end; ti += ti_step, ++ntile) {
+      const long long row0 = tile_row0(ti);
+      const long long tile = row0 / T4_ROWS;            // (index into the tile-blocked saved gates: sampling / evaluation only)
+      const int nrows = tile_rows(ti, row0);
       const int q0 = tile_q0(row0);
+      // same 128 parents as the previous tile and a later restart: the ring still holds their history below prev_q0
+      const int restore_from = (block_major && ti / sched_G == prev_block && prev_q0 <= q0) ? prev_q0 : 0;
+      prev_block = block_major ? ti / sched_G : -1;
+      prev_q0 = q0;
       const bool live = row < nrows;
       int rparent = 0;
       T4_T0();
@@ -383,7 +423,7 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
         const float* pbase = P.par_hist + (size_t)rparent * nhp + sub * 16;
         unsigned char* dbase = ring_cta + (size_t)(2 * sub) * (T4_ROWS * 16) + (size_t)row * 16;
 #pragma unroll 1
-        for (int j = 0; j < q0; ++j) {
+        for (int j = restore_from; j < q0; ++j) {
           if ((int)lastS[j] < q0) continue;           // no step of this tile looks back to it (uniform over the CTA)
           const float* psrc = pbase + (size_t)j * (size_t)P.par_rows * nhp;
           unsigned char* dst = dbase + (size_t)j * (size_t)step_bytes;
@@ -514,9 +554,9 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
     // ======================= head warp: four rows per thread =======================
     const int hrow = lane;
     uint32_t hs = 0;
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-      const long long row0 = tile * T4_ROWS;
-      const int nrows = (int)((total_rows - row0 < (long long)T4_ROWS) ? (total_rows - row0) : (long long)T4_ROWS);
+    for (long long ti = ti_begin; ti < ti_end; ti += ti_step) {
+      const long long row0 = tile_row0(ti);
+      const int nrows = tile_rows(ti, row0);
       const int ts0 = tile_q0(row0), q0 = ts0;
       double rlogp[T4_HEAD_ROWS];
       int rparent[T4_HEAD_ROWS];
