@@ -540,12 +540,13 @@ EXTRA_WORKLOADS = [("tfim1d_n20_gru50", "auto"), ("tfim1d_n20_gru50x3", "auto"),
 def reference_arm(args, w, config, metric, unit, rank):
     """`--impl reference`: the reference's own implementation needs TensorFlow 1.13.1 (unavailable on this box), so the timed
     arm is the oracle port of its algorithm on all host cores, each step a bounded sample of the same workload, large enough
-    that every chunked forward carries at least one full chunk of the reference's size (20 000 rows at C4)."""
+    that the chunked forwards carry full chunks of the reference's size (20 000 rows at C4)."""
     if rank != 0:
         return
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    ns_ref = 160 if "heis" in args.workload else min(w["ns"], 200 if "rydberg" in args.workload else 500)
+    # C4: 300 samples = ~40 000 configurations = two full 20 000-row chunks of the reference's chunk loop per step
+    ns_ref = 300 if "heis" in args.workload else min(w["ns"], 200 if "rydberg" in args.workload else 500)
     for _ in range(max(0, min(args.warmup, 1))):
         oracle_step(w, 2)
     tot_c, tot_t = 0, 0.0
