@@ -424,7 +424,7 @@ class Bench:
                     if peaks else "fallback 1400 (B200_PROFILING.md)")
         common = {"algorithmic_flops_per_launch": alg_flops, "algorithmic_tflops": alg_flops / (eloc_ms * 1e-3) / 1e12,
                   "ffma_peak_tflops_measured": ffma_peak, "launch_ms": eloc_ms}
-        if precision == "tc" and w["eng"]["cell"] == "GRU4":
+        if precision in ("tc", "tc3") and w["eng"]["cell"] == "GRU4":
             # sweep_tc4_kernel: per row and unit cell the dense [(live neighbours)*nhq + 32] x [3*nhq] contraction, nhq = 64*passes;
             # a child flipped in cell t re-runs cells t..T-1 (prefix reuse), three children per cell and sample
             nx, ny, nh = w["eng"]["nx"], w["eng"]["ny"], w["eng"]["num_units"]
@@ -438,16 +438,18 @@ class Bench:
                     t = iy * nx + k
                     keys = [(ix - d, iy), (ix, iy - 1), ((ix + d) % nx, iy), (ix, (iy + 1) % ny)]
                     live = sum(1 for (a, b) in keys if 0 <= a < nx and 0 <= b < ny and stepi(a, b) < t)
-                    site_flops.append(2 * (live * nhq + 32) * 3 * nhq + 2 * nh * 8)
+                    # split precision: hi hi + lo hi + hi lo on the hidden jobs, hi + lo weights on the exact one-hot input job
+                    mh, mx = (3, 2) if precision == "tc3" else (1, 1)
+                    site_flops.append(2 * (mh * live * nhq + mx * 32) * 3 * nhq + 2 * nh * 8)
             suffix = np.cumsum(site_flops[::-1])[::-1]
             per_sample = 3 * float(suffix.sum()) if V.prefix_reuse else 3 * T * float(suffix[0])
             exec_flops = ns * per_sample
             achieved = exec_flops / (eloc_ms * 1e-3) / 1e12
-            return dict(common, bound="tensor", kernel="sweep_tc4_kernel (MODE_CHILD)", achieved=achieved, peak=bf16_peak, unit="TFLOP/s",
+            return dict(common, bound="tensor", kernel=f"sweep_tc4_kernel (MODE_CHILD{', split precision' if precision == 'tc3' else ''})", achieved=achieved, peak=bf16_peak, unit="TFLOP/s",
                         frac=achieved / bf16_peak, traffic=None, peak_source=peak_src, executed_flops_per_launch=exec_flops,
                         mma_columns_per_row_site=3 * nhq,
                         note="executed = MMA flops issued per row (absent neighbours skipped, hidden axis padded to 64 per pass, K=32 "
-                             "input/bias job, prefix reuse counted per row); launch_ms brackets rnnwf_local_energies (enumeration kernels + sweep)")
+                             "input/bias job, prefix reuse counted per row; split precision: three MMAs per K step, all counted); launch_ms brackets rnnwf_local_energies (enumeration kernels + sweep)")
         if precision in ("tc", "tc3"):
             # the tensor-core sweep executes, per row and site, the dense [2*nhp] x [7*16*passes] contraction
             nhp = (w["eng"]["num_units"] + 7) // 8 * 8
@@ -534,7 +536,7 @@ def ffma_peak_probe(dev):
 # (N = 1 only; a few steps each) and reported under "workloads"
 EXTRA_WORKLOADS = [("tfim1d_n20_gru50", "auto"), ("tfim1d_n20_gru50x3", "auto"), ("j1j2_n20_cgru50", "auto"), ("tfim2d_12x12_rnn50", "auto"),
                    ("heis10x10_sq_tgru100", "auto"), ("heis10x10_tri_tgru100", "tc3"), ("heis10x10_tri_tgru100", "fp32"),
-                   ("rydberg_4x4_gru256", "auto"), ("rydberg_8x8_gru256", "auto")]
+                   ("rydberg_4x4_gru256", "auto"), ("rydberg_4x4_gru256", "tc3"), ("rydberg_8x8_gru256", "auto")]
 
 
 def reference_arm(args, w, config, metric, unit, rank):

@@ -61,6 +61,7 @@ struct rnnwf_model_impl {
   bool g1_bwd = false;          // ... and their one-launch reverse sweep (gru1d_bwd.cuh)
   float* d_g1packT = nullptr;
   bool tc_split = false;        // precision 2: split-precision operands (FP16 hi + lo, three MMAs per K step) -- the 1e-5 bound on the tensor cores
+  bool tc4_split = false;       // ... in the split-precision regime (precision tc3)
   bool tc4 = false;             // tensor-core sweep of the four-neighbour GRU (sweep_tc4.cuh); saved state and backward as in the FFMA regime
   int tc_np = 0;
   unsigned char* d_tcB = nullptr;

@@ -33,6 +33,11 @@ cudaError_t g1_pack_bwd_launch(const G1PackSrc& S, int nh, int L, int D, int ND,
 namespace rnnwf {   // sweep_tc_inst.cu
 cudaError_t tc_sweep_set_smem(int cellk, bool biasmma, bool split, int smem_bytes);
 cudaError_t tc_sweep_launch(const SweepParams& P, int cellk, bool biasmma, bool split, int grid, int threads, int smem_bytes, cudaStream_t st);
+// sweep_tc4_inst.cu
+cudaError_t tc4_sweep_set_smem(bool split, int smem_bytes);
+cudaError_t tc4_sweep_launch(const SweepParams& P, bool split, int grid, int threads, int smem_bytes, cudaStream_t st);
+cudaError_t tc4_pack_launch(const float* W, const float* Wg, const float* Wmerge, const float* b, const float* bg, int nh, int NP, bool split,
+                            void* out, cudaStream_t st);
 }
 
 struct rnnwf_model : rnnwf::rnnwf_model_impl {};
@@ -302,14 +307,15 @@ int build_model(rnnwf_model& m) {
   }
   m.tc_enabled = (m.precision >= 1 && (m.cell == CELL_TENSGRU2D || m.cell == CELL_TENS2D || m.cell == CELL_VANILLA2D));
   m.tc_split = m.tc_enabled && m.precision == 2;
-  m.tc4 = (m.precision == 1 && m.cell == CELL_GRU4);
+  m.tc4 = (m.precision >= 1 && m.cell == CELL_GRU4);
+  m.tc4_split = m.tc4 && m.precision == 2;
   // small 1D models in the FFMA regime: dedicated kernels with the whole weight set resident in shared memory (gru1d.cuh)
   m.g1 = (m.precision == 0 && m.cell == CELL_GRU1D && g1_supported(m.nh, m.symL, m.Tsym) && std::getenv("RNNWF_NO_G1") == nullptr);
   m.g1_bwd = m.g1 && g1_bwd_supported(m.nh, m.symL) && std::getenv("RNNWF_NO_G1_BWD") == nullptr;
   if (m.precision == 1 && !m.tc_enabled && !m.tc4)
     return fail(RNNWF_EINVAL, "the tensor-core regime is implemented for the 2D cells (tensorized GRU, tensorized, vanilla RNN, four-neighbour GRU)");
-  if (m.precision == 2 && !m.tc_enabled)
-    return fail(RNNWF_EINVAL, "the split-precision tensor-core regime is implemented for the two-neighbour 2D cells (tensorized GRU, tensorized, vanilla RNN)");
+  if (m.precision == 2 && !m.tc_enabled && !m.tc4)
+    return fail(RNNWF_EINVAL, "the split-precision tensor-core regime is implemented for the 2D cells (tensorized GRU, tensorized, vanilla RNN, four-neighbour GRU)");
   // column passes per site: 16 units x 7 blocks each for the tensorized GRU; the vanilla cell needs one (7 unit pieces)
   m.tc_np = (m.cell == CELL_VANILLA2D) ? 1 : (m.nh + TC_JP - 1) / TC_JP;
   if (m.tc_enabled) {
@@ -436,10 +442,7 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
   }
   if (m.tc4) {
     RNNWF_COUNT_LAUNCH();
-    if (P.mode == MODE_SAMPLE) sweep_tc4_kernel<MODE_SAMPLE><<<s.grid, s.threads, s.smem, st>>>(P);
-    else if (P.mode == MODE_CHILD) sweep_tc4_kernel<MODE_CHILD><<<s.grid, s.threads, s.smem, st>>>(P);
-    else sweep_tc4_kernel<MODE_EVAL><<<s.grid, s.threads, s.smem, st>>>(P);
-    e = cudaGetLastError();
+    e = tc4_sweep_launch(P, m.tc4_split, s.grid, s.threads, s.smem, st);
     if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("tensor-core sweep (four-neighbour GRU) launch: ") + cudaGetErrorString(e));
     return RNNWF_OK;
   }
@@ -447,7 +450,7 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
 }
 
 long long ring_bytes(const rnnwf_model& m, int grid, int Mp) {
-  if (m.tc4) return (long long)grid * m.Q * t4_step_bytes(m.tc_np);   // FP16 chunk images of every site, per persistent CTA
+  if (m.tc4) return (long long)grid * m.Q * t4_step_bytes(m.tc_np, m.tc4_split);   // FP16 chunk images of every site, per persistent CTA
   // tensor-core regime: one FP16 history image per slot in the fixed quad layout of sweep_tc.cuh (TC_RING_SLOT bytes)
   const long long slot = m.tc_enabled ? (long long)tc_ring_slot(m.nhp) * (m.tc_split ? 2 : 1) : (long long)Mp * m.nhp * 4;
   return (long long)grid * m.ring_len * slot;
@@ -614,10 +617,8 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
   }
   if (m->tc4) {
     const int t4s = T4Smem(t4_stages(m->Q), m->Q).total;
-    CREATE_TRY(cudaMalloc(&m->d_tcB, (size_t)m->tc_np * (size_t)t4_pass_bytes(m->tc_np)));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc4_kernel<MODE_SAMPLE>, cudaFuncAttributeMaxDynamicSharedMemorySize, t4s));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc4_kernel<MODE_EVAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, t4s));
-    CREATE_TRY(cudaFuncSetAttribute(sweep_tc4_kernel<MODE_CHILD>, cudaFuncAttributeMaxDynamicSharedMemorySize, t4s));
+    CREATE_TRY(cudaMalloc(&m->d_tcB, (size_t)m->tc_np * (size_t)t4_pass_bytes(m->tc_np, m->tc4_split)));
+    CREATE_TRY(tc4_sweep_set_smem(m->tc4_split, t4s));
   }
   if (m->g1) {
     const G1Layout Y(m->nh, m->symL, m->Tsym);
@@ -760,10 +761,9 @@ int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
     }
   }
   if (h->tc4) {
-    const long long n = (long long)h->tc_np * (t4_pass_bytes(h->tc_np) / 2);
-    RNNWF_COUNT_LAUNCH(); pack_tc4_kernel<<<std::min(2048, cdiv(n, 256)), 256, 0, st>>>(
-        params_dev + h->tensor("W")->offset, params_dev + h->tensor("Wg")->offset, params_dev + h->tensor("Wmerge")->offset,
-        params_dev + h->tensor("b")->offset, params_dev + h->tensor("bg")->offset, h->nh, h->tc_np, reinterpret_cast<__half*>(h->d_tcB));
+    RNNWF_COUNT_LAUNCH();
+    CUDA_TRY(tc4_pack_launch(params_dev + h->tensor("W")->offset, params_dev + h->tensor("Wg")->offset, params_dev + h->tensor("Wmerge")->offset,
+                             params_dev + h->tensor("b")->offset, params_dev + h->tensor("bg")->offset, h->nh, h->tc_np, h->tc4_split, h->d_tcB, st));
   }
   CUDA_TRY(cudaGetLastError());
   h->d_params = params_dev;
@@ -1404,7 +1404,7 @@ int rnnwf_describe(rnnwf_handle h, char* buf, int cap) {
                 h->tc_split ? "tcgen05 split precision: FP16 hi+lo operands, 3 MMAs per K step, FP32 accumulate in TMEM (column passes of 112, double-buffered)"
                 : h->g1 ? "FFMA fp32, dedicated 1D-GRU kernels: one launch per sweep, weights resident in shared memory"
                 : h->tc_enabled ? "tcgen05 FP16 operands, FP32 accumulate in TMEM (column passes of 112, double-buffered)"
-                              : (h->tc4 ? "tcgen05 FP16 operands streamed from the L2 ring (A) and the weight image (B), FP32 accumulate in TMEM (column passes of 192, double-buffered)" : "FFMA fp32"), h->Gblk, h->TJ, h->NTU, h->WC, h->ncb, KC,
+                              : (h->tc4 ? (h->tc4_split ? "tcgen05 split precision: FP16 hi+lo operands streamed from the L2 ring (A) and the weight image (B), 3 MMAs per K step, FP32 accumulate in TMEM (column passes of 192, double-buffered)" : "tcgen05 FP16 operands streamed from the L2 ring (A) and the weight image (B), FP32 accumulate in TMEM (column passes of 192, double-buffered)") : "FFMA fp32"), h->Gblk, h->TJ, h->NTU, h->WC, h->ncb, KC,
                 h->ring_len, (long long)h->num_params);
   return RNNWF_OK;
 }

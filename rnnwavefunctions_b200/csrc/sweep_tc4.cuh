@@ -45,8 +45,13 @@ constexpr int T4_HEAD_ROWS = 4;
 constexpr int T4_MAXNP = 4;                       // num_units <= 256
 constexpr uint32_t T4_TMEM_COLS = 512;
 
-__host__ __device__ inline long long t4_pass_bytes(int NP) { return 4LL * NP * T4_B_BYTES + T4_XB_BYTES; }
-__host__ __device__ inline long long t4_step_bytes(int NP) { return (long long)NP * T4_A_BYTES; }   // one site's ring image
+// Split precision (precision tc3): every FP16 image exists twice, hi + lo of the scaled value (TC_SPLIT_HS h, TC_SPLIT_WS w),
+// and a K job covers 32 hidden units instead of 64 so that a stage still is 40 KB:
+//   stage  = [A hi 8 KB | A lo 8 KB | B hi 12 KB | B lo 12 KB],  six MMAs per job (hi hi + lo hi + hi lo per K = 16 step);
+//   ring   = per site and 64-unit chunk [half 2][hi | lo][k-core 4][row 128][8 halves]   (one 16 KB bulk copy per job);
+//   weights= per pass [job (slot, chunk, half)][hi | lo][k-core 4][n 192][8 halves], then the input / bias job [hi | lo][k-core 4].
+__host__ __device__ inline long long t4_pass_bytes(int NP, bool split = false) { return (4LL * NP * T4_B_BYTES + T4_XB_BYTES) * (split ? 2 : 1); }
+__host__ __device__ inline long long t4_step_bytes(int NP, bool split = false) { return (long long)NP * T4_A_BYTES * (split ? 2 : 1); }   // one site's ring image
 
 struct T4Smem {
   int off_stage, off_xa, off_part, off_headw, off_headb, off_step, off_last, off_sym, off_bar, off_cnt, off_tmem, off_sched, total;
@@ -92,8 +97,11 @@ __device__ __forceinline__ void t4_wait_count(const uint32_t* cnt, uint32_t targ
   __threadfence_block();
 }
 
-template <int MODE>
+template <int MODE, bool SPLIT>
 __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepParams P) {
+  constexpr int KH = SPLIT ? 2 : 1;                      // K jobs per 64-unit chunk
+  constexpr float HS = SPLIT ? TC_SPLIT_HS : 1.0f, DS = SPLIT ? 1.0f / (TC_SPLIT_HS * TC_SPLIT_WS) : 1.0f;
+  constexpr uint32_t A_CHUNK = T4_A_BYTES * KH;          // ring bytes of one 64-unit chunk
   extern __shared__ __align__(128) unsigned char t4_smem[];
   const int NP = P.tc_np;
   const uint32_t NS = (uint32_t)t4_stages(P.Q);
@@ -122,8 +130,8 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int nh = P.nh, nhp = P.nhp;
-  const long long pass_bytes = t4_pass_bytes(NP);
-  const long long step_bytes = t4_step_bytes(NP);
+  const long long pass_bytes = t4_pass_bytes(NP, SPLIT);
+  const long long step_bytes = t4_step_bytes(NP, SPLIT);
 
   if (tid == 0) {
     for (int i = 0; i < T4_MAX_STAGES; ++i) { mbar_init(bar_full + i, 2); mbar_init(bar_empty + i, 1); }   // two producers per stage
@@ -252,7 +260,7 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
       const int q0 = tile_q0(tile_row0(ti));
       for (int q = q0; q < P.Q; ++q, ++hs) {
         const int nact = (stepT[q].x >> 16) & 0xff;
-        const int njobs = nact * NP;
+        const int njobs = nact * NP * KH;
         for (int p = 0; p < NP; ++p, ++it) {
           const uint32_t buf = it & 1u;
           T4_T0();
@@ -270,7 +278,20 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
             if (leader) {
               const uint32_t sa = smem_u32(stage0 + (size_t)s * T4_STAGE);
               const uint64_t bdesc = tc_desc(sa + T4_A_BYTES, B_LBO, SBO);
-              if (!xjob) {
+              if (SPLIT) {
+                // hi hi + lo hi + hi lo per K = 16 step (the one-hot inputs are exact: hi only)
+                const uint64_t blo = tc_desc(sa + T4_A_BYTES + (xjob ? T4_XB_BYTES : T4_B_BYTES / 2), B_LBO, SBO);
+                const uint64_t ahi = xjob ? xdesc : tc_desc(sa, A_LBO, SBO);
+                const uint64_t alo = tc_desc(sa + T4_A_BYTES / 2, A_LBO, SBO);
+                uint32_t accf = (j > 0) ? 1u : 0u;
+#pragma unroll
+                for (int ks = 0; ks < 2; ++ks) {
+                  const uint64_t oa = (uint64_t)((ks * 2 * A_LBO) >> 4), ob = (uint64_t)((ks * 2 * B_LBO) >> 4);
+                  tc_mma_f16(tmem_d, ahi + oa, bdesc + ob, idesc, accf); accf = 1u;
+                  if (!xjob) tc_mma_f16(tmem_d, alo + oa, bdesc + ob, idesc, 1u);
+                  tc_mma_f16(tmem_d, ahi + oa, blo + ob, idesc, 1u);
+                }
+              } else if (!xjob) {
                 const uint64_t adesc = tc_desc(sa, A_LBO, SBO);
 #pragma unroll
                 for (int ks = 0; ks < 4; ++ks)
@@ -305,13 +326,14 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
         const int nact = (e.x >> 16) & 0xff;
         for (int p = 0; p < NP; ++p) {
           const unsigned char* bsrc = P.tc_B + (size_t)p * (size_t)pass_bytes;
-          for (int j = 0; j <= nact * NP; ++j, ++n) {
-            const bool xjob = (j == nact * NP);
+          const int cj = NP * KH;                        // jobs per neighbour
+          for (int j = 0; j <= nact * cj; ++j, ++n) {
+            const bool xjob = (j == nact * cj);
             const uint32_t s = n % NS;
             if (n >= NS) mbar_wait_relaxed(bar_empty + s, ((n / NS) - 1u) & 1u);
             if (leader) {
-              const uint32_t bytes = xjob ? T4_XB_BYTES : bB;
-              const size_t off = xjob ? (size_t)4 * NP * T4_B_BYTES : (size_t)(((e.x >> (4 * (j / NP))) & 15) * NP + (j % NP)) * T4_B_BYTES;
+              const uint32_t bytes = xjob ? T4_XB_BYTES * KH : bB;
+              const size_t off = xjob ? (size_t)4 * cj * T4_B_BYTES : (size_t)(((e.x >> (4 * (j / cj))) & 15) * cj + (j % cj)) * T4_B_BYTES;
               mbar_expect_tx(bar_full + s, bytes);
               bulk_g2s(stage0 + (size_t)s * T4_STAGE + T4_A_BYTES, bsrc + off, bytes, bar_full + s);
             }
@@ -340,7 +362,8 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
           for (int a = 0; a < nact; ++a) {
             const int slot = (e.x >> (4 * a)) & 15;
             const int nb = nbr_of(e, slot);
-            for (int c = 0; c < NP; ++c, ++n) {
+            for (int ck = 0; ck < NP * KH; ++ck, ++n) {
+              const int c = ck / KH;
               const uint32_t s = n % NS;
               T4_T0();
               if (n >= NS) mbar_wait_relaxed(bar_empty + s, ((n / NS) - 1u) & 1u);
@@ -355,7 +378,7 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
               T4_ACC(6);
               if (leader) {
                 mbar_expect_tx(bar_full + s, bA);
-                bulk_g2s(stage0 + (size_t)s * T4_STAGE, ring_cta + (size_t)nb * (size_t)step_bytes + (size_t)c * T4_A_BYTES, bA, bar_full + s);
+                bulk_g2s(stage0 + (size_t)s * T4_STAGE, ring_cta + (size_t)nb * (size_t)step_bytes + (size_t)ck * T4_A_BYTES, bA, bar_full + s);
               }
               __syncwarp();
             }
@@ -378,6 +401,9 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
     const int row = (quarter << 5) + lane;
     const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
     const uint32_t acc0 = tmem_base + lane_base + (uint32_t)(sub * T4_TPS);
+    // this thread's two k-core rows (units 16 sub + [0,8), + [8,16)) inside a 64-unit ring chunk; split precision: the lo image
+    // of the same half follows the hi image at + T4_A_BYTES / 2
+    const size_t ring_thr = (SPLIT ? (size_t)(sub >> 1) * T4_A_BYTES + (size_t)(sub & 1) * 2 * (T4_ROWS * 16) : (size_t)(2 * sub) * (T4_ROWS * 16)) + (size_t)row * 16;
     uint32_t it = 0, hs = 0, ntile = 0;
     long long prev_block = -1;
     int prev_q0 = 0;
@@ -421,7 +447,7 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
       if (MODE == MODE_CHILD && q0 > 0) {
         // (all 16 loads of a step are issued before the first conversion: the gather is latency-bound)
         const float* pbase = P.par_hist + (size_t)rparent * nhp + sub * 16;
-        unsigned char* dbase = ring_cta + (size_t)(2 * sub) * (T4_ROWS * 16) + (size_t)row * 16;
+        unsigned char* dbase = ring_cta + ring_thr;
 #pragma unroll 1
         for (int j = restore_from; j < q0; ++j) {
           if ((int)lastS[j] < q0) continue;           // no step of this tile looks back to it (uniform over the CTA)
@@ -437,11 +463,21 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
             }
 #pragma unroll
           for (int p = 0; p < T4_MAXNP; ++p) {
-            if (p < NP) {
+            if (p < NP && !SPLIT) {
               *reinterpret_cast<uint4*>(dst + (size_t)p * T4_A_BYTES) =
                   make_uint4(pack_f16x2(v[p][0].x, v[p][0].y), pack_f16x2(v[p][0].z, v[p][0].w), pack_f16x2(v[p][1].x, v[p][1].y), pack_f16x2(v[p][1].z, v[p][1].w));
               *reinterpret_cast<uint4*>(dst + (size_t)p * T4_A_BYTES + T4_ROWS * 16) =
                   make_uint4(pack_f16x2(v[p][2].x, v[p][2].y), pack_f16x2(v[p][2].z, v[p][2].w), pack_f16x2(v[p][3].x, v[p][3].y), pack_f16x2(v[p][3].z, v[p][3].w));
+            }
+            if (p < NP && SPLIT) {
+#pragma unroll
+              for (int kc = 0; kc < 2; ++kc) {
+                uint4 hi, lo;
+                split_f16x2(v[p][2 * kc].x * HS, v[p][2 * kc].y * HS, hi.x, lo.x); split_f16x2(v[p][2 * kc].z * HS, v[p][2 * kc].w * HS, hi.y, lo.y);
+                split_f16x2(v[p][2 * kc + 1].x * HS, v[p][2 * kc + 1].y * HS, hi.z, lo.z); split_f16x2(v[p][2 * kc + 1].z * HS, v[p][2 * kc + 1].w * HS, hi.w, lo.w);
+                *reinterpret_cast<uint4*>(dst + (size_t)p * A_CHUNK + (size_t)kc * (T4_ROWS * 16)) = hi;
+                *reinterpret_cast<uint4*>(dst + (size_t)p * A_CHUNK + (size_t)kc * (T4_ROWS * 16) + T4_A_BYTES / 2) = lo;
+              }
             }
           }
         }
@@ -453,12 +489,13 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
       // constant 1 of the bias row sits at position 6 of slot 0
       auto write_x = [&](int q) {
         const int nb = nbr_of(stepT[q], sub);
-        uint32_t w0 = 0u, w1 = 0u, w2 = 0u, w3 = (sub == 0) ? 0x3C00u : 0u;
+        constexpr uint32_t ONE = SPLIT ? 0x5400u : 0x3C00u;      // FP16 1.0 (split precision: TC_SPLIT_HS = 64.0)
+        uint32_t w0 = 0u, w1 = 0u, w2 = 0u, w3 = (sub == 0) ? ONE : 0u;
         if (nb >= 0) {
           const int sy = symS[nb * T4_ROWS + row];
-          w0 = (sy & 1) ? 0x3C000000u : 0x3C00u;
-          w1 = (sy & 2) ? 0x3C000000u : 0x3C00u;
-          w2 = (sy & 4) ? 0x3C000000u : 0x3C00u;
+          w0 = (sy & 1) ? (ONE << 16) : ONE;
+          w1 = (sy & 2) ? (ONE << 16) : ONE;
+          w2 = (sy & 4) ? (ONE << 16) : ONE;
         }
         *reinterpret_cast<uint4*>(xa + (size_t)sub * (T4_ROWS * 16) + (size_t)row * 16) = make_uint4(w0, w1, w2, w3);
         fence_proxy_async_smem();
@@ -476,7 +513,7 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
         float lg[8];
 #pragma unroll
         for (int d = 0; d < 8; ++d) lg[d] = 0.f;
-        unsigned char* ring_q = ring_cta + (size_t)q * (size_t)step_bytes + (size_t)(2 * sub) * (T4_ROWS * 16) + (size_t)row * 16;
+        unsigned char* ring_q = ring_cta + (size_t)q * (size_t)step_bytes + ring_thr;
 #pragma unroll 1
         for (int p = 0; p < NP; ++p, ++it) {
           const uint32_t buf = it & 1u;
@@ -500,9 +537,9 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
           float hv[16];
 #pragma unroll
           for (int e = 0; e < 16; ++e) {
-            const float u = sigmoid_prescaled(__uint_as_float(dg[e]));
-            const float ht = tanh_prescaled(__uint_as_float(ds[e]));
-            const float mv = __uint_as_float(dm[e]);
+            const float u = SPLIT ? 1.0f / (1.0f + expf(-__uint_as_float(dg[e]) * DS)) : sigmoid_prescaled(__uint_as_float(dg[e]));
+            const float ht = SPLIT ? tanhf(__uint_as_float(ds[e]) * DS) : tanh_prescaled(__uint_as_float(ds[e]));
+            const float mv = __uint_as_float(dm[e]) * DS;
             // u ht + (1 - u) m; padding units have zero weights and biases: u = 1/2, ht = m = 0 -> 0
             hv[e] = live ? fmaf(u, ht - mv, mv) : 0.f;
             if (save) {
@@ -517,10 +554,21 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
             for (int e = 0; e < 16; e += 4)
               if (j0 + e < nhp) *reinterpret_cast<float4*>(hrow + e) = make_float4(hv[e], hv[e + 1], hv[e + 2], hv[e + 3]);
           }
-          *reinterpret_cast<uint4*>(ring_q + (size_t)p * T4_A_BYTES) =
-              make_uint4(pack_f16x2(hv[0], hv[1]), pack_f16x2(hv[2], hv[3]), pack_f16x2(hv[4], hv[5]), pack_f16x2(hv[6], hv[7]));
-          *reinterpret_cast<uint4*>(ring_q + (size_t)p * T4_A_BYTES + T4_ROWS * 16) =
-              make_uint4(pack_f16x2(hv[8], hv[9]), pack_f16x2(hv[10], hv[11]), pack_f16x2(hv[12], hv[13]), pack_f16x2(hv[14], hv[15]));
+          if (!SPLIT) {
+            *reinterpret_cast<uint4*>(ring_q + (size_t)p * T4_A_BYTES) =
+                make_uint4(pack_f16x2(hv[0], hv[1]), pack_f16x2(hv[2], hv[3]), pack_f16x2(hv[4], hv[5]), pack_f16x2(hv[6], hv[7]));
+            *reinterpret_cast<uint4*>(ring_q + (size_t)p * T4_A_BYTES + T4_ROWS * 16) =
+                make_uint4(pack_f16x2(hv[8], hv[9]), pack_f16x2(hv[10], hv[11]), pack_f16x2(hv[12], hv[13]), pack_f16x2(hv[14], hv[15]));
+          } else {
+#pragma unroll
+            for (int kc = 0; kc < 2; ++kc) {
+              uint4 hi, lo;
+              split_f16x2(hv[8 * kc] * HS, hv[8 * kc + 1] * HS, hi.x, lo.x); split_f16x2(hv[8 * kc + 2] * HS, hv[8 * kc + 3] * HS, hi.y, lo.y);
+              split_f16x2(hv[8 * kc + 4] * HS, hv[8 * kc + 5] * HS, hi.z, lo.z); split_f16x2(hv[8 * kc + 6] * HS, hv[8 * kc + 7] * HS, hi.w, lo.w);
+              *reinterpret_cast<uint4*>(ring_q + (size_t)p * A_CHUNK + (size_t)kc * (T4_ROWS * 16)) = hi;
+              *reinterpret_cast<uint4*>(ring_q + (size_t)p * A_CHUNK + (size_t)kc * (T4_ROWS * 16) + T4_A_BYTES / 2) = lo;
+            }
+          }
           // chunk p of this step is written: release it to the loader
           fence_proxy_async_global();
           __syncwarp();
@@ -595,9 +643,9 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
           for (int d = 1; d < 8; ++d) mx = fmaxf(mx, l8[k][d]);
           float pr[8], ssum = 0.f;
 #pragma unroll
-          for (int d = 0; d < 8; ++d) { pr[d] = __expf(l8[k][d] - mx); ssum += pr[d]; }
+          for (int d = 0; d < 8; ++d) { pr[d] = SPLIT ? expf(l8[k][d] - mx) : __expf(l8[k][d] - mx); ssum += pr[d]; }
 #pragma unroll
-          for (int d = 0; d < 8; ++d) pr[d] = __fdividef(pr[d], ssum);
+          for (int d = 0; d < 8; ++d) pr[d] = SPLIT ? pr[d] / ssum : __fdividef(pr[d], ssum);
           int sy;
           if (MODE == MODE_SAMPLE) {
             const float u = (P.uniforms != nullptr)
@@ -619,7 +667,7 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
           float ps = pr[0];
 #pragma unroll
           for (int d = 1; d < 8; ++d) if (d == sy) ps = pr[d];
-          rlogp[k] += (double)__logf(ps);
+          rlogp[k] += SPLIT ? (double)logf(ps) : (double)__logf(ps);
           if (P.sv_cum != nullptr && MODE != MODE_CHILD)
             P.sv_cum[(size_t)t * (size_t)P.sv_rows + (size_t)(row0 + row)] = make_double2(rlogp[k], 0.0);
         }
@@ -667,32 +715,39 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
 }
 
 // ---- weight image: [pass NP][job][k-core][n 192][8 halves], jobs = (neighbour slot 4) x (chunk NP) of 8 k-cores, then the
-// input/bias job of 4 k-cores.  Column n = sub * 48 + blk * 16 + e  <->  block blk (s, g, m) of unit 64 p + 16 sub + e.
+// input/bias job of 4 k-cores; split precision: jobs = (slot, chunk, half) of [hi | lo][k-core 4] (layout comment at the top).
+// Column n = sub * 48 + blk * 16 + e  <->  block blk (s, g, m) of unit 64 p + 16 sub + e.
 // Rows of W / Wg (RydbergKagome_2DGRU/MDGRUcell.py:34-46): 24 input rows (slot * 6 + 2 bit + value), then 4 nh hidden rows.
+template <int UNUSED = 0>
 __global__ void pack_tc4_kernel(const float* __restrict__ W, const float* __restrict__ Wg, const float* __restrict__ Wmerge,
-                                const float* __restrict__ b, const float* __restrict__ bg, int nh, int NP, __half* __restrict__ out) {
-  const long long per_pass = t4_pass_bytes(NP) / 2;
+                                const float* __restrict__ b, const float* __restrict__ bg, int nh, int NP, int split, __half* __restrict__ out) {
+  const int KH = split ? 2 : 1;
+  const long long per_pass = t4_pass_bytes(NP, split != 0) / 2;
   const long long total = (long long)NP * per_pass;
-  const long long hjob = T4_B_BYTES / 2;
+  const long long hjob = T4_B_BYTES / 2;                  // halves per job: [part KH][k-core 8 / KH][n 192][8]
+  const long long hpart = hjob / KH;
+  const long long xpart = T4_XB_BYTES / 2;                // input / bias job: [part KH][k-core 4][n 192][8]
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
     const int p = (int)(idx / per_pass);
     long long r = idx - (long long)p * per_pass;
     const int i = (int)(r % 8);
     float v = 0.f;
-    int blk;
-    if (r < 4LL * NP * hjob) {
+    int blk, part;
+    if (r < 4LL * NP * KH * hjob) {
       const int job = (int)(r / hjob); r -= (long long)job * hjob;
+      part = (int)(r / hpart); r -= (long long)part * hpart;
       const int n = (int)((r / 8) % T4_N), kc = (int)(r / (8 * T4_N));
-      const int slot = job / NP, c = job % NP;
+      const int slot = job / (NP * KH), c = (job / KH) % NP, kh = job % KH;
       const int sub = n / T4_TPS, e = n % 16;
       blk = (n % T4_TPS) / 16;
-      const int j = p * T4_UP + sub * 16 + e, k = c * T4_UP + kc * 8 + i;
+      const int j = p * T4_UP + sub * 16 + e, k = c * T4_UP + kh * 32 + kc * 8 + i;
       if (j < nh && k < nh) {
         if (blk == 2) v = Wmerge[(long long)(slot * nh + k) * nh + j];
         else v = (blk == 0 ? W : Wg)[(long long)(24 + slot * nh + k) * nh + j];
       }
     } else {
-      r -= 4LL * NP * hjob;
+      r -= 4LL * NP * KH * hjob;
+      part = (int)(r / xpart); r -= (long long)part * xpart;
       const int n = (int)((r / 8) % T4_N), kc = (int)(r / (8 * T4_N));     // kc = neighbour slot
       const int sub = n / T4_TPS, e = n % 16;
       blk = (n % T4_TPS) / 16;
@@ -702,7 +757,13 @@ __global__ void pack_tc4_kernel(const float* __restrict__ W, const float* __rest
         else if (i == 6 && kc == 0) v = (blk == 0 ? b : bg)[j];
       }
     }
-    out[idx] = __float2half_rn(v * (blk == 1 ? TC_SCALE_GATE : 1.0f));
+    if (split) {
+      v *= TC_SPLIT_WS;
+      const __half hi = __float2half_rn(v);
+      out[idx] = part == 0 ? hi : __float2half_rn(v - __half2float(hi));
+    } else {
+      out[idx] = __float2half_rn(v * (blk == 1 ? TC_SCALE_GATE : 1.0f));
+    }
   }
 }
 

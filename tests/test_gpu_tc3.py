@@ -120,3 +120,83 @@ def test_tc3_more_tiles_than_sms_and_ragged_batches(cuda):
     with torch.no_grad():
         ref = oracle_run(eng, P, samples=s[-300:].cpu().numpy())
     assert_rel(lp[-300:].cpu().numpy(), ref["logp"].numpy(), TOL, "tc3 tail rows of a 38 000-row batch")
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# four-neighbour GRU of the Rydberg Kagome wavefunction (sweep_tc4.cuh, SPLIT instances): both operands streamed as hi + lo
+# images, six MMAs per K = 32 job
+RYD_HAM = [1.7 ** 6, 3.3, 1.0, 2.001]
+
+
+def _mk4(nx, ny, nh, seed=71):
+    eng = Engine(_lib.CELL_GRU4, nx, ny, num_units=nh, seed=seed, precision="tc3")
+    g = torch.Generator().manual_seed(seed + 1)
+    p = eng.params.cpu()
+    eng.set_weights(p + 0.1 * (torch.rand(p.shape, generator=g) - 0.5))
+    assert "split precision" in eng.describe()
+    return eng
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nx,ny,nh,ns", [(3, 3, 40, 120), (2, 3, 64, 37), (4, 4, 256, 300), (5, 3, 100, 200), (1, 1, 40, 50), (1, 4, 33, 130)])
+def test_tc3_gru4_sample_and_logpsi(cuda, nx, ny, nh, ns):
+    eng = _mk4(nx, ny, nh)
+    u = torch.rand(ns, eng.nsteps, generator=torch.Generator().manual_seed(ns), dtype=torch.float32)
+    s, lp, _ = eng.sample(ns, uniforms=u)
+    P = oracle_params(eng)
+    with torch.no_grad():
+        ref = oracle_run(eng, P, uniforms=u, numsamples=ns)
+    ok = (ref["margin"].min(dim=1).values > 1e-6).numpy()
+    assert ok.mean() > 0.95
+    assert (s.cpu().long().numpy()[ok] == ref["samples"].numpy()[ok]).all()
+    assert_rel(lp.cpu().numpy()[ok], ref["logp"].numpy()[ok], TOL, f"tc3 GRU4 {nx}x{ny}x{nh} log P (sampling)")
+    lp2, _ = eng.logpsi(s)
+    assert torch.equal(lp2, lp)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("reuse", [False, True])
+@pytest.mark.parametrize("nx,ny,nh", [(3, 3, 40), (4, 3, 256)])
+def test_tc3_gru4_rydberg_local_energies(cuda, reuse, nx, ny, nh):
+    eng = _mk4(nx, ny, nh, seed=81)
+    ns = 150
+    saved = eng.new_saved(ns) if reuse else None
+    u = torch.rand(ns, eng.nsteps, generator=torch.Generator().manual_seed(5), dtype=torch.float32)
+    s, lp, ph = eng.sample(ns, uniforms=u, saved=saved)
+    e = eng.local_energies(_lib.HAM_RYDBERG, RYD_HAM, s, lp, ph, saved=saved).cpu().numpy()
+    pos = ole.generate_kagome(nx, ny)
+    nb, dist = ole.neighbouring_atoms(pos, RYD_HAM[3], nx, ny)
+    ref = ole.rydberg_local_energies(RYD_HAM[0], RYD_HAM[1], RYD_HAM[2], nb, dist, s.cpu().numpy().astype(np.int64),
+                                     oracle_logpsi_fn(eng, oracle_params(eng)))
+    assert_rel(e.real, ref, TOL, f"tc3 GRU4 E_loc {nx}x{ny}x{nh} reuse={reuse}")
+
+
+@pytest.mark.gpu
+def test_tc3_gru4_c5_size_and_backward(cuda):
+    """8x8 unit cells, 256 units (the primary C5 size): log P against the oracle at 1e-5, prefix reuse on == off, more tiles
+    than SMs; the gradient (tensor-core backward fed by the split-precision sweep's saved state) against the oracle's autograd."""
+    eng = _mk4(8, 8, 256, seed=111)
+    ns = 40
+    u = torch.rand(ns, eng.nsteps, generator=torch.Generator().manual_seed(8), dtype=torch.float32)
+    saved = eng.new_saved(ns)
+    s, lp, ph = eng.sample(ns, uniforms=u, saved=saved)
+    P = oracle_params(eng)
+    with torch.no_grad():
+        ref2 = oracle_run(eng, P, samples=s.cpu().numpy())
+    assert_rel(lp.cpu().numpy(), ref2["logp"].numpy(), TOL, "tc3 GRU4 8x8x256 log P")
+    e = eng.local_energies(_lib.HAM_RYDBERG, RYD_HAM, s, lp, ph, saved=saved).cpu().numpy().real
+    e2 = eng.local_energies(_lib.HAM_RYDBERG, RYD_HAM, s, lp, ph).cpu().numpy().real
+    assert_rel(e, e2, TOL, "tc3 GRU4 8x8x256 E_loc reuse on vs off")
+    # gradient at a size the oracle differentiates in seconds
+    eng = _mk4(3, 3, 72, seed=91)
+    ns = 200
+    saved = eng.new_saved(ns)
+    s, lp, ph = eng.sample(ns, seed=3, saved=saved)
+    E = torch.randn(ns, generator=torch.Generator().manual_seed(10), dtype=torch.float64)
+    Pg = oracle_params(eng, requires_grad=True)
+    r = oracle_run(eng, Pg, samples=s.cpu().long().numpy())
+    costs.cost_real(r["logp"], E).backward()
+    grad = eng.backward(s, saved, costs.seeds_real(E)).cpu()
+    for n, v in eng.views(grad).items():
+        gr = Pg[n].grad
+        assert float((v.double() - gr).abs().max()) <= 1e-2 * float(gr.abs().max()) + 1e-30, f"gradient of {n} differs"
