@@ -55,7 +55,9 @@ typedef struct {
   int32_t u1;            /* 1: U(1) projection (J1J2/ComplexRNNwavefunction.py:85-93; 2DHeisenberg/MDComplexRNN.py:69-76) */
   int32_t magnetization; /* 2*Sz target of the projection */
   int32_t reserved[8];   /* reserved[0] = precision: 0 FP32 FFMA sweep (1e-5 parity), 1 tcgen05 tensor-core sweep
-                          * (FP16 operands, FP32 accumulate in TMEM; 1e-3 parity bound; tensorized 2D GRU cell) */
+                          * (FP16 operands, FP32 accumulate in TMEM; 1e-3 parity bound), 2 tcgen05 sweep in split
+                          * precision (FP16 hi+lo operand pairs, three MMAs per K step; 1e-5 parity).  1 and 2 exist for
+                          * the 2D cells (vanilla RNN, tensorized, tensorized GRU, four-neighbour GRU) */
 } rnnwf_config;
 
 const char* rnnwf_last_error(void);
