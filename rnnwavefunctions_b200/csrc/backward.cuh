@@ -725,6 +725,18 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
     B.rows = R; B.cfg = cfg; B.gates = gates; B.dlog = dlog_base; B.dh = reinterpret_cast<float4*>(dh);
     B.dpT = reinterpret_cast<float*>(ws + L.off_dpT);
     B.wimg = wimg; B.head_w = m.d_head_w; B.hist = hist;
+    { const char* dbg = std::getenv("RNNWF_TC_DEBUG"); B.debug = dbg ? std::atoi(dbg) : 0; }
+    {
+      // horizontal contributions stay on the SM when the horizontal neighbour is always the previous site of the path and no
+      // site is the vertical neighbour of two sites (every 2D zig-zag lattice)
+      bool chain = true;
+      std::vector<int> hits(m.Q, 0);
+      for (int q = 0; q < m.Q; ++q) {
+        if (m.steps[q].nbr[0] >= 0 && m.steps[q].nbr[0] != q - 1) chain = false;
+        if (m.steps[q].nbr[1] >= 0 && ++hits[m.steps[q].nbr[1]] > 1) chain = false;
+      }
+      B.h_chain = (chain && std::getenv("RNNWF_NO_HCHAIN") == nullptr) ? 1 : 0;
+    }
     const long long tiles = (R + TC_ROWS - 1) / TC_ROWS;
     const BtSmem bs(nhp, m.Tsym, m.Q);
     RNNWF_COUNT_LAUNCH();
@@ -754,6 +766,7 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
       const float* himg = reinterpret_cast<const float*>(sb + sv.off_himg);
       D.jobs = d_jobs; D.cls_steps = d_cls; D.steps = m.d_steps; D.Q = m.Q; D.nh = nh; D.nhp = nhp; D.nsites = m.nsites;
       D.rows = R; D.tiles = tiles; D.cfg = cfg; D.site_of_t = m.d_site_of_t; D.dpT = B.dpT; D.himg = himg;
+      { const char* dbg = std::getenv("RNNWF_TC_DEBUG"); D.debug = dbg ? std::atoi(dbg) : 0; }
       const int nsplit = 16;
       if (van) {
         D.gW = nullptr; D.gWg = nullptr; D.gM0 = Gd("Wh"); D.gM1 = Gd("Wv");

@@ -11,6 +11,11 @@
 // L2 in 7 chunks of 16 units, FP32 accumulator [128 x 208] in TMEM).  The K axis of a chunk is ordered exactly like the
 // forward sweep's accumulator columns (thread-major: sub * 28 + block * 4 + e), the N axis like its operand (tc_kunit),
 // so every thread only ever touches its own columns and its own pieces of d h: no atomics, no barriers on d h.
+// d h of a site has two contributions.  The one of its vertical successor is written to global memory with plain stores
+// (each site is the vertical neighbour of at most one site; sites without one read the zero-initialised buffer).  The one
+// of its horizontal successor is consumed by the same thread at the very next site of the sweep, so it never leaves the
+// SM: 20 of the thread's 28 values wait in the 80 TMEM columns left free by the accumulator and the operand buffers,
+// 8 in registers (h_chain lattices: every 2D zig-zag path; otherwise both contributions are read-modify-write in global).
 //
 // Warp roles: warp 0 MMA issue, warps 1..16 four threads per row (thread (row, sub) owns units 16 p + 4 sub + e),
 // warp 17 weight loader.  Everything is synchronised by mbarriers; waits are bounded and trap instead of hanging.
@@ -57,6 +62,8 @@ struct BwdTcParams {
   const float* wimg;            // [variant 3][chunk np][b_bytes / 4]
   const float* head_w;          // [nh][ND]
   const float* hist;            // vanilla cell: saved hidden states [Q][rows][nhp] (elu' = h > 0 ? 1 : h + 1)
+  int h_chain;                  // 1: every horizontal neighbour is the site generated right before (nbr[0] == q - 1 wherever present)
+  int debug;                    // timing experiments (RNNWF_TC_DEBUG bits 19..21: no MMAs / no feature-major stores / no d h update), 0 in production
 };
 
 // tile-blocked layouts shared with the sampling sweep: everything a thread (row, sub) touches for column pass p is
@@ -312,7 +319,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
           if (leader) {
 #pragma unroll
             for (int ks = 0; ks < BT_NK8; ++ks)
-              tc_mma_tf32_ts(tmem_base, tmem_a + (uint32_t)ks * 8u, bd + (uint64_t)ks * kstep, idesc, (p > 0 || ks > 0) ? 1u : 0u);
+              if (!(P.debug & (1 << 19))) tc_mma_tf32_ts(tmem_base, tmem_a + (uint32_t)ks * 8u, bd + (uint64_t)ks * kstep, idesc, (p > 0 || ks > 0) ? 1u : 0u);
             tc_commit(bar_free + s);
             if (p == NCH - 1) tc_commit(bar_D);
           }
@@ -352,10 +359,28 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
     const uint32_t kcol = (uint32_t)tc_koff(nhp, sub);              // its first column inside a neighbour half of D
     const uint32_t a_thr = tmem_A0 + lane_base + (uint32_t)(sub * TC_TPS);   // its 28 columns of operand buffer 0
     const float* const hW = headW + sub * 16;
+    // the horizontal successor's contribution to d h of the next site: columns [432 + 20 sub, + 20) of this row's lane, and hreg
+    const uint32_t stash_thr = tmem_A0 + lane_base + 2u * (uint32_t)BT_K + (uint32_t)(sub * 20);
+    float hreg[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) hreg[i] = 0.f;
+    bool have_h = false;                                            // warp-uniform: the site being processed has a stashed contribution
+    auto h_piece = [&](int p, float (&hc)[4]) {                     // the stash's values of column pass p (units 16 p + 4 sub + e)
+      hc[0] = hc[1] = hc[2] = hc[3] = 0.f;
+      if (!have_h) return;
+      if (p < 5) {
+        uint32_t t[4];
+        tc_ld4(stash_thr + (uint32_t)(4 * p), t);
+        tc_wait_ld();
+        hc[0] = __uint_as_float(t[0]); hc[1] = __uint_as_float(t[1]); hc[2] = __uint_as_float(t[2]); hc[3] = __uint_as_float(t[3]);
+      } else if (p == 5) { hc[0] = hreg[0]; hc[1] = hreg[1]; hc[2] = hreg[2]; hc[3] = hreg[3]; }
+      else { hc[0] = hreg[4]; hc[1] = hreg[5]; hc[2] = hreg[6]; hc[3] = hreg[7]; }
+    };
     uint32_t phF = 0, c = 0, nsite = 0;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const long long row0 = tile * TC_ROWS;
       const bool live = row0 + row < P.rows;
+      have_h = false;
       // ---- symbol table of the tile
       {
         const int8_t* cf = P.cfg + (row0 + row) * P.nsites;
@@ -389,6 +414,8 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
             if (blk < np_own) {                                       // warp-uniform
               float dp[4] = {0.f, 0.f, 0.f, 0.f};
               const int j0 = blk * TC_JP + sub * 4;
+              float hc[4];
+              h_piece(blk, hc);
               if (live) {
                 const float4 dh4 = __ldcg(dhq + (size_t)blk * TC_ROWS);
                 const float4 h4 = __ldg(reinterpret_cast<const float4*>(hq + blk * TC_JP));
@@ -396,7 +423,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                   const float4 w = *reinterpret_cast<const float4*>(hW + blk * (TC_JP * 4) + e * 4);
-                  const float g = dhv[e] + dl[0] * w.x + dl[1] * w.y + dl[2] * w.z + dl[3] * w.w;
+                  const float g = dhv[e] + hc[e] + dl[0] * w.x + dl[1] * w.y + dl[2] * w.z + dl[3] * w.w;
                   dp[e] = (j0 + e < nh) ? g * (hv[e] > 0.f ? 1.f : hv[e] + 1.f) : 0.f;
                   d[blk * 4 + e] = __float_as_uint(dp[e]);
                 }
@@ -430,6 +457,8 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
             if (p < np_own) {
               float ds[4] = {0.f, 0.f, 0.f, 0.f}, dg[4] = {0.f, 0.f, 0.f, 0.f}, dm[4] = {0.f, 0.f, 0.f, 0.f};
               const int j0 = p * TC_JP + sub * 4;
+              float hc[4];
+              h_piece(p, hc);
               if (live) {
                 const float4 dh4 = n_dh, u4 = n_u, t4 = n_t, m4 = n_m;      // loaded one pass ahead
                 if (p + 1 < np_own) {
@@ -443,7 +472,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
   #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                   const float4 w = *reinterpret_cast<const float4*>(hW + p * (TC_JP * 4) + e * 4);
-                  const float g = dhv[e] + dl[0] * w.x + dl[1] * w.y + dl[2] * w.z + dl[3] * w.w;   // heads' contribution
+                  const float g = dhv[e] + hc[e] + dl[0] * w.x + dl[1] * w.y + dl[2] * w.z + dl[3] * w.w;   // + heads' contribution
                   const bool real = (j0 + e < nh);                     // padding units carry nothing (their saved gates are unset)
                   ds[e] = real ? g * uv[e] * (1.f - tv[e] * tv[e]) : 0.f;
                   dg[e] = real ? g * (tv[e] - mv[e]) * uv[e] * (1.f - uv[e]) : 0.f;
@@ -458,7 +487,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
               const size_t sstride = (size_t)P.Q * (size_t)ntiles * nhp * TC_ROWS;
   #pragma unroll
               for (int e = 0; e < 4; ++e) {
-                if (j0 + e < nhp) { o0[(size_t)e * TC_ROWS] = ds[e]; o0[sstride + (size_t)e * TC_ROWS] = dg[e]; o0[2 * sstride + (size_t)e * TC_ROWS] = dm[e]; }
+                if (j0 + e < nhp && !(P.debug & (1 << 20))) { o0[(size_t)e * TC_ROWS] = ds[e]; o0[sstride + (size_t)e * TC_ROWS] = dg[e]; o0[2 * sstride + (size_t)e * TC_ROWS] = dm[e]; }
               }
             }
             if (has_in) {
@@ -479,6 +508,35 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
           ++nsite;
           __syncwarp();
           tc_fence_after();
+          if (P.h_chain) {
+            if (nb1 >= 0) {                                          // vertical neighbour: the only contribution it gets through memory
+              uint32_t d[TC_TPS];
+              tc_ld28(tmem_base + lane_base + (uint32_t)nhp + kcol, d);
+              tc_wait_ld();
+              if (live && !(P.debug & (1 << 21))) {
+                float4* dst = P.dh + tc_dh_index(nb1, tile, ntiles, NP, sub, 0, row);
+#pragma unroll
+                for (int p = 0; p < TC_TPS / 4; ++p)
+                  if (p < np_own)
+                    __stcg(dst + (size_t)p * TC_ROWS, make_float4(__uint_as_float(d[4 * p]), __uint_as_float(d[4 * p + 1]),
+                                                                 __uint_as_float(d[4 * p + 2]), __uint_as_float(d[4 * p + 3])));
+              }
+            }
+            if (nb0 >= 0) {                                          // horizontal neighbour == the next site of this sweep: stays on the SM
+              uint32_t d[TC_TPS];
+              tc_ld28(tmem_base + lane_base + kcol, d);
+              tc_wait_ld();
+              uint32_t lo[16];
+#pragma unroll
+              for (int i = 0; i < 16; ++i) lo[i] = d[i];
+              tc_st16(stash_thr, lo);
+              tc_st4(stash_thr + 16u, make_uint4(d[16], d[17], d[18], d[19]));
+#pragma unroll
+              for (int i = 0; i < 8; ++i) hreg[i] = __uint_as_float(d[20 + i]);
+              tc_wait_st();
+            }
+            have_h = nb0 >= 0;
+          } else
 #pragma unroll
           for (int half = 0; half < 2; ++half) {
             const int nb = half ? nb1 : nb0;                         // warp-uniform
@@ -486,7 +544,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
             uint32_t d[TC_TPS];
             tc_ld28(tmem_base + lane_base + (uint32_t)half * (uint32_t)nhp + kcol, d);
             tc_wait_ld();
-            if (live) {
+            if (live && !(P.debug & (1 << 21))) {
               float4* dst = P.dh + tc_dh_index(nb, tile, ntiles, NP, sub, 0, row);
 #pragma unroll
               for (int p = 0; p < TC_TPS / 4; ++p) {

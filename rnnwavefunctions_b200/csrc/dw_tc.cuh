@@ -18,11 +18,16 @@
 
 namespace rnnwf {
 
-constexpr int DW_THREADS = 32 + 128 + 32;   // warp 0: MMA, warps 1..4: operand writers (lane <-> unit), warp 5: loader
+// The operand writers are a latency chain per chunk (loads -> masks -> three tcgen05.st -> wait -> arrive, ~1600 cycles against
+// ~340 cycles of MMAs), so DW_GROUPS groups of four warps take the chunks round-robin (chunk c -> group c % DW_GROUPS,
+// buffer c % DW_ABUF): three chains in flight per SM.
+constexpr int DW_GROUPS = 3;
+constexpr int DW_THREADS = 32 + 128 * DW_GROUPS + 32;   // warp 0: MMA, then DW_GROUPS x 4 operand-writer warps (lane <-> unit), last warp: loader
 constexpr int DW_KC = 16;                   // rows per operand chunk
 constexpr int DW_CHUNKS = TC_ROWS / DW_KC;  // 8 chunks per item
 constexpr int DW_ABUF = 3;                  // operand chunk buffers in TMEM
-constexpr int DW_PF = 4;                    // operand chunks loaded ahead (registers)
+static_assert(DW_GROUPS == DW_ABUF, "each writer group owns one operand buffer (it follows every phase of that buffer's barrier)");
+constexpr int DW_PF = 3;                    // operand chunks loaded ahead per group (registers)
 
 // hidden-state tile image of one (site, 128-row tile): B operand [unit n][row k], K-major core matrices
 //   float index = ((k / 4) * ncores + n / 8) * 32 + (n % 8) * 4 + (k % 4),     ncores = ceil(nhp / 16) * 2
@@ -57,6 +62,7 @@ struct DwParams {
   float* gW; float* gWg;
   float* gM0; float* gM1;   // unmasked source (src 2): [unit i][unit j] targets of the horizontal / vertical half
   int slab[3];              // which feature-major slab of dpT holds source 0, 1, 2
+  int debug;                // timing experiments (RNNWF_TC_DEBUG bits 16..18: no MMAs / no operand loads / no masked copies), 0 in production
 };
 
 __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) {
@@ -98,19 +104,19 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
       const uint32_t LBO = (uint32_t)ncores * 128u, SBO = 128u;
       const uint64_t bdesc0 = tc_desc(smem_u32(Bst), LBO, SBO);
       const uint32_t idesc = tc_idesc_tf32(TC_ROWS, N);
-      uint32_t phA = 0, phB = 0, c = 0;
+      uint32_t phB = 0, c = 0;
       for (int it = 0; it < job.count; ++it) {
         const uint32_t st = (uint32_t)it & 1u;
         mbar_wait(bar_B + st, (phB >> st) & 1u); phB ^= 1u << st;
         for (int kc = 0; kc < DW_CHUNKS; ++kc, ++c) {
           const uint32_t s = c % DW_ABUF;
-          mbar_wait(bar_A + s, (phA >> s) & 1u); phA ^= 1u << s;
+          mbar_wait(bar_A + s, (c / DW_ABUF) & 1u);
           tc_fence_after();
           if (leader) {
             const uint32_t a0 = tmem_A0 + s * 48u;
             // rows 16 kc .. + 15 of the tile = k-cores 4 kc .. + 3 of the image
             const uint64_t bd = bdesc0 + (uint64_t)((st * img_bytes + (uint32_t)(kc * 4) * LBO) >> 4);
-            for (int b = 0; b < nacc; ++b) {
+            for (int b = 0; b < ((P.debug & (1 << 16)) ? 0 : nacc); ++b) {
 #pragma unroll
               for (int ks = 0; ks < 2; ++ks)
                 tc_mma_tf32_ts(tmem_base + (uint32_t)(b * N), a0 + (uint32_t)(b * 16 + ks * 8), bd + (uint64_t)((ks * 2u * LBO) >> 4), idesc,
@@ -141,95 +147,105 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
         __syncwarp();
       }
     } else {
-      // ======================= operand writers: lane <-> unit =======================
-      const int quarter = warp & 3;
+      // ======================= operand writers: lane <-> unit, DW_GROUPS groups of four warps =======================
+      const int quarter = warp & 3;                                // TMEM lane quarter this warp may access
+      const int grp = (warp - 1) >> 2;
       const int unit = (quarter << 5) + lane;                      // TMEM lane == M index == unit j
       const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
       const bool real = unit < P.nh;
-      uint32_t phF = 0, c = 0;
-      float4 pf[DW_PF][4];
-      for (int it = 0; it < job.count; ++it) {
+      const uint32_t total = (uint32_t)job.count * DW_CHUNKS;      // chunks of this job; chunk c = item (c / 8), rows 16 (c % 8) ..
+      const size_t slab_base = (size_t)P.slab[job.src] * P.Q;
+      auto item_src = [&](int it) -> const float* {
         const int item = job.begin + it;
         const int q = steps_of_cls[item / (int)P.tiles];
         const long long tile = item % (int)P.tiles;
-        // row masks of the item: bit k of word w <-> row 32 w + k has its horizontal / vertical neighbour spin up
-        if (masks) {
-          const StepMeta* sm = P.steps + q;
-          const long long r = tile * TC_ROWS + (warp - 1) * 32 + lane;
-          int sl = 0, su = 0;
-          if (r < P.rows) {
-            const int8_t* cf = P.cfg + r * P.nsites;
-            if (sm->nbr[0] >= 0) sl = cf[P.site_of_t[sm->nbr[0]]] & 1;
-            if (sm->nbr[1] >= 0) su = cf[P.site_of_t[sm->nbr[1]]] & 1;
-          }
-          const uint32_t bl = __ballot_sync(0xffffffffu, sl), bu = __ballot_sync(0xffffffffu, su);
-          if (lane == 0) { maskS[((it & 1) * 2 + 0) * 4 + (warp - 1)] = bl; maskS[((it & 1) * 2 + 1) * 4 + (warp - 1)] = bu; }
-          asm volatile("bar.sync 1, 128;" ::: "memory");           // the four writer warps
+        return P.dpT + (((slab_base + q) * (size_t)P.tiles + (size_t)tile) * P.nhp + (real ? unit : 0)) * TC_ROWS;
+      };
+      // DW_PF chunks of this group are in flight in registers, across item boundaries
+      float4 pf[DW_PF][4];
+      int pf_it = -1;
+      const float* pf_src = nullptr;
+      auto fetch = [&](uint32_t c, float4 (&dst)[4]) {
+        if (c < total) {
+          const int it = (int)(c / DW_CHUNKS);
+          if (it != pf_it) { pf_it = it; pf_src = item_src(it); }
+          const float4* s4 = reinterpret_cast<const float4*>(pf_src) + (c % DW_CHUNKS) * 4;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) dst[i] = (real && !(P.debug & (1 << 17))) ? __ldg(s4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        // operand rows of this unit: DW_PF chunks (16 rows each) are in flight in registers, across item boundaries
-        if (it == 0) {
-          const float* src = P.dpT + ((((size_t)P.slab[job.src] * P.Q + q) * (size_t)P.tiles + (size_t)tile) * P.nhp + (real ? unit : 0)) * TC_ROWS;
+      };
 #pragma unroll
-          for (int k = 0; k < DW_PF; ++k)
+      for (int k = 0; k < DW_PF; ++k) fetch((uint32_t)(grp + k * DW_GROUPS), pf[k]);
+      int cur_it = -1;
+      for (uint32_t cbase = (uint32_t)grp; cbase < total; cbase += DW_PF * DW_GROUPS) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) pf[k][i] = real ? __ldg(reinterpret_cast<const float4*>(src) + k * 4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-        // source of the chunks that will be loaded while this item is processed: its own second half, then the next item
-        const float* src_cur = P.dpT + ((((size_t)P.slab[job.src] * P.Q + q) * (size_t)P.tiles + (size_t)tile) * P.nhp + (real ? unit : 0)) * TC_ROWS;
-        const float* src_nxt = src_cur;
-        if (it + 1 < job.count) {
-          const int item2 = item + 1;
-          const int q2 = steps_of_cls[item2 / (int)P.tiles];
-          const long long tile2 = item2 % (int)P.tiles;
-          src_nxt = P.dpT + ((((size_t)P.slab[job.src] * P.Q + q2) * (size_t)P.tiles + (size_t)tile2) * P.nhp + (real ? unit : 0)) * TC_ROWS;
-        }
-#pragma unroll
-        for (int kc = 0; kc < DW_CHUNKS; ++kc, ++c) {
-          float v[16];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const float4 t = pf[kc % DW_PF][i];
-            v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
-          }
-          {
-            const int kn = kc + DW_PF;                               // chunk to fetch into the slot just freed
-            const bool more = (kn < DW_CHUNKS) || (it + 1 < job.count);
-            const float4* s4 = reinterpret_cast<const float4*>(kn < DW_CHUNKS ? src_cur : src_nxt) + (kn % DW_CHUNKS) * 4;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) pf[kc % DW_PF][i] = (real && more) ? __ldg(s4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-          }
-          const uint32_t s = c % DW_ABUF;
-          if (c >= DW_ABUF) { mbar_wait(bar_Afree + s, (phF >> s) & 1u); phF ^= 1u << s; }
-          const uint32_t a0 = tmem_A0 + lane_base + s * 48u;
-          uint32_t w[16];
-#pragma unroll
-          for (int i = 0; i < 16; ++i) w[i] = __float_as_uint(v[i]);
-          __syncwarp();
-          tc_st16(a0, w);
+       for (int k = 0; k < DW_PF; ++k) {                           // (static register slot k of the prefetch ring)
+        const uint32_t c = cbase + (uint32_t)(k * DW_GROUPS);
+        if (c >= total) break;
+        const int it = (int)(c / DW_CHUNKS), kc = (int)(c % DW_CHUNKS);
+        while (cur_it < it) {
+          // row masks of the next item: bit k of word w <-> row 32 w + k has its horizontal / vertical neighbour spin up.
+          // Every group passes every item (8 chunks over DW_GROUPS <= 4 groups); group 0 computes, all writers meet.
+          ++cur_it;
           if (masks) {
-            const uint32_t ml = (maskS[((it & 1) * 2 + 0) * 4 + (kc >> 1)] >> ((kc & 1) * 16)) & 0xffffu;
-            const uint32_t mu = (maskS[((it & 1) * 2 + 1) * 4 + (kc >> 1)] >> ((kc & 1) * 16)) & 0xffffu;
-#pragma unroll
-            for (int i = 0; i < 16; ++i) w[i] = ((ml >> i) & 1u) ? __float_as_uint(v[i]) : 0u;
-            tc_st16(a0 + 16u, w);
-#pragma unroll
-            for (int i = 0; i < 16; ++i) w[i] = ((mu >> i) & 1u) ? __float_as_uint(v[i]) : 0u;
-            tc_st16(a0 + 32u, w);
+            if (grp == 0) {
+              const int item = job.begin + cur_it;
+              const int q = steps_of_cls[item / (int)P.tiles];
+              const long long tile = item % (int)P.tiles;
+              const StepMeta* sm = P.steps + q;
+              const long long r = tile * TC_ROWS + quarter * 32 + lane;
+              int sl = 0, su = 0;
+              if (r < P.rows) {
+                const int8_t* cf = P.cfg + r * P.nsites;
+                if (sm->nbr[0] >= 0) sl = cf[P.site_of_t[sm->nbr[0]]] & 1;
+                if (sm->nbr[1] >= 0) su = cf[P.site_of_t[sm->nbr[1]]] & 1;
+              }
+              const uint32_t bl = __ballot_sync(0xffffffffu, sl), bu = __ballot_sync(0xffffffffu, su);
+              if (lane == 0) { maskS[((cur_it & 1) * 2 + 0) * 4 + quarter] = bl; maskS[((cur_it & 1) * 2 + 1) * 4 + quarter] = bu; }
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(128 * DW_GROUPS) : "memory");     // all writer warps
           }
-          tc_wait_st();
-          tc_fence_before();
-          mbar_arrive(bar_A + s);
         }
+        float v[16];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { v[4 * i] = pf[k][i].x; v[4 * i + 1] = pf[k][i].y; v[4 * i + 2] = pf[k][i].z; v[4 * i + 3] = pf[k][i].w; }
+        fetch(c + (uint32_t)(DW_PF * DW_GROUPS), pf[k]);           // refill the slot just freed
+        const uint32_t s = c % DW_ABUF, use = c / DW_ABUF;         // buffer s is used for the (use)-th time
+        if (use > 0) mbar_wait(bar_Afree + s, (use - 1u) & 1u);
+        const uint32_t a0 = tmem_A0 + lane_base + s * 48u;
+        uint32_t w[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) w[i] = __float_as_uint(v[i]);
+        __syncwarp();
+        tc_st16(a0, w);
+        if (masks && !(P.debug & (1 << 18))) {
+          const uint32_t ml = (maskS[((it & 1) * 2 + 0) * 4 + (kc >> 1)] >> ((kc & 1) * 16)) & 0xffffu;
+          const uint32_t mu = (maskS[((it & 1) * 2 + 1) * 4 + (kc >> 1)] >> ((kc & 1) * 16)) & 0xffffu;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) w[i] = ((ml >> i) & 1u) ? __float_as_uint(v[i]) : 0u;
+          tc_st16(a0 + 16u, w);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) w[i] = ((mu >> i) & 1u) ? __float_as_uint(v[i]) : 0u;
+          tc_st16(a0 + 32u, w);
+        }
+        tc_wait_st();
+        tc_fence_before();
+        mbar_arrive(bar_A + s);
+       }
       }
-      // ---- flush: wait for the last MMAs, then add this unit's accumulator rows to the gradient
+      // ---- flush: wait for the last MMAs, then add this unit's accumulator rows to the gradient (column blocks shared
+      //      between the groups)
       {
-        // commits complete in order: the last chunk's completion on its buffer is the phase this thread would wait for next
-        const uint32_t last = (c - 1) % DW_ABUF;
-        mbar_wait(bar_Afree + last, (phF >> last) & 1u);
+        // commits complete in order: the completion of the last chunk's commit covers every MMA of the job
+        // (a group that does not own the last chunk's buffer has not followed its phases: the phase before last may still
+        //  be open, the one before that is closed by the group's own last wait -- follow the last two in order)
+        const uint32_t lastc = total - 1u, lastuse = lastc / DW_ABUF;
+        if (lastuse > 0) mbar_wait(bar_Afree + (lastc % DW_ABUF), (lastuse - 1u) & 1u);
+        mbar_wait(bar_Afree + (lastc % DW_ABUF), lastuse & 1u);
         tc_fence_after();
         const bool has_h = job.cls != 2, has_u = job.cls != 1;
         const int nh = P.nh;
-        for (int n0 = 0; n0 < N; n0 += 16) {
+        for (int n0 = 16 * grp; n0 < N; n0 += 16 * DW_GROUPS) {
           uint32_t S[16], Cl[16], Cu[16];
           __syncwarp();
           tc_ld16(tmem_base + lane_base + (uint32_t)n0, S);
