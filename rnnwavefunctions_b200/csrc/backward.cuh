@@ -430,7 +430,7 @@ __global__ void build_onehot_kernel(const BwdStep S, int nslots, float* __restri
 inline cudaError_t backward_init() {
   return cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GT_STAGES * 2 * GT_TILE_BYTES);
 }
-inline int dw_smem_bytes(int nhp) { return 2 * tc_himg_floats(nhp) * 4 + 256; }
+inline int dw_smem_bytes(int nhp) { return 2 * tc_himg_floats(nhp) * 4 + 2 * nhp * DW_APITCH * 4 + 256; }
 inline cudaError_t backward_init_tc(const rnnwf_model_impl& m) {
   cudaError_t e = cudaFuncSetAttribute(bwd_tc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, BtSmem(m.nhp, m.Tsym, m.Q).total);
   if (e != cudaSuccess) return e;

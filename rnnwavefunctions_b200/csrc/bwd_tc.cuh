@@ -32,6 +32,9 @@ namespace rnnwf {
 constexpr int BT_K = TC_TPS * TC_SUB;                 // 112 K elements per chunk (16 units x 7 blocks)
 constexpr int BT_THREADS = 32 + TC_EPI_THREADS + 32;  // warp 0: MMA, warps 1..16: rows, warp 17: loader
 constexpr int BT_NK8 = BT_K / 8;                      // tf32 MMAs (K = 8) per chunk
+// feature-major (ds | dg | dm) tiles [site][tile][unit nhp][TC_DPT_PITCH]: 128 rows + 4 floats of padding per unit row, so that
+// the weight-gradient kernel stages a tile with ONE bulk copy and reads it conflict-free at lane <-> unit (dw_tc.cuh)
+constexpr int TC_DPT_PITCH = TC_ROWS + 4;
 
 struct BtSmem {
   int off_B, off_headw, off_step, off_sym, off_bar, off_tmem, total;
@@ -172,7 +175,7 @@ __global__ void __launch_bounds__(128) vanilla_input_grads_kernel(const float* _
   for (long long it = blockIdx.y; it < nitems; it += gridDim.y) {
     const int q = (int)(it / tiles);
     const long long row = (it % tiles) * TC_ROWS + r;
-    const float v = dpT[((size_t)it * nhp + j) * TC_ROWS + r];
+    const float v = dpT[((size_t)it * nhp + j) * TC_DPT_PITCH + r];
     if (row >= rows) continue;
     const int n0 = steps[q].nbr[0], n1 = steps[q].nbr[1];
     const int8_t* cf = cfg + row * nsites;
@@ -428,10 +431,10 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
                   d[blk * 4 + e] = __float_as_uint(dp[e]);
                 }
               }
-              float* o0 = P.dpT + (((size_t)q * (size_t)ntiles + (size_t)tile) * nhp + j0) * TC_ROWS + row;
+              float* o0 = P.dpT + (((size_t)q * (size_t)ntiles + (size_t)tile) * nhp + j0) * TC_DPT_PITCH + row;
 #pragma unroll
               for (int e = 0; e < 4; ++e)
-                if (j0 + e < nhp) o0[(size_t)e * TC_ROWS] = dp[e];
+                if (j0 + e < nhp) o0[(size_t)e * TC_DPT_PITCH] = dp[e];
             }
           }
           if (has_in) {
@@ -483,11 +486,11 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
                 }
               }
               // feature-major tiles for the weight-gradient kernel (zeros for rows past the end of the batch)
-              float* o0 = P.dpT + (((size_t)q * (size_t)ntiles + (size_t)tile) * nhp + j0) * TC_ROWS + row;
-              const size_t sstride = (size_t)P.Q * (size_t)ntiles * nhp * TC_ROWS;
+              float* o0 = P.dpT + (((size_t)q * (size_t)ntiles + (size_t)tile) * nhp + j0) * TC_DPT_PITCH + row;
+              const size_t sstride = (size_t)P.Q * (size_t)ntiles * nhp * TC_DPT_PITCH;
   #pragma unroll
               for (int e = 0; e < 4; ++e) {
-                if (j0 + e < nhp && !(P.debug & (1 << 20))) { o0[(size_t)e * TC_ROWS] = ds[e]; o0[sstride + (size_t)e * TC_ROWS] = dg[e]; o0[2 * sstride + (size_t)e * TC_ROWS] = dm[e]; }
+                if (j0 + e < nhp && !(P.debug & (1 << 20))) { o0[(size_t)e * TC_DPT_PITCH] = ds[e]; o0[sstride + (size_t)e * TC_DPT_PITCH] = dg[e]; o0[2 * sstride + (size_t)e * TC_DPT_PITCH] = dm[e]; }
               }
             }
             if (has_in) {

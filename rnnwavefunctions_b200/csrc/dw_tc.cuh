@@ -5,9 +5,11 @@
 // The one-hot factors are {0,1} masks over the rows, so for each source s in {ds, dg, dm} and each neighbour half the
 // kernel accumulates three [128 x 112] FP32 tiles in TMEM over all (site, 128-row tile) items it is given:
 //        S = s^T h,    Cl = (sl . s)^T h,    Cu = (su . s)^T h              (contraction over the rows)
-// with tcgen05.mma kind::tf32: the A operand (units x rows) is written into TMEM by the threads that load the
-// feature-major (ds, dg, dm) tiles of the reverse sweep and apply the row masks in registers; the B operand is the
-// hidden-state tile image the sampling sweep saved in UMMA core-matrix order, fetched with one bulk copy per item.
+// with tcgen05.mma kind::tf32: the A operand (units x rows) is written into TMEM by threads (lane <-> unit) that read the
+// feature-major (ds, dg, dm) tile of the reverse sweep from shared memory -- the loader warp stages it there with one
+// bulk copy (the reverse sweep writes the tiles with unit rows padded to 528 bytes), two tiles deep -- and apply the row
+// masks in registers; the B
+// operand is the hidden-state tile image the sampling sweep saved in UMMA core-matrix order, one bulk copy per item.
 // Items of one CTA all belong to one neighbour class (both / horizontal only / vertical only), so at the end
 //        dW[..,0] += S - Cl, dW[..,1] += Cl   (horizontal neighbour present),   dW[..,2] += S - Cu, dW[..,3] += Cu   (vertical)
 // go to the gradient with atomicAdd.  Replaces the expanded operand h (x) x (3.2 GB at the benchmark size) and three
@@ -27,7 +29,7 @@ constexpr int DW_KC = 16;                   // rows per operand chunk
 constexpr int DW_CHUNKS = TC_ROWS / DW_KC;  // 8 chunks per item
 constexpr int DW_ABUF = 3;                  // operand chunk buffers in TMEM
 static_assert(DW_GROUPS == DW_ABUF, "each writer group owns one operand buffer (it follows every phase of that buffer's barrier)");
-constexpr int DW_PF = 3;                    // operand chunks loaded ahead per group (registers)
+constexpr int DW_APITCH = TC_DPT_PITCH;     // floats per unit row of the staged (ds | dg | dm) tile: 528 B, conflict-free 16-byte reads at lane <-> unit
 
 // hidden-state tile image of one (site, 128-row tile): B operand [unit n][row k], K-major core matrices
 //   float index = ((k / 4) * ncores + n / 8) * 32 + (n % 8) * 4 + (k % 4),     ncores = ceil(nhp / 16) * 2
@@ -36,9 +38,9 @@ __host__ __device__ inline int tc_himg_floats(int nhp) { return (TC_ROWS / 4) * 
 __host__ __device__ inline long long tc_himg_bytes(int Q, long long rows, int nhp) {
   return (long long)Q * ((rows + TC_ROWS - 1) / TC_ROWS) * tc_himg_floats(nhp) * 4;
 }
-// feature-major tiles of the reverse sweep: [src 3][site][tile][unit nhp][row 128]
+// feature-major tiles of the reverse sweep: [src 3][site][tile][unit nhp][TC_DPT_PITCH (128 rows + padding)]
 __host__ __device__ inline long long tc_dpt_bytes(int Q, long long rows, int nhp) {
-  return 3LL * Q * ((rows + TC_ROWS - 1) / TC_ROWS) * nhp * TC_ROWS * 4;
+  return 3LL * Q * ((rows + TC_ROWS - 1) / TC_ROWS) * nhp * TC_DPT_PITCH * 4;
 }
 
 struct DwJob {            // one CTA's share: a contiguous range of items of one (source, half, class)
@@ -70,9 +72,14 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
   const int ncores = tc_himg_ncores(P.nhp);
   const uint32_t img_bytes = (uint32_t)tc_himg_floats(P.nhp) * 4u;
   unsigned char* const Bst = dw_smem;                                       // [2][img_bytes]
-  uint64_t* const bars = reinterpret_cast<uint64_t*>(dw_smem + 2 * img_bytes);
-  uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(dw_smem + 2 * img_bytes + 96);
-  uint32_t* const maskS = reinterpret_cast<uint32_t*>(dw_smem + 2 * img_bytes + 128);   // [2 items][2 masks][4 words]
+  const uint32_t at_bytes = (uint32_t)P.nhp * DW_APITCH * 4u;
+  float* const Ast = reinterpret_cast<float*>(dw_smem + 2 * img_bytes);     // [2][nhp][DW_APITCH] staged (ds | dg | dm) tiles
+  unsigned char* const ctl = dw_smem + 2 * img_bytes + 2 * at_bytes;
+  uint64_t* const bars = reinterpret_cast<uint64_t*>(ctl);
+  uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(ctl + 120);
+  uint32_t* const maskS = reinterpret_cast<uint32_t*>(ctl + 128);           // [2 items][2 masks][4 words]
+  uint64_t* const bar_At = bars + 10;     // [2] staged tile landed (complete_tx)
+  uint64_t* const bar_Atfree = bars + 12; // [2] staged tile read by every writer thread
   uint64_t* const bar_A = bars + 0;       // [DW_ABUF] operand chunk written (128 arrivals)
   uint64_t* const bar_Afree = bars + 3;   // [DW_ABUF] operand chunk consumed (commit)
   uint64_t* const bar_B = bars + 6;       // [2] hidden-state tile landed (complete_tx)
@@ -86,7 +93,7 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
   // TMEM map: accumulators [0, 3 N); operand chunks at 3 N: [DW_ABUF buffers][3 blocks][16 columns]
   if (tid == 0) {
     for (int i = 0; i < DW_ABUF; ++i) { mbar_init(bar_A + i, 128); mbar_init(bar_Afree + i, 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(bar_B + i, 1); mbar_init(bar_Bfree + i, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_B + i, 1); mbar_init(bar_Bfree + i, 1); mbar_init(bar_At + i, 1); mbar_init(bar_Atfree + i, 128 * DW_GROUPS); }
     fence_mbar_init();
   }
   if (warp == 0) tc_alloc(tmem_slot, TC_TMEM_COLS);
@@ -129,7 +136,7 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
         }
       }
     } else if (warp == DW_THREADS / 32 - 1) {
-      // ======================= loader warp: one bulk copy per item =======================
+      // ======================= loader warp: per item one bulk copy of the hidden-state image, one per unit row of the tile =====
       const bool leader = elect_one();
       uint32_t phF = 0;
       for (int it = 0; it < job.count; ++it) {
@@ -138,11 +145,18 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
         const int q = steps_of_cls[item / (int)P.tiles];
         const long long tile = item % (int)P.tiles;
         const int nb = P.steps[q].nbr[job.half];
-        if (it >= 2) { mbar_wait_relaxed(bar_Bfree + st, (phF >> st) & 1u); phF ^= 1u << st; }
+        if (it >= 2) {
+          mbar_wait_relaxed(bar_Bfree + st, (phF >> st) & 1u);
+          mbar_wait_relaxed(bar_Atfree + st, (phF >> st) & 1u);
+          phF ^= 1u << st;
+        }
         if (leader) {
           const unsigned char* src = reinterpret_cast<const unsigned char*>(P.himg) + ((size_t)nb * (size_t)P.tiles + (size_t)tile) * img_bytes;
           mbar_expect_tx(bar_B + st, img_bytes);
           bulk_g2s(Bst + (size_t)st * img_bytes, src, img_bytes, bar_B + st);
+          const float* tsrc = P.dpT + (((size_t)P.slab[job.src] * P.Q + q) * (size_t)P.tiles + (size_t)tile) * P.nhp * DW_APITCH;
+          mbar_expect_tx(bar_At + st, (P.debug & (1 << 17)) ? 0u : at_bytes);
+          if (!(P.debug & (1 << 17))) bulk_g2s(Ast + (size_t)st * P.nhp * DW_APITCH, tsrc, at_bytes, bar_At + st);
         }
         __syncwarp();
       }
@@ -154,36 +168,11 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
       const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
       const bool real = unit < P.nh;
       const uint32_t total = (uint32_t)job.count * DW_CHUNKS;      // chunks of this job; chunk c = item (c / 8), rows 16 (c % 8) ..
-      const size_t slab_base = (size_t)P.slab[job.src] * P.Q;
-      auto item_src = [&](int it) -> const float* {
-        const int item = job.begin + it;
-        const int q = steps_of_cls[item / (int)P.tiles];
-        const long long tile = item % (int)P.tiles;
-        return P.dpT + (((slab_base + q) * (size_t)P.tiles + (size_t)tile) * P.nhp + (real ? unit : 0)) * TC_ROWS;
-      };
-      // DW_PF chunks of this group are in flight in registers, across item boundaries
-      float4 pf[DW_PF][4];
-      int pf_it = -1;
-      const float* pf_src = nullptr;
-      auto fetch = [&](uint32_t c, float4 (&dst)[4]) {
-        if (c < total) {
-          const int it = (int)(c / DW_CHUNKS);
-          if (it != pf_it) { pf_it = it; pf_src = item_src(it); }
-          const float4* s4 = reinterpret_cast<const float4*>(pf_src) + (c % DW_CHUNKS) * 4;
-#pragma unroll
-          for (int i = 0; i < 4; ++i) dst[i] = (real && !(P.debug & (1 << 17))) ? __ldg(s4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-      };
-#pragma unroll
-      for (int k = 0; k < DW_PF; ++k) fetch((uint32_t)(grp + k * DW_GROUPS), pf[k]);
       int cur_it = -1;
-      for (uint32_t cbase = (uint32_t)grp; cbase < total; cbase += DW_PF * DW_GROUPS) {
-#pragma unroll
-       for (int k = 0; k < DW_PF; ++k) {                           // (static register slot k of the prefetch ring)
-        const uint32_t c = cbase + (uint32_t)(k * DW_GROUPS);
-        if (c >= total) break;
+      for (uint32_t c = (uint32_t)grp; c < total; c += DW_GROUPS) {
         const int it = (int)(c / DW_CHUNKS), kc = (int)(c % DW_CHUNKS);
         while (cur_it < it) {
+          if (cur_it >= 0) mbar_arrive(bar_Atfree + (cur_it & 1));  // this thread has read its chunks of the previous staged tile
           // row masks of the next item: bit k of word w <-> row 32 w + k has its horizontal / vertical neighbour spin up.
           // Every group passes every item (8 chunks over DW_GROUPS <= 4 groups); group 0 computes, all writers meet.
           ++cur_it;
@@ -205,11 +194,17 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
             }
             asm volatile("bar.sync 1, %0;" ::"n"(128 * DW_GROUPS) : "memory");     // all writer warps
           }
+          mbar_wait(bar_At + (cur_it & 1), ((uint32_t)cur_it >> 1) & 1u);           // the item's staged tile has landed
         }
         float v[16];
+        {
+          const float4* s4 = reinterpret_cast<const float4*>(Ast + ((size_t)(it & 1) * P.nhp + (real ? unit : 0)) * DW_APITCH + kc * DW_KC);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) { v[4 * i] = pf[k][i].x; v[4 * i + 1] = pf[k][i].y; v[4 * i + 2] = pf[k][i].z; v[4 * i + 3] = pf[k][i].w; }
-        fetch(c + (uint32_t)(DW_PF * DW_GROUPS), pf[k]);           // refill the slot just freed
+          for (int i = 0; i < 4; ++i) {
+            const float4 t = real ? s4[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+            v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+          }
+        }
         const uint32_t s = c % DW_ABUF, use = c / DW_ABUF;         // buffer s is used for the (use)-th time
         if (use > 0) mbar_wait(bar_Afree + s, (use - 1u) & 1u);
         const uint32_t a0 = tmem_A0 + lane_base + s * 48u;
@@ -231,7 +226,6 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
         tc_wait_st();
         tc_fence_before();
         mbar_arrive(bar_A + s);
-       }
       }
       // ---- flush: wait for the last MMAs, then add this unit's accumulator rows to the gradient (column blocks shared
       //      between the groups)
@@ -282,9 +276,9 @@ __global__ void __launch_bounds__(128) dpt_rowsum_kernel(const float* __restrict
   __shared__ float red[4];
   const int j = blockIdx.x;
   const long long nitems = (long long)Q * tiles;
-  const float* base = dpT + (size_t)src * Q * tiles * nhp * TC_ROWS + (size_t)j * TC_ROWS + threadIdx.x;
+  const float* base = dpT + (size_t)src * Q * tiles * nhp * TC_DPT_PITCH + (size_t)j * TC_DPT_PITCH + threadIdx.x;
   float s = 0.f;
-  for (long long it = blockIdx.y; it < nitems; it += nsplit) s += base[(size_t)it * nhp * TC_ROWS];
+  for (long long it = blockIdx.y; it < nitems; it += nsplit) s += base[(size_t)it * nhp * TC_DPT_PITCH];
   for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
   __syncthreads();
