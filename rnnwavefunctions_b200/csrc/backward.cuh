@@ -701,8 +701,8 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
   }
 
   // Reduced-precision regime, tensorized GRU: the whole recurrence (heads' push into d h, gate derivatives, input
-  // gradients, scatter to the neighbours) is one persistent tensor-core kernel (bwd_tc.cuh) after one batched
-  // d(logits) kernel; only the operands of the batched weight-gradient GEMMs below are still built per site.
+  // gradients, scatter to the neighbours) is one persistent tensor-core kernel (bwd_tc.cuh); d(logits) of every site is
+  // formed inside it from the heads' outputs the forward sweep saved.
   const bool tc_sweep = m.tc_enabled;
   if (tc_sweep) {
     const bool van = m.cell == CELL_VANILLA2D;
@@ -715,14 +715,10 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
       const bool gated = m.cell == CELL_TENSGRU2D;
       RNNWF_COUNT_LAUNCH(); pack_bwd_tc_kernel<<<512, 256, 0, st>>>(P("W"), gated ? P("Wg") : nullptr, gated ? P("Wmerge") : nullptr, nh, nhp, m.tc_np, wimg);
     }
-    HeadAllParams H;
-    H.Q = m.Q; H.nh = nh; H.nhp = nhp; H.ND = m.ND; H.D = m.D; H.nsites = m.nsites; H.complex_head = m.complex_head;
-    H.u1 = m.u1; H.cap_up = m.cap_up; H.cap_dn = m.cap_dn; H.R = R; H.hist = hist; H.cfg = cfg; H.site_of_t = m.d_site_of_t;
-    H.head_w = m.d_head_w; H.head_b = m.d_head_b; H.seed_logp = seed_logp; H.seed_phase = seed_phase; H.dlog = dlog_base;
-    RNNWF_COUNT_LAUNCH(); head_bwd_all_kernel<<<(unsigned)(((long long)m.Q * R + 7) / 8), 256, 0, st>>>(H);
     BwdTcParams B;
     B.steps = m.d_steps; B.Q = m.Q; B.Tsym = m.Tsym; B.nsites = m.nsites; B.nh = nh; B.nhp = nhp; B.np = pieces; B.ND = m.ND;
     B.rows = R; B.cfg = cfg; B.gates = gates; B.dlog = dlog_base; B.dh = reinterpret_cast<float4*>(dh);
+    B.sv_head = reinterpret_cast<const float4*>(sb + sv.off_head); B.seed_logp = seed_logp; B.seed_phase = seed_phase;
     B.dpT = reinterpret_cast<float*>(ws + L.off_dpT);
     B.wimg = wimg; B.head_w = m.d_head_w; B.hist = hist;
     { const char* dbg = std::getenv("RNNWF_TC_DEBUG"); B.debug = dbg ? std::atoi(dbg) : 0; }

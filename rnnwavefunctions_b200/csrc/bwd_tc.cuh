@@ -59,7 +59,10 @@ struct BwdTcParams {
   long long rows;
   const int8_t* cfg;            // [rows][nsites]
   const float4* gates;          // saved by the sampling sweep, tile-blocked (tc_gate_index)
-  const float* dlog;            // [Q][rows][ND]  d(logits) of every site (head_bwd_all_kernel)
+  float* dlog;                  // [Q][rows][ND]  d(logits) of every site: written here (for the heads' weight gradients)
+  const float4* sv_head;        // [Q][rows] heads' outputs saved by the forward sweep: (p0, p1, phase pre-activation of the symbol, 0)
+  const double* seed_logp;      // [rows] d cost / d log P
+  const double* seed_phase;     // [rows] d cost / d phase (complex head), may be null
   float4* dh;                   // [Q][tiles][sub 4][pass np][row 128] float4, zero-initialised
   float* dpT;                   // [src 3: ds, dg, dm][Q][tiles][unit nhp][row 128]  (feature-major tiles for dw_tc.cuh)
   const float* wimg;            // [variant 3][chunk np][b_bytes / 4]
@@ -197,62 +200,6 @@ __global__ void __launch_bounds__(128) vanilla_input_grads_kernel(const float* _
   }
 }
 
-// ---- d(logits) of every site in one launch --------------------------------------------------------------------
-// One warp per (site, row): recompute the heads from the saved hidden state and form d(logits) for the given seeds
-// (same math as head_bwd_kernel; the push into d h happens inside the reverse sweep).  2D cells: site q <-> symbol q.
-struct HeadAllParams {
-  int Q, nh, nhp, ND, D, nsites, complex_head, u1, cap_up, cap_dn;
-  long long R;
-  const float* hist; const int8_t* cfg; const int16_t* site_of_t;
-  const float* head_w; const float* head_b; const double* seed_logp; const double* seed_phase;
-  float* dlog;
-};
-__global__ void __launch_bounds__(256) head_bwd_all_kernel(const HeadAllParams S) {
-  const int lane = threadIdx.x & 31;
-  const long long w = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (w >= (long long)S.Q * S.R) return;
-  const int q = (int)(w / S.R);
-  const long long row = w - (long long)q * S.R;
-  const float* h = S.hist + ((long long)q * S.R + row) * S.nhp;
-  float part[4] = {0.f, 0.f, 0.f, 0.f};
-  for (int j = lane; j < S.nh; j += 32) {
-    const float hv = h[j];
-#pragma unroll
-    for (int d = 0; d < 4; ++d) if (d < S.ND) part[d] = fmaf(hv, S.head_w[j * S.ND + d], part[d]);
-  }
-#pragma unroll
-  for (int d = 0; d < 4; ++d)
-    for (int o = 16; o > 0; o >>= 1) part[d] += __shfl_xor_sync(0xffffffffu, part[d], o);
-  const int8_t* crow = S.cfg + row * S.nsites;
-  const int s = crow[S.site_of_t[q]] & 1;
-  float p0 = part[0] + S.head_b[0], p1 = part[1] + S.head_b[1];
-  const float mx = fmaxf(p0, p1);
-  p0 = expf(p0 - mx); p1 = expf(p1 - mx);
-  const float ssum = p0 + p1;
-  p0 /= ssum; p1 /= ssum;
-  if (S.u1) {
-    int nup = 0;
-    for (int tt = lane; tt < q; tt += 32) nup += crow[S.site_of_t[tt]] & 1;
-    for (int o = 16; o > 0; o >>= 1) nup += __shfl_xor_sync(0xffffffffu, nup, o);
-    const int ndn = q - nup;
-    p0 *= (S.cap_dn - ndn >= 0) ? 1.f : 0.f;
-    p1 *= (S.cap_up - nup >= 0) ? 1.f : 0.f;
-    const float nrm = p0 + p1;
-    p0 /= nrm; p1 /= nrm;
-  }
-  const float sl = (float)S.seed_logp[row];
-  float dl[4] = {sl * ((s == 0 ? 1.f : 0.f) - p0), sl * ((s == 1 ? 1.f : 0.f) - p1), 0.f, 0.f};
-  if (S.complex_head) {
-    const float sp = (S.seed_phase != nullptr) ? (float)S.seed_phase[row] : 0.f;
-    const float x = ((s == 0) ? part[2] : part[3]) + ((s == 0) ? S.head_b[2] : S.head_b[3]);
-    const float den = 1.f + fabsf(x);
-    const float g = sp * 3.14159265358979f / (den * den);
-    dl[2] = (s == 0) ? g : 0.f;
-    dl[3] = (s == 1) ? g : 0.f;
-  }
-  if (lane < S.ND) S.dlog[((long long)q * S.R + row) * S.ND + lane] = dl[lane];
-}
-
 // ---- the reverse sweep ------------------------------------------------------------------------------------------
 // CELLK: 0 = tensorized GRU (np chunks of 16 units x 7 blocks per site); 1 = vanilla 2D RNN (one chunk per site: the
 // K axis holds d(pre-activation) of all units, position sub * 28 + piece * 4 + e; P.np = unit pieces of the layouts)
@@ -384,6 +331,8 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
       const long long row0 = tile * TC_ROWS;
       const bool live = row0 + row < P.rows;
       have_h = false;
+      const float seed_l = live ? (float)P.seed_logp[row0 + row] : 0.f;
+      const float seed_p = (live && P.seed_phase != nullptr) ? (float)P.seed_phase[row0 + row] : 0.f;
       // ---- symbol table of the tile
       {
         const int8_t* cf = P.cfg + (row0 + row) * P.nsites;
@@ -399,11 +348,25 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
         const bool has_in = sm.w != 0;
         const float cl = (nb0 >= 0) ? (float)tc_sym(symS, nb0, row) : 0.f;
         const float cu = (nb1 >= 0) ? (float)tc_sym(symS, nb1, row) : 0.f;
+        // d(logits) of this (site, row) from the heads' saved outputs: d log p_s / d z_k = [k == s] - p_k (masked softmax),
+        // d phase / d x_s = pi / (1 + |x_s|)^2 (softsign head); 2D cells: site q <-> symbol q
         float dl[4] = {0.f, 0.f, 0.f, 0.f};
         if (live) {
-          const float* dlp = P.dlog + ((size_t)q * (size_t)P.rows + (size_t)(row0 + row)) * P.ND;
-          if (P.ND == 4) { const float4 v = *reinterpret_cast<const float4*>(dlp); dl[0] = v.x; dl[1] = v.y; dl[2] = v.z; dl[3] = v.w; }
-          else { const float2 v = *reinterpret_cast<const float2*>(dlp); dl[0] = v.x; dl[1] = v.y; }
+          const float4 hd = __ldg(P.sv_head + (size_t)q * (size_t)P.rows + (size_t)(row0 + row));
+          const int sy = tc_sym(symS, q, row);
+          dl[0] = seed_l * ((sy == 0 ? 1.f : 0.f) - hd.x);
+          dl[1] = seed_l * ((sy == 1 ? 1.f : 0.f) - hd.y);
+          if (P.ND == 4) {
+            const float den = 1.f + fabsf(hd.z);
+            const float g = seed_p * 3.14159265358979f / (den * den);
+            dl[2] = (sy == 0) ? g : 0.f;
+            dl[3] = (sy == 1) ? g : 0.f;
+          }
+          if (sub == 0) {
+            float* dlp = P.dlog + ((size_t)q * (size_t)P.rows + (size_t)(row0 + row)) * P.ND;
+            if (P.ND == 4) *reinterpret_cast<float4*>(dlp) = make_float4(dl[0], dl[1], dl[2], dl[3]);
+            else *reinterpret_cast<float2*>(dlp) = make_float2(dl[0], dl[1]);
+          }
         }
         if constexpr (CELLK == 1) {
           // ---- vanilla cell: d(pre) = (d h + heads' push) * elu'(pre), elu' = 1 for h > 0 else h + 1; one chunk per site

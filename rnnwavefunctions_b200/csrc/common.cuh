@@ -95,6 +95,7 @@ struct SweepParams {
   float* sv_hist;           // [Q][sv_rows][nhp]
   float4* sv_gates;         // [Q][sv_rows][Gp]
   double2* sv_cum;          // [Tsym][sv_rows]
+  float4* sv_head;          // tensor-core regime: heads' outputs (p0, p1, phase pre-activation of the symbol, 0) [Q][sv_rows]
   float* sv_himg;           // tensor-core regime: hidden states as UMMA tile images per (site, 128-row tile) (dw_tc.cuh)
   long long sv_rows;
   // ---- tensor-core regime (sweep_tc.cuh)

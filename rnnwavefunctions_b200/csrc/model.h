@@ -25,7 +25,7 @@ struct HostVariant {
 };
 
 struct Saved {   // byte offsets inside a caller-provided saved-state buffer for `rows` rows
-  long long off_hist, off_gates, off_cum, off_himg, total;
+  long long off_hist, off_gates, off_cum, off_himg, off_head, total;
 };
 
 struct rnnwf_model_impl {
@@ -107,7 +107,10 @@ struct rnnwf_model_impl {
     s.off_himg = s.off_cum + al((long long)Tsym * rows * 16);
     // tensor-core regime: hidden states once more as ready-made B operand tiles of the weight-gradient kernel
     const long long himg_bytes = tc_enabled ? (long long)Q * ((rows + 127) / 128) * (32LL * (((nhp + 15) / 16) * 2) * 32) * 4 : 0;
-    s.total = s.off_himg + al(himg_bytes);
+    // tensor-core regime: the heads' outputs of every (site, row) -- (p0, p1, phase pre-activation of the symbol, 0) -- so that
+    // the reverse sweep forms d(logits) itself instead of recomputing the heads from the hidden states
+    s.off_head = s.off_himg + al(himg_bytes);
+    s.total = s.off_head + al(tc_enabled ? (long long)Q * rows * 16 : 0);
     return s;
   }
 };

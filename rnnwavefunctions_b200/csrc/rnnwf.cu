@@ -464,6 +464,7 @@ int set_saved(const rnnwf_model& m, SweepParams& P, void* saved, long long rows)
   P.sv_gates = (m.gru_type || (m.tc_enabled && m.cell == CELL_TENS2D)) ? reinterpret_cast<float4*>(b + sv.off_gates) : nullptr;
   P.sv_cum = reinterpret_cast<double2*>(b + sv.off_cum);
   P.sv_himg = m.tc_enabled ? reinterpret_cast<float*>(b + sv.off_himg) : nullptr;
+  P.sv_head = m.tc_enabled ? reinterpret_cast<float4*>(b + sv.off_head) : nullptr;
   P.sv_rows = rows;
   return RNNWF_OK;
 }

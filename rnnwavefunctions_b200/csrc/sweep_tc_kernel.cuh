@@ -667,8 +667,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
             else rphase[k] += (double)(3.14159265358979323846f * __fdividef(xs, 1.0f + fabsf(xs)));
           }
           rnup[k] += sy;
-          if (P.sv_cum != nullptr && MODE != MODE_CHILD)
+          if (P.sv_cum != nullptr && MODE != MODE_CHILD) {
             P.sv_cum[(size_t)t * (size_t)P.sv_rows + (size_t)(row0 + row)] = make_double2(rlogp[k], rphase[k]);
+            // the heads' outputs, for the reverse sweep (bwd_tc.cuh forms d(logits) from them)
+            P.sv_head[(size_t)t * (size_t)P.sv_rows + (size_t)(row0 + row)] = make_float4(p0, p1, P.complex_head ? (sy ? l4[k][3] : l4[k][2]) : 0.f, 0.f);
+          }
           }
           if (MODE == MODE_SAMPLE) {      // drawn symbols of rows 32 k .. 32 k + 31: one ballot word (the head warp's lane == row & 31)
             const uint32_t w = __ballot_sync(0xffffffffu, sy);
