@@ -766,7 +766,7 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
       const int nsplit = 16;
       if (van) {
         D.gW = nullptr; D.gWg = nullptr; D.gM0 = Gd("Wh"); D.gM1 = Gd("Wv");
-        D.slab[0] = D.slab[1] = D.slab[2] = 0;
+        D.slab[0] = D.slab[1] = D.slab[2] = 0; D.gB = nullptr; D.gBg = nullptr;
         if (njobs > 0) { RNNWF_COUNT_LAUNCH(); dw_tc_kernel<<<(unsigned)njobs, DW_THREADS, dw_smem_bytes(nhp), st>>>(D); }   // (a single-site lattice has no neighbour weights)
         RNNWF_COUNT_LAUNCH(); vanilla_input_grads_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, m.d_steps, m.d_site_of_t, cfg, m.Q, tiles, R, nh, nhp,
                                                                                           m.nsites, Gd("b"), Gd("Uh"), Gd("Uv"));
@@ -775,9 +775,20 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
         D.gW = Gd("W"); D.gWg = gated ? Gd("Wg") : nullptr;
         D.gM0 = gated ? Gd("Wmerge") : nullptr; D.gM1 = gated ? Gd("Wmerge") + (long long)nh * nh : nullptr;
         D.slab[0] = 0; D.slab[1] = 1; D.slab[2] = 2;
+        // biases: a free padding position of the hidden-state image holds a constant 1 (sweep_tc_kernel.cuh), so the sums over
+        // the rows come out of the weight-gradient MMAs for every site with a neighbour; the others (site 0) are summed directly
+        const bool bias_mma = nh < tc_himg_ncores(nhp) * 8 && njobs > 0 && std::getenv("RNNWF_NO_BIAS_MMA") == nullptr;
+        int nq = m.Q;
+        if (bias_mma) { nq = 0; while (nq < m.Q && m.steps[nq].nbr[0] < 0 && m.steps[nq].nbr[1] < 0) ++nq; }
+        for (int q = nq; bias_mma && q < m.Q; ++q)
+          if (m.steps[q].nbr[0] < 0 && m.steps[q].nbr[1] < 0) { err = "rnnwf_backward: a site without neighbours inside the path"; return RNNWF_EINVAL; }
+        D.gB = bias_mma ? Gd("b") : nullptr; D.gBg = (bias_mma && gated) ? Gd("bg") : nullptr;
         if (njobs > 0) { RNNWF_COUNT_LAUNCH(); dw_tc_kernel<<<(unsigned)njobs, DW_THREADS, dw_smem_bytes(nhp), st>>>(D); }   // (a single-site lattice has no neighbour weights)
-        RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, 0, m.Q, tiles, nhp, nsplit, Gd("b"));
-        if (gated) { RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, 1, m.Q, tiles, nhp, nsplit, Gd("bg")); }
+        if (nq > 0) {
+          const int ns2 = std::max(1, std::min<int>(nsplit, (int)std::min<long long>(1 << 20, (long long)nq * tiles)));
+          RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, ns2), 128, 0, st>>>(B.dpT, 0, m.Q, nq, tiles, nhp, ns2, Gd("b"));
+          if (gated) { RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, ns2), 128, 0, st>>>(B.dpT, 1, m.Q, nq, tiles, nhp, ns2, Gd("bg")); }
+        }
       }
       RNNWF_COUNT_LAUNCH(); head_grad_himg_kernel<<<std::min<long long>((long long)m.Q * tiles, 4LL * m.num_sms), 128, 0, st>>>(
           himg, dlog_base, m.Q, tiles, R, nh, nhp, m.ND, Gd("dense.W"), m.complex_head ? Gd("dense_phase.W") : nullptr);

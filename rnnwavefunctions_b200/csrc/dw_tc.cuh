@@ -63,6 +63,7 @@ struct DwParams {
   const float* himg;      // hidden-state tile images
   float* gW; float* gWg;
   float* gM0; float* gM1;   // unmasked source (src 2): [unit i][unit j] targets of the horizontal / vertical half
+  float* gB; float* gBg;    // bias gradients of sources 0 / 1 from the constant-1 column (unit position nh) of the hidden-state image, or null
   int slab[3];              // which feature-major slab of dpT holds source 0, 1, 2
   int debug;                // timing experiments (RNNWF_TC_DEBUG bits 16..18: no MMAs / no operand loads / no masked copies), 0 in production
 };
@@ -249,6 +250,12 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
 #pragma unroll
             for (int e = 0; e < 16; ++e) {
               const int i = n0 + e;
+              if (i == nh && masks && (job.half == 0 || job.cls == 2)) {
+                // constant-1 column: sum over the rows of this job's items (every site with a neighbour is counted once:
+                // through its horizontal half, or through the vertical one if it has no horizontal neighbour)
+                float* gb = (job.src == 0) ? P.gB : P.gBg;
+                if (gb != nullptr) atomicAdd(gb + unit, __uint_as_float(S[e]));
+              }
               if (i >= nh) continue;
               const float s = __uint_as_float(S[e]);
               if (!masks) {
@@ -271,11 +278,12 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
 }
 
 // bias gradients from the feature-major tiles: out[j] += sum over all (site, tile, row) of src[j]
-__global__ void __launch_bounds__(128) dpt_rowsum_kernel(const float* __restrict__ dpT, int src, int Q, long long tiles, int nhp,
+// (nq: only the first nq sites -- dw_tc_kernel's constant-1 column covers every site that has a neighbour)
+__global__ void __launch_bounds__(128) dpt_rowsum_kernel(const float* __restrict__ dpT, int src, int Q, int nq, long long tiles, int nhp,
                                                          int nsplit, float* __restrict__ out) {
   __shared__ float red[4];
   const int j = blockIdx.x;
-  const long long nitems = (long long)Q * tiles;
+  const long long nitems = (long long)nq * tiles;
   const float* base = dpT + (size_t)src * Q * tiles * nhp * TC_DPT_PITCH + (size_t)j * TC_DPT_PITCH + threadIdx.x;
   float s = 0.f;
   for (long long it = blockIdx.y; it < nitems; it += nsplit) s += base[(size_t)it * nhp * TC_DPT_PITCH];

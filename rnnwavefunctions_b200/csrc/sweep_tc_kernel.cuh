@@ -546,7 +546,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
               const int j0 = p * TC_JP + sub * 4;
               if (j0 < hnc * 8) {
   #pragma unroll
-                for (int e = 0; e < 4; ++e) sv_i[((j0 + e) >> 3) * 32 + ((j0 + e) & 7) * 4] = hsave[e];
+                for (int e = 0; e < 4; ++e)   // (unit position nh, the first padding unit: a constant 1 -> the bias gradients fall out of dw_tc_kernel's MMAs)
+                  sv_i[((j0 + e) >> 3) * 32 + ((j0 + e) & 7) * 4] = (CELLK != 1 && j0 + e == nh && live) ? 1.0f : hsave[e];
               }
             }
             a_carry += 2u; bSp += TC_JP; hWp += TC_JP * 4; sv_h += TC_JP; sv_g += 3 * TC_ROWS;
