@@ -413,6 +413,15 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
         } else {
           const float4* gq = P.gates + tc_gate_index(q, tile, ntiles, NP, sub, 0, 0, row);
           const float4* dhq = P.dh + tc_dh_index(q, tile, ntiles, NP, sub, 0, row);
+          // The saved gates stream from DRAM and the loop below only looks one column pass ahead: pull the NEXT site's gates
+          // of this warp (np_own passes x 3 quantities x 512 contiguous bytes) into the L2 a whole site ahead.
+          if (q > 0 && (lane & 7) == 0 && !(P.debug & (1 << 22))) {
+            const float4* gn = P.gates + tc_gate_index(q - 1, tile, ntiles, NP, sub, 0, 0, row);
+            for (int i = 0; i < 3 * np_own; ++i) asm volatile("prefetch.global.L2 [%0];" ::"l"(gn + (size_t)i * TC_ROWS));
+            const float4* dn = P.dh + tc_dh_index(q - 1, tile, ntiles, NP, sub, 0, row);       // (its vertical successor wrote it ~2 rows of sites ago)
+            for (int i = 0; i < np_own; ++i) asm volatile("prefetch.global.L2 [%0];" ::"l"(dn + (size_t)i * TC_ROWS));
+            if (sub == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(P.sv_head + (size_t)(q - 1) * (size_t)P.rows + (size_t)(row0 + row)));
+          }
           float4 n_dh = make_float4(0.f, 0.f, 0.f, 0.f), n_u = n_dh, n_t = n_dh, n_m = n_dh;
           if (live && np_own > 0) { n_dh = __ldcg(dhq); n_u = __ldg(gq); n_t = __ldg(gq + TC_ROWS); n_m = __ldg(gq + 2 * TC_ROWS); }
   #pragma unroll 1
