@@ -529,31 +529,37 @@ inline void dw_plan(const rnnwf_model_impl& m, long long R, std::vector<DwJob>& 
     const int c = (h && u) ? 0 : (h ? 1 : (u ? 2 : -1));
     if (c >= 0) cls_steps[(size_t)c * m.Q + cls_count[c]++] = q;
   }
-  struct Group { int src, half, cls; long long items; double w; };
-  std::vector<Group> groups;
-  double total = 0;
+  // The kernel is DRAM-bound (per item one hidden-state tile and one (ds|dg|dm) tile).  Jobs k of the sources (ds, dg, dm) of
+  // one (half, class) get the SAME item ranges, and so do the two halves of a class: CTAs that walk the same (site, tile) items
+  // at the same time share the tiles through the L2 (the hidden-state tile of a half is read by its three sources, the
+  // (ds|dg|dm) tile of a source by both halves).  CTAs per (half, class): greedy on the largest items / CTAs, all sources alike.
+  struct Super { int half, cls; long long items; int n; };
+  std::vector<Super> sup;
   const int src_lo = (m.cell == CELL_VANILLA2D) ? 2 : 0;                // vanilla cell: one unmasked source (d pre -> Wh, Wv)
   const int src_hi = (m.cell == CELL_TENS2D) ? 1 : 3;                   // un-gated tensorized cell: ds -> W only
-  for (int src = src_lo; src < src_hi; ++src)
-    for (int half = 0; half < 2; ++half)
-      for (int cls = 0; cls < 3; ++cls) {
-        if ((half == 0 && cls == 2) || (half == 1 && cls == 1)) continue;   // that neighbour is absent in this class
-        const long long items = (long long)cls_count[cls] * tiles;
-        if (items == 0) continue;
-        const double w = (src == 2 && m.cell != CELL_VANILLA2D) ? 0.5 : 1.0;
-        groups.push_back({src, half, cls, items, w});
-        total += items * w;
-      }
-  jobs.clear();
-  const double target = total / std::max(1, m.num_sms);
-  for (const Group& g : groups) {
-    long long n = (long long)(g.items * g.w / std::max(1e-9, target) + 0.5);
-    n = std::max(1LL, std::min(n, g.items));
-    for (long long k = 0; k < n; ++k) {
-      const long long b = g.items * k / n, e = g.items * (k + 1) / n;
-      jobs.push_back({g.src, g.half, g.cls, (int)b, (int)(e - b)});
+  const int nsrc = src_hi - src_lo;
+  for (int cls = 0; cls < 3; ++cls)
+    for (int half = 0; half < 2; ++half) {
+      if ((half == 0 && cls == 2) || (half == 1 && cls == 1)) continue;   // that neighbour is absent in this class
+      const long long items = (long long)cls_count[cls] * tiles;
+      if (items > 0) sup.push_back({half, cls, items, 1});
     }
+  jobs.clear();
+  if (sup.empty()) return;
+  int used = (int)sup.size() * nsrc;
+  while (used + nsrc <= std::max(m.num_sms, (int)sup.size() * nsrc)) {
+    size_t best = 0;
+    for (size_t k = 1; k < sup.size(); ++k)
+      if ((double)sup[k].items / sup[k].n > (double)sup[best].items / sup[best].n) best = k;
+    if (sup[best].n >= sup[best].items) break;
+    ++sup[best].n; used += nsrc;
   }
+  // launch order: the CTAs that share tiles next to each other (sources innermost)
+  for (const Super& g : sup)
+    for (int k = 0; k < g.n; ++k) {
+      const long long b = g.items * k / g.n, e = g.items * (k + 1) / g.n;
+      for (int src = src_lo; src < src_hi; ++src) jobs.push_back({src, g.half, g.cls, (int)b, (int)(e - b)});
+    }
 }
 
 inline long long backward_workspace_bytes(const rnnwf_model_impl& m, long long R) { return backward_layout(m, R).total; }
@@ -735,9 +741,11 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
     }
     const long long tiles = (R + TC_ROWS - 1) / TC_ROWS;
     const BtSmem bs(nhp, m.Tsym, m.Q);
+    B.tile_rows = tc_tile_rows(R, m.num_sms);
+    const long long vtiles = (tiles * TC_ROWS + B.tile_rows - 1) / B.tile_rows;
     RNNWF_COUNT_LAUNCH();
-    if (van) bwd_tc_kernel<1><<<(unsigned)std::min<long long>(tiles, m.num_sms), BT_THREADS, bs.total, st>>>(B);
-    else bwd_tc_kernel<0><<<(unsigned)std::min<long long>(tiles, m.num_sms), BT_THREADS, bs.total, st>>>(B);
+    if (van) bwd_tc_kernel<1><<<(unsigned)std::min<long long>(vtiles, m.num_sms), BT_THREADS, bs.total, st>>>(B);
+    else bwd_tc_kernel<0><<<(unsigned)std::min<long long>(vtiles, m.num_sms), BT_THREADS, bs.total, st>>>(B);
     // ---- parameter gradients: weights on the tensor cores (dw_tc.cuh), biases and heads as reductions
     {
       DwParams D;

@@ -68,6 +68,7 @@ struct BwdTcParams {
   const float* wimg;            // [variant 3][chunk np][b_bytes / 4]
   const float* head_w;          // [nh][ND]
   const float* hist;            // vanilla cell: saved hidden states [Q][rows][nhp] (elu' = h > 0 ? 1 : h + 1)
+  int tile_rows;                // live rows per tile (<= 128): batches of fewer tiles than SMs are spread over all SMs (as in the forward sweep)
   int h_chain;                  // 1: every horizontal neighbour is the site generated right before (nbr[0] == q - 1 wherever present)
   int debug;                    // timing experiments (RNNWF_TC_DEBUG bits 19..21: no MMAs / no feature-major stores / no d h update), 0 in production
 };
@@ -245,7 +246,9 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t tmem_A0 = tmem_base + ((ncols + 15u) & ~15u);
-  const long long ntiles = (P.rows + TC_ROWS - 1) / TC_ROWS;
+  const long long ntiles = (P.rows + TC_ROWS - 1) / TC_ROWS;        // 128-row tiles of the tile-blocked layouts (gates, d h, feature-major tiles)
+  const int VR = P.tile_rows;                                          // rows this kernel processes per tile
+  const long long vtiles = (ntiles * TC_ROWS + VR - 1) / VR;          // (they cover the rows up to a multiple of 128: zeros are written past the batch)
 
   if (warp == 0) {
     // ======================= MMA warp =======================
@@ -255,7 +258,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
     const uint64_t kstep = (uint64_t)((2u * B_LBO) >> 4);           // two k-cores (8 tf32) per MMA
     const uint32_t idesc = tc_idesc_tf32(TC_ROWS, (int)ncols);
     uint32_t phA = 0, phB = 0, c = 0, nsite = 0;
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    for (long long tile = blockIdx.x; tile < vtiles; tile += gridDim.x) {
       for (int q = P.Q - 1; q >= 0; --q) {
         if (!stepS[q].w) continue;                                  // first site: no inputs to differentiate
         for (int p = 0; p < NCH; ++p, ++c) {
@@ -282,7 +285,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
     // ======================= loader warp: weight chunks =======================
     const bool leader = elect_one();
     uint32_t phF = 0, c = 0;
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    for (long long tile = blockIdx.x; tile < vtiles; tile += gridDim.x) {
       for (int q = P.Q - 1; q >= 0; --q) {
         const short4 sm = stepS[q];
         if (!sm.w) continue;
@@ -327,9 +330,12 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
       else { hc[0] = hreg[4]; hc[1] = hreg[5]; hc[2] = hreg[6]; hc[3] = hreg[7]; }
     };
     uint32_t phF = 0, c = 0, nsite = 0;
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-      const long long row0 = tile * TC_ROWS;
-      const bool live = row0 + row < P.rows;
+    for (long long tile = blockIdx.x; tile < vtiles; tile += gridDim.x) {
+      const long long row0 = tile * VR;
+      const bool live = row < VR && row0 + row < P.rows;
+      const bool stores = row < VR && row0 + row < ntiles * TC_ROWS;   // owns a row of the feature-major tiles (zeros past the batch)
+      const long long stile = (row0 + row) / TC_ROWS;                   // position of the row in the 128-row tile-blocked layouts
+      const int srow = (int)((row0 + row) % TC_ROWS);
       have_h = false;
       const float seed_l = live ? (float)P.seed_logp[row0 + row] : 0.f;
       const float seed_p = (live && P.seed_phase != nullptr) ? (float)P.seed_phase[row0 + row] : 0.f;
@@ -370,7 +376,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
         }
         if constexpr (CELLK == 1) {
           // ---- vanilla cell: d(pre) = (d h + heads' push) * elu'(pre), elu' = 1 for h > 0 else h + 1; one chunk per site
-          const float4* dhq = P.dh + tc_dh_index(q, tile, ntiles, NP, sub, 0, row);
+          const float4* dhq = P.dh + tc_dh_index(q, stile, ntiles, NP, sub, 0, srow);
           const float* hq = P.hist + ((size_t)q * (size_t)P.rows + (size_t)(row0 + row)) * nhp + sub * 4;
           uint32_t d[TC_TPS];
 #pragma unroll
@@ -394,10 +400,10 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
                   d[blk * 4 + e] = __float_as_uint(dp[e]);
                 }
               }
-              float* o0 = P.dpT + (((size_t)q * (size_t)ntiles + (size_t)tile) * nhp + j0) * TC_DPT_PITCH + row;
+              float* o0 = P.dpT + (((size_t)q * (size_t)ntiles + (size_t)stile) * nhp + j0) * TC_DPT_PITCH + srow;
 #pragma unroll
               for (int e = 0; e < 4; ++e)
-                if (j0 + e < nhp) o0[(size_t)e * TC_DPT_PITCH] = dp[e];
+                if (j0 + e < nhp && stores) o0[(size_t)e * TC_DPT_PITCH] = dp[e];
             }
           }
           if (has_in) {
@@ -411,14 +417,14 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
             ++c;
           }
         } else {
-          const float4* gq = P.gates + tc_gate_index(q, tile, ntiles, NP, sub, 0, 0, row);
-          const float4* dhq = P.dh + tc_dh_index(q, tile, ntiles, NP, sub, 0, row);
+          const float4* gq = P.gates + tc_gate_index(q, stile, ntiles, NP, sub, 0, 0, srow);
+          const float4* dhq = P.dh + tc_dh_index(q, stile, ntiles, NP, sub, 0, srow);
           // The saved gates stream from DRAM and the loop below only looks one column pass ahead: pull the NEXT site's gates
           // of this warp (np_own passes x 3 quantities x 512 contiguous bytes) into the L2 a whole site ahead.
           if (q > 0 && (lane & 7) == 0 && !(P.debug & (1 << 22))) {
-            const float4* gn = P.gates + tc_gate_index(q - 1, tile, ntiles, NP, sub, 0, 0, row);
+            const float4* gn = P.gates + tc_gate_index(q - 1, stile, ntiles, NP, sub, 0, 0, srow);
             for (int i = 0; i < 3 * np_own; ++i) asm volatile("prefetch.global.L2 [%0];" ::"l"(gn + (size_t)i * TC_ROWS));
-            const float4* dn = P.dh + tc_dh_index(q - 1, tile, ntiles, NP, sub, 0, row);       // (its vertical successor wrote it ~2 rows of sites ago)
+            const float4* dn = P.dh + tc_dh_index(q - 1, stile, ntiles, NP, sub, 0, srow);       // (its vertical successor wrote it ~2 rows of sites ago)
             for (int i = 0; i < np_own; ++i) asm volatile("prefetch.global.L2 [%0];" ::"l"(dn + (size_t)i * TC_ROWS));
             if (sub == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(P.sv_head + (size_t)(q - 1) * (size_t)P.rows + (size_t)(row0 + row)));
           }
@@ -458,11 +464,11 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
                 }
               }
               // feature-major tiles for the weight-gradient kernel (zeros for rows past the end of the batch)
-              float* o0 = P.dpT + (((size_t)q * (size_t)ntiles + (size_t)tile) * nhp + j0) * TC_DPT_PITCH + row;
+              float* o0 = P.dpT + (((size_t)q * (size_t)ntiles + (size_t)stile) * nhp + j0) * TC_DPT_PITCH + srow;
               const size_t sstride = (size_t)P.Q * (size_t)ntiles * nhp * TC_DPT_PITCH;
   #pragma unroll
               for (int e = 0; e < 4; ++e) {
-                if (j0 + e < nhp && !(P.debug & (1 << 20))) { o0[(size_t)e * TC_DPT_PITCH] = ds[e]; o0[sstride + (size_t)e * TC_DPT_PITCH] = dg[e]; o0[2 * sstride + (size_t)e * TC_DPT_PITCH] = dm[e]; }
+                if (j0 + e < nhp && stores && !(P.debug & (1 << 20))) { o0[(size_t)e * TC_DPT_PITCH] = ds[e]; o0[sstride + (size_t)e * TC_DPT_PITCH] = dg[e]; o0[2 * sstride + (size_t)e * TC_DPT_PITCH] = dm[e]; }
               }
             }
             if (has_in) {
@@ -489,7 +495,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
               tc_ld28(tmem_base + lane_base + (uint32_t)nhp + kcol, d);
               tc_wait_ld();
               if (live && !(P.debug & (1 << 21))) {
-                float4* dst = P.dh + tc_dh_index(nb1, tile, ntiles, NP, sub, 0, row);
+                float4* dst = P.dh + tc_dh_index(nb1, stile, ntiles, NP, sub, 0, srow);
 #pragma unroll
                 for (int p = 0; p < TC_TPS / 4; ++p)
                   if (p < np_own)
@@ -520,7 +526,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bwd_tc_kernel(const BwdTcParams
             tc_ld28(tmem_base + lane_base + (uint32_t)half * (uint32_t)nhp + kcol, d);
             tc_wait_ld();
             if (live && !(P.debug & (1 << 21))) {
-              float4* dst = P.dh + tc_dh_index(nb, tile, ntiles, NP, sub, 0, row);
+              float4* dst = P.dh + tc_dh_index(nb, stile, ntiles, NP, sub, 0, srow);
 #pragma unroll
               for (int p = 0; p < TC_TPS / 4; ++p) {
                 if (p < np_own) {

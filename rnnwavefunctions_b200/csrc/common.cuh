@@ -103,6 +103,7 @@ struct SweepParams {
   const float* tc_bias;        // [2][nhp]: b, bg
   int tc_np;
   unsigned long long* tc_prof;  // optional per-CTA cycle counters (debug)
+  int tile_rows;                      // tensor-core sweeps, sampling / evaluation: live rows per tile (<= 128; rows spread over all SMs)
   int debug_flags;                    // tensor-core sweep timing experiments (RNNWF_TC_DEBUG), 0 in production
   long long sched_ns;          // CHILD mode of single-flip Hamiltonians: samples per (step, bit) group of the regular child list
   int sched_bits;              //   (child index (t bits + k) ns + n), 0 = no regular structure

@@ -338,7 +338,7 @@ int build_model(rnnwf_model& m) {
 // ------------------------------------------------------------------------------------------------
 // sweep launch
 // ------------------------------------------------------------------------------------------------
-struct LaunchShape { int WR, Mp, Mr, threads, smem, grid; };
+struct LaunchShape { int WR, Mp, Mr, threads, smem, grid, tile_rows; };
 
 const void* sweep_fn(const rnnwf_model& m) {
   if (m.NTU == 3 && m.TJ == 5) return reinterpret_cast<const void*>(&sweep_kernel<5, 3>);
@@ -353,7 +353,9 @@ int max_ctas(const rnnwf_model& m) {
   return m.num_sms * occ;
 }
 
-int pick_shape(const rnnwf_model& m, long long rows, LaunchShape& s) {
+// child: the connected-configuration sweep (always full tiles)
+int pick_shape(const rnnwf_model& m, long long rows, LaunchShape& s, bool child = false) {
+  s.tile_rows = 128;
   if (m.g1) {
     const long long tiles = (rows + G1_ROWS - 1) / G1_ROWS;
     s.WR = 2; s.Mp = G1_ROWS; s.Mr = G1_ROWS; s.threads = g1_threads(m.nh); s.smem = G1Layout(m.nh, m.symL, m.Tsym).total_bytes;
@@ -362,8 +364,12 @@ int pick_shape(const rnnwf_model& m, long long rows, LaunchShape& s) {
   }
   if (m.tc_enabled) {
     const TcSmem ts(m.nhp, m.Tsym, m.Q);
-    const long long tiles = (rows + TC_ROWS - 1) / TC_ROWS;
+    long long tiles = (rows + TC_ROWS - 1) / TC_ROWS;
     s.WR = 4; s.Mp = TC_ROWS; s.Mr = TC_ROWS; s.threads = TC_THREADS; s.smem = ts.total;
+    if (!child) {     // sampling / evaluation: fewer tiles than SMs are spread over all SMs (sweep_tc.cuh: tc_tile_rows)
+      s.tile_rows = tc_tile_rows(rows, m.num_sms);
+      tiles = (tiles * TC_ROWS + s.tile_rows - 1) / s.tile_rows;
+    }
     s.grid = (int)std::max(1LL, std::min<long long>(tiles, m.num_sms));
     return RNNWF_OK;
   }
@@ -401,6 +407,7 @@ void fill_model_params(const rnnwf_model& m, const LaunchShape& s, SweepParams& 
   P.complex_head = m.complex_head; P.u1 = m.u1; P.cap_up = m.cap_up; P.cap_dn = m.cap_dn;
   P.Q = m.Q; P.Tsym = m.Tsym; P.symL = m.symL; P.nsites = m.nsites; P.bits = m.bits; P.cps = m.cps;
   P.Gblk = m.Gblk; P.ncb = m.ncb; P.Gp = m.Gp; P.Greal = m.Greal; P.ntu = m.NTU;
+  P.tile_rows = s.tile_rows;
   P.ring_len = m.ring_len; P.WR = s.WR; P.WC = m.WC; P.Mp = s.Mp; P.Mr = s.Mr; P.ncls_max = m.ncls_max;
   P.steps = m.d_steps; P.variants = m.d_variants; P.Wpack = m.d_wpack; P.Xtab = m.d_xtab; P.bias = m.d_bias;
   P.head_w = m.d_head_w; P.head_b = m.d_head_b;
@@ -1043,7 +1050,7 @@ int rnnwf_local_energies(rnnwf_handle h, int hamiltonian, const double* ham, int
   if (!en.have_children) return RNNWF_OK;
 
   LaunchShape s;
-  if ((rc = pick_shape(m, en.nchild_fixed, s))) return rc;
+  if ((rc = pick_shape(m, en.nchild_fixed, s, true))) return rc;
   SweepParams P;
   fill_model_params(m, s, P);
   P.mode = MODE_CHILD; P.rows = en.nchild_fixed; P.rows_dev = en.rows_dev; P.cfg_in = samples_dev; P.children = d_children;

@@ -270,6 +270,14 @@ constexpr float TC_SCALE_CAND = 1.0f, TC_SCALE_GATE = 0.5f;
 // (exact power-of-two scalings that keep the lo parts out of FP16's subnormal range: |h| >= 2e-3, |w| >= 1.2e-4);
 // FP16 overflows beyond |h| = 1023 and |w| = 63.9
 constexpr float TC_SPLIT_HS = 64.0f, TC_SPLIT_WS = 1024.0f;
+// Sampling / evaluation / reverse sweeps over fewer 128-row tiles than SMs: every site is a latency chain per tile, so the
+// rows are spread over all SMs -- live rows per tile (a multiple of 8, <= 128; the MMAs stay 128 rows high).
+inline int tc_tile_rows(long long rows, int num_sms) {
+  const long long tiles = (rows + TC_ROWS - 1) / TC_ROWS;
+  if (tiles >= num_sms || std::getenv("RNNWF_NO_VTILES") != nullptr) return TC_ROWS;
+  const long long per = (tiles * TC_ROWS + num_sms - 1) / num_sms;
+  return (int)std::max<long long>(8, std::min<long long>(TC_ROWS, (per + 7) / 8 * 8));
+}
 __device__ __forceinline__ float mufu_tanh(float x) { float y; asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float sigmoid_prescaled(float x) { return fmaf(0.5f, mufu_tanh(x), 0.5f); }
 __device__ __forceinline__ float tanh_prescaled(float x) { return mufu_tanh(x); }

@@ -131,7 +131,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
 #endif
 
   const long long total_rows = (P.rows_dev != nullptr) ? (long long)(*P.rows_dev) : P.rows;
-  const long long ntiles = (total_rows + TC_ROWS - 1) / TC_ROWS;
+  // Rows per tile.  The connected-configuration sweep always runs full 128-row tiles (it has thousands of them).  Sampling
+  // and evaluation batches are a few dozen tiles, fewer than SMs, and every site is a latency chain per tile: there the
+  // host spreads the rows over all SMs (P.tile_rows <= 128 live rows per tile; the MMAs stay 128 rows high).  The saved
+  // state keeps its 128-row tile-blocked layouts: a thread addresses them through its global row (srow_of / stile_of), and
+  // the tiles cover the batch rounded up to 128 rows so that the images' rows past the batch are written (as zeros).
+  const int VR = (MODE == MODE_CHILD) ? TC_ROWS : P.tile_rows;
+  const long long rows_cover = (MODE == MODE_CHILD) ? total_rows : ((total_rows + TC_ROWS - 1) / TC_ROWS) * TC_ROWS;
+  const long long ntiles = (rows_cover + VR - 1) / VR;
   // first sweep step of a tile: under prefix reuse the tile restarts where its first child departs from its parent
   auto tile_q0 = [&](long long row0) -> int {
     int ts0 = 0;
@@ -158,7 +165,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
     const uint32_t tmem_d = tmem_base + (uint32_t)me * (uint32_t)TC_N;
     uint32_t phA = 0, nuse = 0, it0 = 0;              // operand parity; uses of this warp's buffer; passes before this site
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-      const int q0 = tile_q0(tile * TC_ROWS) * P.symL;
+      const int q0 = tile_q0(tile * VR) * P.symL;
       for (int q = q0; q < P.Q; ++q, it0 += (uint32_t)NP) {
         TC_T0();
         const uint32_t tmem_a = SPLIT ? tmem_A0 : tmem_A0 + (uint32_t)(q & 1) * acols;
@@ -204,7 +211,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
     const uint32_t load_bytes = (P.debug_flags & 1) ? (uint32_t)L.b_bytes / 2 : (uint32_t)L.b_bytes;
     uint32_t phBf = 0, n = 0;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-      const int q0 = tile_q0(tile * TC_ROWS) * P.symL;
+      const int q0 = tile_q0(tile * VR) * P.symL;
       for (int q = q0; q < P.Q; ++q) {
         const short4 sm = metaS[q];
         const int v = (CELLK == 1) ? 0 : ((sm.x >= 0 && sm.y < 0) ? 1 : ((sm.x < 0 && sm.y >= 0) ? 2 : 0));   // first site: any image (operand is zero)
@@ -254,11 +261,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
     uint32_t phM = 0;                                   // parity bits of the two accumulator-full barriers
     uint32_t hs = 0, ntile = 0;                         // steps / tiles processed so far by this CTA
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++ntile) {
-      const long long row0 = tile * TC_ROWS;
-      const int nrows = (int)((total_rows - row0 < (long long)TC_ROWS) ? (total_rows - row0) : (long long)TC_ROWS);
+      const long long row0 = tile * VR;
+      const int nrows = (int)((total_rows - row0 < (long long)VR) ? (total_rows - row0 > 0 ? total_rows - row0 : 0) : (long long)VR);
       const int q0 = tile_q0(row0) * P.symL;
       const bool live = row < nrows;
+      const bool stores = row < VR && row0 + row < rows_cover;       // this thread owns a row of the saved images (zeros past the batch)
       const long long sv_tiles = ((long long)P.sv_rows + TC_ROWS - 1) / TC_ROWS;
+      const long long stile = (row0 + row) / TC_ROWS;                 // position of the row in the 128-row tile-blocked saved layouts
+      const int srow = (int)((row0 + row) % TC_ROWS);
       int rparent = 0;
       // ---- symbol table of the tile (teacher forcing); the head warps must be done with the previous tile's
       if (ntile > 0) mbar_wait(bar_tile, (ntile - 1) & 1);
@@ -443,10 +453,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
               ring_p += (blk & 1) ? (TC_RING_QUAD - 8u) : 8u;
             }
           }
-          if (MODE != MODE_CHILD && P.sv_himg != nullptr) {
+          if (MODE != MODE_CHILD && P.sv_himg != nullptr && stores) {
             // hidden-state tile image for the weight-gradient kernel (zeros for padding units / rows past the batch)
             const int hnc = ((nhp + 15) / 16) * 2;
-            float* sv_i = P.sv_himg + ((size_t)q * (size_t)sv_tiles + (size_t)tile) * (size_t)(32 * hnc * 32) + (size_t)(row >> 2) * hnc * 32 + (row & 3);
+            float* sv_i = P.sv_himg + ((size_t)q * (size_t)sv_tiles + (size_t)stile) * (size_t)(32 * hnc * 32) + (size_t)(srow >> 2) * hnc * 32 + (srow & 3);
             const float* hsrc = P.sv_hist != nullptr ? P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp : nullptr;
 #pragma unroll
             for (int blk = 0; blk < TC_NB; ++blk) {
@@ -466,13 +476,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           const bool save = (MODE != MODE_CHILD) && live && (P.sv_hist != nullptr);
           float* sv_h = save ? P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + sub * 4 : nullptr;
           // saved gates, tile-blocked for the reverse sweep (bwd_tc.cuh: tc_gate_index): one float4 (4 units) per quantity
-          float4* sv_g = save ? P.sv_gates + ((((size_t)q * (size_t)sv_tiles + (size_t)tile) * TC_SUB + sub) * NP) * 3 * TC_ROWS + row : nullptr;
+          float4* sv_g = save ? P.sv_gates + ((((size_t)q * (size_t)sv_tiles + (size_t)stile) * TC_SUB + sub) * NP) * 3 * TC_ROWS + srow : nullptr;
           uint32_t a_carry = a_next + (uint32_t)carry_half * hcols;
           // hidden-state tile image for the weight-gradient kernel (dw_tc.cuh: [row / 4][unit / 8][unit % 8][row % 4]);
           // rows past the end of the batch and padding units are written as zeros
           const int hnc = ((nhp + 15) / 16) * 2;
-          float* sv_i = (MODE != MODE_CHILD && P.sv_himg != nullptr)
-              ? P.sv_himg + ((size_t)q * (size_t)sv_tiles + (size_t)tile) * (size_t)(32 * hnc * 32) + (size_t)(row >> 2) * hnc * 32 + (row & 3) : nullptr;
+          float* sv_i = (MODE != MODE_CHILD && P.sv_himg != nullptr && stores)
+              ? P.sv_himg + ((size_t)q * (size_t)sv_tiles + (size_t)stile) * (size_t)(32 * hnc * 32) + (size_t)(srow >> 2) * hnc * 32 + (srow & 3) : nullptr;
           const float* bSp = bS;
           const float* hWp = hW;
   #pragma unroll 1
@@ -600,8 +610,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
     const int hrow = tid - 32 - TC_EPI_THREADS;          // rows hrow + 32 k
     uint32_t hs = 0;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-      const long long row0 = tile * TC_ROWS;
-      const int nrows = (int)((total_rows - row0 < (long long)TC_ROWS) ? (total_rows - row0) : (long long)TC_ROWS);
+      const long long row0 = tile * VR;
+      const int nrows = (int)((total_rows - row0 < (long long)VR) ? (total_rows - row0 > 0 ? total_rows - row0 : 0) : (long long)VR);
       const int ts0 = tile_q0(row0), q0 = ts0 * P.symL;
       double rlogp[TC_HEAD_ROWS], rphase[TC_HEAD_ROWS];
       int rnup[TC_HEAD_ROWS], rparent[TC_HEAD_ROWS];
