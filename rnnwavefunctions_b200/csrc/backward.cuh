@@ -741,7 +741,8 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
     }
     const long long tiles = (R + TC_ROWS - 1) / TC_ROWS;
     const BtSmem bs(nhp, m.Tsym, m.Q);
-    B.tile_rows = tc_tile_rows(R, m.num_sms);
+    // (the reverse sweep is bound by its per-site chain and the 128-row MMAs: spreading pays once a tile would be at most half live)
+    B.tile_rows = tc_tile_rows(R, m.num_sms) <= TC_ROWS / 2 ? tc_tile_rows(R, m.num_sms) : TC_ROWS;
     const long long vtiles = (tiles * TC_ROWS + B.tile_rows - 1) / B.tile_rows;
     RNNWF_COUNT_LAUNCH();
     if (van) bwd_tc_kernel<1><<<(unsigned)std::min<long long>(vtiles, m.num_sms), BT_THREADS, bs.total, st>>>(B);
