@@ -276,3 +276,41 @@ def test_tc_ungated_tensorized_cell(cuda, nh):
     for n, v in eng.views(grad).items():
         gr = Pg[n].grad
         assert float((v.double() - gr).abs().max()) / (float(gr.abs().max()) + 1e-30) < 1e-2, n
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cell,nx,ny,nh,ns", [(_lib.CELL_TENSGRU2D, 5, 4, 20, 700), (_lib.CELL_TENSGRU2D, 6, 6, 48, 200),
+                                              (_lib.CELL_VANILLA2D, 5, 4, 50, 300), (_lib.CELL_TENS2D, 4, 4, 24, 130)])
+def test_tc_row_spreading_and_on_sm_paths_match_their_fallbacks(cuda, monkeypatch, cell, nx, ny, nh, ns):
+    """The sweeps spread batches of fewer tiles than SMs over all SMs (tile_rows live rows per 128-row tile), the reverse
+    sweep keeps the horizontal half of d h on the SM and the biases' gradients come out of the weight-gradient MMAs: each of
+    these has a plain fallback (full tiles; read-modify-write in global memory; a row-sum kernel) selected by an
+    environment switch read per call -- samples and log psi must be identical, gradients equal to rounding."""
+    cplx = cell != _lib.CELL_VANILLA2D
+    eng = Engine(cell, nx, ny, num_units=nh, complex_head=cplx, u1=cplx, seed=5, precision="tc")
+    p = eng.params.cpu()
+    eng.set_weights(p + 0.1 * (torch.rand(p.shape, generator=torch.Generator().manual_seed(6)) - 0.5))
+    u = torch.rand(ns, eng.nsteps, generator=torch.Generator().manual_seed(7), dtype=torch.float32)
+    seeds = torch.randn(ns, generator=torch.Generator().manual_seed(8), dtype=torch.float64)
+
+    def run():
+        saved = eng.new_saved(ns)
+        s, lp, ph = eng.sample(ns, uniforms=u, saved=saved)
+        g = eng.backward(s, saved, seeds, seeds if cplx else None)
+        sv2 = eng.new_saved(ns)
+        lp2, ph2 = eng.logpsi(s, saved=sv2)
+        g2 = eng.backward(s, sv2, seeds, seeds if cplx else None)
+        return s.cpu(), lp.cpu(), ph.cpu(), lp2.cpu(), g.cpu().double(), g2.cpu().double()
+
+    ref = run()
+    assert torch.equal(ref[1], ref[3])
+    # (the row-sum fallback adds the biases' gradients in FP32, the MMAs round d(pre-activations) to TF32 first: 10 mantissa bits)
+    for var, tol in (("RNNWF_NO_VTILES", 2e-5), ("RNNWF_NO_HCHAIN", 2e-5), ("RNNWF_NO_BIAS_MMA", 3e-3)):
+        monkeypatch.setenv(var, "1")
+        alt = run()
+        monkeypatch.delenv(var)
+        assert torch.equal(ref[0], alt[0]) and torch.equal(ref[1], alt[1]) and torch.equal(ref[2], alt[2]), var
+        for a, b in ((ref[4], alt[4]), (ref[5], alt[5])):
+            err = float((a - b).abs().max()) / float(b.abs().max())
+            print(f"[parity] {var}: gradient differs from the default path by {err:.2e} of its largest entry (bound {tol:.0e})")
+            assert err <= tol, var
