@@ -795,15 +795,17 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
         if (njobs > 0) { RNNWF_COUNT_LAUNCH(); dw_tc_kernel<<<(unsigned)njobs, DW_THREADS, dw_smem_bytes(nhp), st>>>(D); }   // (a single-site lattice has no neighbour weights)
         if (nq > 0) {
           const int ns2 = std::max(1, std::min<int>(nsplit, (int)std::min<long long>(1 << 20, (long long)nq * tiles)));
-          RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, ns2), 128, 0, st>>>(B.dpT, 0, m.Q, nq, tiles, nhp, ns2, Gd("b"));
-          if (gated) { RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, ns2), 128, 0, st>>>(B.dpT, 1, m.Q, nq, tiles, nhp, ns2, Gd("bg")); }
+          RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, ns2, gated ? 2 : 1), 128, 0, st>>>(B.dpT, m.Q, nq, tiles, nhp, ns2, Gd("b"), gated ? Gd("bg") : nullptr);
         }
       }
       RNNWF_COUNT_LAUNCH(); head_grad_himg_kernel<<<std::min<long long>((long long)m.Q * tiles, 4LL * m.num_sms), 128, 0, st>>>(
-          himg, dlog_base, m.Q, tiles, R, nh, nhp, m.ND, Gd("dense.W"), m.complex_head ? Gd("dense_phase.W") : nullptr);
-      const long long RQ = (long long)m.Q * R;
-      G.colsum(dlog_base, m.ND, RQ, m.D, Gd("dense.b"));
-      if (m.complex_head) G.colsum(dlog_base + m.D, m.ND, RQ, 2, Gd("dense_phase.b"));
+          himg, dlog_base, m.Q, tiles, R, nh, nhp, m.ND, Gd("dense.W"), m.complex_head ? Gd("dense_phase.W") : nullptr,
+          (nh <= 124 && m.D == 2) ? Gd("dense.b") : nullptr, (nh <= 124 && m.D == 2 && m.complex_head) ? Gd("dense_phase.b") : nullptr);
+      if (!(nh <= 124 && m.D == 2)) {      // (wide models: the heads' bias gradients as column sums of d(logits))
+        const long long RQ = (long long)m.Q * R;
+        G.colsum(dlog_base, m.ND, RQ, m.D, Gd("dense.b"));
+        if (m.complex_head) G.colsum(dlog_base + m.D, m.ND, RQ, 2, Gd("dense_phase.b"));
+      }
     }
     e = cudaGetLastError();
     if (e != cudaSuccess) { err = std::string("rnnwf_backward kernels: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }

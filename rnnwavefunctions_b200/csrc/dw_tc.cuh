@@ -279,8 +279,11 @@ __global__ void __launch_bounds__(DW_THREADS, 1) dw_tc_kernel(const DwParams P) 
 
 // bias gradients from the feature-major tiles: out[j] += sum over all (site, tile, row) of src[j]
 // (nq: only the first nq sites -- dw_tc_kernel's constant-1 column covers every site that has a neighbour)
-__global__ void __launch_bounds__(128) dpt_rowsum_kernel(const float* __restrict__ dpT, int src, int Q, int nq, long long tiles, int nhp,
-                                                         int nsplit, float* __restrict__ out) {
+// blockIdx.z selects the source (ds -> out0, dg -> out1)
+__global__ void __launch_bounds__(128) dpt_rowsum_kernel(const float* __restrict__ dpT, int Q, int nq, long long tiles, int nhp,
+                                                         int nsplit, float* __restrict__ out0, float* __restrict__ out1) {
+  const int src = blockIdx.z;
+  float* const out = src ? out1 : out0;
   __shared__ float red[4];
   const int j = blockIdx.x;
   const long long nitems = (long long)nq * tiles;
@@ -293,14 +296,17 @@ __global__ void __launch_bounds__(128) dpt_rowsum_kernel(const float* __restrict
   if (threadIdx.x == 0) atomicAdd(out + j, red[0] + red[1] + red[2] + red[3]);
 }
 
-// head weight gradients from the hidden-state tile images: gH[j][d] += sum_rows h_j dlog_d
+// head weight gradients from the hidden-state tile images: gH[j][d] += sum_rows h_j dlog_d; the heads' bias gradients
+// (column sums of d(logits)) are taken along by the last four threads when they own no unit (gB / gBp non-null)
 __global__ void __launch_bounds__(128) head_grad_himg_kernel(const float* __restrict__ himg, const float* __restrict__ dlog, int Q,
                                                              long long tiles, long long rows, int nh, int nhp, int ND,
-                                                             float* __restrict__ gW, float* __restrict__ gWp) {
+                                                             float* __restrict__ gW, float* __restrict__ gWp,
+                                                             float* __restrict__ gB, float* __restrict__ gBp) {
   __shared__ float dl[TC_ROWS * 4];
   const int ncores = tc_himg_ncores(nhp);
   const int j = threadIdx.x;
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  float bsum = 0.f;
   const long long nitems = (long long)Q * tiles;
   for (long long it = blockIdx.x; it < nitems; it += gridDim.x) {
     const int q = (int)(it / tiles);
@@ -312,6 +318,11 @@ __global__ void __launch_bounds__(128) head_grad_himg_kernel(const float* __rest
       dl[i] = (r < rows && d < ND) ? dlog[((size_t)q * rows + r) * ND + d] : 0.f;
     }
     __syncthreads();
+    if (gB != nullptr && j >= 124) {
+      float s = 0.f;
+      for (int r = 0; r < TC_ROWS; ++r) s += dl[r * 4 + (j - 124)];
+      bsum += s;
+    }
     if (j < nh) {
       const float4* img = reinterpret_cast<const float4*>(himg + (size_t)it * tc_himg_floats(nhp)) + (size_t)(j >> 3) * 8 + (j & 7);
       for (int kc = 0; kc < TC_ROWS / 4; ++kc) {
@@ -328,6 +339,11 @@ __global__ void __launch_bounds__(128) head_grad_himg_kernel(const float* __rest
     // dense.W is [nh][D = 2], dense_phase.W is [nh][2]
     atomicAdd(gW + j * 2 + 0, acc[0]); atomicAdd(gW + j * 2 + 1, acc[1]);
     if (gWp != nullptr) { atomicAdd(gWp + j * 2 + 0, acc[2]); atomicAdd(gWp + j * 2 + 1, acc[3]); }
+  }
+  if (gB != nullptr && j >= 124) {
+    const int d = j - 124;                         // dense.b is [2], dense_phase.b is [2]
+    if (d < 2) atomicAdd(gB + d, bsum);
+    else if (gBp != nullptr && d < ND) atomicAdd(gBp + (d - 2), bsum);
   }
 }
 
