@@ -529,36 +529,49 @@ inline void dw_plan(const rnnwf_model_impl& m, long long R, std::vector<DwJob>& 
     const int c = (h && u) ? 0 : (h ? 1 : (u ? 2 : -1));
     if (c >= 0) cls_steps[(size_t)c * m.Q + cls_count[c]++] = q;
   }
-  // The kernel is DRAM-bound (per item one hidden-state tile and one (ds|dg|dm) tile).  Jobs k of the sources (ds, dg, dm) of
-  // one (half, class) get the SAME item ranges, and so do the two halves of a class: CTAs that walk the same (site, tile) items
-  // at the same time share the tiles through the L2 (the hidden-state tile of a half is read by its three sources, the
-  // (ds|dg|dm) tile of a source by both halves).  CTAs per (half, class): greedy on the largest items / CTAs, all sources alike.
-  struct Super { int half, cls; long long items; int n; };
-  std::vector<Super> sup;
+  // One job per CTA and at most one CTA per SM.  The jobs of a neighbour class -- the sources (ds, dg, dm) times the halves --
+  // get the same item ranges; CTAs per class: small search for the best balance.  (Measured dead end: pacing the jobs that
+  // read the same tiles so that they share them through the L2 -- ncu shows 9 % L2 hits -- made the kernel slower whatever
+  // the window: it is bound by the per-item chain of each CTA, not by the 4.2 TB/s of DRAM traffic it generates.)
+  struct Cls { int cls; long long items; int members; int n; };
+  std::vector<Cls> cl;
   const int src_lo = (m.cell == CELL_VANILLA2D) ? 2 : 0;                // vanilla cell: one unmasked source (d pre -> Wh, Wv)
   const int src_hi = (m.cell == CELL_TENS2D) ? 1 : 3;                   // un-gated tensorized cell: ds -> W only
   const int nsrc = src_hi - src_lo;
-  for (int cls = 0; cls < 3; ++cls)
-    for (int half = 0; half < 2; ++half) {
-      if ((half == 0 && cls == 2) || (half == 1 && cls == 1)) continue;   // that neighbour is absent in this class
-      const long long items = (long long)cls_count[cls] * tiles;
-      if (items > 0) sup.push_back({half, cls, items, 1});
-    }
-  jobs.clear();
-  if (sup.empty()) return;
-  int used = (int)sup.size() * nsrc;
-  while (used + nsrc <= std::max(m.num_sms, (int)sup.size() * nsrc)) {
-    size_t best = 0;
-    for (size_t k = 1; k < sup.size(); ++k)
-      if ((double)sup[k].items / sup[k].n > (double)sup[best].items / sup[best].n) best = k;
-    if (sup[best].n >= sup[best].items) break;
-    ++sup[best].n; used += nsrc;
+  for (int cls = 0; cls < 3; ++cls) {
+    const long long items = (long long)cls_count[cls] * tiles;
+    if (items > 0) cl.push_back({cls, items, nsrc * (cls == 0 ? 2 : 1), 1});   // class 0 has both halves
   }
-  // launch order: the CTAs that share tiles next to each other (sources innermost)
-  for (const Super& g : sup)
+  jobs.clear();
+  if (cl.empty()) return;
+  std::sort(cl.begin(), cl.end(), [](const Cls& a, const Cls& b) { return a.items > b.items; });
+  {
+    // the largest class takes what the others leave; the others are enumerated (at most two of them, up to 32 groups each)
+    double best = 1e300;
+    std::vector<int> bestn(cl.size(), 1);
+    const int lim1 = cl.size() > 1 ? (int)std::min<long long>(32, cl[1].items) : 1, lim2 = cl.size() > 2 ? (int)std::min<long long>(32, cl[2].items) : 1;
+    for (int n1 = 1; n1 <= lim1; ++n1)
+      for (int n2 = 1; n2 <= lim2; ++n2) {
+        int rest = m.num_sms;
+        if (cl.size() > 1) rest -= n1 * cl[1].members;
+        if (cl.size() > 2) rest -= n2 * cl[2].members;
+        const int n0 = (int)std::min<long long>(cl[0].items, std::max(1, rest / cl[0].members));
+        double worst = (double)cl[0].items / n0;
+        if (cl.size() > 1) worst = std::max(worst, (double)cl[1].items / n1);
+        if (cl.size() > 2) worst = std::max(worst, (double)cl[2].items / n2);
+        const int used = n0 * cl[0].members + (cl.size() > 1 ? n1 * cl[1].members : 0) + (cl.size() > 2 ? n2 * cl[2].members : 0);
+        if (used > std::max(m.num_sms, (int)(cl[0].members + (cl.size() > 1 ? cl[1].members : 0) + (cl.size() > 2 ? cl[2].members : 0)))) continue;
+        if (worst < best) { best = worst; bestn[0] = n0; if (cl.size() > 1) bestn[1] = n1; if (cl.size() > 2) bestn[2] = n2; }
+      }
+    for (size_t k = 0; k < cl.size(); ++k) cl[k].n = bestn[k];
+  }
+  for (const Cls& g : cl)
     for (int k = 0; k < g.n; ++k) {
       const long long b = g.items * k / g.n, e = g.items * (k + 1) / g.n;
-      for (int src = src_lo; src < src_hi; ++src) jobs.push_back({src, g.half, g.cls, (int)b, (int)(e - b)});
+      for (int half = 0; half < 2; ++half) {
+        if ((half == 0 && g.cls == 2) || (half == 1 && g.cls == 1)) continue;   // that neighbour is absent in this class
+        for (int src = src_lo; src < src_hi; ++src) jobs.push_back({src, half, g.cls, (int)b, (int)(e - b)});
+      }
     }
 }
 
