@@ -298,6 +298,13 @@ __device__ __forceinline__ void tc_issue_pass(uint32_t tmem_d, uint32_t tmem_a, 
     for (int ks = 0; ks < hc; ++ks) tc_mma_f16_ts(tmem_d, tmem_a + (uint32_t)ks * 8u, bdesc + (uint64_t)ks * B_KSTEP, idesc, ks > 0 ? 1u : acc0);
   }
 }
+// K steps [K0, K1) of a column pass, fully unrolled (see tc_issue_pass); `acc_first`: accumulate flag of step K0
+template <int K0, int K1>
+__device__ __forceinline__ void tc_issue_range(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t acc_first) {
+  constexpr uint64_t B_KSTEP = (2ull * (TC_N / 8) * 128) >> 4;
+#pragma unroll
+  for (int ks = K0; ks < K1; ++ks) tc_mma_f16_ts(tmem_d, tmem_a + (uint32_t)ks * 8u, bdesc + (uint64_t)ks * B_KSTEP, idesc, ks > K0 ? 1u : acc_first);
+}
 // the 28 accumulator columns of one epilogue thread (contiguous in TMEM, see pack_tc_kernel): three loads
 __device__ __forceinline__ void tc_ld28(uint32_t taddr, uint32_t (&d)[TC_TPS]) {
   asm volatile(

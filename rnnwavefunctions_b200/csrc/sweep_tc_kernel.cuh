@@ -43,6 +43,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
   uint64_t* const bar_tile = bars + 10;               // head warps are done with the tile's symbol table (64 arrivals)
   uint64_t* const bar_B = bars + 11;                  // [TC_STAGES] weight stage landed (complete_tx)
   uint64_t* const bar_Bfree = bars + 11 + TC_STAGES;  // [TC_STAGES] weight stage consumed (tcgen05.commit)
+  // [2] older-neighbour half of a site's operand written to TMEM (512 arrivals), alternating with the CTA's running site
+  // count: the arrival for site n + 1 comes at the START of site n's epilogue, i.e. possibly before an MMA warp has looked at
+  // site n's phase -- on one barrier that warp could then find itself two phases behind; on two, a barrier's next arrivals
+  // (site n + 2) only start after site n + 1's epilogue has begun, which needs every MMA of site n
+  uint64_t* const bar_Aold = bars + 11 + 2 * TC_STAGES;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int nhp = P.nhp, nh = P.nh, ldb = nhp + TC_JP;
@@ -62,9 +67,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
   // split precision: operands are stored scaled by powers of two (TC_SPLIT_HS, TC_SPLIT_WS) so that their lo parts stay in
   // FP16's normal range; the accumulators are scaled back (exactly) as they are read
   constexpr float HS = SPLIT ? TC_SPLIT_HS : 1.0f, DS = SPLIT ? 1.0f / (TC_SPLIT_HS * TC_SPLIT_WS) : 1.0f;
+  // Early K steps.  The operand of a site is [older-neighbour half | this sweep's previous output ("carry")] in either order;
+  // the older half is in TMEM long before the carry half is complete, and with 13 K steps over 2 x 52 columns six of them
+  // touch one half only.  The first pass of each MMA warp issues those six as soon as the older half has landed -- under the
+  // tail of the previous site's epilogue -- and the other seven once the carry half is there: the site-to-site bubble of the
+  // tensor pipe shrinks by ~2 x 6/13 of a pass.  (Double-buffered operand only: not in the split-precision regime.)
+  const bool pre = !SPLIT && CELLK != 1 && hc == 13 && !(P.debug_flags & 32);
 
   if (tid == 0) {
     mbar_init(bar_A, TC_EPI_THREADS);
+    mbar_init(bar_Aold, TC_EPI_THREADS); mbar_init(bar_Aold + 1, TC_EPI_THREADS);
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_mma + i, 1);
       mbar_init(bar_free + i, TC_EPI_THREADS);
@@ -163,10 +175,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
     const uint64_t bdesc0 = tc_desc(smem_u32(Bst), B_LBO, SBO);
     const uint32_t barA_a = smem_u32(bar_A), barB_a = smem_u32(bar_B), barF_a = smem_u32(bar_free + me);
     const uint32_t tmem_d = tmem_base + (uint32_t)me * (uint32_t)TC_N;
-    uint32_t phA = 0, nuse = 0, it0 = 0;              // operand parity; uses of this warp's buffer; passes before this site
+    uint32_t phA = 0, nsite = 0, nuse = 0, it0 = 0;   // operand parity; sites so far; uses of this warp's buffer; passes before this site
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const int q0 = tile_q0(tile * VR) * P.symL;
-      for (int q = q0; q < P.Q; ++q, it0 += (uint32_t)NP) {
+      for (int q = q0; q < P.Q; ++q, it0 += (uint32_t)NP, ++nsite) {
         TC_T0();
         const uint32_t tmem_a = SPLIT ? tmem_A0 : tmem_A0 + (uint32_t)(q & 1) * acols;
         for (int p = me; p < NP; p += 2) {
@@ -177,15 +189,30 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           TC_ACC(1); TC_EV(2);
           mbar_wait_a(barF_a, (nuse & 1u) ^ 1u); ++nuse;
           TC_ACC(2); TC_EV(3);
+          const uint64_t bd0 = bdesc0 + (uint64_t)((s * (uint32_t)L.b_bytes) >> 4);
+          const uint32_t id = (p == NP - 1) ? idesc_last : idesc;
+          const bool split_k = pre && p == me;        // this warp's first pass of the site: early K steps on the older half
+          const int ch = stepT[q].y >> 16;             // which half of this site's operand is the carry
+          if (split_k) {
+            mbar_wait_a(smem_u32(bar_Aold + (nsite & 1u)), (nsite >> 1) & 1u);
+            tc_fence_after();
+            if (leader) {
+              if (ch == 0) tc_issue_range<7, 13>(tmem_d, tmem_a, bd0, id, 0u);   // older half = columns 52..103: K steps 7..12
+              else tc_issue_range<0, 6>(tmem_d, tmem_a, bd0, id, 0u);            // older half = columns 0..51: K steps 0..5
+            }
+            __syncwarp();
+          }
           if (p == me) {
             mbar_wait_a(barA_a, phA); phA ^= 1u;
             TC_ACC(0); TC_EV(1);
           }
           tc_fence_after();
-          const uint64_t bd0 = bdesc0 + (uint64_t)((s * (uint32_t)L.b_bytes) >> 4);
           if (leader) {
-            const uint32_t id = (p == NP - 1) ? idesc_last : idesc;
-            if (hc == 13) tc_issue_pass<13>(tmem_d, tmem_a, bd0, id);
+            if (split_k) {
+              if (ch == 0) tc_issue_range<0, 7>(tmem_d, tmem_a, bd0, id, 1u);
+              else tc_issue_range<6, 13>(tmem_d, tmem_a, bd0, id, 1u);
+            }
+            else if (hc == 13) tc_issue_pass<13>(tmem_d, tmem_a, bd0, id);
             else tc_issue_pass<0>(tmem_d, tmem_a, bd0, id, hc);
             if (SPLIT) {
               const uint64_t bd1 = bdesc0 + (uint64_t)(((s + 1u) * (uint32_t)L.b_bytes) >> 4);
@@ -369,6 +396,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         if (SPLIT) store_half(onlo, a0 + acols + hcols);
         tc_wait_st();
         tc_fence_before();
+        if (pre) mbar_arrive(bar_Aold + (hs & 1u));        // (hs: the running site count this tile's first site will have)
         mbar_arrive(bar_A);
       };
       {
@@ -390,6 +418,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
         if (has_next && !SPLIT) {
           if (carry_half == 1) set_one(onext);          // the prefetched half is the horizontal one
           store_half(onext, a_next + (uint32_t)(1 - carry_half) * hcols);
+          if (pre) { tc_wait_st(); tc_fence_before(); mbar_arrive(bar_Aold + ((hs + 1u) & 1u)); }   // the MMA warps may start on this half
         }
         // split precision: the operand buffer is still being read by this site's MMAs; fetch the older-neighbour half of the
         // next operand now (its latency hides behind the column passes) and collect this site's pieces in `chi` / `clo`
