@@ -200,3 +200,23 @@ def test_tc3_gru4_c5_size_and_backward(cuda):
     for n, v in eng.views(grad).items():
         gr = Pg[n].grad
         assert float((v.double() - gr).abs().max()) <= 1e-2 * float(gr.abs().max()) + 1e-30, f"gradient of {n} differs"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("precision,tol", [("tc3", 1e-5), ("tc", 1e-3)])
+def test_gru4_c5_size_local_energies_vs_oracle(cuda, precision, tol):
+    """E_loc at the primary C5 size (8x8 unit cells = 192 atoms, 256 units) against the float64 oracle on a handful of samples
+    (193 configurations each), both tensor-core regimes at their bounds, prefix reuse on."""
+    eng = Engine(_lib.CELL_GRU4, 8, 8, num_units=256, seed=121, precision=precision)
+    g = torch.Generator().manual_seed(122)
+    p = eng.params.cpu()
+    eng.set_weights(p + 0.1 * (torch.rand(p.shape, generator=g) - 0.5))
+    ns = 4
+    saved = eng.new_saved(ns)
+    s, lp, ph = eng.sample(ns, seed=9, saved=saved)
+    e = eng.local_energies(_lib.HAM_RYDBERG, RYD_HAM, s, lp, ph, saved=saved).cpu().numpy().real
+    pos = ole.generate_kagome(8, 8)
+    nb, dist = ole.neighbouring_atoms(pos, RYD_HAM[3], 8, 8)
+    ref = ole.rydberg_local_energies(RYD_HAM[0], RYD_HAM[1], RYD_HAM[2], nb, dist, s.cpu().numpy().astype(np.int64),
+                                     oracle_logpsi_fn(eng, oracle_params(eng)))
+    assert_rel(e, ref, tol, f"GRU4 8x8x256 E_loc {precision}")
