@@ -159,6 +159,13 @@ int rnnwf_logpsi_static(rnnwf_handle h, int64_t rows, const int8_t* samples_dev,
 int rnnwf_adam_step(float* params_dev, const float* grad_dev, float* m_dev, float* v_dev, int64_t n, double lr,
                     double beta1, double beta2, double eps, int64_t t, double clip, void* stream);
 
+/* The other optimiser of 2DHeisenberg/Run_RNNWF_2DHeis.py:206-213 (`normalized_gradients`): plain gradient descent on
+ *   sign(g_i) * u_i,   u_i uniform in [0, 1)   ->   theta_i <- theta_i - lr * sign(g_i) * u_i,
+ * one fused pass.  The reference draws u with tf.random_uniform (a stream nobody can reproduce); here u_i is the library's
+ * counter-based generator at (seed, element i, step t), so every rank of a data-parallel job applies the same update from
+ * the same (seed, t) without communicating.  Call rnnwf_set_weights afterwards to repack. */
+int rnnwf_sign_sgd_step(float* params_dev, const float* grad_dev, int64_t n, double lr, uint64_t seed, int64_t t, void* stream);
+
 /* The step between the local energies and the backward: energy moments and the per-sample seeds of the reference's
  * surrogate costs, on the device (replaces the np.mean / np.var of the training loops and the cost lines
  * 1DTFIM/TrainingRNN_1DTFIM.py:157,207-208; J1J2/TrainingRNN_J1J2.py:197,281-282; 2DHeisenberg/Run_RNNWF_2DHeis.py:199,301-302;

@@ -48,6 +48,7 @@ def _load():
         "rnnwf_backward": (C.c_int, [vp, i64, vp, vp, vp, vp, vp, vp, i64, vp]),
         "rnnwf_logpsi_static": (C.c_int, [vp, i64, vp, vp, vp, vp]),
         "rnnwf_adam_step": (C.c_int, [vp, vp, vp, vp, i64, C.c_double, C.c_double, C.c_double, C.c_double, i64, C.c_double, vp]),
+        "rnnwf_sign_sgd_step": (C.c_int, [vp, vp, i64, C.c_double, u64, i64, vp]),
         "rnnwf_energy_moments": (C.c_int, [i64, vp, vp, vp, vp]),
         "rnnwf_cost_seeds": (C.c_int, [i64, vp, vp, vp, C.c_int, C.c_double, C.c_int, vp, vp, vp, vp]),
         "rnnwf_symmetry_epilogue": (C.c_int, [C.c_int, i64, vp, vp, C.POINTER(C.c_double), vp, vp, vp]),

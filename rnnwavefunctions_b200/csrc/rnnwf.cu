@@ -1159,6 +1159,25 @@ int rnnwf_adam_step(float* params_dev, const float* grad_dev, float* m_dev, floa
   return RNNWF_OK;
 }
 
+// theta <- theta - lr sign(g) u,  u = philox_uniform(seed, element, step): the `normalized_gradients` optimiser
+__global__ void __launch_bounds__(256) sign_sgd_step_kernel(float* __restrict__ p, const float* __restrict__ g, long long n, float lr,
+                                                            unsigned long long seed, uint32_t t) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float gi = g[i];
+    const float sg = (gi > 0.f) ? 1.f : (gi < 0.f ? -1.f : 0.f);
+    p[i] -= lr * sg * philox_uniform(seed, (unsigned long long)i, t);
+  }
+}
+
+int rnnwf_sign_sgd_step(float* params_dev, const float* grad_dev, int64_t n, double lr, uint64_t seed, int64_t t, void* stream) {
+  if (params_dev == nullptr || grad_dev == nullptr || n <= 0 || t < 0) return fail(RNNWF_EINVAL, "rnnwf_sign_sgd_step: null argument, n <= 0 or t < 0");
+  RNNWF_COUNT_LAUNCH();
+  sign_sgd_step_kernel<<<std::min(1184, cdiv(n, 256)), 256, 0, static_cast<cudaStream_t>(stream)>>>(params_dev, grad_dev, n, (float)lr,
+                                                                                               (unsigned long long)seed, (uint32_t)t);
+  CUDA_TRY(cudaGetLastError());
+  return RNNWF_OK;
+}
+
 // ---- energy moments and the seeds of the reference's surrogate costs ---------------------------------------
 // moments[8] = {rows, sum Re E, sum Im E, sum (Re E)^2, sum (Im E)^2, sum logP, 0, 0}: one block, FP64, fixed order
 __global__ void __launch_bounds__(1024) energy_moments_kernel(long long rows, const double* __restrict__ eloc, const double* __restrict__ logp,

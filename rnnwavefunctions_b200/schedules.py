@@ -66,6 +66,18 @@ def clip_by_value_(grad, clipvalue):
     return grad.clamp_(-clipvalue, clipvalue)
 
 
+def sign_sgd_step_(params, grad, lr, seed, t):
+    """The `normalized_gradients` optimiser of Run_RNNWF_2DHeis.py:206-213 as one fused device kernel
+    (rnnwf_sign_sgd_step): params -= lr * sign(grad) * u, u the library's counter-based uniforms at (seed, element, t) --
+    every rank applies the same update from the same (seed, t).  Device tensors, float32; call Engine.set_weights after."""
+    import ctypes as C
+    from ._lib import lib, check
+    g = grad if (grad.dtype == torch.float32 and grad.is_contiguous()) else grad.float().contiguous()
+    check(lib.rnnwf_sign_sgd_step(C.c_void_p(params.data_ptr()), C.c_void_p(g.data_ptr()), params.numel(), float(lr), int(seed), int(t),
+                                  C.c_void_p(torch.cuda.current_stream().cuda_stream)), "rnnwf_sign_sgd_step")
+    return params
+
+
 def normalized_gradient(grad, generator=None):
     """sign(g) * U(0,1), used with plain SGD (Run_RNNWF_2DHeis.py:207-213).  The uniforms come from `generator`
     (seed it identically on every rank: the update must be the same everywhere)."""

@@ -166,6 +166,28 @@ def test_fused_adam_step_matches_tf_adam_semantics(cuda):
 
 
 @pytest.mark.gpu
+def test_sign_sgd_step_is_the_normalized_gradients_update(cuda):
+    """rnnwf_sign_sgd_step against theta - lr * sign(g) * u (2DHeisenberg/Run_RNNWF_2DHeis.py:206-213) with the uniforms of the
+    library's counter-based generator reproduced on the host (helpers.philox_uniforms); entries with g = 0 stay untouched."""
+    from rnnwavefunctions_b200 import schedules
+    from helpers import philox_uniforms
+    n = 38502
+    g = torch.Generator().manual_seed(7)
+    p0 = torch.randn(n, generator=g)
+    grad = torch.randn(n, generator=g)
+    grad[::17] = 0.0
+    p = p0.clone().to(cuda)
+    for t in (0, 1, 5):
+        before = p.cpu().clone()
+        schedules.sign_sgd_step_(p, grad.to(cuda), 3e-3, seed=111, t=t)
+        u = torch.from_numpy(philox_uniforms(111, n, t + 1)[:, t].copy())
+        ref = before - (torch.tensor(3e-3, dtype=torch.float32) * torch.sign(grad)) * u
+        torch.testing.assert_close(p.cpu(), ref, rtol=0, atol=5e-7)          # (the kernel may fuse the multiply-subtract)
+        assert torch.equal(p.cpu()[::17], before[::17])                      # sign(0) = 0
+        assert float(u.min()) >= 0.0 and float(u.max()) < 1.0 and abs(float(u.mean()) - 0.5) < 0.01
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("G,with_phase", [(4, True), (16, True), (6, False), (1, True)])
 def test_symmetry_epilogue_and_seeds_match_the_reference_formulas(cuda, G, with_phase):
     """rnnwf_symmetry_epilogue / rnnwf_symmetry_seeds against 2DHeisenberg/MDComplexRNN.py:23-25,290-316 written in torch
