@@ -91,14 +91,15 @@ def J1J2_local_energies(J1, J2, Bz, samples, wf, Marshall_sign=False, periodic=F
 
 def run_J1J2(numsteps=10 ** 5, systemsize=20, J1_=1.0, J2_=0.0, Marshall_sign=False, num_units=50, num_layers=1,
              numsamples=500, learningrate=2.5e-4, seed=111):
-    """J1J2/TrainingRNN_J1J2.py:131-308 -> (meanEnergy, varEnergy).  lr schedule: lr*(1+it/5000)^-1 (:301)."""
+    """J1J2/TrainingRNN_J1J2.py:131-308 -> (meanEnergy, varEnergy).  Constant learning rate (:305-306: "without learning
+    decay"; the Tutorials copy of the script decays it as 1/(1/lr + it/10) instead)."""
     N = systemsize
     wf = RNNwavefunction(N, units=[num_units] * num_layers, seed=seed)
     ham = np.concatenate([[0.0, float(Marshall_sign)], J1_ * np.ones(N), J2_ * np.ones(N), np.zeros(N)])
     v = VMC(wf.engine, _lib.HAM_J1J2, ham, numsamples, lr=learningrate, seed=seed)
     meanEnergy, varEnergy = [], []
     for it in range(numsteps + 1):
-        m, var = v.step(lr=learningrate * (1 + it / 5000) ** (-1))
+        m, var = v.step(lr=learningrate)
         e = v.last["eloc"]
         meanEnergy.append(complex(m))
         varEnergy.append(float(e.real.var(unbiased=False)))   # the reference takes the variance of the real part (:282)

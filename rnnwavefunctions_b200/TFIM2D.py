@@ -3,7 +3,7 @@ Reference: 2DTFIM_2DRNN/MDRNNcell.py, RNNwavefunction.py, Training2DRNN_2DTFIM.p
 import numpy as np
 import torch
 
-from . import _lib
+from . import _lib, schedules
 from .compat import Handle, Placeholder, Session, find_wf, to_numpy
 from .engine import Engine
 from .vmc import VMC
@@ -61,7 +61,7 @@ def run_2DTFIM(numsteps=2 * 10 ** 4, systemsize_x=5, systemsize_y=5, Bx=+2, num_
     v = VMC(wf.engine, _lib.HAM_TFIM2D, ham, numsamples, lr=learningrate, seed=seed)
     meanEnergy, varEnergy = [], []
     for it in range(numsteps + 1):
-        m, var = v.step(lr=learningrate * (1 + it / 5000) ** (-1))
+        m, var = v.step(lr=schedules.lr_tfim2d_2drnn(it, learningrate))
         meanEnergy.append(float(m.real))
         varEnergy.append(float(var))
         if it % 10 == 0:

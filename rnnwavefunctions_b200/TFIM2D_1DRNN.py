@@ -4,7 +4,7 @@ Reference: 2DTFIM_1DRNN/RNNwavefunction.py, Training1DRNN_2DTFIM.py, run_2dTFIM.
 import numpy as np
 import torch
 
-from . import _lib
+from . import _lib, schedules
 from .compat import Handle, Placeholder, Session, find_wf, to_numpy
 from .engine import Engine
 from .vmc import VMC
@@ -53,14 +53,14 @@ def Ising2D_local_energies(Jz, Bx, Nx, Ny, samples, queue_samples=None, log_prob
 
 def run_2DTFIM(numsteps=2 * 10 ** 4, systemsize_x=5, systemsize_y=5, Bx=+2, num_units=50, num_layers=1, numsamples=500,
                learningrate=1e-3, seed=333):
-    """2DTFIM_1DRNN/Training1DRNN_2DTFIM.py:85-233 -> (meanEnergy, varEnergy).  lr schedule lr*(1+it/5000)^-1 (:229)."""
+    """2DTFIM_1DRNN/Training1DRNN_2DTFIM.py:85-233 -> (meanEnergy, varEnergy).  lr schedule 1/(1/lr + it/10) (:229)."""
     Nx, Ny = systemsize_x, systemsize_y
     wf = RNNwavefunction(Nx, Ny, units=[num_units] * num_layers, seed=seed)
     ham = np.concatenate([[float(Bx)], np.ones(Nx * Ny)])
     v = VMC(wf.engine, _lib.HAM_TFIM2D, ham, numsamples, lr=learningrate, seed=seed)
     meanEnergy, varEnergy = [], []
     for it in range(numsteps + 1):
-        m, var = v.step(lr=learningrate * (1 + it / 5000) ** (-1))
+        m, var = v.step(lr=schedules.lr_tfim2d_1drnn(it, learningrate))
         meanEnergy.append(float(m.real))
         varEnergy.append(float(var))
         if it % 10 == 0:

@@ -145,3 +145,30 @@ def test_2dtfim_1drnn_twin(cuda, layers):
     assert_rel(E, ref, 1e-5, f"2DTFIM_1DRNN E_loc, {layers} layer(s)")
     lp = Session().run(lpt, feed_dict={inputs: samples})
     assert_rel(lp, oracle_run(wf.engine, P, samples=samples)["logp"].detach().numpy(), 1e-5, "2DTFIM_1DRNN log P")
+
+
+@pytest.mark.gpu
+def test_training_twins_feed_the_reference_learning_rates(cuda, monkeypatch):
+    """The learning rate each training twin hands to the optimiser step, iteration by iteration, is the reference script's:
+    1DTFIM/TrainingRNN_1DTFIM.py:222 and J1J2/TrainingRNN_J1J2.py:306 constant, 2DTFIM_2DRNN/Training2DRNN_2DTFIM.py:228
+    lr (1 + it/5000)^-1, 2DTFIM_1DRNN/Training1DRNN_2DTFIM.py:229 1 / (1/lr + it/10)."""
+    import io, contextlib
+    from rnnwavefunctions_b200 import TFIM2D, TFIM2D_1DRNN, J1J2, vmc
+    seen = []
+    real_step = vmc.VMC.step
+
+    def spy(self, uniforms=None, lr=None, update=True):
+        seen.append(self.lr if lr is None else lr)
+        return real_step(self, uniforms=uniforms, lr=lr, update=update)
+
+    monkeypatch.setattr(vmc.VMC, "step", spy)
+    its = np.arange(4)
+    for fn, kw, want in (
+            (TFIM1D.run_1DTFIM, dict(systemsize=6, num_units=6, numsamples=20, learningrate=5e-3), 5e-3 + 0 * its),
+            (J1J2.run_J1J2, dict(systemsize=6, J2_=0.2, num_units=6, numsamples=20, learningrate=2.5e-4), 2.5e-4 + 0 * its),
+            (TFIM2D.run_2DTFIM, dict(systemsize_x=3, systemsize_y=3, num_units=6, numsamples=20, learningrate=5e-3), 5e-3 / (1 + its / 5000)),
+            (TFIM2D_1DRNN.run_2DTFIM, dict(systemsize_x=3, systemsize_y=3, num_units=6, numsamples=20, learningrate=1e-3), 1 / (1 / 1e-3 + its / 10))):
+        seen.clear()
+        with contextlib.redirect_stdout(io.StringIO()):
+            fn(numsteps=3, **kw)
+        np.testing.assert_allclose(np.array(seen, dtype=np.float64), want, rtol=1e-12)
