@@ -22,7 +22,7 @@
 #include "bwd_tc4.cuh"
 
 namespace rnnwf {
-cudaError_t g1_bwd_launch(const G1BwdParams& B, int grid, cudaStream_t st);     // gru1d_inst.cu
+cudaError_t g1_bwd_launch(const G1BwdParams& B, int rg, int grid, cudaStream_t st);     // gru1d_inst.cu
 
 // ------------------------------------------------------------------------------------------------
 // generic FP32 GEMM tiles (64x64x16, 256 threads, 4x4 per thread)
@@ -680,7 +680,8 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
       B.dx_in = (l < Ls - 1) ? dh + (long long)((l + 1) & 1) * NR * nhp : nullptr;
       B.dx_out = (l > 0) ? dh + (long long)(l & 1) * NR * nhp : nullptr;
       RNNWF_COUNT_LAUNCH();
-      e = g1_bwd_launch(B, (int)std::min<long long>((R + G1_ROWS - 1) / G1_ROWS, (long long)m.num_sms), st);
+      const int rg = std::getenv("RNNWF_NO_VTILES") == nullptr ? g1_pick_rg(R, m.num_sms) : G1_RG;    // narrow tiles for a training batch
+      e = g1_bwd_launch(B, rg, (int)std::min<long long>((R + 8 * rg - 1) / (8 * rg), 2LL * m.num_sms), st);
       if (e != cudaSuccess) { err = std::string("rnnwf_backward 1D GRU reverse sweep: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
     }
     const long long hstride = (long long)Ls * R * nhp;       // between consecutive sites of one layer in the saved history

@@ -18,10 +18,35 @@
 
 namespace rnnwf {
 
-constexpr int G1_ROWS = 64;          // rows per tile
-constexpr int G1_RG = 8;             // rows per thread
-constexpr int G1_LDH = G1_ROWS + 4;  // row stride of the [unit][row] hidden-state arrays (16-byte aligned, de-phased banks)
+// Rows per thread RG (template parameter of the sweeps) and rows per tile 8 RG.  RG = 8: the connected-configuration sweep and
+// large batches (48 FMA per 5 shared-memory loads).  RG = 2: sampling / evaluation / reverse sweeps of a training batch
+// (500 samples are 8 tiles of 64 rows but 32 of 16: four times the SMs, a quarter of the per-site chain per tile).
+constexpr int G1_ROWS = 64;          // rows per tile at RG = 8
+constexpr int G1_RG = 8;             // rows per thread (wide tiles)
+constexpr int G1_RG_SMALL = 2;       // rows per thread (small batches)
 constexpr int G1_MAXL = 4;
+__host__ __device__ constexpr int g1_ldh(int rows) { return rows + 4; }   // row stride of the [unit][row] arrays (16-byte aligned, de-phased banks)
+// rows per thread for a batch: the narrow tiles while they still fit one wave of CTAs
+// (measured at 500 samples: RG = 2 -> 0.65 ms per C1 step, RG = 4 -> 0.76, RG = 8 -> 0.94; RG = 1 would leave half a warp of
+//  head lanes, which the warp shuffles of the heads do not allow)
+inline int g1_pick_rg(long long rows, int num_sms) { return (rows + 8 * G1_RG_SMALL - 1) / (8 * G1_RG_SMALL) <= 2LL * num_sms ? G1_RG_SMALL : G1_RG; }
+// RG consecutive floats of a [unit][row] array (aligned: RG * 4 bytes)
+template <int RG>
+__device__ __forceinline__ void g1_load_rows(const float* p, float (&a)[RG]) {
+  if constexpr (RG == 8) {
+    const float4 a0 = *reinterpret_cast<const float4*>(p), a1 = *reinterpret_cast<const float4*>(p + 4);
+    a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+  } else if constexpr (RG == 4) {
+    const float4 a0 = *reinterpret_cast<const float4*>(p);
+    a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w;
+  } else if constexpr (RG == 2) {
+    const float2 a0 = *reinterpret_cast<const float2*>(p);
+    a[0] = a0.x; a[1] = a0.y;
+  } else {
+#pragma unroll
+    for (int i = 0; i < RG; ++i) a[i] = p[i];
+  }
+}
 
 // packed parameter image (floats), built by gru1d_pack_kernel, copied verbatim into shared memory:
 //   per layer l: Wh [nh][3][njp] (r, u, candidate-hidden from h_{t-1});  l >= 1: Wx [nh][3][njp] (r, u, candidate-input from
@@ -31,7 +56,7 @@ struct G1Layout {
   int njp, off_wh[G1_MAXL], off_wx[G1_MAXL], off_b[G1_MAXL], off_headw, off_headb, pack_floats;
   // shared memory beyond the parameter image
   int off_H, off_sym, off_part, total_bytes;
-  __host__ __device__ G1Layout(int nh, int L, int N) {
+  __host__ __device__ G1Layout(int nh, int L, int N, int rows = G1_ROWS) {
     njp = (nh + 7) & ~7;
     int o = 0;
     for (int l = 0; l < G1_MAXL; ++l) { off_wh[l] = off_wx[l] = off_b[l] = 0; }
@@ -44,9 +69,9 @@ struct G1Layout {
     off_headb = o; o += 4;
     pack_floats = (o + 3) & ~3;
     int b = pack_floats * 4;
-    off_H = b;    b += L * nh * G1_LDH * 4;
-    off_part = b; b += G1_ROWS * 4 * 4;
-    off_sym = b;  b += ((N * G1_ROWS + 15) & ~15);
+    off_H = b;    b += L * nh * g1_ldh(rows) * 4;
+    off_part = b; b += rows * 4 * 4;
+    off_sym = b;  b += ((N * rows + 15) & ~15);
     total_bytes = b;
   }
 };
@@ -89,18 +114,20 @@ __global__ void gru1d_pack_kernel(const G1PackSrc S, int nh, int L, int N, int D
 
 __device__ __forceinline__ float g1_sigmoid(float x) { return 1.0f / (1.0f + expf(-x)); }
 
-template <int MODE>
+template <int MODE, int RG>
 __global__ void __launch_bounds__(256) gru1d_sweep_kernel(const SweepParams P) {
+  constexpr int ROWS = 8 * RG, LDH = g1_ldh(ROWS);
+  static_assert(2 * ROWS % 32 == 0, "the head lanes (two per row) must be whole warps: they exchange partial sums with warp shuffles");
   extern __shared__ __align__(16) unsigned char g1_smem[];
   const int nh = P.nh, L = P.symL, N = P.Tsym;
-  const G1Layout Y(nh, L, N);
+  const G1Layout Y(nh, L, N, ROWS);
   const int njp = Y.njp;
   float* const Wsm = reinterpret_cast<float*>(g1_smem);
-  float* const Hs = reinterpret_cast<float*>(g1_smem + Y.off_H);            // [L][nh][G1_LDH]
+  float* const Hs = reinterpret_cast<float*>(g1_smem + Y.off_H);            // [L][nh][LDH]
   uint8_t* const symS = g1_smem + Y.off_sym;                               // [N][64]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int rg = lane >> 2, up = warp * 4 + (lane & 3);
-  const int r0 = rg * G1_RG, j0 = 2 * up;
+  const int r0 = rg * RG, j0 = 2 * up;
   const bool jok0 = j0 < nh, jok1 = j0 + 1 < nh;
   const bool act = j0 < njp;           // warps beyond the last unit pair only serve as head lanes
 
@@ -108,14 +135,14 @@ __global__ void __launch_bounds__(256) gru1d_sweep_kernel(const SweepParams P) {
     reinterpret_cast<float4*>(Wsm)[i] = __ldg(reinterpret_cast<const float4*>(P.g1_pack) + i);
 
   const long long total_rows = (P.rows_dev != nullptr) ? (long long)(*P.rows_dev) : P.rows;
-  const long long ntiles = (total_rows + G1_ROWS - 1) / G1_ROWS;
+  const long long ntiles = (total_rows + ROWS - 1) / ROWS;
   // head threads: two lanes per row
   const int hrow = tid >> 1, hhalf = tid & 1;
-  const bool head_thread = tid < 2 * G1_ROWS;
+  const bool head_thread = tid < 2 * ROWS;
 
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    const long long row0 = tile * G1_ROWS;
-    const int nrows = (int)((total_rows - row0 < (long long)G1_ROWS) ? (total_rows - row0) : (long long)G1_ROWS);
+    const long long row0 = tile * ROWS;
+    const int nrows = (int)((total_rows - row0 < (long long)ROWS) ? (total_rows - row0) : (long long)ROWS);
     int ts0 = 0;
     if (MODE == MODE_CHILD && P.par_hist != nullptr) {
       const Child c0 = P.children[row0];
@@ -127,22 +154,22 @@ __global__ void __launch_bounds__(256) gru1d_sweep_kernel(const SweepParams P) {
       for (int idx = tid; idx < nrows * N; idx += blockDim.x) {
         const int r = idx / N, t = idx - r * N;
         const long long src = (MODE == MODE_CHILD) ? (long long)P.children[row0 + r].parent : row0 + r;
-        symS[t * G1_ROWS + r] = (uint8_t)(P.cfg_in[src * N + t] & 1);
+        symS[t * ROWS + r] = (uint8_t)(P.cfg_in[src * N + t] & 1);
       }
     }
-    for (int idx = tid; idx < L * nh * G1_LDH; idx += blockDim.x) Hs[idx] = 0.f;
+    for (int idx = tid; idx < L * nh * LDH; idx += blockDim.x) Hs[idx] = 0.f;
     __syncthreads();
     if (MODE == MODE_CHILD) {
       if (tid < nrows) {
         const Child ch = P.children[row0 + tid];
-        symS[ch.ta * G1_ROWS + tid] ^= 1;
-        if (ch.tb >= 0) symS[ch.tb * G1_ROWS + tid] ^= 1;
+        symS[ch.ta * ROWS + tid] ^= 1;
+        if (ch.tb >= 0) symS[ch.tb * ROWS + tid] ^= 1;
       }
       if (ts0 > 0) {       // prefix reuse: hidden states of every layer after site ts0 - 1, from the parents' saved history
         for (int idx = tid; idx < nrows * L * nh; idx += blockDim.x) {
           const int r = idx / (L * nh), rem = idx - r * (L * nh), l = rem / nh, j = rem - l * nh;
           const int par = P.children[row0 + r].parent;
-          Hs[(l * nh + j) * G1_LDH + r] = __ldg(P.par_hist + ((size_t)((ts0 - 1) * L + l) * (size_t)P.par_rows + (size_t)par) * P.nhp + j);
+          Hs[(l * nh + j) * LDH + r] = __ldg(P.par_hist + ((size_t)((ts0 - 1) * L + l) * (size_t)P.par_rows + (size_t)par) * P.nhp + j);
         }
       }
       __syncthreads();
@@ -154,34 +181,33 @@ __global__ void __launch_bounds__(256) gru1d_sweep_kernel(const SweepParams P) {
     if (head_thread && hrow < nrows && MODE == MODE_CHILD) {
       const Child ch = P.children[row0 + hrow];
       rparent = ch.parent; rcoef = ch.coef;
-      for (int t = 0; t < ts0; ++t) rnup += symS[t * G1_ROWS + hrow];
+      for (int t = 0; t < ts0; ++t) rnup += symS[t * ROWS + hrow];
     }
 
     for (int t = ts0; t < N; ++t) {
       for (int l = 0; l < L; ++l) {
         const int q = t * L + l;
-        float* const Hl = Hs + (size_t)l * nh * G1_LDH;
+        float* const Hl = Hs + (size_t)l * nh * LDH;
         const float* const Wh = Wsm + Y.off_wh[l];
         const float* const Wx = Wsm + Y.off_wx[l];
         const float* const Bl = Wsm + Y.off_b[l];
         // accumulators: [row][unit][r, u, ch, cx]
-        float ar[G1_RG][2], au[G1_RG][2], ach[G1_RG][2], acx[G1_RG][2];
+        float ar[RG][2], au[RG][2], ach[RG][2], acx[RG][2];
 #pragma unroll
-        for (int i = 0; i < G1_RG; ++i)
+        for (int i = 0; i < RG; ++i)
 #pragma unroll
           for (int e = 0; e < 2; ++e) { ar[i][e] = 0.f; au[i][e] = 0.f; ach[i][e] = 0.f; acx[i][e] = 0.f; }
         // ---- hidden part: [r, u, ch] += h_{t-1} Wh
         if (t > 0 && act) {
 #pragma unroll 2
           for (int k = 0; k < nh; ++k) {
-            const float4 a0 = *reinterpret_cast<const float4*>(Hl + k * G1_LDH + r0);
-            const float4 a1 = *reinterpret_cast<const float4*>(Hl + k * G1_LDH + r0 + 4);
-            const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            float a[RG];
+            g1_load_rows<RG>(Hl + k * LDH + r0, a);
             const float2 wr = *reinterpret_cast<const float2*>(Wh + (k * 3 + 0) * njp + j0);
             const float2 wu = *reinterpret_cast<const float2*>(Wh + (k * 3 + 1) * njp + j0);
             const float2 wc = *reinterpret_cast<const float2*>(Wh + (k * 3 + 2) * njp + j0);
 #pragma unroll
-            for (int i = 0; i < G1_RG; ++i) {
+            for (int i = 0; i < RG; ++i) {
               ar[i][0] = fmaf(a[i], wr.x, ar[i][0]); ar[i][1] = fmaf(a[i], wr.y, ar[i][1]);
               au[i][0] = fmaf(a[i], wu.x, au[i][0]); au[i][1] = fmaf(a[i], wu.y, au[i][1]);
               ach[i][0] = fmaf(a[i], wc.x, ach[i][0]); ach[i][1] = fmaf(a[i], wc.y, ach[i][1]);
@@ -190,17 +216,16 @@ __global__ void __launch_bounds__(256) gru1d_sweep_kernel(const SweepParams P) {
         }
         // ---- input part of the layers above the first: [r, u, cx] += h^{l-1}_t Wx
         if (l > 0 && act) {
-          const float* const Hb = Hs + (size_t)(l - 1) * nh * G1_LDH;
+          const float* const Hb = Hs + (size_t)(l - 1) * nh * LDH;
 #pragma unroll 2
           for (int k = 0; k < nh; ++k) {
-            const float4 a0 = *reinterpret_cast<const float4*>(Hb + k * G1_LDH + r0);
-            const float4 a1 = *reinterpret_cast<const float4*>(Hb + k * G1_LDH + r0 + 4);
-            const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            float a[RG];
+            g1_load_rows<RG>(Hb + k * LDH + r0, a);
             const float2 wr = *reinterpret_cast<const float2*>(Wx + (k * 3 + 0) * njp + j0);
             const float2 wu = *reinterpret_cast<const float2*>(Wx + (k * 3 + 1) * njp + j0);
             const float2 wc = *reinterpret_cast<const float2*>(Wx + (k * 3 + 2) * njp + j0);
 #pragma unroll
-            for (int i = 0; i < G1_RG; ++i) {
+            for (int i = 0; i < RG; ++i) {
               ar[i][0] = fmaf(a[i], wr.x, ar[i][0]); ar[i][1] = fmaf(a[i], wr.y, ar[i][1]);
               au[i][0] = fmaf(a[i], wu.x, au[i][0]); au[i][1] = fmaf(a[i], wu.y, au[i][1]);
               acx[i][0] = fmaf(a[i], wc.x, acx[i][0]); acx[i][1] = fmaf(a[i], wc.y, acx[i][1]);
@@ -208,18 +233,18 @@ __global__ void __launch_bounds__(256) gru1d_sweep_kernel(const SweepParams P) {
           }
         }
         // own previous state of the thread's units (read before anybody overwrites it)
-        float hold[G1_RG][2];
+        float hold[RG][2];
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
           const bool ok = (e == 0) ? jok0 : jok1;
           if (ok) {
-            const float4 h0 = *reinterpret_cast<const float4*>(Hl + (j0 + e) * G1_LDH + r0);
-            const float4 h1 = *reinterpret_cast<const float4*>(Hl + (j0 + e) * G1_LDH + r0 + 4);
-            hold[0][e] = h0.x; hold[1][e] = h0.y; hold[2][e] = h0.z; hold[3][e] = h0.w;
-            hold[4][e] = h1.x; hold[5][e] = h1.y; hold[6][e] = h1.z; hold[7][e] = h1.w;
+            float hv[RG];
+            g1_load_rows<RG>(Hl + (j0 + e) * LDH + r0, hv);
+#pragma unroll
+            for (int i = 0; i < RG; ++i) hold[i][e] = hv[i];
           } else {
 #pragma unroll
-            for (int i = 0; i < G1_RG; ++i) hold[i][e] = 0.f;
+            for (int i = 0; i < RG; ++i) hold[i][e] = 0.f;
           }
         }
         __syncthreads();      // everybody has read H^l_{t-1}
@@ -229,11 +254,11 @@ __global__ void __launch_bounds__(256) gru1d_sweep_kernel(const SweepParams P) {
         const bool save = (MODE != MODE_CHILD) && (P.sv_hist != nullptr);
         if (act) {
 #pragma unroll
-        for (int i = 0; i < G1_RG; ++i) {
+        for (int i = 0; i < RG; ++i) {
           const int r = r0 + i;
           float xr[2] = {0.f, 0.f}, xu[2] = {0.f, 0.f}, xc[2] = {acx[i][0], acx[i][1]};
           if (l == 0 && t > 0) {     // one-hot input: a row of the input table (the first input is the zero vector)
-            const float* X0 = Wx + (int)(symS[(t - 1) * G1_ROWS + r] & 1) * 3 * njp + j0;
+            const float* X0 = Wx + (int)(symS[(t - 1) * ROWS + r] & 1) * 3 * njp + j0;
             const float2 v0 = *reinterpret_cast<const float2*>(X0), v1 = *reinterpret_cast<const float2*>(X0 + njp), v2 = *reinterpret_cast<const float2*>(X0 + 2 * njp);
             xr[0] = v0.x; xr[1] = v0.y; xu[0] = v1.x; xu[1] = v1.y; xc[0] = v2.x; xc[1] = v2.y;
           }
@@ -248,8 +273,8 @@ __global__ void __launch_bounds__(256) gru1d_sweep_kernel(const SweepParams P) {
             hn[e] = (1.f - ugate) * c + ugate * hold[i][e];
             gsv[e] = make_float4(rgate, ugate, c, hh);
           }
-          if (jok0) Hl[j0 * G1_LDH + r] = hn[0];
-          if (jok1) Hl[(j0 + 1) * G1_LDH + r] = hn[1];
+          if (jok0) Hl[j0 * LDH + r] = hn[0];
+          if (jok1) Hl[(j0 + 1) * LDH + r] = hn[1];
           if (save && r < nrows) {       // (padding units of the saved history are written as zeros)
             const size_t base = (size_t)q * (size_t)P.sv_rows + (size_t)(row0 + r);
             *reinterpret_cast<float2*>(P.sv_hist + base * P.nhp + j0) = make_float2(jok0 ? hn[0] : 0.f, jok1 ? hn[1] : 0.f);
@@ -265,11 +290,11 @@ __global__ void __launch_bounds__(256) gru1d_sweep_kernel(const SweepParams P) {
 
       // ---- heads on the top layer's state: two lanes per row
       if (head_thread) {
-        const float* const Ht = Hs + (size_t)(L - 1) * nh * G1_LDH;
+        const float* const Ht = Hs + (size_t)(L - 1) * nh * LDH;
         const float* const hw = Wsm + Y.off_headw;
         float lg0 = 0.f, lg1 = 0.f, lg2 = 0.f, lg3 = 0.f;
         for (int j = hhalf; j < nh; j += 2) {
-          const float hv = Ht[j * G1_LDH + hrow];
+          const float hv = Ht[j * LDH + hrow];
           const float4 w = *reinterpret_cast<const float4*>(hw + j * 4);
           lg0 = fmaf(hv, w.x, lg0); lg1 = fmaf(hv, w.y, lg1); lg2 = fmaf(hv, w.z, lg2); lg3 = fmaf(hv, w.w, lg3);
         }
@@ -295,9 +320,9 @@ __global__ void __launch_bounds__(256) gru1d_sweep_kernel(const SweepParams P) {
                                                     : philox_uniform(P.seed, P.row_offset + (unsigned long long)(row0 + hrow), (uint32_t)t);
             const double target = (double)u * ((double)p0 + (double)p1);
             sy = ((double)p0 <= target) ? 1 : 0;
-            symS[t * G1_ROWS + hrow] = (uint8_t)sy;
+            symS[t * ROWS + hrow] = (uint8_t)sy;
           } else {
-            sy = symS[t * G1_ROWS + hrow];
+            sy = symS[t * ROWS + hrow];
           }
           rlogp += log((double)(sy ? p1 : p0));
           if (P.complex_head) {
@@ -333,7 +358,7 @@ __global__ void __launch_bounds__(256) gru1d_sweep_kernel(const SweepParams P) {
         if (P.out_logp != nullptr) P.out_logp[row0 + hrow] = rlogp;
         if (P.out_phase != nullptr) P.out_phase[row0 + hrow] = rphase;
         if (MODE == MODE_SAMPLE && P.cfg_out != nullptr)
-          for (int t = 0; t < N; ++t) P.cfg_out[(size_t)(row0 + hrow) * N + t] = (int8_t)symS[t * G1_ROWS + hrow];
+          for (int t = 0; t < N; ++t) P.cfg_out[(size_t)(row0 + hrow) * N + t] = (int8_t)symS[t * ROWS + hrow];
       }
     }
   }  // tiles

@@ -21,7 +21,7 @@ namespace rnnwf {
 struct G1BwdLayout {
   int njp, off_wh[G1_MAXL], off_wx[G1_MAXL], off_headw, off_headb, pack_floats;
   int off_dH, off_dX, off_DP, off_DL, total_bytes;
-  __host__ __device__ G1BwdLayout(int nh, int L) {
+  __host__ __device__ G1BwdLayout(int nh, int L, int rows = G1_ROWS) {
     njp = (nh + 7) & ~7;
     int o = 0;
     for (int l = 0; l < G1_MAXL; ++l) { off_wh[l] = off_wx[l] = 0; }
@@ -34,10 +34,10 @@ struct G1BwdLayout {
     pack_floats = (o + 3) & ~3;
     // shared memory of one launch (one layer): [WhT | WxT | headW | headB] then the work arrays
     int b = (2 * nh * 3 * njp + nh * 4 + 4) * 4;
-    off_dH = b; b += njp * G1_LDH * 4;           // d h^l from site t+1
+    off_dH = b; b += njp * g1_ldh(rows) * 4;     // d h^l from site t+1
     off_dX = b;                                  // (unused: the hand-over between layers is in global memory)
-    off_DP = b; b += 4 * nh * G1_LDH * 4;        // dr, du, dci, dch of the current site: [4][unit][row]
-    off_DL = b; b += G1_ROWS * 16;               // d(logits) of the current site
+    off_DP = b; b += 4 * nh * g1_ldh(rows) * 4;  // dr, du, dci, dch of the current site: [4][unit][row]
+    off_DL = b; b += rows * 16;                  // d(logits) of the current site
     total_bytes = b;
   }
 };
@@ -93,22 +93,24 @@ struct G1BwdParams {
   float* dx_out;               // [N][R][nhp]: d h^{l-1}_t for the layer below (null for the first layer)
 };
 
-template <int UNUSED = 0>
+template <int RG>
 __global__ void __launch_bounds__(256) gru1d_bwd_kernel(const G1BwdParams P) {
+  constexpr int ROWS = 8 * RG, LDH = g1_ldh(ROWS);
+  static_assert(2 * ROWS % 32 == 0, "the head lanes (two per row) must be whole warps");
   extern __shared__ __align__(16) unsigned char g1b_smem[];
   const int nh = P.nh, L = P.L, N = P.N, l = P.layer;
-  const G1BwdLayout Y(nh, L);
+  const G1BwdLayout Y(nh, L, ROWS);
   const int njp = Y.njp;
   float* const Wsm = reinterpret_cast<float*>(g1b_smem);
-  float* const dH = reinterpret_cast<float*>(g1b_smem + Y.off_dH);     // [njp][G1_LDH]
-  float* const DP = reinterpret_cast<float*>(g1b_smem + Y.off_DP);     // [4][nh][G1_LDH]
+  float* const dH = reinterpret_cast<float*>(g1b_smem + Y.off_dH);     // [njp][LDH]
+  float* const DP = reinterpret_cast<float*>(g1b_smem + Y.off_DP);     // [4][nh][LDH]
   float4* const DL = reinterpret_cast<float4*>(g1b_smem + Y.off_DL);   // [64]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int rg = lane >> 2, up = warp * 4 + (lane & 3);
-  const int r0 = rg * G1_RG, j0 = 2 * up;
+  const int r0 = rg * RG, j0 = 2 * up;
   const bool jok0 = j0 < nh, jok1 = j0 + 1 < nh, act = j0 < njp;
   const int hrow = tid >> 1, hhalf = tid & 1;
-  const bool head_thread = tid < 2 * G1_ROWS;
+  const bool head_thread = tid < 2 * ROWS;
   const long long R = P.R;
 
   const int wsz = nh * 3 * njp;
@@ -121,14 +123,14 @@ __global__ void __launch_bounds__(256) gru1d_bwd_kernel(const G1BwdParams P) {
     if (l > 0) reinterpret_cast<float4*>(WxT)[i] = __ldg(reinterpret_cast<const float4*>(P.packT + Y.off_wx[l]) + i);
   }
   for (int i = tid; i < nh * 4 + 4; i += blockDim.x) hw[i] = __ldg(P.packT + Y.off_headw + i);
-  float* const DPr = DP, *const DPu = DP + nh * G1_LDH, *const DPci = DP + 2 * nh * G1_LDH, *const DPch = DP + 3 * nh * G1_LDH;
+  float* const DPr = DP, *const DPu = DP + nh * LDH, *const DPci = DP + 2 * nh * LDH, *const DPch = DP + 3 * nh * LDH;
 
-  const long long ntiles = (R + G1_ROWS - 1) / G1_ROWS;
+  const long long ntiles = (R + ROWS - 1) / ROWS;
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    const long long row0 = tile * G1_ROWS;
-    const int nrows = (int)((R - row0 < (long long)G1_ROWS) ? (R - row0) : (long long)G1_ROWS);
+    const long long row0 = tile * ROWS;
+    const int nrows = (int)((R - row0 < (long long)ROWS) ? (R - row0) : (long long)ROWS);
     __syncthreads();
-    for (int i = tid; i < njp * G1_LDH; i += blockDim.x) dH[i] = 0.f;
+    for (int i = tid; i < njp * LDH; i += blockDim.x) dH[i] = 0.f;
     // ups before the current site, per row (head lane 0 of the row)
     int nup = 0;
     if (head_thread && hhalf == 0 && hrow < nrows)
@@ -193,11 +195,11 @@ __global__ void __launch_bounds__(256) gru1d_bwd_kernel(const G1BwdParams P) {
       {
         const int q = t * L + l;
         float* const dHl = dH;
-        float keep[G1_RG][2];       // u * d h: the direct path into d h^l_{t-1}
+        float keep[RG][2];       // u * d h: the direct path into d h^l_{t-1}
         // ---- A: d(pre-activations) of this thread's units
         if (act) {
 #pragma unroll
-          for (int i = 0; i < G1_RG; ++i) {
+          for (int i = 0; i < RG; ++i) {
             const int r = r0 + i;
             const bool live = r < nrows;
             const size_t base = (size_t)q * (size_t)R + (size_t)(row0 + r);
@@ -207,7 +209,7 @@ __global__ void __launch_bounds__(256) gru1d_bwd_kernel(const G1BwdParams P) {
             for (int e = 0; e < 2; ++e) {
               const int j = j0 + e;
               const bool ok = (e == 0 ? jok0 : jok1) && live;
-              float dhp = dHl[j * G1_LDH + r];
+              float dhp = dHl[j * LDH + r];
               if (l < L - 1) { if (live) dhp += __ldg(P.dx_in + ((size_t)t * (size_t)R + (size_t)(row0 + r)) * P.nhp + j); }
               else if (j < nh) {
                 const float4 dl = DL[r];
@@ -228,7 +230,7 @@ __global__ void __launch_bounds__(256) gru1d_bwd_kernel(const G1BwdParams P) {
               dch[e] = dcp * g.x;
               keep[i][e] = dhp * g.y;
               if (e == 0 ? jok0 : jok1) {
-                DPr[j * G1_LDH + r] = dr[e]; DPu[j * G1_LDH + r] = du[e]; DPci[j * G1_LDH + r] = dci[e]; DPch[j * G1_LDH + r] = dch[e];
+                DPr[j * LDH + r] = dr[e]; DPu[j * LDH + r] = du[e]; DPci[j * LDH + r] = dci[e]; DPch[j * LDH + r] = dch[e];
               }
             }
             if (live) {
@@ -251,25 +253,23 @@ __global__ void __launch_bounds__(256) gru1d_bwd_kernel(const G1BwdParams P) {
         __syncthreads();
         // ---- B: gradients with respect to the inputs of this cell
         if (act && (t > 0 || l > 0)) {
-          float at[G1_RG][2], ab[G1_RG][2];      // d h^l_{t-1} and d h^{l-1}_t of units (k) j0, j0 + 1
+          float at[RG][2], ab[RG][2];      // d h^l_{t-1} and d h^{l-1}_t of units (k) j0, j0 + 1
 #pragma unroll
-          for (int i = 0; i < G1_RG; ++i) { at[i][0] = keep[i][0]; at[i][1] = keep[i][1]; ab[i][0] = 0.f; ab[i][1] = 0.f; }
+          for (int i = 0; i < RG; ++i) { at[i][0] = keep[i][0]; at[i][1] = keep[i][1]; ab[i][0] = 0.f; ab[i][1] = 0.f; }
           const bool below = l > 0;
 #pragma unroll 2
           for (int j = 0; j < nh; ++j) {
-            float a[4][8];
+            float a[4][RG];
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
               if (g == 2 && !below) continue;
-              const float4 v0 = *reinterpret_cast<const float4*>(DP + (g * nh + j) * G1_LDH + r0);
-              const float4 v1 = *reinterpret_cast<const float4*>(DP + (g * nh + j) * G1_LDH + r0 + 4);
-              a[g][0] = v0.x; a[g][1] = v0.y; a[g][2] = v0.z; a[g][3] = v0.w; a[g][4] = v1.x; a[g][5] = v1.y; a[g][6] = v1.z; a[g][7] = v1.w;
+              g1_load_rows<RG>(DP + (g * nh + j) * LDH + r0, a[g]);
             }
             const float2 wr = *reinterpret_cast<const float2*>(WhT + (j * 3 + 0) * njp + j0);
             const float2 wu = *reinterpret_cast<const float2*>(WhT + (j * 3 + 1) * njp + j0);
             const float2 wc = *reinterpret_cast<const float2*>(WhT + (j * 3 + 2) * njp + j0);
 #pragma unroll
-            for (int i = 0; i < G1_RG; ++i) {
+            for (int i = 0; i < RG; ++i) {
               at[i][0] = fmaf(a[0][i], wr.x, fmaf(a[1][i], wu.x, fmaf(a[3][i], wc.x, at[i][0])));
               at[i][1] = fmaf(a[0][i], wr.y, fmaf(a[1][i], wu.y, fmaf(a[3][i], wc.y, at[i][1])));
             }
@@ -278,16 +278,16 @@ __global__ void __launch_bounds__(256) gru1d_bwd_kernel(const G1BwdParams P) {
               const float2 xu = *reinterpret_cast<const float2*>(WxT + (j * 3 + 1) * njp + j0);
               const float2 xc = *reinterpret_cast<const float2*>(WxT + (j * 3 + 2) * njp + j0);
 #pragma unroll
-              for (int i = 0; i < G1_RG; ++i) {
+              for (int i = 0; i < RG; ++i) {
                 ab[i][0] = fmaf(a[0][i], xr.x, fmaf(a[1][i], xu.x, fmaf(a[2][i], xc.x, ab[i][0])));
                 ab[i][1] = fmaf(a[0][i], xr.y, fmaf(a[1][i], xu.y, fmaf(a[2][i], xc.y, ab[i][1])));
               }
             }
           }
 #pragma unroll
-          for (int i = 0; i < G1_RG; ++i) {
+          for (int i = 0; i < RG; ++i) {
             const int r = r0 + i;
-            dHl[j0 * G1_LDH + r] = at[i][0]; dHl[(j0 + 1) * G1_LDH + r] = at[i][1];
+            dHl[j0 * LDH + r] = at[i][0]; dHl[(j0 + 1) * LDH + r] = at[i][1];
             if (below && r < nrows)
               *reinterpret_cast<float2*>(P.dx_out + ((size_t)t * (size_t)R + (size_t)(row0 + r)) * P.nhp + j0) = make_float2(ab[i][0], ab[i][1]);
           }

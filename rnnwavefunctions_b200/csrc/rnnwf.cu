@@ -23,11 +23,11 @@
 using namespace rnnwf;
 
 namespace rnnwf {   // gru1d_inst.cu
-cudaError_t g1_set_smem(int smem_bytes);
+cudaError_t g1_set_smem(int nh, int L, int N);
 int g1_occupancy(int threads, int smem_bytes);
-cudaError_t g1_sweep_launch(const SweepParams& P, int grid, int threads, int smem_bytes, cudaStream_t st);
+cudaError_t g1_sweep_launch(const SweepParams& P, int rg, int grid, int threads, cudaStream_t st);
 cudaError_t g1_pack_launch(const G1PackSrc& S, int nh, int L, int N, int D, int ND, float* out, cudaStream_t st);
-cudaError_t g1_bwd_set_smem(int smem_bytes);
+cudaError_t g1_bwd_set_smem(int nh, int L);
 cudaError_t g1_pack_bwd_launch(const G1PackSrc& S, int nh, int L, int D, int ND, float* out, cudaStream_t st);
 }
 namespace rnnwf {   // sweep_tc_inst.cu
@@ -357,9 +357,12 @@ int max_ctas(const rnnwf_model& m) {
 int pick_shape(const rnnwf_model& m, long long rows, LaunchShape& s, bool child = false) {
   s.tile_rows = 128;
   if (m.g1) {
-    const long long tiles = (rows + G1_ROWS - 1) / G1_ROWS;
-    s.WR = 2; s.Mp = G1_ROWS; s.Mr = G1_ROWS; s.threads = g1_threads(m.nh); s.smem = G1Layout(m.nh, m.symL, m.Tsym).total_bytes;
-    s.grid = (int)std::max(1LL, std::min<long long>(tiles, (long long)m.num_sms * m.g1_occ));
+    // sampling / evaluation of a training batch: narrow tiles (16 rows) so that the batch spreads over many SMs
+    const int rg = (!child && std::getenv("RNNWF_NO_VTILES") == nullptr) ? g1_pick_rg(rows, m.num_sms) : G1_RG;
+    s.tile_rows = 8 * rg;
+    const long long tiles = (rows + s.tile_rows - 1) / s.tile_rows;
+    s.WR = 2; s.Mp = G1_ROWS; s.Mr = G1_ROWS; s.threads = g1_threads(m.nh); s.smem = G1Layout(m.nh, m.symL, m.Tsym, s.tile_rows).total_bytes;
+    s.grid = (int)std::max(1LL, std::min<long long>(tiles, (long long)m.num_sms * (rg == G1_RG ? m.g1_occ : 2)));
     return RNNWF_OK;
   }
   if (m.tc_enabled) {
@@ -435,7 +438,7 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
   cudaError_t e;
   if (m.g1) {
     RNNWF_COUNT_LAUNCH();
-    e = g1_sweep_launch(P, s.grid, s.threads, s.smem, st);
+    e = g1_sweep_launch(P, s.tile_rows / 8, s.grid, s.threads, st);
     if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("1D GRU sweep launch: ") + cudaGetErrorString(e));
     return RNNWF_OK;
   }
@@ -631,12 +634,12 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
   if (m->g1) {
     const G1Layout Y(m->nh, m->symL, m->Tsym);
     CREATE_TRY(cudaMalloc(&m->d_g1pack, (size_t)Y.pack_floats * 4));
-    CREATE_TRY(g1_set_smem(Y.total_bytes));
+    CREATE_TRY(g1_set_smem(m->nh, m->symL, m->Tsym));
     m->g1_occ = std::max(1, std::min(4, g1_occupancy(g1_threads(m->nh), Y.total_bytes)));
     if (m->g1_bwd) {
       const G1BwdLayout Yb(m->nh, m->symL);
       CREATE_TRY(cudaMalloc(&m->d_g1packT, (size_t)Yb.pack_floats * 4));
-      CREATE_TRY(g1_bwd_set_smem(Yb.total_bytes));
+      CREATE_TRY(g1_bwd_set_smem(m->nh, m->symL));
     }
   }
   CREATE_TRY(backward_init());
