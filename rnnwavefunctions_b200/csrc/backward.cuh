@@ -103,13 +103,13 @@ __global__ void __launch_bounds__(256) gemm_nn_kernel(const float* __restrict__ 
 // C[K1,N] += A[M,K1]^T * B[M,N]; blockIdx.z splits the batch dimension M, partial tiles are added atomically
 // (rows of A may come in blocks: row m lives at A + (m / ablk) * astride + (m % ablk) * lda -- the saved history of one
 // layer of a stacked model is such a set; ablk >= M makes it an ordinary matrix)
-__global__ void __launch_bounds__(256) gemm_tn_atomic_kernel(const float* __restrict__ A, int lda, const float* __restrict__ B,
-                                                             int ldb, float* __restrict__ C, int ldc, long long M, int K1, int N,
-                                                             long long mchunk, long long ablk, long long astride) {
+__device__ __forceinline__ void gemm_tn_atomic_body(const float* __restrict__ A, int lda, const float* __restrict__ B,
+                                                    int ldb, float* __restrict__ C, int ldc, long long M, int K1, int N,
+                                                    long long mchunk, long long ablk, long long astride, int bx, int by, int bz) {
   __shared__ float As[GK][GB + 4], Bs[GK][GB + 4];
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-  const int k0 = blockIdx.y * GB, n0 = blockIdx.x * GB;
-  const long long mlo = (long long)blockIdx.z * mchunk;
+  const int k0 = by * GB, n0 = bx * GB;
+  const long long mlo = (long long)bz * mchunk;
   const long long mhi = (mlo + mchunk < M) ? mlo + mchunk : M;
   float acc[4][4] = {};
   for (long long m0 = mlo; m0 < mhi; m0 += GK) {
@@ -139,16 +139,34 @@ __global__ void __launch_bounds__(256) gemm_tn_atomic_kernel(const float* __rest
       if (kk < K1 && n < N && acc[i][j] != 0.f) atomicAdd(C + (long long)kk * ldc + n, acc[i][j]);
     }
 }
+__global__ void __launch_bounds__(256) gemm_tn_atomic_kernel(const float* __restrict__ A, int lda, const float* __restrict__ B,
+                                                             int ldb, float* __restrict__ C, int ldc, long long M, int K1, int N,
+                                                             long long mchunk, long long ablk, long long astride) {
+  gemm_tn_atomic_body(A, lda, B, ldb, C, ldc, M, K1, N, mchunk, ablk, astride, blockIdx.x, blockIdx.y, blockIdx.z);
+}
+// Several such products (and column sums) in ONE launch: the weight / bias gradients of the small 1D models are a dozen
+// ~50 us GEMMs over the same 10^4 rows -- launch latency, not work.  A block finds its problem by a scan over the list.
+constexpr int GEMM_BATCH_MAX = 24;
+struct GemmTnDesc { const float* A; const float* B; float* C; long long M, mchunk, ablk, astride; int lda, ldb, ldc, K1, N, gx, gy, gz, first; };
+struct GemmTnBatch { GemmTnDesc d[GEMM_BATCH_MAX]; int n; };
+__global__ void __launch_bounds__(256) gemm_tn_batched_kernel(const GemmTnBatch T) {
+  int i = 0;
+  while (i + 1 < T.n && (int)blockIdx.x >= T.d[i + 1].first) ++i;
+  const GemmTnDesc& D = T.d[i];
+  const int b = (int)blockIdx.x - D.first;
+  gemm_tn_atomic_body(D.A, D.lda, D.B, D.ldb, D.C, D.ldc, D.M, D.K1, D.N, D.mchunk, D.ablk, D.astride, b % D.gx, (b / D.gx) % D.gy, b / (D.gx * D.gy));
+}
 
 // out[n] += sum_m X[m, n]   (block = 32 columns x 8 row lanes, 4 loads in flight per thread)
-__global__ void __launch_bounds__(256) colsum_atomic_kernel(const float* __restrict__ X, int ldx, long long M, int N, float* __restrict__ out) {
+__device__ __forceinline__ void colsum_atomic_body(const float* __restrict__ X, int ldx, long long M, int N, float* __restrict__ out,
+                                                   int bx, int by, int gy) {
   __shared__ float red[8][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int n = blockIdx.x * 32 + tx;
-  const long long stride = 8LL * gridDim.y;
+  const int n = bx * 32 + tx;
+  const long long stride = 8LL * gy;
   float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
   if (n < N) {
-    long long m = (long long)blockIdx.y * 8 + ty;
+    long long m = (long long)by * 8 + ty;
     for (; m + 3 * stride < M; m += 4 * stride) {
       s0 += X[m * ldx + n]; s1 += X[(m + stride) * ldx + n]; s2 += X[(m + 2 * stride) * ldx + n]; s3 += X[(m + 3 * stride) * ldx + n];
     }
@@ -162,6 +180,18 @@ __global__ void __launch_bounds__(256) colsum_atomic_kernel(const float* __restr
     for (int k = 0; k < 8; ++k) s += red[k][tx];
     if (s != 0.f) atomicAdd(out + n, s);
   }
+}
+__global__ void __launch_bounds__(256) colsum_atomic_kernel(const float* __restrict__ X, int ldx, long long M, int N, float* __restrict__ out) {
+  colsum_atomic_body(X, ldx, M, N, out, blockIdx.x, blockIdx.y, gridDim.y);
+}
+struct ColsumDesc { const float* X; float* out; long long M; int ldx, N, gx, gy, first; };
+struct ColsumBatch { ColsumDesc d[GEMM_BATCH_MAX]; int n; };
+__global__ void __launch_bounds__(256) colsum_batched_kernel(const ColsumBatch T) {
+  int i = 0;
+  while (i + 1 < T.n && (int)blockIdx.x >= T.d[i + 1].first) ++i;
+  const ColsumDesc& D = T.d[i];
+  const int b = (int)blockIdx.x - D.first;
+  colsum_atomic_body(D.X, D.ldx, D.M, D.N, D.out, b % D.gx, b / D.gx, D.gy);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -580,6 +610,17 @@ inline long long backward_workspace_bytes(const rnnwf_model_impl& m, long long R
 struct Gemm {
   cudaStream_t st;
   bool tc = false;   // reduced-precision regime: long-K weight-gradient GEMMs on the tensor cores (TF32, gemm_tc.cuh)
+  // deferred mode: tn / tn_blocked / colsum calls are collected and go out as ONE launch each at flush() (they only add into
+  // disjoint or atomically updated outputs, so their order does not matter)
+  bool defer = false;
+  mutable GemmTnBatch tb{};
+  mutable ColsumBatch cb{};
+  mutable int tb_blocks = 0, cb_blocks = 0;
+  void flush() const {
+    if (tb.n > 0) { RNNWF_COUNT_LAUNCH(); gemm_tn_batched_kernel<<<tb_blocks, 256, 0, st>>>(tb); }
+    if (cb.n > 0) { RNNWF_COUNT_LAUNCH(); colsum_batched_kernel<<<cb_blocks, 256, 0, st>>>(cb); }
+    tb.n = 0; cb.n = 0; tb_blocks = 0; cb_blocks = 0;
+  }
   // C[K1,N] += A[M,K1]^T B[M,N] with a long reduction M
   void tn_long(const float* A, int lda, const float* B, int ldb, float* C, int ldc, long long M, int K1, int N) const {
     if (tc && N >= 16 && K1 >= 16 && gemm_tc_launch(st, A, lda, 0, B, ldb, 0, C, ldc, K1, N, M, 2)) return;
@@ -614,11 +655,23 @@ struct Gemm {
     long long mchunk = ((M + split - 1) / split + GK - 1) / GK * GK;
     split = (M + mchunk - 1) / mchunk;
     dim3 g((N + GB - 1) / GB, (K1 + GB - 1) / GB, (unsigned)split);
+    if (defer) {
+      if (tb.n == GEMM_BATCH_MAX) flush();
+      tb.d[tb.n++] = GemmTnDesc{A, B, C, M, mchunk, ablk, astride, lda, ldb, ldc, K1, N, (int)g.x, (int)g.y, (int)g.z, tb_blocks};
+      tb_blocks += (int)(g.x * g.y * g.z);
+      return;
+    }
     RNNWF_COUNT_LAUNCH(); gemm_tn_atomic_kernel<<<g, 256, 0, st>>>(A, lda, B, ldb, C, ldc, M, K1, N, mchunk, ablk, astride);
   }
   void colsum(const float* X, int ldx, long long M, int N, float* out) const {
     if (M <= 0 || N <= 0) return;
     dim3 g((N + 31) / 32, (unsigned)std::max<long long>(1, std::min<long long>(1024, M / 64)));
+    if (defer) {
+      if (cb.n == GEMM_BATCH_MAX) flush();
+      cb.d[cb.n++] = ColsumDesc{X, out, M, ldx, N, (int)g.x, (int)g.y, cb_blocks};
+      cb_blocks += (int)(g.x * g.y);
+      return;
+    }
     RNNWF_COUNT_LAUNCH(); colsum_atomic_kernel<<<g, 256, 0, st>>>(X, ldx, M, N, out);
   }
 };
@@ -685,6 +738,7 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
       if (e != cudaSuccess) { err = std::string("rnnwf_backward 1D GRU reverse sweep: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
     }
     const long long hstride = (long long)Ls * R * nhp;       // between consecutive sites of one layer in the saved history
+    G.defer = std::getenv("RNNWF_NO_GEMM_BATCH") == nullptr;   // all weight / bias gradients below: one GEMM launch + one column-sum launch
     for (int l = 0; l < Ls; ++l) {
       const std::string p = "gru" + std::to_string(l) + ".";
       const int din = (l == 0) ? 2 : nh;
@@ -715,6 +769,8 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
       G.tn_blocked(htop, nhp, R, hstride, dlog_base + m.D, m.ND, Gd("dense_phase.W"), 2, NR, nh, 2);
       G.colsum(dlog_base + m.D, m.ND, NR, 2, Gd("dense_phase.b"));
     }
+    G.flush();
+    G.defer = false;
     e = cudaGetLastError();
     if (e != cudaSuccess) { err = std::string("rnnwf_backward kernels: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
     return RNNWF_OK;
