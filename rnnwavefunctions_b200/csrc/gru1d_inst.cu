@@ -13,12 +13,12 @@ G1Kernel g1_pick(int mode) {
   if (mode == MODE_CHILD) return gru1d_sweep_kernel<MODE_CHILD, RG>;
   return gru1d_sweep_kernel<MODE_EVAL, RG>;
 }
-G1Kernel g1_kernel(int mode, int rg) { return rg == G1_RG_SMALL ? g1_pick<G1_RG_SMALL>(mode) : g1_pick<G1_RG>(mode); }
+G1Kernel g1_kernel(int mode, int rg) { return rg == 4 ? g1_pick<4>(mode) : rg == G1_RG_SMALL ? g1_pick<G1_RG_SMALL>(mode) : g1_pick<G1_RG>(mode); }
 }  // namespace
 
 // (the wide instance needs the most shared memory; the attribute is set to each instance's own size)
 cudaError_t g1_set_smem(int nh, int L, int N) {
-  for (int rg : {G1_RG, G1_RG_SMALL})
+  for (int rg : {G1_RG, G1_RG_SMALL, 4})
     for (int mode = 0; mode < 3; ++mode) {
       cudaError_t e = cudaFuncSetAttribute(reinterpret_cast<const void*>(g1_kernel(mode, rg)), cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            G1Layout(nh, L, N, 8 * rg).total_bytes);
