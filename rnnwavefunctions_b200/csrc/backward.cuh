@@ -785,12 +785,10 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
     const int pieces = (nhp + TC_JP - 1) / TC_JP;      // unit pieces per thread layout (== column passes of the tensorized GRU)
     e = cudaMemsetAsync(dh, 0, (size_t)tc_dh_bytes(m.Q, R, pieces), st);
     if (e != cudaSuccess) { err = std::string("rnnwf_backward memset: ") + cudaGetErrorString(e); return RNNWF_ECUDA; }
-    float* wimg = reinterpret_cast<float*>(ws + L.off_wimg);
+    // transposed weight image of the reverse sweep: the tensorized cells keep it in the handle (packed by rnnwf_set_weights together
+    // with the forward images); the vanilla cell packs its single chunk here
+    float* wimg = van ? reinterpret_cast<float*>(ws + L.off_wimg) : m.d_wimgT;
     if (van) { RNNWF_COUNT_LAUNCH(); pack_bwd_tc_vanilla_kernel<<<256, 256, 0, st>>>(P("Wh"), P("Wv"), nh, nhp, wimg); }
-    else {
-      const bool gated = m.cell == CELL_TENSGRU2D;
-      RNNWF_COUNT_LAUNCH(); pack_bwd_tc_kernel<<<512, 256, 0, st>>>(P("W"), gated ? P("Wg") : nullptr, gated ? P("Wmerge") : nullptr, nh, nhp, m.tc_np, wimg);
-    }
     BwdTcParams B;
     B.steps = m.d_steps; B.Q = m.Q; B.Tsym = m.Tsym; B.nsites = m.nsites; B.nh = nh; B.nhp = nhp; B.np = pieces; B.ND = m.ND;
     B.rows = R; B.cfg = cfg; B.gates = gates; B.dlog = dlog_base; B.dh = reinterpret_cast<float4*>(dh);
@@ -843,6 +841,8 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
       D.rows = R; D.tiles = tiles; D.cfg = cfg; D.site_of_t = m.d_site_of_t; D.dpT = B.dpT; D.himg = himg;
       { const char* dbg = std::getenv("RNNWF_TC_DEBUG"); D.debug = dbg ? std::atoi(dbg) : 0; }
       const int nsplit = 16;
+      int rowsum_nq = 0;
+      bool rowsum_gbg = false;
       if (van) {
         D.gW = nullptr; D.gWg = nullptr; D.gM0 = Gd("Wh"); D.gM1 = Gd("Wv");
         D.slab[0] = D.slab[1] = D.slab[2] = 0; D.gB = nullptr; D.gBg = nullptr;
@@ -863,14 +863,18 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
           if (m.steps[q].nbr[0] < 0 && m.steps[q].nbr[1] < 0) { err = "rnnwf_backward: a site without neighbours inside the path"; return RNNWF_EINVAL; }
         D.gB = bias_mma ? Gd("b") : nullptr; D.gBg = (bias_mma && gated) ? Gd("bg") : nullptr;
         if (njobs > 0) { RNNWF_COUNT_LAUNCH(); dw_tc_kernel<<<(unsigned)njobs, DW_THREADS, dw_smem_bytes(nhp), st>>>(D); }   // (a single-site lattice has no neighbour weights)
-        if (nq > 0) {
+        rowsum_nq = nq;                      // the sites without a neighbour: folded into head_grad_himg_kernel below ...
+        if (nq > 0 && !bias_mma) {           // ... unless every site is summed directly (fallback path): its own launch
           const int ns2 = std::max(1, std::min<int>(nsplit, (int)std::min<long long>(1 << 20, (long long)nq * tiles)));
           RNNWF_COUNT_LAUNCH(); dpt_rowsum_kernel<<<dim3(nh, ns2, gated ? 2 : 1), 128, 0, st>>>(B.dpT, m.Q, nq, tiles, nhp, ns2, Gd("b"), gated ? Gd("bg") : nullptr);
+          rowsum_nq = 0;
         }
+        rowsum_gbg = gated;
       }
       RNNWF_COUNT_LAUNCH(); head_grad_himg_kernel<<<std::min<long long>((long long)m.Q * tiles, 4LL * m.num_sms), 128, 0, st>>>(
           himg, dlog_base, m.Q, tiles, R, nh, nhp, m.ND, Gd("dense.W"), m.complex_head ? Gd("dense_phase.W") : nullptr,
-          (nh <= 124 && m.D == 2) ? Gd("dense.b") : nullptr, (nh <= 124 && m.D == 2 && m.complex_head) ? Gd("dense_phase.b") : nullptr);
+          (nh <= 124 && m.D == 2) ? Gd("dense.b") : nullptr, (nh <= 124 && m.D == 2 && m.complex_head) ? Gd("dense_phase.b") : nullptr,
+          B.dpT, rowsum_nq, rowsum_nq > 0 ? Gd("b") : nullptr, (rowsum_nq > 0 && rowsum_gbg) ? Gd("bg") : nullptr);
       if (!(nh <= 124 && m.D == 2)) {      // (wide models: the heads' bias gradients as column sums of d(logits))
         const long long RQ = (long long)m.Q * R;
         G.colsum(dlog_base, m.ND, RQ, m.D, Gd("dense.b"));

@@ -113,12 +113,12 @@ __device__ __forceinline__ void tc_st28(uint32_t taddr, const uint32_t (&d)[TC_T
 // out[variant 3][chunk p][k-core 28][n-core][8 rows][4]:  element (n, k) of chunk p is the derivative of pre-activation
 // block blk of unit j = 16 p + 4 sub + e  (k = sub * 28 + blk * 4 + e) with respect to input i of [h_h ; h_v]
 // (n = half * nhp + position, unit of the half = tc_kunit(position)).  Same variants as pack_tc_kernel.
-__global__ void pack_bwd_tc_kernel(const float* __restrict__ W, const float* __restrict__ Wg, const float* __restrict__ Wmerge,
-                                   int nh, int nhp, int NP, float* __restrict__ out) {
+__device__ __forceinline__ void pack_bwd_tc_body(const float* __restrict__ W, const float* __restrict__ Wg, const float* __restrict__ Wmerge,
+                                                 int nh, int nhp, int NP, float* __restrict__ out, long long vb, long long vg) {
   const int ncores = 2 * nhp / 8;
   const long long per_chunk = (long long)(BT_K / 4) * ncores * 32;
   const long long total = 3LL * NP * per_chunk;
-  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+  for (long long idx = vb * (long long)blockDim.x + threadIdx.x; idx < total; idx += vg * blockDim.x) {
     long long r = idx;
     const int ek = (int)(r % 4); r /= 4;
     const int en = (int)(r % 8); r /= 8;
@@ -146,6 +146,10 @@ __global__ void pack_bwd_tc_kernel(const float* __restrict__ W, const float* __r
     }
     out[idx] = v;
   }
+}
+__global__ void pack_bwd_tc_kernel(const float* __restrict__ W, const float* __restrict__ Wg, const float* __restrict__ Wmerge,
+                                   int nh, int nhp, int NP, float* __restrict__ out) {
+  pack_bwd_tc_body(W, Wg, Wmerge, nh, nhp, NP, out, blockIdx.x, gridDim.x);
 }
 
 // ---- vanilla 2D RNN: one chunk, element (n, k) = d pre_j / d h_{half, i} = W_half[i][j]   (k <-> unit j, n <-> (half, unit i))

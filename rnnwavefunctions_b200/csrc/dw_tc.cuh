@@ -301,12 +301,15 @@ __global__ void __launch_bounds__(128) dpt_rowsum_kernel(const float* __restrict
 __global__ void __launch_bounds__(128) head_grad_himg_kernel(const float* __restrict__ himg, const float* __restrict__ dlog, int Q,
                                                              long long tiles, long long rows, int nh, int nhp, int ND,
                                                              float* __restrict__ gW, float* __restrict__ gWp,
-                                                             float* __restrict__ gB, float* __restrict__ gBp) {
+                                                             float* __restrict__ gB, float* __restrict__ gBp,
+                                                             const float* __restrict__ dpT, int nq, float* __restrict__ gb, float* __restrict__ gbg) {
+  // (dpT, nq, gb, gbg: the cell's bias gradients of the first nq sites -- the ones without a neighbour, which the
+  //  weight-gradient MMAs do not cover -- as row sums of the feature-major (ds | dg) tiles; null / 0: nothing to do)
   __shared__ float dl[TC_ROWS * 4];
   const int ncores = tc_himg_ncores(nhp);
   const int j = threadIdx.x;
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
-  float bsum = 0.f;
+  float bsum = 0.f, cb0 = 0.f, cb1 = 0.f;
   const long long nitems = (long long)Q * tiles;
   for (long long it = blockIdx.x; it < nitems; it += gridDim.x) {
     const int q = (int)(it / tiles);
@@ -318,6 +321,15 @@ __global__ void __launch_bounds__(128) head_grad_himg_kernel(const float* __rest
       dl[i] = (r < rows && d < ND) ? dlog[((size_t)q * rows + r) * ND + d] : 0.f;
     }
     __syncthreads();
+    if (gb != nullptr && q < nq && j < nh) {
+      const float* d0 = dpT + ((size_t)it * nhp + j) * TC_DPT_PITCH;
+      const float* d1 = d0 + (size_t)Q * tiles * nhp * TC_DPT_PITCH;
+      for (int r = 0; r < TC_ROWS; r += 4) {
+        const float4 a = *reinterpret_cast<const float4*>(d0 + r);
+        cb0 += (a.x + a.y) + (a.z + a.w);
+        if (gbg != nullptr) { const float4 c = *reinterpret_cast<const float4*>(d1 + r); cb1 += (c.x + c.y) + (c.z + c.w); }
+      }
+    }
     if (gB != nullptr && j >= 124) {
       float s = 0.f;
       for (int r = 0; r < TC_ROWS; ++r) s += dl[r * 4 + (j - 124)];
@@ -339,6 +351,10 @@ __global__ void __launch_bounds__(128) head_grad_himg_kernel(const float* __rest
     // dense.W is [nh][D = 2], dense_phase.W is [nh][2]
     atomicAdd(gW + j * 2 + 0, acc[0]); atomicAdd(gW + j * 2 + 1, acc[1]);
     if (gWp != nullptr) { atomicAdd(gWp + j * 2 + 0, acc[2]); atomicAdd(gWp + j * 2 + 1, acc[3]); }
+  }
+  if (gb != nullptr && j < nh && nq > 0) {
+    if (cb0 != 0.f) atomicAdd(gb + j, cb0);
+    if (gbg != nullptr && cb1 != 0.f) atomicAdd(gbg + j, cb1);
   }
   if (gB != nullptr && j >= 124) {
     const int d = j - 124;                         // dense.b is [2], dense_phase.b is [2]

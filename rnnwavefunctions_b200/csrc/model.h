@@ -66,6 +66,7 @@ struct rnnwf_model_impl {
   int tc_np = 0;
   unsigned char* d_tcB = nullptr;
   float* d_tcbias = nullptr;
+  float* d_wimgT = nullptr;     // tensorized cells: the reverse sweep's transposed TF32 weight image (bwd_tc.cuh), packed with the forward images
   // weight-gradient kernel work plan (dw_tc.cuh), cached on the device for the last row count it was built for
   mutable long long dw_rows = -1;
   mutable int dw_njobs = 0;

@@ -191,9 +191,9 @@ __global__ void pack_b_kernel(const PackCtx c, float4* __restrict__ dst) {
 }
 
 // heads: dense.W [nh,D] (+ dense_phase.W [nh,2]) -> [nhp][ND]; biases -> [ND]
-__global__ void pack_head_kernel(const float* Wd, const float* bd, const float* Wp, const float* bp, int nh, int nhp,
-                                 int D, int ND, float* head_w, float* head_b) {
-  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < nhp * ND; idx += gridDim.x * blockDim.x) {
+__device__ __forceinline__ void pack_head_body(const float* Wd, const float* bd, const float* Wp, const float* bp, int nh, int nhp,
+                                               int D, int ND, float* head_w, float* head_b, int vb, int vg) {
+  for (int idx = vb * blockDim.x + threadIdx.x; idx < nhp * ND; idx += vg * blockDim.x) {
     const int j = idx / ND, d = idx - j * ND;
     float v = 0.f;
     if (j < nh) {
@@ -203,6 +203,10 @@ __global__ void pack_head_kernel(const float* Wd, const float* bd, const float* 
     head_w[idx] = v;
     if (j == 0) head_b[d] = (d < D) ? bd[d] : ((bp != nullptr && d < D + 2) ? bp[d - D] : 0.f);
   }
+}
+__global__ void pack_head_kernel(const float* Wd, const float* bd, const float* Wp, const float* bp, int nh, int nhp,
+                                 int D, int ND, float* head_w, float* head_b) {
+  pack_head_body(Wd, bd, Wp, bp, nh, nhp, D, ND, head_w, head_b, blockIdx.x, gridDim.x);
 }
 
 }  // namespace rnnwf

@@ -8,16 +8,17 @@ namespace rnnwf {
 // [variant 3][pass NP][k-core kc][n-core 14][8 rows][8 halves]:  B[n][k] of the pass, K-major core matrices
 // (n ordered thread-major, see below).
 // variants: 0 both neighbours, 1 horizontal only, 2 vertical only.
-__global__ void pack_tc_kernel(const float* __restrict__ W, const float* __restrict__ Wg, const float* __restrict__ Wmerge,
-                               const float* __restrict__ b, const float* __restrict__ bg,
-                               int nh, int nhp, int NP, int split, __half* __restrict__ out) {
+// (`vb`, `vg`: the block's index and the number of blocks inside the part of the grid that works on this image)
+__device__ __forceinline__ void pack_tc_body(const float* __restrict__ W, const float* __restrict__ Wg, const float* __restrict__ Wmerge,
+                                             const float* __restrict__ b, const float* __restrict__ bg,
+                                             int nh, int nhp, int NP, int split, __half* __restrict__ out, long long vb, long long vg) {
   // split != 0 (split-precision regime): [variant][pass][part 2: hi, lo][image], unscaled gate weights
   const int kc = 2 * (nhp / 8);
   const int nparts = split ? 2 : 1;
   const long long per_pass = (long long)kc * (TC_N / 8) * 64;
   const long long total = 3LL * NP * nparts * per_pass;
   const float gate_scale = split ? 1.0f : TC_SCALE_GATE;
-  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+  for (long long idx = vb * (long long)blockDim.x + threadIdx.x; idx < total; idx += vg * blockDim.x) {
     long long r = idx;
     const int e = (int)(r % 8); r /= 8;
     const int r8 = (int)(r % 8); r /= 8;
@@ -56,11 +57,21 @@ __global__ void pack_tc_kernel(const float* __restrict__ W, const float* __restr
   }
 }
 
-__global__ void pack_tc_bias_kernel(const float* __restrict__ b, const float* __restrict__ bg, int nh, int nhp, float* __restrict__ out) {
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * nhp; i += gridDim.x * blockDim.x) {
+__global__ void pack_tc_kernel(const float* __restrict__ W, const float* __restrict__ Wg, const float* __restrict__ Wmerge,
+                               const float* __restrict__ b, const float* __restrict__ bg,
+                               int nh, int nhp, int NP, int split, __half* __restrict__ out) {
+  pack_tc_body(W, Wg, Wmerge, b, bg, nh, nhp, NP, split, out, blockIdx.x, gridDim.x);
+}
+
+__device__ __forceinline__ void pack_tc_bias_body(const float* __restrict__ b, const float* __restrict__ bg, int nh, int nhp, float* __restrict__ out,
+                                                  int vb, int vg) {
+  for (int i = vb * blockDim.x + threadIdx.x; i < 2 * nhp; i += vg * blockDim.x) {
     const int which = i / nhp, j = i - which * nhp;
     out[i] = (j < nh) ? (which == 0 ? b[j] : (bg != nullptr ? bg[j] : 0.f)) : 0.f;
   }
+}
+__global__ void pack_tc_bias_kernel(const float* __restrict__ b, const float* __restrict__ bg, int nh, int nhp, float* __restrict__ out) {
+  pack_tc_bias_body(b, bg, nh, nhp, out, blockIdx.x, gridDim.x);
 }
 
 // ---- vanilla 2D RNN (CELLK = 1): one image [k-core kc][n-core 14][8 rows][8 halves], B[n][k] = W_half[unit(k)][unit(n)]

@@ -626,6 +626,7 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
     if (ts.total > 227 * 1024) { rnnwf_destroy(m); return fail(RNNWF_ENOMEM, "tensor-core sweep does not fit in shared memory for this lattice / width"); }
     CREATE_TRY(cudaMalloc(&m->d_tcB, (size_t)3 * m->tc_np * ts.b_bytes * (m->tc_split ? 2 : 1)));
     CREATE_TRY(cudaMalloc(&m->d_tcbias, (size_t)6 * m->nhp * 4));
+    CREATE_TRY(cudaMalloc(&m->d_wimgT, (size_t)3 * ((m->nhp + TC_JP - 1) / TC_JP) * BtSmem(m->nhp, m->Tsym, m->Q).b_bytes));
     const int cellk = (m->cell == CELL_VANILLA2D) ? 1 : (m->cell == CELL_TENS2D ? 2 : 0);
     CREATE_TRY(tc_sweep_set_smem(cellk, cellk != 1 && m->nh < m->nhp, m->tc_split, ts.total));
   }
@@ -665,7 +666,7 @@ int rnnwf_destroy(rnnwf_handle h) {
   if (h == nullptr) return RNNWF_OK;
   cudaFree(h->d_steps); cudaFree(h->d_variants); cudaFree(h->d_site_of_t); cudaFree(h->d_wpack);
   cudaFree(h->d_xtab); cudaFree(h->d_bias); cudaFree(h->d_head_w); cudaFree(h->d_head_b);
-  cudaFree(h->d_hamtab); cudaFree(h->d_g1pack); cudaFree(h->d_g1packT); cudaFree(h->d_tcB); cudaFree(h->d_tcbias); cudaFree(h->d_dw_jobs); cudaFree(h->d_dw_cls); cudaFree(h->d_dw4_jobs); cudaFree(h->d_dw4_sites);
+  cudaFree(h->d_hamtab); cudaFree(h->d_g1pack); cudaFree(h->d_g1packT); cudaFree(h->d_tcB); cudaFree(h->d_tcbias); cudaFree(h->d_wimgT); cudaFree(h->d_dw_jobs); cudaFree(h->d_dw_cls); cudaFree(h->d_dw4_jobs); cudaFree(h->d_dw4_sites);
   delete h;
   return RNNWF_OK;
 }
@@ -729,6 +730,23 @@ static void pack_ffma(rnnwf_handle h, const float* params_dev, cudaStream_t st) 
   h->ffma_stale = false;
 }
 
+// every image a tensorized-cell handle derives from the parameters, in ONE launch: forward FP16 images (pack_tc.cuh), the bias
+// table, the reverse sweep's transposed TF32 image (bwd_tc.cuh) and the heads (pack.cuh); the grid is cut into four parts
+struct PackTcAll {
+  const float *W, *Wg, *Wmerge, *b, *bg, *Wd, *bd, *Wp, *bp;
+  int nh, nhp, NP, split, D, ND, nb_tc, nb_bwd;
+  __half* tcB; float* tcbias; float* wimgT; float* head_w; float* head_b;
+};
+__global__ void __launch_bounds__(256) pack_tc_all_kernel(const PackTcAll A) {
+  int b = blockIdx.x;
+  if (b < A.nb_tc) { pack_tc_body(A.W, A.Wg, A.Wmerge, A.b, A.bg, A.nh, A.nhp, A.NP, A.split, A.tcB, b, A.nb_tc); return; }
+  b -= A.nb_tc;
+  if (b < A.nb_bwd) { pack_bwd_tc_body(A.W, A.Wg, A.Wmerge, A.nh, A.nhp, A.NP, A.wimgT, b, A.nb_bwd); return; }
+  b -= A.nb_bwd;
+  if (b == 0) { pack_tc_bias_body(A.b, A.bg, A.nh, A.nhp, A.tcbias, 0, 1); return; }
+  pack_head_body(A.Wd, A.bd, A.Wp, A.bp, A.nh, A.nhp, A.D, A.ND, A.head_w, A.head_b, b - 1, (int)gridDim.x - A.nb_tc - A.nb_bwd - 1);
+}
+
 int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
   if (h == nullptr || params_dev == nullptr) return fail(RNNWF_EINVAL, "null argument");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -740,9 +758,12 @@ int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
   const TensorInfo* bd = h->tensor("dense.b");
   const TensorInfo* wp = h->tensor("dense_phase.W");
   const TensorInfo* bp = h->tensor("dense_phase.b");
-  RNNWF_COUNT_LAUNCH(); pack_head_kernel<<<cdiv((long long)h->nhp * h->ND, 256), 256, 0, st>>>(
-      params_dev + wd->offset, params_dev + bd->offset, wp ? params_dev + wp->offset : nullptr,
-      bp ? params_dev + bp->offset : nullptr, h->nh, h->nhp, h->D, h->ND, h->d_head_w, h->d_head_b);
+  const bool tc_all = h->tc_enabled && h->cell != CELL_VANILLA2D;     // tensorized cells: everything in one launch below
+  if (!tc_all) {
+    RNNWF_COUNT_LAUNCH(); pack_head_kernel<<<cdiv((long long)h->nhp * h->ND, 256), 256, 0, st>>>(
+        params_dev + wd->offset, params_dev + bd->offset, wp ? params_dev + wp->offset : nullptr,
+        bp ? params_dev + bp->offset : nullptr, h->nh, h->nhp, h->D, h->ND, h->d_head_w, h->d_head_b);
+  }
   if (h->g1) {
     G1PackSrc S;
     std::memset(&S, 0, sizeof(S));
@@ -768,10 +789,14 @@ int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
     } else {
       const long long n = 3LL * h->tc_np * (ts.b_bytes / 2) * (h->tc_split ? 2 : 1);
       auto opt = [&](const char* nm) -> const float* { const TensorInfo* t = h->tensor(nm); return t ? params_dev + t->offset : nullptr; };
-      RNNWF_COUNT_LAUNCH(); pack_tc_kernel<<<std::min(2048, cdiv(n, 256)), 256, 0, st>>>(
-          params_dev + h->tensor("W")->offset, opt("Wg"), opt("Wmerge"), params_dev + h->tensor("b")->offset, opt("bg"),
-          h->nh, h->nhp, h->tc_np, h->tc_split ? 1 : 0, reinterpret_cast<__half*>(h->d_tcB));
-      RNNWF_COUNT_LAUNCH(); pack_tc_bias_kernel<<<1, 256, 0, st>>>(params_dev + h->tensor("b")->offset, opt("bg"), h->nh, h->nhp, h->d_tcbias);
+      PackTcAll A;
+      A.W = params_dev + h->tensor("W")->offset; A.Wg = opt("Wg"); A.Wmerge = opt("Wmerge"); A.b = params_dev + h->tensor("b")->offset; A.bg = opt("bg");
+      A.Wd = params_dev + wd->offset; A.bd = params_dev + bd->offset; A.Wp = wp ? params_dev + wp->offset : nullptr; A.bp = bp ? params_dev + bp->offset : nullptr;
+      A.nh = h->nh; A.nhp = h->nhp; A.NP = h->tc_np; A.split = h->tc_split ? 1 : 0; A.D = h->D; A.ND = h->ND;
+      A.nb_tc = std::min(2048, cdiv(n, 256)); A.nb_bwd = 512;
+      A.tcB = reinterpret_cast<__half*>(h->d_tcB); A.tcbias = h->d_tcbias; A.wimgT = h->d_wimgT; A.head_w = h->d_head_w; A.head_b = h->d_head_b;
+      RNNWF_COUNT_LAUNCH();
+      pack_tc_all_kernel<<<A.nb_tc + A.nb_bwd + 1 + cdiv((long long)h->nhp * h->ND, 256), 256, 0, st>>>(A);
     }
   }
   if (h->tc4) {
