@@ -39,8 +39,9 @@ __global__ void tfim_diag_kernel(const int8_t* __restrict__ cfg, long long ns, i
 }
 
 // every symbol-bit of every sample flipped once: child index (t*bits + k)*ns + n
-__global__ void all_flips_kernel(long long ns, int Tsym, int bits, float coef, Child* __restrict__ children) {
+__global__ void all_flips_kernel(long long ns, int Tsym, int bits, float coef, Child* __restrict__ children, long long* __restrict__ nconn) {
   const long long total = (long long)Tsym * bits * ns;
+  if (nconn != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *nconn = total;     // number of connected configurations
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
     const long long n = idx % ns;
     const int tk = (int)(idx / ns);
@@ -52,33 +53,29 @@ __global__ void all_flips_kernel(long long ns, int Tsym, int bits, float coef, C
 
 // ---- exchange Hamiltonians (J1-J2 chain, square / triangular Heisenberg) ---------------------------
 // site_of_t maps a symbol index to its offset inside a configuration row.
-__global__ void bond_diag_kernel(const int8_t* __restrict__ cfg, long long ns, int nsites, const int16_t* __restrict__ site_of_t,
-                                 const Bond* __restrict__ bonds, int nbonds, const double* __restrict__ Bz, int nBz,
-                                 double* __restrict__ eloc) {
-  for (long long n = blockIdx.x * (long long)blockDim.x + threadIdx.x; n < ns; n += (long long)gridDim.x * blockDim.x) {
-    const int8_t* row = cfg + n * nsites;
-    double e = 0.0;
-    for (int b = 0; b < nbonds; ++b) {
-      const Bond bd = bonds[b];
-      const bool anti = cfg_spin(row, site_of_t[bd.ta]) != cfg_spin(row, site_of_t[bd.tb]);
-      e += anti ? -(double)bd.diag : (double)bd.diag;
-    }
-    for (int i = 0; i < nBz; ++i) e += ((double)cfg_spin(row, i) - 0.5) * Bz[i];  // field term (J1-J2 only, 1D: site == i)
-    eloc[2 * n] = e;
-    eloc[2 * n + 1] = 0.0;
-  }
-}
-
-// counts[ts*ns + n] = number of non-zero exchanges of sample n whose first changed symbol is ts
+// counts[ts*ns + n] = number of non-zero exchanges of sample n whose first changed symbol is ts; the threads of ts == 0 also
+// take the diagonal matrix element of their sample along (bond_diag_kernel's arithmetic; eloc == nullptr: not wanted)
 __global__ void bond_count_kernel(const int8_t* __restrict__ cfg, long long ns, int nsites, int Tsym,
                                   const int16_t* __restrict__ site_of_t, const Bond* __restrict__ bonds,
-                                  const int* __restrict__ bond_start, int* __restrict__ counts) {
+                                  const int* __restrict__ bond_start, int* __restrict__ counts,
+                                  int nbonds, const double* __restrict__ Bz, int nBz, double* __restrict__ eloc) {
   const long long total = (long long)Tsym * ns;
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx <= total; idx += (long long)gridDim.x * blockDim.x) {
     if (idx == total) { counts[idx] = 0; continue; }
     const long long n = idx % ns;
     const int ts = (int)(idx / ns);
     const int8_t* row = cfg + n * nsites;
+    if (ts == 0 && eloc != nullptr) {
+      double e = 0.0;
+      for (int b = 0; b < nbonds; ++b) {
+        const Bond bd = bonds[b];
+        const bool anti = cfg_spin(row, site_of_t[bd.ta]) != cfg_spin(row, site_of_t[bd.tb]);
+        e += anti ? -(double)bd.diag : (double)bd.diag;
+      }
+      for (int i = 0; i < nBz; ++i) e += ((double)cfg_spin(row, i) - 0.5) * Bz[i];
+      eloc[2 * n] = e;
+      eloc[2 * n + 1] = 0.0;
+    }
     const int sa = cfg_spin(row, site_of_t[ts]);
     int c = 0;
     for (int b = bond_start[ts]; b < bond_start[ts + 1]; ++b)
@@ -90,8 +87,9 @@ __global__ void bond_count_kernel(const int8_t* __restrict__ cfg, long long ns, 
 __global__ void bond_fill_kernel(const int8_t* __restrict__ cfg, long long ns, int nsites, int Tsym,
                                  const int16_t* __restrict__ site_of_t, const Bond* __restrict__ bonds,
                                  const int* __restrict__ bond_start, const int* __restrict__ offsets,
-                                 Child* __restrict__ children) {
+                                 Child* __restrict__ children, long long* __restrict__ nconn) {
   const long long total = (long long)Tsym * ns;
+  if (nconn != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *nconn = (long long)offsets[total];   // number of connected configurations
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
     const long long n = idx % ns;
     const int ts = (int)(idx / ns);

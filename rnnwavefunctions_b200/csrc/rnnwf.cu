@@ -543,11 +543,78 @@ __global__ void __launch_bounds__(SCAN_TPB) scan_apply_kernel(const int* __restr
     __syncthreads();
   }
 }
+// The same in ONE launch (chained scan): a block takes a ticket (so that logical block b only ever waits for blocks that
+// have already started), sums its chunk, publishes the sum, adds up the sums of the blocks before it as they appear, and
+// scans its chunk with that offset.  state[0] = ticket, state[1 + b] = sum of block b, state[1 + nblk + b] = its flag; zeroed
+// by the caller before the launch.
+__global__ void __launch_bounds__(SCAN_TPB) scan_chained_kernel(const int* __restrict__ in, int* __restrict__ out, long long n, long long chunk,
+                                                               int nblk, int* __restrict__ state) {
+  __shared__ int red[SCAN_TPB / 32], wsum[SCAN_TPB / 32];
+  __shared__ int bid_s, carry_s;
+  if (threadIdx.x == 0) bid_s = atomicAdd(state, 1);
+  __syncthreads();
+  const int b = bid_s;
+  volatile int* sums = state + 1;
+  volatile int* flags = state + 1 + nblk;
+  const long long lo = b * chunk, hi = (lo + chunk < n) ? lo + chunk : n;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  // ---- own sum, published
+  int s = 0;
+  for (long long i = lo + threadIdx.x; i < hi; i += SCAN_TPB) s += in[i];
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) red[w] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int k = 0; k < SCAN_TPB / 32; ++k) t += red[k];
+    sums[b] = t;
+    __threadfence();
+    flags[b] = 1;
+  }
+  // ---- sum of the blocks before this one
+  int pre = 0;
+  for (int k = threadIdx.x; k < b; k += SCAN_TPB) {
+    for (unsigned spin = 0; flags[k] == 0; ++spin) { __nanosleep(40); if (spin > (1u << 26)) { asm volatile("trap;"); } }
+    __threadfence();
+    pre += sums[k];
+  }
+  for (int o = 16; o > 0; o >>= 1) pre += __shfl_xor_sync(0xffffffffu, pre, o);
+  __syncthreads();
+  if (lane == 0) red[w] = pre;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int k = 0; k < SCAN_TPB / 32; ++k) t += red[k];
+    carry_s = t;
+  }
+  __syncthreads();
+  // ---- scan of the chunk with that offset
+  for (long long base = lo; base < hi; base += SCAN_TPB) {
+    const long long i = base + threadIdx.x;
+    const int v = (i < hi) ? in[i] : 0;
+    int x = v;
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) wsum[w] = x;
+    __syncthreads();
+    int woff = 0;
+    for (int k = 0; k < w; ++k) woff += wsum[k];
+    const int carry = carry_s;
+    if (i < hi) out[i] = carry + woff + x - v;
+    __syncthreads();
+    if (threadIdx.x == SCAN_TPB - 1) carry_s = carry + woff + x;
+    __syncthreads();
+  }
+}
 // exclusive scan of n int32 counts on stream st; tmp holds 2048 ints
 void exclusive_scan(const int* in, int* out, long long n, int* tmp, cudaStream_t st) {
   if (n <= 8192) { RNNWF_COUNT_LAUNCH(); scan_kernel<<<1, 1024, 0, st>>>(in, out, n); return; }
-  const int nblk = (int)std::min<long long>(1024, (n + 4095) / 4096);
+  const int nblk = (int)std::min<long long>(1000, (n + 4095) / 4096);
   const long long chunk = (n + nblk - 1) / nblk;
+  if (std::getenv("RNNWF_SCAN3") == nullptr) {       // one launch
+    cudaMemsetAsync(tmp, 0, (size_t)(1 + 2 * nblk) * sizeof(int), st);
+    RNNWF_COUNT_LAUNCH(); scan_chained_kernel<<<nblk, SCAN_TPB, 0, st>>>(in, out, n, chunk, nblk, tmp);
+    return;
+  }
   RNNWF_COUNT_LAUNCH(); scan_reduce_kernel<<<nblk, SCAN_TPB, 0, st>>>(in, tmp, n, chunk);
   RNNWF_COUNT_LAUNCH(); scan_kernel<<<1, 1024, 0, st>>>(tmp, tmp + 1024, nblk);
   RNNWF_COUNT_LAUNCH(); scan_apply_kernel<<<nblk, SCAN_TPB, 0, st>>>(in, tmp + 1024, out, n, chunk);
@@ -894,13 +961,15 @@ int64_t rnnwf_eloc_workspace_bytes(rnnwf_handle h, int hamiltonian, int64_t rows
 }
 
 namespace {
-struct EnumOut { long long nchild_fixed = 0; const int* rows_dev = nullptr; bool have_children = true; };
+struct EnumOut { long long nchild_fixed = 0; const int* rows_dev = nullptr; bool have_children = true; bool counted = false; };   // counted: *nconn written by the enumeration
 
 // Diagonal matrix elements into eloc_dev and the list of connected configurations (Child records, ordered by first
 // changed generation step) into the workspace -- shared by rnnwf_local_energies and rnnwf_local_energies_sym.
 int enumerate_connected(const rnnwf_model& m, int hamiltonian, const double* ham, int ham_len, long long rows,
-                        const int8_t* samples_dev, double* eloc_dev, char* ws, const ElocLayout& L, cudaStream_t st, EnumOut& out) {
+                        const int8_t* samples_dev, double* eloc_dev, char* ws, const ElocLayout& L, cudaStream_t st, EnumOut& out,
+                        long long* nconn_dev = nullptr) {
   int rc;
+  bool counted = false;          // the enumeration kernels wrote the number of connected configurations to *nconn_dev
   // Hamiltonian tables (couplings, bond list, neighbour table) live in the handle and are rebuilt / uploaded only when the
   // `ham` block changes: a training loop passes the same block every step, so the hot call stages nothing from the host.
   // The host images the uploads read from are kept in the handle, so the stream-ordered copies never outlive their source.
@@ -944,7 +1013,7 @@ int enumerate_connected(const rnnwf_model& m, int hamiltonian, const double* ham
       if (Bx == 0.0) have_children = false;
       else {
         nchild_fixed = (long long)T * rows;
-        RNNWF_COUNT_LAUNCH(); all_flips_kernel<<<std::min(8192, cdiv(nchild_fixed, tpb)), tpb, 0, st>>>(rows, T, 1, (float)(-Bx), d_children);
+        RNNWF_COUNT_LAUNCH(); all_flips_kernel<<<std::min(8192, cdiv(nchild_fixed, tpb)), tpb, 0, st>>>(rows, T, 1, (float)(-Bx), d_children, nconn_dev); counted = nconn_dev != nullptr;
       }
       break;
     }
@@ -988,7 +1057,7 @@ int enumerate_connected(const rnnwf_model& m, int hamiltonian, const double* ham
       if (Omega == 0.0) have_children = false;
       else {
         nchild_fixed = 3LL * T * rows;
-        RNNWF_COUNT_LAUNCH(); all_flips_kernel<<<std::min(8192, cdiv(nchild_fixed, tpb)), tpb, 0, st>>>(rows, T, 3, (float)(-Omega / 2.0), d_children);
+        RNNWF_COUNT_LAUNCH(); all_flips_kernel<<<std::min(8192, cdiv(nchild_fixed, tpb)), tpb, 0, st>>>(rows, T, 3, (float)(-Omega / 2.0), d_children, nconn_dev); counted = nconn_dev != nullptr;
       }
       break;
     }
@@ -1038,11 +1107,14 @@ int enumerate_connected(const rnnwf_model& m, int hamiltonian, const double* ham
         CUDA_TRY(upload(d_bstart, bstart.data(), bstart.size() * 4, m.ham_host[1]));
         if (!Bz.empty()) CUDA_TRY(upload(d_ham, Bz.data(), Bz.size() * 8, m.ham_host[2]));
       }
-      RNNWF_COUNT_LAUNCH(); bond_diag_kernel<<<gsamp, tpb, 0, st>>>(samples_dev, rows, m.nsites, m.d_site_of_t, d_bonds, (int)bonds.size(), d_ham, (int)Bz.size(), eloc_dev);
+      // three launches: counts per (first changed symbol, sample) + the diagonal matrix elements; their exclusive scan; the
+      // child records (+ the number of connected configurations)
       const long long ncnt = (long long)T * rows;
-      RNNWF_COUNT_LAUNCH(); bond_count_kernel<<<std::min(8192, cdiv(ncnt + 1, tpb)), tpb, 0, st>>>(samples_dev, rows, m.nsites, T, m.d_site_of_t, d_bonds, d_bstart, d_counts);
+      RNNWF_COUNT_LAUNCH(); bond_count_kernel<<<std::min(8192, cdiv(ncnt + 1, tpb)), tpb, 0, st>>>(samples_dev, rows, m.nsites, T, m.d_site_of_t, d_bonds, d_bstart, d_counts,
+                                                                                                (int)bonds.size(), d_ham, (int)Bz.size(), eloc_dev);
       exclusive_scan(d_counts, d_offsets, ncnt + 1, reinterpret_cast<int*>(ws + L.off_nchild), st);
-      RNNWF_COUNT_LAUNCH(); bond_fill_kernel<<<std::min(8192, cdiv(ncnt, tpb)), tpb, 0, st>>>(samples_dev, rows, m.nsites, T, m.d_site_of_t, d_bonds, d_bstart, d_offsets, d_children);
+      RNNWF_COUNT_LAUNCH(); bond_fill_kernel<<<std::min(8192, cdiv(ncnt, tpb)), tpb, 0, st>>>(samples_dev, rows, m.nsites, T, m.d_site_of_t, d_bonds, d_bstart, d_offsets, d_children, nconn_dev);
+      counted = nconn_dev != nullptr;
       rows_dev = d_offsets + ncnt;
       nchild_fixed = L.max_children;
       break;
@@ -1052,7 +1124,7 @@ int enumerate_connected(const rnnwf_model& m, int hamiltonian, const double* ham
   }
   CUDA_TRY(cudaGetLastError());
   if (!hit) { m.ham_kind = hamiltonian; m.ham_block.assign(ham, ham + ham_len); }
-  out.nchild_fixed = nchild_fixed; out.rows_dev = rows_dev; out.have_children = have_children;
+  out.nchild_fixed = nchild_fixed; out.rows_dev = rows_dev; out.have_children = have_children; out.counted = counted;
   return RNNWF_OK;
 }
 }  // namespace
@@ -1072,9 +1144,9 @@ int rnnwf_local_energies(rnnwf_handle h, int hamiltonian, const double* ham, int
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   char* ws = static_cast<char*>(workspace_dev);
   EnumOut en;
-  if ((rc = enumerate_connected(m, hamiltonian, ham, ham_len, rows, samples_dev, eloc_dev, ws, L, st, en))) return rc;
+  if ((rc = enumerate_connected(m, hamiltonian, ham, ham_len, rows, samples_dev, eloc_dev, ws, L, st, en, (long long*)nconn_dev))) return rc;
   Child* d_children = reinterpret_cast<Child*>(ws + L.off_children);
-  if (nconn_dev != nullptr) {
+  if (nconn_dev != nullptr && !en.counted) {
     // connected configurations evaluated (+ the diagonal one per sample, already known from `logp`)
     RNNWF_COUNT_LAUNCH(); count_children_kernel<<<1, 32, 0, st>>>(en.have_children ? en.rows_dev : nullptr, en.have_children ? (en.rows_dev ? 0 : en.nchild_fixed) : 0, (long long*)nconn_dev);
   }
@@ -1417,9 +1489,9 @@ int rnnwf_local_energies_sym(rnnwf_handle h, rnnwf_symmetry_handle s, int hamilt
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   char* ws = static_cast<char*>(workspace_dev);
   EnumOut en;
-  if ((rc = enumerate_connected(m, hamiltonian, ham, ham_len, rows, samples_dev, eloc_dev, ws, S.e, st, en))) return rc;
+  if ((rc = enumerate_connected(m, hamiltonian, ham, ham_len, rows, samples_dev, eloc_dev, ws, S.e, st, en, (long long*)nconn_dev))) return rc;
   Child* d_children = reinterpret_cast<Child*>(ws + S.e.off_children);
-  if (nconn_dev != nullptr) {
+  if (nconn_dev != nullptr && !en.counted) {
     RNNWF_COUNT_LAUNCH(); count_children_kernel<<<1, 32, 0, st>>>(en.have_children ? en.rows_dev : nullptr, en.have_children ? (en.rows_dev ? 0 : en.nchild_fixed) : 0, (long long*)nconn_dev);
   }
   int8_t* d_cfg = reinterpret_cast<int8_t*>(ws + S.off_cfg);
