@@ -279,6 +279,13 @@ __global__ void __launch_bounds__(B4_THREADS, 1) bwd4_kernel(const Bwd4Params P)
           for (int kc = 0; kc < 8; ++kc) {
             const int j0 = 64 * sub + 8 * kc;
             float dsv[8], dgv[8], dmv[8];
+            float dh8[8];                                            // this thread's 8 d h values of the chunk: two 16-byte loads
+#pragma unroll
+            for (int i = 0; i < 8; i += 4) {
+              float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (live && j0 + i < nhp) v = *reinterpret_cast<const float4*>(dhq + j0 + i);
+              dh8[i] = v.x; dh8[i + 1] = v.y; dh8[i + 2] = v.z; dh8[i + 3] = v.w;
+            }
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
               const int j = j0 + i;
@@ -286,7 +293,7 @@ __global__ void __launch_bounds__(B4_THREADS, 1) bwd4_kernel(const Bwd4Params P)
               if (live && j < nh) {
                 const float4 wa = *reinterpret_cast<const float4*>(headW + j * 8);
                 const float4 wb = *reinterpret_cast<const float4*>(headW + j * 8 + 4);
-                float d = dhq[j];
+                float d = dh8[i];
                 d = fmaf(wa.x, dl[0], d); d = fmaf(wa.y, dl[1], d); d = fmaf(wa.z, dl[2], d); d = fmaf(wa.w, dl[3], d);
                 d = fmaf(wb.x, dl[4], d); d = fmaf(wb.y, dl[5], d); d = fmaf(wb.z, dl[6], d); d = fmaf(wb.w, dl[7], d);
                 const float4 g = __ldg(gq + (size_t)j * 128);        // (u, h~, m, -)
