@@ -66,6 +66,8 @@ struct rnnwf_model_impl {
   int tc_np = 0;
   unsigned char* d_tcB = nullptr;
   float* d_tcbias = nullptr;
+  bool van2 = false;            // vanilla 2D RNN, split precision: two-tile connected-configuration sweep (sweep_van2.cuh)
+  unsigned char* d_van2B = nullptr;
   float* d_wimgT = nullptr;     // tensorized cells: the reverse sweep's transposed TF32 weight image (bwd_tc.cuh), packed with the forward images
   // weight-gradient kernel work plan (dw_tc.cuh), cached on the device for the last row count it was built for
   mutable long long dw_rows = -1;

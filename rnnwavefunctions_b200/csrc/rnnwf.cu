@@ -19,6 +19,7 @@
 #include "backward.cuh"
 #include "symmetry.cuh"
 #include "gru1d.cuh"
+#include "sweep_van2.cuh"
 
 using namespace rnnwf;
 
@@ -33,6 +34,10 @@ cudaError_t g1_pack_bwd_launch(const G1PackSrc& S, int nh, int L, int D, int ND,
 namespace rnnwf {   // sweep_tc_inst.cu
 cudaError_t tc_sweep_set_smem(int cellk, bool biasmma, bool split, int smem_bytes);
 cudaError_t tc_sweep_launch(const SweepParams& P, int cellk, bool biasmma, bool split, int grid, int threads, int smem_bytes, cudaStream_t st);
+// sweep_van2_inst.cu
+cudaError_t van2_set_smem(int nhp, int Q);
+cudaError_t van2_launch(const SweepParams& P, int grid, cudaStream_t st);
+cudaError_t van2_pack_launch(const float* Wh, const float* Wv, int nh, int nhp, void* out, cudaStream_t st);
 // sweep_tc4_inst.cu
 cudaError_t tc4_sweep_set_smem(bool split, int smem_bytes);
 cudaError_t tc4_sweep_launch(const SweepParams& P, bool split, int grid, int threads, int smem_bytes, cudaStream_t st);
@@ -308,6 +313,7 @@ int build_model(rnnwf_model& m) {
   m.tc_enabled = (m.precision >= 1 && (m.cell == CELL_TENSGRU2D || m.cell == CELL_TENS2D || m.cell == CELL_VANILLA2D));
   m.tc_split = m.tc_enabled && m.precision == 2;
   m.tc4 = (m.precision >= 1 && m.cell == CELL_GRU4);
+  m.van2 = m.tc_split && m.cell == CELL_VANILLA2D && v2_supported(m.nh, m.nhp, m.Q, m.complex_head, m.u1) && std::getenv("RNNWF_NO_VAN2") == nullptr;
   m.tc4_split = m.tc4 && m.precision == 2;
   // small 1D models in the FFMA regime: dedicated kernels with the whole weight set resident in shared memory (gru1d.cuh)
   m.g1 = (m.precision == 0 && m.cell == CELL_GRU1D && g1_supported(m.nh, m.symL, m.Tsym) && std::getenv("RNNWF_NO_G1") == nullptr);
@@ -445,6 +451,16 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
     if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("1D GRU sweep launch: ") + cudaGetErrorString(e));
     return RNNWF_OK;
   }
+  if (m.van2 && P.mode == MODE_CHILD && P.rows_dev == nullptr) {
+    // vanilla 2D RNN, split precision, single-flip child list: two tiles per CTA (sweep_van2.cuh)
+    SweepParams P2 = P;
+    P2.tc_B = m.d_van2B;
+    const long long tiles = (P.rows + V2_ROWS - 1) / V2_ROWS;
+    RNNWF_COUNT_LAUNCH();
+    e = van2_launch(P2, (int)std::max(1LL, std::min<long long>((tiles + 1) / 2, m.num_sms)), st);
+    if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("two-tile vanilla sweep launch: ") + cudaGetErrorString(e));
+    return RNNWF_OK;
+  }
   if (m.tc_enabled) {
     RNNWF_COUNT_LAUNCH();
     const int cellk = (m.cell == CELL_VANILLA2D) ? 1 : (m.cell == CELL_TENS2D ? 2 : 0);
@@ -464,6 +480,10 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
 
 long long ring_bytes(const rnnwf_model& m, int grid, int Mp) {
   if (m.tc4) return (long long)grid * m.Q * t4_step_bytes(m.tc_np, m.tc4_split);   // FP16 chunk images of every site, per persistent CTA
+  if (m.van2) {      // (the two-tile sweep keeps an FP32 ring per tile group; the generic kernel's ring serves sampling / evaluation)
+    const long long slot = (long long)tc_ring_slot(m.nhp) * 2;
+    return (long long)grid * std::max((long long)m.ring_len * slot, v2_ring_bytes(m.ring_len, m.nhp));
+  }
   // tensor-core regime: one FP16 history image per slot in the fixed quad layout of sweep_tc.cuh (TC_RING_SLOT bytes)
   const long long slot = m.tc_enabled ? (long long)tc_ring_slot(m.nhp) * (m.tc_split ? 2 : 1) : (long long)Mp * m.nhp * 4;
   return (long long)grid * m.ring_len * slot;
@@ -697,6 +717,10 @@ int rnnwf_create(const rnnwf_config* cfg, rnnwf_handle* out) {
     const int cellk = (m->cell == CELL_VANILLA2D) ? 1 : (m->cell == CELL_TENS2D ? 2 : 0);
     CREATE_TRY(tc_sweep_set_smem(cellk, cellk != 1 && m->nh < m->nhp, m->tc_split, ts.total));
   }
+  if (m->van2) {
+    CREATE_TRY(cudaMalloc(&m->d_van2B, (size_t)v2_image_bytes(m->nhp)));
+    CREATE_TRY(van2_set_smem(m->nhp, m->Q));
+  }
   if (m->tc4) {
     const int t4s = T4Smem(t4_stages(m->Q), m->Q).total;
     CREATE_TRY(cudaMalloc(&m->d_tcB, (size_t)m->tc_np * (size_t)t4_pass_bytes(m->tc_np, m->tc4_split)));
@@ -733,7 +757,7 @@ int rnnwf_destroy(rnnwf_handle h) {
   if (h == nullptr) return RNNWF_OK;
   cudaFree(h->d_steps); cudaFree(h->d_variants); cudaFree(h->d_site_of_t); cudaFree(h->d_wpack);
   cudaFree(h->d_xtab); cudaFree(h->d_bias); cudaFree(h->d_head_w); cudaFree(h->d_head_b);
-  cudaFree(h->d_hamtab); cudaFree(h->d_g1pack); cudaFree(h->d_g1packT); cudaFree(h->d_tcB); cudaFree(h->d_tcbias); cudaFree(h->d_wimgT); cudaFree(h->d_dw_jobs); cudaFree(h->d_dw_cls); cudaFree(h->d_dw4_jobs); cudaFree(h->d_dw4_sites);
+  cudaFree(h->d_hamtab); cudaFree(h->d_g1pack); cudaFree(h->d_g1packT); cudaFree(h->d_tcB); cudaFree(h->d_tcbias); cudaFree(h->d_wimgT); cudaFree(h->d_van2B); cudaFree(h->d_dw_jobs); cudaFree(h->d_dw_cls); cudaFree(h->d_dw4_jobs); cudaFree(h->d_dw4_sites);
   delete h;
   return RNNWF_OK;
 }
@@ -853,6 +877,10 @@ int rnnwf_set_weights(rnnwf_handle h, const float* params_dev, void* stream) {
           params_dev + h->tensor("Wh")->offset, params_dev + h->tensor("Wv")->offset, h->nh, h->nhp, h->tc_split ? 1 : 0, reinterpret_cast<__half*>(h->d_tcB));
       RNNWF_COUNT_LAUNCH(); pack_tc_vanilla_bias_kernel<<<4, 256, 0, st>>>(params_dev + h->tensor("Uh")->offset, params_dev + h->tensor("Uv")->offset,
                                                                            params_dev + h->tensor("b")->offset, h->nh, h->nhp, h->d_tcbias);
+      if (h->van2) {
+        RNNWF_COUNT_LAUNCH();
+        CUDA_TRY(van2_pack_launch(params_dev + h->tensor("Wh")->offset, params_dev + h->tensor("Wv")->offset, h->nh, h->nhp, h->d_van2B, st));
+      }
     } else {
       const long long n = 3LL * h->tc_np * (ts.b_bytes / 2) * (h->tc_split ? 2 : 1);
       auto opt = [&](const char* nm) -> const float* { const TensorInfo* t = h->tensor(nm); return t ? params_dev + t->offset : nullptr; };
