@@ -456,12 +456,15 @@ class Bench:
             npass = (w["eng"]["num_units"] + 15) // 16
             subs_last = (w["eng"]["num_units"] - 16 * (npass - 1) + 3) // 4       # the last column pass is issued only as wide as its real units
             ncols = 112 * (npass - 1) + (28 * subs_last + 15) // 16 * 16
+            kname = "sweep_tc_kernel"
             if w["eng"]["cell"] == "VANILLA2D":
                 ncols = 112                                                       # one pass per site: 7 unit pieces x 4 threads x 4 units
+                if "two-tile sweep" in eng.describe():                            # sweep_van2_kernel: units in natural order, N = 64
+                    ncols, kname = 64, "sweep_van2_kernel"
             mma_per_kstep = 3 if precision == "tc3" else 1          # split precision: A_hi B_hi + A_lo B_hi + A_hi B_lo
             exec_flops = exec_sites * (mma_per_kstep * 2 * (2 * nhp) * ncols + 2 * w["eng"]["num_units"] * 4)
             achieved = exec_flops / (eloc_ms * 1e-3) / 1e12
-            return dict(common, bound="tensor", kernel=f"sweep_tc_kernel (MODE_CHILD{', split precision' if precision == 'tc3' else ''})",
+            return dict(common, bound="tensor", kernel=f"{kname} (MODE_CHILD{', split precision' if precision == 'tc3' else ''})",
                         achieved=achieved, peak=bf16_peak, unit="TFLOP/s", frac=achieved / bf16_peak, traffic=None, peak_source=peak_src,
                         executed_flops_per_launch=exec_flops, mma_columns_per_row_site=ncols,
                         note="executed = MMA flops actually issued (linearised class trick: 7 accumulator blocks per unit, narrow last pass; "
