@@ -12,8 +12,11 @@
 //   h_q = elu(x_h Uh + h_h Wh + x_v Uv + h_v Wv + b):   acc = [h_h | h_v] (128 x 2 nhp, FP16 hi + lo pairs scaled by 64)
 //                                                              x [Wh; Wv]^T (hi + lo scaled by 1024), three MMAs per K = 16 step;
 //   one-hot inputs and the bias from three small tables (b' of the neighbour variant, dUh, dUv: pack_tc_vanilla_bias_kernel);
-//   two-logit head (real wavefunction), accurate expf / logf, running log P in FP64; E_loc(parent) += coef exp((logP' - logP)/2).
-// History ring in global memory (FP32, [slot][row][units of this thread] -- written and read back by the same thread);
+//   two-logit head (real wavefunction): the two threads of a row exchange their partial logits through shared memory behind
+//   a 64-thread mbarrier and take turns in finishing a site (softmax, log in FP64, running log P in FP64);
+//   E_loc(parent) += coef exp((logP' - logP)/2).
+// History ring in global memory ([slot][row][units of this thread] as the operand's hi / lo words -- written and read back
+// by the same thread, no second split);
 // prefix reuse from the parents' saved history exactly as in the generic kernel.
 // TMEM per group: accumulator 64 columns + operand hi 64 + lo 64 (2 x 192 of 512 columns).
 // Every wait is bounded and traps instead of hanging.
@@ -33,7 +36,7 @@ constexpr int V2_GCOLS = 192;                         // TMEM columns per group:
 __host__ __device__ inline int v2_image_bytes(int nhp) { return 2 * (2 * nhp / 8) * (V2_N / 8) * 128; }
 
 struct V2Smem {
-  int off_B, off_bias, off_headw, off_step, off_sym, off_part, off_bar, off_tmem, total;
+  int off_B, off_bias, off_headw, off_step, off_sym, off_part, off_lp, off_bar, off_tmem, total;
   __host__ __device__ V2Smem(int nhp, int Q) {
     int o = 0;
     off_B = o;     o += v2_image_bytes(nhp);
@@ -41,8 +44,9 @@ struct V2Smem {
     off_headw = o; o += V2_N * 2 * 4 + 16;            // head weights [unit][2], biases [2]
     off_step = o;  o += Q * 8;                        // per site: (nbr0, nbr1, config offset, -)
     off_sym = o;   o += V2_GROUPS * ((Q * V2_ROWS + 15) & ~15);   // symbols of the group's tile, one byte per (site, row)
-    off_part = o;  o += V2_GROUPS * V2_ROWS * 8;      // partial logits of the upper unit half: [group][row] float2
-    off_bar = o;   o += 64;
+    off_part = o;  o += 2 * V2_GROUPS * V2_ROWS * 8;  // partial logits of the row's other unit half: [site parity][group][row] float2
+    off_lp = o;    o += V2_GROUPS * V2_ROWS * 8;      // tile end: the upper half's share of the row's log P (double)
+    off_bar = o;   o += 32 + 2 * V2_GROUPS * 4 * 8;   // operand / accumulator barriers, then [site parity][group][lane quarter] pair barriers
     off_tmem = o;  o += 16;
     total = o;
   }
@@ -73,6 +77,12 @@ __global__ void pack_van2_kernel(const float* __restrict__ Wh, const float* __re
   }
 }
 
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // NU4: 4-unit chunks per thread (units per thread = 4 NU4 = nhp / 2)
 template <int NU4>
 __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepParams P) {
@@ -90,11 +100,13 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
   uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(smem + L.off_tmem);
   uint64_t* const bar_op = bars + 0;                  // [2] group's operand written (256 arrivals)
   uint64_t* const bar_acc = bars + 2;                 // [2] group's accumulator complete (tcgen05.commit)
+  uint64_t* const bar_pair = bars + 4;                // [site parity 2][group 2][quarter 4]: the partner warp's partial logits are written (32 arrivals)
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int nh = P.nh;
 
   if (tid == 0) {
     for (int g = 0; g < V2_GROUPS; ++g) { mbar_init(bar_op + g, V2_GWARPS * 32); mbar_init(bar_acc + g, 1); }
+    for (int i = 0; i < 2 * V2_GROUPS * 4; ++i) mbar_init(bar_pair + i, 32);
     fence_mbar_init();
   }
   if (warp == 2) tc_alloc(tmem_slot, 512);
@@ -163,20 +175,18 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
     const uint32_t a_hi = acc + 64u, a_lo = acc + 128u;
     uint8_t* const symS = smem + L.off_sym + (size_t)g * ((P.Q * V2_ROWS + 15) & ~15);
     float2* const partS = reinterpret_cast<float2*>(smem + L.off_part) + g * V2_ROWS;
+    double* const lpS = reinterpret_cast<double*>(smem + L.off_lp) + g * V2_ROWS;
     float* const ring = P.ring + ((size_t)blockIdx.x * V2_GROUPS + g) * (size_t)P.ring_len * V2_ROWS * NHP + (size_t)row * NHP + u0;
     const int gbar = 1 + g;                             // named barrier of the group's 256 threads
     uint32_t n = 0;
 
-    // write U2 hidden-state values of neighbour slot `slot` (this thread's units) into the operand as hi / lo pairs
-    auto put_operand = [&](int slot, const float (&v)[U2]) {
+    // operand words of 4-unit chunk c: (hi pair 0, hi pair 1, lo pair 0, lo pair 1) of 64 h -- also the ring's storage form
+    auto put_operand = [&](int slot, const uint4 (&w)[NU4]) {
       const uint32_t c0 = (uint32_t)((slot * NHP + u0) >> 1);
 #pragma unroll
       for (int c = 0; c < NU4; ++c) {
-        uint2 hi, lo;
-        split_f16x2(v[4 * c] * HS, v[4 * c + 1] * HS, hi.x, lo.x);
-        split_f16x2(v[4 * c + 2] * HS, v[4 * c + 3] * HS, hi.y, lo.y);
-        tc_st2(a_hi + c0 + 2u * c, hi);
-        tc_st2(a_lo + c0 + 2u * c, lo);
+        tc_st2(a_hi + c0 + 2u * c, make_uint2(w[c].x, w[c].y));
+        tc_st2(a_lo + c0 + 2u * c, make_uint2(w[c].z, w[c].w));
       }
     };
     for (long long k = 0;; ++k) {
@@ -200,52 +210,53 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
         }
       }
       asm volatile("bar.sync %0, %1;" ::"r"(gbar), "n"(V2_GWARPS * 32) : "memory");
-      // hidden state of an earlier site for this thread's units: own ring (sites >= q0 of this tile) or the parent's saved history
-      auto load_h = [&](int nb, float (&v)[U2]) {
+      // hidden state of an earlier site for this thread's units, as operand words: own ring (sites >= q0 of this tile) or
+      // the parent's saved FP32 history (split here)
+      auto load_h = [&](int nb, uint4 (&w)[NU4]) {
         if (nb < 0 || !live) {
 #pragma unroll
-          for (int i = 0; i < U2; ++i) v[i] = 0.f;
+          for (int c = 0; c < NU4; ++c) w[c] = make_uint4(0u, 0u, 0u, 0u);
         } else if (nb >= q0 || P.par_hist == nullptr) {
-          const float* src = ring + (size_t)(nb % P.ring_len) * V2_ROWS * NHP;
+          const uint4* src = reinterpret_cast<const uint4*>(ring + (size_t)(nb % P.ring_len) * V2_ROWS * NHP);
 #pragma unroll
-          for (int c = 0; c < NU4; ++c) {
-            const float4 x = __ldcg(reinterpret_cast<const float4*>(src) + c);
-            v[4 * c] = x.x; v[4 * c + 1] = x.y; v[4 * c + 2] = x.z; v[4 * c + 3] = x.w;
-          }
+          for (int c = 0; c < NU4; ++c) w[c] = __ldcg(src + c);
         } else {
           const float* src = P.par_hist + ((size_t)nb * (size_t)P.par_rows + (size_t)ch.parent) * P.nhp + u0;
 #pragma unroll
           for (int c = 0; c < NU4; ++c) {
             float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
             if (u0 + 4 * c < P.nhp) x = __ldg(reinterpret_cast<const float4*>(src) + c);
-            v[4 * c] = (u0 + 4 * c < nh) ? x.x : 0.f; v[4 * c + 1] = (u0 + 4 * c + 1 < nh) ? x.y : 0.f;
-            v[4 * c + 2] = (u0 + 4 * c + 2 < nh) ? x.z : 0.f; v[4 * c + 3] = (u0 + 4 * c + 3 < nh) ? x.w : 0.f;
+            if (u0 + 4 * c >= nh) x.x = 0.f;
+            if (u0 + 4 * c + 1 >= nh) x.y = 0.f;
+            if (u0 + 4 * c + 2 >= nh) x.z = 0.f;
+            if (u0 + 4 * c + 3 >= nh) x.w = 0.f;
+            split_f16x2(x.x * HS, x.y * HS, w[c].x, w[c].z);
+            split_f16x2(x.z * HS, x.w * HS, w[c].y, w[c].w);
           }
         }
       };
       // ---- operand of the tile's first site: both neighbours from the history
       {
         const short4 e0 = stepS[q0];
-        float v[U2];
-        load_h(e0.x, v);
+        uint4 w[NU4];
+        load_h(e0.x, w);
         __syncwarp();
-        put_operand(0, v);
-        load_h(e0.y, v);
-        put_operand(1, v);
+        put_operand(0, w);
+        load_h(e0.y, w);
+        put_operand(1, w);
         tc_wait_st();
         tc_fence_before();
         mbar_arrive(bar_op + g);
       }
-      double rlogp = 0.0;
+      double rlogp = 0.0;                                  // this thread's share of the row's log P (the sites it finished)
       for (int q = q0; q < P.Q; ++q, ++n) {
         const short4 eq = stepS[q];
         const bool has_next = q + 1 < P.Q;
         // the older neighbour of the next site (not this site's output): fetched before the wait for this site's accumulators
-        short4 en = make_short4(-1, -1, 0, 0);
         int carry_slot = 0;
-        float vold[U2];
+        uint4 vold[NU4];
         if (has_next) {
-          en = stepS[q + 1];
+          const short4 en = stepS[q + 1];
           carry_slot = (en.x == q) ? 0 : 1;                 // the next site's neighbour that is this site: horizontal or (row turn) vertical
           load_h(carry_slot == 0 ? en.y : en.x, vold);
         }
@@ -254,60 +265,76 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
         const float* bv = biasS + (((eq.x >= 0) ? 1 : 0) + ((eq.y >= 0) ? 2 : 0)) * V2_N + u0;
         const float* duh = biasS + 4 * V2_N + u0;
         const float* duv = biasS + 5 * V2_N + u0;
+        uint4* const rdst = reinterpret_cast<uint4*>(ring + (size_t)(q % P.ring_len) * V2_ROWS * NHP);
+        const uint32_t cnew = (uint32_t)((carry_slot * NHP + u0) >> 1);
         mbar_wait(bar_acc + g, n & 1u);
         __syncwarp();
         tc_fence_after();
-        float hnew[U2];
+        uint32_t d[NU4][4];
+#pragma unroll
+        for (int c = 0; c < NU4; ++c) tc_ld4(acc + (uint32_t)(u0 + 4 * c), d[c]);
+        tc_wait_ld();
+        // all MMAs of this site have completed: the operand may be rewritten chunk by chunk
         float lg0 = 0.f, lg1 = 0.f;
 #pragma unroll
         for (int c = 0; c < NU4; ++c) {
-          uint32_t d[4];
-          tc_ld4(acc + (uint32_t)(u0 + 4 * c), d);
-          tc_wait_ld();
           const float4 b4 = *reinterpret_cast<const float4*>(bv + 4 * c);
           const float4 h4 = *reinterpret_cast<const float4*>(duh + 4 * c);
           const float4 v4 = *reinterpret_cast<const float4*>(duv + 4 * c);
           const float bb[4] = {b4.x, b4.y, b4.z, b4.w}, hh[4] = {h4.x, h4.y, h4.z, h4.w}, vv[4] = {v4.x, v4.y, v4.z, v4.w};
+          float hv[4];
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            const float x = fmaf(cu, vv[e], fmaf(cl, hh[e], fmaf(__uint_as_float(d[e]), DS, bb[e])));
-            const float hv = (x > 0.f) ? x : (expf(x) - 1.0f);         // elu; padding units: zero weights and biases -> 0
-            hnew[4 * c + e] = live ? hv : 0.f;
+            const float x = fmaf(cu, vv[e], fmaf(cl, hh[e], fmaf(__uint_as_float(d[c][e]), DS, bb[e])));
+            // elu, branch-free: exp(min(x, 0)) - 1 by ex2.approx (2 ulp, the class of expf); padding units: zero weights and biases -> 0
+            const float em = ex2_approx(fminf(x, 0.f) * 1.4426950408889634f) - 1.0f;
+            hv[e] = live ? ((x > 0.f) ? x : em) : 0.f;
             const float2 w = *reinterpret_cast<const float2*>(headW + 2 * (u0 + 4 * c + e));
-            lg0 = fmaf(hnew[4 * c + e], w.x, lg0); lg1 = fmaf(hnew[4 * c + e], w.y, lg1);
+            lg0 = fmaf(hv[e], w.x, lg0); lg1 = fmaf(hv[e], w.y, lg1);
+          }
+          uint4 w;
+          split_f16x2(hv[0] * HS, hv[1] * HS, w.x, w.z);
+          split_f16x2(hv[2] * HS, hv[3] * HS, w.y, w.w);
+          // ring image of this site (the same thread reads it back as a vertical neighbour ~2 Nx sites later)
+          if (live) __stcg(rdst + c, w);
+          if (has_next) {
+            tc_st2(a_hi + cnew + 2u * c, make_uint2(w.x, w.y));
+            tc_st2(a_lo + cnew + 2u * c, make_uint2(w.z, w.w));
           }
         }
-        // ---- ring image of this site (the same thread reads it back as a vertical neighbour ~2 Nx sites later)
-        if (live) {
-          float* dst = ring + (size_t)(q % P.ring_len) * V2_ROWS * NHP;
-#pragma unroll
-          for (int c = 0; c < NU4; ++c)
-            __stcg(reinterpret_cast<float4*>(dst) + c, make_float4(hnew[4 * c], hnew[4 * c + 1], hnew[4 * c + 2], hnew[4 * c + 3]));
-        }
-        // ---- operand of the next site: all MMAs of this site have completed (their accumulator was just read)
+        // ---- operand of the next site
         if (has_next) {
-          __syncwarp();
-          put_operand(carry_slot, hnew);
           put_operand(1 - carry_slot, vold);
           tc_wait_st();
           tc_fence_before();
           mbar_arrive(bar_op + g);
         }
-        // ---- head: the two unit halves of a row meet in shared memory; the lower half's thread finishes the row
-        if (half == 1) partS[row] = make_float2(lg0, lg1);
-        asm volatile("bar.sync %0, %1;" ::"r"(gbar), "n"(V2_GWARPS * 32) : "memory");
-        if (half == 0 && live) {
-          const float2 o = partS[row];
-          float p0 = lg0 + o.x + headW[2 * V2_N], p1 = lg1 + o.y + headW[2 * V2_N + 1];
-          const float mx = fmaxf(p0, p1);
-          p0 = expf(p0 - mx); p1 = expf(p1 - mx);
-          const int sy = symS[q * V2_ROWS + row];
-          rlogp += log((double)((sy ? p1 : p0) / (p0 + p1)));
+        // ---- head: the two unit halves of a row meet in shared memory; the halves take turns in finishing a site
+        {
+          const uint32_t b = n & 1u;
+          float2* const ps = partS + b * (V2_GROUPS * V2_ROWS);
+          uint64_t* const pb = bar_pair + (b * V2_GROUPS + g) * 4 + quarter;
+          if (half != (int)b) {
+            ps[row] = make_float2(lg0, lg1);
+            mbar_arrive(pb);
+          } else {
+            mbar_wait(pb, (n >> 1) & 1u);
+            if (live) {
+              const float2 o = ps[row];
+              float p0 = lg0 + o.x + headW[2 * V2_N], p1 = lg1 + o.y + headW[2 * V2_N + 1];
+              const float mx = fmaxf(p0, p1);
+              p0 = expf(p0 - mx); p1 = expf(p1 - mx);
+              const int sy = symS[q * V2_ROWS + row];
+              rlogp += log((double)((sy ? p1 : p0) / (p0 + p1)));
+            }
+          }
         }
-        asm volatile("bar.sync %0, %1;" ::"r"(gbar), "n"(V2_GWARPS * 32) : "memory");      // partS may be rewritten
       }
       // ---- tile result: E_loc(parent) += <sigma'|H|sigma> psi(sigma') / psi(sigma)
+      if (half == 1) lpS[row] = rlogp;
+      asm volatile("bar.sync %0, %1;" ::"r"(gbar), "n"(V2_GWARPS * 32) : "memory");
       if (half == 0 && live) {
+        rlogp += lpS[row];
         double base_lp = P.par_logp[ch.parent];
         if (q0 > 0 && P.par_cum != nullptr) base_lp -= P.par_cum[(size_t)(q0 - 1) * (size_t)P.par_rows + ch.parent].x;
         atomicAdd(P.eloc + 2 * (size_t)ch.parent, exp(0.5 * (rlogp - base_lp)) * (double)ch.coef);
