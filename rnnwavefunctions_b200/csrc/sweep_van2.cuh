@@ -29,7 +29,8 @@ constexpr int V2_ROWS = 128;
 constexpr int V2_N = 64;                              // accumulator columns (units, natural order; nhp <= 64)
 constexpr int V2_GROUPS = 2;
 constexpr int V2_GWARPS = 8;                          // element-wise warps per group: (lane quarter 4) x (unit half 2)
-constexpr int V2_THREADS = 32 * (4 + V2_GROUPS * V2_GWARPS);   // warps 0, 1: MMA issue of group 0, 1; warps 2, 3 spare
+constexpr int V2_THREADS = 32 * (2 + V2_GROUPS * V2_GWARPS);   // warps 0, 1: MMA issue of group 0, 1 (576 threads: 112 registers each)
+constexpr int V2_TABP = V2_N + 4;                     // pitch of the input / bias table (rows of one warp's lanes fall into distinct banks)
 constexpr int V2_GCOLS = 192;                         // TMEM columns per group: [acc 64 | operand hi 64 | operand lo 64]
 
 // weight image: [part 2: hi, lo][k-core 2 nhp / 8][n-core 8][8 rows (n)][8 halves (k)],  B[n][k] = 1024 * W_slot(k)[unit(k)][n]
@@ -40,11 +41,11 @@ struct V2Smem {
   __host__ __device__ V2Smem(int nhp, int Q) {
     int o = 0;
     off_B = o;     o += v2_image_bytes(nhp);
-    off_bias = o;  o += 6 * V2_N * 4;                 // b' (4 variants), dUh, dUv: [6][64]
-    off_headw = o; o += V2_N * 2 * 4 + 16;            // head weights [unit][2], biases [2]
+    off_bias = o;  o += 16 * V2_TABP * 4;             // b' (neighbour variant) + sym_l dUh + sym_u dUv: [variant 4][sym_l 2][sym_u 2][68]
+    off_headw = o; o += V2_N * 4 + 16;                // head: w[unit][1] - w[unit][0], then b[1] - b[0]
     off_step = o;  o += Q * 8;                        // per site: (nbr0, nbr1, config offset, -)
     off_sym = o;   o += V2_GROUPS * ((Q * V2_ROWS + 15) & ~15);   // symbols of the group's tile, one byte per (site, row)
-    off_part = o;  o += 2 * V2_GROUPS * V2_ROWS * 8;  // partial logits of the row's other unit half: [site parity][group][row] float2
+    off_part = o;  o += 2 * V2_GROUPS * V2_ROWS * 4;  // partial logit difference of the row's other unit half: [site parity][group][row]
     off_lp = o;    o += V2_GROUPS * V2_ROWS * 8;      // tile end: the upper half's share of the row's log P (double)
     off_bar = o;   o += 32 + 2 * V2_GROUPS * 4 * 8;   // operand / accumulator barriers, then [site parity][group][lane quarter] pair barriers
     off_tmem = o;  o += 16;
@@ -54,7 +55,7 @@ struct V2Smem {
 inline bool v2_supported(int nh, int nhp, int Q, int complex_head, int u1) {
   return !complex_head && !u1 && nhp <= V2_N && (nhp == 32 || nhp == 48 || nhp == 56 || nhp == 64) && nh <= nhp && V2Smem(nhp, Q).total <= 200 * 1024;
 }
-// ring bytes per CTA: [group][slot ring_len][row 128][nhp] FP32
+// ring bytes per CTA: [group][slot ring_len][unit half 2][chunk][row 128] 16-byte words = 4 bytes per (row, unit)
 __host__ __device__ inline long long v2_ring_bytes(int ring_len, int nhp) { return (long long)V2_GROUPS * ring_len * V2_ROWS * nhp * 4; }
 
 template <int UNUSED = 0>
@@ -94,7 +95,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
   const V2Smem L(NHP, P.Q);
   unsigned char* const smem = v2_smem;
   float* const biasS = reinterpret_cast<float*>(smem + L.off_bias);
-  float* const headW = reinterpret_cast<float*>(smem + L.off_headw);          // [64][2], then [2] biases at 128
+  float* const headW = reinterpret_cast<float*>(smem + L.off_headw);          // [64] logit-difference weights, then the bias difference
   short4* const stepS = reinterpret_cast<short4*>(smem + L.off_step);
   uint64_t* const bars = reinterpret_cast<uint64_t*>(smem + L.off_bar);
   uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(smem + L.off_tmem);
@@ -109,17 +110,17 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
     for (int i = 0; i < 2 * V2_GROUPS * 4; ++i) mbar_init(bar_pair + i, 32);
     fence_mbar_init();
   }
-  if (warp == 2) tc_alloc(tmem_slot, 512);
+  if (warp == 0) tc_alloc(tmem_slot, 512);
   for (int i = tid; i < v2_image_bytes(NHP) / 16; i += V2_THREADS)
     reinterpret_cast<uint4*>(smem + L.off_B)[i] = __ldg(reinterpret_cast<const uint4*>(P.tc_B) + i);
-  for (int i = tid; i < 6 * V2_N; i += V2_THREADS) {
-    const int which = i / V2_N, j = i % V2_N;
-    biasS[i] = (j < NHP) ? P.tc_bias[which * NHP + j] : 0.f;
+  for (int i = tid; i < 16 * V2_TABP; i += V2_THREADS) {
+    const int which = i / V2_TABP, j = i % V2_TABP;
+    const int var = which >> 2, sl = (which >> 1) & 1, su = which & 1;
+    biasS[i] = (j < NHP) ? P.tc_bias[var * NHP + j] + (sl ? P.tc_bias[4 * NHP + j] : 0.f) + (su ? P.tc_bias[5 * NHP + j] : 0.f) : 0.f;
   }
-  for (int i = tid; i < V2_N * 2 + 2; i += V2_THREADS) {
-    if (i < V2_N * 2) { const int j = i >> 1, d = i & 1; headW[i] = (j < nh) ? P.head_w[j * P.ND + d] : 0.f; }
-    else headW[i] = P.head_b[i - V2_N * 2];
-  }
+  // two-class softmax: only the difference of the logits enters log p
+  for (int i = tid; i <= V2_N; i += V2_THREADS)
+    headW[i] = (i == V2_N) ? P.head_b[1] - P.head_b[0] : ((i < nh) ? P.head_w[i * P.ND + 1] - P.head_w[i * P.ND] : 0.f);
   for (int i = tid; i < P.Q; i += V2_THREADS) stepS[i] = make_short4(P.steps[i].nbr[0], P.steps[i].nbr[1], P.steps[i].site, 0);
   fence_proxy_async_smem();                           // the weight image is read by the tensor core (async proxy)
   tc_fence_before();
@@ -162,10 +163,10 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
         __syncwarp();
       }
     }
-  } else if (warp >= 4) {
+  } else {
     // ======================= element-wise warps: group, lane quarter, unit half =======================
-    const int g = (warp - 4) / V2_GWARPS;
-    const int wg = (warp - 4) % V2_GWARPS;
+    const int g = (warp - 2) / V2_GWARPS;
+    const int wg = (warp - 2) % V2_GWARPS;
     const int quarter = warp & 3;                       // TMEM lanes this warp may touch: 32 quarter .. + 31
     const int half = wg >> 2;                           // (warps 4..7 / 12..15: half 0; 8..11 / 16..19: half 1 -- warp & 3 runs 0..3 in each)
     const int row = (quarter << 5) + lane;
@@ -174,20 +175,29 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
     const uint32_t acc = tmem_base + lane_base + (uint32_t)(g * V2_GCOLS);
     const uint32_t a_hi = acc + 64u, a_lo = acc + 128u;
     uint8_t* const symS = smem + L.off_sym + (size_t)g * ((P.Q * V2_ROWS + 15) & ~15);
-    float2* const partS = reinterpret_cast<float2*>(smem + L.off_part) + g * V2_ROWS;
+    float* const partS = reinterpret_cast<float*>(smem + L.off_part) + g * V2_ROWS;
     double* const lpS = reinterpret_cast<double*>(smem + L.off_lp) + g * V2_ROWS;
-    float* const ring = P.ring + ((size_t)blockIdx.x * V2_GROUPS + g) * (size_t)P.ring_len * V2_ROWS * NHP + (size_t)row * NHP + u0;
+    // ring of this thread: [slot][unit half][chunk][row] 16-byte operand words (a warp's store covers 512 contiguous bytes)
+    uint4* const ring = reinterpret_cast<uint4*>(P.ring) + (((size_t)blockIdx.x * V2_GROUPS + g) * (size_t)P.ring_len * 2 + half) * (NU4 * V2_ROWS) + row;
+    constexpr int RING_SLOT = 2 * NU4 * V2_ROWS;        // uint4 per slot
+    const int ring_len = P.ring_len;
     const int gbar = 1 + g;                             // named barrier of the group's 256 threads
     uint32_t n = 0;
 
-    // operand words of 4-unit chunk c: (hi pair 0, hi pair 1, lo pair 0, lo pair 1) of 64 h -- also the ring's storage form
-    auto put_operand = [&](int slot, const uint4 (&w)[NU4]) {
+    // the thread's 2 NU4 hi words and 2 NU4 lo words of neighbour slot `slot` into the operand, in the widest stores that fit
+    auto put_words = [&](uint32_t t, const uint32_t (&w)[2 * NU4]) {
+      constexpr int W = 2 * NU4;
+      if constexpr (W >= 8) tc_st8(t, w[0], w[1], w[2], w[3], w[4], w[5], w[6], w[7]);
+      if constexpr (W >= 16) tc_st8(t + 8u, w[8], w[9], w[10], w[11], w[12], w[13], w[14], w[15]);
+      constexpr int O = W / 8 * 8;
+      if constexpr (W - O >= 4) tc_st4(t + (uint32_t)O, make_uint4(w[O], w[O + 1], w[O + 2], w[O + 3]));
+      constexpr int O2 = O + (W - O) / 4 * 4;
+      if constexpr (W - O2 >= 2) tc_st2(t + (uint32_t)O2, make_uint2(w[O2], w[O2 + 1]));
+    };
+    auto put_operand = [&](int slot, const uint32_t (&hi)[2 * NU4], const uint32_t (&lo)[2 * NU4]) {
       const uint32_t c0 = (uint32_t)((slot * NHP + u0) >> 1);
-#pragma unroll
-      for (int c = 0; c < NU4; ++c) {
-        tc_st2(a_hi + c0 + 2u * c, make_uint2(w[c].x, w[c].y));
-        tc_st2(a_lo + c0 + 2u * c, make_uint2(w[c].z, w[c].w));
-      }
+      put_words(a_hi + c0, hi);
+      put_words(a_lo + c0, lo);
     };
     for (long long k = 0;; ++k) {
       const long long tile = tile_of(g, k);
@@ -210,16 +220,19 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
         }
       }
       asm volatile("bar.sync %0, %1;" ::"r"(gbar), "n"(V2_GWARPS * 32) : "memory");
-      // hidden state of an earlier site for this thread's units, as operand words: own ring (sites >= q0 of this tile) or
-      // the parent's saved FP32 history (split here)
-      auto load_h = [&](int nb, uint4 (&w)[NU4]) {
+      // hidden state of an earlier site for this thread's units, as operand words: own ring (sites >= q0 of this tile; `rs` =
+      // the site's ring slot) or the parent's saved FP32 history (split here)
+      auto load_h = [&](int nb, int rs, uint32_t (&hi)[2 * NU4], uint32_t (&lo)[2 * NU4]) {
         if (nb < 0 || !live) {
 #pragma unroll
-          for (int c = 0; c < NU4; ++c) w[c] = make_uint4(0u, 0u, 0u, 0u);
+          for (int i = 0; i < 2 * NU4; ++i) { hi[i] = 0u; lo[i] = 0u; }
         } else if (nb >= q0 || P.par_hist == nullptr) {
-          const uint4* src = reinterpret_cast<const uint4*>(ring + (size_t)(nb % P.ring_len) * V2_ROWS * NHP);
+          const uint4* src = ring + (size_t)rs * RING_SLOT;
 #pragma unroll
-          for (int c = 0; c < NU4; ++c) w[c] = __ldcg(src + c);
+          for (int c = 0; c < NU4; ++c) {
+            const uint4 w = __ldcg(src + c * V2_ROWS);
+            hi[2 * c] = w.x; hi[2 * c + 1] = w.y; lo[2 * c] = w.z; lo[2 * c + 1] = w.w;
+          }
         } else {
           const float* src = P.par_hist + ((size_t)nb * (size_t)P.par_rows + (size_t)ch.parent) * P.nhp + u0;
 #pragma unroll
@@ -230,43 +243,45 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
             if (u0 + 4 * c + 1 >= nh) x.y = 0.f;
             if (u0 + 4 * c + 2 >= nh) x.z = 0.f;
             if (u0 + 4 * c + 3 >= nh) x.w = 0.f;
-            split_f16x2(x.x * HS, x.y * HS, w[c].x, w[c].z);
-            split_f16x2(x.z * HS, x.w * HS, w[c].y, w[c].w);
+            split_f16x2(x.x * HS, x.y * HS, hi[2 * c], lo[2 * c]);
+            split_f16x2(x.z * HS, x.w * HS, hi[2 * c + 1], lo[2 * c + 1]);
           }
         }
       };
       // ---- operand of the tile's first site: both neighbours from the history
+      short4 eq = stepS[q0];
       {
-        const short4 e0 = stepS[q0];
-        uint4 w[NU4];
-        load_h(e0.x, w);
+        uint32_t hi[2 * NU4], lo[2 * NU4];
+        load_h(eq.x, eq.x >= 0 ? eq.x % ring_len : 0, hi, lo);
         __syncwarp();
-        put_operand(0, w);
-        load_h(e0.y, w);
-        put_operand(1, w);
+        put_operand(0, hi, lo);
+        load_h(eq.y, eq.y >= 0 ? eq.y % ring_len : 0, hi, lo);
+        put_operand(1, hi, lo);
         tc_wait_st();
         tc_fence_before();
         mbar_arrive(bar_op + g);
       }
       double rlogp = 0.0;                                  // this thread's share of the row's log P (the sites it finished)
+      int sq = q0 % ring_len;                              // ring slot of site q
       for (int q = q0; q < P.Q; ++q, ++n) {
-        const short4 eq = stepS[q];
         const bool has_next = q + 1 < P.Q;
+        const int sq1 = (sq + 1 == ring_len) ? 0 : sq + 1;
         // the older neighbour of the next site (not this site's output): fetched before the wait for this site's accumulators
+        short4 en = make_short4(-1, -1, 0, 0);
         int carry_slot = 0;
-        uint4 vold[NU4];
+        uint32_t ohi[2 * NU4], olo[2 * NU4];
         if (has_next) {
-          const short4 en = stepS[q + 1];
+          en = stepS[q + 1];
           carry_slot = (en.x == q) ? 0 : 1;                 // the next site's neighbour that is this site: horizontal or (row turn) vertical
-          load_h(carry_slot == 0 ? en.y : en.x, vold);
+          const int nbo = carry_slot == 0 ? en.y : en.x;
+          int rs = sq1 - (q + 1 - nbo);                     // (look-back < ring_len)
+          if (rs < 0) rs += ring_len;
+          load_h(nbo, rs, ohi, olo);
         }
-        const float cl = (eq.x >= 0) ? (float)symS[eq.x * V2_ROWS + row] : 0.f;
-        const float cu = (eq.y >= 0) ? (float)symS[eq.y * V2_ROWS + row] : 0.f;
-        const float* bv = biasS + (((eq.x >= 0) ? 1 : 0) + ((eq.y >= 0) ? 2 : 0)) * V2_N + u0;
-        const float* duh = biasS + 4 * V2_N + u0;
-        const float* duv = biasS + 5 * V2_N + u0;
-        uint4* const rdst = reinterpret_cast<uint4*>(ring + (size_t)(q % P.ring_len) * V2_ROWS * NHP);
-        const uint32_t cnew = (uint32_t)((carry_slot * NHP + u0) >> 1);
+        const int sl = (eq.x >= 0) ? (int)symS[eq.x * V2_ROWS + row] : 0;
+        const int su = (eq.y >= 0) ? (int)symS[eq.y * V2_ROWS + row] : 0;
+        const float* bv = biasS + ((((eq.x >= 0) ? 1 : 0) + ((eq.y >= 0) ? 2 : 0)) * 4 + sl * 2 + su) * V2_TABP + u0;
+        uint4* const rdst = ring + (size_t)sq * RING_SLOT;
         mbar_wait(bar_acc + g, n & 1u);
         __syncwarp();
         tc_fence_after();
@@ -274,37 +289,39 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
 #pragma unroll
         for (int c = 0; c < NU4; ++c) tc_ld4(acc + (uint32_t)(u0 + 4 * c), d[c]);
         tc_wait_ld();
-        // all MMAs of this site have completed: the operand may be rewritten chunk by chunk
-        float lg0 = 0.f, lg1 = 0.f;
+        // ---- new hidden state in place of the accumulators (no ordered instruction in this loop: loads and MUFUs pipeline freely)
+        float lg = 0.f;
 #pragma unroll
         for (int c = 0; c < NU4; ++c) {
           const float4 b4 = *reinterpret_cast<const float4*>(bv + 4 * c);
-          const float4 h4 = *reinterpret_cast<const float4*>(duh + 4 * c);
-          const float4 v4 = *reinterpret_cast<const float4*>(duv + 4 * c);
-          const float bb[4] = {b4.x, b4.y, b4.z, b4.w}, hh[4] = {h4.x, h4.y, h4.z, h4.w}, vv[4] = {v4.x, v4.y, v4.z, v4.w};
-          float hv[4];
+          const float4 w4 = *reinterpret_cast<const float4*>(headW + u0 + 4 * c);
+          const float bb[4] = {b4.x, b4.y, b4.z, b4.w}, ww[4] = {w4.x, w4.y, w4.z, w4.w};
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            const float x = fmaf(cu, vv[e], fmaf(cl, hh[e], fmaf(__uint_as_float(d[c][e]), DS, bb[e])));
+            const float x = fmaf(__uint_as_float(d[c][e]), DS, bb[e]);
             // elu, branch-free: exp(min(x, 0)) - 1 by ex2.approx (2 ulp, the class of expf); padding units: zero weights and biases -> 0
             const float em = ex2_approx(fminf(x, 0.f) * 1.4426950408889634f) - 1.0f;
-            hv[e] = live ? ((x > 0.f) ? x : em) : 0.f;
-            const float2 w = *reinterpret_cast<const float2*>(headW + 2 * (u0 + 4 * c + e));
-            lg0 = fmaf(hv[e], w.x, lg0); lg1 = fmaf(hv[e], w.y, lg1);
+            const float hv = live ? ((x > 0.f) ? x : em) : 0.f;
+            lg = fmaf(hv, ww[e], lg);
+            d[c][e] = __float_as_uint(hv * HS);
           }
-          uint4 w;
-          split_f16x2(hv[0] * HS, hv[1] * HS, w.x, w.z);
-          split_f16x2(hv[2] * HS, hv[3] * HS, w.y, w.w);
-          // ring image of this site (the same thread reads it back as a vertical neighbour ~2 Nx sites later)
-          if (live) __stcg(rdst + c, w);
-          if (has_next) {
-            tc_st2(a_hi + cnew + 2u * c, make_uint2(w.x, w.y));
-            tc_st2(a_lo + cnew + 2u * c, make_uint2(w.z, w.w));
-          }
+        }
+        // ---- hi / lo words of the new state: the ring image of this site (the same thread reads it back as a vertical
+        // neighbour ~2 Nx sites later) and, all MMAs of this site having completed, the next site's operand
+        uint32_t nhi[2 * NU4], nlo[2 * NU4];
+#pragma unroll
+        for (int c = 0; c < NU4; ++c) {
+          split_f16x2(__uint_as_float(d[c][0]), __uint_as_float(d[c][1]), nhi[2 * c], nlo[2 * c]);
+          split_f16x2(__uint_as_float(d[c][2]), __uint_as_float(d[c][3]), nhi[2 * c + 1], nlo[2 * c + 1]);
+        }
+        if (live) {
+#pragma unroll
+          for (int c = 0; c < NU4; ++c) __stcg(rdst + c * V2_ROWS, make_uint4(nhi[2 * c], nhi[2 * c + 1], nlo[2 * c], nlo[2 * c + 1]));
         }
         // ---- operand of the next site
         if (has_next) {
-          put_operand(1 - carry_slot, vold);
+          put_operand(carry_slot, nhi, nlo);
+          put_operand(1 - carry_slot, ohi, olo);
           tc_wait_st();
           tc_fence_before();
           mbar_arrive(bar_op + g);
@@ -312,23 +329,23 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
         // ---- head: the two unit halves of a row meet in shared memory; the halves take turns in finishing a site
         {
           const uint32_t b = n & 1u;
-          float2* const ps = partS + b * (V2_GROUPS * V2_ROWS);
+          float* const ps = partS + b * (V2_GROUPS * V2_ROWS);
           uint64_t* const pb = bar_pair + (b * V2_GROUPS + g) * 4 + quarter;
           if (half != (int)b) {
-            ps[row] = make_float2(lg0, lg1);
+            ps[row] = lg;
             mbar_arrive(pb);
           } else {
             mbar_wait(pb, (n >> 1) & 1u);
             if (live) {
-              const float2 o = ps[row];
-              float p0 = lg0 + o.x + headW[2 * V2_N], p1 = lg1 + o.y + headW[2 * V2_N + 1];
-              const float mx = fmaxf(p0, p1);
-              p0 = expf(p0 - mx); p1 = expf(p1 - mx);
-              const int sy = symS[q * V2_ROWS + row];
-              rlogp += log((double)((sy ? p1 : p0) / (p0 + p1)));
+              // log p(sy) = -softplus(logit(other) - logit(sy))
+              const float dl = lg + ps[row] + headW[V2_N];
+              const float z = symS[q * V2_ROWS + row] ? -dl : dl;
+              rlogp -= (double)(fmaxf(z, 0.f) + logf(1.0f + expf(-fabsf(z))));
             }
           }
         }
+        eq = en;
+        sq = sq1;
       }
       // ---- tile result: E_loc(parent) += <sigma'|H|sigma> psi(sigma') / psi(sigma)
       if (half == 1) lpS[row] = rlogp;
@@ -343,7 +360,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) { __syncwarp(); tc_dealloc(tmem_base, 512); }
+  if (warp == 0) { __syncwarp(); tc_dealloc(tmem_base, 512); }
 }
 
 }  // namespace rnnwf
