@@ -122,6 +122,29 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
   for (int i = tid; i <= V2_N; i += V2_THREADS)
     headW[i] = (i == V2_N) ? P.head_b[1] - P.head_b[0] : ((i < nh) ? P.head_w[i * P.ND + 1] - P.head_w[i * P.ND] : 0.f);
   for (int i = tid; i < P.Q; i += V2_THREADS) stepS[i] = make_short4(P.steps[i].nbr[0], P.steps[i].nbr[1], P.steps[i].site, 0);
+  __syncthreads();
+  if (tid == 0) {
+    // Ring slots.  A site's state is read back once, as the older neighbour of a later site t (the other neighbour of t
+    // is site t - 1, handed over in registers); that read is issued at the top of iteration t - 1, before iteration
+    // t - 1 stores its own state.  So site q may take the slot of any site whose reader t <= q + 1: on the zigzag path
+    // one slot per lattice column, half the look-back window.  w = own slot | slot of the older neighbour << 8.
+    int16_t* const last = reinterpret_cast<int16_t*>(smem + L.off_sym);       // (scratch: the symbols are written later)
+    int16_t* const owner = last + P.Q;
+    for (int q = 0; q < P.Q; ++q) last[q] = -1;
+    for (int t = 1; t < P.Q; ++t) {
+      const int nbo = (stepS[t].x == t - 1) ? stepS[t].y : stepS[t].x;
+      if (nbo >= 0 && last[nbo] < t) last[nbo] = (int16_t)t;
+    }
+    for (int sl = 0; sl < P.ring_len; ++sl) owner[sl] = -1;
+    for (int q = 0; q < P.Q; ++q) {
+      int sl = 0;
+      while (sl < P.ring_len && owner[sl] >= 0 && last[owner[sl]] > q + 1) ++sl;
+      if (sl >= P.ring_len) { asm volatile("trap;"); }
+      owner[sl] = (int16_t)q;
+      const int nbo = (q > 0) ? ((stepS[q].x == q - 1) ? stepS[q].y : stepS[q].x) : -1;
+      stepS[q].w = (short)(sl | ((nbo >= 0 ? (stepS[nbo].w & 0xff) : 0) << 8));
+    }
+  }
   fence_proxy_async_smem();                           // the weight image is read by the tensor core (async proxy)
   tc_fence_before();
   __syncthreads();
@@ -180,7 +203,6 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
     // ring of this thread: [slot][unit half][chunk][row] 16-byte operand words (a warp's store covers 512 contiguous bytes)
     uint4* const ring = reinterpret_cast<uint4*>(P.ring) + (((size_t)blockIdx.x * V2_GROUPS + g) * (size_t)P.ring_len * 2 + half) * (NU4 * V2_ROWS) + row;
     constexpr int RING_SLOT = 2 * NU4 * V2_ROWS;        // uint4 per slot
-    const int ring_len = P.ring_len;
     const int gbar = 1 + g;                             // named barrier of the group's 256 threads
     uint32_t n = 0;
 
@@ -252,20 +274,18 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
       short4 eq = stepS[q0];
       {
         uint32_t hi[2 * NU4], lo[2 * NU4];
-        load_h(eq.x, eq.x >= 0 ? eq.x % ring_len : 0, hi, lo);
+        load_h(eq.x, 0, hi, lo);                            // (before the tile's first site: never the ring)
         __syncwarp();
         put_operand(0, hi, lo);
-        load_h(eq.y, eq.y >= 0 ? eq.y % ring_len : 0, hi, lo);
+        load_h(eq.y, 0, hi, lo);
         put_operand(1, hi, lo);
         tc_wait_st();
         tc_fence_before();
         mbar_arrive(bar_op + g);
       }
-      double rlogp = 0.0;                                  // this thread's share of the row's log P (the sites it finished)
-      int sq = q0 % ring_len;                              // ring slot of site q
+      float lps = 0.f, lpc = 0.f;                          // (compensated FP32 sum: the FP64 pipe is narrow)
       for (int q = q0; q < P.Q; ++q, ++n) {
         const bool has_next = q + 1 < P.Q;
-        const int sq1 = (sq + 1 == ring_len) ? 0 : sq + 1;
         // the older neighbour of the next site (not this site's output): fetched before the wait for this site's accumulators
         short4 en = make_short4(-1, -1, 0, 0);
         int carry_slot = 0;
@@ -274,14 +294,12 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
           en = stepS[q + 1];
           carry_slot = (en.x == q) ? 0 : 1;                 // the next site's neighbour that is this site: horizontal or (row turn) vertical
           const int nbo = carry_slot == 0 ? en.y : en.x;
-          int rs = sq1 - (q + 1 - nbo);                     // (look-back < ring_len)
-          if (rs < 0) rs += ring_len;
-          load_h(nbo, rs, ohi, olo);
+          load_h(nbo, (en.w >> 8) & 0xff, ohi, olo);
         }
         const int sl = (eq.x >= 0) ? (int)symS[eq.x * V2_ROWS + row] : 0;
         const int su = (eq.y >= 0) ? (int)symS[eq.y * V2_ROWS + row] : 0;
         const float* bv = biasS + ((((eq.x >= 0) ? 1 : 0) + ((eq.y >= 0) ? 2 : 0)) * 4 + sl * 2 + su) * V2_TABP + u0;
-        uint4* const rdst = ring + (size_t)sq * RING_SLOT;
+        uint4* const rdst = ring + (size_t)(eq.w & 0xff) * RING_SLOT;
         mbar_wait(bar_acc + g, n & 1u);
         __syncwarp();
         tc_fence_after();
@@ -340,14 +358,17 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
               // log p(sy) = -softplus(logit(other) - logit(sy))
               const float dl = lg + ps[row] + headW[V2_N];
               const float z = symS[q * V2_ROWS + row] ? -dl : dl;
-              rlogp -= (double)(fmaxf(z, 0.f) + logf(1.0f + expf(-fabsf(z))));
+              const float y = -(fmaxf(z, 0.f) + logf(1.0f + expf(-fabsf(z)))) - lpc;
+              const float t = lps + y;
+              lpc = (t - lps) - y;
+              lps = t;
             }
           }
         }
         eq = en;
-        sq = sq1;
       }
       // ---- tile result: E_loc(parent) += <sigma'|H|sigma> psi(sigma') / psi(sigma)
+      double rlogp = (double)lps - (double)lpc;            // this thread's share of the row's log P (the sites it finished)
       if (half == 1) lpS[row] = rlogp;
       asm volatile("bar.sync %0, %1;" ::"r"(gbar), "n"(V2_GWARPS * 32) : "memory");
       if (half == 0 && live) {
