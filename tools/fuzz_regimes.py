@@ -1,6 +1,8 @@
 """Randomised cross-check of the regimes on odd shapes: for random (cell, lattice, width, batch) the tensor-core regimes
 (tc, tc3) against the FFMA regime on the same weights -- sampling with given uniforms, teacher-forced log psi, E_loc with
-prefix reuse, gradient.  Prints one line per case; exits non-zero on the first violation.   python tools/fuzz_regimes.py [cases] [seed]"""
+prefix reuse (and, for the vanilla cell, without it), gradient.  Prints one line per case; exits non-zero at the end if
+any case violated its bound.   python tools/fuzz_regimes.py [cases] [seed] [cell: tensgru | tens | vanilla | gru4]
+(with `vanilla` the widths are drawn from 25..64, the range of the two-tile sweep of sweep_van2.cuh)"""
 import os, sys
 import numpy as np
 import torch
@@ -12,6 +14,9 @@ ncases = int(sys.argv[1]) if len(sys.argv) > 1 else 24
 rng = np.random.RandomState(int(sys.argv[2]) if len(sys.argv) > 2 else 1)
 CELLS = [("tensgru", _lib.CELL_TENSGRU2D, True, _lib.HAM_HEIS2D), ("tens", _lib.CELL_TENS2D, True, _lib.HAM_HEIS2D),
          ("vanilla", _lib.CELL_VANILLA2D, False, _lib.HAM_TFIM2D), ("gru4", _lib.CELL_GRU4, False, _lib.HAM_RYDBERG)]
+only = sys.argv[3] if len(sys.argv) > 3 else None
+if only:
+    CELLS = [c for c in CELLS if c[0] == only]
 bad = 0
 for case in range(ncases):
     name, cell, cplx, ham = CELLS[rng.randint(len(CELLS))]
@@ -19,6 +24,8 @@ for case in range(ncases):
     if name == "gru4":
         nx, ny = min(nx, 4), min(ny, 4)
     nh = int(rng.randint(5, 105 if name != "gru4" else 200))
+    if only == "vanilla":
+        nh = int(rng.randint(25, 65))
     ns = int(rng.choice([1, 7, 64, 129, 300, 1000, 2500]))
     u1 = cplx and (nx * ny) % 2 == 0
     kw = dict(num_units=nh, complex_head=cplx, u1=u1, seed=int(rng.randint(1 << 30)))
@@ -43,6 +50,11 @@ for case in range(ncases):
         sv = eng.new_saved(ns)
         lp, ph = eng.logpsi(s0, saved=sv)
         e = eng.local_energies(ham, hp, s0, lp, ph, saved=sv)
+        if name == "vanilla":      # the same without prefix reuse must agree with the reused one to rounding
+            e_nr = eng.local_energies(ham, hp, s0, lp, ph, saved=None)
+            if float((e_nr - e).abs().max()) > 10 * tol * (float(e0.abs().mean()) + 1e-30):
+                bad += 1
+                line += " | no-reuse E_loc differs  <-- VIOLATION"
         g = eng.backward(s0, sv, seeds, seeds if cplx else None).double()
         scale = float(lp0.abs().mean()) + 1e-30
         elp = float((lp - lp0).abs().max()) / scale
