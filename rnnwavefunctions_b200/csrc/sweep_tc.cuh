@@ -281,6 +281,15 @@ inline int tc_tile_rows(long long rows, int num_sms) {
 __device__ __forceinline__ float mufu_tanh(float x) { float y; asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float sigmoid_prescaled(float x) { return fmaf(0.5f, mufu_tanh(x), 0.5f); }
 __device__ __forceinline__ float tanh_prescaled(float x) { return mufu_tanh(x); }
+// gates of the split-precision regime: ex2.approx (2 ulp) and rcp.approx (1 ulp) -- absolute error below 3e-7, the class of
+// expf / tanhf at a third of their instructions (the epilogue's instruction issue bounds this regime, profiles/r2d_summary.md)
+__device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float sigmoid_split(float x) { return rcp_approx(1.0f + ex2_approx(-1.4426950408889634f * x)); }
+__device__ __forceinline__ float tanh_split(float x) {
+  const float e = ex2_approx(-2.8853900817779268f * fabsf(x));      // exp(-2 |x|)
+  return copysignf((1.0f - e) * rcp_approx(1.0f + e), x);
+}
 
 // symbol of (site t, tile row) in the bit-packed table
 __device__ __forceinline__ int tc_sym(const uint32_t* symS, int t, int row) { return (int)((symS[t * 4 + (row >> 5)] >> (row & 31)) & 1u); }

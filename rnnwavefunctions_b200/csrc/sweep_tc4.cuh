@@ -537,8 +537,8 @@ __global__ void __launch_bounds__(T4_THREADS, 1) sweep_tc4_kernel(const SweepPar
           float hv[16];
 #pragma unroll
           for (int e = 0; e < 16; ++e) {
-            const float u = SPLIT ? 1.0f / (1.0f + expf(-__uint_as_float(dg[e]) * DS)) : sigmoid_prescaled(__uint_as_float(dg[e]));
-            const float ht = SPLIT ? tanhf(__uint_as_float(ds[e]) * DS) : tanh_prescaled(__uint_as_float(ds[e]));
+            const float u = SPLIT ? sigmoid_split(__uint_as_float(dg[e]) * DS) : sigmoid_prescaled(__uint_as_float(dg[e]));
+            const float ht = SPLIT ? tanh_split(__uint_as_float(ds[e]) * DS) : tanh_prescaled(__uint_as_float(ds[e]));
             const float mv = __uint_as_float(dm[e]) * DS;
             // u ht + (1 - u) m; padding units have zero weights and biases: u = 1/2, ht = m = 0 -> 0
             hv[e] = live ? fmaf(u, ht - mv, mv) : 0.f;

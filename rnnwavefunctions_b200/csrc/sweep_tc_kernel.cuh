@@ -547,8 +547,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
                 float mv = __uint_as_float(d[24 + e]);
                 if (SPLIT) { sv *= DS; gv *= DS; mv *= DS; }
                 if (!BIASMMA) { sv += bsv[e]; gv += bgv[e]; }
-                const float u = (CELLK == 2) ? 1.0f : (SPLIT ? 1.0f / (1.0f + expf(-gv)) : sigmoid_prescaled(gv));   // CELLK 2: un-gated tensorized cell, h = tanh(s)
-                const float ht = SPLIT ? tanhf(sv) : tanh_prescaled(sv);
+                const float u = (CELLK == 2) ? 1.0f : (SPLIT ? sigmoid_split(gv) : sigmoid_prescaled(gv));   // CELLK 2: un-gated tensorized cell, h = tanh(s)
+                const float ht = SPLIT ? tanh_split(sv) : tanh_prescaled(sv);
                 // u ht + (1 - u) m.  Padding units (>= num_units) have zero weights and biases: u = 1/2, ht = m = 0 -> 0.
                 const float hv = fmaf(u, ht - mv, mv);
                 hnew[e] = hv;

@@ -78,12 +78,6 @@ __global__ void pack_van2_kernel(const float* __restrict__ Wh, const float* __re
   }
 }
 
-__device__ __forceinline__ float ex2_approx(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-
 // NU4: 4-unit chunks per thread (units per thread = 4 NU4 = nhp / 2)
 template <int NU4>
 __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepParams P) {
