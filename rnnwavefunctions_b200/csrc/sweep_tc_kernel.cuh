@@ -110,6 +110,38 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
     stepT[i] = make_int4((nb0 & 0xffff) | (nb1 << 16), (other & 0xffff) | (carry << 16),
                          (int)((uint32_t)(i % P.ring_len) * RSLOT), other >= 0 ? (int)((uint32_t)(other % P.ring_len) * RSLOT) : 0);
   }
+  if (!(P.debug_flags & 64)) {
+    // Ring slots by live range instead of step number.  A step's image is read back as the older-neighbour half of a later
+    // step t, and that load is issued no later than the top of iteration t - 1 (end of t - 2 outside the split regime),
+    // i.e. before iteration t - 1 stores its own image: step q may take the slot of any step whose last reader is
+    // <= q + 1.  On the zigzag path that is one slot per lattice column instead of the whole look-back window -- half
+    // the ring footprint (C4: 157 -> 86 MB over all CTAs, inside the L2).  (Readers are counted over both neighbours.)
+    __syncthreads();
+    for (int q = tid; q < P.Q; q += TC_THREADS) {
+      int last = -1;
+      for (int t = q + 1; t < P.Q && t <= q + P.ring_len; ++t)
+        if (metaS[t].x == q || metaS[t].y == q) last = t;
+      metaS[q].w = (short)last;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      int* const owner = reinterpret_cast<int*>(symS);      // (scratch: the symbol table is written per tile, later)
+      const int nslot = P.ring_len < P.Tsym * 4 ? P.ring_len : P.Tsym * 4;
+      for (int sl = 0; sl < nslot; ++sl) owner[sl] = -1;
+      for (int q = 0; q < P.Q; ++q) {
+        int sl = 0;
+        while (sl < nslot && owner[sl] >= 0 && metaS[owner[sl]].w > q + 1) ++sl;
+        if (sl >= nslot) { asm volatile("trap;"); }
+        owner[sl] = q;
+        stepT[q].z = (int)((uint32_t)sl * RSLOT);
+      }
+    }
+    __syncthreads();
+    for (int q = tid; q < P.Q; q += TC_THREADS) {
+      const int other = (int)(short)(stepT[q].y & 0xffff);
+      stepT[q].w = other >= 0 ? stepT[other].z : 0;
+    }
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -387,11 +419,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
       uint32_t onext[16], onlo[16];
       // both halves of a step's operand from the history (SPLIT: every step; otherwise the tile's first step only)
       auto operand_from_history = [&](int nb0, int nb1, uint32_t a0) {
-        load_half(onext, onlo, nb0, nb0 >= 0 ? (uint32_t)(nb0 % P.ring_len) * RSLOT : 0u);
+        load_half(onext, onlo, nb0, nb0 >= 0 ? (uint32_t)stepT[nb0].z : 0u);
         set_one(onext);
         store_half(onext, a0);
         if (SPLIT) store_half(onlo, a0 + acols);
-        load_half(onext, onlo, nb1, nb1 >= 0 ? (uint32_t)(nb1 % P.ring_len) * RSLOT : 0u);
+        load_half(onext, onlo, nb1, nb1 >= 0 ? (uint32_t)stepT[nb1].z : 0u);
         store_half(onext, a0 + hcols);
         if (SPLIT) store_half(onlo, a0 + acols + hcols);
         tc_wait_st();
