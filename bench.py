@@ -701,7 +701,7 @@ def main():
 
 # dram__bytes_read.sum + dram__bytes_write.sum of one sweep_tc_kernel<MODE_CHILD> launch of the default workload, from the
 # committed `ncu --set full` capture named here (a constant of that capture, not a measurement of this run)
-NCU_TRAFFIC = {"bytes": 17.1e9, "source": "ncu --set full capture of commit 7ec878e (profiles/r1i_summary.md), one launch, 10^4 samples"}
+NCU_TRAFFIC = {"bytes": 2.04e9, "source": "ncu --set full capture of commit 88ac7d1 (profiles/r2d_summary.md), one launch, 10^4 samples: dram__bytes_read 1.04 GB + dram__bytes_write 0.99 GB (17.1 GB before the ring slots were assigned by live range)"}
 
 
 def executed_sites(w, samples, eng):
