@@ -480,7 +480,7 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
 
 long long ring_bytes(const rnnwf_model& m, int grid, int Mp) {
   if (m.tc4) return (long long)grid * m.Q * t4_step_bytes(m.tc_np, m.tc4_split);   // FP16 chunk images of every site, per persistent CTA
-  if (m.van2) {      // (the two-tile sweep keeps an FP32 ring per tile group; the generic kernel's ring serves sampling / evaluation)
+  if (m.van2) {      // (the two-tile sweep keeps a ring of 32-bit operand words (hi + lo halves) per tile group; the generic kernel's ring serves sampling / evaluation)
     const long long slot = (long long)tc_ring_slot(m.nhp) * 2;
     return (long long)grid * std::max((long long)m.ring_len * slot, v2_ring_bytes(m.ring_len, m.nhp));
   }
