@@ -473,6 +473,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           const bool save = (MODE != MODE_CHILD) && live && (P.sv_hist != nullptr);
           float* sv_h = save ? P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp + sub * 4 : nullptr;
           uint32_t a_carry = a_next + (uint32_t)carry_half * hcols;
+          // hidden-state tile image for the weight-gradient kernel (zeros for padding units / rows past the batch)
+          const bool himg = MODE != MODE_CHILD && P.sv_himg != nullptr && stores;
+          const int hnc = ((nhp + 15) / 16) * 2;
+          float* const sv_i = himg ? P.sv_himg + ((size_t)q * (size_t)sv_tiles + (size_t)stile) * (size_t)(32 * hnc * 32) + (size_t)(srow >> 2) * hnc * 32 + (srow & 3) : nullptr;
           // b' = b + Uh[0] (horizontal neighbour present) + Uv[0] (vertical present); dUh = Uh[1] - Uh[0], dUv likewise
           const float* bv = biasS + (((nb0 >= 0) ? 1 : 0) + ((nb1 >= 0) ? 2 : 0)) * ldb + sub * 4;
           const float* duh = biasS + 4 * ldb + sub * 4;
@@ -507,6 +511,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
               if (SPLIT) { split_f16x2(hnew[0] * HS, hnew[1] * HS, o.x, ol.x); split_f16x2(hnew[2] * HS, hnew[3] * HS, o.y, ol.y); }
               else { o.x = pack_f16x2(hnew[0], hnew[1]); o.y = pack_f16x2(hnew[2], hnew[3]); }
               if (save) *reinterpret_cast<float4*>(sv_h + blk * TC_JP) = make_float4(hnew[0], hnew[1], hnew[2], hnew[3]);
+              if (himg) {   // hidden-state tile image for the weight-gradient kernel, straight from the registers
+                const int j0 = blk * TC_JP + sub * 4;
+                if (j0 < hnc * 8) {
+#pragma unroll
+                  for (int e = 0; e < 4; ++e)
+                    sv_i[((j0 + e) >> 3) * 32 + ((j0 + e) & 7) * 4] = (P.sv_hist != nullptr && j0 + e < nhp) ? hnew[e] : 0.f;
+                }
+              }
               __syncwarp();
               if (has_next && !SPLIT) tc_st2(a_carry + (uint32_t)(2 * blk), o);
               *reinterpret_cast<uint2*>(ring_p) = o;
@@ -514,18 +526,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
               ring_p += (blk & 1) ? (TC_RING_QUAD - 8u) : 8u;
             }
           }
-          if (MODE != MODE_CHILD && P.sv_himg != nullptr && stores) {
-            // hidden-state tile image for the weight-gradient kernel (zeros for padding units / rows past the batch)
-            const int hnc = ((nhp + 15) / 16) * 2;
-            float* sv_i = P.sv_himg + ((size_t)q * (size_t)sv_tiles + (size_t)stile) * (size_t)(32 * hnc * 32) + (size_t)(srow >> 2) * hnc * 32 + (srow & 3);
-            const float* hsrc = P.sv_hist != nullptr ? P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * nhp : nullptr;
+          if (himg) {
+            // (zeros for this thread's unit pieces past the operand's K range that the image still covers)
 #pragma unroll
             for (int blk = 0; blk < TC_NB; ++blk) {
               const int j0 = blk * TC_JP + sub * 4;
-              if (j0 < hnc * 8) {
+              if (blk >= np_own && j0 < hnc * 8) {
 #pragma unroll
-                for (int e = 0; e < 4; ++e)
-                  sv_i[((j0 + e) >> 3) * 32 + ((j0 + e) & 7) * 4] = (live && hsrc != nullptr && j0 + e < nhp) ? hsrc[j0 + e] : 0.f;
+                for (int e = 0; e < 4; ++e) sv_i[((j0 + e) >> 3) * 32 + ((j0 + e) & 7) * 4] = 0.f;
               }
             }
           }
