@@ -451,8 +451,10 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
     if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("1D GRU sweep launch: ") + cudaGetErrorString(e));
     return RNNWF_OK;
   }
-  if (m.van2 && P.mode == MODE_CHILD && P.rows_dev == nullptr) {
-    // vanilla 2D RNN, split precision, single-flip child list: two tiles per CTA (sweep_van2.cuh)
+  if (m.van2 && P.mode == MODE_CHILD && P.rows_dev == nullptr && P.par_hist != nullptr) {
+    // vanilla 2D RNN, split precision, single-flip child list with prefix reuse: two tiles per CTA (sweep_van2.cuh).
+    // (Without the parents' saved state every site of a child would come from this kernel and the parent's log P from the
+    // generic one: two accumulation orders whose rounding does not cancel in the ratio -- that case stays on the generic kernel.)
     SweepParams P2 = P;
     P2.tc_B = m.d_van2B;
     const long long tiles = (P.rows + V2_ROWS - 1) / V2_ROWS;

@@ -76,9 +76,9 @@ def test_tc3_tfim2d_local_energies_c3_size(cuda, reuse):
     # This untrained elu network over 144 sites sits at the conditioning limit of single precision: rounding the hidden
     # state to FP32 once per site already moves log P by 4e-5 (float64 emulation) and the FP32 FFMA regime itself measures
     # 8.6e-6 on these inputs; the FP16 hi+lo pairs carry 22-23 mantissa bits instead of 24 and measure 3.6e-5.
-    # Measured with the two-tile kernel (sweep_van2.cuh): 3.9e-5 with prefix reuse; 4.7e-5 (rms 1.5e-5) without, where the
-    # parents' log P comes from the generic kernel and every site of the children from the two-tile one -- two accumulation
-    # orders, so their rounding no longer cancels in the ratio (the generic kernel on both sides: 3.0e-5, rms 6.8e-6).
+    # Measured with the two-tile kernel (sweep_van2.cuh, prefix reuse): 3.9e-5.  Without reuse the library keeps the generic
+    # kernel (3.0e-5): parents from the generic kernel and every site of the children from the two-tile one would be two
+    # accumulation orders whose rounding no longer cancels in the ratio (4.7e-5, rms 1.5e-5 when tried).
     assert_rel(e.real, ref, 5e-5, f"tc3 vanilla 12x12 E_loc reuse={reuse}")
 
 
