@@ -847,7 +847,7 @@ inline int backward_run(const rnnwf_model_impl& m, long long R, const int8_t* cf
         D.gW = nullptr; D.gWg = nullptr; D.gM0 = Gd("Wh"); D.gM1 = Gd("Wv");
         D.slab[0] = D.slab[1] = D.slab[2] = 0; D.gB = nullptr; D.gBg = nullptr;
         if (njobs > 0) { RNNWF_COUNT_LAUNCH(); dw_tc_kernel<<<(unsigned)njobs, DW_THREADS, dw_smem_bytes(nhp), st>>>(D); }   // (a single-site lattice has no neighbour weights)
-        RNNWF_COUNT_LAUNCH(); vanilla_input_grads_kernel<<<dim3(nh, nsplit), 128, 0, st>>>(B.dpT, m.d_steps, m.d_site_of_t, cfg, m.Q, tiles, R, nh, nhp,
+        RNNWF_COUNT_LAUNCH(); vanilla_input_grads_kernel<<<dim3((nh + VIG_UB - 1) / VIG_UB, (unsigned)std::max<long long>(1, std::min<long long>((long long)m.Q * tiles, 4LL * m.num_sms / ((nh + VIG_UB - 1) / VIG_UB) + 1))), 128, 0, st>>>(B.dpT, m.d_steps, m.d_site_of_t, cfg, m.Q, tiles, R, nh, nhp,
                                                                                           m.nsites, Gd("b"), Gd("Uh"), Gd("Uv"));
       } else {
         const bool gated = m.cell == CELL_TENSGRU2D;

@@ -171,37 +171,60 @@ __global__ void pack_bwd_tc_vanilla_kernel(const float* __restrict__ Wh, const f
 
 // vanilla 2D RNN: gradients of the one-hot input kernels and the bias from the feature-major d(pre) tiles:
 //   db[j] = sum d pre_j,   dUh[c][j] = sum [horizontal neighbour present and sigma_l == c] d pre_j,   dUv likewise.
-// grid (nh, nsplit), 128 threads = the rows of a tile.
+// grid (ceil(nh / 8), nsplit), 128 threads = the rows of a tile.  A CTA sums a block of 8 units over its share of the
+// (site, tile) items, so the two scattered symbol reads per row and item are shared by 8 coalesced 512-byte tile rows
+// (one unit per CTA re-read them 50 times: 656 us at C3; now the tile reads dominate).
+constexpr int VIG_UB = 8;
 __global__ void __launch_bounds__(128) vanilla_input_grads_kernel(const float* __restrict__ dpT, const StepMeta* __restrict__ steps,
                                                                   const int16_t* __restrict__ site_of_t, const int8_t* __restrict__ cfg,
                                                                   int Q, long long tiles, long long rows, int nh, int nhp, int nsites,
                                                                   float* __restrict__ gb, float* __restrict__ gUh, float* __restrict__ gUv) {
-  __shared__ float red[4][5];
-  const int j = blockIdx.x, r = threadIdx.x;
-  float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+  __shared__ float red[4][VIG_UB][5];
+  const int j0 = blockIdx.x * VIG_UB, r = threadIdx.x;
+  float acc[VIG_UB][5];
+#pragma unroll
+  for (int u = 0; u < VIG_UB; ++u)
+#pragma unroll
+    for (int k = 0; k < 5; ++k) acc[u][k] = 0.f;
   const long long nitems = (long long)Q * tiles;
   for (long long it = blockIdx.y; it < nitems; it += gridDim.y) {
     const int q = (int)(it / tiles);
     const long long row = (it % tiles) * TC_ROWS + r;
-    const float v = dpT[((size_t)it * nhp + j) * TC_DPT_PITCH + r];
-    if (row >= rows) continue;
+    const bool alive = row < rows;
+    const float* src = dpT + ((size_t)it * nhp + j0) * TC_DPT_PITCH + r;
+    float v[VIG_UB];
+#pragma unroll
+    for (int u = 0; u < VIG_UB; ++u) v[u] = (alive && j0 + u < nh) ? src[(size_t)u * TC_DPT_PITCH] : 0.f;
     const int n0 = steps[q].nbr[0], n1 = steps[q].nbr[1];
-    const int8_t* cf = cfg + row * nsites;
-    acc[0] += v;
-    if (n0 >= 0) { if (cf[site_of_t[n0]] & 1) acc[2] += v; else acc[1] += v; }
-    if (n1 >= 0) { if (cf[site_of_t[n1]] & 1) acc[4] += v; else acc[3] += v; }
+    const int8_t* cf = cfg + (alive ? row : 0) * nsites;
+    const bool hl = n0 >= 0, hu = n1 >= 0;
+    const bool l1 = hl && (cf[site_of_t[hl ? n0 : 0]] & 1), u1 = hu && (cf[site_of_t[hu ? n1 : 0]] & 1);
+    const bool l0 = hl && !l1, u0 = hu && !u1;
+#pragma unroll
+    for (int u = 0; u < VIG_UB; ++u) {
+      acc[u][0] += v[u];
+      acc[u][1] += l0 ? v[u] : 0.f;
+      acc[u][2] += l1 ? v[u] : 0.f;
+      acc[u][3] += u0 ? v[u] : 0.f;
+      acc[u][4] += u1 ? v[u] : 0.f;
+    }
   }
 #pragma unroll
-  for (int k = 0; k < 5; ++k) {
-    float x = acc[k];
-    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-    if ((r & 31) == 0) red[r >> 5][k] = x;
-  }
+  for (int u = 0; u < VIG_UB; ++u)
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      float x = acc[u][k];
+      for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+      if ((r & 31) == 0) red[r >> 5][u][k] = x;
+    }
   __syncthreads();
-  if (r < 5) {
-    const float x = red[0][r] + red[1][r] + red[2][r] + red[3][r];
-    float* dst = (r == 0) ? gb + j : (r <= 2 ? gUh + (r - 1) * nh + j : gUv + (r - 3) * nh + j);
-    atomicAdd(dst, x);
+  if (r < VIG_UB * 5) {
+    const int u = r / 5, k = r % 5, j = j0 + u;
+    if (j < nh) {
+      const float x = red[0][u][k] + red[1][u][k] + red[2][u][k] + red[3][u][k];
+      float* dst = (k == 0) ? gb + j : (k <= 2 ? gUh + (k - 1) * nh + j : gUv + (k - 3) * nh + j);
+      atomicAdd(dst, x);
+    }
   }
 }
 
