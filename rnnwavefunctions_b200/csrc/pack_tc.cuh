@@ -5,8 +5,8 @@
 namespace rnnwf {
 
 // ---- weight image for the tensor-core sweep --------------------------------------------------------------
-// [variant 3][pass NP][k-core kc][n-core 14][8 rows][8 halves]:  B[n][k] of the pass, K-major core matrices
-// (n ordered thread-major, see below).
+// [variant 3][pass NP][n-core 14][k-core kc][8 rows][8 halves]:  B[n][k] of the pass, K-major core matrices
+// (n ordered thread-major, see below; n-core outermost so that the columns a narrow last pass needs are one contiguous run).
 // variants: 0 both neighbours, 1 horizontal only, 2 vertical only.
 // (`vb`, `vg`: the block's index and the number of blocks inside the part of the grid that works on this image)
 __device__ __forceinline__ void pack_tc_body(const float* __restrict__ W, const float* __restrict__ Wg, const float* __restrict__ Wmerge,
@@ -22,8 +22,8 @@ __device__ __forceinline__ void pack_tc_body(const float* __restrict__ W, const 
     long long r = idx;
     const int e = (int)(r % 8); r /= 8;
     const int r8 = (int)(r % 8); r /= 8;
-    const int ni = (int)(r % (TC_N / 8)); r /= (TC_N / 8);
     const int ki = (int)(r % kc); r /= kc;
+    const int ni = (int)(r % (TC_N / 8)); r /= (TC_N / 8);
     const int part = (int)(r % nparts); r /= nparts;
     const int p = (int)(r % NP); r /= NP;
     const int variant = (int)r;
@@ -74,7 +74,7 @@ __global__ void pack_tc_bias_kernel(const float* __restrict__ b, const float* __
   pack_tc_bias_body(b, bg, nh, nhp, out, blockIdx.x, gridDim.x);
 }
 
-// ---- vanilla 2D RNN (CELLK = 1): one image [k-core kc][n-core 14][8 rows][8 halves], B[n][k] = W_half[unit(k)][unit(n)]
+// ---- vanilla 2D RNN (CELLK = 1): one image [n-core 14][k-core kc][8 rows][8 halves], B[n][k] = W_half[unit(k)][unit(n)]
 // with n = sub * 28 + blk * 4 + e  <->  output unit 16 blk + 4 sub + e, k in the thread-major order of the operand.
 __global__ void pack_tc_vanilla_kernel(const float* __restrict__ Wh, const float* __restrict__ Wv, int nh, int nhp, int split, __half* __restrict__ out) {
   const int kc = 2 * (nhp / 8);
@@ -83,8 +83,8 @@ __global__ void pack_tc_vanilla_kernel(const float* __restrict__ Wh, const float
     long long r = idx;
     const int e = (int)(r % 8); r /= 8;
     const int r8 = (int)(r % 8); r /= 8;
-    const int ni = (int)(r % (TC_N / 8)); r /= (TC_N / 8);
     const int ki = (int)(r % kc); r /= kc;
+    const int ni = (int)(r % (TC_N / 8)); r /= (TC_N / 8);
     const int part = (int)r;
     const int n = ni * 8 + r8, k = ki * 8 + e;
     const int sub = n / TC_TPS, blk = (n % TC_TPS) / 4, j = blk * TC_JP + sub * 4 + (n % 4);

@@ -298,7 +298,7 @@ __device__ __forceinline__ int tc_sym(const uint32_t* symS, int t, int row) { re
 // `acc0`: accumulate flag of the first K step (0 starts a fresh accumulator, 1 adds to it: the split-precision passes).
 template <int HC>
 __device__ __forceinline__ void tc_issue_pass(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, int hc = HC, uint32_t acc0 = 0u) {
-  constexpr uint64_t B_KSTEP = (2ull * (TC_N / 8) * 128) >> 4;   // two k-cores of the weight image per K=16 step
+  constexpr uint64_t B_KSTEP = (2ull * 128) >> 4;   // two k-cores of the weight image per K=16 step (n-core-major image: adjacent)
   if constexpr (HC > 0) {
 #pragma unroll
     for (int ks = 0; ks < HC; ++ks) tc_mma_f16_ts(tmem_d, tmem_a + (uint32_t)ks * 8u, bdesc + (uint64_t)ks * B_KSTEP, idesc, ks > 0 ? 1u : acc0);
@@ -310,7 +310,7 @@ __device__ __forceinline__ void tc_issue_pass(uint32_t tmem_d, uint32_t tmem_a, 
 // K steps [K0, K1) of a column pass, fully unrolled (see tc_issue_pass); `acc_first`: accumulate flag of step K0
 template <int K0, int K1>
 __device__ __forceinline__ void tc_issue_range(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t acc_first) {
-  constexpr uint64_t B_KSTEP = (2ull * (TC_N / 8) * 128) >> 4;
+  constexpr uint64_t B_KSTEP = (2ull * 128) >> 4;
 #pragma unroll
   for (int ks = K0; ks < K1; ++ks) tc_mma_f16_ts(tmem_d, tmem_a + (uint32_t)ks * 8u, bdesc + (uint64_t)ks * B_KSTEP, idesc, ks > K0 ? 1u : acc_first);
 }

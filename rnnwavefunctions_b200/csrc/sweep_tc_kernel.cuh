@@ -52,7 +52,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int nhp = P.nhp, nh = P.nh, ldb = nhp + TC_JP;
   const int NP = P.tc_np, hc = L.kc / 2;              // column passes per site; k-cores (= K16 steps) per neighbour half
-  const uint32_t B_LBO = (TC_N / 8) * 128, SBO = 128;
+  const uint32_t B_LBO = 128, SBO = (uint32_t)L.kc * 128u;      // n-core-major weight image: k-cores adjacent, n-cores kc * 128 bytes apart
   const uint32_t idesc = tc_idesc(TC_ROWS, TC_N);
   // The last column pass holds only num_units - 16 (NP - 1) real units: issue it just wide enough for the epilogue
   // threads that own them (28 columns each, rounded up to the MMA's N granularity of 16).
@@ -268,6 +268,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
     const bool leader = elect_one();
     // debug_flags bit 0 (RNNWF_TC_DEBUG=1, timing experiments only, wrong results): copy half of every weight image
     const uint32_t load_bytes = (P.debug_flags & 1) ? (uint32_t)L.b_bytes / 2 : (uint32_t)L.b_bytes;
+    // the last column pass is issued only as wide as its real units: its image is the first n-cores of the stage
+    const uint32_t last_bytes = (CELLK == 1 || (P.debug_flags & 1)) ? load_bytes : (uint32_t)L.kc * 128u * (uint32_t)(((subs_last * TC_TPS + 15) / 16) * 2);
     uint32_t phBf = 0, n = 0;
     for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const int q0 = tile_q0(tile * VR) * P.symL;
@@ -281,8 +283,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
           if (n >= TC_STAGES) { mbar_wait_relaxed(bar_Bfree + s, (phBf >> s) & 1u); phBf ^= 1u << s; }
           TC_ACC(4); TC_EV(5);
           if (leader) {
-            mbar_expect_tx(bar_B + s, load_bytes);
-            bulk_g2s(Bst + (size_t)s * L.b_bytes, src + (size_t)p * L.b_bytes, load_bytes, bar_B + s);
+            const uint32_t nb = ((p / (int)NPARTS) == NP - 1) ? last_bytes : load_bytes;
+            mbar_expect_tx(bar_B + s, nb);
+            bulk_g2s(Bst + (size_t)s * L.b_bytes, src + (size_t)p * L.b_bytes, nb, bar_B + s);
           }
           __syncwarp();
           TC_ACC(6); TC_EV(6);
