@@ -11,15 +11,19 @@
 //
 //   h_q = elu(x_h Uh + h_h Wh + x_v Uv + h_v Wv + b):   acc = [h_h | h_v] (128 x 2 nhp, FP16 hi + lo pairs scaled by 64)
 //                                                              x [Wh; Wv]^T (hi + lo scaled by 1024), three MMAs per K = 16 step;
-//   one-hot inputs and the bias from three small tables (b' of the neighbour variant, dUh, dUv: pack_tc_vanilla_bias_kernel);
-//   two-logit head (real wavefunction): the two threads of a row exchange their partial logits through shared memory behind
-//   a 64-thread mbarrier and take turns in finishing a site (softmax, log in FP64, running log P in FP64);
+//   one-hot inputs and the bias from one table of 16 rows, b'(neighbour variant) + sigma_l dUh + sigma_u dUv, built at
+//   kernel start from pack_tc_vanilla_bias_kernel's three tables; elu branch-free through ex2.approx;
+//   two-logit head (real wavefunction): only the difference of the logits enters log p = -softplus(logit_other - logit_sigma);
+//   the two threads of a row exchange their partial sums through shared memory behind a 64-thread mbarrier (one per lane
+//   quarter and site parity) and take turns in finishing a site; running log P as a compensated FP32 sum, FP64 at the tile end;
 //   E_loc(parent) += coef exp((logP' - logP)/2).
-// History ring in global memory ([slot][row][units of this thread] as the operand's hi / lo words -- written and read back
-// by the same thread, no second split);
+// History ring in global memory, [slot][unit half][4-unit chunk][row] 16-byte words = the operand's hi / lo words (no second
+// split on the way back), written and read back by the same thread, a warp's access 512 contiguous bytes; slots assigned at
+// kernel start by live range (one per lattice column on the zigzag path, so the rings of all CTAs mostly stay in the L2);
 // prefix reuse from the parents' saved history exactly as in the generic kernel.
 // TMEM per group: accumulator 64 columns + operand hi 64 + lo 64 (2 x 192 of 512 columns).
-// Every wait is bounded and traps instead of hanging.
+// 18 warps: 0, 1 issue the MMAs of group 0, 1; 2..17 element-wise (group, lane quarter = warp & 3, unit half).
+// Every wait is bounded and traps instead of hanging.  Measured history and stall analysis: profiles/r2d_summary.md.
 #pragma once
 #include "sweep_tc.cuh"
 
@@ -29,7 +33,7 @@ constexpr int V2_ROWS = 128;
 constexpr int V2_N = 64;                              // accumulator columns (units, natural order; nhp <= 64)
 constexpr int V2_GROUPS = 2;
 constexpr int V2_GWARPS = 8;                          // element-wise warps per group: (lane quarter 4) x (unit half 2)
-constexpr int V2_THREADS = 32 * (2 + V2_GROUPS * V2_GWARPS);   // warps 0, 1: MMA issue of group 0, 1 (576 threads: 112 registers each)
+constexpr int V2_THREADS = 32 * (2 + V2_GROUPS * V2_GWARPS);   // warps 0, 1: MMA issue of group 0, 1 (576 threads; registers are granted per 4 warps, so 96 each as with 640)
 constexpr int V2_TABP = V2_N + 4;                     // pitch of the input / bias table (rows of one warp's lanes fall into distinct banks)
 constexpr int V2_GCOLS = 192;                         // TMEM columns per group: [acc 64 | operand hi 64 | operand lo 64]
 
@@ -185,7 +189,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
     const int g = (warp - 2) / V2_GWARPS;
     const int wg = (warp - 2) % V2_GWARPS;
     const int quarter = warp & 3;                       // TMEM lanes this warp may touch: 32 quarter .. + 31
-    const int half = wg >> 2;                           // (warps 4..7 / 12..15: half 0; 8..11 / 16..19: half 1 -- warp & 3 runs 0..3 in each)
+    const int half = wg >> 2;                           // (four consecutive warps cover the four lane quarters: warp & 3)
     const int row = (quarter << 5) + lane;
     const int u0 = half * U2;                           // this thread's units u0 .. u0 + U2 - 1
     const uint32_t lane_base = (uint32_t)(quarter * 32) << 16;
