@@ -314,3 +314,38 @@ def test_tc_row_spreading_and_on_sm_paths_match_their_fallbacks(cuda, monkeypatc
             err = float((a - b).abs().max()) / float(b.abs().max())
             print(f"[parity] {var}: gradient differs from the default path by {err:.2e} of its largest entry (bound {tol:.0e})")
             assert err <= tol, var
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cell,nx,ny,nh,prec", [(_lib.CELL_TENSGRU2D, 6, 5, 40, "tc"), (_lib.CELL_TENSGRU2D, 5, 6, 36, "tc3"),
+                                               (_lib.CELL_VANILLA2D, 7, 4, 50, "tc"), (_lib.CELL_TENS2D, 3, 8, 24, "tc")])
+def test_tc_ring_slots_by_live_range_change_nothing(cuda, monkeypatch, cell, nx, ny, nh, prec):
+    """The history ring's slots are assigned by live range (one per lattice column on the zigzag path) instead of
+    step mod (look-back + 1): same arithmetic on the same values, so samples, log psi and E_loc (prefix reuse on and off)
+    must be bit-identical (E_loc: to the order of its FP64 atomic sums) to the modulo slots that RNNWF_TC_DEBUG bit 64
+    restores (read per launch)."""
+    cplx = cell != _lib.CELL_VANILLA2D
+    eng = Engine(cell, nx, ny, num_units=nh, complex_head=cplx, u1=cplx and (nx * ny) % 2 == 0, seed=15, precision=prec)
+    p = eng.params.cpu()
+    eng.set_weights(p + 0.1 * (torch.rand(p.shape, generator=torch.Generator().manual_seed(16)) - 0.5))
+    ns = 333
+    u = torch.rand(ns, eng.nsteps, generator=torch.Generator().manual_seed(17), dtype=torch.float32)
+    ham, hp = (_lib.HAM_TFIM2D, [2.5] + [1.0] * (nx * ny)) if cell == _lib.CELL_VANILLA2D else (_lib.HAM_HEIS2D, [1.0])
+
+    def run():
+        saved = eng.new_saved(ns)
+        s, lp, ph = eng.sample(ns, uniforms=u, saved=saved)
+        lp2, ph2 = eng.logpsi(s)
+        e = eng.local_energies(ham, hp, s, lp, ph, saved=saved)
+        e2 = eng.local_energies(ham, hp, s, lp, ph, saved=None)
+        return [t.cpu() for t in (s, lp, ph, lp2, ph2, e, e2)]
+
+    ref = run()
+    monkeypatch.setenv("RNNWF_TC_DEBUG", "64")
+    alt = run()
+    monkeypatch.delenv("RNNWF_TC_DEBUG")
+    for a, b, name in zip(ref, alt, ("samples", "log P", "phase", "log P (evaluation)", "phase (evaluation)", "E_loc", "E_loc without reuse")):
+        if name.startswith("E_loc"):      # (summed over the children with FP64 atomics: order-dependent in the last bits)
+            assert float((a - b).abs().max()) <= 1e-12 * float(a.abs().max()), name
+        else:
+            assert torch.equal(a, b), name
