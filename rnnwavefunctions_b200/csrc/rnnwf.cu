@@ -451,16 +451,30 @@ int launch_sweep(const rnnwf_model& m, const SweepParams& P, const LaunchShape& 
     if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("1D GRU sweep launch: ") + cudaGetErrorString(e));
     return RNNWF_OK;
   }
-  if (m.van2 && P.mode == MODE_CHILD && P.rows_dev == nullptr && P.par_hist != nullptr) {
-    // vanilla 2D RNN, split precision, single-flip child list with prefix reuse: two tiles per CTA (sweep_van2.cuh).
-    // (Without the parents' saved state every site of a child would come from this kernel and the parent's log P from the
-    // generic one: two accumulation orders whose rounding does not cancel in the ratio -- that case stays on the generic kernel.)
+  if (m.van2 && P.mode == MODE_CHILD && P.rows_dev == nullptr) {
+    // vanilla 2D RNN, split precision, single-flip child list: two tiles per CTA (sweep_van2.cuh).  The parents' log P comes
+    // from the same kernel (sampling / evaluation instances below): one accumulation order on both sides of the ratio.
     SweepParams P2 = P;
     P2.tc_B = m.d_van2B;
     const long long tiles = (P.rows + V2_ROWS - 1) / V2_ROWS;
     RNNWF_COUNT_LAUNCH();
     e = van2_launch(P2, (int)std::max(1LL, std::min<long long>((tiles + 1) / 2, m.num_sms)), st);
     if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("two-tile vanilla sweep launch: ") + cudaGetErrorString(e));
+    return RNNWF_OK;
+  }
+  if (m.van2 && (P.mode == MODE_SAMPLE || P.mode == MODE_EVAL) && P.rows_dev == nullptr && std::getenv("RNNWF_NO_VAN2_SAMPLE") == nullptr) {
+    // vanilla 2D RNN, split precision, sampling / evaluation (with or without saved state): the same two-tile kernel, rows spread over
+    // both tile groups of every SM.  (The ring workspace was checked against s.grid CTAs: never launch more.)
+    SweepParams P2 = P;
+    P2.tc_B = m.d_van2B;
+    const long long tiles128 = (P.rows + V2_ROWS - 1) / V2_ROWS, groups = 2LL * std::max(1, s.grid);
+    long long vr = V2_ROWS;
+    if (tiles128 < groups) vr = std::max<long long>(8, std::min<long long>(V2_ROWS, ((tiles128 * V2_ROWS + groups - 1) / groups + 7) / 8 * 8));
+    P2.tile_rows = (int)vr;
+    const long long ntiles = (tiles128 * V2_ROWS + vr - 1) / vr;
+    RNNWF_COUNT_LAUNCH();
+    e = van2_launch(P2, (int)std::max(1LL, std::min<long long>((ntiles + 1) / 2, s.grid)), st);
+    if (e != cudaSuccess) return fail(RNNWF_ECUDA, std::string("two-tile vanilla sampling sweep launch: ") + cudaGetErrorString(e));
     return RNNWF_OK;
   }
   if (m.tc_enabled) {

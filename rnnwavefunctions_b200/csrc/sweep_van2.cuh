@@ -51,7 +51,7 @@ struct V2Smem {
     off_sym = o;   o += V2_GROUPS * ((Q * V2_ROWS + 15) & ~15);   // symbols of the group's tile, one byte per (site, row)
     off_part = o;  o += 2 * V2_GROUPS * V2_ROWS * 4;  // partial logit difference of the row's other unit half: [site parity][group][row]
     off_lp = o;    o += V2_GROUPS * V2_ROWS * 8;      // tile end: the upper half's share of the row's log P (double)
-    off_bar = o;   o += 32 + 2 * V2_GROUPS * 4 * 8;   // operand / accumulator barriers, then [site parity][group][lane quarter] pair barriers
+    off_bar = o;   o += 32 + 2 * (2 * V2_GROUPS * 4 * 8);   // operand / accumulator barriers, then [site parity][group][lane quarter] pair barriers: partial sums written; (sampling) symbol drawn
     off_tmem = o;  o += 16;
     total = o;
   }
@@ -83,8 +83,10 @@ __global__ void pack_van2_kernel(const float* __restrict__ Wh, const float* __re
 }
 
 // NU4: 4-unit chunks per thread (units per thread = 4 NU4 = nhp / 2)
-template <int NU4>
+template <int NU4, int MODE>
 __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepParams P) {
+  constexpr bool SAMPLE = (MODE == MODE_SAMPLE);        // symbols drawn site by site
+  constexpr bool SV = (MODE != MODE_CHILD);             // sampling / evaluation: own rows, row spreading, saved state, log P out
   constexpr int U2 = 4 * NU4;                         // units per thread
   constexpr int NHP = 2 * U2;                         // padded units
   constexpr int KS = NHP / 8;                         // K = 16 steps over [h_h | h_v]
@@ -100,12 +102,13 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
   uint64_t* const bar_op = bars + 0;                  // [2] group's operand written (256 arrivals)
   uint64_t* const bar_acc = bars + 2;                 // [2] group's accumulator complete (tcgen05.commit)
   uint64_t* const bar_pair = bars + 4;                // [site parity 2][group 2][quarter 4]: the partner warp's partial logits are written (32 arrivals)
+  uint64_t* const bar_symp = bars + 4 + 2 * V2_GROUPS * 4;   // same shape, sampling: the finishing warp has drawn the site's symbols (32 arrivals)
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int nh = P.nh;
 
   if (tid == 0) {
     for (int g = 0; g < V2_GROUPS; ++g) { mbar_init(bar_op + g, V2_GWARPS * 32); mbar_init(bar_acc + g, 1); }
-    for (int i = 0; i < 2 * V2_GROUPS * 4; ++i) mbar_init(bar_pair + i, 32);
+    for (int i = 0; i < 2 * V2_GROUPS * 4; ++i) { mbar_init(bar_pair + i, 32); mbar_init(bar_symp + i, 32); }
     fence_mbar_init();
   }
   if (warp == 0) tc_alloc(tmem_slot, 512);
@@ -149,10 +152,14 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const long long total_rows = (P.rows_dev != nullptr) ? (long long)(*P.rows_dev) : P.rows;
-  const long long ntiles = (total_rows + V2_ROWS - 1) / V2_ROWS;
+  // sampling: tile_rows live rows per 128-row MMA tile so that small batches cover all SMs, and the tiles cover the batch
+  // rounded up to 128 rows (the saved tile images' rows past the batch are written as zeros)
+  const int VR = SV ? P.tile_rows : V2_ROWS;
+  const long long rows_cover = SV ? ((total_rows + V2_ROWS - 1) / V2_ROWS) * V2_ROWS : total_rows;
+  const long long ntiles = (rows_cover + VR - 1) / VR;
   // tile sequence of group g of this CTA: tiles 2 (blockIdx.x + k gridDim.x) + g
   auto tile_of = [&](int g, long long k) -> long long { return 2 * ((long long)blockIdx.x + k * (long long)gridDim.x) + g; };
-  auto tile_q0 = [&](long long row0) -> int { return (P.par_hist != nullptr) ? (int)P.children[row0].ta : 0; };   // single-flip lists: first changed site
+  auto tile_q0 = [&](long long row0) -> int { return (!SV && P.par_hist != nullptr) ? (int)P.children[row0].ta : 0; };   // single-flip lists: first changed site
 
   if (warp < V2_GROUPS) {
     // ======================= MMA warp of group `warp` =======================
@@ -168,7 +175,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
     for (long long k = 0;; ++k) {
       const long long tile = tile_of(g, k);
       if (tile >= ntiles) break;
-      const int q0 = tile_q0(tile * V2_ROWS);
+      const int q0 = tile_q0(tile * VR);
       for (int q = q0; q < P.Q; ++q, ++n) {
         mbar_wait(bar_op + g, n & 1u);
         tc_fence_after();
@@ -222,20 +229,21 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
     for (long long k = 0;; ++k) {
       const long long tile = tile_of(g, k);
       if (tile >= ntiles) break;
-      const long long row0 = tile * V2_ROWS;
-      const int nrows = (int)((total_rows - row0 < (long long)V2_ROWS) ? (total_rows - row0) : (long long)V2_ROWS);
+      const long long row0 = tile * VR;
+      const int nrows = (int)((total_rows - row0 < (long long)VR) ? (total_rows - row0 > 0 ? total_rows - row0 : 0) : (long long)VR);
       const bool live = row < nrows;
+      const bool stores = SV && row < VR && row0 + row < rows_cover;   // owns a row of the saved tile images (zeros past the batch)
       const int q0 = tile_q0(row0);
       Child ch;
       ch.parent = 0; ch.ta = -1; ch.tb = -1; ch.coef = 0.f; ch.ka = ch.kb = 0; ch.pad = 0;
-      if (live) ch = P.children[row0 + row];
-      // ---- symbols of the tile (teacher forcing: the parent's configuration with the child's flip)
+      if (!SV && live) ch = P.children[row0 + row];
+      // ---- symbols of the tile (teacher forcing: the parent's configuration with the child's flip; sampling: drawn site by site)
       asm volatile("bar.sync %0, %1;" ::"r"(gbar), "n"(V2_GWARPS * 32) : "memory");      // the previous tile's symbols are no longer read
-      {
-        const int8_t* c = P.cfg_in + (long long)ch.parent * P.nsites;
+      if (!SAMPLE) {
+        const int8_t* c = P.cfg_in + (SV ? (live ? row0 + row : 0) : (long long)ch.parent) * P.nsites;
         for (int t = half; t < P.Q; t += 2) {
           int sy = 0;
-          if (live) { sy = c[stepS[t].z] & 1; if (t == ch.ta || t == ch.tb) sy ^= 1; }
+          if (live) { sy = c[stepS[t].z] & 1; if (!SV && (t == ch.ta || t == ch.tb)) sy ^= 1; }
           symS[t * V2_ROWS + row] = (uint8_t)sy;
         }
       }
@@ -294,6 +302,8 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
           const int nbo = carry_slot == 0 ? en.y : en.x;
           load_h(nbo, (en.w >> 8) & 0xff, ohi, olo);
         }
+        if (SAMPLE && q > q0 && half != (int)((n - 1u) & 1u))   // the previous site's symbol: drawn by the other thread of the row
+          mbar_wait(bar_symp + (((n - 1u) & 1u) * V2_GROUPS + g) * 4 + quarter, ((n - 1u) >> 1) & 1u);
         const int sl = (eq.x >= 0) ? (int)symS[eq.x * V2_ROWS + row] : 0;
         const int su = (eq.y >= 0) ? (int)symS[eq.y * V2_ROWS + row] : 0;
         const float* bv = biasS + ((((eq.x >= 0) ? 1 : 0) + ((eq.y >= 0) ? 2 : 0)) * 4 + sl * 2 + su) * V2_TABP + u0;
@@ -307,6 +317,14 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
         tc_wait_ld();
         // ---- new hidden state in place of the accumulators (no ordered instruction in this loop: loads and MUFUs pipeline freely)
         float lg = 0.f;
+        // sampling: this site's rows of the saved state (history FP32 [site][row][unit]; tile image, zeros past the batch)
+        float hsv[4];
+        float* const sv_h = (SV && live && P.sv_hist != nullptr) ? P.sv_hist + ((size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)) * NHP + u0 : nullptr;
+        const int hnc = ((NHP + 15) / 16) * 2;
+        float* const sv_i = (SV && stores && P.sv_himg != nullptr)
+                                ? P.sv_himg + ((size_t)q * (size_t)((P.sv_rows + V2_ROWS - 1) / V2_ROWS) + (size_t)((row0 + row) / V2_ROWS)) * (size_t)(32 * hnc * 32) +
+                                      (size_t)(((row0 + row) % V2_ROWS) >> 2) * hnc * 32 + ((row0 + row) & 3)
+                                : nullptr;
 #pragma unroll
         for (int c = 0; c < NU4; ++c) {
           const float4 b4 = *reinterpret_cast<const float4*>(bv + 4 * c);
@@ -320,7 +338,16 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
             const float hv = live ? ((x > 0.f) ? x : em) : 0.f;
             lg = fmaf(hv, ww[e], lg);
             d[c][e] = __float_as_uint(hv * HS);
+            if (SV) {
+              hsv[e] = hv;
+              // hidden-state tile image for the weight-gradient kernel (dw_tc.cuh), straight from the registers
+              if (sv_i != nullptr) { const int j = u0 + 4 * c + e; sv_i[(j >> 3) * 32 + (j & 7) * 4] = (P.sv_hist != nullptr) ? hv : 0.f; }
+            }
           }
+          if (SV && sv_h != nullptr) *reinterpret_cast<float4*>(sv_h + 4 * c) = make_float4(hsv[0], hsv[1], hsv[2], hsv[3]);
+        }
+        if (SV && sv_i != nullptr && half == 1) {       // the image covers the units rounded up to 16
+          for (int j = NHP; j < hnc * 8; ++j) sv_i[(j >> 3) * 32 + (j & 7) * 4] = 0.f;
         }
         // ---- hi / lo words of the new state: the ring image of this site (the same thread reads it back as a vertical
         // neighbour ~2 Nx sites later) and, all MMAs of this site having completed, the next site's operand
@@ -352,20 +379,61 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
             mbar_arrive(pb);
           } else {
             mbar_wait(pb, (n >> 1) & 1u);
-            if (live) {
-              // log p(sy) = -softplus(logit(other) - logit(sy))
-              const float dl = lg + ps[row] + headW[V2_N];
-              const float z = symS[q * V2_ROWS + row] ? -dl : dl;
-              const float y = -(fmaxf(z, 0.f) + logf(1.0f + expf(-fabsf(z)))) - lpc;
-              const float t = lps + y;
-              lpc = (t - lps) - y;
-              lps = t;
+            if (!SV) {
+              if (live) {
+                // log p(sy) = -softplus(logit(other) - logit(sy))
+                const float dl = lg + ps[row] + headW[V2_N];
+                const float z = symS[q * V2_ROWS + row] ? -dl : dl;
+                const float y = -(fmaxf(z, 0.f) + logf(1.0f + expf(-fabsf(z)))) - lpc;
+                const float t = lps + y;
+                lpc = (t - lps) - y;
+                lps = t;
+              }
+            } else {
+              // sampling: draw the site's symbol (inverse CDF on the supplied uniform or the Philox stream, as the generic
+              // kernel), the running log P in FP64 through shared memory (the two threads of a row alternate), the heads'
+              // outputs for the reverse sweep; then publish the symbol to the row's other thread
+              int sy = 0;
+              if (live) {
+                const float dl = lg + ps[row] + headW[V2_N];                 // logit(1) - logit(0)
+                const float ee = expf(-fabsf(dl)), rr = 1.0f / (1.0f + ee);
+                const float p1 = (dl >= 0.f) ? rr : ee * rr, p0 = (dl >= 0.f) ? ee * rr : rr;
+                float u = 0.f;
+                if (SAMPLE) u = (P.uniforms != nullptr) ? P.uniforms[(size_t)(row0 + row) * P.Tsym + q]
+                                                        : philox_uniform(P.seed, P.row_offset + (unsigned long long)(row0 + row), (uint32_t)q);
+                sy = SAMPLE ? (((double)p0 <= (double)u * ((double)p0 + (double)p1)) ? 1 : 0) : (int)symS[q * V2_ROWS + row];
+                const float z = sy ? -dl : dl;
+                const double run = ((q > q0) ? lpS[row] : 0.0) - (double)(fmaxf(z, 0.f) + logf(1.0f + expf(-fabsf(z))));
+                lpS[row] = run;
+                if (P.sv_cum != nullptr) {
+                  P.sv_cum[(size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)] = make_double2(run, 0.0);
+                  P.sv_head[(size_t)q * (size_t)P.sv_rows + (size_t)(row0 + row)] = make_float4(p0, p1, 0.f, 0.f);
+                }
+              }
+              if (SAMPLE) {
+                symS[q * V2_ROWS + row] = (uint8_t)sy;
+                mbar_arrive(bar_symp + (b * V2_GROUPS + g) * 4 + quarter);
+              }
             }
           }
         }
         eq = en;
       }
       // ---- tile result: E_loc(parent) += <sigma'|H|sigma> psi(sigma') / psi(sigma)
+      if (SV) {
+        asm volatile("bar.sync %0, %1;" ::"r"(gbar), "n"(V2_GWARPS * 32) : "memory");      // the last site's symbol and running log P are written
+        if (live) {
+          if (half == 0) {
+            if (P.out_logp != nullptr) P.out_logp[row0 + row] = lpS[row];
+            if (P.out_phase != nullptr) P.out_phase[row0 + row] = 0.0;
+          }
+          if (SAMPLE && P.cfg_out != nullptr) {
+            int8_t* c = P.cfg_out + (size_t)(row0 + row) * P.nsites;
+            for (int t = half; t < P.Q; t += 2) c[stepS[t].z] = (int8_t)symS[t * V2_ROWS + row];
+          }
+        }
+        continue;
+      }
       double rlogp = (double)lps - (double)lpc;            // this thread's share of the row's log P (the sites it finished)
       if (half == 1) lpS[row] = rlogp;
       asm volatile("bar.sync %0, %1;" ::"r"(gbar), "n"(V2_GWARPS * 32) : "memory");
