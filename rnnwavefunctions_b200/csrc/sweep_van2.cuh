@@ -1,5 +1,5 @@
-// Connected-configuration sweep of the vanilla 2D RNN (2DTFIM_2DRNN/MDRNNcell.py:51-66, RNNwavefunction.py:73-178) in the
-// split-precision regime, TWO 128-row tiles per CTA.
+// Sweeps of the vanilla 2D RNN (2DTFIM_2DRNN/MDRNNcell.py:51-66, RNNwavefunction.py:73-178) in the split-precision regime,
+// TWO 128-row tiles per CTA: connected configurations (MODE_CHILD), sampling (MODE_SAMPLE) and evaluation (MODE_EVAL).
 //
 // This cell has ONE tensor-core pass per lattice site (all units at once), so inside a tile the MMAs of a site and the
 // element-wise work on their result are strictly serial: the generic kernel (sweep_tc_kernel.cuh, CELLK = 1) keeps the tensor
@@ -23,6 +23,9 @@
 // prefix reuse from the parents' saved history exactly as in the generic kernel.
 // TMEM per group: accumulator 64 columns + operand hi 64 + lo 64 (2 x 192 of 512 columns).
 // 18 warps: 0, 1 issue the MMAs of group 0, 1; 2..17 element-wise (group, lane quarter = warp & 3, unit half).
+// Sampling / evaluation: tile_rows live rows per tile (small batches cover both groups of all SMs), the saved state of the
+// samples (history, weight-gradient tile image, running log P, heads' outputs) written from the registers; SAMPLE: the finishing
+// thread draws the symbol and signals the row's other thread through a second set of pair mbarriers.
 // Every wait is bounded and traps instead of hanging.  Measured history and stall analysis: profiles/r2d_summary.md.
 #pragma once
 #include "sweep_tc.cuh"
