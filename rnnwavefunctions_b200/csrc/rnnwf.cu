@@ -1575,7 +1575,7 @@ int rnnwf_describe(rnnwf_handle h, char* buf, int cap) {
                 "cell=%d nh=%d (padded %d) steps=%d symbols=%d slots=%d classes=%d | pipe=%s, tile=128 rows x %d col-groups "
                 "(TJ=%d NTU=%d WC=%d passes=%d), k-chunk=%d, ring=%d steps, params=%lld",
                 h->cell, h->nh, h->nhp, h->Q, h->Tsym, h->nslots, h->ncls_max,
-                h->van2 ? "tcgen05 split precision: FP16 hi+lo operands, 3 MMAs per K step, FP32 accumulate in TMEM (column passes of 112, double-buffered: reverse sweep); sampling, evaluation, connected configurations: two-tile sweep (N = 64, weights resident in shared memory)"
+                h->van2 ? "tcgen05 split precision: FP16 hi+lo operands, 3 MMAs per K step, FP32 accumulate in TMEM; sampling, evaluation, connected configurations: two-tile sweep (N = 64, weights resident in shared memory)"
                 : h->tc_split ? "tcgen05 split precision: FP16 hi+lo operands, 3 MMAs per K step, FP32 accumulate in TMEM (column passes of 112, double-buffered)"
                 : h->g1 ? "FFMA fp32, dedicated 1D-GRU kernels: one launch per sweep, weights resident in shared memory"
                 : h->tc_enabled ? "tcgen05 FP16 operands, FP32 accumulate in TMEM (column passes of 112, double-buffered)"
