@@ -278,6 +278,30 @@ int build_model(rnnwf_model& m) {
     for (int k = 0; k < MAX_SLOTS; ++k)
       if (m.steps[q].nbr[k] >= 0) look = std::max(look, q - m.steps[q].nbr[k]);
   m.ring_len = std::min(m.Q, look + 1);
+  // History-ring slots by live range (used by the tensor-core sweeps; sweep_tc_kernel.cuh, sweep_van2.cuh).  A step's image
+  // is read back as a neighbour of later steps; every such load is issued no later than the top of iteration t - 1, before
+  // iteration t - 1 stores its own image, so step q may take the slot of any step whose last reader is <= q + 1: on the
+  // zigzag path one slot per lattice column instead of the whole look-back window.  pad1: readers = all neighbours (generic
+  // kernel); pad2: readers = the neighbour that is not the step right before (two-tile kernel: that one stays in registers).
+  for (int which = 0; which < 2; ++which) {
+    std::vector<int> last(m.Q, -1), owner(m.ring_len, -1), slot(m.Q, 0);
+    for (int t = 1; t < m.Q; ++t) {
+      if (which == 0) {
+        for (int k = 0; k < MAX_SLOTS; ++k) { const int nb = m.steps[t].nbr[k]; if (nb >= 0) last[nb] = std::max(last[nb], t); }
+      } else {
+        const int nb = (m.steps[t].nbr[0] == t - 1) ? m.steps[t].nbr[1] : m.steps[t].nbr[0];
+        if (nb >= 0) last[nb] = std::max(last[nb], t);
+      }
+    }
+    bool ok = true;
+    for (int q = 0; q < m.Q && ok; ++q) {
+      int sl = 0;
+      while (sl < m.ring_len && owner[sl] >= 0 && last[owner[sl]] > q + 1) ++sl;
+      if (sl >= m.ring_len) { ok = false; break; }
+      owner[sl] = q; slot[q] = sl;
+    }
+    for (int q = 0; q < m.Q; ++q) (which == 0 ? m.steps[q].pad1 : m.steps[q].pad2) = ok ? slot[q] : q % m.ring_len;
+  }
 
   // tile shape: TJ in {4,5} for the three-gate cells, 4 otherwise; WC <= 5 warp columns
   int best_tj = 4, best_wc = 1;

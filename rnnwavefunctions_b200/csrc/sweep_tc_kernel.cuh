@@ -107,40 +107,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) sweep_tc_kernel(const SweepPara
     const int nb0 = m->nbr[0], nb1 = m->nbr[1];
     const int carry = (nb0 == i - 1) ? 0 : 1;
     const int other = (carry == 0) ? nb1 : nb0;
-    stepT[i] = make_int4((nb0 & 0xffff) | (nb1 << 16), (other & 0xffff) | (carry << 16),
-                         (int)((uint32_t)(i % P.ring_len) * RSLOT), other >= 0 ? (int)((uint32_t)(other % P.ring_len) * RSLOT) : 0);
-  }
-  if (!(P.debug_flags & 64)) {
-    // Ring slots by live range instead of step number.  A step's image is read back as the older-neighbour half of a later
-    // step t, and that load is issued no later than the top of iteration t - 1 (end of t - 2 outside the split regime),
-    // i.e. before iteration t - 1 stores its own image: step q may take the slot of any step whose last reader is
-    // <= q + 1.  On the zigzag path that is one slot per lattice column instead of the whole look-back window -- half
-    // the ring footprint (C4: 157 -> 86 MB over all CTAs, inside the L2).  (Readers are counted over both neighbours.)
-    __syncthreads();
-    for (int q = tid; q < P.Q; q += TC_THREADS) {
-      int last = -1;
-      for (int t = q + 1; t < P.Q && t <= q + P.ring_len; ++t)
-        if (metaS[t].x == q || metaS[t].y == q) last = t;
-      metaS[q].w = (short)last;
-    }
-    __syncthreads();
-    if (tid == 0) {
-      int* const owner = reinterpret_cast<int*>(symS);      // (scratch: the symbol table is written per tile, later)
-      const int nslot = P.ring_len < P.Tsym * 4 ? P.ring_len : P.Tsym * 4;
-      for (int sl = 0; sl < nslot; ++sl) owner[sl] = -1;
-      for (int q = 0; q < P.Q; ++q) {
-        int sl = 0;
-        while (sl < nslot && owner[sl] >= 0 && metaS[owner[sl]].w > q + 1) ++sl;
-        if (sl >= nslot) { asm volatile("trap;"); }
-        owner[sl] = q;
-        stepT[q].z = (int)((uint32_t)sl * RSLOT);
-      }
-    }
-    __syncthreads();
-    for (int q = tid; q < P.Q; q += TC_THREADS) {
-      const int other = (int)(short)(stepT[q].y & 0xffff);
-      stepT[q].w = other >= 0 ? stepT[other].z : 0;
-    }
+    // Ring slots by live range instead of step number (assigned once on the host, build_model: StepMeta::pad1): an image is
+    // read back by the step below it in the same lattice column, and that load is issued before the step in between stores
+    // (top of iteration t - 1 in the split regime, end of t - 2 otherwise) -- one slot per lattice column on the zigzag path,
+    // half the ring footprint (C4: 157 -> 86 MB over all CTAs, inside the L2).  RNNWF_TC_DEBUG bit 64: slot = step mod ring_len.
+    const bool modslots = (P.debug_flags & 64) != 0;
+    const uint32_t sl_own = modslots ? (uint32_t)(i % P.ring_len) : (uint32_t)m->pad1;
+    const uint32_t sl_other = other < 0 ? 0u : (modslots ? (uint32_t)(other % P.ring_len) : (uint32_t)P.steps[other].pad1);
+    stepT[i] = make_int4((nb0 & 0xffff) | (nb1 << 16), (other & 0xffff) | (carry << 16), (int)(sl_own * RSLOT), (int)(sl_other * RSLOT));
   }
   tc_fence_before();
   __syncthreads();

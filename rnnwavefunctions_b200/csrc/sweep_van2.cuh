@@ -125,29 +125,15 @@ __global__ void __launch_bounds__(V2_THREADS, 1) sweep_van2_kernel(const SweepPa
   // two-class softmax: only the difference of the logits enters log p
   for (int i = tid; i <= V2_N; i += V2_THREADS)
     headW[i] = (i == V2_N) ? P.head_b[1] - P.head_b[0] : ((i < nh) ? P.head_w[i * P.ND + 1] - P.head_w[i * P.ND] : 0.f);
-  for (int i = tid; i < P.Q; i += V2_THREADS) stepS[i] = make_short4(P.steps[i].nbr[0], P.steps[i].nbr[1], P.steps[i].site, 0);
-  __syncthreads();
-  if (tid == 0) {
-    // Ring slots.  A site's state is read back once, as the older neighbour of a later site t (the other neighbour of t
-    // is site t - 1, handed over in registers); that read is issued at the top of iteration t - 1, before iteration
-    // t - 1 stores its own state.  So site q may take the slot of any site whose reader t <= q + 1: on the zigzag path
-    // one slot per lattice column, half the look-back window.  w = own slot | slot of the older neighbour << 8.
-    int16_t* const last = reinterpret_cast<int16_t*>(smem + L.off_sym);       // (scratch: the symbols are written later)
-    int16_t* const owner = last + P.Q;
-    for (int q = 0; q < P.Q; ++q) last[q] = -1;
-    for (int t = 1; t < P.Q; ++t) {
-      const int nbo = (stepS[t].x == t - 1) ? stepS[t].y : stepS[t].x;
-      if (nbo >= 0 && last[nbo] < t) last[nbo] = (int16_t)t;
-    }
-    for (int sl = 0; sl < P.ring_len; ++sl) owner[sl] = -1;
-    for (int q = 0; q < P.Q; ++q) {
-      int sl = 0;
-      while (sl < P.ring_len && owner[sl] >= 0 && last[owner[sl]] > q + 1) ++sl;
-      if (sl >= P.ring_len) { asm volatile("trap;"); }
-      owner[sl] = (int16_t)q;
-      const int nbo = (q > 0) ? ((stepS[q].x == q - 1) ? stepS[q].y : stepS[q].x) : -1;
-      stepS[q].w = (short)(sl | ((nbo >= 0 ? (stepS[nbo].w & 0xff) : 0) << 8));
-    }
+  // Ring slots (assigned once on the host by live range, build_model: StepMeta::pad2).  A site's state is read back once,
+  // as the older neighbour of a later site t (the other neighbour of t is site t - 1, handed over in registers); that read is
+  // issued at the top of iteration t - 1, before iteration t - 1 stores its own state, so site q may take the slot of any
+  // site whose reader t <= q + 1: on the zigzag path one slot per lattice column, half the look-back window.
+  // w = own slot | slot of the older neighbour << 8.
+  for (int i = tid; i < P.Q; i += V2_THREADS) {
+    const StepMeta* m = P.steps + i;
+    const int nbo = (i > 0) ? ((m->nbr[0] == i - 1) ? m->nbr[1] : m->nbr[0]) : -1;
+    stepS[i] = make_short4(m->nbr[0], m->nbr[1], m->site, (short)((m->pad2 & 0xff) | ((nbo >= 0 ? (P.steps[nbo].pad2 & 0xff) : 0) << 8)));
   }
   fence_proxy_async_smem();                           // the weight image is read by the tensor core (async proxy)
   tc_fence_before();
