@@ -60,7 +60,7 @@ struct V2Smem {
   }
 };
 inline bool v2_supported(int nh, int nhp, int Q, int complex_head, int u1) {
-  return !complex_head && !u1 && nhp <= V2_N && (nhp == 32 || nhp == 48 || nhp == 56 || nhp == 64) && nh <= nhp && V2Smem(nhp, Q).total <= 200 * 1024;
+  return !complex_head && !u1 && nhp >= 8 && nhp <= V2_N && nhp % 8 == 0 && nh <= nhp && V2Smem(nhp, Q).total <= 200 * 1024;
 }
 // ring bytes per CTA: [group][slot ring_len][unit half 2][chunk][row 128] 16-byte words = 4 bytes per (row, unit)
 __host__ __device__ inline long long v2_ring_bytes(int ring_len, int nhp) { return (long long)V2_GROUPS * ring_len * V2_ROWS * nhp * 4; }

@@ -8,7 +8,11 @@ using V2Kernel = void (*)(const SweepParams);
 V2Kernel v2_kernel(int nhp, int mode) {
 #define V2_PICK(N) (mode == MODE_SAMPLE ? sweep_van2_kernel<N, MODE_SAMPLE> : (mode == MODE_EVAL ? sweep_van2_kernel<N, MODE_EVAL> : sweep_van2_kernel<N, MODE_CHILD>))
   switch (nhp) {
+    case 8: return V2_PICK(1);
+    case 16: return V2_PICK(2);
+    case 24: return V2_PICK(3);
     case 32: return V2_PICK(4);
+    case 40: return V2_PICK(5);
     case 48: return V2_PICK(6);
     case 56: return V2_PICK(7);
     case 64: return V2_PICK(8);

@@ -2,7 +2,7 @@
 (tc, tc3) against the FFMA regime on the same weights -- sampling with given uniforms, teacher-forced log psi, E_loc with
 prefix reuse (and, for the vanilla cell, without it), gradient.  Prints one line per case; exits non-zero at the end if
 any case violated its bound.   python tools/fuzz_regimes.py [cases] [seed] [cell: tensgru | tens | vanilla | gru4]
-(with `vanilla` the widths are drawn from 25..64, the range of the two-tile sweep of sweep_van2.cuh)"""
+(with `vanilla` the widths are drawn from 5..64, the range of the two-tile sweep of sweep_van2.cuh)"""
 import os, sys
 import numpy as np
 import torch
@@ -25,7 +25,7 @@ for case in range(ncases):
         nx, ny = min(nx, 4), min(ny, 4)
     nh = int(rng.randint(5, 105 if name != "gru4" else 200))
     if only == "vanilla":
-        nh = int(rng.randint(25, 65))
+        nh = int(rng.randint(5, 65))
     ns = int(rng.choice([1, 7, 64, 129, 300, 1000, 2500]))
     u1 = cplx and (nx * ny) % 2 == 0
     kw = dict(num_units=nh, complex_head=cplx, u1=u1, seed=int(rng.randint(1 << 30)))
